@@ -1,0 +1,20 @@
+"""hivemall_b200 -- B200-native (sm_100a CUDA) implementation of Hivemall's data-parallel
+training hot path (train_classifier / train_regressor / train_fm, mhash), behind a C-ABI.
+
+Only the path is here: csrc/ (kernels + C-ABI), udtf.py (host mirror of the UDTF
+interface), mix.py (model averaging across GPUs), synth.py (synthetic inputs for
+bench/tests).  See DESIGN.md.  PARITY WITH THE REFERENCE IS UNPINNED: the mounted
+reference holds no code.
+"""
+from ._lib import HivemallError, UDFArgumentError, LIB_PATH  # noqa: F401
+from .udtf import (  # noqa: F401
+    UDTF, TrainClassifierUDTF, TrainRegressorUDTF, FactorizationMachineUDTF,
+    train_classifier, train_regressor, train_fm, mhash, feature_hashing, parse_options,
+    host_alloc, host_free, DEFAULT_NUM_FEATURES, DEFAULT_HASH_SEED,
+)
+
+__all__ = [
+    "UDTF", "TrainClassifierUDTF", "TrainRegressorUDTF", "FactorizationMachineUDTF",
+    "train_classifier", "train_regressor", "train_fm", "mhash", "feature_hashing",
+    "parse_options", "host_alloc", "host_free", "HivemallError", "UDFArgumentError",
+]

@@ -1,0 +1,123 @@
+// hm_internal.h -- shared declarations of the hivemall_b200 CUDA library (not installed).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <string>
+#include <vector>
+#include "../../include/hivemall_b200.h"
+
+namespace hm {
+
+// ---- errors -----------------------------------------------------------------
+void set_error(const char *fmt, ...);
+#define HM_FAIL(code, ...) do { ::hm::set_error(__VA_ARGS__); return (code); } while (0)
+#define HM_CUDA(expr) do { cudaError_t e_ = (expr); if (e_ != cudaSuccess) { \
+    ::hm::set_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(e_), __FILE__, __LINE__); \
+    return e_ == cudaErrorMemoryAllocation ? HM_ERR_OOM : HM_ERR_CUDA; } } while (0)
+#define HM_TRY(expr) do { hm_status s_ = (expr); if (s_ != HM_OK) return s_; } while (0)
+
+// ---- kernel ids for launch accounting -----------------------------------------
+enum KernelId {
+    K_HASH = 0, K_SEG_PREP, K_SORT_HIST, K_SORT_SCAN, K_SORT_SCATTER,
+    K_LIN_FORWARD, K_LIN_UPDATE, K_FM_FORWARD, K_FM_UPDATE, K_PREDICT,
+    K_EXPORT, K_MISC, K_NUM_KERNELS
+};
+extern const char *const kKernelNames[K_NUM_KERNELS];
+
+// Launch bookkeeping: counts every launch; when profiling is on, brackets each
+// launch with events on the launching stream and accumulates per-kernel time.
+struct Launcher {
+    cudaStream_t stream = nullptr;
+    bool profiling = false;
+    int64_t launches = 0;
+    int64_t count[K_NUM_KERNELS] = {0};
+    double ms[K_NUM_KERNELS] = {0};
+    double bytes[K_NUM_KERNELS] = {0};
+    struct Pending { int id; cudaEvent_t a, b; };
+    std::vector<Pending> pending;
+    std::vector<cudaEvent_t> pool;
+
+    void begin(int id, double alg_bytes);
+    void end(int id);
+    void drain();      // resolve pending event pairs into ms[] (synchronises)
+    void release();
+};
+
+#define HM_LAUNCH(L, id, alg_bytes, ...) do { (L).begin((id), (alg_bytes)); __VA_ARGS__; (L).end(id); } while (0)
+
+constexpr int kNumSMs = 148;
+
+// ---- segmented radix sort (hm_sort.cu) ----------------------------------------
+constexpr int kMaxSegs = 256;          // mini-batches sorted per launch
+constexpr int kSortTile = 4096;        // elements per sort tile
+struct SortScratch {
+    // device
+    uint32_t *key[2] = {nullptr, nullptr};
+    uint32_t *pay[2] = {nullptr, nullptr};
+    uint32_t *tile_hist = nullptr;     // [seg][digit][tile_in_seg]
+    uint32_t *row_sum = nullptr;       // [seg*256 + digit] (+1)
+    uint32_t *seg_off = nullptr;       // [kMaxSegs+1] element offset of each mini-batch in the block
+    uint32_t *seg_tile_off = nullptr;  // [kMaxSegs+1]
+    int64_t cap_elems = 0;
+    int64_t cap_tiles = 0;
+};
+hm_status sort_scratch_reserve(SortScratch &s, int64_t elems);
+void sort_scratch_free(SortScratch &s);
+// Fill seg_off / seg_tile_off for rows [row0, row0+n_rows) split every `mini_batch` rows.
+hm_status launch_seg_prep(Launcher &L, SortScratch &s, const int64_t *d_rowptr, int64_t row0,
+                          int64_t n_rows, int32_t mini_batch, int n_segs);
+// Stable sort of each segment by the low `key_bits` bits of d_feature[base + e].
+// Result: s.key[*out_buf], s.pay[*out_buf] hold (feature, e) sorted per segment.
+hm_status launch_segmented_sort(Launcher &L, SortScratch &s, const uint32_t *d_feature_block,
+                                int64_t n_elems, int n_segs, int key_bits, int *out_buf);
+
+// ---- hashing (hm_hash.cu) -----------------------------------------------------
+hm_status launch_mhash(Launcher &L, const uint8_t *d_bytes, const int64_t *d_offsets, int64_t n,
+                       uint32_t seed, int32_t num_features, int32_t *d_out);
+hm_status launch_feature_hashing(Launcher &L, const uint8_t *d_bytes, const int64_t *d_offsets, int64_t n,
+                                 uint32_t seed, int32_t num_features, int32_t *d_index, float *d_value);
+
+// ---- linear learner kernels (hm_linear.cu) ------------------------------------
+struct StepScalars {      // per mini-batch scalars computed on the host in double
+    float eta;
+    float adam_alpha;
+    double inv_denom_unused;
+    int32_t n_rows;       // rows in this mini-batch
+};
+struct LinearArgs {
+    hm_config cfg;
+    float *w;
+    float *state;         // state_width floats per feature, interleaved
+    int state_width;
+};
+// margins/dloss for rows [row0, row0+n) of the chunk; also writes contrib[e] = dloss*x
+hm_status launch_linear_forward(Launcher &L, const LinearArgs &a, const int64_t *d_rowptr, int64_t row0,
+                                int32_t n_rows, int64_t block_row0, const uint32_t *d_feature,
+                                const float *d_value, const float *d_label, float *d_margin,
+                                float *d_dloss, float *d_contrib, uint32_t *d_bad, int64_t nnz_hint);
+// reduce-by-feature over the sorted segment `seg` and apply the optimizer
+struct UpdateScratch {
+    void *boundary = nullptr;     // per-CTA open-segment summaries
+    uint32_t *done_counter = nullptr;
+    int grid = 0;
+};
+hm_status update_scratch_reserve(UpdateScratch &u);
+void update_scratch_free(UpdateScratch &u);
+hm_status launch_linear_update(Launcher &L, const LinearArgs &a, const StepScalars &sc, UpdateScratch &us,
+                               const uint32_t *d_sorted_key, const uint32_t *d_sorted_pay,
+                               const uint32_t *d_seg_off, int seg, const float *d_contrib, int64_t nnz_hint);
+hm_status launch_predict_linear(Launcher &L, const float *w, int64_t dims, int64_t n_rows, const int64_t *d_rowptr,
+                                const uint32_t *d_feature, const float *d_value, float *d_out, uint32_t *d_bad);
+// model table: features with w != 0, ascending
+struct ExportScratch { uint32_t *counts = nullptr; int64_t cap = 0; };
+hm_status launch_export_count(Launcher &L, ExportScratch &es, const float *w, const uint8_t *touched,
+                              int64_t dims, int64_t *d_total);
+hm_status launch_export_write(Launcher &L, ExportScratch &es, const float *w, const uint8_t *touched,
+                              int64_t dims, int32_t *d_feature, float *d_weight);
+hm_status launch_scale(Launcher &L, float *p, int64_t n, float scale);
+hm_status launch_fill_u32(Launcher &L, uint32_t *p, int64_t n, uint32_t v);
+
+// ---- options (hm_options.cpp) -------------------------------------------------
+hm_status parse_options(const char *function_name, const char *options, hm_config *out);
+
+}  // namespace hm

@@ -1,0 +1,889 @@
+// hm_learner.cu -- host side of the UDTF lifecycle and the extern "C" boundary.
+//
+// Mirrors the Hive UDTF contract that BASELINE.json's north_star fixes for this path:
+// initialize(options) -> process(row)* -> close() -> forward(model rows).  The reference
+// mount has no source to cite (README.md:20-22).  What happens between process() and the
+// kernels:
+//
+//   host CSR slice --H2D (copy stream; truly async when the caller used hm_host_alloc)--> chunk
+//   chunk = [rows left over from the previous slice | new rows]          (device resident)
+//   full mini-batches of the chunk are grouped into blocks (<= kMaxSegs mini-batches,
+//   <= kBlockElemCap elements); per block: seg_prep + segmented sort (once, data only), then
+//   per mini-batch: linear_forward + linear_update on the compute stream.
+//   Rows that do not fill a mini-batch wait at the end of the chunk for the next slice or close().
+//
+// There is no CPU compute path: every entry point that trains or predicts needs a device.
+#include "hm_internal.h"
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <new>
+
+namespace hm {
+
+const char *last_error_cstr();
+
+// ---- Launcher --------------------------------------------------------------------
+
+void Launcher::begin(int id, double alg_bytes)
+{
+    launches++;
+    count[id]++;
+    bytes[id] += alg_bytes;
+    if (!profiling) return;
+    Pending p;
+    p.id = id;
+    for (cudaEvent_t *e : {&p.a, &p.b}) {
+        if (!pool.empty()) { *e = pool.back(); pool.pop_back(); }
+        else cudaEventCreate(e);
+    }
+    cudaEventRecord(p.a, stream);
+    pending.push_back(p);
+}
+
+void Launcher::end(int)
+{
+    if (!profiling) return;
+    cudaEventRecord(pending.back().b, stream);
+    if (pending.size() >= 4096) drain();
+}
+
+void Launcher::drain()
+{
+    if (pending.empty()) return;
+    cudaStreamSynchronize(stream);
+    for (const Pending &p : pending) {
+        float t = 0.f;
+        if (cudaEventElapsedTime(&t, p.a, p.b) == cudaSuccess) ms[p.id] += (double)t;
+        pool.push_back(p.a);
+        pool.push_back(p.b);
+    }
+    pending.clear();
+}
+
+void Launcher::release()
+{
+    drain();
+    for (cudaEvent_t e : pool) cudaEventDestroy(e);
+    pool.clear();
+}
+
+namespace {
+
+constexpr int64_t kBlockElemCap = (int64_t)1 << 26;   // elements sorted per launch set
+constexpr int64_t kSliceRows = (int64_t)1 << 21;      // host rows copied per H2D slice
+
+struct DevBuf {
+    void *p = nullptr;
+    size_t cap = 0;
+    hm_status reserve(size_t bytes)
+    {
+        if (bytes <= cap) return HM_OK;
+        if (p) cudaFree(p);   // cudaFree waits for work that may still use the old buffer
+        p = nullptr; cap = 0;
+        size_t want = bytes + bytes / 4 + 256;
+        cudaError_t e = cudaMalloc(&p, want);
+        if (e != cudaSuccess) { cudaGetLastError(); want = bytes; e = cudaMalloc(&p, want); }
+        if (e != cudaSuccess) { cudaGetLastError(); p = nullptr; HM_FAIL(HM_ERR_OOM, "cudaMalloc(%zu bytes) failed: %s", bytes, cudaGetErrorString(e)); }
+        cap = want;
+        return HM_OK;
+    }
+    void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+    template <class T> T *as() const { return reinterpret_cast<T *>(p); }
+};
+
+// A run of rows resident on the device.  Owned chunks hold copies of host data (rowptr is
+// 0-based inside the chunk); views alias caller memory (hm_udtf_process_device).
+struct Chunk {
+    bool view = false;
+    int64_t rows = 0;                   // rows whose mini-batches are listed in mb_abs
+    DevBuf rowptr, feat, val, label;    // owned storage
+    const int64_t *v_rowptr = nullptr;  // view storage
+    const uint32_t *v_feat = nullptr;
+    const float *v_val = nullptr, *v_label = nullptr;
+    std::vector<int64_t> mb_abs;        // rowptr value at every mini-batch boundary of rows [0, rows)
+    cudaEvent_t free_ev = nullptr;      // recorded on the compute stream when the chunk may be overwritten
+    const int64_t *rp() const { return view ? v_rowptr : rowptr.as<int64_t>(); }
+    const uint32_t *ft() const { return view ? v_feat : feat.as<uint32_t>(); }
+    const float *vl() const { return view ? v_val : val.as<float>(); }
+    const float *lb() const { return view ? v_label : label.as<float>(); }
+    void release()
+    {
+        rowptr.release(); feat.release(); val.release(); label.release();
+        if (free_ev) cudaEventDestroy(free_ev);
+        free_ev = nullptr;
+    }
+};
+
+__global__ void gather_rowptr_kernel(const int64_t *__restrict__ rowptr, int64_t n_rows, int32_t step,
+                                     int64_t n_out, int64_t *__restrict__ out)
+{
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_out; i += (int64_t)gridDim.x * blockDim.x) {
+        int64_t r = i * step;
+        if (r > n_rows) r = n_rows;
+        out[i] = rowptr[r];
+    }
+}
+
+int bits_for(int64_t dims)
+{
+    int b = 0;
+    while (((int64_t)1 << b) < dims) b++;
+    return b < 1 ? 1 : b;
+}
+
+}  // namespace
+}  // namespace hm
+
+using namespace hm;
+
+struct hm_udtf {
+    hm_config cfg;
+    int device = 0;
+    Launcher L;
+    cudaStream_t compute = nullptr, copy = nullptr;
+    cudaEvent_t copied_ev = nullptr, stage_ev[2] = {nullptr, nullptr};
+    // model replica
+    float *w = nullptr, *state = nullptr;
+    int state_width = 0;
+    int64_t t = 0;
+    // scratch
+    SortScratch sort;
+    UpdateScratch upd;
+    ExportScratch exp;
+    DevBuf margin, dloss, contrib, mb_gather, exp_feat, exp_weight, tmp_a, tmp_b, tmp_c, tmp_d;
+    uint32_t *d_bad = nullptr;
+    int64_t *d_total = nullptr;
+    // data
+    std::vector<Chunk *> retained;   // pass-1 chunks kept for -iters > 1
+    std::vector<Chunk *> pool;       // recycled chunk storage
+    Chunk *tail = nullptr;           // chunk whose last rows do not fill a mini-batch yet
+    int64_t tail_row0 = 0;           // first untrained row of `tail`
+    std::vector<int64_t> tail_rp;    // host copy of the untrained rows' rowptr, 0-based (size tail_rows+1)
+    int64_t *h_stage[2] = {nullptr, nullptr};
+    int64_t h_stage_cap[2] = {0, 0};
+    int stage_turn = 0;
+    int64_t *h_small = nullptr;      // pinned scratch for small D2H reads
+    int64_t h_small_cap = 0;
+    bool device_rows_short = false;  // a process_device call ended on a short mini-batch
+    hm_stats stats;
+    bool closed = false;
+    int64_t model_rows = -1;
+
+    int64_t tail_rows() const { return tail_rp.empty() ? 0 : (int64_t)tail_rp.size() - 1; }
+};
+
+namespace {
+
+struct DeviceGuard {
+    int prev = -1;
+    bool ok = true;
+    explicit DeviceGuard(int dev)
+    {
+        if (cudaGetDevice(&prev) != cudaSuccess) { prev = -1; ok = false; cudaGetLastError(); }
+        if (cudaSetDevice(dev) != cudaSuccess) { ok = false; cudaGetLastError(); }
+    }
+    ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+};
+
+hm_status ensure_small(hm_udtf *u, int64_t n)
+{
+    if (n <= u->h_small_cap) return HM_OK;
+    if (u->h_small) cudaFreeHost(u->h_small);
+    u->h_small = nullptr; u->h_small_cap = 0;
+    HM_CUDA(cudaMallocHost(&u->h_small, (size_t)(n + 64) * sizeof(int64_t)));
+    u->h_small_cap = n + 64;
+    return HM_OK;
+}
+
+float eta_at(const hm_config &c, int64_t t)
+{
+    switch (c.eta_sched) {
+    case HM_ETA_INVERSE: return (float)((double)c.eta0 / std::pow((double)t, (double)c.power_t));
+    case HM_ETA_SIMPLE: return (float)((double)c.eta0 / (1.0 + (double)t / c.total_steps));
+    default: return c.eta0;
+    }
+}
+
+float adam_alpha_at(const hm_config &c, float eta, int64_t t)
+{
+    const double b1 = std::pow((double)c.beta1, (double)t), b2 = std::pow((double)c.beta2, (double)t);
+    return (float)((double)eta * std::sqrt(1.0 - b2) / (1.0 - b1));
+}
+
+// Train rows [row0, row0+n_rows) of a chunk.  mb_abs[i] is the chunk rowptr value at
+// row0 + min(i*B, n_rows), i = 0..n_mb.
+hm_status train_rows(hm_udtf *u, const Chunk &c, int64_t row0, int64_t n_rows, const int64_t *mb_abs, int64_t n_mb)
+{
+    if (n_rows <= 0) return HM_OK;
+    const int32_t B = u->cfg.mini_batch;
+    const int key_bits = bits_for(u->cfg.dims);
+    LinearArgs a;
+    a.cfg = u->cfg; a.w = u->w; a.state = u->state; a.state_width = u->state_width;
+    int64_t m0 = 0;
+    while (m0 < n_mb) {
+        // greedy block: <= kMaxSegs mini-batches and <= kBlockElemCap elements (at least one)
+        int64_t m1 = m0 + 1;
+        while (m1 < n_mb && m1 - m0 < kMaxSegs && mb_abs[m1 + 1] - mb_abs[m0] <= kBlockElemCap) m1++;
+        const int n_segs = (int)(m1 - m0);
+        const int64_t b_row0 = row0 + m0 * B;
+        const int64_t b_rows = std::min<int64_t>(n_rows - m0 * B, (int64_t)n_segs * B);
+        const int64_t b_nnz = mb_abs[m1] - mb_abs[m0];
+        if (b_nnz >= ((int64_t)1 << 31))
+            HM_FAIL(HM_ERR_UNSUPPORTED, "a mini-batch of %lld elements exceeds the 2^31 block limit", (long long)b_nnz);
+        HM_TRY(sort_scratch_reserve(u->sort, b_nnz));
+        HM_TRY(u->margin.reserve((size_t)b_rows * sizeof(float)));
+        HM_TRY(u->dloss.reserve((size_t)b_rows * sizeof(float)));
+        HM_TRY(u->contrib.reserve((size_t)std::max<int64_t>(b_nnz, 1) * sizeof(float)));
+        HM_TRY(launch_seg_prep(u->L, u->sort, c.rp(), b_row0, b_rows, B, n_segs));
+        int buf = 0;
+        HM_TRY(launch_segmented_sort(u->L, u->sort, c.ft() + mb_abs[m0], b_nnz, n_segs, key_bits, &buf));
+        for (int s = 0; s < n_segs; s++) {
+            const int64_t mrow0 = b_row0 + (int64_t)s * B;
+            const int32_t mrows = (int32_t)std::min<int64_t>(B, row0 + n_rows - mrow0);
+            const int64_t mnnz = mb_abs[m0 + s + 1] - mb_abs[m0 + s];
+            u->t += 1;
+            StepScalars sc;
+            sc.eta = eta_at(u->cfg, u->t);
+            sc.adam_alpha = u->cfg.opt == HM_OPT_ADAM ? adam_alpha_at(u->cfg, sc.eta, u->t) : 0.f;
+            sc.inv_denom_unused = 0;
+            sc.n_rows = mrows;
+            HM_TRY(launch_linear_forward(u->L, a, c.rp(), mrow0, mrows, b_row0, c.ft(), c.vl(), c.lb(),
+                                         u->margin.as<float>(), u->dloss.as<float>(), u->contrib.as<float>(),
+                                         u->d_bad, mnnz));
+            HM_TRY(launch_linear_update(u->L, a, sc, u->upd, u->sort.key[buf], u->sort.pay[buf], u->sort.seg_off, s,
+                                        u->contrib.as<float>(), mnnz));
+            u->stats.mini_batches++;
+        }
+        u->stats.rows += b_rows;
+        u->stats.nnz += b_nnz;
+        m0 = m1;
+    }
+    return HM_OK;
+}
+
+Chunk *acquire_chunk(hm_udtf *u)
+{
+    if (!u->pool.empty()) {
+        Chunk *c = u->pool.back();
+        u->pool.pop_back();
+        return c;
+    }
+    return new (std::nothrow) Chunk();
+}
+
+// The compute stream is (or will be, in stream order) done with `c`: recycle or retain it.
+hm_status retire_chunk(hm_udtf *u, Chunk *c, bool retain)
+{
+    if (retain) { u->retained.push_back(c); return HM_OK; }
+    if (c->view) { delete c; return HM_OK; }
+    if (!c->free_ev) HM_CUDA(cudaEventCreateWithFlags(&c->free_ev, cudaEventDisableTiming));
+    HM_CUDA(cudaEventRecord(c->free_ev, u->compute));
+    c->rows = 0;
+    c->mb_abs.clear();
+    u->pool.push_back(c);
+    return HM_OK;
+}
+
+// One slice of host rows: build [tail | slice] on the device, train the full mini-batches.
+hm_status process_slice(hm_udtf *u, int64_t n, const int64_t *rowptr, const int32_t *feature, const float *value,
+                        const float *label)
+{
+    const int32_t B = u->cfg.mini_batch;
+    const int64_t t_rows = u->tail_rows();
+    const int64_t t_nnz = t_rows ? u->tail_rp.back() : 0;
+    const int64_t nnz = rowptr[n] - rowptr[0];
+    const int64_t rows = t_rows + n, elems = t_nnz + nnz;
+    if (nnz < 0) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "rowptr is not non-decreasing");
+
+    Chunk *c = acquire_chunk(u);
+    if (!c) HM_FAIL(HM_ERR_OOM, "out of host memory");
+    // A recycled chunk may still be read by queued compute work: make the copy stream wait for it.
+    if (c->free_ev) HM_CUDA(cudaStreamWaitEvent(u->copy, c->free_ev, 0));
+    // (growing a buffer frees the old one; cudaFree itself waits for outstanding work)
+    HM_TRY(c->rowptr.reserve((size_t)(rows + 1) * sizeof(int64_t)));
+    HM_TRY(c->feat.reserve((size_t)std::max<int64_t>(elems, 1) * sizeof(uint32_t)));
+    HM_TRY(c->val.reserve((size_t)std::max<int64_t>(elems, 1) * sizeof(float)));
+    HM_TRY(c->label.reserve((size_t)std::max<int64_t>(rows, 1) * sizeof(float)));
+
+    // rowptr of the new chunk, rebased on the host into pinned staging
+    const int turn = u->stage_turn;
+    u->stage_turn ^= 1;
+    if (u->stage_ev[turn]) HM_CUDA(cudaEventSynchronize(u->stage_ev[turn]));
+    if (rows + 1 > u->h_stage_cap[turn]) {
+        if (u->h_stage[turn]) cudaFreeHost(u->h_stage[turn]);
+        u->h_stage[turn] = nullptr; u->h_stage_cap[turn] = 0;
+        HM_CUDA(cudaMallocHost(&u->h_stage[turn], (size_t)(rows + 1 + rows / 4) * sizeof(int64_t)));
+        u->h_stage_cap[turn] = rows + 1 + rows / 4;
+    }
+    int64_t *st = u->h_stage[turn];
+    for (int64_t i = 0; i < t_rows; i++) st[i] = u->tail_rp[i];
+    const int64_t base = rowptr[0];
+    for (int64_t i = 0; i <= n; i++) {
+        const int64_t v = rowptr[i] - base;
+        if (i > 0 && rowptr[i] < rowptr[i - 1]) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "rowptr decreases at row %lld", (long long)i);
+        st[t_rows + i] = t_nnz + v;
+    }
+
+    // carried rows: device-to-device on the compute stream (ordered after their producer)
+    if (t_rows) {
+        const Chunk *o = u->tail;
+        const int64_t o_e0 = o->mb_abs.empty() ? 0 : o->mb_abs.back();
+        HM_CUDA(cudaMemcpyAsync(c->feat.p, o->ft() + o_e0, (size_t)t_nnz * 4, cudaMemcpyDeviceToDevice, u->compute));
+        HM_CUDA(cudaMemcpyAsync(c->val.p, o->vl() + o_e0, (size_t)t_nnz * 4, cudaMemcpyDeviceToDevice, u->compute));
+        HM_CUDA(cudaMemcpyAsync(c->label.p, o->lb() + u->tail_row0, (size_t)t_rows * 4, cudaMemcpyDeviceToDevice, u->compute));
+    }
+    if (u->tail) {
+        // the old tail chunk is finished once the copies above have run
+        Chunk *o = u->tail;
+        u->tail = nullptr;
+        HM_TRY(retire_chunk(u, o, u->cfg.iters > 1 && o->rows > 0));
+        if (u->cfg.iters > 1 && o->rows == 0) { /* nothing trained from it: already pooled */ }
+    }
+    // new rows: host-to-device on the copy stream
+    HM_CUDA(cudaMemcpyAsync(c->rowptr.p, st, (size_t)(rows + 1) * 8, cudaMemcpyHostToDevice, u->copy));
+    if (nnz) {
+        HM_CUDA(cudaMemcpyAsync(c->feat.as<uint32_t>() + t_nnz, feature + base, (size_t)nnz * 4, cudaMemcpyHostToDevice, u->copy));
+        HM_CUDA(cudaMemcpyAsync(c->val.as<float>() + t_nnz, value + base, (size_t)nnz * 4, cudaMemcpyHostToDevice, u->copy));
+    }
+    HM_CUDA(cudaMemcpyAsync(c->label.as<float>() + t_rows, label, (size_t)n * 4, cudaMemcpyHostToDevice, u->copy));
+    if (!u->stage_ev[turn]) HM_CUDA(cudaEventCreateWithFlags(&u->stage_ev[turn], cudaEventDisableTiming));
+    HM_CUDA(cudaEventRecord(u->stage_ev[turn], u->copy));
+    HM_CUDA(cudaStreamWaitEvent(u->compute, u->stage_ev[turn], 0));
+    u->stats.h2d_bytes += (rows + 1) * 8 + nnz * 8 + n * 4;
+
+    // full mini-batches
+    const int64_t n_mb = rows / B;
+    const int64_t train = n_mb * B;
+    c->rows = train;
+    c->mb_abs.resize((size_t)n_mb + 1);
+    for (int64_t i = 0; i <= n_mb; i++) c->mb_abs[(size_t)i] = st[i * B];
+    HM_TRY(train_rows(u, *c, 0, train, c->mb_abs.data(), n_mb));
+
+    // what is left waits in this chunk
+    u->tail = c;
+    u->tail_row0 = train;
+    u->tail_rp.resize((size_t)(rows - train) + 1);
+    for (int64_t i = 0; i <= rows - train; i++) u->tail_rp[(size_t)i] = st[train + i] - st[train];
+    if (rows == train) u->tail_rp.clear();
+    return HM_OK;
+}
+
+hm_status check_bad(hm_udtf *u)
+{
+    uint32_t bad = 0;
+    HM_CUDA(cudaMemcpyAsync(u->h_small, u->d_bad, sizeof(uint32_t), cudaMemcpyDeviceToHost, u->compute));
+    HM_CUDA(cudaStreamSynchronize(u->compute));
+    std::memcpy(&bad, u->h_small, sizeof(bad));
+    if (bad) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "a feature index was negative or >= dims (%lld); those elements were ignored",
+                     (long long)u->cfg.dims);
+    return HM_OK;
+}
+
+hm_status create_impl(const hm_config &cfg, int device, hm_udtf **out)
+{
+    if (!out) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "out must not be NULL");
+    *out = nullptr;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+        cudaGetLastError();
+        HM_FAIL(HM_ERR_CUDA, "no CUDA device: hivemall_b200 has no CPU fallback");
+    }
+    if (device < 0 || device >= ndev) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "device %d out of range [0, %d)", device, ndev);
+    if (cfg.task == HM_TASK_FM) HM_FAIL(HM_ERR_UNSUPPORTED, "train_fm is not built yet");
+    if (cfg.dims < 1 || cfg.dims > ((int64_t)1 << 31)) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "dims out of range");
+    if (cfg.mini_batch < 1) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "mini_batch must be >= 1");
+    DeviceGuard g(device);
+    hm_udtf *u = new (std::nothrow) hm_udtf();
+    if (!u) HM_FAIL(HM_ERR_OOM, "out of host memory");
+    u->cfg = cfg;
+    u->device = device;
+    std::memset(&u->stats, 0, sizeof(u->stats));
+    hm_status s = [&]() -> hm_status {
+        HM_CUDA(cudaStreamCreateWithFlags(&u->compute, cudaStreamNonBlocking));
+        HM_CUDA(cudaStreamCreateWithFlags(&u->copy, cudaStreamNonBlocking));
+        u->L.stream = u->compute;
+        u->state_width = cfg.opt == HM_OPT_SGD ? 0 : (cfg.opt == HM_OPT_ADAGRAD ? 1 : 2);
+        HM_CUDA(cudaMalloc(&u->w, (size_t)cfg.dims * sizeof(float)));
+        HM_CUDA(cudaMemsetAsync(u->w, 0, (size_t)cfg.dims * sizeof(float), u->compute));
+        if (u->state_width) {
+            HM_CUDA(cudaMalloc(&u->state, (size_t)cfg.dims * u->state_width * sizeof(float)));
+            HM_CUDA(cudaMemsetAsync(u->state, 0, (size_t)cfg.dims * u->state_width * sizeof(float), u->compute));
+        }
+        HM_CUDA(cudaMalloc(&u->d_bad, sizeof(uint32_t)));
+        HM_CUDA(cudaMemsetAsync(u->d_bad, 0, sizeof(uint32_t), u->compute));
+        HM_CUDA(cudaMalloc(&u->d_total, sizeof(int64_t)));
+        HM_TRY(update_scratch_reserve(u->upd));
+        HM_TRY(ensure_small(u, 1024));
+        HM_CUDA(cudaStreamSynchronize(u->compute));
+        return HM_OK;
+    }();
+    if (s != HM_OK) { hm_udtf_destroy(u); return s; }
+    *out = u;
+    return HM_OK;
+}
+
+}  // namespace
+
+// =================================================================================
+//                                   extern "C"
+// =================================================================================
+
+extern "C" {
+
+const char *hm_last_error(void) { return hm::last_error_cstr(); }
+int hm_abi_version(void) { return HM_ABI_VERSION; }
+
+int hm_device_count(void)
+{
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+hm_status hm_host_alloc(void **out, int64_t bytes)
+{
+    if (!out || bytes < 0) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "bad arguments to hm_host_alloc");
+    *out = nullptr;
+    HM_CUDA(cudaMallocHost(out, (size_t)std::max<int64_t>(bytes, 1)));
+    return HM_OK;
+}
+
+hm_status hm_host_free(void *p)
+{
+    if (p) HM_CUDA(cudaFreeHost(p));
+    return HM_OK;
+}
+
+hm_status hm_parse_options(const char *function_name, const char *options, hm_config *out)
+{
+    return hm::parse_options(function_name, options, out);
+}
+
+// ---- hashing -----------------------------------------------------------------------
+
+static hm_status hash_host(const uint8_t *bytes, const int64_t *offsets, int64_t n, uint32_t seed,
+                           int32_t num_features, int32_t *out_index, float *out_value, int device, bool with_value)
+{
+    if (n < 0 || (n > 0 && (!bytes || !offsets || !out_index)) || (with_value && n > 0 && !out_value))
+        HM_FAIL(HM_ERR_INVALID_ARGUMENT, "NULL buffer passed to feature hashing");
+    if (num_features < 1) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "num_features must be >= 1");
+    if (n == 0) return HM_OK;
+    int ndev = hm_device_count();
+    if (ndev == 0) HM_FAIL(HM_ERR_CUDA, "no CUDA device: hivemall_b200 has no CPU fallback");
+    if (device < 0 || device >= ndev) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "device %d out of range", device);
+    DeviceGuard g(device);
+    const int64_t nbytes = offsets[n];
+    if (offsets[0] != 0 || nbytes < 0) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "offsets must start at 0 and be non-decreasing");
+    uint8_t *d_bytes = nullptr; int64_t *d_off = nullptr; int32_t *d_idx = nullptr; float *d_val = nullptr;
+    cudaStream_t st = nullptr;
+    Launcher L;
+    hm_status s = [&]() -> hm_status {
+        HM_CUDA(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+        L.stream = st;
+        HM_CUDA(cudaMalloc(&d_bytes, (size_t)nbytes + 32));
+        HM_CUDA(cudaMalloc(&d_off, (size_t)(n + 1) * 8));
+        HM_CUDA(cudaMalloc(&d_idx, (size_t)n * 4));
+        if (with_value) HM_CUDA(cudaMalloc(&d_val, (size_t)n * 4));
+        HM_CUDA(cudaMemcpyAsync(d_bytes, bytes, (size_t)nbytes, cudaMemcpyHostToDevice, st));
+        HM_CUDA(cudaMemcpyAsync(d_off, offsets, (size_t)(n + 1) * 8, cudaMemcpyHostToDevice, st));
+        if (with_value) HM_TRY(launch_feature_hashing(L, d_bytes, d_off, n, seed, num_features, d_idx, d_val));
+        else HM_TRY(launch_mhash(L, d_bytes, d_off, n, seed, num_features, d_idx));
+        HM_CUDA(cudaMemcpyAsync(out_index, d_idx, (size_t)n * 4, cudaMemcpyDeviceToHost, st));
+        if (with_value) HM_CUDA(cudaMemcpyAsync(out_value, d_val, (size_t)n * 4, cudaMemcpyDeviceToHost, st));
+        HM_CUDA(cudaStreamSynchronize(st));
+        return HM_OK;
+    }();
+    cudaFree(d_bytes); cudaFree(d_off); cudaFree(d_idx); cudaFree(d_val);
+    if (st) cudaStreamDestroy(st);
+    return s;
+}
+
+hm_status hm_mhash(const uint8_t *bytes, const int64_t *offsets, int64_t n, uint32_t seed, int32_t num_features,
+                   int32_t *out, int device)
+{
+    return hash_host(bytes, offsets, n, seed, num_features, out, nullptr, device, false);
+}
+
+hm_status hm_feature_hashing(const uint8_t *bytes, const int64_t *offsets, int64_t n, uint32_t seed,
+                             int32_t num_features, int32_t *out_index, float *out_value, int device)
+{
+    return hash_host(bytes, offsets, n, seed, num_features, out_index, out_value, device, true);
+}
+
+hm_status hm_mhash_device(const uint8_t *d_bytes, const int64_t *d_offsets, int64_t n, uint32_t seed,
+                          int32_t num_features, int32_t *d_out, void *stream)
+{
+    if (n < 0 || (n > 0 && (!d_bytes || !d_offsets || !d_out))) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "NULL buffer passed to hm_mhash_device");
+    if (num_features < 1) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "num_features must be >= 1");
+    Launcher L;
+    L.stream = reinterpret_cast<cudaStream_t>(stream);
+    return launch_mhash(L, d_bytes, d_offsets, n, seed, num_features, d_out);
+}
+
+// ---- lifecycle ---------------------------------------------------------------------
+
+hm_status hm_udtf_create(const char *function_name, const char *options, int device, hm_udtf **out)
+{
+    hm_config cfg;
+    HM_TRY(hm::parse_options(function_name, options, &cfg));
+    return create_impl(cfg, device, out);
+}
+
+hm_status hm_udtf_create_from_config(const hm_config *cfg, int device, hm_udtf **out)
+{
+    if (!cfg) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "cfg must not be NULL");
+    return create_impl(*cfg, device, out);
+}
+
+hm_status hm_udtf_process(hm_udtf *u, int64_t n_rows, const int64_t *rowptr, const int32_t *feature,
+                          const float *value, const float *label)
+{
+    if (!u) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "NULL learner");
+    if (u->closed) HM_FAIL(HM_ERR_STATE, "process() after close()");
+    if (u->device_rows_short) HM_FAIL(HM_ERR_STATE, "process() after a device call that ended on a short mini-batch");
+    if (n_rows < 0 || (n_rows > 0 && (!rowptr || !label))) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "NULL buffer passed to process()");
+    if (n_rows == 0) return HM_OK;
+    if (rowptr[n_rows] > rowptr[0] && (!feature || !value)) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "NULL feature/value buffer");
+    DeviceGuard g(u->device);
+    // slices sized to whole mini-batches so that copies and training overlap
+    const int64_t B = u->cfg.mini_batch;
+    int64_t slice = std::max<int64_t>(kSliceRows / B * B, B);
+    for (int64_t r = 0; r < n_rows; r += slice) {
+        const int64_t n = std::min(slice, n_rows - r);
+        HM_TRY(process_slice(u, n, rowptr + r, feature, value, label + r));
+    }
+    return HM_OK;
+}
+
+hm_status hm_udtf_process_strings(hm_udtf *u, int64_t n_rows, const int64_t *rowptr, const uint8_t *bytes,
+                                  const int64_t *offsets, const float *label)
+{
+    if (!u) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "NULL learner");
+    if (u->closed) HM_FAIL(HM_ERR_STATE, "process() after close()");
+    if (n_rows < 0 || (n_rows > 0 && (!rowptr || !label || !offsets))) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "NULL buffer passed to process_strings()");
+    if (n_rows == 0) return HM_OK;
+    const int64_t s0 = rowptr[0], s1 = rowptr[n_rows];
+    const int64_t n = s1 - s0;
+    if (n < 0) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "rowptr is not non-decreasing");
+    std::vector<int32_t> idx((size_t)std::max<int64_t>(n, 1));
+    std::vector<float> val((size_t)std::max<int64_t>(n, 1));
+    std::vector<int64_t> off((size_t)n + 1), rp((size_t)n_rows + 1);
+    const int64_t b0 = offsets[s0];
+    for (int64_t i = 0; i <= n; i++) off[(size_t)i] = offsets[s0 + i] - b0;
+    for (int64_t i = 0; i <= n_rows; i++) rp[(size_t)i] = rowptr[i] - s0;
+    if (n > 0) {
+        if (!bytes) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "NULL bytes buffer");
+        if (u->cfg.dims > 0x7fffffffLL) HM_FAIL(HM_ERR_UNSUPPORTED, "feature hashing needs dims < 2^31");
+        HM_TRY(hash_host(bytes + b0, off.data(), n, u->cfg.hash_seed, (int32_t)u->cfg.dims, idx.data(), val.data(),
+                         u->device, true));
+    }
+    return hm_udtf_process(u, n_rows, rp.data(), idx.data(), val.data(), label);
+}
+
+hm_status hm_udtf_process_device(hm_udtf *u, int64_t n_rows, int64_t nnz, const int64_t *d_rowptr,
+                                 const int32_t *d_feature, const float *d_value, const float *d_label)
+{
+    if (!u) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "NULL learner");
+    if (u->closed) HM_FAIL(HM_ERR_STATE, "process() after close()");
+    if (u->tail_rows() > 0) HM_FAIL(HM_ERR_STATE, "process_device() while %lld host rows wait for a full mini-batch", (long long)u->tail_rows());
+    if (u->device_rows_short) HM_FAIL(HM_ERR_STATE, "process_device() after a call that ended on a short mini-batch");
+    if (n_rows < 0 || nnz < 0 || (n_rows > 0 && (!d_rowptr || !d_label)) || (nnz > 0 && (!d_feature || !d_value)))
+        HM_FAIL(HM_ERR_INVALID_ARGUMENT, "bad arguments to process_device()");
+    if (n_rows == 0) return HM_OK;
+    DeviceGuard g(u->device);
+    const int64_t B = u->cfg.mini_batch;
+    const int64_t n_mb = (n_rows + B - 1) / B;
+    Chunk *c = new (std::nothrow) Chunk();
+    if (!c) HM_FAIL(HM_ERR_OOM, "out of host memory");
+    c->view = true;
+    c->rows = n_rows;
+    c->v_rowptr = d_rowptr; c->v_feat = reinterpret_cast<const uint32_t *>(d_feature);
+    c->v_val = d_value; c->v_label = d_label;
+    // rowptr at the mini-batch boundaries, read back on the copy stream (the rows are resident already)
+    hm_status s = [&]() -> hm_status {
+        HM_TRY(u->mb_gather.reserve((size_t)(n_mb + 1) * sizeof(int64_t)));
+        HM_TRY(ensure_small(u, n_mb + 1));
+        const int grid = (int)std::min<int64_t>((n_mb + 256) / 256, 1024);
+        gather_rowptr_kernel<<<grid, 256, 0, u->copy>>>(d_rowptr, n_rows, (int32_t)B, n_mb + 1, u->mb_gather.as<int64_t>());
+        u->L.launches++; u->L.count[K_MISC]++;
+        HM_CUDA(cudaGetLastError());
+        HM_CUDA(cudaMemcpyAsync(u->h_small, u->mb_gather.p, (size_t)(n_mb + 1) * 8, cudaMemcpyDeviceToHost, u->copy));
+        HM_CUDA(cudaStreamSynchronize(u->copy));
+        u->stats.d2h_bytes += (n_mb + 1) * 8;
+        c->mb_abs.assign(u->h_small, u->h_small + n_mb + 1);
+        if (c->mb_abs.back() - c->mb_abs.front() != nnz)
+            HM_FAIL(HM_ERR_INVALID_ARGUMENT, "nnz (%lld) does not match d_rowptr (%lld)", (long long)nnz,
+                    (long long)(c->mb_abs.back() - c->mb_abs.front()));
+        return train_rows(u, *c, 0, n_rows, c->mb_abs.data(), n_mb);
+    }();
+    if (s != HM_OK) { delete c; return s; }
+    if (n_rows % B) u->device_rows_short = true;
+    return retire_chunk(u, c, u->cfg.iters > 1);
+}
+
+hm_status hm_udtf_close(hm_udtf *u, int64_t *n_model_rows)
+{
+    if (!u) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "NULL learner");
+    DeviceGuard g(u->device);
+    if (!u->closed) {
+        // last short mini-batch
+        if (u->tail) {
+            Chunk *c = u->tail;
+            const int64_t t_rows = u->tail_rows();
+            if (t_rows > 0) {
+                const int64_t e0 = c->mb_abs.empty() ? 0 : c->mb_abs.back();
+                int64_t mb[2] = {e0, e0 + u->tail_rp.back()};
+                HM_TRY(train_rows(u, *c, u->tail_row0, t_rows, mb, 1));
+                if (c->mb_abs.empty()) c->mb_abs.push_back(e0);
+                c->mb_abs.push_back(mb[1]);
+                c->rows += t_rows;
+            }
+            u->tail = nullptr;
+            u->tail_rp.clear();
+            HM_TRY(retire_chunk(u, c, u->cfg.iters > 1 && c->rows > 0));
+        }
+        // remaining passes over the retained rows, same order, same mini-batch boundaries
+        for (int it = 1; it < u->cfg.iters; it++)
+            for (Chunk *c : u->retained) {
+                const int64_t B = u->cfg.mini_batch;
+                const int64_t n_mb = (c->rows + B - 1) / B;
+                HM_TRY(train_rows(u, *c, 0, c->rows, c->mb_abs.data(), n_mb));
+            }
+        u->closed = true;
+    }
+    HM_TRY(check_bad(u));
+    HM_TRY(launch_export_count(u->L, u->exp, u->w, nullptr, u->cfg.dims, u->d_total));
+    HM_CUDA(cudaMemcpyAsync(u->h_small, u->d_total, sizeof(int64_t), cudaMemcpyDeviceToHost, u->compute));
+    HM_CUDA(cudaStreamSynchronize(u->compute));
+    u->stats.d2h_bytes += 8;
+    u->model_rows = u->h_small[0];
+    u->L.drain();
+    if (n_model_rows) *n_model_rows = u->model_rows;
+    return HM_OK;
+}
+
+hm_status hm_udtf_forward(hm_udtf *u, int32_t *feature, float *weight, float *, int64_t cap, int64_t *n_written)
+{
+    if (!u) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "NULL learner");
+    if (!u->closed) HM_FAIL(HM_ERR_STATE, "forward() before close()");
+    if (cap < 0 || (cap > 0 && (!feature || !weight))) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "bad arguments to forward()");
+    DeviceGuard g(u->device);
+    // recount: the replica may have been averaged since close()
+    HM_TRY(launch_export_count(u->L, u->exp, u->w, nullptr, u->cfg.dims, u->d_total));
+    HM_CUDA(cudaMemcpyAsync(u->h_small, u->d_total, sizeof(int64_t), cudaMemcpyDeviceToHost, u->compute));
+    HM_CUDA(cudaStreamSynchronize(u->compute));
+    const int64_t n = u->h_small[0];
+    u->model_rows = n;
+    if (n > cap) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "model table has %lld rows but capacity is %lld", (long long)n, (long long)cap);
+    if (n > 0) {
+        HM_TRY(u->exp_feat.reserve((size_t)n * 4));
+        HM_TRY(u->exp_weight.reserve((size_t)n * 4));
+        HM_TRY(launch_export_write(u->L, u->exp, u->w, nullptr, u->cfg.dims, u->exp_feat.as<int32_t>(),
+                                   u->exp_weight.as<float>()));
+        HM_CUDA(cudaMemcpyAsync(feature, u->exp_feat.p, (size_t)n * 4, cudaMemcpyDeviceToHost, u->compute));
+        HM_CUDA(cudaMemcpyAsync(weight, u->exp_weight.p, (size_t)n * 4, cudaMemcpyDeviceToHost, u->compute));
+        HM_CUDA(cudaStreamSynchronize(u->compute));
+        u->stats.d2h_bytes += n * 8;
+    }
+    if (n_written) *n_written = n;
+    return HM_OK;
+}
+
+hm_status hm_udtf_destroy(hm_udtf *u)
+{
+    if (!u) return HM_OK;
+    DeviceGuard g(u->device);
+    if (u->compute) cudaStreamSynchronize(u->compute);
+    if (u->copy) cudaStreamSynchronize(u->copy);
+    u->L.release();
+    for (Chunk *c : u->retained) { c->release(); delete c; }
+    for (Chunk *c : u->pool) { c->release(); delete c; }
+    if (u->tail) { u->tail->release(); delete u->tail; }
+    sort_scratch_free(u->sort);
+    update_scratch_free(u->upd);
+    cudaFree(u->exp.counts);
+    for (DevBuf *b : {&u->margin, &u->dloss, &u->contrib, &u->mb_gather, &u->exp_feat, &u->exp_weight, &u->tmp_a,
+                      &u->tmp_b, &u->tmp_c, &u->tmp_d})
+        b->release();
+    cudaFree(u->w); cudaFree(u->state); cudaFree(u->d_bad); cudaFree(u->d_total);
+    for (int i = 0; i < 2; i++) {
+        if (u->h_stage[i]) cudaFreeHost(u->h_stage[i]);
+        if (u->stage_ev[i]) cudaEventDestroy(u->stage_ev[i]);
+    }
+    if (u->h_small) cudaFreeHost(u->h_small);
+    if (u->copied_ev) cudaEventDestroy(u->copied_ev);
+    if (u->compute) cudaStreamDestroy(u->compute);
+    if (u->copy) cudaStreamDestroy(u->copy);
+    cudaGetLastError();
+    delete u;
+    return HM_OK;
+}
+
+// ---- replica access ----------------------------------------------------------------
+
+int hm_udtf_num_arrays(const hm_udtf *u) { return u ? (u->state ? 2 : 1) : 0; }
+
+hm_status hm_udtf_array(hm_udtf *u, int which, const char **name, void **d_ptr, int64_t *n_floats, int32_t *width)
+{
+    if (!u) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "NULL learner");
+    if (which == 0) {
+        if (name) *name = "w";
+        if (d_ptr) *d_ptr = u->w;
+        if (n_floats) *n_floats = u->cfg.dims;
+        if (width) *width = 1;
+        return HM_OK;
+    }
+    if (which == 1 && u->state) {
+        if (name) *name = "state";
+        if (d_ptr) *d_ptr = u->state;
+        if (n_floats) *n_floats = u->cfg.dims * u->state_width;
+        if (width) *width = u->state_width;
+        return HM_OK;
+    }
+    HM_FAIL(HM_ERR_INVALID_ARGUMENT, "array index %d out of range", which);
+}
+
+static hm_status array_copy(hm_udtf *u, int which, float *host, const float *host_in, int64_t n)
+{
+    void *d = nullptr;
+    int64_t len = 0;
+    HM_TRY(hm_udtf_array(u, which, nullptr, &d, &len, nullptr));
+    if (!host && !host_in) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "NULL host buffer");
+    if (n != len) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "array %d holds %lld floats, caller passed %lld", which, (long long)len, (long long)n);
+    DeviceGuard g(u->device);
+    HM_CUDA(cudaStreamSynchronize(u->copy));
+    if (host) {
+        HM_CUDA(cudaMemcpyAsync(host, d, (size_t)n * 4, cudaMemcpyDeviceToHost, u->compute));
+        u->stats.d2h_bytes += n * 4;
+    } else {
+        HM_CUDA(cudaMemcpyAsync(d, host_in, (size_t)n * 4, cudaMemcpyHostToDevice, u->compute));
+        u->stats.h2d_bytes += n * 4;
+    }
+    HM_CUDA(cudaStreamSynchronize(u->compute));
+    return HM_OK;
+}
+
+hm_status hm_udtf_read_array(hm_udtf *u, int which, float *host, int64_t n)
+{
+    if (!u || !host) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "NULL argument");
+    return array_copy(u, which, host, nullptr, n);
+}
+
+hm_status hm_udtf_write_array(hm_udtf *u, int which, const float *host, int64_t n)
+{
+    if (!u || !host) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "NULL argument");
+    return array_copy(u, which, nullptr, host, n);
+}
+
+hm_status hm_udtf_get_step(const hm_udtf *u, int64_t *t)
+{
+    if (!u || !t) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "NULL argument");
+    *t = u->t;
+    return HM_OK;
+}
+
+hm_status hm_udtf_set_step(hm_udtf *u, int64_t t)
+{
+    if (!u || t < 0) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "bad argument");
+    u->t = t;
+    return HM_OK;
+}
+
+hm_status hm_udtf_sync(hm_udtf *u)
+{
+    if (!u) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "NULL learner");
+    DeviceGuard g(u->device);
+    HM_CUDA(cudaStreamSynchronize(u->copy));
+    HM_CUDA(cudaStreamSynchronize(u->compute));
+    return HM_OK;
+}
+
+void *hm_udtf_stream(hm_udtf *u) { return u ? (void *)u->compute : nullptr; }
+
+hm_status hm_udtf_scale_replica(hm_udtf *u, float scale)
+{
+    if (!u) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "NULL learner");
+    DeviceGuard g(u->device);
+    HM_TRY(launch_scale(u->L, u->w, u->cfg.dims, scale));
+    if (u->state) HM_TRY(launch_scale(u->L, u->state, u->cfg.dims * u->state_width, scale));
+    return HM_OK;
+}
+
+// ---- prediction --------------------------------------------------------------------
+
+hm_status hm_udtf_predict_device(hm_udtf *u, int64_t n_rows, const int64_t *d_rowptr, const int32_t *d_feature,
+                                 const float *d_value, float *d_out)
+{
+    if (!u) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "NULL learner");
+    if (n_rows < 0 || (n_rows > 0 && (!d_rowptr || !d_out))) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "bad arguments to predict");
+    DeviceGuard g(u->device);
+    return launch_predict_linear(u->L, u->w, u->cfg.dims, n_rows, d_rowptr, reinterpret_cast<const uint32_t *>(d_feature),
+                                 d_value, d_out, u->d_bad);
+}
+
+hm_status hm_udtf_predict(hm_udtf *u, int64_t n_rows, const int64_t *rowptr, const int32_t *feature,
+                          const float *value, float *out)
+{
+    if (!u) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "NULL learner");
+    if (n_rows < 0 || (n_rows > 0 && (!rowptr || !out))) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "bad arguments to predict");
+    if (n_rows == 0) return HM_OK;
+    DeviceGuard g(u->device);
+    const int64_t base = rowptr[0], nnz = rowptr[n_rows] - base;
+    if (nnz < 0 || (nnz > 0 && (!feature || !value))) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "bad CSR passed to predict");
+    HM_TRY(u->tmp_a.reserve((size_t)(n_rows + 1) * 8));
+    HM_TRY(u->tmp_b.reserve((size_t)std::max<int64_t>(nnz, 1) * 4));
+    HM_TRY(u->tmp_c.reserve((size_t)std::max<int64_t>(nnz, 1) * 4));
+    HM_TRY(u->tmp_d.reserve((size_t)n_rows * 4));
+    std::vector<int64_t> rp((size_t)n_rows + 1);
+    for (int64_t i = 0; i <= n_rows; i++) rp[(size_t)i] = rowptr[i] - base;
+    HM_CUDA(cudaMemcpyAsync(u->tmp_a.p, rp.data(), (size_t)(n_rows + 1) * 8, cudaMemcpyHostToDevice, u->compute));
+    if (nnz) {
+        HM_CUDA(cudaMemcpyAsync(u->tmp_b.p, feature + base, (size_t)nnz * 4, cudaMemcpyHostToDevice, u->compute));
+        HM_CUDA(cudaMemcpyAsync(u->tmp_c.p, value + base, (size_t)nnz * 4, cudaMemcpyHostToDevice, u->compute));
+    }
+    HM_TRY(launch_predict_linear(u->L, u->w, u->cfg.dims, n_rows, u->tmp_a.as<int64_t>(), u->tmp_b.as<uint32_t>(),
+                                 u->tmp_c.as<float>(), u->tmp_d.as<float>(), u->d_bad));
+    HM_CUDA(cudaMemcpyAsync(out, u->tmp_d.p, (size_t)n_rows * 4, cudaMemcpyDeviceToHost, u->compute));
+    HM_CUDA(cudaStreamSynchronize(u->compute));   // also keeps `rp` alive long enough
+    u->stats.h2d_bytes += (n_rows + 1) * 8 + nnz * 8;
+    u->stats.d2h_bytes += n_rows * 4;
+    return HM_OK;
+}
+
+// ---- measurement -------------------------------------------------------------------
+
+hm_status hm_udtf_stats(const hm_udtf *u, hm_stats *out)
+{
+    if (!u || !out) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "NULL argument");
+    *out = u->stats;
+    out->kernel_launches = u->L.launches;
+    return HM_OK;
+}
+
+hm_status hm_udtf_set_profiling(hm_udtf *u, int on)
+{
+    if (!u) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "NULL learner");
+    DeviceGuard g(u->device);
+    if (!on) u->L.drain();
+    u->L.profiling = on != 0;
+    return HM_OK;
+}
+
+int hm_udtf_num_kernels(const hm_udtf *) { return K_NUM_KERNELS; }
+
+hm_status hm_udtf_kernel_time(hm_udtf *u, int i, const char **name, int64_t *launches, double *total_ms,
+                              double *algorithmic_bytes)
+{
+    if (!u || i < 0 || i >= K_NUM_KERNELS) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "bad argument");
+    DeviceGuard g(u->device);
+    u->L.drain();
+    if (name) *name = kKernelNames[i];
+    if (launches) *launches = u->L.count[i];
+    if (total_ms) *total_ms = u->L.ms[i];
+    if (algorithmic_bytes) *algorithmic_bytes = u->L.bytes[i];
+    return HM_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,603 @@
+// hm_linear.cu -- kernels of the linear learner (train_classifier / train_regressor).
+//
+// Stands in for the mini-batch path of the GeneralLearnerBaseUDTF family that
+// BASELINE.json's north_star names (logistic / hinge / squared loss; SGD, AdaGrad,
+// AdaDelta, Adam, FTRL under -mini_batch).  The reference mount has no source
+// (README.md:20-22); the arithmetic contract is DESIGN.md section 3 and the CPU oracle
+// (oracle/hm_oracle.c) restates the same contract independently.
+//
+//   linear_forward_kernel   warp per row: gather w, margin in fp64, dloss, contrib = dloss*x
+//   linear_update_kernel    reduce-by-feature over the feature-sorted mini-batch (fp64 sums,
+//                           fixed order, no float atomics) fused with the optimizer update;
+//                           the last CTA to finish also resolves segments that straddle CTAs
+//   predict / export / scale helpers
+#include "hm_internal.h"
+
+namespace hm {
+
+namespace {
+
+constexpr int kFwdThreads = 256;
+constexpr int kUpdThreads = 256;
+constexpr int kUpdItems = 8;
+constexpr int kUpdTile = kUpdThreads * kUpdItems;  // 2048
+
+// ---- scalar math of DESIGN.md section 3 (every fp32 op rounded on its own) ------
+
+__device__ __forceinline__ float hm_exp(float x)
+{
+    x = fminf(fmaxf(x, -87.0f), 88.0f);
+    const float n = rintf(__fmul_rn(x, 1.44269504f));
+    float r = __fsub_rn(x, __fmul_rn(n, 0.693359375f));
+    r = __fsub_rn(r, __fmul_rn(n, -2.12194440e-4f));
+    float p = 1.3888889e-3f;
+    p = __fadd_rn(__fmul_rn(p, r), 8.3333333e-3f);
+    p = __fadd_rn(__fmul_rn(p, r), 4.1666667e-2f);
+    p = __fadd_rn(__fmul_rn(p, r), 1.6666667e-1f);
+    p = __fadd_rn(__fmul_rn(p, r), 0.5f);
+    p = __fadd_rn(__fmul_rn(p, r), 1.0f);
+    p = __fadd_rn(__fmul_rn(p, r), 1.0f);
+    return __fmul_rn(p, __int_as_float(((int)n + 127) << 23));
+}
+
+__device__ __forceinline__ float dloss_of(int loss, float m, float y)
+{
+    if (loss == HM_LOSS_LOG) return __fdiv_rn(-y, __fadd_rn(1.0f, hm_exp(__fmul_rn(y, m))));
+    if (loss == HM_LOSS_HINGE) return __fmul_rn(y, m) < 1.0f ? -y : 0.0f;
+    return __fsub_rn(m, y);
+}
+
+__device__ __forceinline__ double warp_sum(double v)
+{
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+// ---- forward ---------------------------------------------------------------------
+
+struct FwdParams {
+    const float *w;
+    const int64_t *rowptr;   // chunk row pointer (absolute element positions in the chunk)
+    const uint32_t *feature;
+    const float *value;
+    const float *label;
+    float *margin;           // indexed by row of the BLOCK
+    float *dloss;            // idem
+    float *contrib;          // indexed by element of the BLOCK
+    int64_t block_row0;      // first row of the block in the chunk
+    int64_t row0;            // first row of this mini-batch in the chunk
+    int32_t n_rows;
+    int32_t task, loss;
+    int32_t write_contrib;
+    uint32_t dims;
+    uint32_t *bad;           // set to 1 when a feature index >= dims is met (that element scores 0)
+};
+
+__global__ void __launch_bounds__(kFwdThreads) linear_forward_kernel(FwdParams P)
+{
+    const int lane = threadIdx.x & 31;
+    const int warps_per_cta = kFwdThreads / 32;
+    const int64_t block_base = P.rowptr[P.block_row0];
+    for (int r = blockIdx.x * warps_per_cta + (threadIdx.x >> 5); r < P.n_rows; r += gridDim.x * warps_per_cta) {
+        const int64_t row = P.row0 + r;
+        const int64_t p0 = P.rowptr[row], p1 = P.rowptr[row + 1];
+        double acc = 0.0;
+        for (int64_t p = p0 + lane; p < p1; p += 32) {
+            const uint32_t f = P.feature[p];
+            if (f < P.dims) acc += (double)__fmul_rn(__ldg(P.w + f), P.value[p]);
+            else atomicOr(P.bad, 1u);
+        }
+        acc = warp_sum(acc);
+        const float m = (float)acc;
+        if (P.write_contrib) {
+            const float lab = P.label[row];
+            const float y = P.task == HM_TASK_CLASSIFIER ? (lab > 0.0f ? 1.0f : -1.0f) : lab;
+            const float dl = dloss_of(P.loss, m, y);
+            if (lane == 0) { P.margin[row - P.block_row0] = m; P.dloss[row - P.block_row0] = dl; }
+            for (int64_t p = p0 + lane; p < p1; p += 32)
+                P.contrib[p - block_base] = __fmul_rn(dl, P.value[p]);
+        } else if (lane == 0) {
+            P.margin[row - P.block_row0] = m;
+        }
+    }
+}
+
+// ---- update ------------------------------------------------------------------------
+
+struct SegRec {           // a (feature, partial sum) record; valid == 0 means empty
+    double sum;
+    uint32_t key, cnt, valid, pad;
+};
+struct Boundary { SegRec first, last; };
+
+struct UpdParams {
+    float *w;
+    float *state;
+    uint8_t *touched;        // nullable
+    const uint32_t *skey;    // sorted features of the block
+    const uint32_t *spay;    // sorted element positions (relative to block)
+    const float *contrib;
+    const uint32_t *seg_off;
+    Boundary *boundary;
+    uint32_t *done_counter;
+    int32_t seg;
+    uint32_t dims;
+    int32_t opt, reg, grad_norm, state_width;
+    float eta, adam_alpha, lambda, eps, rho, beta1, beta2, alpha, beta, lambda1, lambda2;
+    double n_rows;
+};
+
+// One coordinate: DESIGN.md 3.4-3.6.
+__device__ __forceinline__ void apply_update(const UpdParams &P, uint32_t j, double sum, uint32_t cnt)
+{
+    if (j >= P.dims) return;  // flagged by the forward kernel; never touch memory outside the replica
+    const double denom = P.grad_norm == HM_NORM_BATCH ? P.n_rows : (P.grad_norm == HM_NORM_COUNT ? (double)cnt : 1.0);
+    float g = (float)(sum / denom);
+    float wv = P.w[j];
+    float *st = P.state + (size_t)j * P.state_width;
+    if (P.reg == HM_REG_L2 && P.opt != HM_OPT_FTRL) g = __fadd_rn(g, __fmul_rn(P.lambda, wv));
+    switch (P.opt) {
+    case HM_OPT_SGD:
+        wv = __fsub_rn(wv, __fmul_rn(P.eta, g));
+        break;
+    case HM_OPT_ADAGRAD: {
+        const float G = __fadd_rn(st[0], __fmul_rn(g, g));
+        st[0] = G;
+        wv = __fsub_rn(wv, __fdiv_rn(__fmul_rn(P.eta, g), __fadd_rn(__fsqrt_rn(G), P.eps)));
+        break;
+    }
+    case HM_OPT_ADADELTA: {
+        const float2 s = *reinterpret_cast<float2 *>(st);
+        const float omr = __fsub_rn(1.0f, P.rho);
+        const float E = __fadd_rn(__fmul_rn(P.rho, s.x), __fmul_rn(__fmul_rn(omr, g), g));
+        const float dx = __fmul_rn(__fdiv_rn(__fsqrt_rn(__fadd_rn(s.y, P.eps)), __fsqrt_rn(__fadd_rn(E, P.eps))), g);
+        const float D = __fadd_rn(__fmul_rn(P.rho, s.y), __fmul_rn(__fmul_rn(omr, dx), dx));
+        *reinterpret_cast<float2 *>(st) = make_float2(E, D);
+        wv = __fsub_rn(wv, dx);
+        break;
+    }
+    case HM_OPT_ADAM: {
+        const float2 s = *reinterpret_cast<float2 *>(st);
+        const float m = __fadd_rn(__fmul_rn(P.beta1, s.x), __fmul_rn(__fsub_rn(1.0f, P.beta1), g));
+        const float v = __fadd_rn(__fmul_rn(P.beta2, s.y), __fmul_rn(__fmul_rn(__fsub_rn(1.0f, P.beta2), g), g));
+        *reinterpret_cast<float2 *>(st) = make_float2(m, v);
+        wv = __fsub_rn(wv, __fdiv_rn(__fmul_rn(P.adam_alpha, m), __fadd_rn(__fsqrt_rn(v), P.eps)));
+        break;
+    }
+    case HM_OPT_FTRL: {
+        const float2 s = *reinterpret_cast<float2 *>(st);  // (z, n)
+        const float n1 = __fadd_rn(s.y, __fmul_rn(g, g));
+        const float sq1 = __fsqrt_rn(n1);
+        const float sigma = __fdiv_rn(__fsub_rn(sq1, __fsqrt_rn(s.y)), P.alpha);
+        const float z = __fsub_rn(__fadd_rn(s.x, g), __fmul_rn(sigma, wv));
+        *reinterpret_cast<float2 *>(st) = make_float2(z, n1);
+        if (fabsf(z) <= P.lambda1) wv = 0.0f;
+        else {
+            const float sgn = z < 0.0f ? -1.0f : 1.0f;
+            const float num = __fsub_rn(z, __fmul_rn(sgn, P.lambda1));
+            const float den = __fadd_rn(__fdiv_rn(__fadd_rn(P.beta, sq1), P.alpha), P.lambda2);
+            wv = -__fdiv_rn(num, den);
+        }
+        break;
+    }
+    }
+    if (P.reg == HM_REG_L1 && P.opt != HM_OPT_FTRL) {
+        const float a = __fsub_rn(fabsf(wv), __fmul_rn(P.eta, P.lambda));
+        wv = a > 0.0f ? copysignf(a, wv) : 0.0f;
+    }
+    P.w[j] = wv;
+    if (P.touched) P.touched[j] = 1;
+}
+
+__device__ __forceinline__ int pad_idx(int q) { return q + (q >> 5); }
+
+// Segmented-scan element: f = "a segment head lies in the span", (v, c) = sum / count of the
+// span's trailing run.  combine(a, b) for a before b.
+struct Scan { double v; uint32_t c; uint32_t f; };
+__device__ __forceinline__ Scan combine(const Scan &a, const Scan &b)
+{
+    Scan r;
+    r.f = a.f | b.f;
+    r.v = b.f ? b.v : a.v + b.v;
+    r.c = b.f ? b.c : a.c + b.c;
+    return r;
+}
+
+__global__ void __launch_bounds__(kUpdThreads) linear_update_kernel(UpdParams P)
+{
+    __shared__ uint32_t s_key[kUpdTile + kUpdTile / 32 + 2];
+    __shared__ float s_val[kUpdTile + kUpdTile / 32 + 2];
+    __shared__ Scan s_warp[kUpdThreads / 32];
+    __shared__ SegRec s_carry;       // open trailing segment of the previous tile
+    __shared__ uint32_t s_carry_open;
+    __shared__ uint32_t s_is_last;
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const uint32_t s0 = P.seg_off[P.seg], s1 = P.seg_off[P.seg + 1];
+    const uint32_t n = s1 - s0;
+    // contiguous split of the sorted mini-batch over the grid, in whole tiles
+    const uint32_t tiles = (n + kUpdTile - 1) / kUpdTile;
+    const uint32_t tiles_per_cta = (tiles + gridDim.x - 1) / gridDim.x;
+    const uint32_t lo = min(n, blockIdx.x * tiles_per_cta * kUpdTile);
+    const uint32_t hi = min(n, lo + tiles_per_cta * kUpdTile);
+
+    Boundary out;
+    out.first.valid = 0; out.first.sum = 0; out.first.key = 0; out.first.cnt = 0; out.first.pad = 0;
+    out.last = out.first;
+    if (tid == 0) { s_carry.valid = 0; s_carry_open = 0; }
+    __syncthreads();
+
+    for (uint32_t t0 = lo; t0 < hi; t0 += kUpdTile) {
+        const int n_tile = (int)min((uint32_t)kUpdTile, hi - t0);
+        // ---- coalesced striped load + gather of contributions
+        uint32_t k[kUpdItems], e[kUpdItems];
+#pragma unroll
+        for (int i = 0; i < kUpdItems; i++) {
+            const int q = i * kUpdThreads + tid;
+            k[i] = q < n_tile ? __ldg(P.skey + s0 + t0 + q) : 0u;
+            e[i] = q < n_tile ? __ldg(P.spay + s0 + t0 + q) : 0u;
+        }
+#pragma unroll
+        for (int i = 0; i < kUpdItems; i++) {
+            const int q = i * kUpdThreads + tid;
+            if (q < n_tile) { s_key[pad_idx(q)] = k[i]; s_val[pad_idx(q)] = __ldg(P.contrib + e[i]); }
+        }
+        __syncthreads();
+        const SegRec carry = s_carry;
+        const uint32_t carry_open = s_carry_open;
+        const bool first_tile = t0 == lo;
+        const uint32_t key0 = s_key[pad_idx(0)];
+        const bool edge_continues = carry.valid && carry.key == key0;
+        // does a segment touching this tile's left edge also touch the CTA's left edge?
+        const bool edge_open = first_tile ? true : (edge_continues && carry_open != 0);
+        __syncthreads();  // everyone has read the carry before it is overwritten below
+
+        // ---- pass 1: thread summaries (items [8*tid, 8*tid+8)).  A "head" is an item at tile
+        // position >= 1 whose feature differs from its predecessor; position 0 is never a head:
+        // it either continues the carried segment or starts afresh with an empty running sum.
+        const int q0 = tid * kUpdItems;
+        Scan mine; mine.v = 0.0; mine.c = 0; mine.f = 0;
+        if (tid == 0 && edge_continues) { mine.v = carry.sum; mine.c = carry.cnt; }
+        uint32_t kk[kUpdItems]; float vv[kUpdItems];
+        const uint32_t prev_key = (q0 > 0 && q0 < n_tile) ? s_key[pad_idx(q0 - 1)] : 0u;
+#pragma unroll
+        for (int i = 0; i < kUpdItems; i++) {
+            const int q = q0 + i;
+            if (q < n_tile) {
+                kk[i] = s_key[pad_idx(q)]; vv[i] = s_val[pad_idx(q)];
+                const bool head = q > 0 && kk[i] != (i == 0 ? prev_key : kk[i - 1]);
+                if (head) { mine.v = 0.0; mine.c = 0; mine.f = 1; }
+                mine.v += (double)vv[i]; mine.c += 1;
+            }
+        }
+        // ---- exclusive segmented scan of the summaries over the CTA
+        Scan inc = mine;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            Scan up;
+            up.v = __shfl_up_sync(0xffffffffu, inc.v, o);
+            up.c = __shfl_up_sync(0xffffffffu, inc.c, o);
+            up.f = __shfl_up_sync(0xffffffffu, inc.f, o);
+            if (lane >= o) inc = combine(up, inc);
+        }
+        if (lane == 31) s_warp[warp] = inc;
+        Scan ex;
+        ex.v = __shfl_up_sync(0xffffffffu, inc.v, 1);
+        ex.c = __shfl_up_sync(0xffffffffu, inc.c, 1);
+        ex.f = __shfl_up_sync(0xffffffffu, inc.f, 1);
+        if (lane == 0) { ex.v = 0.0; ex.c = 0; ex.f = 0; }
+        __syncthreads();
+        Scan wp; wp.v = 0.0; wp.c = 0; wp.f = 0;
+        for (int w2 = 0; w2 < warp; w2++) wp = combine(wp, s_warp[w2]);
+        const Scan cin = combine(wp, ex);
+
+        // ---- pass 2: walk again, close segments
+        double run = cin.v; uint32_t cnt = cin.c; bool seen_head = cin.f != 0;
+        if (tid == 0 && edge_continues) { run = carry.sum; cnt = carry.cnt; }
+        // the carried segment ended exactly at the tile edge: thread 0 retires it
+        if (tid == 0 && carry.valid && !edge_continues) {
+            if (carry_open) out.first = carry; else apply_update(P, carry.key, carry.sum, carry.cnt);
+        }
+#pragma unroll
+        for (int i = 0; i < kUpdItems; i++) {
+            const int q = q0 + i;
+            if (q < n_tile) {
+                const bool head = q > 0 && kk[i] != (i == 0 ? prev_key : kk[i - 1]);
+                if (head) { run = 0.0; cnt = 0; seen_head = true; }
+                run += (double)vv[i]; cnt += 1;
+                // open: the segment reaches the tile's left edge and, through it, the CTA's left edge
+                const bool open = !seen_head && edge_open;
+                if (q == n_tile - 1) {
+                    s_carry.sum = run; s_carry.key = kk[i]; s_carry.cnt = cnt; s_carry.valid = 1; s_carry.pad = 0;
+                    s_carry_open = open ? 1u : 0u;
+                } else if (s_key[pad_idx(q + 1)] != kk[i]) {
+                    if (open) {
+                        out.first.sum = run; out.first.key = kk[i]; out.first.cnt = cnt; out.first.valid = 1;
+                    } else {
+                        apply_update(P, kk[i], run, cnt);
+                    }
+                }
+            }
+        }
+        __syncthreads();
+    }
+    // ---- publish this CTA's boundary records
+    // out.first may have been produced by any thread: reduce through shared memory.
+    __shared__ SegRec s_first;
+    if (tid == 0) s_first.valid = 0;
+    __syncthreads();
+    if (out.first.valid) s_first = out.first;   // at most one thread of the CTA holds a valid first
+    __syncthreads();
+    if (tid == 0) {
+        Boundary b;
+        b.first = s_first;
+        b.last.valid = 0; b.last.sum = 0; b.last.key = 0; b.last.cnt = 0; b.last.pad = 0;
+        if (lo < hi) {
+            const SegRec carry = s_carry;
+            if (s_carry_open) b.first = carry;   // the whole CTA range is one segment
+            else b.last = carry;
+        }
+        P.boundary[blockIdx.x] = b;
+        __threadfence();
+        const uint32_t ticket = atomicAdd(P.done_counter, 1u);
+        s_is_last = ticket == gridDim.x - 1;
+    }
+    __syncthreads();
+    if (!s_is_last) return;
+    // ---- the last CTA to finish merges the boundary records in CTA order
+    __threadfence();
+    const volatile SegRec *rec = reinterpret_cast<const volatile SegRec *>(P.boundary);
+    const int n_rec = 2 * (int)gridDim.x;
+    for (int i = tid; i < n_rec; i += kUpdThreads) {
+        if (!rec[i].valid) continue;
+        const uint32_t key = rec[i].key;
+        // a run starts here unless the previous valid record has the same feature
+        int j = i - 1;
+        while (j >= 0 && !rec[j].valid) j--;
+        if (j >= 0 && rec[j].key == key) continue;
+        double sum = rec[i].sum; uint32_t cnt = rec[i].cnt;
+        for (j = i + 1; j < n_rec; j++) {
+            if (!rec[j].valid) continue;
+            if (rec[j].key != key) break;
+            sum += rec[j].sum; cnt += rec[j].cnt;
+        }
+        apply_update(P, key, sum, cnt);
+    }
+    if (tid == 0) *P.done_counter = 0;   // ready for the next launch on this stream
+}
+
+// ---- model table --------------------------------------------------------------------
+
+constexpr int kExpThreads = 256;
+constexpr int kExpTile = 4096;
+
+__device__ __forceinline__ bool emit(const float *w, const uint8_t *touched, int64_t j)
+{
+    return touched ? touched[j] != 0 : w[j] != 0.0f;
+}
+
+__global__ void __launch_bounds__(kExpThreads)
+export_count_kernel(const float *__restrict__ w, const uint8_t *__restrict__ touched, int64_t dims,
+                    uint32_t *__restrict__ counts)
+{
+    __shared__ uint32_t s_tot;
+    if (threadIdx.x == 0) s_tot = 0;
+    __syncthreads();
+    const int64_t j0 = (int64_t)blockIdx.x * kExpTile;
+    uint32_t c = 0;
+    for (int i = 0; i < kExpTile / kExpThreads; i++) {
+        const int64_t j = j0 + i * kExpThreads + threadIdx.x;
+        if (j < dims && emit(w, touched, j)) c++;
+    }
+    c = __reduce_add_sync(0xffffffffu, c);
+    if ((threadIdx.x & 31) == 0 && c) atomicAdd(&s_tot, c);
+    __syncthreads();
+    if (threadIdx.x == 0) counts[blockIdx.x] = s_tot;
+}
+
+__global__ void __launch_bounds__(1024) export_scan_kernel(uint32_t *__restrict__ counts, int n, int64_t *total)
+{
+    // exclusive scan of counts[0..n) by one CTA; counts[n] and *total receive the sum
+    __shared__ uint32_t warp_tot[32];
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    const int per = (n + 1023) / 1024;
+    const int lo = t * per, hi = min(lo + per, n);
+    uint32_t s = 0;
+    for (int i = lo; i < hi; i++) s += counts[i];
+    uint32_t inc = s;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { uint32_t v = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += v; }
+    if (lane == 31) warp_tot[warp] = inc;
+    __syncthreads();
+    if (warp == 0) {
+        uint32_t v = warp_tot[lane], iv = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { uint32_t u = __shfl_up_sync(0xffffffffu, iv, o); if (lane >= o) iv += u; }
+        warp_tot[lane] = iv - v;
+        if (lane == 31) *total = (int64_t)iv;
+    }
+    __syncthreads();
+    uint32_t run = warp_tot[warp] + inc - s;
+    for (int i = lo; i < hi; i++) { uint32_t v = counts[i]; counts[i] = run; run += v; }
+}
+
+__global__ void __launch_bounds__(kExpThreads)
+export_write_kernel(const float *__restrict__ w, const uint8_t *__restrict__ touched, int64_t dims,
+                    const uint32_t *__restrict__ offsets, int32_t *__restrict__ feature, float *__restrict__ weight)
+{
+    __shared__ uint32_t warp_tot[kExpThreads / 32];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int64_t j0 = (int64_t)blockIdx.x * kExpTile;
+    uint32_t base = offsets[blockIdx.x];
+    // blocked arrangement keeps the output ascending: thread t owns 16 consecutive features
+    const int per = kExpTile / kExpThreads;
+    uint32_t flags = 0;
+    for (int i = 0; i < per; i++) {
+        const int64_t j = j0 + (int64_t)threadIdx.x * per + i;
+        if (j < dims && emit(w, touched, j)) flags |= 1u << i;
+    }
+    const uint32_t c = __popc(flags);
+    uint32_t inc = c;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { uint32_t v = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += v; }
+    if (lane == 31) warp_tot[warp] = inc;
+    __syncthreads();
+    uint32_t wbase = 0;
+    for (int w2 = 0; w2 < warp; w2++) wbase += warp_tot[w2];
+    uint32_t pos = base + wbase + inc - c;
+    for (int i = 0; i < per; i++) {
+        if (flags & (1u << i)) {
+            const int64_t j = j0 + (int64_t)threadIdx.x * per + i;
+            feature[pos] = (int32_t)j;
+            weight[pos] = w[j];
+            pos++;
+        }
+    }
+}
+
+__global__ void scale_kernel(float *__restrict__ p, int64_t n, float scale)
+{
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+        p[i] = __fmul_rn(p[i], scale);
+}
+
+__global__ void fill_u32_kernel(uint32_t *__restrict__ p, int64_t n, uint32_t v)
+{
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+        p[i] = v;
+}
+
+int grid_for(int64_t ctas_wanted, int per_sm)
+{
+    const int64_t cap = (int64_t)kNumSMs * per_sm;
+    if (ctas_wanted < 1) ctas_wanted = 1;
+    return (int)(ctas_wanted < cap ? ctas_wanted : cap);
+}
+
+}  // namespace
+
+hm_status launch_linear_forward(Launcher &L, const LinearArgs &a, const int64_t *d_rowptr, int64_t row0,
+                                int32_t n_rows, int64_t block_row0, const uint32_t *d_feature,
+                                const float *d_value, const float *d_label, float *d_margin,
+                                float *d_dloss, float *d_contrib, uint32_t *d_bad, int64_t nnz_hint)
+{
+    if (n_rows <= 0) return HM_OK;
+    FwdParams P;
+    P.w = a.w; P.rowptr = d_rowptr; P.feature = d_feature; P.value = d_value; P.label = d_label;
+    P.margin = d_margin; P.dloss = d_dloss; P.contrib = d_contrib;
+    P.block_row0 = block_row0; P.row0 = row0; P.n_rows = n_rows;
+    P.task = a.cfg.task; P.loss = a.cfg.loss; P.write_contrib = 1;
+    P.dims = (uint32_t)a.cfg.dims; P.bad = d_bad;
+    const int grid = grid_for(((int64_t)n_rows + 7) / 8, 8);
+    // algorithmic bytes: idx+val read, w gather, contrib write, label+rowptr+margin+dloss per row
+    const double bytes = 16.0 * (double)nnz_hint + 24.0 * (double)n_rows;
+    HM_LAUNCH(L, K_LIN_FORWARD, bytes, (linear_forward_kernel<<<grid, kFwdThreads, 0, L.stream>>>(P)));
+    HM_CUDA(cudaGetLastError());
+    return HM_OK;
+}
+
+hm_status launch_predict_linear(Launcher &L, const float *w, int64_t dims, int64_t n_rows, const int64_t *d_rowptr,
+                                const uint32_t *d_feature, const float *d_value, float *d_out, uint32_t *d_bad)
+{
+    if (n_rows <= 0) return HM_OK;
+    if (n_rows > 0x7fffffff) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "predict: too many rows in one call");
+    FwdParams P;
+    P.w = w; P.rowptr = d_rowptr; P.feature = d_feature; P.value = d_value; P.label = nullptr;
+    P.margin = d_out; P.dloss = nullptr; P.contrib = nullptr;
+    P.block_row0 = 0; P.row0 = 0; P.n_rows = (int32_t)n_rows;
+    P.task = 0; P.loss = 0; P.write_contrib = 0;
+    P.dims = (uint32_t)dims; P.bad = d_bad;
+    const int grid = grid_for((n_rows + 7) / 8, 8);
+    HM_LAUNCH(L, K_PREDICT, 0.0, (linear_forward_kernel<<<grid, kFwdThreads, 0, L.stream>>>(P)));
+    HM_CUDA(cudaGetLastError());
+    return HM_OK;
+}
+
+hm_status update_scratch_reserve(UpdateScratch &u)
+{
+    if (u.boundary) return HM_OK;
+    u.grid = kNumSMs * 2;
+    HM_CUDA(cudaMalloc(&u.boundary, (size_t)u.grid * sizeof(Boundary)));
+    HM_CUDA(cudaMalloc(&u.done_counter, sizeof(uint32_t)));
+    HM_CUDA(cudaMemset(u.done_counter, 0, sizeof(uint32_t)));
+    return HM_OK;
+}
+
+void update_scratch_free(UpdateScratch &u)
+{
+    cudaFree(u.boundary); cudaFree(u.done_counter);
+    u.boundary = nullptr; u.done_counter = nullptr; u.grid = 0;
+}
+
+hm_status launch_linear_update(Launcher &L, const LinearArgs &a, const StepScalars &sc, UpdateScratch &us,
+                               const uint32_t *d_sorted_key, const uint32_t *d_sorted_pay,
+                               const uint32_t *d_seg_off, int seg, const float *d_contrib, int64_t nnz_hint)
+{
+    UpdParams P;
+    P.w = a.w; P.state = a.state; P.touched = nullptr;
+    P.skey = d_sorted_key; P.spay = d_sorted_pay; P.contrib = d_contrib; P.seg_off = d_seg_off;
+    P.boundary = reinterpret_cast<Boundary *>(us.boundary); P.done_counter = us.done_counter;
+    P.seg = seg; P.dims = (uint32_t)a.cfg.dims;
+    P.opt = a.cfg.opt; P.reg = a.cfg.reg; P.grad_norm = a.cfg.grad_norm; P.state_width = a.state_width;
+    P.eta = sc.eta; P.adam_alpha = sc.adam_alpha; P.lambda = a.cfg.lambda; P.eps = a.cfg.eps; P.rho = a.cfg.rho;
+    P.beta1 = a.cfg.beta1; P.beta2 = a.cfg.beta2; P.alpha = a.cfg.alpha; P.beta = a.cfg.beta;
+    P.lambda1 = a.cfg.lambda1; P.lambda2 = a.cfg.lambda2;
+    P.n_rows = (double)sc.n_rows;
+    int64_t tiles = (nnz_hint + kUpdTile - 1) / kUpdTile;
+    int grid = grid_for(tiles, 2);
+    if (grid > us.grid) grid = us.grid;
+    // algorithmic bytes: sorted key+payload, contrib gather; state traffic is per unique feature (unknown here)
+    const double bytes = 12.0 * (double)nnz_hint;
+    HM_LAUNCH(L, K_LIN_UPDATE, bytes, (linear_update_kernel<<<grid, kUpdThreads, 0, L.stream>>>(P)));
+    HM_CUDA(cudaGetLastError());
+    return HM_OK;
+}
+
+hm_status launch_export_count(Launcher &L, ExportScratch &es, const float *w, const uint8_t *touched,
+                              int64_t dims, int64_t *d_total)
+{
+    const int64_t ctas = (dims + kExpTile - 1) / kExpTile;
+    if (ctas + 1 > es.cap) {
+        if (es.counts) cudaFree(es.counts);
+        es.counts = nullptr;
+        HM_CUDA(cudaMalloc(&es.counts, (size_t)(ctas + 1) * sizeof(uint32_t)));
+        es.cap = ctas + 1;
+    }
+    HM_LAUNCH(L, K_EXPORT, 4.0 * (double)dims,
+              (export_count_kernel<<<(unsigned)ctas, kExpThreads, 0, L.stream>>>(w, touched, dims, es.counts)));
+    HM_LAUNCH(L, K_EXPORT, 0.0, (export_scan_kernel<<<1, 1024, 0, L.stream>>>(es.counts, (int)ctas, d_total)));
+    HM_CUDA(cudaGetLastError());
+    return HM_OK;
+}
+
+hm_status launch_export_write(Launcher &L, ExportScratch &es, const float *w, const uint8_t *touched,
+                              int64_t dims, int32_t *d_feature, float *d_weight)
+{
+    const int64_t ctas = (dims + kExpTile - 1) / kExpTile;
+    HM_LAUNCH(L, K_EXPORT, 4.0 * (double)dims,
+              (export_write_kernel<<<(unsigned)ctas, kExpThreads, 0, L.stream>>>(w, touched, dims, es.counts,
+                                                                                 d_feature, d_weight)));
+    HM_CUDA(cudaGetLastError());
+    return HM_OK;
+}
+
+hm_status launch_scale(Launcher &L, float *p, int64_t n, float scale)
+{
+    if (n <= 0) return HM_OK;
+    HM_LAUNCH(L, K_MISC, 8.0 * (double)n,
+              (scale_kernel<<<grid_for((n + 1023) / 1024, 8), 256, 0, L.stream>>>(p, n, scale)));
+    HM_CUDA(cudaGetLastError());
+    return HM_OK;
+}
+
+hm_status launch_fill_u32(Launcher &L, uint32_t *p, int64_t n, uint32_t v)
+{
+    if (n <= 0) return HM_OK;
+    HM_LAUNCH(L, K_MISC, 4.0 * (double)n,
+              (fill_u32_kernel<<<grid_for((n + 1023) / 1024, 8), 256, 0, L.stream>>>(p, n, v)));
+    HM_CUDA(cudaGetLastError());
+    return HM_OK;
+}
+
+}  // namespace hm

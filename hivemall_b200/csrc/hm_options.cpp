@@ -1,0 +1,243 @@
+// hm_options.cpp -- UDTF option-string parser.
+//
+// Stands in for the option handling of the train_classifier / train_regressor /
+// train_fm UDTFs that BASELINE.json names ("keeping the UDTF option strings").
+// The reference mount has no source (README.md:20-22), so the grammar below is this
+// library's own: whitespace-separated "-name value" pairs and bare "-flag"s, names
+// case-sensitive, enum values case-insensitive.  The option names that BASELINE.json
+// itself spells out (-loss logloss, -opt AdaGrad, -mini_batch 128) are accepted
+// verbatim.  Anything unknown is an error, never ignored.
+#include "hm_internal.h"
+#include <algorithm>
+#include <cctype>
+#include <cerrno>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <sstream>
+
+namespace hm {
+
+static thread_local char g_err[1024] = "";
+
+void set_error(const char *fmt, ...)
+{
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+const char *last_error_cstr() { return g_err; }
+
+static std::string lower(std::string s)
+{
+    std::transform(s.begin(), s.end(), s.begin(), [](unsigned char c) { return (char)std::tolower(c); });
+    return s;
+}
+
+static bool to_f(const std::string &v, double *out)
+{
+    errno = 0;
+    char *end = nullptr;
+    double d = std::strtod(v.c_str(), &end);
+    if (end == v.c_str() || *end != '\0' || errno == ERANGE || !std::isfinite(d)) return false;
+    *out = d;
+    return true;
+}
+
+static bool to_i(const std::string &v, int64_t *out)
+{
+    errno = 0;
+    char *end = nullptr;
+    long long d = std::strtoll(v.c_str(), &end, 10);
+    if (end == v.c_str() || *end != '\0' || errno == ERANGE) return false;
+    *out = (int64_t)d;
+    return true;
+}
+
+static void defaults(hm_config *c, int task)
+{
+    std::memset(c, 0, sizeof(*c));
+    c->task = task;
+    c->loss = task == HM_TASK_REGRESSOR ? HM_LOSS_SQUARED : HM_LOSS_LOG;
+    c->opt = task == HM_TASK_FM ? HM_OPT_SGD : HM_OPT_ADAGRAD;
+    c->eta_sched = HM_ETA_FIXED;
+    c->reg = HM_REG_NONE;
+    c->grad_norm = HM_NORM_BATCH;
+    c->mini_batch = 1;
+    c->iters = 1;
+    c->dims = (int64_t)1 << 24;
+    c->total_steps = 10000.0;
+    c->eta0 = task == HM_TASK_FM ? 0.05f : 0.1f;
+    c->power_t = 0.1f;
+    c->lambda = 1e-4f;
+    c->eps = 1e-6f;
+    c->rho = 0.95f;
+    c->beta1 = 0.9f;
+    c->beta2 = 0.999f;
+    c->alpha = 0.1f;
+    c->beta = 1.0f;
+    c->lambda1 = 0.001f;
+    c->lambda2 = 0.0f;
+    c->factors = 5;
+    c->fm_classification = 0;
+    c->sigma = 0.1f;
+    c->lambda_w0 = 0.01f;
+    c->lambda_w = 0.01f;
+    c->lambda_v = 0.01f;
+    c->seed = 31;
+    c->mix_interval = 0;
+    c->hash_seed = 0x9747b28cu;
+}
+
+hm_status parse_options(const char *function_name, const char *options, hm_config *out)
+{
+    if (!function_name || !out) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "function_name and out must not be NULL");
+    std::string fn = function_name;
+    int task;
+    if (fn == "train_classifier") task = HM_TASK_CLASSIFIER;
+    else if (fn == "train_regressor") task = HM_TASK_REGRESSOR;
+    else if (fn == "train_fm") task = HM_TASK_FM;
+    else HM_FAIL(HM_ERR_INVALID_ARGUMENT, "unknown function '%s' (expected train_classifier, train_regressor or train_fm)", function_name);
+    hm_config c;
+    defaults(&c, task);
+
+    std::vector<std::string> tok;
+    {
+        std::istringstream is(options ? options : "");
+        std::string t;
+        while (is >> t) tok.push_back(t);
+    }
+    bool loss_given = false;
+    for (size_t i = 0; i < tok.size(); i++) {
+        const std::string &name = tok[i];
+        if (name.size() < 2 || name[0] != '-')
+            HM_FAIL(HM_ERR_INVALID_ARGUMENT, "expected an option starting with '-', got '%s'", name.c_str());
+        // ---- flags
+        if (name == "-classification" || name == "-c") {
+            if (task != HM_TASK_FM) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "%s is a train_fm option", name.c_str());
+            c.fm_classification = 1;
+            continue;
+        }
+        if (name == "-dense" || name == "-densemodel") continue;  // the model replica is always dense
+        // ---- valued options
+        if (i + 1 >= tok.size()) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "option '%s' needs a value", name.c_str());
+        const std::string &v = tok[++i];
+        const std::string lv = lower(v);
+        double d = 0;
+        int64_t n = 0;
+        auto need_f = [&](double lo, double hi) -> bool {
+            if (!to_f(v, &d) || d < lo || d > hi) {
+                set_error("option '%s': '%s' is not a number in [%g, %g]", name.c_str(), v.c_str(), lo, hi);
+                return false;
+            }
+            return true;
+        };
+        auto need_i = [&](int64_t lo, int64_t hi) -> bool {
+            if (!to_i(v, &n) || n < lo || n > hi) {
+                set_error("option '%s': '%s' is not an integer in [%lld, %lld]", name.c_str(), v.c_str(),
+                          (long long)lo, (long long)hi);
+                return false;
+            }
+            return true;
+        };
+#define NEED_F(lo, hi) if (!need_f((lo), (hi))) return HM_ERR_INVALID_ARGUMENT
+#define NEED_I(lo, hi) if (!need_i((lo), (hi))) return HM_ERR_INVALID_ARGUMENT
+        if (name == "-loss" || name == "-loss_function") {
+            if (task == HM_TASK_FM) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "-loss is not a train_fm option (use -classification)");
+            if (lv == "logloss" || lv == "logistic" || lv == "log") c.loss = HM_LOSS_LOG;
+            else if (lv == "hinge" || lv == "hingeloss") c.loss = HM_LOSS_HINGE;
+            else if (lv == "squared" || lv == "squaredloss" || lv == "squared_loss") c.loss = HM_LOSS_SQUARED;
+            else HM_FAIL(HM_ERR_INVALID_ARGUMENT, "option -loss: unknown loss '%s' (logloss, hinge, squared)", v.c_str());
+            loss_given = true;
+        } else if (name == "-opt" || name == "-optimizer") {
+            if (lv == "sgd") c.opt = HM_OPT_SGD;
+            else if (lv == "adagrad") c.opt = HM_OPT_ADAGRAD;
+            else if (lv == "adadelta") c.opt = HM_OPT_ADADELTA;
+            else if (lv == "adam") c.opt = HM_OPT_ADAM;
+            else if (lv == "ftrl") c.opt = HM_OPT_FTRL;
+            else HM_FAIL(HM_ERR_INVALID_ARGUMENT, "option -opt: unknown optimizer '%s' (sgd, adagrad, adadelta, adam, ftrl)", v.c_str());
+        } else if (name == "-mini_batch" || name == "-mini_batch_size") {
+            NEED_I(1, (int64_t)1 << 26); c.mini_batch = (int32_t)n;
+        } else if (name == "-iters" || name == "-iter" || name == "-iterations") {
+            NEED_I(1, 1000000); c.iters = (int32_t)n;
+        } else if (name == "-dims" || name == "-feature_dimensions" || name == "-p" || name == "-num_features") {
+            NEED_I(1, (int64_t)1 << 31); c.dims = n;
+        } else if (name == "-eta0" || name == "-eta_0") {
+            NEED_F(0.0, 1e6); c.eta0 = (float)d;
+        } else if (name == "-eta") {
+            if (lv == "fixed") c.eta_sched = HM_ETA_FIXED;
+            else if (lv == "inverse" || lv == "inv" || lv == "invscaling") c.eta_sched = HM_ETA_INVERSE;
+            else if (lv == "simple") c.eta_sched = HM_ETA_SIMPLE;
+            else HM_FAIL(HM_ERR_INVALID_ARGUMENT, "option -eta: unknown schedule '%s' (fixed, inverse, simple)", v.c_str());
+        } else if (name == "-power_t") {
+            NEED_F(0.0, 10.0); c.power_t = (float)d;
+        } else if (name == "-total_steps" || name == "-t") {
+            NEED_F(1.0, 1e18); c.total_steps = d;
+        } else if (name == "-reg" || name == "-regularization") {
+            if (lv == "no" || lv == "none") c.reg = HM_REG_NONE;
+            else if (lv == "l1") c.reg = HM_REG_L1;
+            else if (lv == "l2") c.reg = HM_REG_L2;
+            else HM_FAIL(HM_ERR_INVALID_ARGUMENT, "option -reg: unknown regularization '%s' (no, l1, l2)", v.c_str());
+        } else if (name == "-lambda") {
+            NEED_F(0.0, 1e6); c.lambda = (float)d;
+        } else if (name == "-eps") {
+            NEED_F(0.0, 1.0); c.eps = (float)d;
+        } else if (name == "-rho" || name == "-decay") {
+            NEED_F(0.0, 1.0); c.rho = (float)d;
+        } else if (name == "-beta1") {
+            NEED_F(0.0, 0.999999); c.beta1 = (float)d;
+        } else if (name == "-beta2") {
+            NEED_F(0.0, 0.9999999); c.beta2 = (float)d;
+        } else if (name == "-alpha") {
+            NEED_F(1e-12, 1e6); c.alpha = (float)d;
+        } else if (name == "-beta") {
+            NEED_F(0.0, 1e6); c.beta = (float)d;
+        } else if (name == "-lambda1" || name == "-l1") {
+            NEED_F(0.0, 1e6); c.lambda1 = (float)d;
+        } else if (name == "-lambda2" || name == "-l2") {
+            NEED_F(0.0, 1e6); c.lambda2 = (float)d;
+        } else if (name == "-grad_norm") {
+            if (lv == "batch") c.grad_norm = HM_NORM_BATCH;
+            else if (lv == "count") c.grad_norm = HM_NORM_COUNT;
+            else if (lv == "sum") c.grad_norm = HM_NORM_SUM;
+            else HM_FAIL(HM_ERR_INVALID_ARGUMENT, "option -grad_norm: unknown mode '%s' (batch, count, sum)", v.c_str());
+        } else if (name == "-factors" || name == "-factor" || name == "-f" || name == "-k") {
+            if (task != HM_TASK_FM) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "%s is a train_fm option", name.c_str());
+            NEED_I(1, 256); c.factors = (int32_t)n;
+        } else if (name == "-sigma") {
+            NEED_F(0.0, 1e3); c.sigma = (float)d;
+        } else if (name == "-lambda0" || name == "-lambda_w0") {
+            NEED_F(0.0, 1e6); c.lambda_w0 = (float)d;
+        } else if (name == "-lambdaW" || name == "-lambda_w") {
+            NEED_F(0.0, 1e6); c.lambda_w = (float)d;
+        } else if (name == "-lambdaV" || name == "-lambda_v") {
+            NEED_F(0.0, 1e6); c.lambda_v = (float)d;
+        } else if (name == "-seed") {
+            NEED_I(0, 0xffffffffLL); c.seed = (uint32_t)n;
+        } else if (name == "-hash_seed") {
+            NEED_I(0, 0xffffffffLL); c.hash_seed = (uint32_t)n;
+        } else if (name == "-mix_interval") {
+            NEED_I(0, (int64_t)1 << 30); c.mix_interval = (int32_t)n;
+        } else {
+            HM_FAIL(HM_ERR_INVALID_ARGUMENT, "unknown option '%s' for %s", name.c_str(), function_name);
+        }
+#undef NEED_F
+#undef NEED_I
+    }
+    // cross-option checks
+    if (task == HM_TASK_CLASSIFIER && c.loss == HM_LOSS_SQUARED && loss_given)
+        ;  // allowed: squared loss on +-1 targets
+    if (task == HM_TASK_REGRESSOR && c.loss != HM_LOSS_SQUARED)
+        HM_FAIL(HM_ERR_INVALID_ARGUMENT, "train_regressor supports -loss squared only");
+    if (task == HM_TASK_FM && c.opt != HM_OPT_SGD && c.opt != HM_OPT_ADAGRAD)
+        HM_FAIL(HM_ERR_INVALID_ARGUMENT, "train_fm supports -opt sgd or adagrad");
+    if (task == HM_TASK_FM) c.loss = c.fm_classification ? HM_LOSS_LOG : HM_LOSS_SQUARED;
+    *out = c;
+    return HM_OK;
+}
+
+}  // namespace hm

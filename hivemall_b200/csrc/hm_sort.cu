@@ -1,0 +1,338 @@
+// hm_sort.cu -- stable segmented LSD radix sort: the "sort-by-feature" half of the
+// deterministic gradient reduction that BASELINE.json's north_star asks for ("the loss
+// gradient fused with a deterministic sort-by-feature segmented reduction (no float
+// atomics)").  No reference source exists to cite (README.md:20-22).
+//
+// One launch set sorts up to kMaxSegs mini-batches ("segments") of an ingest block at
+// once.  Segment s is the element range [seg_off[s], seg_off[s+1]) of the block's CSR;
+// inside each segment elements are ordered by feature id, ties by original position
+// (stable), so the later per-feature sum always adds rows in row order.
+//
+// Per 8-bit digit pass:  hist (reads keys, 4 B/elem)  ->  two tiny scans  ->
+// scatter (reads key+payload, writes key+payload, 16 B/elem).  The first pass reads the
+// CSR feature array directly and synthesises the payload (element position), so no copy
+// of the input is made.  Integer counting only; atomics are integer (order-independent).
+#include "hm_internal.h"
+
+namespace hm {
+
+const char *const kKernelNames[K_NUM_KERNELS] = {
+    "hash", "seg_prep", "sort_hist", "sort_scan", "sort_scatter", "linear_forward",
+    "linear_update", "fm_forward", "fm_update", "predict", "export", "misc"};
+
+namespace {
+
+constexpr int kSortThreads = 256;
+constexpr int kSortWarps = kSortThreads / 32;
+constexpr int kSortItems = kSortTile / kSortThreads;  // 16
+constexpr int kRadix = 256;
+
+__global__ void seg_prep_kernel(const int64_t *__restrict__ rowptr, int64_t row0, int64_t n_rows,
+                                int32_t mini_batch, int n_segs, uint32_t *__restrict__ seg_off,
+                                uint32_t *__restrict__ seg_tile_off)
+{
+    __shared__ uint32_t off[kMaxSegs + 1];
+    const int t = threadIdx.x;
+    const int64_t base = rowptr[row0];
+    for (int s = t; s <= n_segs; s += blockDim.x) {
+        int64_t r = (int64_t)s * mini_batch;
+        if (r > n_rows) r = n_rows;
+        off[s] = (uint32_t)(rowptr[row0 + r] - base);
+        seg_off[s] = off[s];
+    }
+    __syncthreads();
+    if (t == 0) {
+        uint32_t run = 0;
+        for (int s = 0; s < n_segs; s++) {
+            seg_tile_off[s] = run;
+            run += (off[s + 1] - off[s] + kSortTile - 1) / kSortTile;
+        }
+        seg_tile_off[n_segs] = run;
+    }
+}
+
+// Which segment does global tile index `tile` belong to?  (last s with tile_off[s] <= tile)
+__device__ __forceinline__ int find_seg(const uint32_t *tile_off, int n_segs, uint32_t tile)
+{
+    int lo = 0, hi = n_segs;  // invariant: tile_off[lo] <= tile < tile_off[hi]
+    while (hi - lo > 1) {
+        int mid = (lo + hi) >> 1;
+        if (tile_off[mid] <= tile) lo = mid; else hi = mid;
+    }
+    return lo;
+}
+
+__global__ void __launch_bounds__(kSortThreads)
+sort_hist_kernel(const uint32_t *__restrict__ keys, const uint32_t *__restrict__ seg_off,
+                 const uint32_t *__restrict__ seg_tile_off, int n_segs, int shift,
+                 uint32_t *__restrict__ tile_hist, uint32_t *__restrict__ row_sum)
+{
+    __shared__ uint32_t s_off[kMaxSegs + 1], s_toff[kMaxSegs + 1];
+    __shared__ uint32_t hist[kSortWarps][kRadix];
+    for (int s = threadIdx.x; s <= n_segs; s += kSortThreads) { s_off[s] = seg_off[s]; s_toff[s] = seg_tile_off[s]; }
+    __syncthreads();
+    const uint32_t total = s_toff[n_segs];
+    const int warp = threadIdx.x >> 5;
+    for (uint32_t tile = blockIdx.x; tile < total; tile += gridDim.x) {
+        const int seg = find_seg(s_toff, n_segs, tile);
+        const uint32_t tis = tile - s_toff[seg], nt = s_toff[seg + 1] - s_toff[seg];
+        const uint32_t e0 = s_off[seg] + tis * kSortTile;
+        const uint32_t e1 = min(e0 + (uint32_t)kSortTile, s_off[seg + 1]);
+#pragma unroll
+        for (int w = 0; w < kSortWarps; w++) hist[w][threadIdx.x] = 0;
+        __syncthreads();
+        uint32_t k[kSortItems];
+#pragma unroll
+        for (int i = 0; i < kSortItems; i++) {
+            const uint32_t e = e0 + i * kSortThreads + threadIdx.x;
+            k[i] = e < e1 ? __ldg(keys + e) : 0u;
+        }
+#pragma unroll
+        for (int i = 0; i < kSortItems; i++) {
+            const uint32_t e = e0 + i * kSortThreads + threadIdx.x;
+            if (e < e1) atomicAdd(&hist[warp][(k[i] >> shift) & (kRadix - 1)], 1u);
+        }
+        __syncthreads();
+        uint32_t c = 0;
+#pragma unroll
+        for (int w = 0; w < kSortWarps; w++) c += hist[w][threadIdx.x];
+        tile_hist[(size_t)s_toff[seg] * kRadix + (size_t)threadIdx.x * nt + tis] = c;
+        if (c) atomicAdd(&row_sum[seg * kRadix + threadIdx.x], c);
+        __syncthreads();
+    }
+}
+
+// In-place exclusive scan of row_sum[0..n) by one CTA of 1024 threads.
+__global__ void __launch_bounds__(1024) scan_rows_kernel(uint32_t *__restrict__ row_sum, int n)
+{
+    __shared__ uint32_t warp_tot[32];
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    const int per = (n + 1023) / 1024;
+    const int lo = t * per, hi = min(lo + per, n);
+    uint32_t s = 0;
+    for (int i = lo; i < hi; i++) s += row_sum[i];
+    uint32_t inc = s;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { uint32_t v = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += v; }
+    if (lane == 31) warp_tot[warp] = inc;
+    __syncthreads();
+    if (warp == 0) {
+        uint32_t v = warp_tot[lane], iv = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { uint32_t u = __shfl_up_sync(0xffffffffu, iv, o); if (lane >= o) iv += u; }
+        warp_tot[lane] = iv - v;
+    }
+    __syncthreads();
+    uint32_t run = warp_tot[warp] + inc - s;
+    for (int i = lo; i < hi; i++) { uint32_t v = row_sum[i]; row_sum[i] = run; run += v; }
+}
+
+// One warp per (segment, digit) row of tile_hist: exclusive scan along the row, plus row base.
+__global__ void __launch_bounds__(kSortThreads)
+scan_tiles_kernel(uint32_t *__restrict__ tile_hist, const uint32_t *__restrict__ row_base,
+                  const uint32_t *__restrict__ seg_tile_off, int n_segs)
+{
+    const int lane = threadIdx.x & 31;
+    const int row = blockIdx.x * kSortWarps + (threadIdx.x >> 5);
+    if (row >= n_segs * kRadix) return;
+    const int seg = row / kRadix, d = row % kRadix;
+    const uint32_t t0 = seg_tile_off[seg], nt = seg_tile_off[seg + 1] - t0;
+    uint32_t *p = tile_hist + (size_t)t0 * kRadix + (size_t)d * nt;
+    uint32_t run = row_base[row];
+    for (uint32_t k0 = 0; k0 < nt; k0 += 32) {
+        const uint32_t k = k0 + lane;
+        const uint32_t v = k < nt ? p[k] : 0u;
+        uint32_t inc = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { uint32_t u = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += u; }
+        if (k < nt) p[k] = run + inc - v;
+        run += __shfl_sync(0xffffffffu, inc, 31);
+    }
+}
+
+template <bool FIRST>
+__global__ void __launch_bounds__(kSortThreads)
+sort_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint32_t *__restrict__ pay_in,
+                    uint32_t *__restrict__ keys_out, uint32_t *__restrict__ pay_out,
+                    const uint32_t *__restrict__ seg_off, const uint32_t *__restrict__ seg_tile_off,
+                    int n_segs, int shift, const uint32_t *__restrict__ tile_hist)
+{
+    __shared__ uint32_t s_off[kMaxSegs + 1], s_toff[kMaxSegs + 1];
+    __shared__ uint32_t s_key[kSortTile], s_pay[kSortTile];
+    __shared__ uint32_t wcnt[kSortWarps][kRadix];
+    __shared__ uint32_t dig_base[kRadix], gofs[kRadix], warp_tot[kSortWarps];
+    for (int s = threadIdx.x; s <= n_segs; s += kSortThreads) { s_off[s] = seg_off[s]; s_toff[s] = seg_tile_off[s]; }
+    __syncthreads();
+    const uint32_t total = s_toff[n_segs];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t lt_mask = (1u << lane) - 1u;
+    for (uint32_t tile = blockIdx.x; tile < total; tile += gridDim.x) {
+        const int seg = find_seg(s_toff, n_segs, tile);
+        const uint32_t tis = tile - s_toff[seg], nt = s_toff[seg + 1] - s_toff[seg];
+        const uint32_t e0 = s_off[seg] + tis * kSortTile;
+        const uint32_t e1 = min(e0 + (uint32_t)kSortTile, s_off[seg + 1]);
+        // warp-striped load: warp w owns tile positions [w*512, (w+1)*512), round i, lane
+        uint32_t key[kSortItems], pay[kSortItems], rank[kSortItems];
+#pragma unroll
+        for (int i = 0; i < kSortItems; i++) {
+            const uint32_t e = e0 + warp * (32 * kSortItems) + i * 32 + lane;
+            key[i] = e < e1 ? __ldg(keys_in + e) : 0xffffffffu;
+            pay[i] = FIRST ? e : (e < e1 ? __ldg(pay_in + e) : 0u);
+        }
+#pragma unroll
+        for (int w = 0; w < kSortWarps; w++) wcnt[w][threadIdx.x] = 0;
+        __syncthreads();
+        // stable rank of every element among equal digits inside its warp
+#pragma unroll
+        for (int i = 0; i < kSortItems; i++) {
+            const uint32_t e = e0 + warp * (32 * kSortItems) + i * 32 + lane;
+            const bool valid = e < e1;
+            const uint32_t d = (key[i] >> shift) & (kRadix - 1);
+            const uint32_t active = __ballot_sync(0xffffffffu, valid);
+            uint32_t peers = 0, prev = 0;
+            if (valid) { peers = __match_any_sync(active, d); prev = wcnt[warp][d]; }
+            __syncwarp();
+            if (valid) {
+                const uint32_t r = __popc(peers & lt_mask);
+                if (r == 0) wcnt[warp][d] = prev + __popc(peers);
+                rank[i] = prev + r;
+            }
+            __syncwarp();
+        }
+        __syncthreads();
+        // per-digit: exclusive scan over warps, then exclusive scan over digits
+        {
+            const int d = threadIdx.x;
+            uint32_t run = 0;
+#pragma unroll
+            for (int w = 0; w < kSortWarps; w++) { uint32_t c = wcnt[w][d]; wcnt[w][d] = run; run += c; }
+            uint32_t inc = run;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) { uint32_t v = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += v; }
+            if (lane == 31) warp_tot[warp] = inc;
+            __syncthreads();
+            uint32_t wbase = 0;
+#pragma unroll
+            for (int w = 0; w < kSortWarps; w++) if (w < warp) wbase += warp_tot[w];
+            const uint32_t ex = wbase + inc - run;
+            dig_base[d] = ex;
+            gofs[d] = tile_hist[(size_t)s_toff[seg] * kRadix + (size_t)d * nt + tis] - ex;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int i = 0; i < kSortItems; i++) {
+            const uint32_t e = e0 + warp * (32 * kSortItems) + i * 32 + lane;
+            if (e < e1) {
+                const uint32_t d = (key[i] >> shift) & (kRadix - 1);
+                const uint32_t pos = dig_base[d] + wcnt[warp][d] + rank[i];
+                s_key[pos] = key[i];
+                s_pay[pos] = pay[i];
+            }
+        }
+        __syncthreads();
+        const uint32_t n_tile = e1 - e0;
+        for (uint32_t p = threadIdx.x; p < n_tile; p += kSortThreads) {
+            const uint32_t k = s_key[p];
+            const uint32_t g = gofs[(k >> shift) & (kRadix - 1)] + p;
+            keys_out[g] = k;
+            pay_out[g] = s_pay[p];
+        }
+        __syncthreads();
+    }
+}
+
+int persistent_grid(int64_t work_items, int per_sm)
+{
+    int64_t cap = (int64_t)kNumSMs * per_sm;
+    if (work_items < 1) work_items = 1;
+    return (int)(work_items < cap ? work_items : cap);
+}
+
+}  // namespace
+
+hm_status sort_scratch_reserve(SortScratch &s, int64_t elems)
+{
+    if (elems < 1) elems = 1;
+    if (!s.seg_off) {
+        HM_CUDA(cudaMalloc(&s.seg_off, (kMaxSegs + 1) * sizeof(uint32_t)));
+        HM_CUDA(cudaMalloc(&s.seg_tile_off, (kMaxSegs + 1) * sizeof(uint32_t)));
+        HM_CUDA(cudaMalloc(&s.row_sum, (size_t)kMaxSegs * kRadix * sizeof(uint32_t)));
+    }
+    if (elems > s.cap_elems) {
+        for (int b = 0; b < 2; b++) {
+            if (s.key[b]) cudaFree(s.key[b]);
+            if (s.pay[b]) cudaFree(s.pay[b]);
+            s.key[b] = s.pay[b] = nullptr;
+        }
+        if (s.tile_hist) cudaFree(s.tile_hist);
+        s.tile_hist = nullptr;
+        s.cap_elems = 0;
+        int64_t cap = elems + elems / 8;
+        for (int b = 0; b < 2; b++) {
+            HM_CUDA(cudaMalloc(&s.key[b], (size_t)cap * sizeof(uint32_t)));
+            HM_CUDA(cudaMalloc(&s.pay[b], (size_t)cap * sizeof(uint32_t)));
+        }
+        s.cap_tiles = cap / kSortTile + kMaxSegs + 1;
+        HM_CUDA(cudaMalloc(&s.tile_hist, (size_t)s.cap_tiles * kRadix * sizeof(uint32_t)));
+        s.cap_elems = cap;
+    }
+    return HM_OK;
+}
+
+void sort_scratch_free(SortScratch &s)
+{
+    for (int b = 0; b < 2; b++) { cudaFree(s.key[b]); cudaFree(s.pay[b]); s.key[b] = s.pay[b] = nullptr; }
+    cudaFree(s.tile_hist); cudaFree(s.row_sum); cudaFree(s.seg_off); cudaFree(s.seg_tile_off);
+    s.tile_hist = s.row_sum = s.seg_off = s.seg_tile_off = nullptr;
+    s.cap_elems = s.cap_tiles = 0;
+}
+
+hm_status launch_seg_prep(Launcher &L, SortScratch &s, const int64_t *d_rowptr, int64_t row0,
+                          int64_t n_rows, int32_t mini_batch, int n_segs)
+{
+    if (n_segs < 1 || n_segs > kMaxSegs) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "segment count %d out of range", n_segs);
+    HM_LAUNCH(L, K_SEG_PREP, 0.0,
+              (seg_prep_kernel<<<1, 256, 0, L.stream>>>(d_rowptr, row0, n_rows, mini_batch, n_segs, s.seg_off,
+                                                        s.seg_tile_off)));
+    HM_CUDA(cudaGetLastError());
+    return HM_OK;
+}
+
+hm_status launch_segmented_sort(Launcher &L, SortScratch &s, const uint32_t *d_feature_block,
+                                int64_t n_elems, int n_segs, int key_bits, int *out_buf)
+{
+    if (n_elems > s.cap_elems) HM_FAIL(HM_ERR_STATE, "sort scratch too small (%lld > %lld)", (long long)n_elems,
+                                       (long long)s.cap_elems);
+    int passes = (key_bits + 7) / 8;
+    if (passes < 1) passes = 1;
+    const int64_t max_tiles = n_elems / kSortTile + n_segs;
+    const int grid = persistent_grid(max_tiles, 6);
+    const int rows = n_segs * kRadix;
+    for (int p = 0; p < passes; p++) {
+        const int shift = 8 * p;
+        const uint32_t *kin = p == 0 ? d_feature_block : s.key[(p - 1) & 1];
+        const uint32_t *pin = p == 0 ? nullptr : s.pay[(p - 1) & 1];
+        uint32_t *kout = s.key[p & 1], *pout = s.pay[p & 1];
+        HM_CUDA(cudaMemsetAsync(s.row_sum, 0, (size_t)rows * sizeof(uint32_t), L.stream));
+        HM_LAUNCH(L, K_SORT_HIST, 4.0 * (double)n_elems,
+                  (sort_hist_kernel<<<grid, kSortThreads, 0, L.stream>>>(kin, s.seg_off, s.seg_tile_off, n_segs, shift,
+                                                                         s.tile_hist, s.row_sum)));
+        HM_LAUNCH(L, K_SORT_SCAN, 0.0, (scan_rows_kernel<<<1, 1024, 0, L.stream>>>(s.row_sum, rows)));
+        HM_LAUNCH(L, K_SORT_SCAN, 0.0,
+                  (scan_tiles_kernel<<<(rows + kSortWarps - 1) / kSortWarps, kSortThreads, 0, L.stream>>>(
+                      s.tile_hist, s.row_sum, s.seg_tile_off, n_segs)));
+        if (p == 0)
+            HM_LAUNCH(L, K_SORT_SCATTER, 12.0 * (double)n_elems,
+                      (sort_scatter_kernel<true><<<grid, kSortThreads, 0, L.stream>>>(
+                          kin, pin, kout, pout, s.seg_off, s.seg_tile_off, n_segs, shift, s.tile_hist)));
+        else
+            HM_LAUNCH(L, K_SORT_SCATTER, 16.0 * (double)n_elems,
+                      (sort_scatter_kernel<false><<<grid, kSortThreads, 0, L.stream>>>(
+                          kin, pin, kout, pout, s.seg_off, s.seg_tile_off, n_segs, shift, s.tile_hist)));
+    }
+    HM_CUDA(cudaGetLastError());
+    *out_buf = (passes - 1) & 1;
+    return HM_OK;
+}
+
+}  // namespace hm

@@ -1,0 +1,316 @@
+"""Host-side mirror of the UDTF interface of the hot path, over the C-ABI.
+
+BASELINE.json's north_star fixes the surface: `train_classifier`, `train_regressor`,
+`train_fm` UDTFs with option strings, the lifecycle initialize -> process(row)* ->
+close -> forward(model rows), plus the `mhash` / `feature_hashing` UDFs.  The reference
+mount has no source (/root/reference/README.md:20-22), so names follow north_star and
+argument meaning follows include/hivemall_b200.h.  The reference host language (Java)
+has no toolchain in this image; INTEGRATION.md shows the JNI stub over the same C-ABI.
+
+Everything computes on the GPU through libhivemall_b200.so.  numpy is used for host
+buffers only; torch is optional and only wraps device memory.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Iterable, Sequence
+
+import numpy as np
+
+from . import _lib
+from ._lib import HivemallError, HmConfig, HmStats, UDFArgumentError, check  # noqa: F401
+
+DEFAULT_NUM_FEATURES = 1 << 24
+DEFAULT_HASH_SEED = 0x9747B28C
+
+
+def _ptr(a) -> C.c_void_p:
+    if a is None:
+        return C.c_void_p(0)
+    if isinstance(a, np.ndarray):
+        return C.c_void_p(a.ctypes.data)
+    if isinstance(a, int):
+        return C.c_void_p(a)
+    if hasattr(a, "data_ptr"):  # torch tensor
+        return C.c_void_p(a.data_ptr())
+    raise TypeError(f"cannot take the address of {type(a)!r}")
+
+
+def _pack_strings(strings: Sequence[str | bytes]):
+    enc = [s.encode("utf-8") if isinstance(s, str) else bytes(s) for s in strings]
+    offsets = np.zeros(len(enc) + 1, dtype=np.int64)
+    if enc:
+        offsets[1:] = np.cumsum([len(b) for b in enc])
+    data = np.frombuffer(b"".join(enc), dtype=np.uint8) if enc else np.zeros(0, dtype=np.uint8)
+    return np.ascontiguousarray(data), offsets
+
+
+def parse_options(function_name: str, options: str = "") -> HmConfig:
+    cfg = HmConfig()
+    check(_lib.load().hm_parse_options(function_name.encode(), options.encode(), C.byref(cfg)))
+    return cfg
+
+
+def mhash(strings: Sequence[str | bytes], num_features: int = DEFAULT_NUM_FEATURES,
+          seed: int = DEFAULT_HASH_SEED, device: int = 0) -> np.ndarray:
+    """mhash UDF over a batch of feature names: MurmurHash3_x86_32 folded into
+    [0, num_features) on the GPU.  Returns int32 indices."""
+    data, offsets = _pack_strings(strings)
+    out = np.empty(len(strings), dtype=np.int32)
+    check(_lib.load().hm_mhash(_ptr(data), _ptr(offsets), len(strings), seed & 0xFFFFFFFF, num_features,
+                               _ptr(out), device))
+    return out
+
+
+def feature_hashing(features: Sequence[str | bytes], num_features: int = DEFAULT_NUM_FEATURES,
+                    seed: int = DEFAULT_HASH_SEED, device: int = 0):
+    """feature_hashing UDF over "name:value" strings -> (int32 index, float32 value)."""
+    data, offsets = _pack_strings(features)
+    idx = np.empty(len(features), dtype=np.int32)
+    val = np.empty(len(features), dtype=np.float32)
+    check(_lib.load().hm_feature_hashing(_ptr(data), _ptr(offsets), len(features), seed & 0xFFFFFFFF,
+                                         num_features, _ptr(idx), _ptr(val), device))
+    return idx, val
+
+
+def host_alloc(nbytes: int) -> tuple[int, np.ndarray]:
+    """Pinned host buffer (address, uint8 view).  Free with host_free(address)."""
+    p = C.c_void_p()
+    check(_lib.load().hm_host_alloc(C.byref(p), nbytes))
+    buf = (C.c_uint8 * max(nbytes, 1)).from_address(p.value)
+    return p.value, np.frombuffer(buf, dtype=np.uint8, count=nbytes)
+
+
+def host_free(address: int) -> None:
+    check(_lib.load().hm_host_free(C.c_void_p(address)))
+
+
+class _DeviceArray:
+    """Zero-copy view of a replica array for consumers of __cuda_array_interface__
+    (torch.as_tensor, cupy.asarray)."""
+
+    def __init__(self, ptr: int, n: int, owner):
+        self._owner = owner
+        self.__cuda_array_interface__ = {
+            "shape": (n,), "typestr": "<f4", "data": (ptr, False), "version": 3, "strides": None}
+
+
+class UDTF:
+    """One UDTF instance = one model replica on one GPU."""
+
+    function_name = ""
+
+    def __init__(self, options: str = "", device: int = 0, function_name: str | None = None):
+        self._lib = _lib.load()
+        self._h = C.c_void_p()
+        self.function_name = function_name or self.function_name
+        self.options = options
+        self.device = device
+        self.config = parse_options(self.function_name, options)
+        check(self._lib.hm_udtf_create(self.function_name.encode(), options.encode(), device, C.byref(self._h)))
+        self._rows: list = []
+        self._labels: list[float] = []
+        self._row_flush = 4096
+        self._keep = []  # host buffers that must outlive asynchronous copies
+
+    # ---- lifecycle ---------------------------------------------------------------
+    def process(self, features: Iterable, label: float) -> None:
+        """process() of one row.  `features` holds "name:value" strings or (index, value)
+        pairs.  Rows are buffered on the host and pushed in small batches; mini-batch
+        boundaries are those of the row stream, not of the pushes."""
+        self._rows.append(list(features))
+        self._labels.append(float(label))
+        if len(self._rows) >= self._row_flush:
+            self._flush_rows()
+
+    def _flush_rows(self) -> None:
+        if not self._rows:
+            return
+        rows, labels = self._rows, np.asarray(self._labels, dtype=np.float32)
+        self._rows, self._labels = [], []
+        rowptr = np.zeros(len(rows) + 1, dtype=np.int64)
+        rowptr[1:] = np.cumsum([len(r) for r in rows])
+        flat = [f for r in rows for f in r]
+        if flat and isinstance(flat[0], (str, bytes)):
+            data, offsets = _pack_strings(flat)
+            check(self._lib.hm_udtf_process_strings(self._h, len(rows), _ptr(rowptr), _ptr(data), _ptr(offsets),
+                                                    _ptr(labels)))
+            self.sync()
+        else:
+            idx = np.asarray([f[0] for f in flat], dtype=np.int32)
+            val = np.asarray([f[1] for f in flat], dtype=np.float32)
+            self.process_batch(rowptr, idx, val, labels)
+            self.sync()
+
+    def process_batch(self, rowptr, feature, value, label) -> None:
+        """process() of many rows at once from host CSR arrays (int64 rowptr, int32
+        feature, float32 value, float32 label).  Asynchronous: keep the arrays alive and
+        unmodified until sync()/close()."""
+        rowptr = np.ascontiguousarray(rowptr, dtype=np.int64)
+        feature = np.ascontiguousarray(feature, dtype=np.int32)
+        value = np.ascontiguousarray(value, dtype=np.float32)
+        label = np.ascontiguousarray(label, dtype=np.float32)
+        n = len(rowptr) - 1
+        if len(label) != n:
+            raise UDFArgumentError(1, f"label has {len(label)} entries for {n} rows")
+        if n and (rowptr[-1] > len(feature) or rowptr[-1] > len(value)):
+            raise UDFArgumentError(1, "rowptr points past the end of feature/value")
+        self._keep.append((rowptr, feature, value, label))
+        check(self._lib.hm_udtf_process(self._h, n, _ptr(rowptr), _ptr(feature), _ptr(value), _ptr(label)))
+
+    def process_pointers(self, n_rows: int, rowptr: int, feature: int, value: int, label: int) -> None:
+        """process() from raw HOST addresses (pinned buffers from host_alloc)."""
+        check(self._lib.hm_udtf_process(self._h, n_rows, _ptr(rowptr), _ptr(feature), _ptr(value), _ptr(label)))
+
+    def process_device(self, n_rows: int, nnz: int, rowptr, feature, value, label) -> None:
+        """process() of rows already in device memory (torch CUDA tensors or raw
+        addresses): int64 rowptr, int32 feature, float32 value/label."""
+        check(self._lib.hm_udtf_process_device(self._h, n_rows, nnz, _ptr(rowptr), _ptr(feature), _ptr(value),
+                                               _ptr(label)))
+
+    def close(self) -> int:
+        """close(): trains what is buffered, runs the remaining -iters passes, waits for
+        the GPU.  Returns the number of model-table rows."""
+        self._flush_rows()
+        n = C.c_int64()
+        check(self._lib.hm_udtf_close(self._h, C.byref(n)))
+        self._keep.clear()
+        return n.value
+
+    def forward(self):
+        """forward(): the model table as numpy arrays (feature int32, weight float32[,
+        Vif float32 (rows, factors)]), ascending feature order."""
+        n = self.close()
+        k = self.config.factors if self.function_name == "train_fm" else 0
+        feat = np.empty(n, dtype=np.int32)
+        wt = np.empty(n, dtype=np.float32)
+        vif = np.empty((n, k), dtype=np.float32) if k else None
+        m = C.c_int64()
+        check(self._lib.hm_udtf_forward(self._h, _ptr(feat), _ptr(wt), _ptr(vif), n, C.byref(m)))
+        if k:
+            return feat[: m.value], wt[: m.value], vif[: m.value]
+        return feat[: m.value], wt[: m.value]
+
+    def destroy(self) -> None:
+        if getattr(self, "_h", None) is not None and self._h:
+            self._lib.hm_udtf_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.destroy()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.destroy()
+
+    # ---- replica -----------------------------------------------------------------
+    def sync(self) -> None:
+        check(self._lib.hm_udtf_sync(self._h))
+        self._keep.clear()
+
+    @property
+    def stream(self) -> int:
+        return self._lib.hm_udtf_stream(self._h) or 0
+
+    @property
+    def step(self) -> int:
+        t = C.c_int64()
+        check(self._lib.hm_udtf_get_step(self._h, C.byref(t)))
+        return t.value
+
+    @step.setter
+    def step(self, t: int) -> None:
+        check(self._lib.hm_udtf_set_step(self._h, t))
+
+    def arrays(self) -> dict:
+        """name -> (device address, number of floats, interleave width)."""
+        out = {}
+        for i in range(self._lib.hm_udtf_num_arrays(self._h)):
+            name, p, n, w = C.c_char_p(), C.c_void_p(), C.c_int64(), C.c_int32()
+            check(self._lib.hm_udtf_array(self._h, i, C.byref(name), C.byref(p), C.byref(n), C.byref(w)))
+            out[name.value.decode()] = (p.value, n.value, w.value)
+        return out
+
+    def array_view(self, name: str) -> _DeviceArray:
+        p, n, _ = self.arrays()[name]
+        return _DeviceArray(p, n, self)
+
+    def _array_index(self, name: str) -> int:
+        names = list(self.arrays())
+        if name not in names:
+            raise KeyError(f"no replica array {name!r}; this learner has {names}")
+        return names.index(name)
+
+    def array_to_host(self, name: str) -> np.ndarray:
+        """Copy a replica array to the host (tests, checkpoints)."""
+        _, n, _ = self.arrays()[name]
+        out = np.empty(n, dtype=np.float32)
+        check(self._lib.hm_udtf_read_array(self._h, self._array_index(name), _ptr(out), n))
+        return out
+
+    def array_from_host(self, name: str, values) -> None:
+        """Overwrite a replica array from the host (warm start)."""
+        values = np.ascontiguousarray(values, dtype=np.float32).reshape(-1)
+        check(self._lib.hm_udtf_write_array(self._h, self._array_index(name), _ptr(values), len(values)))
+
+    def scale_replica(self, scale: float) -> None:
+        check(self._lib.hm_udtf_scale_replica(self._h, scale))
+
+    # ---- prediction --------------------------------------------------------------
+    def predict(self, rowptr, feature, value) -> np.ndarray:
+        rowptr = np.ascontiguousarray(rowptr, dtype=np.int64)
+        feature = np.ascontiguousarray(feature, dtype=np.int32)
+        value = np.ascontiguousarray(value, dtype=np.float32)
+        out = np.empty(len(rowptr) - 1, dtype=np.float32)
+        check(self._lib.hm_udtf_predict(self._h, len(out), _ptr(rowptr), _ptr(feature), _ptr(value), _ptr(out)))
+        return out
+
+    def predict_device(self, n_rows: int, rowptr, feature, value, out) -> None:
+        check(self._lib.hm_udtf_predict_device(self._h, n_rows, _ptr(rowptr), _ptr(feature), _ptr(value), _ptr(out)))
+
+    # ---- measurement ---------------------------------------------------------------
+    def stats(self) -> HmStats:
+        s = HmStats()
+        check(self._lib.hm_udtf_stats(self._h, C.byref(s)))
+        return s
+
+    def set_profiling(self, on: bool) -> None:
+        check(self._lib.hm_udtf_set_profiling(self._h, int(on)))
+
+    def kernel_times(self) -> dict:
+        """name -> dict(launches, ms, bytes) collected while profiling was on."""
+        out = {}
+        for i in range(self._lib.hm_udtf_num_kernels(self._h)):
+            name, n, ms, b = C.c_char_p(), C.c_int64(), C.c_double(), C.c_double()
+            check(self._lib.hm_udtf_kernel_time(self._h, i, C.byref(name), C.byref(n), C.byref(ms), C.byref(b)))
+            out[name.value.decode()] = {"launches": n.value, "ms": ms.value, "bytes": b.value}
+        return out
+
+
+class TrainClassifierUDTF(UDTF):
+    function_name = "train_classifier"
+
+
+class TrainRegressorUDTF(UDTF):
+    function_name = "train_regressor"
+
+
+class FactorizationMachineUDTF(UDTF):
+    function_name = "train_fm"
+
+
+def train_classifier(options: str = "", device: int = 0) -> TrainClassifierUDTF:
+    return TrainClassifierUDTF(options, device)
+
+
+def train_regressor(options: str = "", device: int = 0) -> TrainRegressorUDTF:
+    return TrainRegressorUDTF(options, device)
+
+
+def train_fm(options: str = "", device: int = 0) -> FactorizationMachineUDTF:
+    return FactorizationMachineUDTF(options, device)

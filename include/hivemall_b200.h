@@ -1,0 +1,206 @@
+/*
+ * hivemall_b200.h -- C-ABI of the B200-native Hivemall training hot path.
+ *
+ * One shared library (hivemall_b200/libhivemall_b200.so, plain CUDA C++, no torch
+ * types) exports everything a JNI / Panama binding of the path would call.
+ *
+ * Reference citations.  The mounted reference (/root/reference, maropu/hivemall)
+ * is a README-only deprecation stub (README.md:20 "development moved to the ASF
+ * repository", README.md:22 "This repository became deprecated"); it has no
+ * source file to cite.  Each entry point therefore names the interface that
+ * BASELINE.json's north_star says it stands in for (the Hive UDTF lifecycle of
+ * train_classifier / train_regressor / train_fm, and the mhash / feature_hashing
+ * UDFs).  PARITY IS UNPINNED until real sources are mounted; every fact that
+ * would have to be read from them is a run-time parameter here, not a constant.
+ *
+ * Conventions
+ *  - every function returns HM_OK (0) or an hm_status error code and never throws;
+ *    hm_last_error() returns the calling thread's last message.
+ *  - "host" pointers are ordinary (ideally pinned, see hm_host_alloc) CPU memory;
+ *    "device" pointers (prefix d_) are CUDA device memory on the learner's device.
+ *  - a learner handle is not thread-safe; use one handle per thread / per GPU
+ *    (a Hive task owns exactly one UDTF instance, which is the same rule).
+ *  - there is no CPU fallback: without a CUDA device every compute entry point
+ *    fails with HM_ERR_CUDA.
+ */
+#ifndef HIVEMALL_B200_H
+#define HIVEMALL_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define HM_ABI_VERSION 1
+
+typedef enum hm_status {
+    HM_OK = 0,
+    HM_ERR_INVALID_ARGUMENT = 1, /* bad option string / bad argument (UDFArgumentException role) */
+    HM_ERR_CUDA = 2,             /* CUDA runtime failure or no device */
+    HM_ERR_STATE = 3,            /* call out of lifecycle order (HiveException role) */
+    HM_ERR_OOM = 4,              /* device or host allocation failed */
+    HM_ERR_UNSUPPORTED = 5       /* valid option that this build does not implement */
+} hm_status;
+
+enum { HM_TASK_CLASSIFIER = 0, HM_TASK_REGRESSOR = 1, HM_TASK_FM = 2 };
+enum { HM_LOSS_LOG = 0, HM_LOSS_HINGE = 1, HM_LOSS_SQUARED = 2 };
+enum { HM_OPT_SGD = 0, HM_OPT_ADAGRAD = 1, HM_OPT_ADADELTA = 2, HM_OPT_ADAM = 3, HM_OPT_FTRL = 4 };
+enum { HM_ETA_FIXED = 0, HM_ETA_INVERSE = 1, HM_ETA_SIMPLE = 2 };
+enum { HM_REG_NONE = 0, HM_REG_L1 = 1, HM_REG_L2 = 2 };
+enum { HM_NORM_BATCH = 0, HM_NORM_COUNT = 1, HM_NORM_SUM = 2 };
+
+/* Numeric form of a UDTF option string (hm_parse_options fills it). */
+typedef struct hm_config {
+    int32_t task, loss, opt, eta_sched, reg, grad_norm;
+    int32_t mini_batch, iters;
+    int64_t dims;
+    double  total_steps;
+    float   eta0, power_t;
+    float   lambda;
+    float   eps;
+    float   rho;
+    float   beta1, beta2;
+    float   alpha, beta, lambda1, lambda2;
+    int32_t factors;
+    int32_t fm_classification;
+    float   sigma;
+    float   lambda_w0, lambda_w, lambda_v;
+    uint32_t seed;
+    int32_t mix_interval;    /* mini-batches between model averaging; 0 = end of epoch */
+    uint32_t hash_seed;      /* MurmurHash3 seed used by feature hashing */
+    int32_t reserved[8];
+} hm_config;
+
+typedef struct hm_udtf hm_udtf; /* opaque learner = one UDTF instance on one GPU */
+
+/* Counters since creation. */
+typedef struct hm_stats {
+    int64_t rows, nnz, mini_batches, kernel_launches;
+    int64_t h2d_bytes, d2h_bytes;
+    double  loss_sum_last_epoch;  /* filled by hm_udtf_close when -track_loss is set */
+} hm_stats;
+
+/* ---- library ------------------------------------------------------------- */
+
+/* Thread-local text of the most recent error.  Never NULL. */
+const char *hm_last_error(void);
+int hm_abi_version(void);
+/* Number of CUDA devices visible; 0 when there is none (compute calls then fail). */
+int hm_device_count(void);
+
+/* Pinned host memory for the host-buffer entry points (JNI: wrap in a direct
+ * ByteBuffer).  Pageable memory is accepted everywhere but copies slower. */
+hm_status hm_host_alloc(void **out, int64_t bytes);
+hm_status hm_host_free(void *p);
+
+/* ---- feature hashing  (stands in for the mhash / feature_hashing UDFs) ---- */
+
+/* mhash over n UTF-8 strings packed back to back in `bytes`; string i is
+ * bytes[offsets[i] .. offsets[i+1]).  out[i] = MurmurHash3_x86_32(string, seed)
+ * folded into [0, num_features) with Java % semantics (negative remainders are
+ * shifted up by num_features).  Host buffers; runs the CUDA kernel on `device`. */
+hm_status hm_mhash(const uint8_t *bytes, const int64_t *offsets, int64_t n,
+                   uint32_t seed, int32_t num_features, int32_t *out, int device);
+/* Same, buffers already on the device, asynchronous on `stream` (a cudaStream_t). */
+hm_status hm_mhash_device(const uint8_t *d_bytes, const int64_t *d_offsets, int64_t n,
+                          uint32_t seed, int32_t num_features, int32_t *d_out, void *stream);
+/* feature_hashing over "name:value" / "name" feature strings: the name part (up
+ * to the LAST ':' when what follows parses as a number) is hashed as above, the
+ * value part is parsed as a float (1.0 when absent).  A name made only of decimal
+ * digits is taken as an index already and passed through unhashed. */
+hm_status hm_feature_hashing(const uint8_t *bytes, const int64_t *offsets, int64_t n,
+                             uint32_t seed, int32_t num_features,
+                             int32_t *out_index, float *out_value, int device);
+
+/* ---- option strings (stands in for the UDTF's getOptions/processOptions) --- */
+
+/* function_name: "train_classifier" | "train_regressor" | "train_fm".
+ * Unknown options, missing values and out-of-range numbers are
+ * HM_ERR_INVALID_ARGUMENT with the offending token in hm_last_error(). */
+hm_status hm_parse_options(const char *function_name, const char *options, hm_config *out);
+
+/* ---- UDTF lifecycle ------------------------------------------------------- */
+
+/* initialize(): parse options, allocate the model replica on `device`. */
+hm_status hm_udtf_create(const char *function_name, const char *options, int device, hm_udtf **out);
+/* Same from an already-numeric config. */
+hm_status hm_udtf_create_from_config(const hm_config *cfg, int device, hm_udtf **out);
+
+/* process() for n_rows rows at once, HOST buffers in CSR form: row i owns
+ * feature[rowptr[i] .. rowptr[i+1]) / value[...]; rowptr[0] may be non-zero.
+ * Rows are consumed in order; a mini-batch is trained as soon as -mini_batch rows
+ * are buffered, exactly as if process() had been called row by row.
+ * Copies host->device inside the call (asynchronously when the buffers are pinned). */
+hm_status hm_udtf_process(hm_udtf *u, int64_t n_rows, const int64_t *rowptr,
+                          const int32_t *feature, const float *value, const float *label);
+/* process() for rows whose features are still strings ("name:value"); hashes on
+ * the GPU with the learner's hash_seed into [0, dims) and then behaves as above.
+ * rowptr indexes strings; string s is bytes[offsets[s] .. offsets[s+1]). */
+hm_status hm_udtf_process_strings(hm_udtf *u, int64_t n_rows, const int64_t *rowptr,
+                                  const uint8_t *bytes, const int64_t *offsets, const float *label);
+/* process() for rows already resident in device memory (no copies).  n_rows must
+ * be a multiple of -mini_batch unless this is the last call before close(), and
+ * no host-buffered remainder may be pending.  nnz = d_rowptr[n_rows]-d_rowptr[0]. */
+hm_status hm_udtf_process_device(hm_udtf *u, int64_t n_rows, int64_t nnz, const int64_t *d_rowptr,
+                                 const int32_t *d_feature, const float *d_value, const float *d_label);
+
+/* close(): train the last short mini-batch, run the remaining -iters passes over
+ * the retained rows, wait for the GPU, and report the model-table row count. */
+hm_status hm_udtf_close(hm_udtf *u, int64_t *n_model_rows);
+/* forward(): copy the model table to host arrays of capacity `cap` rows.
+ * Linear learners emit (feature, weight) for every weight != 0 in ascending
+ * feature order.  train_fm emits a first row with feature = -1 holding w0, then
+ * (feature, Wi, Vif[factors]) for every feature seen in training, ascending;
+ * vif must hold cap * factors floats (NULL for linear learners). */
+hm_status hm_udtf_forward(hm_udtf *u, int32_t *feature, float *weight, float *vif,
+                          int64_t cap, int64_t *n_written);
+hm_status hm_udtf_destroy(hm_udtf *u);
+
+/* ---- model replica access (MIX averaging, warm start, tests) -------------- */
+
+/* Device arrays that make up the replica.  which = 0..n-1; name is one of
+ * "w", "state" (optimizer slots, `width` floats interleaved per feature),
+ * "V", "gV" (dims x factors), "w0" (1 float, then its accumulator).  The pointers stay valid
+ * until destroy; call hm_udtf_sync before reading them from another stream. */
+int hm_udtf_num_arrays(const hm_udtf *u);
+hm_status hm_udtf_array(hm_udtf *u, int which, const char **name, void **d_ptr,
+                        int64_t *n_floats, int32_t *width);
+/* Copy replica array `which` to / from a host buffer of n floats (n must equal the
+ * array's length).  Synchronous.  write_array is the warm-start path. */
+hm_status hm_udtf_read_array(hm_udtf *u, int which, float *host, int64_t n);
+hm_status hm_udtf_write_array(hm_udtf *u, int which, const float *host, int64_t n);
+/* Update counter t (mini-batches applied so far); settable for warm start / MIX. */
+hm_status hm_udtf_get_step(const hm_udtf *u, int64_t *t);
+hm_status hm_udtf_set_step(hm_udtf *u, int64_t t);
+/* Wait until all work queued on the learner's streams has finished. */
+hm_status hm_udtf_sync(hm_udtf *u);
+/* The learner's compute stream as a cudaStream_t (for event timing by callers). */
+void *hm_udtf_stream(hm_udtf *u);
+/* Multiply every replica array by `scale` on the learner's stream (the 1/P step
+ * of sum-then-scale averaging after an all-reduce). */
+hm_status hm_udtf_scale_replica(hm_udtf *u, float scale);
+
+/* ---- prediction (held-out AUC / logloss for parity) ----------------------- */
+
+/* out[i] = margin of row i under the current model (linear: w.x ; fm: y_hat). */
+hm_status hm_udtf_predict(hm_udtf *u, int64_t n_rows, const int64_t *rowptr,
+                          const int32_t *feature, const float *value, float *out);
+hm_status hm_udtf_predict_device(hm_udtf *u, int64_t n_rows, const int64_t *d_rowptr,
+                                 const int32_t *d_feature, const float *d_value, float *d_out);
+
+/* ---- measurement ----------------------------------------------------------- */
+
+hm_status hm_udtf_stats(const hm_udtf *u, hm_stats *out);
+/* When on, every kernel launch is bracketed by CUDA events on the launching
+ * stream and accumulated per kernel name (slows the run: use a separate pass). */
+hm_status hm_udtf_set_profiling(hm_udtf *u, int on);
+/* Per-kernel totals collected while profiling was on.  i = 0..n-1. */
+int hm_udtf_num_kernels(const hm_udtf *u);
+hm_status hm_udtf_kernel_time(hm_udtf *u, int i, const char **name, int64_t *launches,
+                              double *total_ms, double *algorithmic_bytes);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* HIVEMALL_B200_H */

@@ -1,0 +1,417 @@
+/*
+ * hm_oracle.c -- CPU oracle for the hivemall_b200 hot path.  TEST INFRASTRUCTURE ONLY.
+ *
+ * PARITY UNPINNED (see hm_oracle.h): the reference mount holds no code
+ * (/root/reference/README.md:20-22), so every function below follows a published
+ * algorithm plus the arithmetic contract of DESIGN.md section 3, not Hivemall source.
+ * Plain scalar loops, hash-map-free: a dense double accumulator per feature.
+ *
+ * Build: gcc -O2 -ffp-contract=off -fno-fast-math -shared -fPIC (oracle/Makefile).
+ * -ffp-contract=off matters: DESIGN.md section 3 rounds every fp32 operation separately.
+ */
+#include "hm_oracle.h"
+#include <math.h>
+#include <stdlib.h>
+#include <string.h>
+
+/* ---------------------------------------------------------------- hashing */
+
+static inline uint32_t rotl32(uint32_t x, int r) { return (x << r) | (x >> (32 - r)); }
+
+static inline uint32_t fmix32(uint32_t h)
+{
+    h ^= h >> 16; h *= 0x85ebca6bu;
+    h ^= h >> 13; h *= 0xc2b2ae35u;
+    h ^= h >> 16;
+    return h;
+}
+
+/* MurmurHash3_x86_32, Austin Appleby's published algorithm (SMHasher, public domain).
+ * Pinned by tests/golden/murmur3_kat.json incl. the SMHasher verification value 0xB0F57EE3. */
+uint32_t hmo_murmur3_x86_32(const void *key, int64_t len, uint32_t seed)
+{
+    const uint8_t *data = (const uint8_t *)key;
+    const int64_t nblocks = len / 4;
+    uint32_t h1 = seed;
+    const uint32_t c1 = 0xcc9e2d51u, c2 = 0x1b873593u;
+    for (int64_t i = 0; i < nblocks; i++) {
+        uint32_t k1 = (uint32_t)data[4 * i] | ((uint32_t)data[4 * i + 1] << 8) |
+                      ((uint32_t)data[4 * i + 2] << 16) | ((uint32_t)data[4 * i + 3] << 24);
+        k1 *= c1; k1 = rotl32(k1, 15); k1 *= c2;
+        h1 ^= k1; h1 = rotl32(h1, 13); h1 = h1 * 5u + 0xe6546b64u;
+    }
+    const uint8_t *tail = data + nblocks * 4;
+    uint32_t k1 = 0;
+    switch (len & 3) {
+    case 3: k1 ^= (uint32_t)tail[2] << 16; /* fallthrough */
+    case 2: k1 ^= (uint32_t)tail[1] << 8;  /* fallthrough */
+    case 1: k1 ^= (uint32_t)tail[0];
+        k1 *= c1; k1 = rotl32(k1, 15); k1 *= c2; h1 ^= k1;
+    }
+    h1 ^= (uint32_t)len;
+    return fmix32(h1);
+}
+
+int32_t hmo_fold(uint32_t h, int32_t num_features)
+{
+    int32_t r = (int32_t)h % num_features; /* C99 truncating remainder == Java % */
+    if (r < 0) r += num_features;
+    return r;
+}
+
+void hmo_mhash_batch(const uint8_t *bytes, const int64_t *offsets, int64_t n,
+                     uint32_t seed, int32_t num_features, int32_t *out)
+{
+    for (int64_t i = 0; i < n; i++)
+        out[i] = hmo_fold(hmo_murmur3_x86_32(bytes + offsets[i], offsets[i + 1] - offsets[i], seed),
+                          num_features);
+}
+
+/* ---------------------------------------------------------------- scalar math */
+
+/* Cody-Waite reduction + degree-6 Horner, every op rounded to fp32. */
+float hmo_exp(float x)
+{
+    x = fminf(fmaxf(x, -87.0f), 88.0f);
+    float n = rintf(x * 1.44269504f);
+    float r = x - n * 0.693359375f;
+    r = r - n * -2.12194440e-4f;
+    float p = 1.3888889e-3f;
+    p = p * r + 8.3333333e-3f;
+    p = p * r + 4.1666667e-2f;
+    p = p * r + 1.6666667e-1f;
+    p = p * r + 0.5f;
+    p = p * r + 1.0f;
+    p = p * r + 1.0f;
+    union { uint32_t u; float f; } s;
+    s.u = (uint32_t)((int32_t)n + 127) << 23;
+    return p * s.f;
+}
+
+float hmo_dloss(int32_t loss, float m, float y)
+{
+    switch (loss) {
+    case HMO_LOSS_LOG:   return -y / (1.0f + hmo_exp(y * m));
+    case HMO_LOSS_HINGE: return (y * m < 1.0f) ? -y : 0.0f;
+    default:             return m - y;
+    }
+}
+
+double hmo_loss(int32_t loss, float m, float y)
+{
+    double z = (double)y * (double)m;
+    switch (loss) {
+    case HMO_LOSS_LOG:   return z > 0 ? log1p(exp(-z)) : -z + log1p(exp(z));
+    case HMO_LOSS_HINGE: return z < 1.0 ? 1.0 - z : 0.0;
+    default: { double d = (double)m - (double)y; return 0.5 * d * d; }
+    }
+}
+
+float hmo_eta(const hmo_config *c, int64_t t)
+{
+    switch (c->eta_sched) {
+    case HMO_ETA_INVERSE: return (float)((double)c->eta0 / pow((double)t, (double)c->power_t));
+    case HMO_ETA_SIMPLE:  return (float)((double)c->eta0 / (1.0 + (double)t / c->total_steps));
+    default:              return c->eta0;
+    }
+}
+
+static inline float target_of(const hmo_config *c, float label)
+{
+    if (c->task == HMO_TASK_CLASSIFIER) return label > 0.0f ? 1.0f : -1.0f;
+    return label;
+}
+
+/* ---------------------------------------------------------------- optimizers */
+
+/* One coordinate update, DESIGN.md 3.6.  alpha_t is Adam's bias-corrected step. */
+static void update_coord(const hmo_config *c, float eta, float alpha_t, float g,
+                         float *w, float *s1, float *s2)
+{
+    float wv = *w;
+    if (c->reg == HMO_REG_L2 && c->opt != HMO_OPT_FTRL) g = g + c->lambda * wv;
+    switch (c->opt) {
+    case HMO_OPT_SGD:
+        wv = wv - eta * g;
+        break;
+    case HMO_OPT_ADAGRAD: {
+        float G = *s1 + g * g;
+        *s1 = G;
+        wv = wv - (eta * g) / (sqrtf(G) + c->eps);
+        break;
+    }
+    case HMO_OPT_ADADELTA: {
+        float E = c->rho * *s1 + ((1.0f - c->rho) * g) * g;
+        float dx = (sqrtf(*s2 + c->eps) / sqrtf(E + c->eps)) * g;
+        *s2 = c->rho * *s2 + ((1.0f - c->rho) * dx) * dx;
+        *s1 = E;
+        wv = wv - dx;
+        break;
+    }
+    case HMO_OPT_ADAM: {
+        float m = c->beta1 * *s1 + (1.0f - c->beta1) * g;
+        float v = c->beta2 * *s2 + ((1.0f - c->beta2) * g) * g;
+        *s1 = m; *s2 = v;
+        wv = wv - (alpha_t * m) / (sqrtf(v) + c->eps);
+        break;
+    }
+    case HMO_OPT_FTRL: {
+        float n0 = *s2;
+        float n1 = n0 + g * g;
+        float sigma = (sqrtf(n1) - sqrtf(n0)) / c->alpha;
+        float z = *s1 + g - sigma * wv;
+        *s1 = z; *s2 = n1;
+        if (fabsf(z) <= c->lambda1) wv = 0.0f;
+        else {
+            float sgn = z < 0.0f ? -1.0f : 1.0f;
+            wv = -(z - sgn * c->lambda1) / ((c->beta + sqrtf(n1)) / c->alpha + c->lambda2);
+        }
+        break;
+    }
+    }
+    if (c->reg == HMO_REG_L1 && c->opt != HMO_OPT_FTRL) {
+        float a = fabsf(wv) - eta * c->lambda;
+        wv = a > 0.0f ? copysignf(a, wv) : 0.0f;
+    }
+    *w = wv;
+}
+
+static float adam_alpha(const hmo_config *c, float eta, int64_t t)
+{
+    double b1 = pow((double)c->beta1, (double)t), b2 = pow((double)c->beta2, (double)t);
+    return (float)((double)eta * sqrt(1.0 - b2) / (1.0 - b1));
+}
+
+/* ---------------------------------------------------------------- linear learner */
+
+void hmo_predict_linear(int64_t n_rows, const int64_t *rowptr, const uint32_t *idx,
+                        const float *val, const float *w, float *margin)
+{
+    for (int64_t i = 0; i < n_rows; i++) {
+        double acc = 0.0;
+        for (int64_t p = rowptr[i]; p < rowptr[i + 1]; p++)
+            acc += (double)w[idx[p]] * (double)val[p];
+        margin[i] = (float)acc;
+    }
+}
+
+int hmo_train_linear(const hmo_config *c, int64_t n_rows, const int64_t *rowptr,
+                     const uint32_t *idx, const float *val, const float *label,
+                     float *w, float *s1, float *s2, int64_t *t,
+                     float *margins, double *loss_sum)
+{
+    if (c->mini_batch < 1 || c->dims < 1) return -1;
+    const int64_t B = c->mini_batch;
+    double *gsum = (double *)calloc((size_t)c->dims, sizeof(double));
+    uint32_t *cnt = (uint32_t *)calloc((size_t)c->dims, sizeof(uint32_t));
+    float *dl = (float *)malloc((size_t)B * sizeof(float));
+    /* features touched by the current batch, in first-touch order */
+    int64_t max_touch = 0;
+    for (int64_t b0 = 0; b0 < n_rows; b0 += B) {
+        int64_t e = b0 + B < n_rows ? b0 + B : n_rows;
+        if (rowptr[e] - rowptr[b0] > max_touch) max_touch = rowptr[e] - rowptr[b0];
+    }
+    uint32_t *touch = (uint32_t *)malloc((size_t)(max_touch > 0 ? max_touch : 1) * sizeof(uint32_t));
+    if (!gsum || !cnt || !dl || !touch) { free(gsum); free(cnt); free(dl); free(touch); return -2; }
+    double lsum = 0.0;
+    float dummy = 0.0f;
+    for (int32_t it = 0; it < c->iters; it++) {
+        lsum = 0.0;
+        for (int64_t b0 = 0; b0 < n_rows; b0 += B) {
+            const int64_t b1 = b0 + B < n_rows ? b0 + B : n_rows;
+            const int64_t nb = b1 - b0;
+            /* score every row of the batch with the weights as they stand */
+            for (int64_t i = b0; i < b1; i++) {
+                double acc = 0.0;
+                for (int64_t p = rowptr[i]; p < rowptr[i + 1]; p++) {
+                    if ((int64_t)idx[p] >= c->dims) { free(gsum); free(cnt); free(dl); free(touch); return -3; }
+                    acc += (double)w[idx[p]] * (double)val[p];
+                }
+                float m = (float)acc;
+                float y = target_of(c, label[i]);
+                dl[i - b0] = hmo_dloss(c->loss, m, y);
+                lsum += hmo_loss(c->loss, m, y);
+                if (margins) margins[i] = m;
+            }
+            /* per-feature gradient sums in double */
+            int64_t nt = 0;
+            for (int64_t i = b0; i < b1; i++)
+                for (int64_t p = rowptr[i]; p < rowptr[i + 1]; p++) {
+                    uint32_t j = idx[p];
+                    if (cnt[j]++ == 0) touch[nt++] = j;
+                    gsum[j] += (double)dl[i - b0] * (double)val[p];
+                }
+            /* one optimizer update per touched feature */
+            *t += 1;
+            const float eta = hmo_eta(c, *t);
+            const float alpha_t = c->opt == HMO_OPT_ADAM ? adam_alpha(c, eta, *t) : 0.0f;
+            for (int64_t k = 0; k < nt; k++) {
+                uint32_t j = touch[k];
+                double denom = c->grad_norm == HMO_NORM_BATCH ? (double)nb
+                             : c->grad_norm == HMO_NORM_COUNT ? (double)cnt[j] : 1.0;
+                float g = (float)(gsum[j] / denom);
+                update_coord(c, eta, alpha_t, g, &w[j], s1 ? &s1[j] : &dummy, s2 ? &s2[j] : &dummy);
+                gsum[j] = 0.0; cnt[j] = 0;
+            }
+        }
+    }
+    if (loss_sum) *loss_sum = lsum;
+    free(gsum); free(cnt); free(dl); free(touch);
+    return 0;
+}
+
+int64_t hmo_model_table(const float *w, int64_t dims, int32_t *feature, float *weight, int64_t cap)
+{
+    int64_t n = 0;
+    for (int64_t j = 0; j < dims; j++)
+        if (w[j] != 0.0f) {
+            if (n < cap) { feature[n] = (int32_t)j; weight[n] = w[j]; }
+            n++;
+        }
+    return n;
+}
+
+/* ---------------------------------------------------------------- factorization machine */
+
+/* V[j][f] = sigma * u, u in [-1,1) from a 24-bit integer hash. */
+void hmo_fm_init_v(const hmo_config *c, float *V)
+{
+    const int64_t n = c->dims * (int64_t)c->factors;
+    for (int64_t q = 0; q < n; q++) {
+        uint32_t h = fmix32((uint32_t)q * 0x9E3779B1u + c->seed);
+        float u = ((float)(h >> 8) * 5.9604644775390625e-08f - 0.5f) * 2.0f;
+        V[q] = c->sigma * u;
+    }
+}
+
+static float fm_score(const hmo_config *c, const int64_t *rowptr, const uint32_t *idx,
+                      const float *val, int64_t i, float w0, const float *w, const float *V,
+                      float *S32 /* factors, nullable */)
+{
+    const int k = c->factors;
+    double lin = 0.0;
+    for (int64_t p = rowptr[i]; p < rowptr[i + 1]; p++)
+        lin += (double)w[idx[p]] * (double)val[p];
+    double inter = 0.0;
+    for (int f = 0; f < k; f++) {
+        double S = 0.0, Q = 0.0;
+        for (int64_t p = rowptr[i]; p < rowptr[i + 1]; p++) {
+            double vx = (double)V[(int64_t)idx[p] * k + f] * (double)val[p];
+            S += vx;
+            Q += vx * vx;
+        }
+        float s32 = (float)S;
+        if (S32) S32[f] = s32;
+        inter += (double)s32 * (double)s32 - Q;
+    }
+    return (float)((double)w0 + lin + 0.5 * inter);
+}
+
+void hmo_predict_fm(const hmo_config *c, int64_t n_rows, const int64_t *rowptr,
+                    const uint32_t *idx, const float *val, float w0, const float *w,
+                    const float *V, float *pred)
+{
+    for (int64_t i = 0; i < n_rows; i++)
+        pred[i] = fm_score(c, rowptr, idx, val, i, w0, w, V, NULL);
+}
+
+/* SGD or AdaGrad on one FM parameter with its own L2 strength. */
+static inline void fm_step(const hmo_config *c, float eta, float g, float lam, float *th, float *acc)
+{
+    float v = *th;
+    g = g + lam * v;
+    if (c->opt == HMO_OPT_ADAGRAD) {
+        float G = *acc + g * g;
+        *acc = G;
+        v = v - (eta * g) / (sqrtf(G) + c->eps);
+    } else {
+        v = v - eta * g;
+    }
+    *th = v;
+}
+
+int hmo_train_fm(const hmo_config *c, int64_t n_rows, const int64_t *rowptr,
+                 const uint32_t *idx, const float *val, const float *label,
+                 float *w0, float *w, float *V, float *gw0, float *gw, float *gv,
+                 uint8_t *touched, int64_t *t, float *preds, double *loss_sum)
+{
+    const int k = c->factors;
+    const int64_t B = c->mini_batch;
+    if (B < 1 || k < 1) return -1;
+    /* per-feature sums for the batch: A1 = sum dl*x, A2 = sum (dl*x)*x, GS[f] = sum (dl*x)*S[f] */
+    double *A1 = (double *)calloc((size_t)c->dims, sizeof(double));
+    double *A2 = (double *)calloc((size_t)c->dims, sizeof(double));
+    uint32_t *cnt = (uint32_t *)calloc((size_t)c->dims, sizeof(uint32_t));
+    int64_t max_touch = 1;
+    for (int64_t b0 = 0; b0 < n_rows; b0 += B) {
+        int64_t e = b0 + B < n_rows ? b0 + B : n_rows;
+        if (rowptr[e] - rowptr[b0] > max_touch) max_touch = rowptr[e] - rowptr[b0];
+    }
+    uint32_t *touch = (uint32_t *)malloc((size_t)max_touch * sizeof(uint32_t));
+    /* GS is kept per touched slot (slot index stored in cnt-parallel array) */
+    uint32_t *slot = (uint32_t *)malloc((size_t)c->dims * sizeof(uint32_t));
+    double *GS = (double *)malloc((size_t)max_touch * k * sizeof(double));
+    float *dl = (float *)malloc((size_t)B * sizeof(float));
+    float *S = (float *)malloc((size_t)B * k * sizeof(float));
+    if (!A1 || !A2 || !cnt || !touch || !slot || !GS || !dl || !S) return -2;
+    float dummy = 0.0f;
+    double lsum = 0.0;
+    for (int32_t it = 0; it < c->iters; it++) {
+        lsum = 0.0;
+        for (int64_t b0 = 0; b0 < n_rows; b0 += B) {
+            const int64_t b1 = b0 + B < n_rows ? b0 + B : n_rows;
+            const int64_t nb = b1 - b0;
+            double g0 = 0.0;
+            for (int64_t i = b0; i < b1; i++) {
+                float p = fm_score(c, rowptr, idx, val, i, *w0, w, V, S + (i - b0) * k);
+                float d;
+                if (c->fm_classification) {
+                    float y = label[i] > 0.0f ? 1.0f : -1.0f;
+                    d = hmo_dloss(HMO_LOSS_LOG, p, y);
+                    lsum += hmo_loss(HMO_LOSS_LOG, p, y);
+                } else {
+                    d = p - label[i];
+                    lsum += hmo_loss(HMO_LOSS_SQUARED, p, label[i]);
+                }
+                dl[i - b0] = d;
+                g0 += (double)d;
+                if (preds) preds[i] = p;
+            }
+            int64_t nt = 0;
+            for (int64_t i = b0; i < b1; i++)
+                for (int64_t p = rowptr[i]; p < rowptr[i + 1]; p++) {
+                    uint32_t j = idx[p];
+                    if (cnt[j]++ == 0) {
+                        slot[j] = (uint32_t)nt;
+                        for (int f = 0; f < k; f++) GS[nt * k + f] = 0.0;
+                        touch[nt++] = j;
+                    }
+                    double c1 = (double)dl[i - b0] * (double)val[p];
+                    A1[j] += c1;
+                    A2[j] += c1 * (double)val[p];
+                    double *gs = GS + (int64_t)slot[j] * k;
+                    const float *Si = S + (i - b0) * k;
+                    for (int f = 0; f < k; f++) gs[f] += c1 * (double)Si[f];
+                }
+            *t += 1;
+            const float eta = hmo_eta(c, *t);
+            const double denom = c->grad_norm == HMO_NORM_SUM ? 1.0 : (double)nb;
+            fm_step(c, eta, (float)(g0 / denom), c->lambda_w0, w0, gw0 ? gw0 : &dummy);
+            for (int64_t q = 0; q < nt; q++) {
+                uint32_t j = touch[q];
+                double dj = c->grad_norm == HMO_NORM_COUNT ? (double)cnt[j] : denom;
+                fm_step(c, eta, (float)(A1[j] / dj), c->lambda_w, &w[j], gw ? &gw[j] : &dummy);
+                for (int f = 0; f < k; f++) {
+                    float *v = &V[(int64_t)j * k + f];
+                    double G = GS[q * k + f] - (double)*v * A2[j];
+                    fm_step(c, eta, (float)(G / dj), c->lambda_v, v, gv ? &gv[(int64_t)j * k + f] : &dummy);
+                }
+                if (touched) touched[j] = 1;
+                A1[j] = 0.0; A2[j] = 0.0; cnt[j] = 0;
+            }
+        }
+    }
+    if (loss_sum) *loss_sum = lsum;
+    free(A1); free(A2); free(cnt); free(touch); free(slot); free(GS); free(dl); free(S);
+    return 0;
+}

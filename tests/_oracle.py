@@ -1,0 +1,196 @@
+"""ctypes binding of the CPU oracle (oracle/hm_oracle.c).  Test infrastructure only:
+nothing under hivemall_b200/ imports this."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ORACLE_LIB = os.path.join(ROOT, "oracle", "_build", "libhm_oracle.so")
+
+
+class HmoConfig(C.Structure):
+    _fields_ = [
+        ("task", C.c_int32), ("loss", C.c_int32), ("opt", C.c_int32), ("eta_sched", C.c_int32),
+        ("reg", C.c_int32), ("grad_norm", C.c_int32), ("mini_batch", C.c_int32), ("iters", C.c_int32),
+        ("dims", C.c_int64), ("total_steps", C.c_double),
+        ("eta0", C.c_float), ("power_t", C.c_float), ("lambda_", C.c_float), ("eps", C.c_float),
+        ("rho", C.c_float), ("beta1", C.c_float), ("beta2", C.c_float),
+        ("alpha", C.c_float), ("beta", C.c_float), ("lambda1", C.c_float), ("lambda2", C.c_float),
+        ("factors", C.c_int32), ("fm_classification", C.c_int32), ("sigma", C.c_float),
+        ("lambda_w0", C.c_float), ("lambda_w", C.c_float), ("lambda_v", C.c_float),
+        ("seed", C.c_uint32),
+    ]
+
+
+_P = C.c_void_p
+_lib = None
+
+
+def lib() -> C.CDLL:
+    global _lib
+    if _lib is None:
+        if not os.path.exists(ORACLE_LIB):
+            import subprocess
+            subprocess.check_call(["make", "-C", os.path.join(ROOT, "oracle")])
+        L = C.CDLL(ORACLE_LIB)
+        L.hmo_murmur3_x86_32.restype = C.c_uint32
+        L.hmo_murmur3_x86_32.argtypes = [C.c_char_p, C.c_int64, C.c_uint32]
+        L.hmo_fold.restype = C.c_int32
+        L.hmo_fold.argtypes = [C.c_uint32, C.c_int32]
+        L.hmo_mhash_batch.restype = None
+        L.hmo_mhash_batch.argtypes = [_P, _P, C.c_int64, C.c_uint32, C.c_int32, _P]
+        L.hmo_exp.restype = C.c_float
+        L.hmo_exp.argtypes = [C.c_float]
+        L.hmo_dloss.restype = C.c_float
+        L.hmo_dloss.argtypes = [C.c_int32, C.c_float, C.c_float]
+        L.hmo_loss.restype = C.c_double
+        L.hmo_loss.argtypes = [C.c_int32, C.c_float, C.c_float]
+        L.hmo_eta.restype = C.c_float
+        L.hmo_eta.argtypes = [C.POINTER(HmoConfig), C.c_int64]
+        L.hmo_train_linear.restype = C.c_int
+        L.hmo_train_linear.argtypes = [C.POINTER(HmoConfig), C.c_int64, _P, _P, _P, _P, _P, _P, _P,
+                                       C.POINTER(C.c_int64), _P, C.POINTER(C.c_double)]
+        L.hmo_predict_linear.restype = None
+        L.hmo_predict_linear.argtypes = [C.c_int64, _P, _P, _P, _P, _P]
+        L.hmo_fm_init_v.restype = None
+        L.hmo_fm_init_v.argtypes = [C.POINTER(HmoConfig), _P]
+        L.hmo_train_fm.restype = C.c_int
+        L.hmo_train_fm.argtypes = [C.POINTER(HmoConfig), C.c_int64, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P,
+                                   C.POINTER(C.c_int64), _P, C.POINTER(C.c_double)]
+        L.hmo_predict_fm.restype = None
+        L.hmo_predict_fm.argtypes = [C.POINTER(HmoConfig), C.c_int64, _P, _P, _P, C.c_float, _P, _P, _P]
+        L.hmo_model_table.restype = C.c_int64
+        L.hmo_model_table.argtypes = [_P, C.c_int64, _P, _P, C.c_int64]
+        _lib = L
+    return _lib
+
+
+def _p(a):
+    return C.c_void_p(a.ctypes.data) if a is not None else C.c_void_p(0)
+
+
+def config_from(hm_cfg) -> HmoConfig:
+    """Copy the numeric fields of the product's parsed hm_config into an oracle config."""
+    c = HmoConfig()
+    for name, _ in HmoConfig._fields_:
+        setattr(c, name, getattr(hm_cfg, name))
+    if c.task == 2:  # HM_TASK_FM has no oracle task id; the FM entry points do not read it
+        c.task = 1
+    return c
+
+
+def murmur3(data: bytes, seed: int) -> int:
+    return lib().hmo_murmur3_x86_32(data, len(data), seed & 0xFFFFFFFF)
+
+
+def mhash(strings, num_features: int, seed: int) -> np.ndarray:
+    enc = [s.encode("utf-8") if isinstance(s, str) else bytes(s) for s in strings]
+    off = np.zeros(len(enc) + 1, dtype=np.int64)
+    if enc:
+        off[1:] = np.cumsum([len(b) for b in enc])
+    data = np.frombuffer(b"".join(enc) + b"\0", dtype=np.uint8).copy()
+    out = np.empty(len(enc), dtype=np.int32)
+    lib().hmo_mhash_batch(_p(data), _p(off), len(enc), seed & 0xFFFFFFFF, num_features, _p(out))
+    return out
+
+
+class LinearResult:
+    def __init__(self, w, s1, s2, t, margins, loss_sum):
+        self.w, self.s1, self.s2, self.t, self.margins, self.loss_sum = w, s1, s2, t, margins, loss_sum
+
+    def state(self, width: int) -> np.ndarray:
+        """Optimizer slots interleaved the way the product stores them."""
+        if width == 0:
+            return np.zeros(0, dtype=np.float32)
+        if width == 1:
+            return self.s1.copy()
+        return np.stack([self.s1, self.s2], axis=1).reshape(-1).copy()
+
+
+def train_linear(cfg: HmoConfig, rowptr, feature, value, label, w=None, s1=None, s2=None, t=0) -> LinearResult:
+    rowptr = np.ascontiguousarray(rowptr, dtype=np.int64)
+    feature = np.ascontiguousarray(feature).astype(np.uint32)
+    value = np.ascontiguousarray(value, dtype=np.float32)
+    label = np.ascontiguousarray(label, dtype=np.float32)
+    n = len(rowptr) - 1
+    d = int(cfg.dims)
+    w = np.zeros(d, np.float32) if w is None else np.array(w, np.float32)
+    s1 = np.zeros(d, np.float32) if s1 is None else np.array(s1, np.float32)
+    s2 = np.zeros(d, np.float32) if s2 is None else np.array(s2, np.float32)
+    margins = np.zeros(n, np.float32)
+    tt = C.c_int64(t)
+    ls = C.c_double(0.0)
+    rc = lib().hmo_train_linear(C.byref(cfg), n, _p(rowptr), _p(feature), _p(value), _p(label), _p(w), _p(s1),
+                                _p(s2), C.byref(tt), _p(margins), C.byref(ls))
+    if rc != 0:
+        raise RuntimeError(f"hmo_train_linear failed: {rc}")
+    return LinearResult(w, s1, s2, tt.value, margins, ls.value)
+
+
+def predict_linear(rowptr, feature, value, w) -> np.ndarray:
+    rowptr = np.ascontiguousarray(rowptr, dtype=np.int64)
+    feature = np.ascontiguousarray(feature).astype(np.uint32)
+    value = np.ascontiguousarray(value, dtype=np.float32)
+    w = np.ascontiguousarray(w, dtype=np.float32)
+    out = np.empty(len(rowptr) - 1, np.float32)
+    lib().hmo_predict_linear(len(out), _p(rowptr), _p(feature), _p(value), _p(w), _p(out))
+    return out
+
+
+def model_table(w):
+    w = np.ascontiguousarray(w, dtype=np.float32)
+    n = lib().hmo_model_table(_p(w), len(w), None, None, 0)
+    f = np.empty(n, np.int32)
+    wt = np.empty(n, np.float32)
+    lib().hmo_model_table(_p(w), len(w), _p(f), _p(wt), n)
+    return f, wt
+
+
+class FmResult:
+    pass
+
+
+def fm_init_v(cfg: HmoConfig) -> np.ndarray:
+    V = np.empty(int(cfg.dims) * int(cfg.factors), np.float32)
+    lib().hmo_fm_init_v(C.byref(cfg), _p(V))
+    return V
+
+
+def train_fm(cfg: HmoConfig, rowptr, feature, value, label) -> FmResult:
+    rowptr = np.ascontiguousarray(rowptr, dtype=np.int64)
+    feature = np.ascontiguousarray(feature).astype(np.uint32)
+    value = np.ascontiguousarray(value, dtype=np.float32)
+    label = np.ascontiguousarray(label, dtype=np.float32)
+    n = len(rowptr) - 1
+    d, k = int(cfg.dims), int(cfg.factors)
+    r = FmResult()
+    r.w0 = np.zeros(1, np.float32)
+    r.gw0 = np.zeros(1, np.float32)
+    r.w = np.zeros(d, np.float32)
+    r.gw = np.zeros(d, np.float32)
+    r.V = fm_init_v(cfg)
+    r.gv = np.zeros(d * k, np.float32)
+    r.touched = np.zeros(d, np.uint8)
+    r.preds = np.zeros(n, np.float32)
+    tt = C.c_int64(0)
+    ls = C.c_double(0.0)
+    rc = lib().hmo_train_fm(C.byref(cfg), n, _p(rowptr), _p(feature), _p(value), _p(label), _p(r.w0), _p(r.w),
+                            _p(r.V), _p(r.gw0), _p(r.gw), _p(r.gv), _p(r.touched), C.byref(tt), _p(r.preds),
+                            C.byref(ls))
+    if rc != 0:
+        raise RuntimeError(f"hmo_train_fm failed: {rc}")
+    r.t, r.loss_sum = tt.value, ls.value
+    return r
+
+
+def predict_fm(cfg: HmoConfig, rowptr, feature, value, w0, w, V) -> np.ndarray:
+    rowptr = np.ascontiguousarray(rowptr, dtype=np.int64)
+    feature = np.ascontiguousarray(feature).astype(np.uint32)
+    value = np.ascontiguousarray(value, dtype=np.float32)
+    out = np.empty(len(rowptr) - 1, np.float32)
+    lib().hmo_predict_fm(C.byref(cfg), len(out), _p(rowptr), _p(feature), _p(value), float(w0),
+                         _p(np.ascontiguousarray(w, np.float32)), _p(np.ascontiguousarray(V, np.float32)), _p(out))
+    return out

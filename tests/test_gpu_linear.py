@@ -1,0 +1,167 @@
+"""Parity of the CUDA linear learner with the CPU oracle, through the C-ABI.
+
+PARITY UNPINNED w.r.t. Hivemall itself (no reference source is mounted): what is checked
+is the product against oracle/hm_oracle.c, two independent statements of DESIGN.md
+section 3, on identical rows, order, seed and mini-batch size.
+"""
+import numpy as np
+import pytest
+
+import hivemall_b200 as hm
+from hivemall_b200 import synth
+
+import _oracle
+from _util import assert_weights_close, run_gpu_linear, run_oracle_linear
+
+pytestmark = pytest.mark.gpu
+
+OPTS = ["sgd", "adagrad", "adadelta", "adam", "ftrl"]
+
+
+@pytest.mark.parametrize("opt", OPTS)
+def test_a9a_shaped_all_optimizers(opt):
+    """configs[0] shape: 123 binary features, -mini_batch 128, every optimizer."""
+    data = synth.a9a_like(4096 + 37, seed=0)      # ragged tail: last mini-batch is short
+    options = f"-loss logloss -opt {opt} -mini_batch 128 -dims 124 -eta0 0.1"
+    u, w, state = run_gpu_linear("train_classifier", options, data)
+    ref, ref_state = run_oracle_linear("train_classifier", options, data)
+    assert u.step == ref.t == (4096 + 37 + 127) // 128
+    assert_weights_close(w, ref.w, f"w[{opt}]")
+    assert_weights_close(state, ref_state, f"state[{opt}]")
+    u.destroy()
+
+
+def test_config0_full_model_table():
+    """configs[0] in full: 32K rows, logloss + AdaGrad, -mini_batch 128; the model table
+    (feature order and weights) and held-out AUC / logloss agree with the oracle."""
+    data = synth.a9a_like(32768, seed=0)
+    options = "-loss logloss -opt AdaGrad -mini_batch 128 -dims 124"
+    u, w, _ = run_gpu_linear("train_classifier", options, data, pushes=[10000, 10000, 12768])
+    ref, _ = run_oracle_linear("train_classifier", options, data)
+    assert_weights_close(w, ref.w)
+    feat, wt = u.forward()
+    ofeat, owt = _oracle.model_table(ref.w)
+    assert np.array_equal(feat, ofeat)            # bit-exact feature ordering of the model table
+    assert_weights_close(wt, owt, "model table weights")
+    held = synth.a9a_like(8192, seed=0, row0=1 << 20)
+    rp, f, v, y = held.numpy()
+    import torch
+    m_gpu = torch.from_numpy(u.predict(rp, f, v))
+    m_ref = torch.from_numpy(_oracle.predict_linear(rp, f, v, ref.w))
+    yt = torch.from_numpy(y)
+    assert abs(synth.auc(m_gpu, yt) - synth.auc(m_ref, yt)) < 1e-4
+    assert abs(synth.logloss(m_gpu, yt) - synth.logloss(m_ref, yt)) < 1e-4
+    assert synth.auc(m_gpu, yt) > 0.7             # it learned something
+    u.destroy()
+
+
+@pytest.mark.parametrize("loss,fn", [("logloss", "train_classifier"), ("hinge", "train_classifier"),
+                                     ("squared", "train_regressor")])
+def test_losses_on_ragged_rows(loss, fn):
+    """Uneven rows incl. empty ones, duplicate features inside a row, signed values."""
+    data = synth.ragged(3000, dims=5000, max_nnz=60, seed=3, regression=(fn == "train_regressor"))
+    options = f"-loss {loss} -opt adagrad -mini_batch 256 -dims 5000 -eta0 0.05"
+    u, w, state = run_gpu_linear(fn, options, data)
+    ref, ref_state = run_oracle_linear(fn, options, data)
+    assert_weights_close(w, ref.w)
+    assert_weights_close(state, ref_state, "state")
+    u.destroy()
+
+
+@pytest.mark.parametrize("opt", ["ftrl", "adam"])
+def test_criteo_shaped_hashed_dims(opt):
+    """configs[1]/[3] shape at oracle-sized scale: 39 feats/row, 2^20 hashed dims, mini-batches
+    large enough that hot features span many CTAs of the update kernel."""
+    data = synth.criteo_like(40000, dims=1 << 20, seed=1, regression=(opt == "adam"))
+    fn = "train_regressor" if opt == "adam" else "train_classifier"
+    loss = "squared" if opt == "adam" else "logloss"
+    options = f"-loss {loss} -opt {opt} -mini_batch 8192 -dims {1 << 20} -eta0 0.01"
+    u, w, state = run_gpu_linear(fn, options, data)
+    ref, ref_state = run_oracle_linear(fn, options, data)
+    assert_weights_close(w, ref.w)
+    assert_weights_close(state, ref_state, "state")
+    u.destroy()
+
+
+def test_push_boundaries_do_not_matter():
+    """Mini-batch boundaries belong to the row stream, not to the process() calls."""
+    data = synth.criteo_like(5000, dims=1 << 16, seed=2)
+    options = f"-opt adagrad -mini_batch 300 -dims {1 << 16}"
+    _, w1, s1 = run_gpu_linear("train_classifier", options, data, pushes=[5000])
+    _, w2, s2 = run_gpu_linear("train_classifier", options, data, pushes=[1, 299, 17, 1000, 2, 3681])
+    assert np.array_equal(w1, w2) and np.array_equal(s1, s2)   # same launches on the same data: bit-identical
+
+
+def test_iters_and_schedules():
+    data = synth.ragged(2000, dims=800, max_nnz=20, seed=5)
+    for extra in ["-iters 3 -eta inverse -power_t 0.2", "-iters 2 -eta simple -total_steps 10 -reg l2 -lambda 0.01",
+                  "-iters 2 -reg l1 -lambda 0.001 -opt sgd", "-grad_norm count", "-grad_norm sum -eta0 0.001"]:
+        options = f"-opt adagrad -mini_batch 128 -dims 800 {extra}"
+        u, w, state = run_gpu_linear("train_classifier", options, data, pushes=[700, 1300])
+        ref, ref_state = run_oracle_linear("train_classifier", options, data)
+        assert u.step == ref.t
+        assert_weights_close(w, ref.w, f"w[{extra}]")
+        assert_weights_close(state, ref_state, f"state[{extra}]")
+        u.destroy()
+
+
+def test_deterministic_rerun():
+    """No float atomics anywhere: two runs are bit-identical."""
+    data = synth.criteo_like(30000, dims=1 << 18, seed=7)
+    options = f"-opt ftrl -mini_batch 4096 -dims {1 << 18}"
+    _, w1, s1 = run_gpu_linear("train_classifier", options, data)
+    _, w2, s2 = run_gpu_linear("train_classifier", options, data)
+    assert np.array_equal(w1, w2) and np.array_equal(s1, s2)
+
+
+def test_edge_cases():
+    # empty input: close() on a learner that saw nothing gives an empty model table
+    u = hm.train_classifier("-dims 100 -mini_batch 8")
+    assert u.close() == 0
+    f, w = u.forward()
+    assert len(f) == 0 and len(w) == 0
+    u.destroy()
+    # rows with no features at all
+    u = hm.train_classifier("-dims 100 -mini_batch 4")
+    u.process_batch(np.zeros(11, np.int64), np.zeros(0, np.int32), np.zeros(0, np.float32), np.ones(10, np.float32))
+    assert u.close() == 0 and u.step == 3
+    u.destroy()
+    # a single row, mini-batch larger than the data
+    u = hm.train_classifier("-dims 10 -mini_batch 1000 -opt sgd -eta0 1.0")
+    u.process([(3, 2.0), (7, -1.0)], 1)
+    assert u.close() == 2
+    f, w = u.forward()
+    assert list(f) == [3, 7]
+    np.testing.assert_allclose(w, [1.0, -0.5], rtol=1e-6)   # -eta * dloss * x, dloss = -1/(1+e^0) = -0.5
+    u.destroy()
+    # out-of-range feature index is an error at close(), not a crash
+    u = hm.train_classifier("-dims 10 -mini_batch 2")
+    u.process([(10, 1.0)], 1)
+    with pytest.raises(hm.UDFArgumentError):
+        u.close()
+    u.destroy()
+    # lifecycle errors
+    u = hm.train_classifier("-dims 10")
+    with pytest.raises(hm.HivemallError):   # forward() before close()
+        hm.udtf.check(u._lib.hm_udtf_forward(u._h, None, None, None, 0, None))
+    u.close()
+    with pytest.raises(hm.HivemallError):
+        u.process_batch(np.zeros(2, np.int64), np.zeros(0, np.int32), np.zeros(0, np.float32), np.ones(1, np.float32))
+    u.destroy()
+
+
+def test_process_device_matches_host_path():
+    import torch
+    data = synth.criteo_like(16384, dims=1 << 18, seed=11, device="cuda")
+    options = f"-opt ftrl -mini_batch 4096 -dims {1 << 18}"
+    u = hm.train_classifier(options)
+    u.process_device(data.rows, data.nnz, data.rowptr, data.feature, data.value, data.label)
+    u.close()
+    w_dev = u.array_to_host("w")
+    host = synth.Csr(data.rowptr.cpu(), data.feature.cpu(), data.value.cpu(), data.label.cpu())
+    _, w_host, _ = run_gpu_linear("train_classifier", options, host)
+    assert np.array_equal(w_dev, w_host)
+    ref, _ = run_oracle_linear("train_classifier", options, host)
+    assert_weights_close(w_dev, ref.w)
+    torch.cuda.synchronize()
+    u.destroy()
