@@ -190,7 +190,7 @@ void hmo_predict_linear(int64_t n_rows, const int64_t *rowptr, const uint32_t *i
     for (int64_t i = 0; i < n_rows; i++) {
         double acc = 0.0;
         for (int64_t p = rowptr[i]; p < rowptr[i + 1]; p++)
-            acc += (double)w[idx[p]] * (double)val[p];
+            acc += (double)(w[idx[p]] * val[p]);   /* fp32 product, fp64 sum */
         margin[i] = (float)acc;
     }
 }
@@ -225,7 +225,7 @@ int hmo_train_linear(const hmo_config *c, int64_t n_rows, const int64_t *rowptr,
                 double acc = 0.0;
                 for (int64_t p = rowptr[i]; p < rowptr[i + 1]; p++) {
                     if ((int64_t)idx[p] >= c->dims) { free(gsum); free(cnt); free(dl); free(touch); return -3; }
-                    acc += (double)w[idx[p]] * (double)val[p];
+                    acc += (double)(w[idx[p]] * val[p]);   /* fp32 product, fp64 sum */
                 }
                 float m = (float)acc;
                 float y = target_of(c, label[i]);
@@ -239,7 +239,7 @@ int hmo_train_linear(const hmo_config *c, int64_t n_rows, const int64_t *rowptr,
                 for (int64_t p = rowptr[i]; p < rowptr[i + 1]; p++) {
                     uint32_t j = idx[p];
                     if (cnt[j]++ == 0) touch[nt++] = j;
-                    gsum[j] += (double)dl[i - b0] * (double)val[p];
+                    gsum[j] += (double)(dl[i - b0] * val[p]);   /* fp32 product, fp64 sum (3.4) */
                 }
             /* one optimizer update per touched feature */
             *t += 1;
