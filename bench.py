@@ -1,0 +1,406 @@
+#!/usr/bin/env python
+"""bench.py -- examples/sec of the training hot path on B200, with roofline and CPU baseline.
+
+Workload (BASELINE.json configs[1]): train_classifier, logistic loss + FTRL, 2^24 hashed
+dims, Criteo-shaped synthetic rows (39 features/row), 100M rows per GPU, -mini_batch 65536
+(BASELINE.json leaves the mini-batch size open; it is stated in `config`).
+
+A "step" is one pass of the hot path over one ingest block of ROWS_PER_STEP rows (64
+mini-batches): segmented sort-by-feature of the block, then per mini-batch the forward
+and the fused reduce+update kernels.  Inputs are far larger than L2 (1.3 GB per step).
+
+  value     rows/s with the block already resident in HBM (hm_udtf_process_device)
+  e2e       rows/s through the host-buffer C-ABI call (hm_udtf_process on pinned host
+            memory: H2D inside the timed region, plus a D2H read of the last mini-batch's
+            margins every step)
+  roofline  dominant kernel (largest share of device time), per-launch algorithmic bytes /
+            CUDA-event duration on the learner's stream, against MEASURED_PEAKS.json
+  cpu_baseline  the oracle (oracle/hm_oracle.c, OpenMP) on a bounded sample of the same
+            workload on the host cores; kind "port": the reference mount holds no code
+
+`--impl reference` times the CPU arm alone.  No published reference number exists
+(BASELINE.md), so vs_baseline is null.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+DIMS = 1 << 24
+MINI_BATCH = 65536
+ROWS_PER_STEP = 1 << 22
+TOTAL_ROWS = 24 * ROWS_PER_STEP          # 100,663,296 rows >= the 100M of configs[1]
+OPTIONS = f"-loss logloss -opt ftrl -mini_batch {MINI_BATCH} -dims {DIMS} -alpha 0.05 -lambda1 0.0001"
+NNZ_PER_ROW = 39
+SEED = 1
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=24)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--rows-per-step", type=int, default=ROWS_PER_STEP)
+    ap.add_argument("--total-rows", type=int, default=TOTAL_ROWS)
+    ap.add_argument("--cpu-sample-rows", type=int, default=0, help="0 = sized for ~15 s")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    return ap.parse_args()
+
+
+# ------------------------------------------------------------------------- helpers
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms while a region runs."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index = index
+        self.proc = None
+        self.lines: list[str] = []
+
+    def __enter__(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                 "-lms", "200"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+        return self
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def __exit__(self, *exc):
+        if self.proc:
+            time.sleep(0.25)
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=2)
+            except subprocess.TimeoutExpired:
+                self.proc.kill()
+
+    def summary(self) -> dict:
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            parts = [p.strip() for p in ln.split(",")]
+            if len(parts) < 7:
+                continue
+            try:
+                sm.append(float(parts[0]))
+                mx.append(float(parts[1]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, parts[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        return {"sm_mhz": statistics.median(sm), "sm_max_mhz": max(mx), "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+def jsonable(o, path="out"):
+    """Plain-Python copy of the result dict (numpy / torch scalars -> float / int)."""
+    if isinstance(o, dict):
+        return {k: jsonable(v, f"{path}.{k}") for k, v in o.items()}
+    if isinstance(o, (list, tuple)):
+        return [jsonable(v, f"{path}[]") for v in o]
+    if o is None or isinstance(o, (bool, int, float, str)):
+        return o
+    if hasattr(o, "item"):
+        print(f"bench.py: {path} was a {type(o).__name__}", file=sys.stderr)
+        return o.item()
+    return str(o)
+
+
+def measured_peaks() -> tuple[float, str]:
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    try:
+        with open(path) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def cpu_baseline(rows: int, threads: int) -> dict:
+    """Oracle (OpenMP) on the first `rows` rows of the same synthetic stream."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import hivemall_b200 as hm
+    from hivemall_b200 import synth
+    import _oracle
+    cfg = _oracle.config_from(hm.parse_options("train_classifier", OPTIONS))
+    pieces = []
+    for r0 in range(0, rows, 1 << 20):
+        pieces.append(synth.criteo_like(min(1 << 20, rows - r0), dims=DIMS, seed=SEED, row0=r0))
+    import numpy as np
+    feature = np.concatenate([p.feature.numpy() for p in pieces])
+    value = np.concatenate([p.value.numpy() for p in pieces])
+    label = np.concatenate([p.label.numpy() for p in pieces])
+    rowptr = np.arange(rows + 1, dtype=np.int64) * NNZ_PER_ROW
+    _oracle.train_linear_mt(cfg, rowptr[: MINI_BATCH + 1], feature, value, label[:MINI_BATCH], threads)  # page in
+    t0 = time.perf_counter()
+    _oracle.train_linear_mt(cfg, rowptr, feature, value, label, threads)
+    dt = time.perf_counter() - t0
+    return {"value": rows / dt, "unit": "examples/s", "cores": threads, "kind": "port",
+            "sample": f"first {rows} rows of the same stream, {OPTIONS}, oracle/hm_oracle.c hmo_train_linear_mt "
+                      f"({threads} OpenMP threads, {dt:.1f} s); kind=port because the reference mount holds no code",
+            "seconds": dt}
+
+
+def run_reference_arm(args) -> None:
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    threads = os.cpu_count() or 1
+    # calibrate so that each step is a bounded sample (~5 s), whole run within a few minutes
+    probe = cpu_baseline(2 * MINI_BATCH, threads)
+    rows = int(max(2 * MINI_BATCH, min(probe["value"] * 5.0, 16 * MINI_BATCH)))
+    rows = rows // MINI_BATCH * MINI_BATCH
+    times = []
+    for i in range(args.warmup + args.steps):
+        r = cpu_baseline(rows, threads)
+        if i >= args.warmup:
+            times.append(r["seconds"])
+    dt = sum(times) / len(times)
+    value = rows / dt
+    out = {
+        "impl": "reference", "metric": "examples/sec (train_classifier logloss+FTRL, 2^24 hashed dims, Criteo-shaped)",
+        "value": value, "unit": "examples/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32 (fp64 sums)", "data": "synthetic",
+        "config": {"workload": "configs[1]: train_classifier logistic+FTRL, 2^24 dims, Criteo-shaped 39 feats/row",
+                   "options": OPTIONS, "mini_batch": MINI_BATCH, "rows_per_step": rows,
+                   "note": "CPU arm; each step is a bounded sample of the stream"},
+        "cpu_baseline": {"value": value, "unit": "examples/s", "cores": threads, "kind": "port",
+                         "sample": f"{rows} rows per step, OpenMP oracle; the reference mount holds no code to run"},
+        "e2e": {"value": value, "unit": "examples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(out))
+
+
+# ------------------------------------------------------------------------- GPU arm
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference_arm(args)
+        return
+
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    import hivemall_b200 as hm
+    from hivemall_b200 import synth, mix
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: hivemall_b200 has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    K, W = args.steps, args.warmup
+    rps = args.rows_per_step // MINI_BATCH * MINI_BATCH
+    n_blocks = max(1, min(args.total_rows // rps, K + W))
+    # ---- synthetic rows of this rank's shard, resident in HBM
+    row_base = rank * args.total_rows
+    blocks = []
+    for b in range(n_blocks):
+        parts = [synth.criteo_like(min(1 << 20, rps - r), dims=DIMS, seed=SEED, device=dev, row0=row_base + b * rps + r)
+                 for r in range(0, rps, 1 << 20)]
+        feature = torch.cat([p.feature for p in parts])
+        value = torch.cat([p.value for p in parts])
+        label = torch.cat([p.label for p in parts])
+        rowptr = torch.arange(rps + 1, device=dev, dtype=torch.int64) * NNZ_PER_ROW
+        blocks.append((rowptr, feature, value, label))
+        del parts
+    nnz_step = rps * NNZ_PER_ROW
+    torch.cuda.synchronize()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-resident arm ------------------------------------------------------
+    u = hm.train_classifier(OPTIONS, device=local_rank)
+    mixer = mix.ReplicaMixer(u, world) if world > 1 else None
+    stream = torch.cuda.ExternalStream(u.stream, device=dev)
+
+    def step_device(i):
+        rowptr, feature, value, label = blocks[i % n_blocks]
+        u.process_device(rps, nnz_step, rowptr, feature, value, label)
+        if mixer:
+            mixer.mix()     # MIX averaging at the step boundary (every 64 mini-batches)
+
+    for i in range(W):
+        step_device(i)
+    u.sync()
+    barrier()
+    launches0 = u.stats().kernel_launches
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with ClockSampler(local_rank) as clocks:
+        with torch.cuda.stream(stream):
+            e0.record()
+        for i in range(W, W + K):
+            step_device(i)
+        with torch.cuda.stream(stream):
+            e1.record()
+        u.sync()
+        barrier()
+    ms = e0.elapsed_time(e1)
+    launches = u.stats().kernel_launches - launches0
+    if world > 1:
+        tms = torch.tensor([ms], device=dev)
+        dist.all_reduce(tms, op=dist.ReduceOp.MAX)
+        ms = float(tms)
+    rows_per_s = world * rps * K / (ms / 1e3)
+
+    # ---- same steps again with per-kernel CUDA events (roofline of the dominant kernel)
+    u.set_profiling(True)
+    p0, p1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with torch.cuda.stream(stream):
+        p0.record()
+    for i in range(W + K, W + 2 * K):
+        step_device(i)
+    with torch.cuda.stream(stream):
+        p1.record()
+    u.sync()
+    u.set_profiling(False)
+    ms_prof = p0.elapsed_time(p1)
+    kt = {k: v for k, v in u.kernel_times().items() if v["launches"] > 0}
+    total_kernel_ms = sum(v["ms"] for v in kt.values())
+    dom = max(kt, key=lambda k: kt[k]["ms"])
+    d = kt[dom]
+    peak, peak_src = measured_peaks()
+    achieved = (d["bytes"] / d["launches"]) / (d["ms"] / d["launches"] * 1e-3) / 1e9 if d["ms"] > 0 else 0.0
+    roofline = {
+        "bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s",
+        "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+        "launches": d["launches"], "avg_us": d["ms"] / d["launches"] * 1e3,
+        "algorithmic_bytes_per_launch": d["bytes"] / d["launches"],
+        "share_of_kernel_time": d["ms"] / total_kernel_ms if total_kernel_ms else None,
+        "kernels": {k: {"launches": v["launches"], "ms": round(v["ms"], 3),
+                        "GBps": round(v["bytes"] / (v["ms"] * 1e-3) / 1e9, 1) if v["ms"] > 0 and v["bytes"] > 0 else None}
+                    for k, v in sorted(kt.items(), key=lambda kv: -kv[1]["ms"])},
+        "profiled_ms_per_step": ms_prof / K,
+    }
+    # whole-pipeline view: algorithmic bytes of every kernel over the plain timed region
+    pipeline_bytes = sum(v["bytes"] for v in kt.values()) / K
+    roofline["pipeline_GBps"] = pipeline_bytes / (ms / K * 1e-3) / 1e9
+
+    # ---- end-to-end arm: host buffers through hm_udtf_process ----------------------
+    e2e = None
+    if not args.no_e2e:
+        n_host = min(n_blocks, 4)
+        host = []
+        for b in range(n_host):
+            rowptr, feature, value, label = blocks[b]
+            arrs = []
+            for t in (rowptr, feature, value, label):
+                addr, view = hm.host_alloc(t.numel() * t.element_size())
+                pinned = torch.frombuffer(view, dtype=t.dtype)
+                pinned.copy_(t)
+                arrs.append((addr, pinned))
+            host.append(arrs)
+        torch.cuda.synchronize()
+        v = hm.train_classifier(OPTIONS, device=local_rank)
+        mixer2 = mix.ReplicaMixer(v, world) if world > 1 else None
+        margins = np.empty(MINI_BATCH, dtype=np.float32)
+        losses = []
+
+        def step_host(i):
+            (rp, _), (ft, _), (vl, _), (lb, lbt) = host[i % n_host]
+            v.process_pointers(rps, rp, ft, vl, lb)
+            if mixer2:
+                mixer2.mix()
+            m = v.last_margins(margins)                      # D2H read of the step's result, waits
+            y = lbt[rps - len(m):].numpy() * 2 - 1
+            losses.append(float(np.mean(np.logaddexp(0.0, -y * m))))
+
+        for i in range(W):
+            step_host(i)
+        barrier()
+        t0 = time.perf_counter()
+        for i in range(W, W + K):
+            step_host(i)
+        v.sync()
+        barrier()
+        dt = time.perf_counter() - t0
+        if world > 1:
+            tdt = torch.tensor([dt], device=dev)
+            dist.all_reduce(tdt, op=dist.ReduceOp.MAX)
+            dt = float(tdt)
+        h2d = (rps + 1) * 8 + nnz_step * 8 + rps * 4
+        e2e = {"value": world * rps * K / dt, "unit": "examples/s", "h2d_bytes_per_step": h2d,
+               "d2h_bytes_per_step": MINI_BATCH * 4, "ms_per_step": dt / K * 1e3,
+               "last_minibatch_logloss": losses[-1], "pcie_GBps": h2d * K / dt / 1e9,
+               "timing": "host wall clock around K calls, each ending in a blocking D2H read"}
+        v.destroy()
+        for arrs in host:
+            for addr, _ in arrs:
+                hm.host_free(addr)
+
+    # ---- CPU baseline (rank 0, N=1 only) -------------------------------------------
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        threads = os.cpu_count() or 1
+        rows = args.cpu_sample_rows
+        if rows <= 0:
+            probe = cpu_baseline(2 * MINI_BATCH, threads)
+            rows = int(max(2 * MINI_BATCH, min(probe["value"] * 15.0, 256 * MINI_BATCH)))
+        rows = max(MINI_BATCH, rows // MINI_BATCH * MINI_BATCH)
+        cpu = cpu_baseline(rows, threads)
+        cpu.pop("seconds", None)
+
+    if rank == 0:
+        out = {
+            "metric": "examples/sec (train_classifier logloss+FTRL, 2^24 hashed dims, Criteo-shaped)",
+            "value": rows_per_s, "unit": "examples/s", "n_gpus": world, "steps": K, "warmup": W,
+            "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32 (fp64 sums)", "data": "synthetic",
+            "nnz_per_sec": rows_per_s * NNZ_PER_ROW,
+            "config": {
+                "workload": "configs[1]: train_classifier logistic+FTRL, 2^24 hashed dims, Criteo-shaped "
+                            "synthetic (39 feats/row), 100M rows per GPU",
+                "options": OPTIONS, "mini_batch": MINI_BATCH, "rows_per_step": rps,
+                "mini_batches_per_step": rps // MINI_BATCH, "rows_resident_per_gpu": n_blocks * rps,
+                "l2": "inputs larger than L2 (1.3 GB streamed per step)",
+                "mix": "all-reduce of w and (z,n) every step" if world > 1 else "none (1 GPU)",
+                "parallelism": f"dp{world}: row shards, full replica per GPU",
+            },
+            "roofline": roofline,
+            "cpu_baseline": cpu,
+            "e2e": e2e,
+            "gpu_launches": int(launches),
+            "clocks": clocks.summary(),
+        }
+        print(json.dumps(jsonable(out)))
+    u.destroy()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -29,9 +29,9 @@ const char *last_error_cstr();
 void Launcher::begin(int id, double alg_bytes)
 {
     launches++;
-    count[id]++;
-    bytes[id] += alg_bytes;
     if (!profiling) return;
+    count[id]++;            // per-kernel statistics cover profiled launches only
+    bytes[id] += alg_bytes;
     Pending p;
     p.id = id;
     for (cudaEvent_t *e : {&p.a, &p.b}) {
@@ -166,6 +166,7 @@ struct hm_udtf {
     int stage_turn = 0;
     int64_t *h_small = nullptr;      // pinned scratch for small D2H reads
     int64_t h_small_cap = 0;
+    int64_t last_margin_off = 0, last_margin_n = 0;   // last mini-batch's slice of `margin`
     bool device_rows_short = false;  // a process_device call ended on a short mini-batch
     hm_stats stats;
     bool closed = false;
@@ -255,6 +256,8 @@ hm_status train_rows(hm_udtf *u, const Chunk &c, int64_t row0, int64_t n_rows, c
             HM_TRY(launch_linear_update(u->L, a, sc, u->upd, u->sort.key[buf], u->sort.pay[buf], u->sort.seg_off, s,
                                         u->contrib.as<float>(), mnnz));
             u->stats.mini_batches++;
+            u->last_margin_off = mrow0 - b_row0;
+            u->last_margin_n = mrows;
         }
         u->stats.rows += b_rows;
         u->stats.nnz += b_nnz;
@@ -607,7 +610,7 @@ hm_status hm_udtf_process_device(hm_udtf *u, int64_t n_rows, int64_t nnz, const 
         HM_TRY(ensure_small(u, n_mb + 1));
         const int grid = (int)std::min<int64_t>((n_mb + 256) / 256, 1024);
         gather_rowptr_kernel<<<grid, 256, 0, u->copy>>>(d_rowptr, n_rows, (int32_t)B, n_mb + 1, u->mb_gather.as<int64_t>());
-        u->L.launches++; u->L.count[K_MISC]++;
+        u->L.launches++;
         HM_CUDA(cudaGetLastError());
         HM_CUDA(cudaMemcpyAsync(u->h_small, u->mb_gather.p, (size_t)(n_mb + 1) * 8, cudaMemcpyDeviceToHost, u->copy));
         HM_CUDA(cudaStreamSynchronize(u->copy));
@@ -849,6 +852,21 @@ hm_status hm_udtf_predict(hm_udtf *u, int64_t n_rows, const int64_t *rowptr, con
     HM_CUDA(cudaStreamSynchronize(u->compute));   // also keeps `rp` alive long enough
     u->stats.h2d_bytes += (n_rows + 1) * 8 + nnz * 8;
     u->stats.d2h_bytes += n_rows * 4;
+    return HM_OK;
+}
+
+hm_status hm_udtf_last_margins(hm_udtf *u, float *host, int64_t cap, int64_t *n)
+{
+    if (!u || !n || cap < 0 || (cap > 0 && !host)) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "bad arguments to last_margins");
+    DeviceGuard g(u->device);
+    const int64_t m = std::min(cap, u->last_margin_n);
+    if (m > 0) {
+        HM_CUDA(cudaMemcpyAsync(host, u->margin.as<float>() + u->last_margin_off, (size_t)m * 4, cudaMemcpyDeviceToHost,
+                                u->compute));
+        u->stats.d2h_bytes += m * 4;
+    }
+    HM_CUDA(cudaStreamSynchronize(u->compute));
+    *n = m;
     return HM_OK;
 }
 

@@ -273,6 +273,14 @@ class UDTF:
     def predict_device(self, n_rows: int, rowptr, feature, value, out) -> None:
         check(self._lib.hm_udtf_predict_device(self._h, n_rows, _ptr(rowptr), _ptr(feature), _ptr(value), _ptr(out)))
 
+    def last_margins(self, out: np.ndarray | None = None) -> np.ndarray:
+        """Margins of the most recently trained mini-batch (device->host copy, waits)."""
+        if out is None:
+            out = np.empty(self.config.mini_batch, dtype=np.float32)
+        n = C.c_int64()
+        check(self._lib.hm_udtf_last_margins(self._h, _ptr(out), len(out), C.byref(n)))
+        return out[: n.value]
+
     # ---- measurement ---------------------------------------------------------------
     def stats(self) -> HmStats:
         s = HmStats()

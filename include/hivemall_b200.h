@@ -189,6 +189,11 @@ hm_status hm_udtf_predict(hm_udtf *u, int64_t n_rows, const int64_t *rowptr,
 hm_status hm_udtf_predict_device(hm_udtf *u, int64_t n_rows, const int64_t *d_rowptr,
                                  const int32_t *d_feature, const float *d_value, float *d_out);
 
+/* Margins the rows of the most recently trained mini-batch had when they were scored
+ * (before that mini-batch's update): the per-step training signal a caller logs or turns
+ * into a loss.  Copies min(cap, rows) floats to `host`, waits for the GPU, sets *n. */
+hm_status hm_udtf_last_margins(hm_udtf *u, float *host, int64_t cap, int64_t *n);
+
 /* ---- measurement ----------------------------------------------------------- */
 
 hm_status hm_udtf_stats(const hm_udtf *u, hm_stats *out);

@@ -13,6 +13,9 @@
 #include <math.h>
 #include <stdlib.h>
 #include <string.h>
+#ifdef _OPENMP
+#include <omp.h>
+#endif
 
 /* ---------------------------------------------------------------- hashing */
 
@@ -257,6 +260,112 @@ int hmo_train_linear(const hmo_config *c, int64_t n_rows, const int64_t *rowptr,
     }
     if (loss_sum) *loss_sum = lsum;
     free(gsum); free(cnt); free(dl); free(touch);
+    return 0;
+}
+
+/* Multi-threaded variant for the timed CPU baseline: same arithmetic and the same
+ * per-feature summation order (rows in order), so the result is bit-identical to
+ * hmo_train_linear.  Per mini-batch: (1) rows are scored in parallel, each thread owning
+ * a contiguous row slice; (2) each thread buckets its slice's (feature, dloss*x) pairs by
+ * the thread that owns the feature (contiguous feature ranges); (3) each owner walks the
+ * buckets addressed to it in source-thread order -- i.e. in row order -- accumulates in
+ * fp64 and applies the optimizer to its features. */
+typedef struct { uint32_t j; float c; } hmo_pair;
+
+int hmo_train_linear_mt(const hmo_config *c, int64_t n_rows, const int64_t *rowptr,
+                        const uint32_t *idx, const float *val, const float *label,
+                        float *w, float *s1, float *s2, int64_t *t, int threads)
+{
+    if (c->mini_batch < 1 || c->dims < 1 || threads < 1) return -1;
+    if (threads > 256) threads = 256;
+    const int64_t B = c->mini_batch;
+    const int T = threads;
+    double *gsum = (double *)calloc((size_t)c->dims, sizeof(double));
+    uint32_t *cnt = (uint32_t *)calloc((size_t)c->dims, sizeof(uint32_t));
+    float *dl = (float *)malloc((size_t)B * sizeof(float));
+    int64_t max_touch = 1;
+    for (int64_t b0 = 0; b0 < n_rows; b0 += B) {
+        int64_t e = b0 + B < n_rows ? b0 + B : n_rows;
+        if (rowptr[e] - rowptr[b0] > max_touch) max_touch = rowptr[e] - rowptr[b0];
+    }
+    hmo_pair *pairs = (hmo_pair *)malloc((size_t)max_touch * sizeof(hmo_pair));
+    uint32_t *touch = (uint32_t *)malloc((size_t)max_touch * sizeof(uint32_t));
+    int64_t *off = (int64_t *)calloc((size_t)T * (T + 1), sizeof(int64_t));  /* off[src][owner] */
+    if (!gsum || !cnt || !dl || !pairs || !touch || !off) return -2;
+    const int64_t per_owner = (c->dims + T - 1) / T;
+    float dummy[256];
+    for (int32_t it = 0; it < c->iters; it++) {
+        for (int64_t b0 = 0; b0 < n_rows; b0 += B) {
+            const int64_t b1 = b0 + B < n_rows ? b0 + B : n_rows;
+            const int64_t nb = b1 - b0;
+            const int64_t e0 = rowptr[b0];
+            *t += 1;
+            const float eta = hmo_eta(c, *t);
+            const float alpha_t = c->opt == HMO_OPT_ADAM ? adam_alpha(c, eta, *t) : 0.0f;
+#pragma omp parallel num_threads(T)
+            {
+#ifdef _OPENMP
+                const int tid = omp_get_thread_num(), nth = omp_get_num_threads();
+#else
+                const int tid = 0, nth = 1;
+#endif
+                /* this thread's contiguous row slice */
+                const int64_t r0 = b0 + nb * tid / nth, r1 = b0 + nb * (tid + 1) / nth;
+                int64_t *my = off + (int64_t)tid * (T + 1);
+                for (int k = 0; k <= T; k++) my[k] = 0;
+                for (int64_t i = r0; i < r1; i++) {
+                    double acc = 0.0;
+                    for (int64_t p = rowptr[i]; p < rowptr[i + 1]; p++) {
+                        acc += (double)(w[idx[p]] * val[p]);
+                        my[idx[p] / per_owner + 1]++;
+                    }
+                    dl[i - b0] = hmo_dloss(c->loss, (float)acc, target_of(c, label[i]));
+                }
+                /* bucket offsets inside this thread's region of `pairs` (region = its element range) */
+                const int64_t base = rowptr[r0] - e0;
+                int64_t run = base;
+                for (int k = 0; k < nth; k++) { int64_t n = my[k + 1]; my[k] = run; run += n; }
+                my[nth] = run;
+                int64_t cur[256];
+                for (int k = 0; k < nth; k++) cur[k] = my[k];
+                for (int64_t i = r0; i < r1; i++)
+                    for (int64_t p = rowptr[i]; p < rowptr[i + 1]; p++) {
+                        const uint32_t j = idx[p];
+                        hmo_pair *q = &pairs[cur[j / per_owner]++];
+                        q->j = j;
+                        q->c = dl[i - b0] * val[p];
+                    }
+#pragma omp barrier
+                /* owner phase.  Owner k receives recv[k] elements, so it touches at most recv[k]
+                 * features: its touched list is the slice of `touch` after all lower owners'. */
+                int64_t tbase = 0;
+                for (int k = 0; k < tid; k++)
+                    for (int src = 0; src < nth; src++) {
+                        const int64_t *so = off + (int64_t)src * (T + 1);
+                        tbase += so[k + 1] - so[k];
+                    }
+                uint32_t *mine = touch + tbase;
+                int64_t nt = 0;
+                for (int src = 0; src < nth; src++) {
+                    const int64_t *so = off + (int64_t)src * (T + 1);
+                    for (int64_t q = so[tid]; q < so[tid + 1]; q++) {
+                        const uint32_t j = pairs[q].j;
+                        if (cnt[j]++ == 0) mine[nt++] = j;
+                        gsum[j] += (double)pairs[q].c;
+                    }
+                }
+                for (int64_t k = 0; k < nt; k++) {
+                    const uint32_t j = mine[k];
+                    const double denom = c->grad_norm == HMO_NORM_BATCH ? (double)nb
+                                       : c->grad_norm == HMO_NORM_COUNT ? (double)cnt[j] : 1.0;
+                    const float g = (float)(gsum[j] / denom);
+                    update_coord(c, eta, alpha_t, g, &w[j], s1 ? &s1[j] : &dummy[tid], s2 ? &s2[j] : &dummy[tid]);
+                    gsum[j] = 0.0; cnt[j] = 0;
+                }
+            }
+        }
+    }
+    free(pairs); free(touch); free(off); free(gsum); free(cnt); free(dl);
     return 0;
 }
 

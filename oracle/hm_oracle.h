@@ -82,6 +82,12 @@ int hmo_train_linear(const hmo_config *c, int64_t n_rows, const int64_t *rowptr,
                      float *w, float *s1, float *s2, int64_t *t,
                      float *margins, double *loss_sum);
 
+/* Same result bit for bit, rows and features spread over `threads` OpenMP threads
+ * (the timed CPU baseline of bench.py). */
+int hmo_train_linear_mt(const hmo_config *c, int64_t n_rows, const int64_t *rowptr,
+                        const uint32_t *idx, const float *val, const float *label,
+                        float *w, float *s1, float *s2, int64_t *t, int threads);
+
 /* margin[i] = sum_j w[idx]*val, DESIGN.md section 3.1 arithmetic. */
 void hmo_predict_linear(int64_t n_rows, const int64_t *rowptr, const uint32_t *idx,
                         const float *val, const float *w, float *margin);

@@ -53,6 +53,9 @@ def lib() -> C.CDLL:
         L.hmo_train_linear.restype = C.c_int
         L.hmo_train_linear.argtypes = [C.POINTER(HmoConfig), C.c_int64, _P, _P, _P, _P, _P, _P, _P,
                                        C.POINTER(C.c_int64), _P, C.POINTER(C.c_double)]
+        L.hmo_train_linear_mt.restype = C.c_int
+        L.hmo_train_linear_mt.argtypes = [C.POINTER(HmoConfig), C.c_int64, _P, _P, _P, _P, _P, _P, _P,
+                                          C.POINTER(C.c_int64), C.c_int]
         L.hmo_predict_linear.restype = None
         L.hmo_predict_linear.argtypes = [C.c_int64, _P, _P, _P, _P, _P]
         L.hmo_fm_init_v.restype = None
@@ -128,6 +131,24 @@ def train_linear(cfg: HmoConfig, rowptr, feature, value, label, w=None, s1=None,
     if rc != 0:
         raise RuntimeError(f"hmo_train_linear failed: {rc}")
     return LinearResult(w, s1, s2, tt.value, margins, ls.value)
+
+
+def train_linear_mt(cfg: HmoConfig, rowptr, feature, value, label, threads: int) -> LinearResult:
+    """OpenMP variant used as the timed CPU baseline; inputs must already be contiguous
+    int64 / uint32-compatible / float32 arrays (no copies are made of the big ones)."""
+    rowptr = np.ascontiguousarray(rowptr, dtype=np.int64)
+    feature = np.ascontiguousarray(feature)
+    assert feature.dtype in (np.int32, np.uint32)
+    value = np.ascontiguousarray(value, dtype=np.float32)
+    label = np.ascontiguousarray(label, dtype=np.float32)
+    d = int(cfg.dims)
+    w, s1, s2 = np.zeros(d, np.float32), np.zeros(d, np.float32), np.zeros(d, np.float32)
+    tt = C.c_int64(0)
+    rc = lib().hmo_train_linear_mt(C.byref(cfg), len(rowptr) - 1, _p(rowptr), _p(feature), _p(value), _p(label),
+                                   _p(w), _p(s1), _p(s2), C.byref(tt), threads)
+    if rc != 0:
+        raise RuntimeError(f"hmo_train_linear_mt failed: {rc}")
+    return LinearResult(w, s1, s2, tt.value, None, 0.0)
 
 
 def predict_linear(rowptr, feature, value, w) -> np.ndarray:
