@@ -1,0 +1,191 @@
+"""The CPU oracle against (a) the public MurmurHash3 known answers -- the only part of the
+path that CAN be pinned, since the reference mount holds no code -- and (b) an independent
+numpy restatement of DESIGN.md section 3 on small inputs, (c) its own OpenMP variant."""
+import json
+import os
+import struct
+
+import numpy as np
+import pytest
+
+import hivemall_b200 as hm
+from hivemall_b200 import synth
+
+import _oracle
+
+GOLDEN = os.path.join(os.path.dirname(__file__), "golden", "murmur3_kat.json")
+
+
+def test_murmur3_public_vectors():
+    kat = json.load(open(GOLDEN))
+    assert len(kat["vectors"]) >= 19
+    for v in kat["vectors"]:
+        assert _oracle.murmur3(bytes.fromhex(v["hex"]), v["seed"]) == v["hash"], v
+
+
+def test_murmur3_smhasher_verification_value():
+    kat = json.load(open(GOLDEN))
+    key = bytes(range(256))
+    hashes = b"".join(struct.pack("<I", _oracle.murmur3(key[:i], 256 - i)) for i in range(256))
+    assert _oracle.murmur3(hashes, 0) == kat["smhasher_verification"] == 0xB0F57EE3
+
+
+def test_fold_is_java_remainder():
+    L = _oracle.lib()
+    assert L.hmo_fold(0xFFFFFFF9, 4) == 1          # (int)-7 % 4 = -3 -> +4
+    assert L.hmo_fold(7, 4) == 3
+    assert L.hmo_fold(0x80000000, 1 << 24) == 0
+    for h in [0, 1, 0x7FFFFFFF, 0x80000001, 0xDEADBEEF]:
+        assert L.hmo_fold(h, 1 << 24) == (h & 0xFFFFFF)  # power of two: same as masking
+        assert 0 <= L.hmo_fold(h, 16777213) < 16777213
+
+
+def test_exp_accuracy():
+    L = _oracle.lib()
+    xs = np.linspace(-87, 88, 20001).astype(np.float32)
+    got = np.array([L.hmo_exp(float(x)) for x in xs], dtype=np.float64)
+    want = np.exp(xs.astype(np.float64))
+    assert np.max(np.abs(got - want) / want) < 4e-7
+    assert L.hmo_exp(0.0) == 1.0 and L.hmo_exp(-1000.0) > 0 and np.isfinite(L.hmo_exp(1000.0))
+
+
+# ---- independent numpy restatement of the linear learner (float32 ops via numpy scalars) ----
+
+F = np.float32
+
+
+def np_exp(x):
+    x = F(min(max(x, F(-87.0)), F(88.0)))
+    n = F(np.rint(F(x * F(1.44269504))))
+    r = F(x - F(n * F(0.693359375)))
+    r = F(r - F(n * F(-2.12194440e-4)))
+    p = F(1.3888889e-3)
+    for c in (8.3333333e-3, 4.1666667e-2, 1.6666667e-1, 0.5, 1.0, 1.0):
+        p = F(F(p * r) + F(c))
+    return F(p * F(2.0) ** int(n))
+
+
+def np_dloss(loss, m, y):
+    if loss == 0:
+        return F(F(-y) / F(F(1.0) + np_exp(F(y * m))))
+    if loss == 1:
+        return F(-y) if F(y * m) < F(1.0) else F(0.0)
+    return F(m - y)
+
+
+def np_train(cfg, rowptr, feat, val, label):
+    D, B = int(cfg.dims), int(cfg.mini_batch)
+    w = np.zeros(D, F); s1 = np.zeros(D, F); s2 = np.zeros(D, F)
+    n = len(label); t = 0
+    for _ in range(cfg.iters):
+        for b0 in range(0, n, B):
+            b1 = min(n, b0 + B)
+            dl = []
+            for i in range(b0, b1):
+                acc = 0.0
+                for p in range(rowptr[i], rowptr[i + 1]):
+                    acc += float(F(w[feat[p]] * val[p]))
+                y = (F(1.0) if label[i] > 0 else F(-1.0)) if cfg.task == 0 else F(label[i])
+                dl.append(np_dloss(cfg.loss, F(acc), y))
+            sums, cnts = {}, {}
+            for i in range(b0, b1):
+                for p in range(rowptr[i], rowptr[i + 1]):
+                    j = int(feat[p])
+                    sums[j] = sums.get(j, 0.0) + float(F(dl[i - b0] * val[p]))
+                    cnts[j] = cnts.get(j, 0) + 1
+            t += 1
+            eta = F(_oracle.lib().hmo_eta(cfg, t))
+            for j, sm in sums.items():
+                den = float(b1 - b0) if cfg.grad_norm == 0 else (float(cnts[j]) if cfg.grad_norm == 1 else 1.0)
+                g = F(sm / den)
+                wv = w[j]
+                if cfg.reg == 2 and cfg.opt != 4:
+                    g = F(g + F(F(cfg.lambda_) * wv))
+                if cfg.opt == 0:
+                    wv = F(wv - F(eta * g))
+                elif cfg.opt == 1:
+                    s1[j] = F(s1[j] + F(g * g))
+                    wv = F(wv - F(F(eta * g) / F(np.sqrt(s1[j]) + F(cfg.eps))))
+                elif cfg.opt == 4:
+                    n1 = F(s2[j] + F(g * g))
+                    sig = F(F(np.sqrt(n1) - np.sqrt(s2[j])) / F(cfg.alpha))
+                    z = F(F(s1[j] + g) - F(sig * wv))
+                    s1[j], s2[j] = z, n1
+                    if abs(z) <= F(cfg.lambda1):
+                        wv = F(0.0)
+                    else:
+                        sg = F(-1.0) if z < 0 else F(1.0)
+                        wv = F(-F(F(z - F(sg * F(cfg.lambda1))) /
+                                  F(F(F(F(cfg.beta) + np.sqrt(n1)) / F(cfg.alpha)) + F(cfg.lambda2))))
+                else:
+                    raise NotImplementedError
+                w[j] = wv
+    return w, s1, s2, t
+
+
+@pytest.mark.parametrize("options,fn", [
+    ("-loss logloss -opt sgd -mini_batch 7 -dims 50 -eta0 0.5", "train_classifier"),
+    ("-loss logloss -opt adagrad -mini_batch 16 -dims 50 -iters 2", "train_classifier"),
+    ("-loss hinge -opt adagrad -mini_batch 5 -dims 50 -grad_norm count", "train_classifier"),
+    ("-loss logloss -opt ftrl -mini_batch 11 -dims 50 -alpha 0.5 -lambda1 0.01 -lambda2 0.1", "train_classifier"),
+    ("-loss squared -opt adagrad -mini_batch 9 -dims 50 -reg l2 -lambda 0.1 -eta inverse", "train_regressor"),
+])
+def test_oracle_matches_numpy_restatement(options, fn):
+    data = synth.ragged(120, dims=50, max_nnz=9, seed=2, regression=(fn == "train_regressor"))
+    rp, f, v, y = data.numpy()
+    cfg = _oracle.config_from(hm.parse_options(fn, options))
+    res = _oracle.train_linear(cfg, rp, f, v, y)
+    w, s1, s2, t = np_train(cfg, rp, f, v, y)
+    assert res.t == t
+    assert np.array_equal(res.w, w), np.abs(res.w - w).max()
+    assert np.array_equal(res.s1, s1) and np.array_equal(res.s2, s2)
+
+
+@pytest.mark.parametrize("opt", ["sgd", "adagrad", "adadelta", "adam", "ftrl"])
+def test_openmp_variant_is_bit_identical(opt):
+    data = synth.criteo_like(3000, dims=1 << 14, seed=3)
+    rp, f, v, y = data.numpy()
+    cfg = _oracle.config_from(hm.parse_options("train_classifier", f"-opt {opt} -mini_batch 256 -dims {1 << 14} -iters 2"))
+    a = _oracle.train_linear(cfg, rp, f, v, y)
+    for threads in (1, 3, 4):
+        b = _oracle.train_linear_mt(cfg, rp, f, v, y, threads)
+        assert np.array_equal(a.w, b.w) and np.array_equal(a.s1, b.s1) and np.array_equal(a.s2, b.s2)
+        assert a.t == b.t
+
+
+def test_oracle_learns_and_model_table_is_sorted():
+    data = synth.a9a_like(4096, seed=0)
+    rp, f, v, y = data.numpy()
+    cfg = _oracle.config_from(hm.parse_options("train_classifier", "-opt adagrad -mini_batch 128 -dims 124"))
+    res = _oracle.train_linear(cfg, rp, f, v, y)
+    import torch
+    assert synth.auc(torch.from_numpy(_oracle.predict_linear(rp, f, v, res.w)), torch.from_numpy(y)) > 0.7
+    feat, wt = _oracle.model_table(res.w)
+    assert np.all(np.diff(feat) > 0) and np.all(wt != 0) and len(feat) == np.count_nonzero(res.w)
+
+
+def test_oracle_rejects_out_of_range_feature():
+    cfg = _oracle.config_from(hm.parse_options("train_classifier", "-dims 4 -mini_batch 2"))
+    with pytest.raises(RuntimeError):
+        _oracle.train_linear(cfg, np.array([0, 1]), np.array([4]), np.array([1.0]), np.array([1.0]))
+
+
+def test_fm_oracle_runs_and_learns():
+    data = synth.criteo_like(2000, dims=1 << 10, seed=5)
+    rp, f, v, y = data.numpy()
+    cfg = _oracle.config_from(hm.parse_options("train_fm", f"-factors 4 -classification -mini_batch 100 -dims {1 << 10} -iters 3 -opt adagrad -eta0 0.1"))
+    r = _oracle.train_fm(cfg, rp, f, v, y)
+    import torch
+    p = _oracle.predict_fm(cfg, rp, f, v, r.w0[0], r.w, r.V)
+    assert np.isfinite(p).all() and synth.auc(torch.from_numpy(p), torch.from_numpy(y)) > 0.6
+    assert r.touched.sum() == len(np.unique(f))
+
+
+def test_synth_is_deterministic_and_shaped():
+    a = synth.criteo_like(1000, dims=1 << 24, seed=1)
+    b = synth.criteo_like(500, dims=1 << 24, seed=1, row0=500)
+    assert a.nnz == 39000 and int(a.feature.max()) < (1 << 24) and int(a.feature.min()) >= 0
+    assert np.array_equal(a.feature.numpy()[500 * 39:], b.feature.numpy())      # streams are position-addressed
+    assert np.array_equal(a.label.numpy()[500:], b.label.numpy())
+    k = synth.a9a_like(100)
+    assert k.nnz == 1400 and int(k.feature.max()) < 123
