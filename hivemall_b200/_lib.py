@@ -83,6 +83,7 @@ SIGNATURES = {
     "hm_udtf_predict": (C.c_int, [_P, C.c_int64, _P, _P, _P, _P]),
     "hm_udtf_predict_device": (C.c_int, [_P, C.c_int64, _P, _P, _P, _P]),
     "hm_udtf_last_margins": (C.c_int, [_P, _P, C.c_int64, C.POINTER(C.c_int64)]),
+    "hm_model_table_noalloc": (C.c_int, [_P, C.c_int64, _P, _P, C.c_int64, _P, _P]),
     "hm_udtf_stats": (C.c_int, [_P, C.POINTER(HmStats)]),
     "hm_udtf_set_profiling": (C.c_int, [_P, C.c_int]),
     "hm_udtf_num_kernels": (C.c_int, [_P]),

@@ -12,6 +12,8 @@
 //                           the last CTA to finish also resolves segments that straddle CTAs
 //   predict / export / scale helpers
 #include "hm_internal.h"
+#include <algorithm>
+#include <mutex>
 
 namespace hm {
 
@@ -601,3 +603,101 @@ hm_status launch_fill_u32(Launcher &L, uint32_t *p, int64_t n, uint32_t v)
 }
 
 }  // namespace hm
+
+// =====================================================================================
+//  hm_model_table_noalloc -- model table with no device allocation
+// =====================================================================================
+//
+// hm_udtf_forward() sizes and allocates its compaction scratch (one counter per 4096
+// features) and its output staging with cudaMalloc.  Some hosts of this library must not do
+// that: an executor that was handed a fixed slice of a GPU shared with other tasks and has
+// already spent it on its own buffers, or a serving loop next to other tenants' streams, for
+// which the device-wide synchronisation hidden inside cudaMalloc / cudaFree is a stall it
+// cannot afford.  For them the counters live in the file-scope array below, which every GPU
+// that loads this library carries until the process exits (64 KiB), and the caller brings
+// the input and all outputs.
+//
+// The array's name is only a host-side handle in host code, so the device address is looked
+// up once per device with cudaGetSymbolAddress while that device is current (first call on
+// the device; make that call before starting any stream capture) and that address is what
+// the kernels receive.
+
+namespace {
+constexpr int64_t kNoAllocMaxDims = HM_MODEL_TABLE_NOALLOC_MAX_DIMS;
+constexpr int kNoAllocMaxTiles = (int)(kNoAllocMaxDims / hm::kExpTile);
+constexpr int kNoAllocMaxDevices = 64;
+}  // namespace
+
+static __device__ __align__(256) uint32_t hm_noalloc_tile_counts[kNoAllocMaxTiles + 64];
+
+namespace {
+
+std::mutex g_noalloc_mutex;
+uint32_t *g_noalloc_counts[kNoAllocMaxDevices] = {nullptr};
+
+// Same ordered compaction as export_write_kernel, but never writes past `cap` rows: the row
+// count is only known on the device, so the guard has to be here.
+__global__ void __launch_bounds__(hm::kExpThreads)
+export_write_capped_kernel(const float *__restrict__ w, int64_t dims, const uint32_t *__restrict__ offsets,
+                           int32_t *__restrict__ feature, float *__restrict__ weight, uint32_t cap)
+{
+    __shared__ uint32_t warp_tot[hm::kExpThreads / 32];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int per = hm::kExpTile / hm::kExpThreads;
+    const int64_t j0 = (int64_t)blockIdx.x * hm::kExpTile + (int64_t)threadIdx.x * per;
+    uint32_t flags = 0;
+    for (int i = 0; i < per; i++)
+        if (j0 + i < dims && w[j0 + i] != 0.0f) flags |= 1u << i;
+    const uint32_t c = __popc(flags);
+    uint32_t inc = c;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { uint32_t v = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += v; }
+    if (lane == 31) warp_tot[warp] = inc;
+    __syncthreads();
+    uint32_t pos = offsets[blockIdx.x] + inc - c;
+    for (int w2 = 0; w2 < warp; w2++) pos += warp_tot[w2];
+    for (int i = 0; i < per; i++)
+        if (flags & (1u << i)) {
+            if (pos < cap) { feature[pos] = (int32_t)(j0 + i); weight[pos] = w[j0 + i]; }
+            pos++;
+        }
+}
+
+}  // namespace
+
+extern "C" hm_status hm_model_table_noalloc(const float *d_w, int64_t dims, int32_t *d_feature, float *d_weight,
+                                            int64_t cap, int64_t *d_n_rows, void *stream)
+{
+    using namespace hm;
+    if (!d_w || !d_n_rows || cap < 0 || (cap > 0 && (!d_feature || !d_weight)))
+        HM_FAIL(HM_ERR_INVALID_ARGUMENT, "hm_model_table_noalloc: NULL buffer or negative capacity");
+    if (dims < 1 || dims > kNoAllocMaxDims)
+        HM_FAIL(HM_ERR_INVALID_ARGUMENT,
+                "hm_model_table_noalloc: dims = %lld is outside [1, %lld]; the built-in scratch is sized for at most "
+                "%lld features (use hm_udtf_forward, which allocates, for larger models)",
+                (long long)dims, (long long)kNoAllocMaxDims, (long long)kNoAllocMaxDims);
+    int dev = -1;
+    HM_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= kNoAllocMaxDevices) HM_FAIL(HM_ERR_UNSUPPORTED, "hm_model_table_noalloc: device ordinal %d", dev);
+    uint32_t *counts = nullptr;
+    {
+        // once per device, with that device current: the symbol's address on THIS device
+        std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+        if (!g_noalloc_counts[dev]) {
+            void *p = nullptr;
+            HM_CUDA(cudaGetSymbolAddress(&p, hm_noalloc_tile_counts));
+            g_noalloc_counts[dev] = static_cast<uint32_t *>(p);
+        }
+        counts = g_noalloc_counts[dev];
+    }
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    const int tiles = (int)((dims + kExpTile - 1) / kExpTile);
+    const uint32_t cap32 = (uint32_t)std::min<int64_t>(cap, 0xffffffffLL);
+    // counts[0 .. tiles) are all rewritten by the first kernel before anything reads them, and
+    // *d_n_rows is written by the second: nothing left over from an earlier call is ever read.
+    export_count_kernel<<<tiles, kExpThreads, 0, st>>>(d_w, nullptr, dims, counts);
+    export_scan_kernel<<<1, 1024, 0, st>>>(counts, tiles, d_n_rows);
+    export_write_capped_kernel<<<tiles, kExpThreads, 0, st>>>(d_w, dims, counts, d_feature, d_weight, cap32);
+    HM_CUDA(cudaGetLastError());
+    return HM_OK;
+}

@@ -85,6 +85,19 @@ def host_free(address: int) -> None:
     check(_lib.load().hm_host_free(C.c_void_p(address)))
 
 
+NOALLOC_MAX_DIMS = 1 << 26
+
+
+def model_table_noalloc(d_w, dims: int, d_feature, d_weight, cap: int, d_n_rows, stream: int = 0) -> None:
+    """Model table of a dense device weight array without any device allocation inside the
+    library (for callers that must not call cudaMalloc: see hm_model_table_noalloc in the
+    header).  Every argument is device memory the caller owns (torch CUDA tensors or raw
+    addresses); the row count lands in d_n_rows[0] on the device.  Asynchronous on `stream`
+    of the current device.  dims is limited to NOALLOC_MAX_DIMS; calls must not overlap."""
+    check(_lib.load().hm_model_table_noalloc(_ptr(d_w), dims, _ptr(d_feature), _ptr(d_weight), cap,
+                                             _ptr(d_n_rows), C.c_void_p(stream)))
+
+
 class _DeviceArray:
     """Zero-copy view of a replica array for consumers of __cuda_array_interface__
     (torch.as_tensor, cupy.asarray)."""

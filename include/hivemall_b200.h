@@ -194,6 +194,36 @@ hm_status hm_udtf_predict_device(hm_udtf *u, int64_t n_rows, const int64_t *d_ro
  * into a loss.  Copies min(cap, rows) floats to `host`, waits for the GPU, sets *n. */
 hm_status hm_udtf_last_margins(hm_udtf *u, float *host, int64_t cap, int64_t *n);
 
+/* ---- model table without device allocation ---------------------------------- */
+
+/* Largest model hm_model_table_noalloc accepts (its built-in scratch is 64 KiB per GPU). */
+#define HM_MODEL_TABLE_NOALLOC_MAX_DIMS (1 << 26)
+
+/* Has no counterpart in the reference: it exists for hosts of this library that may not
+ * allocate device memory at the moment they need the model table -- a task that was given a
+ * fixed share of a GPU it shares with other tasks, or a loop running beside other work on
+ * the GPU that cannot absorb the device-wide stall cudaMalloc / cudaFree bring with them.
+ * (hm_udtf_forward allocates its scratch and staging buffers.)
+ *
+ * Writes the model table of the dense weight array d_w[dims] (device memory, e.g. the "w"
+ * pointer from hm_udtf_array after hm_udtf_sync): (feature, weight) for every weight != 0,
+ * ascending feature order, into the caller's device arrays d_feature / d_weight of `cap`
+ * rows, and the row count into *d_n_rows (device memory).  If *d_n_rows > cap only the
+ * first `cap` rows were written.  All work is queued on `stream` (a cudaStream_t) of the
+ * CURRENT device; nothing is copied to the host and the call does not wait.
+ *
+ * It calls no cudaMalloc / cudaFree and no library routine that allocates.  Its scratch is
+ * one array compiled into the library (every GPU that loads the library holds those 64 KiB
+ * until the process exits), hence the limit: dims > HM_MODEL_TABLE_NOALLOC_MAX_DIMS is
+ * rejected with HM_ERR_INVALID_ARGUMENT.  The first call on each device looks up that
+ * array's device address; make that first call before any stream capture begins.  The
+ * array is shared by every call on the device and keeps whatever the last call left in
+ * it; each call overwrites the part it reads before reading it, so nothing needs clearing,
+ * but two calls that overlap on the GPU (different streams, or different threads) race on
+ * it and produce garbage -- serialise them. */
+hm_status hm_model_table_noalloc(const float *d_w, int64_t dims, int32_t *d_feature, float *d_weight,
+                                 int64_t cap, int64_t *d_n_rows, void *stream);
+
 /* ---- measurement ----------------------------------------------------------- */
 
 hm_status hm_udtf_stats(const hm_udtf *u, hm_stats *out);
