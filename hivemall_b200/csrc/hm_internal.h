@@ -52,8 +52,9 @@ constexpr int kMaxSegs = 256;          // mini-batches sorted per launch
 constexpr int kSortTile = 4096;        // elements per sort tile
 struct SortScratch {
     // device
-    uint32_t *key[2] = {nullptr, nullptr};
-    uint32_t *pay[2] = {nullptr, nullptr};
+    uint32_t *key[2] = {nullptr, nullptr};   // feature ids, ping-pong
+    uint2 *pay[2] = {nullptr, nullptr};      // (row inside the mini-batch, value bits), ping-pong
+    uint32_t *erow = nullptr;                // row id of every element of the block (input of pass 1)
     uint32_t *tile_hist = nullptr;     // [seg][digit][tile_in_seg]
     uint32_t *row_sum = nullptr;       // [seg*256 + digit] (+1)
     uint32_t *seg_off = nullptr;       // [kMaxSegs+1] element offset of each mini-batch in the block
@@ -65,11 +66,11 @@ hm_status sort_scratch_reserve(SortScratch &s, int64_t elems);
 void sort_scratch_free(SortScratch &s);
 // Fill seg_off / seg_tile_off for rows [row0, row0+n_rows) split every `mini_batch` rows.
 hm_status launch_seg_prep(Launcher &L, SortScratch &s, const int64_t *d_rowptr, int64_t row0,
-                          int64_t n_rows, int32_t mini_batch, int n_segs);
-// Stable sort of each segment by the low `key_bits` bits of d_feature[base + e].
-// Result: s.key[*out_buf], s.pay[*out_buf] hold (feature, e) sorted per segment.
+                          int64_t n_rows, int64_t n_elems, int32_t mini_batch, int n_segs);
+// Stable sort of each segment by the low `key_bits` bits of the feature id.
+// Result: s.key[*out_buf], s.pay[*out_buf] hold (feature, (row, value)) sorted per segment.
 hm_status launch_segmented_sort(Launcher &L, SortScratch &s, const uint32_t *d_feature_block,
-                                int64_t n_elems, int n_segs, int key_bits, int *out_buf);
+                                const float *d_value_block, int64_t n_elems, int n_segs, int key_bits, int *out_buf);
 
 // ---- hashing (hm_hash.cu) -----------------------------------------------------
 hm_status launch_mhash(Launcher &L, const uint8_t *d_bytes, const int64_t *d_offsets, int64_t n,
@@ -90,11 +91,11 @@ struct LinearArgs {
     float *state;         // state_width floats per feature, interleaved
     int state_width;
 };
-// margins/dloss for rows [row0, row0+n) of the chunk; also writes contrib[e] = dloss*x
+// margin (per block row) and dloss (per mini-batch row) for rows [row0, row0+n) of the chunk
 hm_status launch_linear_forward(Launcher &L, const LinearArgs &a, const int64_t *d_rowptr, int64_t row0,
                                 int32_t n_rows, int64_t block_row0, const uint32_t *d_feature,
                                 const float *d_value, const float *d_label, float *d_margin,
-                                float *d_dloss, float *d_contrib, uint32_t *d_bad, int64_t nnz_hint);
+                                float *d_dloss, uint32_t *d_bad, int64_t nnz_hint);
 // reduce-by-feature over the sorted segment `seg` and apply the optimizer
 struct UpdateScratch {
     void *boundary = nullptr;     // per-CTA open-segment summaries
@@ -104,8 +105,8 @@ struct UpdateScratch {
 hm_status update_scratch_reserve(UpdateScratch &u);
 void update_scratch_free(UpdateScratch &u);
 hm_status launch_linear_update(Launcher &L, const LinearArgs &a, const StepScalars &sc, UpdateScratch &us,
-                               const uint32_t *d_sorted_key, const uint32_t *d_sorted_pay,
-                               const uint32_t *d_seg_off, int seg, const float *d_contrib, int64_t nnz_hint);
+                               const uint32_t *d_sorted_key, const uint2 *d_sorted_pay,
+                               const uint32_t *d_seg_off, int seg, const float *d_dloss, int64_t nnz_hint);
 hm_status launch_predict_linear(Launcher &L, const float *w, int64_t dims, int64_t n_rows, const int64_t *d_rowptr,
                                 const uint32_t *d_feature, const float *d_value, float *d_out, uint32_t *d_bad);
 // model table: features with w != 0, ascending

@@ -235,11 +235,11 @@ hm_status train_rows(hm_udtf *u, const Chunk &c, int64_t row0, int64_t n_rows, c
             HM_FAIL(HM_ERR_UNSUPPORTED, "a mini-batch of %lld elements exceeds the 2^31 block limit", (long long)b_nnz);
         HM_TRY(sort_scratch_reserve(u->sort, b_nnz));
         HM_TRY(u->margin.reserve((size_t)b_rows * sizeof(float)));
-        HM_TRY(u->dloss.reserve((size_t)b_rows * sizeof(float)));
-        HM_TRY(u->contrib.reserve((size_t)std::max<int64_t>(b_nnz, 1) * sizeof(float)));
-        HM_TRY(launch_seg_prep(u->L, u->sort, c.rp(), b_row0, b_rows, B, n_segs));
+        HM_TRY(u->dloss.reserve((size_t)std::min<int64_t>(b_rows, B) * sizeof(float)));
+        HM_TRY(launch_seg_prep(u->L, u->sort, c.rp(), b_row0, b_rows, b_nnz, B, n_segs));
         int buf = 0;
-        HM_TRY(launch_segmented_sort(u->L, u->sort, c.ft() + mb_abs[m0], b_nnz, n_segs, key_bits, &buf));
+        HM_TRY(launch_segmented_sort(u->L, u->sort, c.ft() + mb_abs[m0], c.vl() + mb_abs[m0], b_nnz, n_segs, key_bits,
+                                     &buf));
         for (int s = 0; s < n_segs; s++) {
             const int64_t mrow0 = b_row0 + (int64_t)s * B;
             const int32_t mrows = (int32_t)std::min<int64_t>(B, row0 + n_rows - mrow0);
@@ -251,10 +251,9 @@ hm_status train_rows(hm_udtf *u, const Chunk &c, int64_t row0, int64_t n_rows, c
             sc.inv_denom_unused = 0;
             sc.n_rows = mrows;
             HM_TRY(launch_linear_forward(u->L, a, c.rp(), mrow0, mrows, b_row0, c.ft(), c.vl(), c.lb(),
-                                         u->margin.as<float>(), u->dloss.as<float>(), u->contrib.as<float>(),
-                                         u->d_bad, mnnz));
+                                         u->margin.as<float>(), u->dloss.as<float>(), u->d_bad, mnnz));
             HM_TRY(launch_linear_update(u->L, a, sc, u->upd, u->sort.key[buf], u->sort.pay[buf], u->sort.seg_off, s,
-                                        u->contrib.as<float>(), mnnz));
+                                        u->dloss.as<float>(), mnnz));
             u->stats.mini_batches++;
             u->last_margin_off = mrow0 - b_row0;
             u->last_margin_n = mrows;

@@ -6,10 +6,11 @@
 // (README.md:20-22); the arithmetic contract is DESIGN.md section 3 and the CPU oracle
 // (oracle/hm_oracle.c) restates the same contract independently.
 //
-//   linear_forward_kernel   warp per row: gather w, margin in fp64, dloss, contrib = dloss*x
-//   linear_update_kernel    reduce-by-feature over the feature-sorted mini-batch (fp64 sums,
-//                           fixed order, no float atomics) fused with the optimizer update;
-//                           the last CTA to finish also resolves segments that straddle CTAs
+//   linear_forward_kernel   warp per row: gather w, margin in fp64, dloss[row]
+//   linear_update_kernel    streams the feature-sorted mini-batch (feature, row, value), forms
+//                           dloss[row]*value, reduce-by-feature in fp64 in a fixed order (no float
+//                           atomics) fused with the optimizer update; only segments that really
+//                           straddle two CTAs are left to the last CTA to finish
 //   predict / export / scale helpers
 #include "hm_internal.h"
 #include <algorithm>
@@ -64,14 +65,13 @@ struct FwdParams {
     const uint32_t *feature;
     const float *value;
     const float *label;
-    float *margin;           // indexed by row of the BLOCK
-    float *dloss;            // idem
-    float *contrib;          // indexed by element of the BLOCK
+    float *margin;           // indexed by row of the BLOCK (kept for hm_udtf_last_margins)
+    float *dloss;            // indexed by row of the MINI-BATCH (table read by the update kernel)
     int64_t block_row0;      // first row of the block in the chunk
     int64_t row0;            // first row of this mini-batch in the chunk
     int32_t n_rows;
     int32_t task, loss;
-    int32_t write_contrib;
+    int32_t train;           // 0: prediction only
     uint32_t dims;
     uint32_t *bad;           // set to 1 when a feature index >= dims is met (that element scores 0)
 };
@@ -80,46 +80,47 @@ __global__ void __launch_bounds__(kFwdThreads) linear_forward_kernel(FwdParams P
 {
     const int lane = threadIdx.x & 31;
     const int warps_per_cta = kFwdThreads / 32;
-    const int64_t block_base = P.rowptr[P.block_row0];
     for (int r = blockIdx.x * warps_per_cta + (threadIdx.x >> 5); r < P.n_rows; r += gridDim.x * warps_per_cta) {
         const int64_t row = P.row0 + r;
         const int64_t p0 = P.rowptr[row], p1 = P.rowptr[row + 1];
         double acc = 0.0;
         for (int64_t p = p0 + lane; p < p1; p += 32) {
-            const uint32_t f = P.feature[p];
-            if (f < P.dims) acc += (double)__fmul_rn(__ldg(P.w + f), P.value[p]);
+            const uint32_t f = __ldcs(P.feature + p);
+            const float x = __ldcs(P.value + p);
+            if (f < P.dims) acc += (double)__fmul_rn(__ldg(P.w + f), x);
             else atomicOr(P.bad, 1u);
         }
         acc = warp_sum(acc);
         const float m = (float)acc;
-        if (P.write_contrib) {
-            const float lab = P.label[row];
-            const float y = P.task == HM_TASK_CLASSIFIER ? (lab > 0.0f ? 1.0f : -1.0f) : lab;
-            const float dl = dloss_of(P.loss, m, y);
-            if (lane == 0) { P.margin[row - P.block_row0] = m; P.dloss[row - P.block_row0] = dl; }
-            for (int64_t p = p0 + lane; p < p1; p += 32)
-                P.contrib[p - block_base] = __fmul_rn(dl, P.value[p]);
-        } else if (lane == 0) {
+        if (lane == 0) {
             P.margin[row - P.block_row0] = m;
+            if (P.train) {
+                const float lab = P.label[row];
+                const float y = P.task == HM_TASK_CLASSIFIER ? (lab > 0.0f ? 1.0f : -1.0f) : lab;
+                P.dloss[r] = dloss_of(P.loss, m, y);
+            }
         }
     }
 }
 
 // ---- update ------------------------------------------------------------------------
 
-struct SegRec {           // a (feature, partial sum) record; valid == 0 means empty
+struct SegRec {           // a (feature, partial sum) record; cnt == 0 means empty
     double sum;
-    uint32_t key, cnt, valid, pad;
+    uint32_t key, cnt;
 };
 struct Boundary { SegRec first, last; };
+
+constexpr int kUpdMaxGrid = 2048;     // CTAs per launch; beyond that each CTA walks consecutive tiles
+constexpr int kUpdMergeChunk = 1536;  // boundary records merged per shared-memory chunk
 
 struct UpdParams {
     float *w;
     float *state;
     uint8_t *touched;        // nullable
     const uint32_t *skey;    // sorted features of the block
-    const uint32_t *spay;    // sorted element positions (relative to block)
-    const float *contrib;
+    const uint2 *spay;       // sorted (row in mini-batch, value bits)
+    const float *dloss;      // dloss of every row of this mini-batch
     const uint32_t *seg_off;
     Boundary *boundary;
     uint32_t *done_counter;
@@ -127,53 +128,74 @@ struct UpdParams {
     uint32_t dims;
     int32_t opt, reg, grad_norm, state_width;
     float eta, adam_alpha, lambda, eps, rho, beta1, beta2, alpha, beta, lambda1, lambda2;
-    double n_rows;
+    double inv_rows;         // 1 / rows of the mini-batch, computed on the host in fp64
+    int32_t n_active;        // CTAs launched (all own at least one tile unless the segment is empty)
 };
 
-// One coordinate: DESIGN.md 3.4-3.6.
-__device__ __forceinline__ void apply_update(const UpdParams &P, uint32_t j, double sum, uint32_t cnt)
+// Replica record of one feature while it is being updated.
+struct Rec { float w, s1, s2; };
+
+__device__ __forceinline__ Rec load_rec(const UpdParams &P, uint32_t j)
 {
-    if (j >= P.dims) return;  // flagged by the forward kernel; never touch memory outside the replica
-    const double denom = P.grad_norm == HM_NORM_BATCH ? P.n_rows : (P.grad_norm == HM_NORM_COUNT ? (double)cnt : 1.0);
-    float g = (float)(sum / denom);
-    float wv = P.w[j];
-    float *st = P.state + (size_t)j * P.state_width;
+    Rec r; r.w = P.w[j]; r.s1 = 0.f; r.s2 = 0.f;
+    if (P.state_width == 1) r.s1 = P.state[j];
+    else if (P.state_width == 2) { const float2 s = reinterpret_cast<const float2 *>(P.state)[j]; r.s1 = s.x; r.s2 = s.y; }
+    return r;
+}
+
+__device__ __forceinline__ void store_rec(const UpdParams &P, uint32_t j, const Rec &r)
+{
+    P.w[j] = r.w;
+    if (P.state_width == 1) P.state[j] = r.s1;
+    else if (P.state_width == 2) reinterpret_cast<float2 *>(P.state)[j] = make_float2(r.s1, r.s2);
+    if (P.touched) P.touched[j] = 1;
+}
+
+// mean gradient of one feature from its fp64 sum: DESIGN.md 3.4
+__device__ __forceinline__ float grad_of(const UpdParams &P, double sum, uint32_t cnt)
+{
+    if (P.grad_norm == HM_NORM_BATCH) return (float)(sum * P.inv_rows);
+    if (P.grad_norm == HM_NORM_COUNT) return (float)(sum / (double)cnt);
+    return (float)sum;
+}
+
+// One coordinate step: DESIGN.md 3.5-3.6 (every fp32 operation rounded on its own).
+__device__ __forceinline__ void step_rec(const UpdParams &P, Rec &r, float g)
+{
+    float wv = r.w;
     if (P.reg == HM_REG_L2 && P.opt != HM_OPT_FTRL) g = __fadd_rn(g, __fmul_rn(P.lambda, wv));
     switch (P.opt) {
     case HM_OPT_SGD:
         wv = __fsub_rn(wv, __fmul_rn(P.eta, g));
         break;
     case HM_OPT_ADAGRAD: {
-        const float G = __fadd_rn(st[0], __fmul_rn(g, g));
-        st[0] = G;
+        const float G = __fadd_rn(r.s1, __fmul_rn(g, g));
+        r.s1 = G;
         wv = __fsub_rn(wv, __fdiv_rn(__fmul_rn(P.eta, g), __fadd_rn(__fsqrt_rn(G), P.eps)));
         break;
     }
     case HM_OPT_ADADELTA: {
-        const float2 s = *reinterpret_cast<float2 *>(st);
         const float omr = __fsub_rn(1.0f, P.rho);
-        const float E = __fadd_rn(__fmul_rn(P.rho, s.x), __fmul_rn(__fmul_rn(omr, g), g));
-        const float dx = __fmul_rn(__fdiv_rn(__fsqrt_rn(__fadd_rn(s.y, P.eps)), __fsqrt_rn(__fadd_rn(E, P.eps))), g);
-        const float D = __fadd_rn(__fmul_rn(P.rho, s.y), __fmul_rn(__fmul_rn(omr, dx), dx));
-        *reinterpret_cast<float2 *>(st) = make_float2(E, D);
+        const float E = __fadd_rn(__fmul_rn(P.rho, r.s1), __fmul_rn(__fmul_rn(omr, g), g));
+        const float dx = __fmul_rn(__fdiv_rn(__fsqrt_rn(__fadd_rn(r.s2, P.eps)), __fsqrt_rn(__fadd_rn(E, P.eps))), g);
+        r.s2 = __fadd_rn(__fmul_rn(P.rho, r.s2), __fmul_rn(__fmul_rn(omr, dx), dx));
+        r.s1 = E;
         wv = __fsub_rn(wv, dx);
         break;
     }
     case HM_OPT_ADAM: {
-        const float2 s = *reinterpret_cast<float2 *>(st);
-        const float m = __fadd_rn(__fmul_rn(P.beta1, s.x), __fmul_rn(__fsub_rn(1.0f, P.beta1), g));
-        const float v = __fadd_rn(__fmul_rn(P.beta2, s.y), __fmul_rn(__fmul_rn(__fsub_rn(1.0f, P.beta2), g), g));
-        *reinterpret_cast<float2 *>(st) = make_float2(m, v);
+        const float m = __fadd_rn(__fmul_rn(P.beta1, r.s1), __fmul_rn(__fsub_rn(1.0f, P.beta1), g));
+        const float v = __fadd_rn(__fmul_rn(P.beta2, r.s2), __fmul_rn(__fmul_rn(__fsub_rn(1.0f, P.beta2), g), g));
+        r.s1 = m; r.s2 = v;
         wv = __fsub_rn(wv, __fdiv_rn(__fmul_rn(P.adam_alpha, m), __fadd_rn(__fsqrt_rn(v), P.eps)));
         break;
     }
-    case HM_OPT_FTRL: {
-        const float2 s = *reinterpret_cast<float2 *>(st);  // (z, n)
-        const float n1 = __fadd_rn(s.y, __fmul_rn(g, g));
+    case HM_OPT_FTRL: {   // (s1, s2) = (z, n)
+        const float n1 = __fadd_rn(r.s2, __fmul_rn(g, g));
         const float sq1 = __fsqrt_rn(n1);
-        const float sigma = __fdiv_rn(__fsub_rn(sq1, __fsqrt_rn(s.y)), P.alpha);
-        const float z = __fsub_rn(__fadd_rn(s.x, g), __fmul_rn(sigma, wv));
-        *reinterpret_cast<float2 *>(st) = make_float2(z, n1);
+        const float sigma = __fdiv_rn(__fsub_rn(sq1, __fsqrt_rn(r.s2)), P.alpha);
+        const float z = __fsub_rn(__fadd_rn(r.s1, g), __fmul_rn(sigma, wv));
+        r.s1 = z; r.s2 = n1;
         if (fabsf(z) <= P.lambda1) wv = 0.0f;
         else {
             const float sgn = z < 0.0f ? -1.0f : 1.0f;
@@ -188,32 +210,71 @@ __device__ __forceinline__ void apply_update(const UpdParams &P, uint32_t j, dou
         const float a = __fsub_rn(fabsf(wv), __fmul_rn(P.eta, P.lambda));
         wv = a > 0.0f ? copysignf(a, wv) : 0.0f;
     }
-    P.w[j] = wv;
-    if (P.touched) P.touched[j] = 1;
+    r.w = wv;
 }
 
 __device__ __forceinline__ int pad_idx(int q) { return q + (q >> 5); }
 
 // Segmented-scan element: f = "a segment head lies in the span", (v, c) = sum / count of the
-// span's trailing run.  combine(a, b) for a before b.
-struct Scan { double v; uint32_t c; uint32_t f; };
+// span's trailing run, k = number of segments closed in the span (plain sum).
+struct Scan { double v; uint32_t c; uint32_t f; uint32_t k; };
 __device__ __forceinline__ Scan combine(const Scan &a, const Scan &b)
 {
     Scan r;
     r.f = a.f | b.f;
     r.v = b.f ? b.v : a.v + b.v;
     r.c = b.f ? b.c : a.c + b.c;
+    r.k = a.k + b.k;
     return r;
 }
 
-__global__ void __launch_bounds__(kUpdThreads) linear_update_kernel(UpdParams P)
+constexpr int kUpdPadded = kUpdTile + kUpdTile / 32 + 2;
+constexpr int kUpdList = kUpdTile + 8;
+constexpr int kUpdBatch = 4;         // independent record updates in flight per thread
+// shared memory is used twice: tile + closed-segment list while streaming, record buffers in the merge
+constexpr size_t kUpdSmemTile = (size_t)kUpdPadded * 8 + (size_t)kUpdList * 8;
+constexpr size_t kUpdSmemMerge = (size_t)kUpdMergeChunk * 24;
+constexpr size_t kUpdSmem = kUpdSmemTile > kUpdSmemMerge ? kUpdSmemTile : kUpdSmemMerge;
+
+// Apply the optimizer to list entries [0, n): kUpdBatch independent read-modify-writes per thread
+// are issued together so that their DRAM latencies overlap.  Entries are distinct features;
+// 0xffffffff marks a slot to skip.
+__device__ __forceinline__ void apply_list(const UpdParams &P, const uint32_t *l_key, const float *l_g, int n, int tid)
 {
-    __shared__ uint32_t s_key[kUpdTile + kUpdTile / 32 + 2];
-    __shared__ float s_val[kUpdTile + kUpdTile / 32 + 2];
+    for (int i0 = 0; i0 < n; i0 += kUpdThreads * kUpdBatch) {
+        uint32_t j[kUpdBatch]; float g[kUpdBatch]; Rec r[kUpdBatch]; bool ok[kUpdBatch];
+#pragma unroll
+        for (int u = 0; u < kUpdBatch; u++) {
+            const int i = i0 + u * kUpdThreads + tid;
+            ok[u] = i < n;
+            j[u] = ok[u] ? l_key[i] : 0u;
+            g[u] = ok[u] ? l_g[i] : 0.f;
+            ok[u] = ok[u] && j[u] < P.dims;
+        }
+#pragma unroll
+        for (int u = 0; u < kUpdBatch; u++) if (ok[u]) r[u] = load_rec(P, j[u]);
+#pragma unroll
+        for (int u = 0; u < kUpdBatch; u++) if (ok[u]) step_rec(P, r[u], g[u]);
+#pragma unroll
+        for (int u = 0; u < kUpdBatch; u++) if (ok[u]) store_rec(P, j[u], r[u]);
+    }
+}
+
+__global__ void __launch_bounds__(kUpdThreads, 3) linear_update_kernel(UpdParams P)
+{
+    __shared__ __align__(16) unsigned char smem_raw[kUpdSmem];
+    uint32_t *s_key = reinterpret_cast<uint32_t *>(smem_raw);
+    float *s_val = reinterpret_cast<float *>(smem_raw + (size_t)kUpdPadded * 4);
+    uint32_t *l_key = reinterpret_cast<uint32_t *>(smem_raw + (size_t)kUpdPadded * 8);
+    float *l_g = reinterpret_cast<float *>(smem_raw + (size_t)kUpdPadded * 8 + (size_t)kUpdList * 4);
     __shared__ Scan s_warp[kUpdThreads / 32];
     __shared__ SegRec s_carry;       // open trailing segment of the previous tile
+    __shared__ SegRec s_first;
+    __shared__ SegRec s_mcarry;
     __shared__ uint32_t s_carry_open;
     __shared__ uint32_t s_is_last;
+    __shared__ uint32_t s_edge[2];   // does the CTA's range start / end on a true segment boundary?
+    __shared__ int s_nlist;
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint32_t s0 = P.seg_off[P.seg], s1 = P.seg_off[P.seg + 1];
@@ -224,53 +285,71 @@ __global__ void __launch_bounds__(kUpdThreads) linear_update_kernel(UpdParams P)
     const uint32_t lo = min(n, blockIdx.x * tiles_per_cta * kUpdTile);
     const uint32_t hi = min(n, lo + tiles_per_cta * kUpdTile);
 
-    Boundary out;
-    out.first.valid = 0; out.first.sum = 0; out.first.key = 0; out.first.cnt = 0; out.first.pad = 0;
-    out.last = out.first;
-    if (tid == 0) { s_carry.valid = 0; s_carry_open = 0; }
+    SegRec first;                    // this thread's candidate for the CTA's left-open segment
+    first.cnt = 0; first.sum = 0; first.key = 0;
+    if (tid == 0) {
+        s_carry.cnt = 0; s_carry_open = 0; s_first.cnt = 0;
+        // Peek at the neighbours of the range: a first segment that really starts at `lo`, or a last
+        // segment that really ends at `hi`, is complete inside this CTA and never reaches the merge.
+        s_edge[0] = (lo < hi) && (lo == 0 || __ldg(P.skey + s0 + lo - 1) != __ldg(P.skey + s0 + lo));
+        s_edge[1] = (lo < hi) && (hi == n || __ldg(P.skey + s0 + hi) != __ldg(P.skey + s0 + hi - 1));
+    }
     __syncthreads();
+    const bool left_closed = s_edge[0] != 0, right_closed = s_edge[1] != 0;
 
     for (uint32_t t0 = lo; t0 < hi; t0 += kUpdTile) {
         const int n_tile = (int)min((uint32_t)kUpdTile, hi - t0);
-        // ---- coalesced striped load + gather of contributions
-        uint32_t k[kUpdItems], e[kUpdItems];
+        // ---- coalesced striped load; contribution = dloss[row] * value (fp32 product)
+        uint32_t k[kUpdItems]; uint2 pv[kUpdItems];
 #pragma unroll
         for (int i = 0; i < kUpdItems; i++) {
             const int q = i * kUpdThreads + tid;
-            k[i] = q < n_tile ? __ldg(P.skey + s0 + t0 + q) : 0u;
-            e[i] = q < n_tile ? __ldg(P.spay + s0 + t0 + q) : 0u;
+            if (q < n_tile) { k[i] = __ldcs(P.skey + s0 + t0 + q); pv[i] = __ldcs(P.spay + s0 + t0 + q); }
         }
 #pragma unroll
         for (int i = 0; i < kUpdItems; i++) {
             const int q = i * kUpdThreads + tid;
-            if (q < n_tile) { s_key[pad_idx(q)] = k[i]; s_val[pad_idx(q)] = __ldg(P.contrib + e[i]); }
+            if (q < n_tile) {
+                s_key[pad_idx(q)] = k[i];
+                s_val[pad_idx(q)] = __fmul_rn(__ldg(P.dloss + pv[i].x), __uint_as_float(pv[i].y));
+            }
         }
         __syncthreads();
         const SegRec carry = s_carry;
         const uint32_t carry_open = s_carry_open;
         const bool first_tile = t0 == lo;
+        const bool last_tile = t0 + kUpdTile >= hi;
         const uint32_t key0 = s_key[pad_idx(0)];
-        const bool edge_continues = carry.valid && carry.key == key0;
-        // does a segment touching this tile's left edge also touch the CTA's left edge?
-        const bool edge_open = first_tile ? true : (edge_continues && carry_open != 0);
+        const bool edge_continues = carry.cnt != 0 && carry.key == key0;
+        // does a segment touching this tile's left edge reach past the CTA's left edge?
+        const bool edge_open = first_tile ? !left_closed : (edge_continues && carry_open != 0);
+        // the carried segment ended exactly at the tile edge and is complete: thread 0 lists it
+        const bool retire_carry = carry.cnt != 0 && !edge_continues && !carry_open;
+        // the tile's last item closes its segment when the CTA's range ends on a true boundary
+        const bool close_tail = last_tile && right_closed;
         __syncthreads();  // everyone has read the carry before it is overwritten below
 
         // ---- pass 1: thread summaries (items [8*tid, 8*tid+8)).  A "head" is an item at tile
         // position >= 1 whose feature differs from its predecessor; position 0 is never a head:
         // it either continues the carried segment or starts afresh with an empty running sum.
+        // An item "closes" its segment when the next item has another feature.
         const int q0 = tid * kUpdItems;
-        Scan mine; mine.v = 0.0; mine.c = 0; mine.f = 0;
+        Scan mine; mine.v = 0.0; mine.c = 0; mine.f = 0; mine.k = (tid == 0 && retire_carry) ? 1u : 0u;
         if (tid == 0 && edge_continues) { mine.v = carry.sum; mine.c = carry.cnt; }
-        uint32_t kk[kUpdItems]; float vv[kUpdItems];
+        uint32_t kk[kUpdItems + 1]; float vv[kUpdItems];
         const uint32_t prev_key = (q0 > 0 && q0 < n_tile) ? s_key[pad_idx(q0 - 1)] : 0u;
+#pragma unroll
+        for (int i = 0; i <= kUpdItems; i++) kk[i] = q0 + i < n_tile ? s_key[pad_idx(q0 + i)] : 0u;
 #pragma unroll
         for (int i = 0; i < kUpdItems; i++) {
             const int q = q0 + i;
             if (q < n_tile) {
-                kk[i] = s_key[pad_idx(q)]; vv[i] = s_val[pad_idx(q)];
+                vv[i] = s_val[pad_idx(q)];
                 const bool head = q > 0 && kk[i] != (i == 0 ? prev_key : kk[i - 1]);
                 if (head) { mine.v = 0.0; mine.c = 0; mine.f = 1; }
                 mine.v += (double)vv[i]; mine.c += 1;
+                const bool closes = q < n_tile - 1 ? kk[i + 1] != kk[i] : close_tail;
+                if (closes) mine.k += 1;
             }
         }
         // ---- exclusive segmented scan of the summaries over the CTA
@@ -281,6 +360,7 @@ __global__ void __launch_bounds__(kUpdThreads) linear_update_kernel(UpdParams P)
             up.v = __shfl_up_sync(0xffffffffu, inc.v, o);
             up.c = __shfl_up_sync(0xffffffffu, inc.c, o);
             up.f = __shfl_up_sync(0xffffffffu, inc.f, o);
+            up.k = __shfl_up_sync(0xffffffffu, inc.k, o);
             if (lane >= o) inc = combine(up, inc);
         }
         if (lane == 31) s_warp[warp] = inc;
@@ -288,18 +368,21 @@ __global__ void __launch_bounds__(kUpdThreads) linear_update_kernel(UpdParams P)
         ex.v = __shfl_up_sync(0xffffffffu, inc.v, 1);
         ex.c = __shfl_up_sync(0xffffffffu, inc.c, 1);
         ex.f = __shfl_up_sync(0xffffffffu, inc.f, 1);
-        if (lane == 0) { ex.v = 0.0; ex.c = 0; ex.f = 0; }
+        ex.k = __shfl_up_sync(0xffffffffu, inc.k, 1);
+        if (lane == 0) { ex.v = 0.0; ex.c = 0; ex.f = 0; ex.k = 0; }
         __syncthreads();
-        Scan wp; wp.v = 0.0; wp.c = 0; wp.f = 0;
+        Scan wp; wp.v = 0.0; wp.c = 0; wp.f = 0; wp.k = 0;
         for (int w2 = 0; w2 < warp; w2++) wp = combine(wp, s_warp[w2]);
         const Scan cin = combine(wp, ex);
+        if (tid == kUpdThreads - 1) s_nlist = (int)(cin.k + mine.k);
 
-        // ---- pass 2: walk again, close segments
+        // ---- pass 2: walk again; every closed segment goes to the list, in feature order
         double run = cin.v; uint32_t cnt = cin.c; bool seen_head = cin.f != 0;
+        int slot = (int)cin.k;
         if (tid == 0 && edge_continues) { run = carry.sum; cnt = carry.cnt; }
-        // the carried segment ended exactly at the tile edge: thread 0 retires it
-        if (tid == 0 && carry.valid && !edge_continues) {
-            if (carry_open) out.first = carry; else apply_update(P, carry.key, carry.sum, carry.cnt);
+        if (tid == 0 && carry.cnt != 0 && !edge_continues) {
+            if (carry_open) first = carry;
+            else { l_key[slot] = carry.key; l_g[slot] = grad_of(P, carry.sum, carry.cnt); slot++; }
         }
 #pragma unroll
         for (int i = 0; i < kUpdItems; i++) {
@@ -308,37 +391,39 @@ __global__ void __launch_bounds__(kUpdThreads) linear_update_kernel(UpdParams P)
                 const bool head = q > 0 && kk[i] != (i == 0 ? prev_key : kk[i - 1]);
                 if (head) { run = 0.0; cnt = 0; seen_head = true; }
                 run += (double)vv[i]; cnt += 1;
-                // open: the segment reaches the tile's left edge and, through it, the CTA's left edge
+                // open: the segment reaches the tile's left edge and, through it, past the CTA's left edge
                 const bool open = !seen_head && edge_open;
-                if (q == n_tile - 1) {
-                    s_carry.sum = run; s_carry.key = kk[i]; s_carry.cnt = cnt; s_carry.valid = 1; s_carry.pad = 0;
-                    s_carry_open = open ? 1u : 0u;
-                } else if (s_key[pad_idx(q + 1)] != kk[i]) {
+                const bool closes = q < n_tile - 1 ? kk[i + 1] != kk[i] : close_tail;
+                if (closes) {
                     if (open) {
-                        out.first.sum = run; out.first.key = kk[i]; out.first.cnt = cnt; out.first.valid = 1;
+                        first.sum = run; first.key = kk[i]; first.cnt = cnt;
+                        l_key[slot] = 0xffffffffu; l_g[slot] = 0.f;   // placeholder: skipped by apply_list
                     } else {
-                        apply_update(P, kk[i], run, cnt);
+                        l_key[slot] = kk[i]; l_g[slot] = grad_of(P, run, cnt);
                     }
+                    slot++;
+                    if (q == n_tile - 1) { s_carry.cnt = 0; s_carry_open = 0; }
+                } else if (q == n_tile - 1) {
+                    s_carry.sum = run; s_carry.key = kk[i]; s_carry.cnt = cnt;
+                    s_carry_open = open ? 1u : 0u;
                 }
             }
         }
         __syncthreads();
+        // ---- optimizer step for the listed features, latencies overlapped
+        apply_list(P, l_key, l_g, s_nlist, tid);
+        __syncthreads();
     }
-    // ---- publish this CTA's boundary records
-    // out.first may have been produced by any thread: reduce through shared memory.
-    __shared__ SegRec s_first;
-    if (tid == 0) s_first.valid = 0;
-    __syncthreads();
-    if (out.first.valid) s_first = out.first;   // at most one thread of the CTA holds a valid first
+    // ---- publish this CTA's boundary records (at most one thread holds a valid `first`)
+    if (first.cnt != 0) s_first = first;
     __syncthreads();
     if (tid == 0) {
         Boundary b;
         b.first = s_first;
-        b.last.valid = 0; b.last.sum = 0; b.last.key = 0; b.last.cnt = 0; b.last.pad = 0;
-        if (lo < hi) {
-            const SegRec carry = s_carry;
-            if (s_carry_open) b.first = carry;   // the whole CTA range is one segment
-            else b.last = carry;
+        b.last.cnt = 0; b.last.sum = 0; b.last.key = 0;
+        if (lo < hi && s_carry.cnt != 0) {
+            if (s_carry_open) b.first = s_carry;   // the whole CTA range lies inside one segment
+            else b.last = s_carry;
         }
         P.boundary[blockIdx.x] = b;
         __threadfence();
@@ -347,24 +432,57 @@ __global__ void __launch_bounds__(kUpdThreads) linear_update_kernel(UpdParams P)
     }
     __syncthreads();
     if (!s_is_last) return;
-    // ---- the last CTA to finish merges the boundary records in CTA order
+    // ---- the last CTA to finish merges the boundary records in CTA order.  Records are staged
+    // in shared memory a chunk at a time; a run of equal features that reaches the end of a chunk
+    // is carried into the next one as its slot 0.  Completed runs go to a list and are applied
+    // with the same batched step as above.
     __threadfence();
+    const int n_rec = 2 * P.n_active;
+    double *m_sum = reinterpret_cast<double *>(smem_raw);
+    uint32_t *m_key = reinterpret_cast<uint32_t *>(smem_raw + (size_t)kUpdMergeChunk * 8);
+    uint32_t *m_cnt = m_key + kUpdMergeChunk;
+    uint32_t *ml_key = m_cnt + kUpdMergeChunk;
+    float *ml_g = reinterpret_cast<float *>(ml_key + kUpdMergeChunk);
     const volatile SegRec *rec = reinterpret_cast<const volatile SegRec *>(P.boundary);
-    const int n_rec = 2 * (int)gridDim.x;
-    for (int i = tid; i < n_rec; i += kUpdThreads) {
-        if (!rec[i].valid) continue;
-        const uint32_t key = rec[i].key;
-        // a run starts here unless the previous valid record has the same feature
-        int j = i - 1;
-        while (j >= 0 && !rec[j].valid) j--;
-        if (j >= 0 && rec[j].key == key) continue;
-        double sum = rec[i].sum; uint32_t cnt = rec[i].cnt;
-        for (j = i + 1; j < n_rec; j++) {
-            if (!rec[j].valid) continue;
-            if (rec[j].key != key) break;
-            sum += rec[j].sum; cnt += rec[j].cnt;
+    if (tid == 0) s_mcarry.cnt = 0;
+    __syncthreads();
+    for (int c0 = 0; c0 < n_rec; c0 += kUpdMergeChunk - 1) {
+        const int n_in = min(kUpdMergeChunk - 1, n_rec - c0);
+        const bool last_chunk = c0 + n_in >= n_rec;
+        if (tid == 0) {
+            m_sum[0] = s_mcarry.sum; m_key[0] = s_mcarry.key; m_cnt[0] = s_mcarry.cnt;
+            s_mcarry.cnt = 0;        // re-set below by the run that reaches the end of this chunk
+            s_nlist = 0;
         }
-        apply_update(P, key, sum, cnt);
+        for (int i = tid; i < n_in; i += kUpdThreads) {
+            m_sum[i + 1] = rec[c0 + i].sum; m_key[i + 1] = rec[c0 + i].key; m_cnt[i + 1] = rec[c0 + i].cnt;
+        }
+        __syncthreads();
+        const int n_slots = n_in + 1;
+        for (int i = tid; i < n_slots; i += kUpdThreads) {
+            if (m_cnt[i] == 0) continue;
+            const uint32_t key = m_key[i];
+            // a run starts here unless the previous non-empty slot has the same feature
+            int j = i - 1;
+            while (j >= 0 && m_cnt[j] == 0) j--;
+            if (j >= 0 && m_key[j] == key) continue;
+            double sum = m_sum[i]; uint32_t cnt = m_cnt[i];
+            for (j = i + 1; j < n_slots; j++) {
+                if (m_cnt[j] == 0) continue;
+                if (m_key[j] != key) break;
+                sum += m_sum[j]; cnt += m_cnt[j];
+            }
+            if (j >= n_slots && !last_chunk) {
+                // the one run that contains the last non-empty slot: it may continue in the next chunk
+                s_mcarry.sum = sum; s_mcarry.key = key; s_mcarry.cnt = cnt;
+            } else {
+                const int slot = atomicAdd(&s_nlist, 1);
+                ml_key[slot] = key; ml_g[slot] = grad_of(P, sum, cnt);
+            }
+        }
+        __syncthreads();
+        apply_list(P, ml_key, ml_g, s_nlist, tid);
+        __syncthreads();
     }
     if (tid == 0) *P.done_counter = 0;   // ready for the next launch on this stream
 }
@@ -482,18 +600,18 @@ int grid_for(int64_t ctas_wanted, int per_sm)
 hm_status launch_linear_forward(Launcher &L, const LinearArgs &a, const int64_t *d_rowptr, int64_t row0,
                                 int32_t n_rows, int64_t block_row0, const uint32_t *d_feature,
                                 const float *d_value, const float *d_label, float *d_margin,
-                                float *d_dloss, float *d_contrib, uint32_t *d_bad, int64_t nnz_hint)
+                                float *d_dloss, uint32_t *d_bad, int64_t nnz_hint)
 {
     if (n_rows <= 0) return HM_OK;
     FwdParams P;
     P.w = a.w; P.rowptr = d_rowptr; P.feature = d_feature; P.value = d_value; P.label = d_label;
-    P.margin = d_margin; P.dloss = d_dloss; P.contrib = d_contrib;
+    P.margin = d_margin; P.dloss = d_dloss;
     P.block_row0 = block_row0; P.row0 = row0; P.n_rows = n_rows;
-    P.task = a.cfg.task; P.loss = a.cfg.loss; P.write_contrib = 1;
+    P.task = a.cfg.task; P.loss = a.cfg.loss; P.train = 1;
     P.dims = (uint32_t)a.cfg.dims; P.bad = d_bad;
     const int grid = grid_for(((int64_t)n_rows + 7) / 8, 8);
-    // algorithmic bytes: idx+val read, w gather, contrib write, label+rowptr+margin+dloss per row
-    const double bytes = 16.0 * (double)nnz_hint + 24.0 * (double)n_rows;
+    // algorithmic bytes: feature+value read, w gather per element; rowptr, label, margin, dloss per row
+    const double bytes = 12.0 * (double)nnz_hint + 20.0 * (double)n_rows;
     HM_LAUNCH(L, K_LIN_FORWARD, bytes, (linear_forward_kernel<<<grid, kFwdThreads, 0, L.stream>>>(P)));
     HM_CUDA(cudaGetLastError());
     return HM_OK;
@@ -506,9 +624,9 @@ hm_status launch_predict_linear(Launcher &L, const float *w, int64_t dims, int64
     if (n_rows > 0x7fffffff) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "predict: too many rows in one call");
     FwdParams P;
     P.w = w; P.rowptr = d_rowptr; P.feature = d_feature; P.value = d_value; P.label = nullptr;
-    P.margin = d_out; P.dloss = nullptr; P.contrib = nullptr;
+    P.margin = d_out; P.dloss = nullptr;
     P.block_row0 = 0; P.row0 = 0; P.n_rows = (int32_t)n_rows;
-    P.task = 0; P.loss = 0; P.write_contrib = 0;
+    P.task = 0; P.loss = 0; P.train = 0;
     P.dims = (uint32_t)dims; P.bad = d_bad;
     const int grid = grid_for((n_rows + 7) / 8, 8);
     HM_LAUNCH(L, K_PREDICT, 0.0, (linear_forward_kernel<<<grid, kFwdThreads, 0, L.stream>>>(P)));
@@ -519,7 +637,7 @@ hm_status launch_predict_linear(Launcher &L, const float *w, int64_t dims, int64
 hm_status update_scratch_reserve(UpdateScratch &u)
 {
     if (u.boundary) return HM_OK;
-    u.grid = kNumSMs * 2;
+    u.grid = kUpdMaxGrid;
     HM_CUDA(cudaMalloc(&u.boundary, (size_t)u.grid * sizeof(Boundary)));
     HM_CUDA(cudaMalloc(&u.done_counter, sizeof(uint32_t)));
     HM_CUDA(cudaMemset(u.done_counter, 0, sizeof(uint32_t)));
@@ -533,23 +651,27 @@ void update_scratch_free(UpdateScratch &u)
 }
 
 hm_status launch_linear_update(Launcher &L, const LinearArgs &a, const StepScalars &sc, UpdateScratch &us,
-                               const uint32_t *d_sorted_key, const uint32_t *d_sorted_pay,
-                               const uint32_t *d_seg_off, int seg, const float *d_contrib, int64_t nnz_hint)
+                               const uint32_t *d_sorted_key, const uint2 *d_sorted_pay,
+                               const uint32_t *d_seg_off, int seg, const float *d_dloss, int64_t nnz_hint)
 {
     UpdParams P;
     P.w = a.w; P.state = a.state; P.touched = nullptr;
-    P.skey = d_sorted_key; P.spay = d_sorted_pay; P.contrib = d_contrib; P.seg_off = d_seg_off;
+    P.skey = d_sorted_key; P.spay = d_sorted_pay; P.dloss = d_dloss; P.seg_off = d_seg_off;
     P.boundary = reinterpret_cast<Boundary *>(us.boundary); P.done_counter = us.done_counter;
     P.seg = seg; P.dims = (uint32_t)a.cfg.dims;
     P.opt = a.cfg.opt; P.reg = a.cfg.reg; P.grad_norm = a.cfg.grad_norm; P.state_width = a.state_width;
     P.eta = sc.eta; P.adam_alpha = sc.adam_alpha; P.lambda = a.cfg.lambda; P.eps = a.cfg.eps; P.rho = a.cfg.rho;
     P.beta1 = a.cfg.beta1; P.beta2 = a.cfg.beta2; P.alpha = a.cfg.alpha; P.beta = a.cfg.beta;
     P.lambda1 = a.cfg.lambda1; P.lambda2 = a.cfg.lambda2;
-    P.n_rows = (double)sc.n_rows;
-    int64_t tiles = (nnz_hint + kUpdTile - 1) / kUpdTile;
-    int grid = grid_for(tiles, 2);
-    if (grid > us.grid) grid = us.grid;
-    // algorithmic bytes: sorted key+payload, contrib gather; state traffic is per unique feature (unknown here)
+    P.inv_rows = 1.0 / (double)sc.n_rows;
+    // one tile per CTA up to kUpdMaxGrid CTAs; beyond that each CTA walks consecutive tiles.
+    // nnz_hint is exact (the host knows rowptr at every mini-batch boundary).
+    const int64_t tiles = std::max<int64_t>((nnz_hint + kUpdTile - 1) / kUpdTile, 1);
+    const int64_t tiles_per_cta = (tiles + us.grid - 1) / us.grid;
+    const int grid = (int)((tiles + tiles_per_cta - 1) / tiles_per_cta);
+    P.n_active = grid;
+    // algorithmic bytes: sorted feature + (row, value) stream; dloss table and the per-feature
+    // state traffic (number of distinct features is data dependent) are not counted
     const double bytes = 12.0 * (double)nnz_hint;
     HM_LAUNCH(L, K_LIN_UPDATE, bytes, (linear_update_kernel<<<grid, kUpdThreads, 0, L.stream>>>(P)));
     HM_CUDA(cudaGetLastError());

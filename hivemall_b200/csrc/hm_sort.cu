@@ -8,10 +8,14 @@
 // inside each segment elements are ordered by feature id, ties by original position
 // (stable), so the later per-feature sum always adds rows in row order.
 //
+// Payload of every element is (row inside its mini-batch, value): with it the update kernel
+// streams the sorted mini-batch and only looks up dloss[row] in a table of mini_batch floats,
+// instead of gathering 4 bytes per element at random (profiles/r01a_summary.md).
+//
 // Per 8-bit digit pass:  hist (reads keys, 4 B/elem)  ->  two tiny scans  ->
-// scatter (reads key+payload, writes key+payload, 16 B/elem).  The first pass reads the
-// CSR feature array directly and synthesises the payload (element position), so no copy
-// of the input is made.  Integer counting only; atomics are integer (order-independent).
+// scatter (reads key+payload, writes key+payload, 24 B/elem).  The first pass reads the
+// CSR feature/value arrays directly plus the row ids written by expand_rows, so no copy of
+// the input is made.  Integer counting only; atomics are integer (order-independent).
 #include "hm_internal.h"
 
 namespace hm {
@@ -48,6 +52,20 @@ __global__ void seg_prep_kernel(const int64_t *__restrict__ rowptr, int64_t row0
             run += (off[s + 1] - off[s] + kSortTile - 1) / kSortTile;
         }
         seg_tile_off[n_segs] = run;
+    }
+}
+
+// erow[e] = row of element e counted from the start of its mini-batch.  Warp per row.
+__global__ void __launch_bounds__(256)
+expand_rows_kernel(const int64_t *__restrict__ rowptr, int64_t row0, int64_t n_rows, int32_t mini_batch,
+                   uint32_t *__restrict__ erow)
+{
+    const int lane = threadIdx.x & 31;
+    const int64_t base = rowptr[row0];
+    for (int64_t r = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5); r < n_rows; r += (int64_t)gridDim.x * 8) {
+        const int64_t p0 = rowptr[row0 + r] - base, p1 = rowptr[row0 + r + 1] - base;
+        const uint32_t local = (uint32_t)(r % mini_batch);
+        for (int64_t p = p0 + lane; p < p1; p += 32) erow[p] = local;
     }
 }
 
@@ -150,15 +168,20 @@ scan_tiles_kernel(uint32_t *__restrict__ tile_hist, const uint32_t *__restrict__
     }
 }
 
+constexpr size_t kScatterSmem = (size_t)kSortTile * 4 + (size_t)kSortTile * 8;   // keys + payloads
+
 template <bool FIRST>
 __global__ void __launch_bounds__(kSortThreads)
-sort_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint32_t *__restrict__ pay_in,
-                    uint32_t *__restrict__ keys_out, uint32_t *__restrict__ pay_out,
+sort_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint2 *__restrict__ pay_in,
+                    const uint32_t *__restrict__ erow_in, const float *__restrict__ val_in,
+                    uint32_t *__restrict__ keys_out, uint2 *__restrict__ pay_out,
                     const uint32_t *__restrict__ seg_off, const uint32_t *__restrict__ seg_tile_off,
                     int n_segs, int shift, const uint32_t *__restrict__ tile_hist)
 {
+    extern __shared__ __align__(16) unsigned char dyn_smem[];
+    uint32_t *s_key = reinterpret_cast<uint32_t *>(dyn_smem);
+    uint2 *s_pay = reinterpret_cast<uint2 *>(dyn_smem + (size_t)kSortTile * 4);
     __shared__ uint32_t s_off[kMaxSegs + 1], s_toff[kMaxSegs + 1];
-    __shared__ uint32_t s_key[kSortTile], s_pay[kSortTile];
     __shared__ uint32_t wcnt[kSortWarps][kRadix];
     __shared__ uint32_t dig_base[kRadix], gofs[kRadix], warp_tot[kSortWarps];
     for (int s = threadIdx.x; s <= n_segs; s += kSortThreads) { s_off[s] = seg_off[s]; s_toff[s] = seg_tile_off[s]; }
@@ -172,12 +195,12 @@ sort_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint32_t *__rest
         const uint32_t e0 = s_off[seg] + tis * kSortTile;
         const uint32_t e1 = min(e0 + (uint32_t)kSortTile, s_off[seg + 1]);
         // warp-striped load: warp w owns tile positions [w*512, (w+1)*512), round i, lane
-        uint32_t key[kSortItems], pay[kSortItems], rank[kSortItems];
+        const uint32_t ew = e0 + warp * (32 * kSortItems) + lane;
+        uint32_t key[kSortItems], rank[kSortItems];
 #pragma unroll
         for (int i = 0; i < kSortItems; i++) {
-            const uint32_t e = e0 + warp * (32 * kSortItems) + i * 32 + lane;
-            key[i] = e < e1 ? __ldg(keys_in + e) : 0xffffffffu;
-            pay[i] = FIRST ? e : (e < e1 ? __ldg(pay_in + e) : 0u);
+            const uint32_t e = ew + i * 32;
+            key[i] = e < e1 ? __ldcs(keys_in + e) : 0xffffffffu;
         }
 #pragma unroll
         for (int w = 0; w < kSortWarps; w++) wcnt[w][threadIdx.x] = 0;
@@ -185,8 +208,7 @@ sort_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint32_t *__rest
         // stable rank of every element among equal digits inside its warp
 #pragma unroll
         for (int i = 0; i < kSortItems; i++) {
-            const uint32_t e = e0 + warp * (32 * kSortItems) + i * 32 + lane;
-            const bool valid = e < e1;
+            const bool valid = ew + i * 32 < e1;
             const uint32_t d = (key[i] >> shift) & (kRadix - 1);
             const uint32_t active = __ballot_sync(0xffffffffu, valid);
             uint32_t peers = 0, prev = 0;
@@ -219,14 +241,17 @@ sort_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint32_t *__rest
             gofs[d] = tile_hist[(size_t)s_toff[seg] * kRadix + (size_t)d * nt + tis] - ex;
         }
         __syncthreads();
+        // place keys and payloads at their tile-local sorted position (payload loaded only now:
+        // sixteen independent loads in flight per thread, no registers held across the ranking)
 #pragma unroll
         for (int i = 0; i < kSortItems; i++) {
-            const uint32_t e = e0 + warp * (32 * kSortItems) + i * 32 + lane;
+            const uint32_t e = ew + i * 32;
             if (e < e1) {
                 const uint32_t d = (key[i] >> shift) & (kRadix - 1);
                 const uint32_t pos = dig_base[d] + wcnt[warp][d] + rank[i];
                 s_key[pos] = key[i];
-                s_pay[pos] = pay[i];
+                s_pay[pos] = FIRST ? make_uint2(__ldcs(erow_in + e), __float_as_uint(__ldcs(val_in + e)))
+                                   : __ldcs(pay_in + e);
             }
         }
         __syncthreads();
@@ -262,16 +287,18 @@ hm_status sort_scratch_reserve(SortScratch &s, int64_t elems)
         for (int b = 0; b < 2; b++) {
             if (s.key[b]) cudaFree(s.key[b]);
             if (s.pay[b]) cudaFree(s.pay[b]);
-            s.key[b] = s.pay[b] = nullptr;
+            s.key[b] = nullptr; s.pay[b] = nullptr;
         }
         if (s.tile_hist) cudaFree(s.tile_hist);
-        s.tile_hist = nullptr;
+        if (s.erow) cudaFree(s.erow);
+        s.tile_hist = nullptr; s.erow = nullptr;
         s.cap_elems = 0;
         int64_t cap = elems + elems / 8;
         for (int b = 0; b < 2; b++) {
             HM_CUDA(cudaMalloc(&s.key[b], (size_t)cap * sizeof(uint32_t)));
-            HM_CUDA(cudaMalloc(&s.pay[b], (size_t)cap * sizeof(uint32_t)));
+            HM_CUDA(cudaMalloc(&s.pay[b], (size_t)cap * sizeof(uint2)));
         }
+        HM_CUDA(cudaMalloc(&s.erow, (size_t)cap * sizeof(uint32_t)));
         s.cap_tiles = cap / kSortTile + kMaxSegs + 1;
         HM_CUDA(cudaMalloc(&s.tile_hist, (size_t)s.cap_tiles * kRadix * sizeof(uint32_t)));
         s.cap_elems = cap;
@@ -281,26 +308,36 @@ hm_status sort_scratch_reserve(SortScratch &s, int64_t elems)
 
 void sort_scratch_free(SortScratch &s)
 {
-    for (int b = 0; b < 2; b++) { cudaFree(s.key[b]); cudaFree(s.pay[b]); s.key[b] = s.pay[b] = nullptr; }
-    cudaFree(s.tile_hist); cudaFree(s.row_sum); cudaFree(s.seg_off); cudaFree(s.seg_tile_off);
-    s.tile_hist = s.row_sum = s.seg_off = s.seg_tile_off = nullptr;
+    for (int b = 0; b < 2; b++) { cudaFree(s.key[b]); cudaFree(s.pay[b]); s.key[b] = nullptr; s.pay[b] = nullptr; }
+    cudaFree(s.tile_hist); cudaFree(s.row_sum); cudaFree(s.seg_off); cudaFree(s.seg_tile_off); cudaFree(s.erow);
+    s.tile_hist = s.row_sum = s.seg_off = s.seg_tile_off = s.erow = nullptr;
     s.cap_elems = s.cap_tiles = 0;
 }
 
 hm_status launch_seg_prep(Launcher &L, SortScratch &s, const int64_t *d_rowptr, int64_t row0,
-                          int64_t n_rows, int32_t mini_batch, int n_segs)
+                          int64_t n_rows, int64_t n_elems, int32_t mini_batch, int n_segs)
 {
     if (n_segs < 1 || n_segs > kMaxSegs) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "segment count %d out of range", n_segs);
     HM_LAUNCH(L, K_SEG_PREP, 0.0,
               (seg_prep_kernel<<<1, 256, 0, L.stream>>>(d_rowptr, row0, n_rows, mini_batch, n_segs, s.seg_off,
                                                         s.seg_tile_off)));
+    // row id of every element (4 B/elem written; rowptr read once)
+    HM_LAUNCH(L, K_SEG_PREP, 4.0 * (double)n_elems + 8.0 * (double)n_rows,
+              (expand_rows_kernel<<<persistent_grid((n_rows + 7) / 8, 8), 256, 0, L.stream>>>(
+                  d_rowptr, row0, n_rows, mini_batch, s.erow)));
     HM_CUDA(cudaGetLastError());
     return HM_OK;
 }
 
 hm_status launch_segmented_sort(Launcher &L, SortScratch &s, const uint32_t *d_feature_block,
-                                int64_t n_elems, int n_segs, int key_bits, int *out_buf)
+                                const float *d_value_block, int64_t n_elems, int n_segs, int key_bits, int *out_buf)
 {
+    static bool attr_set = false;   // > 48 KB of dynamic shared memory needs opting in, once per process
+    if (!attr_set) {
+        HM_CUDA(cudaFuncSetAttribute(sort_scatter_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kScatterSmem));
+        HM_CUDA(cudaFuncSetAttribute(sort_scatter_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kScatterSmem));
+        attr_set = true;
+    }
     if (n_elems > s.cap_elems) HM_FAIL(HM_ERR_STATE, "sort scratch too small (%lld > %lld)", (long long)n_elems,
                                        (long long)s.cap_elems);
     int passes = (key_bits + 7) / 8;
@@ -311,8 +348,9 @@ hm_status launch_segmented_sort(Launcher &L, SortScratch &s, const uint32_t *d_f
     for (int p = 0; p < passes; p++) {
         const int shift = 8 * p;
         const uint32_t *kin = p == 0 ? d_feature_block : s.key[(p - 1) & 1];
-        const uint32_t *pin = p == 0 ? nullptr : s.pay[(p - 1) & 1];
-        uint32_t *kout = s.key[p & 1], *pout = s.pay[p & 1];
+        const uint2 *pin = p == 0 ? nullptr : s.pay[(p - 1) & 1];
+        uint32_t *kout = s.key[p & 1];
+        uint2 *pout = s.pay[p & 1];
         HM_CUDA(cudaMemsetAsync(s.row_sum, 0, (size_t)rows * sizeof(uint32_t), L.stream));
         HM_LAUNCH(L, K_SORT_HIST, 4.0 * (double)n_elems,
                   (sort_hist_kernel<<<grid, kSortThreads, 0, L.stream>>>(kin, s.seg_off, s.seg_tile_off, n_segs, shift,
@@ -322,13 +360,15 @@ hm_status launch_segmented_sort(Launcher &L, SortScratch &s, const uint32_t *d_f
                   (scan_tiles_kernel<<<(rows + kSortWarps - 1) / kSortWarps, kSortThreads, 0, L.stream>>>(
                       s.tile_hist, s.row_sum, s.seg_tile_off, n_segs)));
         if (p == 0)
-            HM_LAUNCH(L, K_SORT_SCATTER, 12.0 * (double)n_elems,
-                      (sort_scatter_kernel<true><<<grid, kSortThreads, 0, L.stream>>>(
-                          kin, pin, kout, pout, s.seg_off, s.seg_tile_off, n_segs, shift, s.tile_hist)));
+            HM_LAUNCH(L, K_SORT_SCATTER, 24.0 * (double)n_elems,
+                      (sort_scatter_kernel<true><<<grid, kSortThreads, kScatterSmem, L.stream>>>(
+                          kin, pin, s.erow, d_value_block, kout, pout, s.seg_off, s.seg_tile_off, n_segs, shift,
+                          s.tile_hist)));
         else
-            HM_LAUNCH(L, K_SORT_SCATTER, 16.0 * (double)n_elems,
-                      (sort_scatter_kernel<false><<<grid, kSortThreads, 0, L.stream>>>(
-                          kin, pin, kout, pout, s.seg_off, s.seg_tile_off, n_segs, shift, s.tile_hist)));
+            HM_LAUNCH(L, K_SORT_SCATTER, 24.0 * (double)n_elems,
+                      (sort_scatter_kernel<false><<<grid, kSortThreads, kScatterSmem, L.stream>>>(
+                          kin, pin, nullptr, nullptr, kout, pout, s.seg_off, s.seg_tile_off, n_segs, shift,
+                          s.tile_hist)));
     }
     HM_CUDA(cudaGetLastError());
     *out_buf = (passes - 1) & 1;

@@ -185,6 +185,15 @@ static float adam_alpha(const hmo_config *c, float eta, int64_t t)
     return (float)((double)eta * sqrt(1.0 - b2) / (1.0 - b1));
 }
 
+/* the per-feature fp64 sum becomes the fp32 mean gradient.  Batch
+ * normalisation multiplies by the fp64 reciprocal of the row count (one rounding). */
+static inline float mean_grad(const hmo_config *c, double sum, uint32_t cnt, double inv_nb)
+{
+    if (c->grad_norm == HMO_NORM_BATCH) return (float)(sum * inv_nb);
+    if (c->grad_norm == HMO_NORM_COUNT) return (float)(sum / (double)cnt);
+    return (float)sum;
+}
+
 /* ---------------------------------------------------------------- linear learner */
 
 void hmo_predict_linear(int64_t n_rows, const int64_t *rowptr, const uint32_t *idx,
@@ -248,11 +257,10 @@ int hmo_train_linear(const hmo_config *c, int64_t n_rows, const int64_t *rowptr,
             *t += 1;
             const float eta = hmo_eta(c, *t);
             const float alpha_t = c->opt == HMO_OPT_ADAM ? adam_alpha(c, eta, *t) : 0.0f;
+            const double inv_nb = 1.0 / (double)nb;
             for (int64_t k = 0; k < nt; k++) {
                 uint32_t j = touch[k];
-                double denom = c->grad_norm == HMO_NORM_BATCH ? (double)nb
-                             : c->grad_norm == HMO_NORM_COUNT ? (double)cnt[j] : 1.0;
-                float g = (float)(gsum[j] / denom);
+                float g = mean_grad(c, gsum[j], cnt[j], inv_nb);
                 update_coord(c, eta, alpha_t, g, &w[j], s1 ? &s1[j] : &dummy, s2 ? &s2[j] : &dummy);
                 gsum[j] = 0.0; cnt[j] = 0;
             }
@@ -299,6 +307,7 @@ int hmo_train_linear_mt(const hmo_config *c, int64_t n_rows, const int64_t *rowp
             const int64_t b1 = b0 + B < n_rows ? b0 + B : n_rows;
             const int64_t nb = b1 - b0;
             const int64_t e0 = rowptr[b0];
+            const double inv_nb = 1.0 / (double)nb;
             *t += 1;
             const float eta = hmo_eta(c, *t);
             const float alpha_t = c->opt == HMO_OPT_ADAM ? adam_alpha(c, eta, *t) : 0.0f;
@@ -356,9 +365,7 @@ int hmo_train_linear_mt(const hmo_config *c, int64_t n_rows, const int64_t *rowp
                 }
                 for (int64_t k = 0; k < nt; k++) {
                     const uint32_t j = mine[k];
-                    const double denom = c->grad_norm == HMO_NORM_BATCH ? (double)nb
-                                       : c->grad_norm == HMO_NORM_COUNT ? (double)cnt[j] : 1.0;
-                    const float g = (float)(gsum[j] / denom);
+                    const float g = mean_grad(c, gsum[j], cnt[j], inv_nb);
                     update_coord(c, eta, alpha_t, g, &w[j], s1 ? &s1[j] : &dummy[tid], s2 ? &s2[j] : &dummy[tid]);
                     gsum[j] = 0.0; cnt[j] = 0;
                 }

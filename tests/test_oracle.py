@@ -96,8 +96,7 @@ def np_train(cfg, rowptr, feat, val, label):
             t += 1
             eta = F(_oracle.lib().hmo_eta(cfg, t))
             for j, sm in sums.items():
-                den = float(b1 - b0) if cfg.grad_norm == 0 else (float(cnts[j]) if cfg.grad_norm == 1 else 1.0)
-                g = F(sm / den)
+                g = F(sm * (1.0 / float(b1 - b0))) if cfg.grad_norm == 0 else (F(sm / float(cnts[j])) if cfg.grad_norm == 1 else F(sm))
                 wv = w[j]
                 if cfg.reg == 2 and cfg.opt != 4:
                     g = F(g + F(F(cfg.lambda_) * wv))
