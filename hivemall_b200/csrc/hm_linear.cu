@@ -110,6 +110,7 @@ struct SegRec {           // a (feature, partial sum) record; cnt == 0 means emp
     uint32_t key, cnt;
 };
 struct Boundary { SegRec first, last; };
+static_assert(sizeof(SegRec) == 16, "the merge reads boundary records as 16-byte vectors");
 
 constexpr int kUpdMaxGrid = 2048;     // CTAs per launch; beyond that each CTA walks consecutive tiles
 constexpr int kUpdMergeChunk = 1536;  // boundary records merged per shared-memory chunk
@@ -287,16 +288,17 @@ __global__ void __launch_bounds__(kUpdThreads, 3) linear_update_kernel(UpdParams
 
     SegRec first;                    // this thread's candidate for the CTA's left-open segment
     first.cnt = 0; first.sum = 0; first.key = 0;
-    if (tid == 0) {
-        s_carry.cnt = 0; s_carry_open = 0; s_first.cnt = 0;
-        // Peek at the neighbours of the range: a first segment that really starts at `lo`, or a last
-        // segment that really ends at `hi`, is complete inside this CTA and never reaches the merge.
-        s_edge[0] = (lo < hi) && (lo == 0 || __ldg(P.skey + s0 + lo - 1) != __ldg(P.skey + s0 + lo));
-        s_edge[1] = (lo < hi) && (hi == n || __ldg(P.skey + s0 + hi) != __ldg(P.skey + s0 + hi - 1));
+    if (tid == 0) { s_carry.cnt = 0; s_carry_open = 0; s_first.cnt = 0; }
+    // Peek at the neighbours of the range: a first segment that really starts at `lo`, or a last
+    // segment that really ends at `hi`, is complete inside this CTA and never reaches the merge.
+    // The four loads are issued here and only consumed after the first tile's barrier, so they
+    // overlap the tile loads instead of adding a round trip.
+    if (tid == 32 && lo < hi) {
+        const uint32_t a0 = lo == 0 ? 0u : __ldg(P.skey + s0 + lo - 1), a1 = __ldg(P.skey + s0 + lo);
+        const uint32_t b0 = __ldg(P.skey + s0 + hi - 1), b1 = hi == n ? 0u : __ldg(P.skey + s0 + hi);
+        s_edge[0] = lo == 0 || a0 != a1;
+        s_edge[1] = hi == n || b0 != b1;
     }
-    __syncthreads();
-    const bool left_closed = s_edge[0] != 0, right_closed = s_edge[1] != 0;
-
     for (uint32_t t0 = lo; t0 < hi; t0 += kUpdTile) {
         const int n_tile = (int)min((uint32_t)kUpdTile, hi - t0);
         // ---- coalesced striped load; contribution = dloss[row] * value (fp32 product)
@@ -315,6 +317,7 @@ __global__ void __launch_bounds__(kUpdThreads, 3) linear_update_kernel(UpdParams
             }
         }
         __syncthreads();
+        const bool left_closed = s_edge[0] != 0, right_closed = s_edge[1] != 0;
         const SegRec carry = s_carry;
         const uint32_t carry_open = s_carry_open;
         const bool first_tile = t0 == lo;
@@ -443,37 +446,58 @@ __global__ void __launch_bounds__(kUpdThreads, 3) linear_update_kernel(UpdParams
     uint32_t *m_cnt = m_key + kUpdMergeChunk;
     uint32_t *ml_key = m_cnt + kUpdMergeChunk;
     float *ml_g = reinterpret_cast<float *>(ml_key + kUpdMergeChunk);
-    const volatile SegRec *rec = reinterpret_cast<const volatile SegRec *>(P.boundary);
+    const uint4 *rec4 = reinterpret_cast<const uint4 *>(P.boundary);   // SegRec = {double sum; u32 key; u32 cnt}
     if (tid == 0) s_mcarry.cnt = 0;
     __syncthreads();
+    __shared__ int s_wsum[kUpdThreads / 32];
+    constexpr int kPer = (kUpdMergeChunk + kUpdThreads - 1) / kUpdThreads;   // records per thread and chunk
     for (int c0 = 0; c0 < n_rec; c0 += kUpdMergeChunk - 1) {
         const int n_in = min(kUpdMergeChunk - 1, n_rec - c0);
         const bool last_chunk = c0 + n_in >= n_rec;
+        // Each thread takes kPer CONSECUTIVE records (one 16-byte L2 load each, all in flight
+        // together), keeps the non-empty ones, and an exclusive block scan of the counts gives
+        // every survivor its place: the compact list keeps CTA order.  Slot 0 is the carried run.
+        uint4 raw[kPer];
+        int mine = 0;
+#pragma unroll
+        for (int u = 0; u < kPer; u++) {
+            const int i = tid * kPer + u;
+            raw[u] = i < n_in ? __ldcg(rec4 + c0 + i) : make_uint4(0u, 0u, 0u, 0u);
+        }
+#pragma unroll
+        for (int u = 0; u < kPer; u++) mine += raw[u].w != 0u;
+        int inc = mine;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const int v = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += v; }
+        if (lane == 31) s_wsum[warp] = inc;
+        const bool have_carry = s_mcarry.cnt != 0;
+        __syncthreads();
+        int pos = (have_carry ? 1 : 0) + inc - mine;
+        for (int w2 = 0; w2 < warp; w2++) pos += s_wsum[w2];
+        int n_slots = have_carry ? 1 : 0;
+        for (int w2 = 0; w2 < kUpdThreads / 32; w2++) n_slots += s_wsum[w2];
         if (tid == 0) {
-            m_sum[0] = s_mcarry.sum; m_key[0] = s_mcarry.key; m_cnt[0] = s_mcarry.cnt;
-            s_mcarry.cnt = 0;        // re-set below by the run that reaches the end of this chunk
+            if (have_carry) { m_sum[0] = s_mcarry.sum; m_key[0] = s_mcarry.key; m_cnt[0] = s_mcarry.cnt; }
             s_nlist = 0;
         }
-        for (int i = tid; i < n_in; i += kUpdThreads) {
-            m_sum[i + 1] = rec[c0 + i].sum; m_key[i + 1] = rec[c0 + i].key; m_cnt[i + 1] = rec[c0 + i].cnt;
-        }
-        __syncthreads();
-        const int n_slots = n_in + 1;
-        for (int i = tid; i < n_slots; i += kUpdThreads) {
-            if (m_cnt[i] == 0) continue;
-            const uint32_t key = m_key[i];
-            // a run starts here unless the previous non-empty slot has the same feature
-            int j = i - 1;
-            while (j >= 0 && m_cnt[j] == 0) j--;
-            if (j >= 0 && m_key[j] == key) continue;
-            double sum = m_sum[i]; uint32_t cnt = m_cnt[i];
-            for (j = i + 1; j < n_slots; j++) {
-                if (m_cnt[j] == 0) continue;
-                if (m_key[j] != key) break;
-                sum += m_sum[j]; cnt += m_cnt[j];
+#pragma unroll
+        for (int u = 0; u < kPer; u++)
+            if (raw[u].w != 0u) {
+                m_sum[pos] = __hiloint2double((int)raw[u].y, (int)raw[u].x);
+                m_key[pos] = raw[u].z; m_cnt[pos] = raw[u].w;
+                pos++;
             }
+        __syncthreads();
+        if (tid == 0) s_mcarry.cnt = 0;   // re-set below by the run that reaches the end of this chunk
+        __syncthreads();
+        for (int i = tid; i < n_slots; i += kUpdThreads) {
+            const uint32_t key = m_key[i];
+            if (i > 0 && m_key[i - 1] == key) continue;      // not the start of a run
+            double sum = m_sum[i]; uint32_t cnt = m_cnt[i];
+            int j = i + 1;
+            for (; j < n_slots && m_key[j] == key; j++) { sum += m_sum[j]; cnt += m_cnt[j]; }
             if (j >= n_slots && !last_chunk) {
-                // the one run that contains the last non-empty slot: it may continue in the next chunk
+                // the run that contains the chunk's last record may continue in the next chunk
                 s_mcarry.sum = sum; s_mcarry.key = key; s_mcarry.cnt = cnt;
             } else {
                 const int slot = atomicAdd(&s_nlist, 1);
