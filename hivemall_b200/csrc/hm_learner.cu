@@ -145,8 +145,9 @@ struct hm_udtf {
     cudaStream_t compute = nullptr, copy = nullptr;
     cudaEvent_t copied_ev = nullptr, stage_ev[2] = {nullptr, nullptr};
     // model replica
-    float *w = nullptr, *state = nullptr;
-    int state_width = 0;
+    float *rec = nullptr;            // dims x rec_width floats: (w[, slot1[, slot2, unused]]) per feature
+    int rec_width = 1;
+    int state_width = 0;             // optimizer slots per feature (0, 1 or 2)
     int64_t t = 0;
     // scratch
     SortScratch sort;
@@ -221,7 +222,7 @@ hm_status train_rows(hm_udtf *u, const Chunk &c, int64_t row0, int64_t n_rows, c
     const int32_t B = u->cfg.mini_batch;
     const int key_bits = bits_for(u->cfg.dims);
     LinearArgs a;
-    a.cfg = u->cfg; a.w = u->w; a.state = u->state; a.state_width = u->state_width;
+    a.cfg = u->cfg; a.rec = u->rec; a.rec_width = u->rec_width;
     int64_t m0 = 0;
     while (m0 < n_mb) {
         // greedy block: <= kMaxSegs mini-batches and <= kBlockElemCap elements (at least one)
@@ -407,12 +408,9 @@ hm_status create_impl(const hm_config &cfg, int device, hm_udtf **out)
         HM_CUDA(cudaStreamCreateWithFlags(&u->copy, cudaStreamNonBlocking));
         u->L.stream = u->compute;
         u->state_width = cfg.opt == HM_OPT_SGD ? 0 : (cfg.opt == HM_OPT_ADAGRAD ? 1 : 2);
-        HM_CUDA(cudaMalloc(&u->w, (size_t)cfg.dims * sizeof(float)));
-        HM_CUDA(cudaMemsetAsync(u->w, 0, (size_t)cfg.dims * sizeof(float), u->compute));
-        if (u->state_width) {
-            HM_CUDA(cudaMalloc(&u->state, (size_t)cfg.dims * u->state_width * sizeof(float)));
-            HM_CUDA(cudaMemsetAsync(u->state, 0, (size_t)cfg.dims * u->state_width * sizeof(float), u->compute));
-        }
+        u->rec_width = u->state_width == 0 ? 1 : (u->state_width == 1 ? 2 : 4);
+        HM_CUDA(cudaMalloc(&u->rec, (size_t)cfg.dims * u->rec_width * sizeof(float)));
+        HM_CUDA(cudaMemsetAsync(u->rec, 0, (size_t)cfg.dims * u->rec_width * sizeof(float), u->compute));
         HM_CUDA(cudaMalloc(&u->d_bad, sizeof(uint32_t)));
         HM_CUDA(cudaMemsetAsync(u->d_bad, 0, sizeof(uint32_t), u->compute));
         HM_CUDA(cudaMalloc(&u->d_total, sizeof(int64_t)));
@@ -656,7 +654,7 @@ hm_status hm_udtf_close(hm_udtf *u, int64_t *n_model_rows)
         u->closed = true;
     }
     HM_TRY(check_bad(u));
-    HM_TRY(launch_export_count(u->L, u->exp, u->w, nullptr, u->cfg.dims, u->d_total));
+    HM_TRY(launch_export_count(u->L, u->exp, u->rec, u->rec_width, nullptr, u->cfg.dims, u->d_total));
     HM_CUDA(cudaMemcpyAsync(u->h_small, u->d_total, sizeof(int64_t), cudaMemcpyDeviceToHost, u->compute));
     HM_CUDA(cudaStreamSynchronize(u->compute));
     u->stats.d2h_bytes += 8;
@@ -673,7 +671,7 @@ hm_status hm_udtf_forward(hm_udtf *u, int32_t *feature, float *weight, float *, 
     if (cap < 0 || (cap > 0 && (!feature || !weight))) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "bad arguments to forward()");
     DeviceGuard g(u->device);
     // recount: the replica may have been averaged since close()
-    HM_TRY(launch_export_count(u->L, u->exp, u->w, nullptr, u->cfg.dims, u->d_total));
+    HM_TRY(launch_export_count(u->L, u->exp, u->rec, u->rec_width, nullptr, u->cfg.dims, u->d_total));
     HM_CUDA(cudaMemcpyAsync(u->h_small, u->d_total, sizeof(int64_t), cudaMemcpyDeviceToHost, u->compute));
     HM_CUDA(cudaStreamSynchronize(u->compute));
     const int64_t n = u->h_small[0];
@@ -682,7 +680,7 @@ hm_status hm_udtf_forward(hm_udtf *u, int32_t *feature, float *weight, float *, 
     if (n > 0) {
         HM_TRY(u->exp_feat.reserve((size_t)n * 4));
         HM_TRY(u->exp_weight.reserve((size_t)n * 4));
-        HM_TRY(launch_export_write(u->L, u->exp, u->w, nullptr, u->cfg.dims, u->exp_feat.as<int32_t>(),
+        HM_TRY(launch_export_write(u->L, u->exp, u->rec, u->rec_width, nullptr, u->cfg.dims, u->exp_feat.as<int32_t>(),
                                    u->exp_weight.as<float>()));
         HM_CUDA(cudaMemcpyAsync(feature, u->exp_feat.p, (size_t)n * 4, cudaMemcpyDeviceToHost, u->compute));
         HM_CUDA(cudaMemcpyAsync(weight, u->exp_weight.p, (size_t)n * 4, cudaMemcpyDeviceToHost, u->compute));
@@ -709,7 +707,7 @@ hm_status hm_udtf_destroy(hm_udtf *u)
     for (DevBuf *b : {&u->margin, &u->dloss, &u->contrib, &u->mb_gather, &u->exp_feat, &u->exp_weight, &u->tmp_a,
                       &u->tmp_b, &u->tmp_c, &u->tmp_d})
         b->release();
-    cudaFree(u->w); cudaFree(u->state); cudaFree(u->d_bad); cudaFree(u->d_total);
+    cudaFree(u->rec); cudaFree(u->d_bad); cudaFree(u->d_total);
     for (int i = 0; i < 2; i++) {
         if (u->h_stage[i]) cudaFreeHost(u->h_stage[i]);
         if (u->stage_ev[i]) cudaEventDestroy(u->stage_ev[i]);
@@ -725,42 +723,37 @@ hm_status hm_udtf_destroy(hm_udtf *u)
 
 // ---- replica access ----------------------------------------------------------------
 
-int hm_udtf_num_arrays(const hm_udtf *u) { return u ? (u->state ? 2 : 1) : 0; }
+int hm_udtf_num_arrays(const hm_udtf *u) { return u ? 1 : 0; }
 
 hm_status hm_udtf_array(hm_udtf *u, int which, const char **name, void **d_ptr, int64_t *n_floats, int32_t *width)
 {
     if (!u) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "NULL learner");
-    if (which == 0) {
-        if (name) *name = "w";
-        if (d_ptr) *d_ptr = u->w;
-        if (n_floats) *n_floats = u->cfg.dims;
-        if (width) *width = 1;
-        return HM_OK;
-    }
-    if (which == 1 && u->state) {
-        if (name) *name = "state";
-        if (d_ptr) *d_ptr = u->state;
-        if (n_floats) *n_floats = u->cfg.dims * u->state_width;
-        if (width) *width = u->state_width;
-        return HM_OK;
-    }
-    HM_FAIL(HM_ERR_INVALID_ARGUMENT, "array index %d out of range", which);
+    if (which != 0) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "array index %d out of range", which);
+    if (name) *name = "replica";
+    if (d_ptr) *d_ptr = u->rec;
+    if (n_floats) *n_floats = u->cfg.dims * u->rec_width;
+    if (width) *width = u->rec_width;
+    return HM_OK;
 }
 
+// Logical arrays inside the interleaved replica: 0 = "w" (dims floats), 1 = "state"
+// (dims x state_width floats, slots interleaved per feature).
 static hm_status array_copy(hm_udtf *u, int which, float *host, const float *host_in, int64_t n)
 {
-    void *d = nullptr;
-    int64_t len = 0;
-    HM_TRY(hm_udtf_array(u, which, nullptr, &d, &len, nullptr));
-    if (!host && !host_in) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "NULL host buffer");
+    if (which != 0 && !(which == 1 && u->state_width > 0)) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "array index %d out of range", which);
+    const int width = which == 0 ? 1 : u->state_width, off = which == 0 ? 0 : 1;
+    const int64_t len = u->cfg.dims * width;
     if (n != len) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "array %d holds %lld floats, caller passed %lld", which, (long long)len, (long long)n);
     DeviceGuard g(u->device);
     HM_CUDA(cudaStreamSynchronize(u->copy));
+    HM_TRY(u->tmp_a.reserve((size_t)n * 4));
     if (host) {
-        HM_CUDA(cudaMemcpyAsync(host, d, (size_t)n * 4, cudaMemcpyDeviceToHost, u->compute));
+        HM_TRY(launch_strided_copy(u->L, u->tmp_a.as<float>(), u->rec, u->cfg.dims, u->rec_width, off, width, true));
+        HM_CUDA(cudaMemcpyAsync(host, u->tmp_a.p, (size_t)n * 4, cudaMemcpyDeviceToHost, u->compute));
         u->stats.d2h_bytes += n * 4;
     } else {
-        HM_CUDA(cudaMemcpyAsync(d, host_in, (size_t)n * 4, cudaMemcpyHostToDevice, u->compute));
+        HM_CUDA(cudaMemcpyAsync(u->tmp_a.p, host_in, (size_t)n * 4, cudaMemcpyHostToDevice, u->compute));
+        HM_TRY(launch_strided_copy(u->L, u->tmp_a.as<float>(), u->rec, u->cfg.dims, u->rec_width, off, width, false));
         u->stats.h2d_bytes += n * 4;
     }
     HM_CUDA(cudaStreamSynchronize(u->compute));
@@ -808,8 +801,7 @@ hm_status hm_udtf_scale_replica(hm_udtf *u, float scale)
 {
     if (!u) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "NULL learner");
     DeviceGuard g(u->device);
-    HM_TRY(launch_scale(u->L, u->w, u->cfg.dims, scale));
-    if (u->state) HM_TRY(launch_scale(u->L, u->state, u->cfg.dims * u->state_width, scale));
+    HM_TRY(launch_scale(u->L, u->rec, u->cfg.dims * u->rec_width, scale));
     return HM_OK;
 }
 
@@ -821,7 +813,7 @@ hm_status hm_udtf_predict_device(hm_udtf *u, int64_t n_rows, const int64_t *d_ro
     if (!u) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "NULL learner");
     if (n_rows < 0 || (n_rows > 0 && (!d_rowptr || !d_out))) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "bad arguments to predict");
     DeviceGuard g(u->device);
-    return launch_predict_linear(u->L, u->w, u->cfg.dims, n_rows, d_rowptr, reinterpret_cast<const uint32_t *>(d_feature),
+    return launch_predict_linear(u->L, u->rec, u->rec_width, u->cfg.dims, n_rows, d_rowptr, reinterpret_cast<const uint32_t *>(d_feature),
                                  d_value, d_out, u->d_bad);
 }
 
@@ -845,7 +837,7 @@ hm_status hm_udtf_predict(hm_udtf *u, int64_t n_rows, const int64_t *rowptr, con
         HM_CUDA(cudaMemcpyAsync(u->tmp_b.p, feature + base, (size_t)nnz * 4, cudaMemcpyHostToDevice, u->compute));
         HM_CUDA(cudaMemcpyAsync(u->tmp_c.p, value + base, (size_t)nnz * 4, cudaMemcpyHostToDevice, u->compute));
     }
-    HM_TRY(launch_predict_linear(u->L, u->w, u->cfg.dims, n_rows, u->tmp_a.as<int64_t>(), u->tmp_b.as<uint32_t>(),
+    HM_TRY(launch_predict_linear(u->L, u->rec, u->rec_width, u->cfg.dims, n_rows, u->tmp_a.as<int64_t>(), u->tmp_b.as<uint32_t>(),
                                  u->tmp_c.as<float>(), u->tmp_d.as<float>(), u->d_bad));
     HM_CUDA(cudaMemcpyAsync(out, u->tmp_d.p, (size_t)n_rows * 4, cudaMemcpyDeviceToHost, u->compute));
     HM_CUDA(cudaStreamSynchronize(u->compute));   // also keeps `rp` alive long enough

@@ -60,7 +60,8 @@ __device__ __forceinline__ double warp_sum(double v)
 // ---- forward ---------------------------------------------------------------------
 
 struct FwdParams {
-    const float *w;
+    const float *w;          // weight of feature f is w[f * w_stride] (records are interleaved)
+    int32_t w_stride;
     const int64_t *rowptr;   // chunk row pointer (absolute element positions in the chunk)
     const uint32_t *feature;
     const float *value;
@@ -87,7 +88,7 @@ __global__ void __launch_bounds__(kFwdThreads) linear_forward_kernel(FwdParams P
         for (int64_t p = p0 + lane; p < p1; p += 32) {
             const uint32_t f = __ldcs(P.feature + p);
             const float x = __ldcs(P.value + p);
-            if (f < P.dims) acc += (double)__fmul_rn(__ldg(P.w + f), x);
+            if (f < P.dims) acc += (double)__fmul_rn(__ldg(P.w + (size_t)f * P.w_stride), x);
             else atomicOr(P.bad, 1u);
         }
         acc = warp_sum(acc);
@@ -116,8 +117,8 @@ constexpr int kUpdMaxGrid = 2048;     // CTAs per launch; beyond that each CTA w
 constexpr int kUpdMergeChunk = 1536;  // boundary records merged per shared-memory chunk
 
 struct UpdParams {
-    float *w;
-    float *state;
+    float *rec;              // replica: rec_width floats per feature = (w[, slot1[, slot2, unused]])
+    int32_t rec_width;       // 1, 2 or 4
     uint8_t *touched;        // nullable
     const uint32_t *skey;    // sorted features of the block
     const uint2 *spay;       // sorted (row in mini-batch, value bits)
@@ -127,7 +128,7 @@ struct UpdParams {
     uint32_t *done_counter;
     int32_t seg;
     uint32_t dims;
-    int32_t opt, reg, grad_norm, state_width;
+    int32_t opt, reg, grad_norm;
     float eta, adam_alpha, lambda, eps, rho, beta1, beta2, alpha, beta, lambda1, lambda2;
     double inv_rows;         // 1 / rows of the mini-batch, computed on the host in fp64
     int32_t n_active;        // CTAs launched (all own at least one tile unless the segment is empty)
@@ -136,19 +137,22 @@ struct UpdParams {
 // Replica record of one feature while it is being updated.
 struct Rec { float w, s1, s2; };
 
+// One 4-, 8- or 16-byte access per feature: weight and optimizer slots share a 32-byte sector,
+// so the forward kernel's gather has already pulled the whole record into L2.
 __device__ __forceinline__ Rec load_rec(const UpdParams &P, uint32_t j)
 {
-    Rec r; r.w = P.w[j]; r.s1 = 0.f; r.s2 = 0.f;
-    if (P.state_width == 1) r.s1 = P.state[j];
-    else if (P.state_width == 2) { const float2 s = reinterpret_cast<const float2 *>(P.state)[j]; r.s1 = s.x; r.s2 = s.y; }
+    Rec r; r.s1 = 0.f; r.s2 = 0.f;
+    if (P.rec_width == 4) { const float4 v = reinterpret_cast<const float4 *>(P.rec)[j]; r.w = v.x; r.s1 = v.y; r.s2 = v.z; }
+    else if (P.rec_width == 2) { const float2 v = reinterpret_cast<const float2 *>(P.rec)[j]; r.w = v.x; r.s1 = v.y; }
+    else r.w = P.rec[j];
     return r;
 }
 
 __device__ __forceinline__ void store_rec(const UpdParams &P, uint32_t j, const Rec &r)
 {
-    P.w[j] = r.w;
-    if (P.state_width == 1) P.state[j] = r.s1;
-    else if (P.state_width == 2) reinterpret_cast<float2 *>(P.state)[j] = make_float2(r.s1, r.s2);
+    if (P.rec_width == 4) reinterpret_cast<float4 *>(P.rec)[j] = make_float4(r.w, r.s1, r.s2, 0.f);
+    else if (P.rec_width == 2) reinterpret_cast<float2 *>(P.rec)[j] = make_float2(r.w, r.s1);
+    else P.rec[j] = r.w;
     if (P.touched) P.touched[j] = 1;
 }
 
@@ -516,13 +520,13 @@ __global__ void __launch_bounds__(kUpdThreads, 3) linear_update_kernel(UpdParams
 constexpr int kExpThreads = 256;
 constexpr int kExpTile = 4096;
 
-__device__ __forceinline__ bool emit(const float *w, const uint8_t *touched, int64_t j)
+__device__ __forceinline__ bool emit(const float *w, int stride, const uint8_t *touched, int64_t j)
 {
-    return touched ? touched[j] != 0 : w[j] != 0.0f;
+    return touched ? touched[j] != 0 : w[j * stride] != 0.0f;
 }
 
 __global__ void __launch_bounds__(kExpThreads)
-export_count_kernel(const float *__restrict__ w, const uint8_t *__restrict__ touched, int64_t dims,
+export_count_kernel(const float *__restrict__ w, int stride, const uint8_t *__restrict__ touched, int64_t dims,
                     uint32_t *__restrict__ counts)
 {
     __shared__ uint32_t s_tot;
@@ -532,7 +536,7 @@ export_count_kernel(const float *__restrict__ w, const uint8_t *__restrict__ tou
     uint32_t c = 0;
     for (int i = 0; i < kExpTile / kExpThreads; i++) {
         const int64_t j = j0 + i * kExpThreads + threadIdx.x;
-        if (j < dims && emit(w, touched, j)) c++;
+        if (j < dims && emit(w, stride, touched, j)) c++;
     }
     c = __reduce_add_sync(0xffffffffu, c);
     if ((threadIdx.x & 31) == 0 && c) atomicAdd(&s_tot, c);
@@ -567,7 +571,7 @@ __global__ void __launch_bounds__(1024) export_scan_kernel(uint32_t *__restrict_
 }
 
 __global__ void __launch_bounds__(kExpThreads)
-export_write_kernel(const float *__restrict__ w, const uint8_t *__restrict__ touched, int64_t dims,
+export_write_kernel(const float *__restrict__ w, int stride, const uint8_t *__restrict__ touched, int64_t dims,
                     const uint32_t *__restrict__ offsets, int32_t *__restrict__ feature, float *__restrict__ weight)
 {
     __shared__ uint32_t warp_tot[kExpThreads / 32];
@@ -579,7 +583,7 @@ export_write_kernel(const float *__restrict__ w, const uint8_t *__restrict__ tou
     uint32_t flags = 0;
     for (int i = 0; i < per; i++) {
         const int64_t j = j0 + (int64_t)threadIdx.x * per + i;
-        if (j < dims && emit(w, touched, j)) flags |= 1u << i;
+        if (j < dims && emit(w, stride, touched, j)) flags |= 1u << i;
     }
     const uint32_t c = __popc(flags);
     uint32_t inc = c;
@@ -594,7 +598,7 @@ export_write_kernel(const float *__restrict__ w, const uint8_t *__restrict__ tou
         if (flags & (1u << i)) {
             const int64_t j = j0 + (int64_t)threadIdx.x * per + i;
             feature[pos] = (int32_t)j;
-            weight[pos] = w[j];
+            weight[pos] = w[j * stride];
             pos++;
         }
     }
@@ -604,6 +608,19 @@ __global__ void scale_kernel(float *__restrict__ p, int64_t n, float scale)
 {
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
         p[i] = __fmul_rn(p[i], scale);
+}
+
+// dst[i*width + c] = src[i*stride + off + c]  (gather == true)  or the reverse (scatter)
+__global__ void strided_copy_kernel(float *__restrict__ dense, float *__restrict__ strided, int64_t n, int stride,
+                                    int off, int width, bool gather)
+{
+    const int64_t total = n * width;
+    for (int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; q < total; q += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t i = q / width;
+        const int c = (int)(q - i * width);
+        if (gather) dense[q] = strided[i * stride + off + c];
+        else strided[i * stride + off + c] = dense[q];
+    }
 }
 
 __global__ void fill_u32_kernel(uint32_t *__restrict__ p, int64_t n, uint32_t v)
@@ -628,7 +645,7 @@ hm_status launch_linear_forward(Launcher &L, const LinearArgs &a, const int64_t 
 {
     if (n_rows <= 0) return HM_OK;
     FwdParams P;
-    P.w = a.w; P.rowptr = d_rowptr; P.feature = d_feature; P.value = d_value; P.label = d_label;
+    P.w = a.rec; P.w_stride = a.rec_width; P.rowptr = d_rowptr; P.feature = d_feature; P.value = d_value; P.label = d_label;
     P.margin = d_margin; P.dloss = d_dloss;
     P.block_row0 = block_row0; P.row0 = row0; P.n_rows = n_rows;
     P.task = a.cfg.task; P.loss = a.cfg.loss; P.train = 1;
@@ -641,13 +658,13 @@ hm_status launch_linear_forward(Launcher &L, const LinearArgs &a, const int64_t 
     return HM_OK;
 }
 
-hm_status launch_predict_linear(Launcher &L, const float *w, int64_t dims, int64_t n_rows, const int64_t *d_rowptr,
+hm_status launch_predict_linear(Launcher &L, const float *w, int w_stride, int64_t dims, int64_t n_rows, const int64_t *d_rowptr,
                                 const uint32_t *d_feature, const float *d_value, float *d_out, uint32_t *d_bad)
 {
     if (n_rows <= 0) return HM_OK;
     if (n_rows > 0x7fffffff) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "predict: too many rows in one call");
     FwdParams P;
-    P.w = w; P.rowptr = d_rowptr; P.feature = d_feature; P.value = d_value; P.label = nullptr;
+    P.w = w; P.w_stride = w_stride; P.rowptr = d_rowptr; P.feature = d_feature; P.value = d_value; P.label = nullptr;
     P.margin = d_out; P.dloss = nullptr;
     P.block_row0 = 0; P.row0 = 0; P.n_rows = (int32_t)n_rows;
     P.task = 0; P.loss = 0; P.train = 0;
@@ -679,11 +696,11 @@ hm_status launch_linear_update(Launcher &L, const LinearArgs &a, const StepScala
                                const uint32_t *d_seg_off, int seg, const float *d_dloss, int64_t nnz_hint)
 {
     UpdParams P;
-    P.w = a.w; P.state = a.state; P.touched = nullptr;
+    P.rec = a.rec; P.rec_width = a.rec_width; P.touched = nullptr;
     P.skey = d_sorted_key; P.spay = d_sorted_pay; P.dloss = d_dloss; P.seg_off = d_seg_off;
     P.boundary = reinterpret_cast<Boundary *>(us.boundary); P.done_counter = us.done_counter;
     P.seg = seg; P.dims = (uint32_t)a.cfg.dims;
-    P.opt = a.cfg.opt; P.reg = a.cfg.reg; P.grad_norm = a.cfg.grad_norm; P.state_width = a.state_width;
+    P.opt = a.cfg.opt; P.reg = a.cfg.reg; P.grad_norm = a.cfg.grad_norm;
     P.eta = sc.eta; P.adam_alpha = sc.adam_alpha; P.lambda = a.cfg.lambda; P.eps = a.cfg.eps; P.rho = a.cfg.rho;
     P.beta1 = a.cfg.beta1; P.beta2 = a.cfg.beta2; P.alpha = a.cfg.alpha; P.beta = a.cfg.beta;
     P.lambda1 = a.cfg.lambda1; P.lambda2 = a.cfg.lambda2;
@@ -702,7 +719,7 @@ hm_status launch_linear_update(Launcher &L, const LinearArgs &a, const StepScala
     return HM_OK;
 }
 
-hm_status launch_export_count(Launcher &L, ExportScratch &es, const float *w, const uint8_t *touched,
+hm_status launch_export_count(Launcher &L, ExportScratch &es, const float *w, int w_stride, const uint8_t *touched,
                               int64_t dims, int64_t *d_total)
 {
     const int64_t ctas = (dims + kExpTile - 1) / kExpTile;
@@ -713,18 +730,18 @@ hm_status launch_export_count(Launcher &L, ExportScratch &es, const float *w, co
         es.cap = ctas + 1;
     }
     HM_LAUNCH(L, K_EXPORT, 4.0 * (double)dims,
-              (export_count_kernel<<<(unsigned)ctas, kExpThreads, 0, L.stream>>>(w, touched, dims, es.counts)));
+              (export_count_kernel<<<(unsigned)ctas, kExpThreads, 0, L.stream>>>(w, w_stride, touched, dims, es.counts)));
     HM_LAUNCH(L, K_EXPORT, 0.0, (export_scan_kernel<<<1, 1024, 0, L.stream>>>(es.counts, (int)ctas, d_total)));
     HM_CUDA(cudaGetLastError());
     return HM_OK;
 }
 
-hm_status launch_export_write(Launcher &L, ExportScratch &es, const float *w, const uint8_t *touched,
+hm_status launch_export_write(Launcher &L, ExportScratch &es, const float *w, int w_stride, const uint8_t *touched,
                               int64_t dims, int32_t *d_feature, float *d_weight)
 {
     const int64_t ctas = (dims + kExpTile - 1) / kExpTile;
     HM_LAUNCH(L, K_EXPORT, 4.0 * (double)dims,
-              (export_write_kernel<<<(unsigned)ctas, kExpThreads, 0, L.stream>>>(w, touched, dims, es.counts,
+              (export_write_kernel<<<(unsigned)ctas, kExpThreads, 0, L.stream>>>(w, w_stride, touched, dims, es.counts,
                                                                                  d_feature, d_weight)));
     HM_CUDA(cudaGetLastError());
     return HM_OK;
@@ -735,6 +752,17 @@ hm_status launch_scale(Launcher &L, float *p, int64_t n, float scale)
     if (n <= 0) return HM_OK;
     HM_LAUNCH(L, K_MISC, 8.0 * (double)n,
               (scale_kernel<<<grid_for((n + 1023) / 1024, 8), 256, 0, L.stream>>>(p, n, scale)));
+    HM_CUDA(cudaGetLastError());
+    return HM_OK;
+}
+
+hm_status launch_strided_copy(Launcher &L, float *dense, float *strided, int64_t n, int stride, int off, int width,
+                              bool gather)
+{
+    if (n <= 0 || width <= 0) return HM_OK;
+    HM_LAUNCH(L, K_MISC, 8.0 * (double)n * width,
+              (strided_copy_kernel<<<grid_for((n * width + 1023) / 1024, 8), 256, 0, L.stream>>>(dense, strided, n, stride,
+                                                                                                off, width, gather)));
     HM_CUDA(cudaGetLastError());
     return HM_OK;
 }
@@ -841,7 +869,7 @@ extern "C" hm_status hm_model_table_noalloc(const float *d_w, int64_t dims, int3
     const uint32_t cap32 = (uint32_t)std::min<int64_t>(cap, 0xffffffffLL);
     // counts[0 .. tiles) are all rewritten by the first kernel before anything reads them, and
     // *d_n_rows is written by the second: nothing left over from an earlier call is ever read.
-    export_count_kernel<<<tiles, kExpThreads, 0, st>>>(d_w, nullptr, dims, counts);
+    export_count_kernel<<<tiles, kExpThreads, 0, st>>>(d_w, 1, nullptr, dims, counts);
     export_scan_kernel<<<1, 1024, 0, st>>>(counts, tiles, d_n_rows);
     export_write_capped_kernel<<<tiles, kExpThreads, 0, st>>>(d_w, dims, counts, d_feature, d_weight, cap32);
     HM_CUDA(cudaGetLastError());

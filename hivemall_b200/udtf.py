@@ -253,23 +253,26 @@ class UDTF:
         p, n, _ = self.arrays()[name]
         return _DeviceArray(p, n, self)
 
-    def _array_index(self, name: str) -> int:
-        names = list(self.arrays())
-        if name not in names:
-            raise KeyError(f"no replica array {name!r}; this learner has {names}")
-        return names.index(name)
+    _LOGICAL = {"w": 0, "state": 1}
+
+    @property
+    def state_width(self) -> int:
+        """Optimizer slots per feature (0 SGD, 1 AdaGrad, 2 otherwise)."""
+        return {0: 0, 1: 1}.get(self.config.opt, 2)
 
     def array_to_host(self, name: str) -> np.ndarray:
-        """Copy a replica array to the host (tests, checkpoints)."""
-        _, n, _ = self.arrays()[name]
+        """Copy a logical model array to the host: "w" (dims floats) or "state"
+        (dims * state_width floats, a feature's slots adjacent)."""
+        n = self.config.dims * (1 if name == "w" else self.state_width)
         out = np.empty(n, dtype=np.float32)
-        check(self._lib.hm_udtf_read_array(self._h, self._array_index(name), _ptr(out), n))
+        if n:
+            check(self._lib.hm_udtf_read_array(self._h, self._LOGICAL[name], _ptr(out), n))
         return out
 
     def array_from_host(self, name: str, values) -> None:
-        """Overwrite a replica array from the host (warm start)."""
+        """Overwrite a logical model array from the host (warm start)."""
         values = np.ascontiguousarray(values, dtype=np.float32).reshape(-1)
-        check(self._lib.hm_udtf_write_array(self._h, self._array_index(name), _ptr(values), len(values)))
+        check(self._lib.hm_udtf_write_array(self._h, self._LOGICAL[name], _ptr(values), len(values)))
 
     def scale_replica(self, scale: float) -> None:
         check(self._lib.hm_udtf_scale_replica(self._h, scale))

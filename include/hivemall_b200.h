@@ -159,15 +159,18 @@ hm_status hm_udtf_destroy(hm_udtf *u);
 
 /* ---- model replica access (MIX averaging, warm start, tests) -------------- */
 
-/* Device arrays that make up the replica.  which = 0..n-1; name is one of
- * "w", "state" (optimizer slots, `width` floats interleaved per feature),
- * "V", "gV" (dims x factors), "w0" (1 float, then its accumulator).  The pointers stay valid
- * until destroy; call hm_udtf_sync before reading them from another stream. */
+/* Device memory that makes up the replica (what MIX averaging all-reduces).  which = 0..n-1.
+ * A linear learner has ONE array, "replica": `width` floats per feature, interleaved so that
+ * a feature's weight and optimizer slots share a memory sector: width 1 = (w) for SGD,
+ * 2 = (w, G) for AdaGrad, 4 = (w, slot1, slot2, unused) for AdaDelta (E[g^2], E[dx^2]),
+ * Adam (m, v) and FTRL (z, n).  n_floats = dims * width.  The pointer stays valid until
+ * destroy; call hm_udtf_sync before touching it from another stream. */
 int hm_udtf_num_arrays(const hm_udtf *u);
 hm_status hm_udtf_array(hm_udtf *u, int which, const char **name, void **d_ptr,
                         int64_t *n_floats, int32_t *width);
-/* Copy replica array `which` to / from a host buffer of n floats (n must equal the
- * array's length).  Synchronous.  write_array is the warm-start path. */
+/* Copy a LOGICAL array of the model to / from a host buffer of n floats: which = 0 is the
+ * dense weight vector w (n = dims); which = 1 is the optimizer state (n = dims * slots, the
+ * slots of a feature adjacent).  Synchronous.  write_array is the warm-start path. */
 hm_status hm_udtf_read_array(hm_udtf *u, int which, float *host, int64_t n);
 hm_status hm_udtf_write_array(hm_udtf *u, int which, const float *host, int64_t n);
 /* Update counter t (mini-batches applied so far); settable for warm start / MIX. */
@@ -205,8 +208,8 @@ hm_status hm_udtf_last_margins(hm_udtf *u, float *host, int64_t cap, int64_t *n)
  * the GPU that cannot absorb the device-wide stall cudaMalloc / cudaFree bring with them.
  * (hm_udtf_forward allocates its scratch and staging buffers.)
  *
- * Writes the model table of the dense weight array d_w[dims] (device memory, e.g. the "w"
- * pointer from hm_udtf_array after hm_udtf_sync): (feature, weight) for every weight != 0,
+ * Writes the model table of the dense weight array d_w[dims] (device memory, one float per
+ * feature): (feature, weight) for every weight != 0,
  * ascending feature order, into the caller's device arrays d_feature / d_weight of `cap`
  * rows, and the row count into *d_n_rows (device memory).  If *d_n_rows > cap only the
  * first `cap` rows were written.  All work is queued on `stream` (a cudaStream_t) of the

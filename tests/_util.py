@@ -43,7 +43,7 @@ def run_gpu_linear(function_name: str, options: str, data: synth.Csr, pushes=Non
     assert r0 == n
     u.close()
     w = u.array_to_host("w")
-    state = u.array_to_host("state") if "state" in u.arrays() else np.zeros(0, np.float32)
+    state = u.array_to_host("state")
     return u, w, state
 
 

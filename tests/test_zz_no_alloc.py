@@ -28,14 +28,14 @@ def _trained(seed, dims, rows):
 def _noalloc_table(u, cap):
     import torch
     dims = u.config.dims
-    w_ptr, n, _ = u.arrays()["w"]
-    assert n == dims
+    w_dev = torch.from_numpy(u.array_to_host("w")).cuda()      # dense weights, one float per feature
+    assert w_dev.numel() == dims
     feat = torch.full((cap,), -7, dtype=torch.int32, device="cuda")
     wt = torch.full((cap,), float("nan"), dtype=torch.float32, device="cuda")
     n_rows = torch.full((1,), -1, dtype=torch.int64, device="cuda")
     u.sync()
     torch.cuda.synchronize()
-    udtf.model_table_noalloc(w_ptr, dims, feat, wt, cap, n_rows, stream=0)
+    udtf.model_table_noalloc(w_dev, dims, feat, wt, cap, n_rows, stream=0)
     torch.cuda.synchronize()
     return int(n_rows.item()), feat.cpu().numpy(), wt.cpu().numpy()
 
