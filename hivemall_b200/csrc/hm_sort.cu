@@ -30,6 +30,11 @@ constexpr int kSortThreads = 256;
 constexpr int kSortWarps = kSortThreads / 32;
 constexpr int kSortItems = kSortTile / kSortThreads;  // 16
 constexpr int kRadix = 256;
+// the scatter kernel covers the same 4096-element tile with twice the threads: more warps per SM
+constexpr int kScatThreads = 512;
+constexpr int kScatWarps = kScatThreads / 32;
+constexpr int kScatItems = kSortTile / kScatThreads;  // 8
+constexpr int kScatCtasPerSm = 2;
 
 __global__ void seg_prep_kernel(const int64_t *__restrict__ rowptr, int64_t row0, int64_t n_rows,
                                 int32_t mini_batch, int n_segs, uint32_t *__restrict__ seg_off,
@@ -171,7 +176,7 @@ scan_tiles_kernel(uint32_t *__restrict__ tile_hist, const uint32_t *__restrict__
 constexpr size_t kScatterSmem = (size_t)kSortTile * 4 + (size_t)kSortTile * 8;   // keys + payloads
 
 template <bool FIRST>
-__global__ void __launch_bounds__(kSortThreads)
+__global__ void __launch_bounds__(kScatThreads, kScatCtasPerSm)
 sort_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint2 *__restrict__ pay_in,
                     const uint32_t *__restrict__ erow_in, const float *__restrict__ val_in,
                     uint32_t *__restrict__ keys_out, uint2 *__restrict__ pay_out,
@@ -182,9 +187,9 @@ sort_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint2 *__restric
     uint32_t *s_key = reinterpret_cast<uint32_t *>(dyn_smem);
     uint2 *s_pay = reinterpret_cast<uint2 *>(dyn_smem + (size_t)kSortTile * 4);
     __shared__ uint32_t s_off[kMaxSegs + 1], s_toff[kMaxSegs + 1];
-    __shared__ uint32_t wcnt[kSortWarps][kRadix];
-    __shared__ uint32_t dig_base[kRadix], gofs[kRadix], warp_tot[kSortWarps];
-    for (int s = threadIdx.x; s <= n_segs; s += kSortThreads) { s_off[s] = seg_off[s]; s_toff[s] = seg_tile_off[s]; }
+    __shared__ uint32_t wcnt[kScatWarps][kRadix];
+    __shared__ uint32_t dig_base[kRadix], gofs[kRadix], warp_tot[kRadix / 32];
+    for (int s = threadIdx.x; s <= n_segs; s += kScatThreads) { s_off[s] = seg_off[s]; s_toff[s] = seg_tile_off[s]; }
     __syncthreads();
     const uint32_t total = s_toff[n_segs];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -195,19 +200,18 @@ sort_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint2 *__restric
         const uint32_t e0 = s_off[seg] + tis * kSortTile;
         const uint32_t e1 = min(e0 + (uint32_t)kSortTile, s_off[seg + 1]);
         // warp-striped load: warp w owns tile positions [w*512, (w+1)*512), round i, lane
-        const uint32_t ew = e0 + warp * (32 * kSortItems) + lane;
-        uint32_t key[kSortItems], rank[kSortItems];
+        const uint32_t ew = e0 + warp * (32 * kScatItems) + lane;
+        uint32_t key[kScatItems], rank[kScatItems];
 #pragma unroll
-        for (int i = 0; i < kSortItems; i++) {
+        for (int i = 0; i < kScatItems; i++) {
             const uint32_t e = ew + i * 32;
             key[i] = e < e1 ? __ldcs(keys_in + e) : 0xffffffffu;
         }
-#pragma unroll
-        for (int w = 0; w < kSortWarps; w++) wcnt[w][threadIdx.x] = 0;
+        for (int q = threadIdx.x; q < kScatWarps * kRadix; q += kScatThreads) (&wcnt[0][0])[q] = 0;
         __syncthreads();
         // stable rank of every element among equal digits inside its warp
 #pragma unroll
-        for (int i = 0; i < kSortItems; i++) {
+        for (int i = 0; i < kScatItems; i++) {
             const bool valid = ew + i * 32 < e1;
             const uint32_t d = (key[i] >> shift) & (kRadix - 1);
             const uint32_t active = __ballot_sync(0xffffffffu, valid);
@@ -224,27 +228,33 @@ sort_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint2 *__restric
         __syncthreads();
         // per-digit: exclusive scan over warps, then exclusive scan over digits
         {
+            // the first kRadix threads own one digit each
             const int d = threadIdx.x;
+            const bool owner = d < kRadix;
             uint32_t run = 0;
+            if (owner) {
 #pragma unroll
-            for (int w = 0; w < kSortWarps; w++) { uint32_t c = wcnt[w][d]; wcnt[w][d] = run; run += c; }
+                for (int w = 0; w < kScatWarps; w++) { uint32_t c = wcnt[w][d]; wcnt[w][d] = run; run += c; }
+            }
             uint32_t inc = run;
 #pragma unroll
             for (int o = 1; o < 32; o <<= 1) { uint32_t v = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += v; }
-            if (lane == 31) warp_tot[warp] = inc;
+            if (lane == 31 && owner) warp_tot[warp] = inc;
             __syncthreads();
-            uint32_t wbase = 0;
+            if (owner) {
+                uint32_t wbase = 0;
 #pragma unroll
-            for (int w = 0; w < kSortWarps; w++) if (w < warp) wbase += warp_tot[w];
-            const uint32_t ex = wbase + inc - run;
-            dig_base[d] = ex;
-            gofs[d] = tile_hist[(size_t)s_toff[seg] * kRadix + (size_t)d * nt + tis] - ex;
+                for (int w = 0; w < kRadix / 32; w++) if (w < warp) wbase += warp_tot[w];
+                const uint32_t ex = wbase + inc - run;
+                dig_base[d] = ex;
+                gofs[d] = tile_hist[(size_t)s_toff[seg] * kRadix + (size_t)d * nt + tis] - ex;
+            }
         }
         __syncthreads();
         // place keys and payloads at their tile-local sorted position (payload loaded only now:
         // sixteen independent loads in flight per thread, no registers held across the ranking)
 #pragma unroll
-        for (int i = 0; i < kSortItems; i++) {
+        for (int i = 0; i < kScatItems; i++) {
             const uint32_t e = ew + i * 32;
             if (e < e1) {
                 const uint32_t d = (key[i] >> shift) & (kRadix - 1);
@@ -256,7 +266,7 @@ sort_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint2 *__restric
         }
         __syncthreads();
         const uint32_t n_tile = e1 - e0;
-        for (uint32_t p = threadIdx.x; p < n_tile; p += kSortThreads) {
+        for (uint32_t p = threadIdx.x; p < n_tile; p += kScatThreads) {
             const uint32_t k = s_key[p];
             const uint32_t g = gofs[(k >> shift) & (kRadix - 1)] + p;
             keys_out[g] = k;
@@ -361,12 +371,12 @@ hm_status launch_segmented_sort(Launcher &L, SortScratch &s, const uint32_t *d_f
                       s.tile_hist, s.row_sum, s.seg_tile_off, n_segs)));
         if (p == 0)
             HM_LAUNCH(L, K_SORT_SCATTER, 24.0 * (double)n_elems,
-                      (sort_scatter_kernel<true><<<grid, kSortThreads, kScatterSmem, L.stream>>>(
+                      (sort_scatter_kernel<true><<<grid, kScatThreads, kScatterSmem, L.stream>>>(
                           kin, pin, s.erow, d_value_block, kout, pout, s.seg_off, s.seg_tile_off, n_segs, shift,
                           s.tile_hist)));
         else
             HM_LAUNCH(L, K_SORT_SCATTER, 24.0 * (double)n_elems,
-                      (sort_scatter_kernel<false><<<grid, kSortThreads, kScatterSmem, L.stream>>>(
+                      (sort_scatter_kernel<false><<<grid, kScatThreads, kScatterSmem, L.stream>>>(
                           kin, pin, nullptr, nullptr, kout, pout, s.seg_off, s.seg_tile_off, n_segs, shift,
                           s.tile_hist)));
     }
