@@ -194,18 +194,31 @@ sort_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint2 *__restric
     const uint32_t total = s_toff[n_segs];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint32_t lt_mask = (1u << lane) - 1u;
-    for (uint32_t tile = blockIdx.x; tile < total; tile += gridDim.x) {
-        const int seg = find_seg(s_toff, n_segs, tile);
-        const uint32_t tis = tile - s_toff[seg], nt = s_toff[seg + 1] - s_toff[seg];
-        const uint32_t e0 = s_off[seg] + tis * kSortTile;
-        const uint32_t e1 = min(e0 + (uint32_t)kSortTile, s_off[seg + 1]);
-        // warp-striped load: warp w owns tile positions [w*512, (w+1)*512), round i, lane
+    // keys of the first tile; later tiles are prefetched while the previous one is written out
+    uint32_t key[kScatItems], rank[kScatItems];
+    uint32_t tile = blockIdx.x;
+    int seg = 0; uint32_t tis = 0, nt = 0, e0 = 0, e1 = 0;
+    if (tile < total) {
+        seg = find_seg(s_toff, n_segs, tile);
+        tis = tile - s_toff[seg]; nt = s_toff[seg + 1] - s_toff[seg];
+        e0 = s_off[seg] + tis * kSortTile;
+        e1 = min(e0 + (uint32_t)kSortTile, s_off[seg + 1]);
+#pragma unroll
+        for (int i = 0; i < kScatItems; i++) {
+            const uint32_t e = e0 + warp * (32 * kScatItems) + lane + i * 32;
+            key[i] = e < e1 ? __ldcs(keys_in + e) : 0xffffffffu;
+        }
+    }
+    for (; tile < total; tile += gridDim.x) {
+        // warp-striped: warp w owns tile positions [w*256, (w+1)*256), round i, lane
         const uint32_t ew = e0 + warp * (32 * kScatItems) + lane;
-        uint32_t key[kScatItems], rank[kScatItems];
+        // payloads are requested now and consumed after the ranking
+        uint2 pay[kScatItems];
 #pragma unroll
         for (int i = 0; i < kScatItems; i++) {
             const uint32_t e = ew + i * 32;
-            key[i] = e < e1 ? __ldcs(keys_in + e) : 0xffffffffu;
+            if (e < e1) pay[i] = FIRST ? make_uint2(__ldcs(erow_in + e), __float_as_uint(__ldcs(val_in + e)))
+                                       : __ldcs(pay_in + e);
         }
         for (int q = threadIdx.x; q < kScatWarps * kRadix; q += kScatThreads) (&wcnt[0][0])[q] = 0;
         __syncthreads();
@@ -260,12 +273,25 @@ sort_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint2 *__restric
                 const uint32_t d = (key[i] >> shift) & (kRadix - 1);
                 const uint32_t pos = dig_base[d] + wcnt[warp][d] + rank[i];
                 s_key[pos] = key[i];
-                s_pay[pos] = FIRST ? make_uint2(__ldcs(erow_in + e), __float_as_uint(__ldcs(val_in + e)))
-                                   : __ldcs(pay_in + e);
+                s_pay[pos] = pay[i];
             }
         }
         __syncthreads();
         const uint32_t n_tile = e1 - e0;
+        // next tile's coordinates and keys (the key registers are free from here on)
+        const uint32_t next = tile + gridDim.x;
+        int nseg = 0; uint32_t ntis = 0, nnt = 0, ne0 = 0, ne1 = 0;
+        if (next < total) {
+            nseg = find_seg(s_toff, n_segs, next);
+            ntis = next - s_toff[nseg]; nnt = s_toff[nseg + 1] - s_toff[nseg];
+            ne0 = s_off[nseg] + ntis * kSortTile;
+            ne1 = min(ne0 + (uint32_t)kSortTile, s_off[nseg + 1]);
+#pragma unroll
+            for (int i = 0; i < kScatItems; i++) {
+                const uint32_t e = ne0 + warp * (32 * kScatItems) + lane + i * 32;
+                key[i] = e < ne1 ? __ldcs(keys_in + e) : 0xffffffffu;
+            }
+        }
         for (uint32_t p = threadIdx.x; p < n_tile; p += kScatThreads) {
             const uint32_t k = s_key[p];
             const uint32_t g = gofs[(k >> shift) & (kRadix - 1)] + p;
@@ -273,6 +299,7 @@ sort_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint2 *__restric
             pay_out[g] = s_pay[p];
         }
         __syncthreads();
+        seg = nseg; tis = ntis; nt = nnt; e0 = ne0; e1 = ne1;
     }
 }
 
