@@ -110,12 +110,19 @@ struct SegRec {           // a (feature, partial sum) record; cnt == 0 means emp
     double sum;
     uint32_t key, cnt;
 };
-struct Boundary { SegRec first, last; };
-static_assert(sizeof(SegRec) == 16, "the merge reads boundary records as 16-byte vectors");
+static_assert(sizeof(SegRec) == 16, "boundary records travel as 16-byte vectors");
 
-constexpr int kUpdMaxGrid = 2048;     // CTAs per launch; beyond that each CTA walks consecutive tiles
-constexpr int kUpdMergeChunk = 1536;  // boundary records merged per shared-memory chunk
+constexpr int kUpdMaxGrid = 1536;     // CTAs per launch; beyond that each CTA walks consecutive tiles
 
+// Segments that really straddle CTAs are the hot features' long runs.  Each CTA leaves two
+// 16-byte records: `first` = its piece of a segment that began in an earlier CTA (or the
+// whole range, when the range lies inside one segment), `last` = its trailing segment when
+// that one continues into the next CTA.  Pieces of one segment therefore sit in CONSECUTIVE
+// CTAs: last[c], first[c+1], first[c+2], ... -- the last CTA to finish sums them in that order.
+struct BoundaryRecs {
+    uint4 *first, *last;   // SegRec as bits, one per CTA
+    uint32_t *ticket;
+};
 struct UpdParams {
     float *rec;              // replica: rec_width floats per feature = (w[, slot1[, slot2, unused]])
     int32_t rec_width;       // 1, 2 or 4
@@ -124,8 +131,7 @@ struct UpdParams {
     const uint2 *spay;       // sorted (row in mini-batch, value bits)
     const float *dloss;      // dloss of every row of this mini-batch
     const uint32_t *seg_off;
-    Boundary *boundary;
-    uint32_t *done_counter;
+    BoundaryRecs br;
     int32_t seg;
     uint32_t dims;
     int32_t opt, reg, grad_norm;
@@ -238,7 +244,7 @@ constexpr int kUpdList = kUpdTile + 8;
 constexpr int kUpdBatch = 4;         // independent record updates in flight per thread
 // shared memory is used twice: tile + closed-segment list while streaming, record buffers in the merge
 constexpr size_t kUpdSmemTile = (size_t)kUpdPadded * 8 + (size_t)kUpdList * 8;
-constexpr size_t kUpdSmemMerge = (size_t)kUpdMergeChunk * 24;
+constexpr size_t kUpdSmemMerge = (size_t)kUpdMaxGrid * 24;   // staged `first` records + output list
 constexpr size_t kUpdSmem = kUpdSmemTile > kUpdSmemMerge ? kUpdSmemTile : kUpdSmemMerge;
 
 // Apply the optimizer to list entries [0, n): kUpdBatch independent read-modify-writes per thread
@@ -265,6 +271,11 @@ __device__ __forceinline__ void apply_list(const UpdParams &P, const uint32_t *l
     }
 }
 
+__device__ __forceinline__ uint4 rec_bits(const SegRec &r)
+{
+    return make_uint4((uint32_t)__double2loint(r.sum), (uint32_t)__double2hiint(r.sum), r.key, r.cnt);
+}
+
 __global__ void __launch_bounds__(kUpdThreads, 3) linear_update_kernel(UpdParams P)
 {
     __shared__ __align__(16) unsigned char smem_raw[kUpdSmem];
@@ -274,8 +285,7 @@ __global__ void __launch_bounds__(kUpdThreads, 3) linear_update_kernel(UpdParams
     float *l_g = reinterpret_cast<float *>(smem_raw + (size_t)kUpdPadded * 8 + (size_t)kUpdList * 4);
     __shared__ Scan s_warp[kUpdThreads / 32];
     __shared__ SegRec s_carry;       // open trailing segment of the previous tile
-    __shared__ SegRec s_first;
-    __shared__ SegRec s_mcarry;
+    __shared__ SegRec s_first;       // the CTA's piece of a segment that began before its range
     __shared__ uint32_t s_carry_open;
     __shared__ uint32_t s_is_last;
     __shared__ uint32_t s_edge[2];   // does the CTA's range start / end on a true segment boundary?
@@ -290,9 +300,7 @@ __global__ void __launch_bounds__(kUpdThreads, 3) linear_update_kernel(UpdParams
     const uint32_t lo = min(n, blockIdx.x * tiles_per_cta * kUpdTile);
     const uint32_t hi = min(n, lo + tiles_per_cta * kUpdTile);
 
-    SegRec first;                    // this thread's candidate for the CTA's left-open segment
-    first.cnt = 0; first.sum = 0; first.key = 0;
-    if (tid == 0) { s_carry.cnt = 0; s_carry_open = 0; s_first.cnt = 0; }
+    if (tid == 0) { s_carry.cnt = 0; s_carry_open = 0; s_first.cnt = 0; s_is_last = 0; }
     // Peek at the neighbours of the range: a first segment that really starts at `lo`, or a last
     // segment that really ends at `hi`, is complete inside this CTA and never reaches the merge.
     // The four loads are issued here and only consumed after the first tile's barrier, so they
@@ -303,6 +311,8 @@ __global__ void __launch_bounds__(kUpdThreads, 3) linear_update_kernel(UpdParams
         s_edge[0] = lo == 0 || a0 != a1;
         s_edge[1] = hi == n || b0 != b1;
     }
+    if (lo >= hi) __syncthreads();   // (the tile loop below has its own barriers)
+
     for (uint32_t t0 = lo; t0 < hi; t0 += kUpdTile) {
         const int n_tile = (int)min((uint32_t)kUpdTile, hi - t0);
         // ---- coalesced striped load; contribution = dloss[row] * value (fp32 product)
@@ -388,7 +398,7 @@ __global__ void __launch_bounds__(kUpdThreads, 3) linear_update_kernel(UpdParams
         int slot = (int)cin.k;
         if (tid == 0 && edge_continues) { run = carry.sum; cnt = carry.cnt; }
         if (tid == 0 && carry.cnt != 0 && !edge_continues) {
-            if (carry_open) first = carry;
+            if (carry_open) s_first = carry;
             else { l_key[slot] = carry.key; l_g[slot] = grad_of(P, carry.sum, carry.cnt); slot++; }
         }
 #pragma unroll
@@ -402,8 +412,8 @@ __global__ void __launch_bounds__(kUpdThreads, 3) linear_update_kernel(UpdParams
                 const bool open = !seen_head && edge_open;
                 const bool closes = q < n_tile - 1 ? kk[i + 1] != kk[i] : close_tail;
                 if (closes) {
-                    if (open) {
-                        first.sum = run; first.key = kk[i]; first.cnt = cnt;
+                    if (open) {     // at most one such segment per CTA
+                        s_first.sum = run; s_first.key = kk[i]; s_first.cnt = cnt;
                         l_key[slot] = 0xffffffffu; l_g[slot] = 0.f;   // placeholder: skipped by apply_list
                     } else {
                         l_key[slot] = kk[i]; l_g[slot] = grad_of(P, run, cnt);
@@ -417,102 +427,67 @@ __global__ void __launch_bounds__(kUpdThreads, 3) linear_update_kernel(UpdParams
             }
         }
         __syncthreads();
+        // ---- after the last tile the CTA's boundary pieces are final: publish them and take the
+        // completion ticket now, so that both round trips overlap the optimizer step below
+        if (last_tile && tid == 0) {
+            const uint4 none = make_uint4(0u, 0u, 0u, 0u);
+            const bool whole = s_carry.cnt != 0 && s_carry_open;     // the range lies inside one segment
+            P.br.first[blockIdx.x] = whole ? rec_bits(s_carry) : (s_first.cnt != 0 ? rec_bits(s_first) : none);
+            P.br.last[blockIdx.x] = (!whole && s_carry.cnt != 0) ? rec_bits(s_carry) : none;
+            __threadfence();
+            s_is_last = atomicAdd(P.br.ticket, 1u) == gridDim.x - 1;
+        }
         // ---- optimizer step for the listed features, latencies overlapped
         apply_list(P, l_key, l_g, s_nlist, tid);
         __syncthreads();
     }
-    // ---- publish this CTA's boundary records (at most one thread holds a valid `first`)
-    if (first.cnt != 0) s_first = first;
-    __syncthreads();
-    if (tid == 0) {
-        Boundary b;
-        b.first = s_first;
-        b.last.cnt = 0; b.last.sum = 0; b.last.key = 0;
-        if (lo < hi && s_carry.cnt != 0) {
-            if (s_carry_open) b.first = s_carry;   // the whole CTA range lies inside one segment
-            else b.last = s_carry;
-        }
-        P.boundary[blockIdx.x] = b;
-        __threadfence();
-        const uint32_t ticket = atomicAdd(P.done_counter, 1u);
-        s_is_last = ticket == gridDim.x - 1;
-    }
-    __syncthreads();
-    if (!s_is_last) return;
-    // ---- the last CTA to finish merges the boundary records in CTA order.  Records are staged
-    // in shared memory a chunk at a time; a run of equal features that reaches the end of a chunk
-    // is carried into the next one as its slot 0.  Completed runs go to a list and are applied
-    // with the same batched step as above.
-    __threadfence();
-    const int n_rec = 2 * P.n_active;
-    double *m_sum = reinterpret_cast<double *>(smem_raw);
-    uint32_t *m_key = reinterpret_cast<uint32_t *>(smem_raw + (size_t)kUpdMergeChunk * 8);
-    uint32_t *m_cnt = m_key + kUpdMergeChunk;
-    uint32_t *ml_key = m_cnt + kUpdMergeChunk;
-    float *ml_g = reinterpret_cast<float *>(ml_key + kUpdMergeChunk);
-    const uint4 *rec4 = reinterpret_cast<const uint4 *>(P.boundary);   // SegRec = {double sum; u32 key; u32 cnt}
-    if (tid == 0) s_mcarry.cnt = 0;
-    __syncthreads();
-    __shared__ int s_wsum[kUpdThreads / 32];
-    constexpr int kPer = (kUpdMergeChunk + kUpdThreads - 1) / kUpdThreads;   // records per thread and chunk
-    for (int c0 = 0; c0 < n_rec; c0 += kUpdMergeChunk - 1) {
-        const int n_in = min(kUpdMergeChunk - 1, n_rec - c0);
-        const bool last_chunk = c0 + n_in >= n_rec;
-        // Each thread takes kPer CONSECUTIVE records (one 16-byte L2 load each, all in flight
-        // together), keeps the non-empty ones, and an exclusive block scan of the counts gives
-        // every survivor its place: the compact list keeps CTA order.  Slot 0 is the carried run.
-        uint4 raw[kPer];
-        int mine = 0;
-#pragma unroll
-        for (int u = 0; u < kPer; u++) {
-            const int i = tid * kPer + u;
-            raw[u] = i < n_in ? __ldcg(rec4 + c0 + i) : make_uint4(0u, 0u, 0u, 0u);
-        }
-#pragma unroll
-        for (int u = 0; u < kPer; u++) mine += raw[u].w != 0u;
-        int inc = mine;
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) { const int v = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += v; }
-        if (lane == 31) s_wsum[warp] = inc;
-        const bool have_carry = s_mcarry.cnt != 0;
-        __syncthreads();
-        int pos = (have_carry ? 1 : 0) + inc - mine;
-        for (int w2 = 0; w2 < warp; w2++) pos += s_wsum[w2];
-        int n_slots = have_carry ? 1 : 0;
-        for (int w2 = 0; w2 < kUpdThreads / 32; w2++) n_slots += s_wsum[w2];
+    if (lo >= hi) {   // a CTA without elements leaves empty records and still takes its ticket
         if (tid == 0) {
-            if (have_carry) { m_sum[0] = s_mcarry.sum; m_key[0] = s_mcarry.key; m_cnt[0] = s_mcarry.cnt; }
-            s_nlist = 0;
+            P.br.first[blockIdx.x] = make_uint4(0u, 0u, 0u, 0u);
+            P.br.last[blockIdx.x] = make_uint4(0u, 0u, 0u, 0u);
+            __threadfence();
+            s_is_last = atomicAdd(P.br.ticket, 1u) == gridDim.x - 1;
         }
-#pragma unroll
-        for (int u = 0; u < kPer; u++)
-            if (raw[u].w != 0u) {
-                m_sum[pos] = __hiloint2double((int)raw[u].y, (int)raw[u].x);
-                m_key[pos] = raw[u].z; m_cnt[pos] = raw[u].w;
-                pos++;
-            }
-        __syncthreads();
-        if (tid == 0) s_mcarry.cnt = 0;   // re-set below by the run that reaches the end of this chunk
-        __syncthreads();
-        for (int i = tid; i < n_slots; i += kUpdThreads) {
-            const uint32_t key = m_key[i];
-            if (i > 0 && m_key[i - 1] == key) continue;      // not the start of a run
-            double sum = m_sum[i]; uint32_t cnt = m_cnt[i];
-            int j = i + 1;
-            for (; j < n_slots && m_key[j] == key; j++) { sum += m_sum[j]; cnt += m_cnt[j]; }
-            if (j >= n_slots && !last_chunk) {
-                // the run that contains the chunk's last record may continue in the next chunk
-                s_mcarry.sum = sum; s_mcarry.key = key; s_mcarry.cnt = cnt;
-            } else {
-                const int slot = atomicAdd(&s_nlist, 1);
-                ml_key[slot] = key; ml_g[slot] = grad_of(P, sum, cnt);
-            }
-        }
-        __syncthreads();
-        apply_list(P, ml_key, ml_g, s_nlist, tid);
         __syncthreads();
     }
-    if (tid == 0) *P.done_counter = 0;   // ready for the next launch on this stream
+    if (!s_is_last) return;
+
+    // ---- the last CTA to finish resolves the straddling segments.  `first` records are staged
+    // in shared memory; the thread that owns CTA c starts a run at last[c] and walks first[c+1],
+    // first[c+2], ... while the feature matches (fixed order, fp64).  No sorting is needed.
+    __threadfence();
+    const int G = (int)gridDim.x;
+    uint4 *f_sm = reinterpret_cast<uint4 *>(smem_raw);
+    uint32_t *ml_key = reinterpret_cast<uint32_t *>(smem_raw + (size_t)kUpdMaxGrid * 16);
+    float *ml_g = reinterpret_cast<float *>(ml_key + kUpdMaxGrid);
+    constexpr int kPer = (kUpdMaxGrid + kUpdThreads - 1) / kUpdThreads;
+    uint4 mylast[kPer];
+    if (tid == 0) s_nlist = 0;
+#pragma unroll
+    for (int u = 0; u < kPer; u++) {
+        const int c = u * kUpdThreads + tid;
+        if (c < G) { f_sm[c] = __ldcg(P.br.first + c); mylast[u] = __ldcg(P.br.last + c); }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int u = 0; u < kPer; u++) {
+        const int c = u * kUpdThreads + tid;
+        if (c < G && mylast[u].w != 0u) {
+            const uint32_t key = mylast[u].z;
+            double sum = __hiloint2double((int)mylast[u].y, (int)mylast[u].x);
+            uint32_t cnt = mylast[u].w;
+            for (int j = c + 1; j < G; j++) {
+                const uint4 f = f_sm[j];
+                if (f.w == 0u || f.z != key) break;
+                sum += __hiloint2double((int)f.y, (int)f.x); cnt += f.w;
+            }
+            const int sl = atomicAdd(&s_nlist, 1);     // distinct features: list order is irrelevant
+            ml_key[sl] = key; ml_g[sl] = grad_of(P, sum, cnt);
+        }
+    }
+    __syncthreads();
+    apply_list(P, ml_key, ml_g, s_nlist, tid);
+    if (tid == 0) *P.br.ticket = 0;   // ready for the next launch on this stream
 }
 
 // ---- model table --------------------------------------------------------------------
@@ -679,15 +654,17 @@ hm_status update_scratch_reserve(UpdateScratch &u)
 {
     if (u.boundary) return HM_OK;
     u.grid = kUpdMaxGrid;
-    HM_CUDA(cudaMalloc(&u.boundary, (size_t)u.grid * sizeof(Boundary)));
-    HM_CUDA(cudaMalloc(&u.done_counter, sizeof(uint32_t)));
-    HM_CUDA(cudaMemset(u.done_counter, 0, sizeof(uint32_t)));
+    // [ first: grid x 16 B | last: grid x 16 B | ticket ]
+    const size_t bytes = (size_t)2 * u.grid * 16 + 16;
+    HM_CUDA(cudaMalloc(&u.boundary, bytes));
+    HM_CUDA(cudaMemset(u.boundary, 0, bytes));
+    u.done_counter = reinterpret_cast<uint32_t *>(static_cast<char *>(u.boundary) + (size_t)2 * u.grid * 16);
     return HM_OK;
 }
 
 void update_scratch_free(UpdateScratch &u)
 {
-    cudaFree(u.boundary); cudaFree(u.done_counter);
+    cudaFree(u.boundary);
     u.boundary = nullptr; u.done_counter = nullptr; u.grid = 0;
 }
 
@@ -698,7 +675,9 @@ hm_status launch_linear_update(Launcher &L, const LinearArgs &a, const StepScala
     UpdParams P;
     P.rec = a.rec; P.rec_width = a.rec_width; P.touched = nullptr;
     P.skey = d_sorted_key; P.spay = d_sorted_pay; P.dloss = d_dloss; P.seg_off = d_seg_off;
-    P.boundary = reinterpret_cast<Boundary *>(us.boundary); P.done_counter = us.done_counter;
+    P.br.first = reinterpret_cast<uint4 *>(us.boundary);
+    P.br.last = P.br.first + us.grid;
+    P.br.ticket = us.done_counter;
     P.seg = seg; P.dims = (uint32_t)a.cfg.dims;
     P.opt = a.cfg.opt; P.reg = a.cfg.reg; P.grad_norm = a.cfg.grad_norm;
     P.eta = sc.eta; P.adam_alpha = sc.adam_alpha; P.lambda = a.cfg.lambda; P.eps = a.cfg.eps; P.rho = a.cfg.rho;
