@@ -1,0 +1,571 @@
+// hm_fm.cu -- kernels of the factorization-machine learner (train_fm).
+//
+// Stands in for FactorizationMachineUDTF, which BASELINE.json's north_star names ("train_fm's
+// FactorizationMachineUDTF", "FM O(k*nnz) pairwise term", model rows carrying Vif).  The
+// reference mount has no source (README.md:20-22); the model is Rendle's published FM and the
+// arithmetic is DESIGN.md 3.8 (fp32 products, fp64 sums), restated independently in
+// oracle/hm_oracle.c.
+//
+//   fm_forward_kernel  warp per row, lanes over factors: S_f = sum_j v_jf x_j accumulated in
+//                      ROW ORDER in fp64 (bit-identical to a sequential loop), y_hat, dloss,
+//                      and the table S32[row][f] the update needs
+//   fm_update_kernel   warp per 1024-element chunk of the feature-sorted mini-batch, lanes over
+//                      factors, elements taken in order: per-feature sums A1, A2, GS_f in fp64;
+//                      finished features wait in a shared-memory list and are stepped 16 at a
+//                      time so their factor-row loads overlap
+//   fm_merge_kernel    features whose run straddles chunks (hot features): pieces sit in
+//                      consecutive chunks, one warp walks them in order; one extra CTA sums dloss
+//                      for the w0 step
+//
+// Replica layout: w0rec = (w0, acc); wrec[j] = (w_j[, acc]); vrec[j] = (V_j0..V_j,k-1[, acc_0..acc_k-1]).
+// With k = 16 and AdaGrad a feature's factor record is exactly one 128-byte line.
+#include "hm_internal.h"
+#include <algorithm>
+
+namespace hm {
+
+namespace {
+
+constexpr int kFmChunk = 1024;      // sorted elements per warp
+constexpr int kFmBatch = 16;        // elements (and pending feature steps) per inner batch
+constexpr int kFmWarps = 4;         // warps per CTA in update / merge
+
+__device__ __forceinline__ uint32_t fmix32(uint32_t h)
+{
+    h ^= h >> 16; h *= 0x85ebca6bu;
+    h ^= h >> 13; h *= 0xc2b2ae35u;
+    h ^= h >> 16;
+    return h;
+}
+
+__device__ __forceinline__ float hm_exp(float x)   // DESIGN.md 3.2, same sequence as hm_linear.cu
+{
+    x = fminf(fmaxf(x, -87.0f), 88.0f);
+    const float n = rintf(__fmul_rn(x, 1.44269504f));
+    float r = __fsub_rn(x, __fmul_rn(n, 0.693359375f));
+    r = __fsub_rn(r, __fmul_rn(n, -2.12194440e-4f));
+    float p = 1.3888889e-3f;
+    p = __fadd_rn(__fmul_rn(p, r), 8.3333333e-3f);
+    p = __fadd_rn(__fmul_rn(p, r), 4.1666667e-2f);
+    p = __fadd_rn(__fmul_rn(p, r), 1.6666667e-1f);
+    p = __fadd_rn(__fmul_rn(p, r), 0.5f);
+    p = __fadd_rn(__fmul_rn(p, r), 1.0f);
+    p = __fadd_rn(__fmul_rn(p, r), 1.0f);
+    return __fmul_rn(p, __int_as_float(((int)n + 127) << 23));
+}
+
+__device__ __forceinline__ double warp_sum(double v)
+{
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+__global__ void fm_init_v_kernel(float *__restrict__ vrec, int64_t dims, int k, int vw, float sigma, uint32_t seed)
+{
+    const int64_t n = dims * k;
+    for (int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; q < n; q += (int64_t)gridDim.x * blockDim.x) {
+        const uint32_t h = fmix32((uint32_t)q * 0x9E3779B1u + seed);
+        const float u = __fmul_rn(__fsub_rn(__fmul_rn((float)(h >> 8), 5.9604644775390625e-08f), 0.5f), 2.0f);
+        vrec[(q / k) * vw + (q % k)] = __fmul_rn(sigma, u);
+    }
+}
+
+// ---- forward ---------------------------------------------------------------------
+
+struct FmFwdParams {
+    const float *w0rec, *wrec, *vrec;
+    int32_t ww, vw, k;
+    const int64_t *rowptr;
+    const uint32_t *feature;
+    const float *value;
+    const float *label;
+    float *margin;       // y_hat, indexed by row of the block (prediction: row of the call)
+    float *dloss;        // indexed by row of the mini-batch
+    float *stab;         // S32[row of the mini-batch][k]
+    int64_t block_row0, row0;
+    int32_t n_rows, classification, train;
+    uint32_t dims;
+    uint32_t *bad;
+};
+
+template <int NF>
+__global__ void __launch_bounds__(256) fm_forward_kernel(FmFwdParams P)
+{
+    const int lane = threadIdx.x & 31;
+    const int k = P.k;
+    const float w0 = P.w0rec[0];
+    for (int r = blockIdx.x * 8 + (threadIdx.x >> 5); r < P.n_rows; r += gridDim.x * 8) {
+        const int64_t row = P.row0 + r;
+        const int64_t p0 = P.rowptr[row], p1 = P.rowptr[row + 1];
+        // linear term: lanes over elements, fp64 tree
+        double lin = 0.0;
+        for (int64_t p = p0 + lane; p < p1; p += 32) {
+            const uint32_t f = P.feature[p];
+            if (f < P.dims) lin += (double)__fmul_rn(__ldg(P.wrec + (size_t)f * P.ww), P.value[p]);
+            else atomicOr(P.bad, 1u);
+        }
+        lin = warp_sum(lin);
+        // factor sums: lanes over f, elements in row order (4 factor-row loads in flight)
+        double S[NF], Q[NF];
+#pragma unroll
+        for (int q = 0; q < NF; q++) { S[q] = 0.0; Q[q] = 0.0; }
+        for (int64_t p = p0; p < p1; p += 4) {
+            float v[4][NF], x[4];
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+                const bool ok = p + u < p1;
+                const uint32_t f = ok ? P.feature[p + u] : 0u;
+                x[u] = ok ? P.value[p + u] : 0.0f;
+                const bool in = ok && f < P.dims;
+#pragma unroll
+                for (int q = 0; q < NF; q++) {
+                    const int fi = lane + 32 * q;
+                    v[u][q] = (in && fi < k) ? __ldg(P.vrec + (size_t)f * P.vw + fi) : 0.0f;
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < 4; u++)
+                if (p + u < p1) {
+#pragma unroll
+                    for (int q = 0; q < NF; q++) {
+                        const float px = __fmul_rn(v[u][q], x[u]);
+                        S[q] += (double)px;
+                        Q[q] += (double)__fmul_rn(px, px);
+                    }
+                }
+        }
+        double inter = 0.0;
+#pragma unroll
+        for (int q = 0; q < NF; q++) {
+            const int fi = lane + 32 * q;
+            const float s32 = (float)S[q];
+            if (fi < k) {
+                inter += (double)__fmul_rn(s32, s32) - Q[q];
+                if (P.train) P.stab[(size_t)r * k + fi] = s32;
+            }
+        }
+        inter = warp_sum(inter);
+        const float yhat = (float)((double)w0 + lin + 0.5 * inter);
+        if (lane == 0) {
+            P.margin[row - P.block_row0] = yhat;
+            if (P.train) {
+                const float lab = P.label[row];
+                float d;
+                if (P.classification) {
+                    const float y = lab > 0.0f ? 1.0f : -1.0f;
+                    d = __fdiv_rn(-y, __fadd_rn(1.0f, hm_exp(__fmul_rn(y, yhat))));
+                } else {
+                    d = __fsub_rn(yhat, lab);
+                }
+                P.dloss[r] = d;
+            }
+        }
+    }
+}
+
+// ---- update ------------------------------------------------------------------------
+
+struct FmPieceHdr { double a1, a2; uint32_t key, cnt; uint32_t pad[2]; };   // 32 bytes
+static_assert(sizeof(FmPieceHdr) == 32, "piece headers are 32 bytes");
+
+struct FmUpdParams {
+    float *w0rec, *wrec, *vrec;
+    uint8_t *touched;
+    int32_t ww, vw, k;
+    const uint32_t *skey;
+    const uint2 *spay;
+    const float *dloss;
+    const float *stab;
+    const uint32_t *seg_off;
+    int32_t seg;
+    uint32_t dims;
+    int32_t adagrad, grad_norm;
+    float eta, eps, lambda_w0, lambda_w, lambda_v;
+    double inv_rows;
+    int32_t n_rows;
+    // pieces of features whose run straddles chunks: one `first` and one `last` per chunk
+    FmPieceHdr *first_hdr, *last_hdr;
+    double *first_gs, *last_gs;      // [chunk][k]
+    int32_t n_chunks;
+};
+
+__device__ __forceinline__ float fm_grad(const FmUpdParams &P, double sum, uint32_t cnt)
+{
+    if (P.grad_norm == HM_NORM_BATCH) return (float)(sum * P.inv_rows);
+    if (P.grad_norm == HM_NORM_COUNT) return (float)(sum / (double)cnt);
+    return (float)sum;
+}
+
+// SGD or AdaGrad on one parameter with its own L2 strength.
+__device__ __forceinline__ void fm_step(const FmUpdParams &P, float g, float lam, float &th, float &acc)
+{
+    g = __fadd_rn(g, __fmul_rn(lam, th));
+    if (P.adagrad) {
+        acc = __fadd_rn(acc, __fmul_rn(g, g));
+        th = __fsub_rn(th, __fdiv_rn(__fmul_rn(P.eta, g), __fadd_rn(__fsqrt_rn(acc), P.eps)));
+    } else {
+        th = __fsub_rn(th, __fmul_rn(P.eta, g));
+    }
+}
+
+// Step the (up to kFmBatch) finished features waiting in the warp's shared-memory list:
+// all factor rows are requested first, then stepped and stored.  Lane i also steps w of entry i.
+template <int NF>
+__device__ __forceinline__ void fm_apply_pending(const FmUpdParams &P, int npend, const FmPieceHdr *ph,
+                                                 const double *pgs, int lane)
+{
+    const int k = P.k;
+    float v[kFmBatch][NF], a[kFmBatch][NF];
+#pragma unroll
+    for (int i = 0; i < kFmBatch; i++)
+        if (i < npend) {
+            const uint32_t j = ph[i].key;
+#pragma unroll
+            for (int q = 0; q < NF; q++) {
+                const int fi = lane + 32 * q;
+                const bool in = fi < k && j < P.dims;
+                v[i][q] = in ? P.vrec[(size_t)j * P.vw + fi] : 0.0f;
+                a[i][q] = (in && P.adagrad) ? P.vrec[(size_t)j * P.vw + k + fi] : 0.0f;
+            }
+        }
+    float wv = 0.0f, wa = 0.0f;
+    const bool mine = lane < npend && ph[lane < kFmBatch ? lane : 0].key < P.dims;
+    if (mine) {
+        const uint32_t j = ph[lane].key;
+        wv = P.wrec[(size_t)j * P.ww];
+        if (P.adagrad) wa = P.wrec[(size_t)j * P.ww + 1];
+    }
+#pragma unroll
+    for (int i = 0; i < kFmBatch; i++)
+        if (i < npend) {
+            const uint32_t j = ph[i].key;
+            const double a2 = ph[i].a2;
+            const uint32_t cnt = ph[i].cnt;
+#pragma unroll
+            for (int q = 0; q < NF; q++) {
+                const int fi = lane + 32 * q;
+                if (fi < k && j < P.dims) {
+                    const double G = pgs[i * k + fi] - (double)v[i][q] * a2;
+                    fm_step(P, fm_grad(P, G, cnt), P.lambda_v, v[i][q], a[i][q]);
+                    P.vrec[(size_t)j * P.vw + fi] = v[i][q];
+                    if (P.adagrad) P.vrec[(size_t)j * P.vw + k + fi] = a[i][q];
+                }
+            }
+        }
+    if (mine) {
+        const uint32_t j = ph[lane].key;
+        fm_step(P, fm_grad(P, ph[lane].a1, ph[lane].cnt), P.lambda_w, wv, wa);
+        P.wrec[(size_t)j * P.ww] = wv;
+        if (P.adagrad) P.wrec[(size_t)j * P.ww + 1] = wa;
+        P.touched[j] = 1;
+    }
+}
+
+template <int NF>
+__global__ void __launch_bounds__(kFmWarps * 32) fm_update_kernel(FmUpdParams P)
+{
+    extern __shared__ __align__(16) unsigned char fm_smem[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int k = P.k;
+    // per warp: kFmBatch headers + kFmBatch * k sums
+    const size_t per_warp = (size_t)kFmBatch * (sizeof(FmPieceHdr) + (size_t)k * sizeof(double));
+    FmPieceHdr *ph = reinterpret_cast<FmPieceHdr *>(fm_smem + per_warp * warp);
+    double *pgs = reinterpret_cast<double *>(fm_smem + per_warp * warp + kFmBatch * sizeof(FmPieceHdr));
+
+    const uint32_t s0 = P.seg_off[P.seg], n = P.seg_off[P.seg + 1] - s0;
+    const int chunk = blockIdx.x * kFmWarps + warp;
+    if (chunk >= P.n_chunks) return;
+    const uint32_t c0 = (uint32_t)chunk * kFmChunk, c1 = min(n, c0 + (uint32_t)kFmChunk);
+    FmPieceHdr none; none.a1 = 0; none.a2 = 0; none.key = 0; none.cnt = 0; none.pad[0] = none.pad[1] = 0;
+    if (c0 >= c1) {
+        if (lane == 0) { P.first_hdr[chunk] = none; P.last_hdr[chunk] = none; }
+        return;
+    }
+    // does the chunk's first / last feature run continue outside the chunk?
+    const bool left_open = c0 > 0 && __ldg(P.skey + s0 + c0 - 1) == __ldg(P.skey + s0 + c0);
+    const bool right_open = c1 < n && __ldg(P.skey + s0 + c1) == __ldg(P.skey + s0 + c1 - 1);
+
+    uint32_t cur_key = 0, cnt = 0;
+    bool have = false, cur_open_left = false, wrote_first = false;
+    double a1 = 0.0, a2 = 0.0, gs[NF];
+#pragma unroll
+    for (int q = 0; q < NF; q++) gs[q] = 0.0;
+    int npend = 0;
+
+    // a finished feature: to the `first` piece if its run began before the chunk, else to the list
+    auto close_segment = [&]() {
+        if (cur_open_left) {
+            if (lane == 0) { FmPieceHdr h = none; h.a1 = a1; h.a2 = a2; h.key = cur_key; h.cnt = cnt; P.first_hdr[chunk] = h; }
+#pragma unroll
+            for (int q = 0; q < NF; q++) { const int fi = lane + 32 * q; if (fi < k) P.first_gs[(size_t)chunk * k + fi] = gs[q]; }
+            wrote_first = true;
+        } else {
+            if (lane == 0) { ph[npend].a1 = a1; ph[npend].a2 = a2; ph[npend].key = cur_key; ph[npend].cnt = cnt; }
+#pragma unroll
+            for (int q = 0; q < NF; q++) { const int fi = lane + 32 * q; if (fi < k) pgs[npend * k + fi] = gs[q]; }
+            npend++;
+        }
+    };
+
+    for (uint32_t b0 = c0; b0 < c1; b0 += kFmBatch) {
+        // headers of the batch: lanes 0..15 take one element each
+        const uint32_t e = b0 + lane;
+        const bool valid = lane < kFmBatch && e < c1;
+        uint32_t key_l = 0xffffffffu, row_l = 0;
+        float c1_l = 0.0f, c2_l = 0.0f;
+        if (valid) {
+            key_l = __ldcs(P.skey + s0 + e);
+            const uint2 pv = __ldcs(P.spay + s0 + e);
+            row_l = pv.x;
+            const float x = __uint_as_float(pv.y);
+            c1_l = __fmul_rn(__ldg(P.dloss + row_l), x);
+            c2_l = __fmul_rn(c1_l, x);
+        }
+        // S rows of all elements of the batch, requested together
+        float srow[kFmBatch][NF];
+        const int nb = (int)min((uint32_t)kFmBatch, c1 - b0);
+#pragma unroll
+        for (int u = 0; u < kFmBatch; u++) {
+            const uint32_t row_u = __shfl_sync(0xffffffffu, row_l, u);
+#pragma unroll
+            for (int q = 0; q < NF; q++) {
+                const int fi = lane + 32 * q;
+                srow[u][q] = (u < nb && fi < k) ? __ldg(P.stab + (size_t)row_u * k + fi) : 0.0f;
+            }
+        }
+        // elements in sorted order (warp-uniform control flow)
+#pragma unroll
+        for (int u = 0; u < kFmBatch; u++) {
+            const uint32_t key_u = __shfl_sync(0xffffffffu, key_l, u);
+            const float c1_u = __shfl_sync(0xffffffffu, c1_l, u);
+            const float c2_u = __shfl_sync(0xffffffffu, c2_l, u);
+            if (u < nb) {
+                if (!have || key_u != cur_key) {
+                    if (have) close_segment();
+                    cur_open_left = !have && left_open;     // only the chunk's first run can be open to the left
+                    have = true; cur_key = key_u; cnt = 0; a1 = 0.0; a2 = 0.0;
+#pragma unroll
+                    for (int q = 0; q < NF; q++) gs[q] = 0.0;
+                }
+                a1 += (double)c1_u; a2 += (double)c2_u; cnt += 1;
+#pragma unroll
+                for (int q = 0; q < NF; q++) gs[q] += (double)__fmul_rn(c1_u, srow[u][q]);
+            }
+        }
+        __syncwarp();
+        if (npend > 0) { fm_apply_pending<NF>(P, npend, ph, pgs, lane); npend = 0; }
+        __syncwarp();
+    }
+    // the chunk's trailing run is finished here only if it really ends at the chunk's end
+    if (have && !right_open) {
+        close_segment(); have = false;
+        __syncwarp();
+        if (npend > 0) { fm_apply_pending<NF>(P, npend, ph, pgs, lane); npend = 0; }
+        __syncwarp();
+    }
+    // publish the pieces (every chunk writes both headers, so nothing stale is ever read)
+    if (have) {   // trailing run continues in the next chunk
+        if (cur_open_left) {        // the whole chunk lies inside one run: it is a `first` piece
+            if (lane == 0) { FmPieceHdr h = none; h.a1 = a1; h.a2 = a2; h.key = cur_key; h.cnt = cnt; P.first_hdr[chunk] = h; P.last_hdr[chunk] = none; }
+#pragma unroll
+            for (int q = 0; q < NF; q++) { const int fi = lane + 32 * q; if (fi < k) P.first_gs[(size_t)chunk * k + fi] = gs[q]; }
+            wrote_first = true;
+        } else {
+            if (lane == 0) { FmPieceHdr h = none; h.a1 = a1; h.a2 = a2; h.key = cur_key; h.cnt = cnt; P.last_hdr[chunk] = h; }
+#pragma unroll
+            for (int q = 0; q < NF; q++) { const int fi = lane + 32 * q; if (fi < k) P.last_gs[(size_t)chunk * k + fi] = gs[q]; }
+        }
+    } else if (lane == 0) {
+        P.last_hdr[chunk] = none;
+    }
+    if (!wrote_first && lane == 0) P.first_hdr[chunk] = none;
+}
+
+// One warp per chunk: a non-empty `last` piece starts a run that continues through the `first`
+// pieces of the following chunks while the feature matches.  The extra last CTA steps w0.
+template <int NF>
+__global__ void __launch_bounds__(kFmWarps * 32) fm_merge_kernel(FmUpdParams P)
+{
+    __shared__ __align__(16) unsigned char m_smem[kFmWarps * (sizeof(FmPieceHdr) + 256 * sizeof(double))];
+    __shared__ double s_part[kFmWarps];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int k = P.k;
+    if ((int)blockIdx.x == (P.n_chunks + kFmWarps - 1) / kFmWarps) {
+        // ---- w0: fp64 sum of dloss over the mini-batch in a fixed order
+        double s = 0.0;
+        for (int i = threadIdx.x; i < P.n_rows; i += kFmWarps * 32) s += (double)P.dloss[i];
+        s = warp_sum(s);
+        if (lane == 0) s_part[warp] = s;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            double tot = 0.0;
+            for (int w = 0; w < kFmWarps; w++) tot += s_part[w];
+            float w0 = P.w0rec[0], acc = P.w0rec[1];
+            const float g = P.grad_norm == HM_NORM_SUM ? (float)tot : (float)(tot * P.inv_rows);
+            fm_step(P, g, P.lambda_w0, w0, acc);
+            P.w0rec[0] = w0; P.w0rec[1] = acc;
+        }
+        return;
+    }
+    const int c = blockIdx.x * kFmWarps + warp;
+    if (c >= P.n_chunks) return;
+    const FmPieceHdr start = P.last_hdr[c];
+    if (start.cnt == 0) return;
+    double a1 = start.a1, a2 = start.a2, gs[NF];
+    uint32_t cnt = start.cnt;
+#pragma unroll
+    for (int q = 0; q < NF; q++) { const int fi = lane + 32 * q; gs[q] = fi < k ? P.last_gs[(size_t)c * k + fi] : 0.0; }
+    // walk forward four pieces at a time: the loads are issued together, the adds stay in order
+    int j = c + 1;
+    bool more = true;
+    while (more && j < P.n_chunks) {
+        FmPieceHdr h[4]; double g4[4][NF];
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const int jj = min(j + u, P.n_chunks - 1);
+            h[u] = P.first_hdr[jj];
+#pragma unroll
+            for (int q = 0; q < NF; q++) { const int fi = lane + 32 * q; g4[u][q] = fi < k ? P.first_gs[(size_t)jj * k + fi] : 0.0; }
+        }
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            if (more && j + u < P.n_chunks && h[u].cnt != 0 && h[u].key == start.key) {
+                a1 += h[u].a1; a2 += h[u].a2; cnt += h[u].cnt;
+#pragma unroll
+                for (int q = 0; q < NF; q++) gs[q] += g4[u][q];
+            } else {
+                more = false;
+            }
+        }
+        j += 4;
+    }
+    // one finished feature: reuse the batched step with a list of length 1
+    FmPieceHdr *ph = reinterpret_cast<FmPieceHdr *>(m_smem + (size_t)warp * (sizeof(FmPieceHdr) + 256 * sizeof(double)));
+    double *pgs = reinterpret_cast<double *>(reinterpret_cast<unsigned char *>(ph) + sizeof(FmPieceHdr));
+    if (lane == 0) { ph[0].a1 = a1; ph[0].a2 = a2; ph[0].key = start.key; ph[0].cnt = cnt; }
+#pragma unroll
+    for (int q = 0; q < NF; q++) { const int fi = lane + 32 * q; if (fi < k) pgs[fi] = gs[q]; }
+    __syncwarp();
+    fm_apply_pending<NF>(P, 1, ph, pgs, lane);
+}
+
+__global__ void fm_gather_vif_kernel(const float *__restrict__ vrec, int vw, int k, const int32_t *__restrict__ feature,
+                                     int64_t n, float *__restrict__ vif)
+{
+    const int64_t total = n * k;
+    for (int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; q < total; q += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t m = q / k;
+        vif[q] = vrec[(size_t)feature[m] * vw + (q - m * k)];
+    }
+}
+
+int fm_grid(int64_t ctas_wanted, int per_sm)
+{
+    const int64_t cap = (int64_t)kNumSMs * per_sm;
+    if (ctas_wanted < 1) ctas_wanted = 1;
+    return (int)(ctas_wanted < cap ? ctas_wanted : cap);
+}
+
+size_t fm_update_smem(int k) { return (size_t)kFmWarps * kFmBatch * (sizeof(FmPieceHdr) + (size_t)k * sizeof(double)); }
+
+}  // namespace
+
+hm_status launch_fm_init_v(Launcher &L, const FmArgs &a)
+{
+    const int64_t n = a.cfg.dims * a.k;
+    HM_LAUNCH(L, K_MISC, 4.0 * (double)n,
+              (fm_init_v_kernel<<<fm_grid((n + 1023) / 1024, 8), 256, 0, L.stream>>>(a.vrec, a.cfg.dims, a.k, a.vw,
+                                                                                    a.cfg.sigma, a.cfg.seed)));
+    HM_CUDA(cudaGetLastError());
+    return HM_OK;
+}
+
+hm_status launch_fm_forward(Launcher &L, const FmArgs &a, const int64_t *d_rowptr, int64_t row0, int32_t n_rows,
+                            int64_t block_row0, const uint32_t *d_feature, const float *d_value, const float *d_label,
+                            float *d_margin, float *d_dloss, float *d_stab, uint32_t *d_bad, int64_t nnz_hint, bool train)
+{
+    if (n_rows <= 0) return HM_OK;
+    FmFwdParams P;
+    P.w0rec = a.w0rec; P.wrec = a.wrec; P.vrec = a.vrec; P.ww = a.ww; P.vw = a.vw; P.k = a.k;
+    P.rowptr = d_rowptr; P.feature = d_feature; P.value = d_value; P.label = d_label;
+    P.margin = d_margin; P.dloss = d_dloss; P.stab = d_stab;
+    P.block_row0 = block_row0; P.row0 = row0; P.n_rows = n_rows;
+    P.classification = a.cfg.fm_classification; P.train = train ? 1 : 0;
+    P.dims = (uint32_t)a.cfg.dims; P.bad = d_bad;
+    const int grid = fm_grid(((int64_t)n_rows + 7) / 8, 8);
+    // algorithmic bytes: feature+value, w and the k factors per element; S table row + scalars per row
+    const double bytes = (12.0 + 4.0 * a.k) * (double)nnz_hint + (20.0 + 4.0 * a.k) * (double)n_rows;
+    const int id = train ? K_FM_FORWARD : K_PREDICT;
+    if (a.k <= 32) HM_LAUNCH(L, id, bytes, (fm_forward_kernel<1><<<grid, 256, 0, L.stream>>>(P)));
+    else HM_LAUNCH(L, id, bytes, (fm_forward_kernel<2><<<grid, 256, 0, L.stream>>>(P)));
+    HM_CUDA(cudaGetLastError());
+    return HM_OK;
+}
+
+hm_status fm_scratch_reserve(FmScratch &s, int64_t max_mb_elems, int k)
+{
+    const int64_t chunks = (max_mb_elems + kFmChunk - 1) / kFmChunk + 1;
+    if (chunks <= s.cap_chunks && k == s.k) return HM_OK;
+    fm_scratch_free(s);
+    HM_CUDA(cudaMalloc(&s.hdr, (size_t)chunks * 2 * sizeof(FmPieceHdr)));
+    HM_CUDA(cudaMalloc(&s.gs, (size_t)chunks * 2 * k * sizeof(double)));
+    s.cap_chunks = chunks; s.k = k;
+    return HM_OK;
+}
+
+void fm_scratch_free(FmScratch &s)
+{
+    cudaFree(s.hdr); cudaFree(s.gs);
+    s.hdr = nullptr; s.gs = nullptr; s.cap_chunks = 0; s.k = 0;
+}
+
+hm_status launch_fm_update(Launcher &L, const FmArgs &a, const StepScalars &sc, FmScratch &fs,
+                           const uint32_t *d_sorted_key, const uint2 *d_sorted_pay, const uint32_t *d_seg_off, int seg,
+                           const float *d_dloss, const float *d_stab, int64_t nnz)
+{
+    static bool attr_set = false;
+    if (!attr_set) {
+        HM_CUDA(cudaFuncSetAttribute(fm_update_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fm_update_smem(32)));
+        HM_CUDA(cudaFuncSetAttribute(fm_update_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fm_update_smem(64)));
+        attr_set = true;
+    }
+    const int n_chunks = (int)std::max<int64_t>((nnz + kFmChunk - 1) / kFmChunk, 1);
+    if (n_chunks > fs.cap_chunks) HM_FAIL(HM_ERR_STATE, "fm scratch too small");
+    FmUpdParams P;
+    P.w0rec = a.w0rec; P.wrec = a.wrec; P.vrec = a.vrec; P.touched = a.touched;
+    P.ww = a.ww; P.vw = a.vw; P.k = a.k;
+    P.skey = d_sorted_key; P.spay = d_sorted_pay; P.dloss = d_dloss; P.stab = d_stab; P.seg_off = d_seg_off; P.seg = seg;
+    P.dims = (uint32_t)a.cfg.dims;
+    P.adagrad = a.cfg.opt == HM_OPT_ADAGRAD; P.grad_norm = a.cfg.grad_norm;
+    P.eta = sc.eta; P.eps = a.cfg.eps; P.lambda_w0 = a.cfg.lambda_w0; P.lambda_w = a.cfg.lambda_w; P.lambda_v = a.cfg.lambda_v;
+    P.inv_rows = 1.0 / (double)sc.n_rows; P.n_rows = sc.n_rows;
+    P.first_hdr = reinterpret_cast<FmPieceHdr *>(fs.hdr); P.last_hdr = P.first_hdr + fs.cap_chunks;
+    P.first_gs = fs.gs; P.last_gs = fs.gs + (size_t)fs.cap_chunks * a.k;
+    P.n_chunks = n_chunks;
+    const int ctas = (n_chunks + kFmWarps - 1) / kFmWarps;
+    // algorithmic bytes: sorted stream, S row per element (the per-feature record traffic is data dependent)
+    const double bytes = (12.0 + 4.0 * a.k) * (double)nnz;
+    const size_t smem = fm_update_smem(a.k);
+    if (a.k <= 32) {
+        HM_LAUNCH(L, K_FM_UPDATE, bytes, (fm_update_kernel<1><<<ctas, kFmWarps * 32, smem, L.stream>>>(P)));
+        HM_LAUNCH(L, K_FM_UPDATE, 0.0, (fm_merge_kernel<1><<<ctas + 1, kFmWarps * 32, 0, L.stream>>>(P)));
+    } else {
+        HM_LAUNCH(L, K_FM_UPDATE, bytes, (fm_update_kernel<2><<<ctas, kFmWarps * 32, smem, L.stream>>>(P)));
+        HM_LAUNCH(L, K_FM_UPDATE, 0.0, (fm_merge_kernel<2><<<ctas + 1, kFmWarps * 32, 0, L.stream>>>(P)));
+    }
+    HM_CUDA(cudaGetLastError());
+    return HM_OK;
+}
+
+hm_status launch_fm_gather_vif(Launcher &L, const FmArgs &a, const int32_t *d_feature, int64_t n, float *d_vif)
+{
+    if (n <= 0) return HM_OK;
+    HM_LAUNCH(L, K_EXPORT, 8.0 * (double)n * a.k,
+              (fm_gather_vif_kernel<<<fm_grid((n * a.k + 1023) / 1024, 8), 256, 0, L.stream>>>(a.vrec, a.vw, a.k, d_feature,
+                                                                                            n, d_vif)));
+    HM_CUDA(cudaGetLastError());
+    return HM_OK;
+}
+
+}  // namespace hm

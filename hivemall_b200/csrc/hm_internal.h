@@ -119,6 +119,32 @@ hm_status launch_fill_u32(Launcher &L, uint32_t *p, int64_t n, uint32_t v);
 hm_status launch_strided_copy(Launcher &L, float *dense, float *strided, int64_t n, int stride, int off, int width,
                               bool gather);
 
+// ---- factorization machine kernels (hm_fm.cu) ------------------------------------
+struct FmArgs {
+    hm_config cfg;
+    float *w0rec;        // (w0, accumulator)
+    float *wrec;         // ww floats per feature: (w[, accumulator])
+    float *vrec;         // vw floats per feature: (V_0..V_k-1[, accumulators])
+    uint8_t *touched;    // 1 for every feature seen in training
+    int ww, vw, k;
+};
+struct FmScratch {       // pieces of features whose run straddles update chunks
+    void *hdr = nullptr;
+    double *gs = nullptr;
+    int64_t cap_chunks = 0;
+    int k = 0;
+};
+hm_status fm_scratch_reserve(FmScratch &s, int64_t max_mb_elems, int k);
+void fm_scratch_free(FmScratch &s);
+hm_status launch_fm_init_v(Launcher &L, const FmArgs &a);
+hm_status launch_fm_forward(Launcher &L, const FmArgs &a, const int64_t *d_rowptr, int64_t row0, int32_t n_rows,
+                            int64_t block_row0, const uint32_t *d_feature, const float *d_value, const float *d_label,
+                            float *d_margin, float *d_dloss, float *d_stab, uint32_t *d_bad, int64_t nnz_hint, bool train);
+hm_status launch_fm_update(Launcher &L, const FmArgs &a, const StepScalars &sc, FmScratch &fs,
+                           const uint32_t *d_sorted_key, const uint2 *d_sorted_pay, const uint32_t *d_seg_off, int seg,
+                           const float *d_dloss, const float *d_stab, int64_t nnz);
+hm_status launch_fm_gather_vif(Launcher &L, const FmArgs &a, const int32_t *d_feature, int64_t n, float *d_vif);
+
 // ---- options (hm_options.cpp) -------------------------------------------------
 hm_status parse_options(const char *function_name, const char *options, hm_config *out);
 

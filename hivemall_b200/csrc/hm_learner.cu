@@ -148,6 +148,13 @@ struct hm_udtf {
     float *rec = nullptr;            // dims x rec_width floats: (w[, slot1[, slot2, unused]]) per feature
     int rec_width = 1;
     int state_width = 0;             // optimizer slots per feature (0, 1 or 2)
+    // train_fm replica
+    bool fm = false;
+    float *w0rec = nullptr, *wrec = nullptr, *vrec = nullptr;
+    uint8_t *touched = nullptr;
+    int ww = 1, vw = 0, k = 0;
+    FmScratch fms;
+    DevBuf stab, exp_vif;
     int64_t t = 0;
     // scratch
     SortScratch sort;
@@ -214,6 +221,18 @@ float adam_alpha_at(const hm_config &c, float eta, int64_t t)
     return (float)((double)eta * std::sqrt(1.0 - b2) / (1.0 - b1));
 }
 
+FmArgs fm_args(const hm_udtf *u)
+{
+    FmArgs a;
+    a.cfg = u->cfg; a.w0rec = u->w0rec; a.wrec = u->wrec; a.vrec = u->vrec; a.touched = u->touched;
+    a.ww = u->ww; a.vw = u->vw; a.k = u->k;
+    return a;
+}
+
+// what the model table is read from: (weights, stride, touched bitmap or NULL)
+const float *table_w(const hm_udtf *u) { return u->fm ? u->wrec : u->rec; }
+int table_stride(const hm_udtf *u) { return u->fm ? u->ww : u->rec_width; }
+
 // Train rows [row0, row0+n_rows) of a chunk.  mb_abs[i] is the chunk rowptr value at
 // row0 + min(i*B, n_rows), i = 0..n_mb.
 hm_status train_rows(hm_udtf *u, const Chunk &c, int64_t row0, int64_t n_rows, const int64_t *mb_abs, int64_t n_mb)
@@ -237,6 +256,12 @@ hm_status train_rows(hm_udtf *u, const Chunk &c, int64_t row0, int64_t n_rows, c
         HM_TRY(sort_scratch_reserve(u->sort, b_nnz));
         HM_TRY(u->margin.reserve((size_t)b_rows * sizeof(float)));
         HM_TRY(u->dloss.reserve((size_t)std::min<int64_t>(b_rows, B) * sizeof(float)));
+        if (u->fm) {
+            int64_t max_mb = 0;
+            for (int64_t m = m0; m < m1; m++) max_mb = std::max(max_mb, mb_abs[m + 1] - mb_abs[m]);
+            HM_TRY(fm_scratch_reserve(u->fms, max_mb, u->k));
+            HM_TRY(u->stab.reserve((size_t)std::min<int64_t>(b_rows, B) * u->k * sizeof(float)));
+        }
         HM_TRY(launch_seg_prep(u->L, u->sort, c.rp(), b_row0, b_rows, b_nnz, B, n_segs));
         int buf = 0;
         HM_TRY(launch_segmented_sort(u->L, u->sort, c.ft() + mb_abs[m0], c.vl() + mb_abs[m0], b_nnz, n_segs, key_bits,
@@ -251,10 +276,19 @@ hm_status train_rows(hm_udtf *u, const Chunk &c, int64_t row0, int64_t n_rows, c
             sc.adam_alpha = u->cfg.opt == HM_OPT_ADAM ? adam_alpha_at(u->cfg, sc.eta, u->t) : 0.f;
             sc.inv_denom_unused = 0;
             sc.n_rows = mrows;
-            HM_TRY(launch_linear_forward(u->L, a, c.rp(), mrow0, mrows, b_row0, c.ft(), c.vl(), c.lb(),
-                                         u->margin.as<float>(), u->dloss.as<float>(), u->d_bad, mnnz));
-            HM_TRY(launch_linear_update(u->L, a, sc, u->upd, u->sort.key[buf], u->sort.pay[buf], u->sort.seg_off, s,
-                                        u->dloss.as<float>(), mnnz));
+            if (u->fm) {
+                const FmArgs fa = fm_args(u);
+                HM_TRY(launch_fm_forward(u->L, fa, c.rp(), mrow0, mrows, b_row0, c.ft(), c.vl(), c.lb(),
+                                         u->margin.as<float>(), u->dloss.as<float>(), u->stab.as<float>(), u->d_bad, mnnz,
+                                         true));
+                HM_TRY(launch_fm_update(u->L, fa, sc, u->fms, u->sort.key[buf], u->sort.pay[buf], u->sort.seg_off, s,
+                                        u->dloss.as<float>(), u->stab.as<float>(), mnnz));
+            } else {
+                HM_TRY(launch_linear_forward(u->L, a, c.rp(), mrow0, mrows, b_row0, c.ft(), c.vl(), c.lb(),
+                                             u->margin.as<float>(), u->dloss.as<float>(), u->d_bad, mnnz));
+                HM_TRY(launch_linear_update(u->L, a, sc, u->upd, u->sort.key[buf], u->sort.pay[buf], u->sort.seg_off, s,
+                                            u->dloss.as<float>(), mnnz));
+            }
             u->stats.mini_batches++;
             u->last_margin_off = mrow0 - b_row0;
             u->last_margin_n = mrows;
@@ -394,7 +428,8 @@ hm_status create_impl(const hm_config &cfg, int device, hm_udtf **out)
         HM_FAIL(HM_ERR_CUDA, "no CUDA device: hivemall_b200 has no CPU fallback");
     }
     if (device < 0 || device >= ndev) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "device %d out of range [0, %d)", device, ndev);
-    if (cfg.task == HM_TASK_FM) HM_FAIL(HM_ERR_UNSUPPORTED, "train_fm is not built yet");
+    if (cfg.task == HM_TASK_FM && (cfg.factors < 1 || cfg.factors > 64))
+        HM_FAIL(HM_ERR_UNSUPPORTED, "train_fm supports 1..64 factors in this build (got %d)", cfg.factors);
     if (cfg.dims < 1 || cfg.dims > ((int64_t)1 << 31)) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "dims out of range");
     if (cfg.mini_batch < 1) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "mini_batch must be >= 1");
     DeviceGuard g(device);
@@ -408,9 +443,27 @@ hm_status create_impl(const hm_config &cfg, int device, hm_udtf **out)
         HM_CUDA(cudaStreamCreateWithFlags(&u->copy, cudaStreamNonBlocking));
         u->L.stream = u->compute;
         u->state_width = cfg.opt == HM_OPT_SGD ? 0 : (cfg.opt == HM_OPT_ADAGRAD ? 1 : 2);
-        u->rec_width = u->state_width == 0 ? 1 : (u->state_width == 1 ? 2 : 4);
-        HM_CUDA(cudaMalloc(&u->rec, (size_t)cfg.dims * u->rec_width * sizeof(float)));
-        HM_CUDA(cudaMemsetAsync(u->rec, 0, (size_t)cfg.dims * u->rec_width * sizeof(float), u->compute));
+        if (cfg.task == HM_TASK_FM) {
+            u->fm = true;
+            u->k = cfg.factors;
+            const bool ada = cfg.opt == HM_OPT_ADAGRAD;
+            u->ww = ada ? 2 : 1;
+            u->vw = ada ? 2 * u->k : u->k;
+            const size_t tb = ((size_t)cfg.dims + 3) / 4 * 4;
+            HM_CUDA(cudaMalloc(&u->w0rec, 2 * sizeof(float)));
+            HM_CUDA(cudaMalloc(&u->wrec, (size_t)cfg.dims * u->ww * sizeof(float)));
+            HM_CUDA(cudaMalloc(&u->vrec, (size_t)cfg.dims * u->vw * sizeof(float)));
+            HM_CUDA(cudaMalloc(&u->touched, tb));
+            HM_CUDA(cudaMemsetAsync(u->w0rec, 0, 2 * sizeof(float), u->compute));
+            HM_CUDA(cudaMemsetAsync(u->wrec, 0, (size_t)cfg.dims * u->ww * sizeof(float), u->compute));
+            HM_CUDA(cudaMemsetAsync(u->vrec, 0, (size_t)cfg.dims * u->vw * sizeof(float), u->compute));
+            HM_CUDA(cudaMemsetAsync(u->touched, 0, tb, u->compute));
+            HM_TRY(launch_fm_init_v(u->L, fm_args(u)));
+        } else {
+            u->rec_width = u->state_width == 0 ? 1 : (u->state_width == 1 ? 2 : 4);
+            HM_CUDA(cudaMalloc(&u->rec, (size_t)cfg.dims * u->rec_width * sizeof(float)));
+            HM_CUDA(cudaMemsetAsync(u->rec, 0, (size_t)cfg.dims * u->rec_width * sizeof(float), u->compute));
+        }
         HM_CUDA(cudaMalloc(&u->d_bad, sizeof(uint32_t)));
         HM_CUDA(cudaMemsetAsync(u->d_bad, 0, sizeof(uint32_t), u->compute));
         HM_CUDA(cudaMalloc(&u->d_total, sizeof(int64_t)));
@@ -654,40 +707,53 @@ hm_status hm_udtf_close(hm_udtf *u, int64_t *n_model_rows)
         u->closed = true;
     }
     HM_TRY(check_bad(u));
-    HM_TRY(launch_export_count(u->L, u->exp, u->rec, u->rec_width, nullptr, u->cfg.dims, u->d_total));
+    HM_TRY(launch_export_count(u->L, u->exp, table_w(u), table_stride(u), u->touched, u->cfg.dims, u->d_total));
     HM_CUDA(cudaMemcpyAsync(u->h_small, u->d_total, sizeof(int64_t), cudaMemcpyDeviceToHost, u->compute));
     HM_CUDA(cudaStreamSynchronize(u->compute));
     u->stats.d2h_bytes += 8;
-    u->model_rows = u->h_small[0];
+    u->model_rows = u->h_small[0] + (u->fm ? 1 : 0);   // train_fm: plus the w0 row
     u->L.drain();
     if (n_model_rows) *n_model_rows = u->model_rows;
     return HM_OK;
 }
 
-hm_status hm_udtf_forward(hm_udtf *u, int32_t *feature, float *weight, float *, int64_t cap, int64_t *n_written)
+hm_status hm_udtf_forward(hm_udtf *u, int32_t *feature, float *weight, float *vif, int64_t cap, int64_t *n_written)
 {
     if (!u) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "NULL learner");
     if (!u->closed) HM_FAIL(HM_ERR_STATE, "forward() before close()");
     if (cap < 0 || (cap > 0 && (!feature || !weight))) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "bad arguments to forward()");
+    if (u->fm && cap > 0 && !vif) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "train_fm forward() needs a vif buffer");
     DeviceGuard g(u->device);
     // recount: the replica may have been averaged since close()
-    HM_TRY(launch_export_count(u->L, u->exp, u->rec, u->rec_width, nullptr, u->cfg.dims, u->d_total));
+    HM_TRY(launch_export_count(u->L, u->exp, table_w(u), table_stride(u), u->touched, u->cfg.dims, u->d_total));
     HM_CUDA(cudaMemcpyAsync(u->h_small, u->d_total, sizeof(int64_t), cudaMemcpyDeviceToHost, u->compute));
     HM_CUDA(cudaStreamSynchronize(u->compute));
     const int64_t n = u->h_small[0];
-    u->model_rows = n;
-    if (n > cap) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "model table has %lld rows but capacity is %lld", (long long)n, (long long)cap);
+    const int64_t head = u->fm ? 1 : 0;     // train_fm: row 0 is (feature -1, w0, zeros)
+    u->model_rows = n + head;
+    if (n + head > cap) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "model table has %lld rows but capacity is %lld", (long long)(n + head), (long long)cap);
+    if (u->fm) {
+        feature[0] = -1;
+        HM_CUDA(cudaMemcpyAsync(weight, u->w0rec, 4, cudaMemcpyDeviceToHost, u->compute));
+        std::memset(vif, 0, (size_t)u->k * 4);
+    }
     if (n > 0) {
         HM_TRY(u->exp_feat.reserve((size_t)n * 4));
         HM_TRY(u->exp_weight.reserve((size_t)n * 4));
-        HM_TRY(launch_export_write(u->L, u->exp, u->rec, u->rec_width, nullptr, u->cfg.dims, u->exp_feat.as<int32_t>(),
-                                   u->exp_weight.as<float>()));
-        HM_CUDA(cudaMemcpyAsync(feature, u->exp_feat.p, (size_t)n * 4, cudaMemcpyDeviceToHost, u->compute));
-        HM_CUDA(cudaMemcpyAsync(weight, u->exp_weight.p, (size_t)n * 4, cudaMemcpyDeviceToHost, u->compute));
-        HM_CUDA(cudaStreamSynchronize(u->compute));
+        HM_TRY(launch_export_write(u->L, u->exp, table_w(u), table_stride(u), u->touched, u->cfg.dims,
+                                   u->exp_feat.as<int32_t>(), u->exp_weight.as<float>()));
+        HM_CUDA(cudaMemcpyAsync(feature + head, u->exp_feat.p, (size_t)n * 4, cudaMemcpyDeviceToHost, u->compute));
+        HM_CUDA(cudaMemcpyAsync(weight + head, u->exp_weight.p, (size_t)n * 4, cudaMemcpyDeviceToHost, u->compute));
         u->stats.d2h_bytes += n * 8;
+        if (u->fm) {
+            HM_TRY(u->exp_vif.reserve((size_t)n * u->k * 4));
+            HM_TRY(launch_fm_gather_vif(u->L, fm_args(u), u->exp_feat.as<int32_t>(), n, u->exp_vif.as<float>()));
+            HM_CUDA(cudaMemcpyAsync(vif + head * u->k, u->exp_vif.p, (size_t)n * u->k * 4, cudaMemcpyDeviceToHost, u->compute));
+            u->stats.d2h_bytes += n * u->k * 4;
+        }
     }
-    if (n_written) *n_written = n;
+    HM_CUDA(cudaStreamSynchronize(u->compute));
+    if (n_written) *n_written = n + head;
     return HM_OK;
 }
 
@@ -708,6 +774,9 @@ hm_status hm_udtf_destroy(hm_udtf *u)
                       &u->tmp_b, &u->tmp_c, &u->tmp_d})
         b->release();
     cudaFree(u->rec); cudaFree(u->d_bad); cudaFree(u->d_total);
+    cudaFree(u->w0rec); cudaFree(u->wrec); cudaFree(u->vrec); cudaFree(u->touched);
+    fm_scratch_free(u->fms);
+    u->stab.release(); u->exp_vif.release();
     for (int i = 0; i < 2; i++) {
         if (u->h_stage[i]) cudaFreeHost(u->h_stage[i]);
         if (u->stage_ev[i]) cudaEventDestroy(u->stage_ev[i]);
@@ -723,37 +792,53 @@ hm_status hm_udtf_destroy(hm_udtf *u)
 
 // ---- replica access ----------------------------------------------------------------
 
-int hm_udtf_num_arrays(const hm_udtf *u) { return u ? 1 : 0; }
+int hm_udtf_num_arrays(const hm_udtf *u) { return u ? (u->fm ? 4 : 1) : 0; }
 
 hm_status hm_udtf_array(hm_udtf *u, int which, const char **name, void **d_ptr, int64_t *n_floats, int32_t *width)
 {
     if (!u) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "NULL learner");
-    if (which != 0) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "array index %d out of range", which);
-    if (name) *name = "replica";
-    if (d_ptr) *d_ptr = u->rec;
-    if (n_floats) *n_floats = u->cfg.dims * u->rec_width;
-    if (width) *width = u->rec_width;
+    const char *nm = nullptr; void *p = nullptr; int64_t n = 0; int32_t w = 0;
+    if (!u->fm && which == 0) { nm = "replica"; p = u->rec; n = u->cfg.dims * u->rec_width; w = u->rec_width; }
+    else if (u->fm && which == 0) { nm = "w0"; p = u->w0rec; n = 2; w = 2; }
+    else if (u->fm && which == 1) { nm = "w"; p = u->wrec; n = u->cfg.dims * u->ww; w = u->ww; }
+    else if (u->fm && which == 2) { nm = "V"; p = u->vrec; n = u->cfg.dims * u->vw; w = u->vw; }
+    else if (u->fm && which == 3) { nm = "touched"; p = u->touched; n = (u->cfg.dims + 3) / 4; w = 0; }
+    else HM_FAIL(HM_ERR_INVALID_ARGUMENT, "array index %d out of range", which);
+    if (name) *name = nm;
+    if (d_ptr) *d_ptr = p;
+    if (n_floats) *n_floats = n;
+    if (width) *width = w;
     return HM_OK;
 }
 
-// Logical arrays inside the interleaved replica: 0 = "w" (dims floats), 1 = "state"
-// (dims x state_width floats, slots interleaved per feature).
+// Logical arrays inside the interleaved replica.  Linear: 0 = w (dims), 1 = state (dims x slots).
+// train_fm: 0 = w (dims), 1 = V (dims x factors), 2 = w0 (1), 3 = AdaGrad accumulators of w,
+// 4 = of V, 5 = of w0.
 static hm_status array_copy(hm_udtf *u, int which, float *host, const float *host_in, int64_t n)
 {
-    if (which != 0 && !(which == 1 && u->state_width > 0)) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "array index %d out of range", which);
-    const int width = which == 0 ? 1 : u->state_width, off = which == 0 ? 0 : 1;
-    const int64_t len = u->cfg.dims * width;
+    float *base = nullptr; int64_t rows = u->cfg.dims; int stride = 1, off = 0, width = 1;
+    const bool ada = u->cfg.opt == HM_OPT_ADAGRAD;
+    if (!u->fm && which == 0) { base = u->rec; stride = u->rec_width; }
+    else if (!u->fm && which == 1 && u->state_width > 0) { base = u->rec; stride = u->rec_width; off = 1; width = u->state_width; }
+    else if (u->fm && which == 0) { base = u->wrec; stride = u->ww; }
+    else if (u->fm && which == 1) { base = u->vrec; stride = u->vw; width = u->k; }
+    else if (u->fm && which == 2) { base = u->w0rec; rows = 1; stride = 2; }
+    else if (u->fm && ada && which == 3) { base = u->wrec; stride = u->ww; off = 1; }
+    else if (u->fm && ada && which == 4) { base = u->vrec; stride = u->vw; off = u->k; width = u->k; }
+    else if (u->fm && ada && which == 5) { base = u->w0rec; rows = 1; stride = 2; off = 1; }
+    else HM_FAIL(HM_ERR_INVALID_ARGUMENT, "array index %d out of range", which);
+    const int64_t len = rows * width;
     if (n != len) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "array %d holds %lld floats, caller passed %lld", which, (long long)len, (long long)n);
     DeviceGuard g(u->device);
     HM_CUDA(cudaStreamSynchronize(u->copy));
     HM_TRY(u->tmp_a.reserve((size_t)n * 4));
     if (host) {
-        HM_TRY(launch_strided_copy(u->L, u->tmp_a.as<float>(), u->rec, u->cfg.dims, u->rec_width, off, width, true));
+        HM_TRY(launch_strided_copy(u->L, u->tmp_a.as<float>(), base, rows, stride, off, width, true));
         HM_CUDA(cudaMemcpyAsync(host, u->tmp_a.p, (size_t)n * 4, cudaMemcpyDeviceToHost, u->compute));
         u->stats.d2h_bytes += n * 4;
     } else {
         HM_CUDA(cudaMemcpyAsync(u->tmp_a.p, host_in, (size_t)n * 4, cudaMemcpyHostToDevice, u->compute));
-        HM_TRY(launch_strided_copy(u->L, u->tmp_a.as<float>(), u->rec, u->cfg.dims, u->rec_width, off, width, false));
+        HM_TRY(launch_strided_copy(u->L, u->tmp_a.as<float>(), base, rows, stride, off, width, false));
         u->stats.h2d_bytes += n * 4;
     }
     HM_CUDA(cudaStreamSynchronize(u->compute));
@@ -801,7 +886,13 @@ hm_status hm_udtf_scale_replica(hm_udtf *u, float scale)
 {
     if (!u) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "NULL learner");
     DeviceGuard g(u->device);
-    HM_TRY(launch_scale(u->L, u->rec, u->cfg.dims * u->rec_width, scale));
+    if (u->fm) {
+        HM_TRY(launch_scale(u->L, u->w0rec, 2, scale));
+        HM_TRY(launch_scale(u->L, u->wrec, u->cfg.dims * u->ww, scale));
+        HM_TRY(launch_scale(u->L, u->vrec, u->cfg.dims * u->vw, scale));
+    } else {
+        HM_TRY(launch_scale(u->L, u->rec, u->cfg.dims * u->rec_width, scale));
+    }
     return HM_OK;
 }
 
@@ -813,6 +904,11 @@ hm_status hm_udtf_predict_device(hm_udtf *u, int64_t n_rows, const int64_t *d_ro
     if (!u) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "NULL learner");
     if (n_rows < 0 || (n_rows > 0 && (!d_rowptr || !d_out))) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "bad arguments to predict");
     DeviceGuard g(u->device);
+    if (u->fm) {
+        if (n_rows > 0x7fffffff) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "predict: too many rows in one call");
+        return launch_fm_forward(u->L, fm_args(u), d_rowptr, 0, (int32_t)n_rows, 0, reinterpret_cast<const uint32_t *>(d_feature),
+                                 d_value, nullptr, d_out, nullptr, nullptr, u->d_bad, 0, false);
+    }
     return launch_predict_linear(u->L, u->rec, u->rec_width, u->cfg.dims, n_rows, d_rowptr, reinterpret_cast<const uint32_t *>(d_feature),
                                  d_value, d_out, u->d_bad);
 }
@@ -837,8 +933,14 @@ hm_status hm_udtf_predict(hm_udtf *u, int64_t n_rows, const int64_t *rowptr, con
         HM_CUDA(cudaMemcpyAsync(u->tmp_b.p, feature + base, (size_t)nnz * 4, cudaMemcpyHostToDevice, u->compute));
         HM_CUDA(cudaMemcpyAsync(u->tmp_c.p, value + base, (size_t)nnz * 4, cudaMemcpyHostToDevice, u->compute));
     }
-    HM_TRY(launch_predict_linear(u->L, u->rec, u->rec_width, u->cfg.dims, n_rows, u->tmp_a.as<int64_t>(), u->tmp_b.as<uint32_t>(),
-                                 u->tmp_c.as<float>(), u->tmp_d.as<float>(), u->d_bad));
+    if (u->fm) {
+        if (n_rows > 0x7fffffff) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "predict: too many rows in one call");
+        HM_TRY(launch_fm_forward(u->L, fm_args(u), u->tmp_a.as<int64_t>(), 0, (int32_t)n_rows, 0, u->tmp_b.as<uint32_t>(),
+                                 u->tmp_c.as<float>(), nullptr, u->tmp_d.as<float>(), nullptr, nullptr, u->d_bad, nnz, false));
+    } else {
+        HM_TRY(launch_predict_linear(u->L, u->rec, u->rec_width, u->cfg.dims, n_rows, u->tmp_a.as<int64_t>(), u->tmp_b.as<uint32_t>(),
+                                     u->tmp_c.as<float>(), u->tmp_d.as<float>(), u->d_bad));
+    }
     HM_CUDA(cudaMemcpyAsync(out, u->tmp_d.p, (size_t)n_rows * 4, cudaMemcpyDeviceToHost, u->compute));
     HM_CUDA(cudaStreamSynchronize(u->compute));   // also keeps `rp` alive long enough
     u->stats.h2d_bytes += (n_rows + 1) * 8 + nnz * 8;

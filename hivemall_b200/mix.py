@@ -53,9 +53,13 @@ class ReplicaMixer:
         self.world = world
         self.group = group
         self.stream = torch.cuda.ExternalStream(udtf.stream, device=f"cuda:{udtf.device}")
-        self.tensors = [torch.as_tensor(udtf.array_view(name), device=f"cuda:{udtf.device}")
-                        for name in udtf.arrays()]
-        self.bytes_per_mix = sum(t.numel() * 4 for t in self.tensors)
+        dev = f"cuda:{udtf.device}"
+        arrays = udtf.arrays()
+        # float arrays are averaged; width 0 marks a byte map ("touched") that is OR-ed (max)
+        self.tensors = [torch.as_tensor(udtf.array_view(name), device=dev) for name, a in arrays.items() if a[2] > 0]
+        self.byte_maps = [torch.as_tensor(udtf.array_view(name), device=dev).view(torch.uint8)
+                          for name, a in arrays.items() if a[2] == 0]
+        self.bytes_per_mix = sum(t.numel() * 4 for t in self.tensors) + sum(t.numel() for t in self.byte_maps)
         self.mixes = 0
 
     def mix(self) -> None:
@@ -68,5 +72,7 @@ class ReplicaMixer:
         with torch.cuda.stream(self.stream):
             for t in self.tensors:
                 dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.group)
+            for t in self.byte_maps:
+                dist.all_reduce(t, op=dist.ReduceOp.MAX, group=self.group)
         self.udtf.scale_replica(1.0 / self.world)
         self.mixes += 1

@@ -254,25 +254,38 @@ class UDTF:
         return _DeviceArray(p, n, self)
 
     _LOGICAL = {"w": 0, "state": 1}
+    _LOGICAL_FM = {"w": 0, "V": 1, "w0": 2, "gw": 3, "gV": 4, "gw0": 5}
 
     @property
     def state_width(self) -> int:
         """Optimizer slots per feature (0 SGD, 1 AdaGrad, 2 otherwise)."""
         return {0: 0, 1: 1}.get(self.config.opt, 2)
 
+    def _logical(self, name: str) -> tuple[int, int]:
+        """(index, length) of a logical model array."""
+        d = self.config.dims
+        if self.function_name == "train_fm":
+            k = self.config.factors
+            n = {"w": d, "V": d * k, "w0": 1, "gw": d, "gV": d * k, "gw0": 1}[name]
+            return self._LOGICAL_FM[name], n
+        return self._LOGICAL[name], d * (1 if name == "w" else self.state_width)
+
     def array_to_host(self, name: str) -> np.ndarray:
-        """Copy a logical model array to the host: "w" (dims floats) or "state"
-        (dims * state_width floats, a feature's slots adjacent)."""
-        n = self.config.dims * (1 if name == "w" else self.state_width)
+        """Copy a logical model array to the host.  Linear learners: "w" (dims floats),
+        "state" (dims * state_width floats, a feature's slots adjacent).  train_fm: "w",
+        "V" (dims * factors, row per feature), "w0", and with -opt adagrad the accumulators
+        "gw", "gV", "gw0"."""
+        which, n = self._logical(name)
         out = np.empty(n, dtype=np.float32)
         if n:
-            check(self._lib.hm_udtf_read_array(self._h, self._LOGICAL[name], _ptr(out), n))
+            check(self._lib.hm_udtf_read_array(self._h, which, _ptr(out), n))
         return out
 
     def array_from_host(self, name: str, values) -> None:
         """Overwrite a logical model array from the host (warm start)."""
+        which, _ = self._logical(name)
         values = np.ascontiguousarray(values, dtype=np.float32).reshape(-1)
-        check(self._lib.hm_udtf_write_array(self._h, self._LOGICAL[name], _ptr(values), len(values)))
+        check(self._lib.hm_udtf_write_array(self._h, which, _ptr(values), len(values)))
 
     def scale_replica(self, scale: float) -> None:
         check(self._lib.hm_udtf_scale_replica(self._h, scale))

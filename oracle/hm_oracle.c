@@ -404,21 +404,22 @@ static float fm_score(const hmo_config *c, const int64_t *rowptr, const uint32_t
                       const float *val, int64_t i, float w0, const float *w, const float *V,
                       float *S32 /* factors, nullable */)
 {
+    /* fp32 products, fp64 sums, S_f rounded to fp32 before it is squared */
     const int k = c->factors;
     double lin = 0.0;
     for (int64_t p = rowptr[i]; p < rowptr[i + 1]; p++)
-        lin += (double)w[idx[p]] * (double)val[p];
+        lin += (double)(w[idx[p]] * val[p]);
     double inter = 0.0;
     for (int f = 0; f < k; f++) {
         double S = 0.0, Q = 0.0;
         for (int64_t p = rowptr[i]; p < rowptr[i + 1]; p++) {
-            double vx = (double)V[(int64_t)idx[p] * k + f] * (double)val[p];
-            S += vx;
-            Q += vx * vx;
+            float vx = V[(int64_t)idx[p] * k + f] * val[p];
+            S += (double)vx;
+            Q += (double)(vx * vx);
         }
         float s32 = (float)S;
         if (S32) S32[f] = s32;
-        inter += (double)s32 * (double)s32 - Q;
+        inter += (double)(s32 * s32) - Q;
     }
     return (float)((double)w0 + lin + 0.5 * inter);
 }
@@ -454,7 +455,8 @@ int hmo_train_fm(const hmo_config *c, int64_t n_rows, const int64_t *rowptr,
     const int k = c->factors;
     const int64_t B = c->mini_batch;
     if (B < 1 || k < 1) return -1;
-    /* per-feature sums for the batch: A1 = sum dl*x, A2 = sum (dl*x)*x, GS[f] = sum (dl*x)*S[f] */
+    /* per-feature fp64 sums over the batch (c1 = dl*x in fp32):
+     * A1 = sum c1, A2 = sum (c1*x), GS[f] = sum (c1*S32[row][f]) */
     double *A1 = (double *)calloc((size_t)c->dims, sizeof(double));
     double *A2 = (double *)calloc((size_t)c->dims, sizeof(double));
     uint32_t *cnt = (uint32_t *)calloc((size_t)c->dims, sizeof(uint32_t));
@@ -464,7 +466,6 @@ int hmo_train_fm(const hmo_config *c, int64_t n_rows, const int64_t *rowptr,
         if (rowptr[e] - rowptr[b0] > max_touch) max_touch = rowptr[e] - rowptr[b0];
     }
     uint32_t *touch = (uint32_t *)malloc((size_t)max_touch * sizeof(uint32_t));
-    /* GS is kept per touched slot (slot index stored in cnt-parallel array) */
     uint32_t *slot = (uint32_t *)malloc((size_t)c->dims * sizeof(uint32_t));
     double *GS = (double *)malloc((size_t)max_touch * k * sizeof(double));
     float *dl = (float *)malloc((size_t)B * sizeof(float));
@@ -477,6 +478,7 @@ int hmo_train_fm(const hmo_config *c, int64_t n_rows, const int64_t *rowptr,
         for (int64_t b0 = 0; b0 < n_rows; b0 += B) {
             const int64_t b1 = b0 + B < n_rows ? b0 + B : n_rows;
             const int64_t nb = b1 - b0;
+            const double inv_nb = 1.0 / (double)nb;
             double g0 = 0.0;
             for (int64_t i = b0; i < b1; i++) {
                 float p = fm_score(c, rowptr, idx, val, i, *w0, w, V, S + (i - b0) * k);
@@ -497,30 +499,31 @@ int hmo_train_fm(const hmo_config *c, int64_t n_rows, const int64_t *rowptr,
             for (int64_t i = b0; i < b1; i++)
                 for (int64_t p = rowptr[i]; p < rowptr[i + 1]; p++) {
                     uint32_t j = idx[p];
+                    if ((int64_t)j >= c->dims) return -3;
                     if (cnt[j]++ == 0) {
                         slot[j] = (uint32_t)nt;
                         for (int f = 0; f < k; f++) GS[nt * k + f] = 0.0;
                         touch[nt++] = j;
                     }
-                    double c1 = (double)dl[i - b0] * (double)val[p];
-                    A1[j] += c1;
-                    A2[j] += c1 * (double)val[p];
+                    const float c1 = dl[i - b0] * val[p];
+                    A1[j] += (double)c1;
+                    A2[j] += (double)(c1 * val[p]);
                     double *gs = GS + (int64_t)slot[j] * k;
                     const float *Si = S + (i - b0) * k;
-                    for (int f = 0; f < k; f++) gs[f] += c1 * (double)Si[f];
+                    for (int f = 0; f < k; f++) gs[f] += (double)(c1 * Si[f]);
                 }
             *t += 1;
             const float eta = hmo_eta(c, *t);
-            const double denom = c->grad_norm == HMO_NORM_SUM ? 1.0 : (double)nb;
-            fm_step(c, eta, (float)(g0 / denom), c->lambda_w0, w0, gw0 ? gw0 : &dummy);
+            fm_step(c, eta, c->grad_norm == HMO_NORM_SUM ? (float)g0 : (float)(g0 * inv_nb), c->lambda_w0, w0,
+                    gw0 ? gw0 : &dummy);
             for (int64_t q = 0; q < nt; q++) {
                 uint32_t j = touch[q];
-                double dj = c->grad_norm == HMO_NORM_COUNT ? (double)cnt[j] : denom;
-                fm_step(c, eta, (float)(A1[j] / dj), c->lambda_w, &w[j], gw ? &gw[j] : &dummy);
+                fm_step(c, eta, mean_grad(c, A1[j], cnt[j], inv_nb), c->lambda_w, &w[j], gw ? &gw[j] : &dummy);
                 for (int f = 0; f < k; f++) {
                     float *v = &V[(int64_t)j * k + f];
                     double G = GS[q * k + f] - (double)*v * A2[j];
-                    fm_step(c, eta, (float)(G / dj), c->lambda_v, v, gv ? &gv[(int64_t)j * k + f] : &dummy);
+                    fm_step(c, eta, mean_grad(c, G, cnt[j], inv_nb), c->lambda_v, v,
+                            gv ? &gv[(int64_t)j * k + f] : &dummy);
                 }
                 if (touched) touched[j] = 1;
                 A1[j] = 0.0; A2[j] = 0.0; cnt[j] = 0;
