@@ -42,6 +42,15 @@ TOTAL_ROWS = 24 * ROWS_PER_STEP          # 100,663,296 rows >= the 100M of confi
 OPTIONS = f"-loss logloss -opt ftrl -mini_batch {MINI_BATCH} -dims {DIMS} -alpha 0.05 -lambda1 0.0001"
 NNZ_PER_ROW = 39
 SEED = 1
+# name -> (UDTF, options, label).  The default is BASELINE.json configs[1]; "fm16" is configs[2]
+# (a secondary measurement: `python bench.py --workload fm16`).
+WORKLOADS = {
+    "ftrl": ("train_classifier", OPTIONS,
+             "configs[1]: train_classifier logistic+FTRL, 2^24 hashed dims, Criteo-shaped synthetic (39 feats/row), "
+             "100M rows per GPU"),
+    "fm16": ("train_fm", f"-factors 16 -classification -opt adagrad -mini_batch {MINI_BATCH} -dims {DIMS} -eta0 0.05",
+             "configs[2]: train_fm k=16 AdaGrad, 2^24 hashed dims, Criteo-shaped synthetic (39 feats/row)"),
+}
 
 
 def parse_args():
@@ -53,6 +62,7 @@ def parse_args():
     ap.add_argument("--rows-per-step", type=int, default=ROWS_PER_STEP)
     ap.add_argument("--total-rows", type=int, default=TOTAL_ROWS)
     ap.add_argument("--cpu-sample-rows", type=int, default=0, help="0 = sized for ~15 s")
+    ap.add_argument("--workload", default="ftrl", choices=sorted(WORKLOADS))
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     return ap.parse_args()
@@ -139,13 +149,15 @@ def measured_peaks() -> tuple[float, str]:
         return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
-def cpu_baseline(rows: int, threads: int) -> dict:
-    """Oracle (OpenMP) on the first `rows` rows of the same synthetic stream."""
+def cpu_baseline(rows: int, threads: int, workload: str = "ftrl") -> dict:
+    """Oracle (OpenMP for the linear learner, scalar for train_fm) on the first `rows` rows of
+    the same synthetic stream."""
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     import hivemall_b200 as hm
     from hivemall_b200 import synth
     import _oracle
-    cfg = _oracle.config_from(hm.parse_options("train_classifier", OPTIONS))
+    fn, options, _ = WORKLOADS[workload]
+    cfg = _oracle.config_from(hm.parse_options(fn, options))
     pieces = []
     for r0 in range(0, rows, 1 << 20):
         pieces.append(synth.criteo_like(min(1 << 20, rows - r0), dims=DIMS, seed=SEED, row0=r0))
@@ -154,13 +166,21 @@ def cpu_baseline(rows: int, threads: int) -> dict:
     value = np.concatenate([p.value.numpy() for p in pieces])
     label = np.concatenate([p.label.numpy() for p in pieces])
     rowptr = np.arange(rows + 1, dtype=np.int64) * NNZ_PER_ROW
-    _oracle.train_linear_mt(cfg, rowptr[: MINI_BATCH + 1], feature, value, label[:MINI_BATCH], threads)  # page in
-    t0 = time.perf_counter()
-    _oracle.train_linear_mt(cfg, rowptr, feature, value, label, threads)
-    dt = time.perf_counter() - t0
+    if fn == "train_fm":
+        threads = 1
+        t0 = time.perf_counter()
+        _oracle.train_fm(cfg, rowptr, feature, value, label)
+        dt = time.perf_counter() - t0
+        what = "hmo_train_fm (scalar)"
+    else:
+        _oracle.train_linear_mt(cfg, rowptr[: MINI_BATCH + 1], feature, value, label[:MINI_BATCH], threads)  # page in
+        t0 = time.perf_counter()
+        _oracle.train_linear_mt(cfg, rowptr, feature, value, label, threads)
+        dt = time.perf_counter() - t0
+        what = f"hmo_train_linear_mt ({threads} OpenMP threads)"
     return {"value": rows / dt, "unit": "examples/s", "cores": threads, "kind": "port",
-            "sample": f"first {rows} rows of the same stream, {OPTIONS}, oracle/hm_oracle.c hmo_train_linear_mt "
-                      f"({threads} OpenMP threads, {dt:.1f} s); kind=port because the reference mount holds no code",
+            "sample": f"first {rows} rows of the same stream, {options}, oracle/hm_oracle.c {what}, {dt:.1f} s; "
+                      f"kind=port because the reference mount holds no code",
             "seconds": dt}
 
 
@@ -170,23 +190,23 @@ def run_reference_arm(args) -> None:
         return
     threads = os.cpu_count() or 1
     # calibrate so that each step is a bounded sample (~5 s), whole run within a few minutes
-    probe = cpu_baseline(2 * MINI_BATCH, threads)
+    probe = cpu_baseline(2 * MINI_BATCH, threads, args.workload)
     rows = int(max(2 * MINI_BATCH, min(probe["value"] * 5.0, 16 * MINI_BATCH)))
     rows = rows // MINI_BATCH * MINI_BATCH
     times = []
     for i in range(args.warmup + args.steps):
-        r = cpu_baseline(rows, threads)
+        r = cpu_baseline(rows, threads, args.workload)
         if i >= args.warmup:
             times.append(r["seconds"])
     dt = sum(times) / len(times)
     value = rows / dt
     out = {
-        "impl": "reference", "metric": "examples/sec (train_classifier logloss+FTRL, 2^24 hashed dims, Criteo-shaped)",
+        "impl": "reference", "metric": METRIC[args.workload],
         "value": value, "unit": "examples/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32 (fp64 sums)", "data": "synthetic",
-        "config": {"workload": "configs[1]: train_classifier logistic+FTRL, 2^24 dims, Criteo-shaped 39 feats/row",
-                   "options": OPTIONS, "mini_batch": MINI_BATCH, "rows_per_step": rows,
+        "config": {"workload": WORKLOADS[args.workload][2],
+                   "options": WORKLOADS[args.workload][1], "mini_batch": MINI_BATCH, "rows_per_step": rows,
                    "note": "CPU arm; each step is a bounded sample of the stream"},
         "cpu_baseline": {"value": value, "unit": "examples/s", "cores": threads, "kind": "port",
                          "sample": f"{rows} rows per step, OpenMP oracle; the reference mount holds no code to run"},
@@ -195,6 +215,9 @@ def run_reference_arm(args) -> None:
     }
     print(json.dumps(out))
 
+
+METRIC = {"ftrl": "examples/sec (train_classifier logloss+FTRL, 2^24 hashed dims, Criteo-shaped)",
+          "fm16": "examples/sec (train_fm k=16 AdaGrad, 2^24 hashed dims, Criteo-shaped)"}
 
 # ------------------------------------------------------------------------- GPU arm
 
@@ -244,7 +267,8 @@ def main():
         torch.cuda.synchronize()
 
     # ---- device-resident arm ------------------------------------------------------
-    u = hm.train_classifier(OPTIONS, device=local_rank)
+    fn, options, wl_label = WORKLOADS[args.workload]
+    u = hm.UDTF(options, local_rank, function_name=fn)
     mixer = mix.ReplicaMixer(u, world) if world > 1 else None
     stream = torch.cuda.ExternalStream(u.stream, device=dev)
 
@@ -325,7 +349,7 @@ def main():
                 arrs.append((addr, pinned))
             host.append(arrs)
         torch.cuda.synchronize()
-        v = hm.train_classifier(OPTIONS, device=local_rank)
+        v = hm.UDTF(options, local_rank, function_name=fn)
         mixer2 = mix.ReplicaMixer(v, world) if world > 1 else None
         margins = np.empty(MINI_BATCH, dtype=np.float32)
         losses = []
@@ -368,26 +392,25 @@ def main():
         threads = os.cpu_count() or 1
         rows = args.cpu_sample_rows
         if rows <= 0:
-            probe = cpu_baseline(2 * MINI_BATCH, threads)
-            rows = int(max(2 * MINI_BATCH, min(probe["value"] * 15.0, 256 * MINI_BATCH)))
+            probe = cpu_baseline(2 * MINI_BATCH, threads, args.workload)
+            rows = int(max(2 * MINI_BATCH, min(probe["value"] * 15.0, 1024 * MINI_BATCH)))
         rows = max(MINI_BATCH, rows // MINI_BATCH * MINI_BATCH)
-        cpu = cpu_baseline(rows, threads)
+        cpu = cpu_baseline(rows, threads, args.workload)
         cpu.pop("seconds", None)
 
     if rank == 0:
         out = {
-            "metric": "examples/sec (train_classifier logloss+FTRL, 2^24 hashed dims, Criteo-shaped)",
+            "metric": METRIC[args.workload],
             "value": rows_per_s, "unit": "examples/s", "n_gpus": world, "steps": K, "warmup": W,
             "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32 (fp64 sums)", "data": "synthetic",
             "nnz_per_sec": rows_per_s * NNZ_PER_ROW,
             "config": {
-                "workload": "configs[1]: train_classifier logistic+FTRL, 2^24 hashed dims, Criteo-shaped "
-                            "synthetic (39 feats/row), 100M rows per GPU",
-                "options": OPTIONS, "mini_batch": MINI_BATCH, "rows_per_step": rps,
+                "workload": wl_label,
+                "options": options, "mini_batch": MINI_BATCH, "rows_per_step": rps,
                 "mini_batches_per_step": rps // MINI_BATCH, "rows_resident_per_gpu": n_blocks * rps,
                 "l2": "inputs larger than L2 (1.3 GB streamed per step)",
-                "mix": "all-reduce of w and (z,n) every step" if world > 1 else "none (1 GPU)",
+                "mix": "all-reduce of every replica array every step (64 mini-batches)" if world > 1 else "none (1 GPU)",
                 "parallelism": f"dp{world}: row shards, full replica per GPU",
             },
             "roofline": roofline,
