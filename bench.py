@@ -319,9 +319,15 @@ def main():
     d = kt[dom]
     peak, peak_src = measured_peaks()
     achieved = (d["bytes"] / d["launches"]) / (d["ms"] / d["launches"] * 1e-3) / 1e9 if d["ms"] > 0 else 0.0
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            tj = json.load(f)
+        traffic, traffic_src = tj.get(dom), tj.get("capture")
+    except Exception:
+        traffic, traffic_src = None, None
     roofline = {
         "bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s",
-        "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+        "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
         "launches": d["launches"], "avg_us": d["ms"] / d["launches"] * 1e3,
         "algorithmic_bytes_per_launch": d["bytes"] / d["launches"],
         "share_of_kernel_time": d["ms"] / total_kernel_ms if total_kernel_ms else None,
