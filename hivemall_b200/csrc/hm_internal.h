@@ -54,8 +54,8 @@ struct SortScratch {
     // device
     uint32_t *key[2] = {nullptr, nullptr};   // feature ids, ping-pong
     uint2 *pay[2] = {nullptr, nullptr};      // (row inside the mini-batch, value bits), ping-pong
-    uint32_t *erow = nullptr;                // row id of every element of the block (input of pass 1)
     uint32_t *tile_hist = nullptr;     // [seg][digit][tile_in_seg]
+    int32_t *tile_row0 = nullptr;      // first row (inside its mini-batch) of every tile
     uint32_t *row_sum = nullptr;       // [seg*256 + digit] (+1)
     uint32_t *seg_off = nullptr;       // [kMaxSegs+1] element offset of each mini-batch in the block
     uint32_t *seg_tile_off = nullptr;  // [kMaxSegs+1]
@@ -70,7 +70,9 @@ hm_status launch_seg_prep(Launcher &L, SortScratch &s, const int64_t *d_rowptr, 
 // Stable sort of each segment by the low `key_bits` bits of the feature id.
 // Result: s.key[*out_buf], s.pay[*out_buf] hold (feature, (row, value)) sorted per segment.
 hm_status launch_segmented_sort(Launcher &L, SortScratch &s, const uint32_t *d_feature_block,
-                                const float *d_value_block, int64_t n_elems, int n_segs, int key_bits, int *out_buf);
+                                const float *d_value_block, const int64_t *d_rowptr, int64_t block_row0,
+                                int64_t block_rows, int32_t mini_batch, int64_t n_elems, int n_segs, int key_bits,
+                                int *out_buf);
 
 // ---- hashing (hm_hash.cu) -----------------------------------------------------
 hm_status launch_mhash(Launcher &L, const uint8_t *d_bytes, const int64_t *d_offsets, int64_t n,

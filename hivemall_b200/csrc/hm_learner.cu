@@ -264,8 +264,8 @@ hm_status train_rows(hm_udtf *u, const Chunk &c, int64_t row0, int64_t n_rows, c
         }
         HM_TRY(launch_seg_prep(u->L, u->sort, c.rp(), b_row0, b_rows, b_nnz, B, n_segs));
         int buf = 0;
-        HM_TRY(launch_segmented_sort(u->L, u->sort, c.ft() + mb_abs[m0], c.vl() + mb_abs[m0], b_nnz, n_segs, key_bits,
-                                     &buf));
+        HM_TRY(launch_segmented_sort(u->L, u->sort, c.ft() + mb_abs[m0], c.vl() + mb_abs[m0], c.rp(), b_row0, b_rows, B,
+                                     b_nnz, n_segs, key_bits, &buf));
         for (int s = 0; s < n_segs; s++) {
             const int64_t mrow0 = b_row0 + (int64_t)s * B;
             const int32_t mrows = (int32_t)std::min<int64_t>(B, row0 + n_rows - mrow0);

@@ -14,8 +14,8 @@
 //
 // Per 8-bit digit pass:  hist (reads keys, 4 B/elem)  ->  two tiny scans  ->
 // scatter (reads key+payload, writes key+payload, 24 B/elem).  The first pass reads the
-// CSR feature/value arrays directly plus the row ids written by expand_rows, so no copy of
-// the input is made.  Integer counting only; atomics are integer (order-independent).
+// CSR feature/value arrays directly and looks the row ids up in the row pointer (20 B/elem),
+// so no copy of the input is made.  Integer counting only; atomics are integer (order-independent).
 #include "hm_internal.h"
 
 namespace hm {
@@ -60,20 +60,6 @@ __global__ void seg_prep_kernel(const int64_t *__restrict__ rowptr, int64_t row0
     }
 }
 
-// erow[e] = row of element e counted from the start of its mini-batch.  Warp per row.
-__global__ void __launch_bounds__(256)
-expand_rows_kernel(const int64_t *__restrict__ rowptr, int64_t row0, int64_t n_rows, int32_t mini_batch,
-                   uint32_t *__restrict__ erow)
-{
-    const int lane = threadIdx.x & 31;
-    const int64_t base = rowptr[row0];
-    for (int64_t r = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5); r < n_rows; r += (int64_t)gridDim.x * 8) {
-        const int64_t p0 = rowptr[row0 + r] - base, p1 = rowptr[row0 + r + 1] - base;
-        const uint32_t local = (uint32_t)(r % mini_batch);
-        for (int64_t p = p0 + lane; p < p1; p += 32) erow[p] = local;
-    }
-}
-
 // Which segment does global tile index `tile` belong to?  (last s with tile_off[s] <= tile)
 __device__ __forceinline__ int find_seg(const uint32_t *tile_off, int n_segs, uint32_t tile)
 {
@@ -83,6 +69,26 @@ __device__ __forceinline__ int find_seg(const uint32_t *tile_off, int n_segs, ui
         if (tile_off[mid] <= tile) lo = mid; else hi = mid;
     }
     return lo;
+}
+
+// One thread per sort tile: the row of the mini-batch that holds the tile's first element.
+__global__ void tile_row0_kernel(const int64_t *__restrict__ rowptr, int64_t block_row0, int64_t block_rows,
+                                 int32_t mini_batch, const uint32_t *__restrict__ seg_off,
+                                 const uint32_t *__restrict__ seg_tile_off, int n_segs, int32_t *__restrict__ tile_row0)
+{
+    const uint32_t total = seg_tile_off[n_segs];
+    const int64_t base = rowptr[block_row0];
+    for (uint32_t tile = blockIdx.x * blockDim.x + threadIdx.x; tile < total; tile += gridDim.x * blockDim.x) {
+        const int seg = find_seg(seg_tile_off, n_segs, tile);
+        const uint32_t e0 = seg_off[seg] + (tile - seg_tile_off[seg]) * kSortTile;
+        const int64_t *rp = rowptr + block_row0 + (int64_t)seg * mini_batch;
+        int lo = 0, hi = (int)min((int64_t)mini_batch, block_rows - (int64_t)seg * mini_batch);
+        while (hi - lo > 1) {   // rp[lo] - base <= e0 < rp[hi] - base
+            const int mid = (lo + hi) >> 1;
+            if ((uint32_t)(rp[mid] - base) <= e0) lo = mid; else hi = mid;
+        }
+        tile_row0[tile] = lo;
+    }
 }
 
 __global__ void __launch_bounds__(kSortThreads)
@@ -173,12 +179,25 @@ scan_tiles_kernel(uint32_t *__restrict__ tile_hist, const uint32_t *__restrict__
     }
 }
 
+// First pass only: the row of an element is not stored anywhere, it is looked up in the CSR row
+// pointer.  Per tile one warp finds the row holding the tile's first element (32-ary search, a
+// handful of L2 round trips), the CTA stages the row-pointer slice that covers the tile in shared
+// memory, and every element binary-searches that slice.
+struct RowLookup {
+    const int64_t *rowptr;   // chunk row pointer
+    int64_t block_row0;      // first row of the block
+    int64_t block_rows;      // rows in the block
+    int32_t mini_batch;
+    const int32_t *tile_row0; // first row (inside its mini-batch) of every sort tile
+};
+constexpr int kRowSlice = 1024;   // staged row-pointer entries; tiles that need more fall back to global searches
+
 constexpr size_t kScatterSmem = (size_t)kSortTile * 4 + (size_t)kSortTile * 8;   // keys + payloads
 
 template <bool FIRST>
 __global__ void __launch_bounds__(kScatThreads, kScatCtasPerSm)
 sort_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint2 *__restrict__ pay_in,
-                    const uint32_t *__restrict__ erow_in, const float *__restrict__ val_in,
+                    RowLookup rl, const float *__restrict__ val_in,
                     uint32_t *__restrict__ keys_out, uint2 *__restrict__ pay_out,
                     const uint32_t *__restrict__ seg_off, const uint32_t *__restrict__ seg_tile_off,
                     int n_segs, int shift, const uint32_t *__restrict__ tile_hist)
@@ -189,6 +208,8 @@ sort_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint2 *__restric
     __shared__ uint32_t s_off[kMaxSegs + 1], s_toff[kMaxSegs + 1];
     __shared__ uint32_t wcnt[kScatWarps][kRadix];
     __shared__ uint32_t dig_base[kRadix], gofs[kRadix], warp_tot[kRadix / 32];
+    __shared__ uint32_t s_rows[FIRST ? kRowSlice + 1 : 1];
+    __shared__ int s_nr;
     for (int s = threadIdx.x; s <= n_segs; s += kScatThreads) { s_off[s] = seg_off[s]; s_toff[s] = seg_tile_off[s]; }
     __syncthreads();
     const uint32_t total = s_toff[n_segs];
@@ -198,11 +219,22 @@ sort_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint2 *__restric
     uint32_t key[kScatItems], rank[kScatItems];
     uint32_t tile = blockIdx.x;
     int seg = 0; uint32_t tis = 0, nt = 0, e0 = 0, e1 = 0;
+    int cur_ra = 0; uint32_t slice_v = 0;   // first pass: the tile's first row and one row-pointer entry per thread
+    // row-pointer entry `ra + tid` of a tile, relative to the block (first pass only)
+    auto load_slice = [&](int sg, uint32_t tl, int *ra_out) -> uint32_t {
+        const int ra = rl.tile_row0[tl];
+        *ra_out = ra;
+        const int mb_rows = (int)min((int64_t)rl.mini_batch, rl.block_rows - (int64_t)sg * rl.mini_batch);
+        const int64_t r = (int64_t)ra + threadIdx.x;
+        if (r > mb_rows) return 0xffffffffu;
+        return (uint32_t)(rl.rowptr[rl.block_row0 + (int64_t)sg * rl.mini_batch + r] - rl.rowptr[rl.block_row0]);
+    };
     if (tile < total) {
         seg = find_seg(s_toff, n_segs, tile);
         tis = tile - s_toff[seg]; nt = s_toff[seg + 1] - s_toff[seg];
         e0 = s_off[seg] + tis * kSortTile;
         e1 = min(e0 + (uint32_t)kSortTile, s_off[seg + 1]);
+        if (FIRST) slice_v = load_slice(seg, tile, &cur_ra);
 #pragma unroll
         for (int i = 0; i < kScatItems; i++) {
             const uint32_t e = e0 + warp * (32 * kScatItems) + lane + i * 32;
@@ -214,11 +246,68 @@ sort_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint2 *__restric
         const uint32_t ew = e0 + warp * (32 * kScatItems) + lane;
         // payloads are requested now and consumed after the ranking
         uint2 pay[kScatItems];
+        if (FIRST) {
+            const int64_t base = rl.rowptr[rl.block_row0];
+            const int64_t mb_row0 = rl.block_row0 + (int64_t)seg * rl.mini_batch;
+            const int mb_rows = (int)min((int64_t)rl.mini_batch, rl.block_rows - (int64_t)seg * rl.mini_batch);
+            const int64_t *rp = rl.rowptr + mb_row0;
+            const int ra = cur_ra;
+            // stage rp[ra ..] - base.  The first kScatThreads entries were prefetched into `slice_v`
+            // with the keys and almost always cover the tile (one barrier); otherwise keep loading.
+            int nr = min(kScatThreads - 1, mb_rows - ra);
+            if ((int)threadIdx.x <= nr) s_rows[threadIdx.x] = slice_v;
+            __syncthreads();
+            if (s_rows[nr] < e1) {            // uniform: the prefetched part does not reach the tile's end
+                nr = -1;
+                for (int i0 = kScatThreads; i0 <= kRowSlice; i0 += kScatThreads) {
+                    if (threadIdx.x == 0) s_nr = 0x7fffffff;
+                    __syncthreads();
+                    const int i = i0 + threadIdx.x;
+                    int hit = 0x7fffffff;
+                    if (i <= kRowSlice && ra + i <= mb_rows) {
+                        const uint32_t v = (uint32_t)(rp[ra + i] - base);
+                        s_rows[i] = v;
+                        if (v >= e1) hit = i;
+                    }
+                    const int wmin = __reduce_min_sync(0xffffffffu, hit);
+                    if (lane == 0 && wmin != 0x7fffffff) atomicMin(&s_nr, wmin);
+                    __syncthreads();
+                    const int got = s_nr;
+                    __syncthreads();
+                    if (got != 0x7fffffff) { nr = got; break; }
+                }
+            }
+            // a thread's elements are 32 apart and ascending: search once, then walk forward
+            int idx = 0;
+            bool searched = false;
 #pragma unroll
-        for (int i = 0; i < kScatItems; i++) {
-            const uint32_t e = ew + i * 32;
-            if (e < e1) pay[i] = FIRST ? make_uint2(__ldcs(erow_in + e), __float_as_uint(__ldcs(val_in + e)))
-                                       : __ldcs(pay_in + e);
+            for (int i = 0; i < kScatItems; i++) {
+                const uint32_t e = ew + i * 32;
+                if (e < e1) {
+                    int row;
+                    if (nr >= 0) {
+                        if (!searched) {
+                            int lo = 0, hi = nr;        // s_rows[lo] <= e < s_rows[hi]
+                            while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (s_rows[mid] <= e) lo = mid; else hi = mid; }
+                            idx = lo; searched = true;
+                        } else {
+                            while (s_rows[idx + 1] <= e) idx++;     // s_rows[nr] >= e1 > e bounds the walk
+                        }
+                        row = ra + idx;
+                    } else {
+                        int lo = ra, hi = mb_rows;  // slice too small (very short rows): search the row pointer itself
+                        while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if ((uint32_t)(rp[mid] - base) <= e) lo = mid; else hi = mid; }
+                        row = lo;
+                    }
+                    pay[i] = make_uint2((uint32_t)row, __float_as_uint(__ldcs(val_in + e)));
+                }
+            }
+        } else {
+#pragma unroll
+            for (int i = 0; i < kScatItems; i++) {
+                const uint32_t e = ew + i * 32;
+                if (e < e1) pay[i] = __ldcs(pay_in + e);
+            }
         }
         for (int q = threadIdx.x; q < kScatWarps * kRadix; q += kScatThreads) (&wcnt[0][0])[q] = 0;
         __syncthreads();
@@ -286,6 +375,7 @@ sort_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint2 *__restric
             ntis = next - s_toff[nseg]; nnt = s_toff[nseg + 1] - s_toff[nseg];
             ne0 = s_off[nseg] + ntis * kSortTile;
             ne1 = min(ne0 + (uint32_t)kSortTile, s_off[nseg + 1]);
+            if (FIRST) slice_v = load_slice(nseg, next, &cur_ra);
 #pragma unroll
             for (int i = 0; i < kScatItems; i++) {
                 const uint32_t e = ne0 + warp * (32 * kScatItems) + lane + i * 32;
@@ -327,17 +417,17 @@ hm_status sort_scratch_reserve(SortScratch &s, int64_t elems)
             s.key[b] = nullptr; s.pay[b] = nullptr;
         }
         if (s.tile_hist) cudaFree(s.tile_hist);
-        if (s.erow) cudaFree(s.erow);
-        s.tile_hist = nullptr; s.erow = nullptr;
+        if (s.tile_row0) cudaFree(s.tile_row0);
+        s.tile_hist = nullptr; s.tile_row0 = nullptr;
         s.cap_elems = 0;
         int64_t cap = elems + elems / 8;
         for (int b = 0; b < 2; b++) {
             HM_CUDA(cudaMalloc(&s.key[b], (size_t)cap * sizeof(uint32_t)));
             HM_CUDA(cudaMalloc(&s.pay[b], (size_t)cap * sizeof(uint2)));
         }
-        HM_CUDA(cudaMalloc(&s.erow, (size_t)cap * sizeof(uint32_t)));
         s.cap_tiles = cap / kSortTile + kMaxSegs + 1;
         HM_CUDA(cudaMalloc(&s.tile_hist, (size_t)s.cap_tiles * kRadix * sizeof(uint32_t)));
+        HM_CUDA(cudaMalloc(&s.tile_row0, (size_t)s.cap_tiles * sizeof(int32_t)));
         s.cap_elems = cap;
     }
     return HM_OK;
@@ -346,8 +436,8 @@ hm_status sort_scratch_reserve(SortScratch &s, int64_t elems)
 void sort_scratch_free(SortScratch &s)
 {
     for (int b = 0; b < 2; b++) { cudaFree(s.key[b]); cudaFree(s.pay[b]); s.key[b] = nullptr; s.pay[b] = nullptr; }
-    cudaFree(s.tile_hist); cudaFree(s.row_sum); cudaFree(s.seg_off); cudaFree(s.seg_tile_off); cudaFree(s.erow);
-    s.tile_hist = s.row_sum = s.seg_off = s.seg_tile_off = s.erow = nullptr;
+    cudaFree(s.tile_hist); cudaFree(s.row_sum); cudaFree(s.seg_off); cudaFree(s.seg_tile_off); cudaFree(s.tile_row0);
+    s.tile_hist = s.row_sum = s.seg_off = s.seg_tile_off = nullptr; s.tile_row0 = nullptr;
     s.cap_elems = s.cap_tiles = 0;
 }
 
@@ -358,16 +448,19 @@ hm_status launch_seg_prep(Launcher &L, SortScratch &s, const int64_t *d_rowptr, 
     HM_LAUNCH(L, K_SEG_PREP, 0.0,
               (seg_prep_kernel<<<1, 256, 0, L.stream>>>(d_rowptr, row0, n_rows, mini_batch, n_segs, s.seg_off,
                                                         s.seg_tile_off)));
-    // row id of every element (4 B/elem written; rowptr read once)
-    HM_LAUNCH(L, K_SEG_PREP, 4.0 * (double)n_elems + 8.0 * (double)n_rows,
-              (expand_rows_kernel<<<persistent_grid((n_rows + 7) / 8, 8), 256, 0, L.stream>>>(
-                  d_rowptr, row0, n_rows, mini_batch, s.erow)));
+    // first row of every sort tile (one thread per tile; used by the first scatter pass)
+    const int64_t max_tiles = n_elems / kSortTile + n_segs;
+    HM_LAUNCH(L, K_SEG_PREP, 0.0,
+              (tile_row0_kernel<<<persistent_grid((max_tiles + 127) / 128, 8), 128, 0, L.stream>>>(
+                  d_rowptr, row0, n_rows, mini_batch, s.seg_off, s.seg_tile_off, n_segs, s.tile_row0)));
     HM_CUDA(cudaGetLastError());
     return HM_OK;
 }
 
 hm_status launch_segmented_sort(Launcher &L, SortScratch &s, const uint32_t *d_feature_block,
-                                const float *d_value_block, int64_t n_elems, int n_segs, int key_bits, int *out_buf)
+                                const float *d_value_block, const int64_t *d_rowptr, int64_t block_row0,
+                                int64_t block_rows, int32_t mini_batch, int64_t n_elems, int n_segs, int key_bits,
+                                int *out_buf)
 {
     static bool attr_set = false;   // > 48 KB of dynamic shared memory needs opting in, once per process
     if (!attr_set) {
@@ -382,6 +475,9 @@ hm_status launch_segmented_sort(Launcher &L, SortScratch &s, const uint32_t *d_f
     const int64_t max_tiles = n_elems / kSortTile + n_segs;
     const int grid = persistent_grid(max_tiles, 6);
     const int rows = n_segs * kRadix;
+    RowLookup rl;
+    rl.rowptr = d_rowptr; rl.block_row0 = block_row0; rl.block_rows = block_rows; rl.mini_batch = mini_batch;
+    rl.tile_row0 = s.tile_row0;
     for (int p = 0; p < passes; p++) {
         const int shift = 8 * p;
         const uint32_t *kin = p == 0 ? d_feature_block : s.key[(p - 1) & 1];
@@ -397,14 +493,14 @@ hm_status launch_segmented_sort(Launcher &L, SortScratch &s, const uint32_t *d_f
                   (scan_tiles_kernel<<<(rows + kSortWarps - 1) / kSortWarps, kSortThreads, 0, L.stream>>>(
                       s.tile_hist, s.row_sum, s.seg_tile_off, n_segs)));
         if (p == 0)
-            HM_LAUNCH(L, K_SORT_SCATTER, 24.0 * (double)n_elems,
+            HM_LAUNCH(L, K_SORT_SCATTER, 20.0 * (double)n_elems + 8.0 * (double)block_rows,
                       (sort_scatter_kernel<true><<<grid, kScatThreads, kScatterSmem, L.stream>>>(
-                          kin, pin, s.erow, d_value_block, kout, pout, s.seg_off, s.seg_tile_off, n_segs, shift,
+                          kin, pin, rl, d_value_block, kout, pout, s.seg_off, s.seg_tile_off, n_segs, shift,
                           s.tile_hist)));
         else
             HM_LAUNCH(L, K_SORT_SCATTER, 24.0 * (double)n_elems,
                       (sort_scatter_kernel<false><<<grid, kScatThreads, kScatterSmem, L.stream>>>(
-                          kin, pin, nullptr, nullptr, kout, pout, s.seg_off, s.seg_tile_off, n_segs, shift,
+                          kin, pin, rl, nullptr, kout, pout, s.seg_off, s.seg_tile_off, n_segs, shift,
                           s.tile_hist)));
     }
     HM_CUDA(cudaGetLastError());
