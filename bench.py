@@ -335,6 +335,9 @@ def main():
                         "GBps": round(v["bytes"] / (v["ms"] * 1e-3) / 1e9, 1) if v["ms"] > 0 and v["bytes"] > 0 else None}
                     for k, v in sorted(kt.items(), key=lambda kv: -kv[1]["ms"])},
         "profiled_ms_per_step": ms_prof / K,
+        "note": "per-kernel times come from a second pass of the same K steps with a CUDA-event pair around every "
+                "launch and the sort/train stream overlap switched off (each kernel timed alone); `value` comes "
+                "from the plain pass with the overlap on",
     }
     # whole-pipeline view: algorithmic bytes of every kernel over the plain timed region
     pipeline_bytes = sum(v["bytes"] for v in kt.values()) / K

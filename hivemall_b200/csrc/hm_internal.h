@@ -72,7 +72,7 @@ hm_status launch_seg_prep(Launcher &L, SortScratch &s, const int64_t *d_rowptr, 
 hm_status launch_segmented_sort(Launcher &L, SortScratch &s, const uint32_t *d_feature_block,
                                 const float *d_value_block, const int64_t *d_rowptr, int64_t block_row0,
                                 int64_t block_rows, int32_t mini_batch, int64_t n_elems, int n_segs, int key_bits,
-                                int *out_buf);
+                                int *out_buf, int ctas_per_sm);
 
 // ---- hashing (hm_hash.cu) -----------------------------------------------------
 hm_status launch_mhash(Launcher &L, const uint8_t *d_bytes, const int64_t *d_offsets, int64_t n,
@@ -84,7 +84,6 @@ hm_status launch_feature_hashing(Launcher &L, const uint8_t *d_bytes, const int6
 struct StepScalars {      // per mini-batch scalars computed on the host in double
     float eta;
     float adam_alpha;
-    double inv_denom_unused;
     int32_t n_rows;       // rows in this mini-batch
 };
 struct LinearArgs {

@@ -18,6 +18,7 @@
 #include <cmath>
 #include <cstdio>
 #include <cstring>
+#include <cstdlib>
 #include <new>
 
 namespace hm {
@@ -72,7 +73,10 @@ void Launcher::release()
 namespace {
 
 constexpr int64_t kBlockElemCap = (int64_t)1 << 26;   // elements sorted per launch set
-constexpr int64_t kSliceRows = (int64_t)1 << 21;      // host rows copied per H2D slice
+// Host rows copied per H2D slice.  Small enough that the training of the last slice of a call
+// (which cannot overlap a copy) is short, large enough for >= 4 mini-batches per sort block:
+// measured on B200 (bench.py e2e, mini-batch 65536): 2^21 -> 127 M rows/s, 2^20 -> 142, 2^19 -> 151, 2^18 -> 154.
+constexpr int64_t kSliceRows = (int64_t)1 << 19;
 
 struct DevBuf {
     void *p = nullptr;
@@ -141,9 +145,11 @@ using namespace hm;
 struct hm_udtf {
     hm_config cfg;
     int device = 0;
-    Launcher L;
-    cudaStream_t compute = nullptr, copy = nullptr;
-    cudaEvent_t copied_ev = nullptr, stage_ev[2] = {nullptr, nullptr};
+    Launcher L, Ls;                  // compute stream / sort stream
+    cudaStream_t compute = nullptr, copy = nullptr, sorter = nullptr;
+    cudaEvent_t sorted_ev[2] = {nullptr, nullptr}, trained_ev[2] = {nullptr, nullptr}, ready_ev = nullptr;
+    bool trained_valid[2] = {false, false};
+    cudaEvent_t stage_ev[2] = {nullptr, nullptr};
     // model replica
     float *rec = nullptr;            // dims x rec_width floats: (w[, slot1[, slot2, unused]]) per feature
     int rec_width = 1;
@@ -157,10 +163,10 @@ struct hm_udtf {
     DevBuf stab, exp_vif;
     int64_t t = 0;
     // scratch
-    SortScratch sort;
+    SortScratch sort[2];             // block k+1 is sorted (sort stream) while block k trains (compute stream)
     UpdateScratch upd;
     ExportScratch exp;
-    DevBuf margin, dloss, contrib, mb_gather, exp_feat, exp_weight, tmp_a, tmp_b, tmp_c, tmp_d;
+    DevBuf margin, dloss, mb_gather, exp_feat, exp_weight, tmp_a, tmp_b, tmp_c, tmp_d;
     uint32_t *d_bad = nullptr;
     int64_t *d_total = nullptr;
     // data
@@ -235,6 +241,10 @@ int table_stride(const hm_udtf *u) { return u->fm ? u->ww : u->rec_width; }
 
 // Train rows [row0, row0+n_rows) of a chunk.  mb_abs[i] is the chunk rowptr value at
 // row0 + min(i*B, n_rows), i = 0..n_mb.
+//
+// The rows are cut into blocks (<= kMaxSegs mini-batches, <= kBlockElemCap elements).  Sorting a
+// block needs only the data, so block k+1 is sorted on the sort stream while block k trains on
+// the compute stream (two scratch sets, two events each way).
 hm_status train_rows(hm_udtf *u, const Chunk &c, int64_t row0, int64_t n_rows, const int64_t *mb_abs, int64_t n_mb)
 {
     if (n_rows <= 0) return HM_OK;
@@ -242,60 +252,96 @@ hm_status train_rows(hm_udtf *u, const Chunk &c, int64_t row0, int64_t n_rows, c
     const int key_bits = bits_for(u->cfg.dims);
     LinearArgs a;
     a.cfg = u->cfg; a.rec = u->rec; a.rec_width = u->rec_width;
-    int64_t m0 = 0;
-    while (m0 < n_mb) {
+    struct Plan { int64_t m0, m1, row0, rows, nnz; int n_segs; };
+    std::vector<Plan> plan;
+    for (int64_t m0 = 0; m0 < n_mb;) {
         // greedy block: <= kMaxSegs mini-batches and <= kBlockElemCap elements (at least one)
         int64_t m1 = m0 + 1;
         while (m1 < n_mb && m1 - m0 < kMaxSegs && mb_abs[m1 + 1] - mb_abs[m0] <= kBlockElemCap) m1++;
-        const int n_segs = (int)(m1 - m0);
-        const int64_t b_row0 = row0 + m0 * B;
-        const int64_t b_rows = std::min<int64_t>(n_rows - m0 * B, (int64_t)n_segs * B);
-        const int64_t b_nnz = mb_abs[m1] - mb_abs[m0];
-        if (b_nnz >= ((int64_t)1 << 31))
-            HM_FAIL(HM_ERR_UNSUPPORTED, "a mini-batch of %lld elements exceeds the 2^31 block limit", (long long)b_nnz);
-        HM_TRY(sort_scratch_reserve(u->sort, b_nnz));
-        HM_TRY(u->margin.reserve((size_t)b_rows * sizeof(float)));
-        HM_TRY(u->dloss.reserve((size_t)std::min<int64_t>(b_rows, B) * sizeof(float)));
+        Plan p;
+        p.m0 = m0; p.m1 = m1; p.n_segs = (int)(m1 - m0);
+        p.row0 = row0 + m0 * B;
+        p.rows = std::min<int64_t>(n_rows - m0 * B, (int64_t)p.n_segs * B);
+        p.nnz = mb_abs[m1] - mb_abs[m0];
+        if (p.nnz >= ((int64_t)1 << 31))
+            HM_FAIL(HM_ERR_UNSUPPORTED, "a mini-batch of %lld elements exceeds the 2^31 block limit", (long long)p.nnz);
+        plan.push_back(p);
+        m0 = m1;
+    }
+    // everything queued on the compute stream so far (copies of these rows included) precedes the sorts
+    HM_CUDA(cudaEventRecord(u->ready_ev, u->compute));
+    HM_CUDA(cudaStreamWaitEvent(u->sorter, u->ready_ev, 0));
+    int out_buf[2] = {0, 0};
+    auto enqueue_sort = [&](size_t bi) -> hm_status {
+        const Plan &p = plan[bi];
+        const int set = (int)(bi & 1);
+        // the scratch set is free once the block that used it last has been trained
+        if (u->trained_valid[set]) HM_CUDA(cudaStreamWaitEvent(u->sorter, u->trained_ev[set], 0));
+        HM_TRY(sort_scratch_reserve(u->sort[set], p.nnz));
+        HM_TRY(launch_seg_prep(u->Ls, u->sort[set], c.rp(), p.row0, p.rows, p.nnz, B, p.n_segs));
+        HM_TRY(launch_segmented_sort(u->Ls, u->sort[set], c.ft() + mb_abs[p.m0], c.vl() + mb_abs[p.m0], c.rp(), p.row0,
+                                     p.rows, B, p.nnz, p.n_segs, key_bits, &out_buf[set], 0));
+        HM_CUDA(cudaEventRecord(u->sorted_ev[set], u->sorter));
+        return HM_OK;
+    };
+    // While per-kernel profiling is on, the two streams are serialised so that every kernel is
+    // timed alone (overlapped kernels stretch each other's event-to-event time).
+    const bool overlap = !u->L.profiling;
+    HM_TRY(enqueue_sort(0));
+    for (size_t bi = 0; bi < plan.size(); bi++) {
+        const Plan &p = plan[bi];
+        const int set = (int)(bi & 1);
+        if (bi + 1 < plan.size()) {
+            if (!overlap) {     // the next sort starts only after everything queued for training so far
+                HM_CUDA(cudaEventRecord(u->ready_ev, u->compute));
+                HM_CUDA(cudaStreamWaitEvent(u->sorter, u->ready_ev, 0));
+            }
+            HM_TRY(enqueue_sort(bi + 1));
+            if (!overlap) {     // ... and training waits for it
+                HM_CUDA(cudaStreamWaitEvent(u->compute, u->sorted_ev[(bi + 1) & 1], 0));
+            }
+        }
+        HM_CUDA(cudaStreamWaitEvent(u->compute, u->sorted_ev[set], 0));
+        SortScratch &ss = u->sort[set];
+        const int buf = out_buf[set];
+        HM_TRY(u->margin.reserve((size_t)p.rows * sizeof(float)));
+        HM_TRY(u->dloss.reserve((size_t)std::min<int64_t>(p.rows, B) * sizeof(float)));
         if (u->fm) {
             int64_t max_mb = 0;
-            for (int64_t m = m0; m < m1; m++) max_mb = std::max(max_mb, mb_abs[m + 1] - mb_abs[m]);
+            for (int64_t m = p.m0; m < p.m1; m++) max_mb = std::max(max_mb, mb_abs[m + 1] - mb_abs[m]);
             HM_TRY(fm_scratch_reserve(u->fms, max_mb, u->k));
-            HM_TRY(u->stab.reserve((size_t)std::min<int64_t>(b_rows, B) * u->k * sizeof(float)));
+            HM_TRY(u->stab.reserve((size_t)std::min<int64_t>(p.rows, B) * u->k * sizeof(float)));
         }
-        HM_TRY(launch_seg_prep(u->L, u->sort, c.rp(), b_row0, b_rows, b_nnz, B, n_segs));
-        int buf = 0;
-        HM_TRY(launch_segmented_sort(u->L, u->sort, c.ft() + mb_abs[m0], c.vl() + mb_abs[m0], c.rp(), b_row0, b_rows, B,
-                                     b_nnz, n_segs, key_bits, &buf));
-        for (int s = 0; s < n_segs; s++) {
-            const int64_t mrow0 = b_row0 + (int64_t)s * B;
+        for (int s = 0; s < p.n_segs; s++) {
+            const int64_t mrow0 = p.row0 + (int64_t)s * B;
             const int32_t mrows = (int32_t)std::min<int64_t>(B, row0 + n_rows - mrow0);
-            const int64_t mnnz = mb_abs[m0 + s + 1] - mb_abs[m0 + s];
+            const int64_t mnnz = mb_abs[p.m0 + s + 1] - mb_abs[p.m0 + s];
             u->t += 1;
             StepScalars sc;
             sc.eta = eta_at(u->cfg, u->t);
             sc.adam_alpha = u->cfg.opt == HM_OPT_ADAM ? adam_alpha_at(u->cfg, sc.eta, u->t) : 0.f;
-            sc.inv_denom_unused = 0;
             sc.n_rows = mrows;
             if (u->fm) {
                 const FmArgs fa = fm_args(u);
-                HM_TRY(launch_fm_forward(u->L, fa, c.rp(), mrow0, mrows, b_row0, c.ft(), c.vl(), c.lb(),
+                HM_TRY(launch_fm_forward(u->L, fa, c.rp(), mrow0, mrows, p.row0, c.ft(), c.vl(), c.lb(),
                                          u->margin.as<float>(), u->dloss.as<float>(), u->stab.as<float>(), u->d_bad, mnnz,
                                          true));
-                HM_TRY(launch_fm_update(u->L, fa, sc, u->fms, u->sort.key[buf], u->sort.pay[buf], u->sort.seg_off, s,
+                HM_TRY(launch_fm_update(u->L, fa, sc, u->fms, ss.key[buf], ss.pay[buf], ss.seg_off, s,
                                         u->dloss.as<float>(), u->stab.as<float>(), mnnz));
             } else {
-                HM_TRY(launch_linear_forward(u->L, a, c.rp(), mrow0, mrows, b_row0, c.ft(), c.vl(), c.lb(),
+                HM_TRY(launch_linear_forward(u->L, a, c.rp(), mrow0, mrows, p.row0, c.ft(), c.vl(), c.lb(),
                                              u->margin.as<float>(), u->dloss.as<float>(), u->d_bad, mnnz));
-                HM_TRY(launch_linear_update(u->L, a, sc, u->upd, u->sort.key[buf], u->sort.pay[buf], u->sort.seg_off, s,
+                HM_TRY(launch_linear_update(u->L, a, sc, u->upd, ss.key[buf], ss.pay[buf], ss.seg_off, s,
                                             u->dloss.as<float>(), mnnz));
             }
             u->stats.mini_batches++;
-            u->last_margin_off = mrow0 - b_row0;
+            u->last_margin_off = mrow0 - p.row0;
             u->last_margin_n = mrows;
         }
-        u->stats.rows += b_rows;
-        u->stats.nnz += b_nnz;
-        m0 = m1;
+        HM_CUDA(cudaEventRecord(u->trained_ev[set], u->compute));
+        u->trained_valid[set] = true;
+        u->stats.rows += p.rows;
+        u->stats.nnz += p.nnz;
     }
     return HM_OK;
 }
@@ -441,7 +487,14 @@ hm_status create_impl(const hm_config &cfg, int device, hm_udtf **out)
     hm_status s = [&]() -> hm_status {
         HM_CUDA(cudaStreamCreateWithFlags(&u->compute, cudaStreamNonBlocking));
         HM_CUDA(cudaStreamCreateWithFlags(&u->copy, cudaStreamNonBlocking));
+        HM_CUDA(cudaStreamCreateWithFlags(&u->sorter, cudaStreamNonBlocking));
         u->L.stream = u->compute;
+        u->Ls.stream = u->sorter;
+        for (int i = 0; i < 2; i++) {
+            HM_CUDA(cudaEventCreateWithFlags(&u->sorted_ev[i], cudaEventDisableTiming));
+            HM_CUDA(cudaEventCreateWithFlags(&u->trained_ev[i], cudaEventDisableTiming));
+        }
+        HM_CUDA(cudaEventCreateWithFlags(&u->ready_ev, cudaEventDisableTiming));
         u->state_width = cfg.opt == HM_OPT_SGD ? 0 : (cfg.opt == HM_OPT_ADAGRAD ? 1 : 2);
         if (cfg.task == HM_TASK_FM) {
             u->fm = true;
@@ -602,7 +655,7 @@ hm_status hm_udtf_process(hm_udtf *u, int64_t n_rows, const int64_t *rowptr, con
     DeviceGuard g(u->device);
     // slices sized to whole mini-batches so that copies and training overlap
     const int64_t B = u->cfg.mini_batch;
-    int64_t slice = std::max<int64_t>(kSliceRows / B * B, B);
+    int64_t slice = std::max<int64_t>(kSliceRows / B * B, 4 * B);
     for (int64_t r = 0; r < n_rows; r += slice) {
         const int64_t n = std::min(slice, n_rows - r);
         HM_TRY(process_slice(u, n, rowptr + r, feature, value, label + r));
@@ -713,6 +766,7 @@ hm_status hm_udtf_close(hm_udtf *u, int64_t *n_model_rows)
     u->stats.d2h_bytes += 8;
     u->model_rows = u->h_small[0] + (u->fm ? 1 : 0);   // train_fm: plus the w0 row
     u->L.drain();
+    u->Ls.drain();
     if (n_model_rows) *n_model_rows = u->model_rows;
     return HM_OK;
 }
@@ -763,14 +817,22 @@ hm_status hm_udtf_destroy(hm_udtf *u)
     DeviceGuard g(u->device);
     if (u->compute) cudaStreamSynchronize(u->compute);
     if (u->copy) cudaStreamSynchronize(u->copy);
+    if (u->sorter) cudaStreamSynchronize(u->sorter);
     u->L.release();
+    u->Ls.release();
     for (Chunk *c : u->retained) { c->release(); delete c; }
     for (Chunk *c : u->pool) { c->release(); delete c; }
     if (u->tail) { u->tail->release(); delete u->tail; }
-    sort_scratch_free(u->sort);
+    sort_scratch_free(u->sort[0]);
+    sort_scratch_free(u->sort[1]);
+    for (int i = 0; i < 2; i++) {
+        if (u->sorted_ev[i]) cudaEventDestroy(u->sorted_ev[i]);
+        if (u->trained_ev[i]) cudaEventDestroy(u->trained_ev[i]);
+    }
+    if (u->ready_ev) cudaEventDestroy(u->ready_ev);
     update_scratch_free(u->upd);
     cudaFree(u->exp.counts);
-    for (DevBuf *b : {&u->margin, &u->dloss, &u->contrib, &u->mb_gather, &u->exp_feat, &u->exp_weight, &u->tmp_a,
+    for (DevBuf *b : {&u->margin, &u->dloss, &u->mb_gather, &u->exp_feat, &u->exp_weight, &u->tmp_a,
                       &u->tmp_b, &u->tmp_c, &u->tmp_d})
         b->release();
     cudaFree(u->rec); cudaFree(u->d_bad); cudaFree(u->d_total);
@@ -782,9 +844,9 @@ hm_status hm_udtf_destroy(hm_udtf *u)
         if (u->stage_ev[i]) cudaEventDestroy(u->stage_ev[i]);
     }
     if (u->h_small) cudaFreeHost(u->h_small);
-    if (u->copied_ev) cudaEventDestroy(u->copied_ev);
     if (u->compute) cudaStreamDestroy(u->compute);
     if (u->copy) cudaStreamDestroy(u->copy);
+    if (u->sorter) cudaStreamDestroy(u->sorter);
     cudaGetLastError();
     delete u;
     return HM_OK;
@@ -876,6 +938,7 @@ hm_status hm_udtf_sync(hm_udtf *u)
     if (!u) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "NULL learner");
     DeviceGuard g(u->device);
     HM_CUDA(cudaStreamSynchronize(u->copy));
+    HM_CUDA(cudaStreamSynchronize(u->sorter));
     HM_CUDA(cudaStreamSynchronize(u->compute));
     return HM_OK;
 }
@@ -969,7 +1032,7 @@ hm_status hm_udtf_stats(const hm_udtf *u, hm_stats *out)
 {
     if (!u || !out) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "NULL argument");
     *out = u->stats;
-    out->kernel_launches = u->L.launches;
+    out->kernel_launches = u->L.launches + u->Ls.launches;
     return HM_OK;
 }
 
@@ -977,8 +1040,9 @@ hm_status hm_udtf_set_profiling(hm_udtf *u, int on)
 {
     if (!u) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "NULL learner");
     DeviceGuard g(u->device);
-    if (!on) u->L.drain();
+    if (!on) { u->L.drain(); u->Ls.drain(); }
     u->L.profiling = on != 0;
+    u->Ls.profiling = on != 0;
     return HM_OK;
 }
 
@@ -990,10 +1054,11 @@ hm_status hm_udtf_kernel_time(hm_udtf *u, int i, const char **name, int64_t *lau
     if (!u || i < 0 || i >= K_NUM_KERNELS) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "bad argument");
     DeviceGuard g(u->device);
     u->L.drain();
+    u->Ls.drain();
     if (name) *name = kKernelNames[i];
-    if (launches) *launches = u->L.count[i];
-    if (total_ms) *total_ms = u->L.ms[i];
-    if (algorithmic_bytes) *algorithmic_bytes = u->L.bytes[i];
+    if (launches) *launches = u->L.count[i] + u->Ls.count[i];
+    if (total_ms) *total_ms = u->L.ms[i] + u->Ls.ms[i];
+    if (algorithmic_bytes) *algorithmic_bytes = u->L.bytes[i] + u->Ls.bytes[i];
     return HM_OK;
 }
 

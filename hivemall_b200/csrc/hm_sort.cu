@@ -460,7 +460,7 @@ hm_status launch_seg_prep(Launcher &L, SortScratch &s, const int64_t *d_rowptr, 
 hm_status launch_segmented_sort(Launcher &L, SortScratch &s, const uint32_t *d_feature_block,
                                 const float *d_value_block, const int64_t *d_rowptr, int64_t block_row0,
                                 int64_t block_rows, int32_t mini_batch, int64_t n_elems, int n_segs, int key_bits,
-                                int *out_buf)
+                                int *out_buf, int ctas_per_sm)
 {
     static bool attr_set = false;   // > 48 KB of dynamic shared memory needs opting in, once per process
     if (!attr_set) {
@@ -473,7 +473,9 @@ hm_status launch_segmented_sort(Launcher &L, SortScratch &s, const uint32_t *d_f
     int passes = (key_bits + 7) / 8;
     if (passes < 1) passes = 1;
     const int64_t max_tiles = n_elems / kSortTile + n_segs;
-    const int grid = persistent_grid(max_tiles, 6);
+    // ctas_per_sm == 0: take the whole GPU; otherwise leave room for kernels of another stream
+    const int grid = persistent_grid(max_tiles, ctas_per_sm > 0 ? ctas_per_sm : 6);
+    const int hist_grid = persistent_grid(max_tiles, ctas_per_sm > 0 ? 2 * ctas_per_sm : 6);
     const int rows = n_segs * kRadix;
     RowLookup rl;
     rl.rowptr = d_rowptr; rl.block_row0 = block_row0; rl.block_rows = block_rows; rl.mini_batch = mini_batch;
@@ -486,7 +488,7 @@ hm_status launch_segmented_sort(Launcher &L, SortScratch &s, const uint32_t *d_f
         uint2 *pout = s.pay[p & 1];
         HM_CUDA(cudaMemsetAsync(s.row_sum, 0, (size_t)rows * sizeof(uint32_t), L.stream));
         HM_LAUNCH(L, K_SORT_HIST, 4.0 * (double)n_elems,
-                  (sort_hist_kernel<<<grid, kSortThreads, 0, L.stream>>>(kin, s.seg_off, s.seg_tile_off, n_segs, shift,
+                  (sort_hist_kernel<<<hist_grid, kSortThreads, 0, L.stream>>>(kin, s.seg_off, s.seg_tile_off, n_segs, shift,
                                                                          s.tile_hist, s.row_sum)));
         HM_LAUNCH(L, K_SORT_SCAN, 0.0, (scan_rows_kernel<<<1, 1024, 0, L.stream>>>(s.row_sum, rows)));
         HM_LAUNCH(L, K_SORT_SCAN, 0.0,
