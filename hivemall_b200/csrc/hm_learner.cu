@@ -149,6 +149,7 @@ struct hm_udtf {
     cudaStream_t compute = nullptr, copy = nullptr, sorter = nullptr;
     cudaEvent_t sorted_ev[2] = {nullptr, nullptr}, trained_ev[2] = {nullptr, nullptr}, ready_ev = nullptr;
     bool trained_valid[2] = {false, false};
+    size_t sort_turn = 0;            // blocks sorted so far: picks the scratch set, across calls
     cudaEvent_t stage_ev[2] = {nullptr, nullptr};
     // model replica
     float *rec = nullptr;            // dims x rec_width floats: (w[, slot1[, slot2, unused]]) per feature
@@ -245,7 +246,8 @@ int table_stride(const hm_udtf *u) { return u->fm ? u->ww : u->rec_width; }
 // The rows are cut into blocks (<= kMaxSegs mini-batches, <= kBlockElemCap elements).  Sorting a
 // block needs only the data, so block k+1 is sorted on the sort stream while block k trains on
 // the compute stream (two scratch sets, two events each way).
-hm_status train_rows(hm_udtf *u, const Chunk &c, int64_t row0, int64_t n_rows, const int64_t *mb_abs, int64_t n_mb)
+hm_status train_rows(hm_udtf *u, const Chunk &c, int64_t row0, int64_t n_rows, const int64_t *mb_abs, int64_t n_mb,
+                     bool rows_ready = false)
 {
     if (n_rows <= 0) return HM_OK;
     const int32_t B = u->cfg.mini_batch;
@@ -268,13 +270,18 @@ hm_status train_rows(hm_udtf *u, const Chunk &c, int64_t row0, int64_t n_rows, c
         plan.push_back(p);
         m0 = m1;
     }
-    // everything queued on the compute stream so far (copies of these rows included) precedes the sorts
-    HM_CUDA(cudaEventRecord(u->ready_ev, u->compute));
-    HM_CUDA(cudaStreamWaitEvent(u->sorter, u->ready_ev, 0));
+    // Rows that were copied in by this library: everything queued on the compute stream so far
+    // (their copies included) precedes the sorts.  Rows that are already resident (device views,
+    // replays of retained chunks) need no such wait: the sort only reads data, so it may start
+    // while the previous call's last block is still training or being averaged.
+    if (!rows_ready || u->L.profiling) {
+        HM_CUDA(cudaEventRecord(u->ready_ev, u->compute));
+        HM_CUDA(cudaStreamWaitEvent(u->sorter, u->ready_ev, 0));
+    }
     int out_buf[2] = {0, 0};
     auto enqueue_sort = [&](size_t bi) -> hm_status {
         const Plan &p = plan[bi];
-        const int set = (int)(bi & 1);
+        const int set = (int)((u->sort_turn + bi) & 1);
         // the scratch set is free once the block that used it last has been trained
         if (u->trained_valid[set]) HM_CUDA(cudaStreamWaitEvent(u->sorter, u->trained_ev[set], 0));
         HM_TRY(sort_scratch_reserve(u->sort[set], p.nnz));
@@ -290,7 +297,7 @@ hm_status train_rows(hm_udtf *u, const Chunk &c, int64_t row0, int64_t n_rows, c
     HM_TRY(enqueue_sort(0));
     for (size_t bi = 0; bi < plan.size(); bi++) {
         const Plan &p = plan[bi];
-        const int set = (int)(bi & 1);
+        const int set = (int)((u->sort_turn + bi) & 1);
         if (bi + 1 < plan.size()) {
             if (!overlap) {     // the next sort starts only after everything queued for training so far
                 HM_CUDA(cudaEventRecord(u->ready_ev, u->compute));
@@ -298,7 +305,7 @@ hm_status train_rows(hm_udtf *u, const Chunk &c, int64_t row0, int64_t n_rows, c
             }
             HM_TRY(enqueue_sort(bi + 1));
             if (!overlap) {     // ... and training waits for it
-                HM_CUDA(cudaStreamWaitEvent(u->compute, u->sorted_ev[(bi + 1) & 1], 0));
+                HM_CUDA(cudaStreamWaitEvent(u->compute, u->sorted_ev[(u->sort_turn + bi + 1) & 1], 0));
             }
         }
         HM_CUDA(cudaStreamWaitEvent(u->compute, u->sorted_ev[set], 0));
@@ -343,6 +350,7 @@ hm_status train_rows(hm_udtf *u, const Chunk &c, int64_t row0, int64_t n_rows, c
         u->stats.rows += p.rows;
         u->stats.nnz += p.nnz;
     }
+    u->sort_turn += plan.size();
     return HM_OK;
 }
 
@@ -722,7 +730,7 @@ hm_status hm_udtf_process_device(hm_udtf *u, int64_t n_rows, int64_t nnz, const 
         if (c->mb_abs.back() - c->mb_abs.front() != nnz)
             HM_FAIL(HM_ERR_INVALID_ARGUMENT, "nnz (%lld) does not match d_rowptr (%lld)", (long long)nnz,
                     (long long)(c->mb_abs.back() - c->mb_abs.front()));
-        return train_rows(u, *c, 0, n_rows, c->mb_abs.data(), n_mb);
+        return train_rows(u, *c, 0, n_rows, c->mb_abs.data(), n_mb, true);
     }();
     if (s != HM_OK) { delete c; return s; }
     if (n_rows % B) u->device_rows_short = true;
@@ -755,7 +763,7 @@ hm_status hm_udtf_close(hm_udtf *u, int64_t *n_model_rows)
             for (Chunk *c : u->retained) {
                 const int64_t B = u->cfg.mini_batch;
                 const int64_t n_mb = (c->rows + B - 1) / B;
-                HM_TRY(train_rows(u, *c, 0, c->rows, c->mb_abs.data(), n_mb));
+                HM_TRY(train_rows(u, *c, 0, c->rows, c->mb_abs.data(), n_mb, true));
             }
         u->closed = true;
     }
