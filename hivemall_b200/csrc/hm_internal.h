@@ -86,10 +86,21 @@ struct StepScalars {      // per mini-batch scalars computed on the host in doub
     float adam_alpha;
     int32_t n_rows;       // rows in this mini-batch
 };
+// Where a feature's weight is read from.  Plain: base[j * stride].  FTRL keeps only (z, n) per
+// feature (8-byte records, a 2^24-dim replica is 128 MiB and largely stays in L2) and the weight
+// is the closed form of DESIGN.md 3.6 evaluated on the fly -- bit-identical to what a stored
+// weight would hold, because a stored weight is always that same function of the same (z, n).
+struct WeightView {
+    const float *base;
+    int32_t stride;
+    int32_t ftrl;         // 1: base holds (z, n) pairs and the weight is derived
+    float alpha, beta, lambda1, lambda2;
+};
 struct LinearArgs {
     hm_config cfg;
-    float *rec;           // replica: rec_width floats per feature, weight first
-    int rec_width;        // 1 (SGD), 2 (AdaGrad), 4 (two-slot optimizers; last float unused)
+    float *rec;           // replica: rec_width floats per feature
+    int rec_width;        // 1 (SGD: w), 2 (AdaGrad: w, G; FTRL: z, n), 4 (AdaDelta, Adam: w, s1, s2, unused)
+    WeightView wv;
 };
 // margin (per block row) and dloss (per mini-batch row) for rows [row0, row0+n) of the chunk
 hm_status launch_linear_forward(Launcher &L, const LinearArgs &a, const int64_t *d_rowptr, int64_t row0,
@@ -107,16 +118,17 @@ void update_scratch_free(UpdateScratch &u);
 hm_status launch_linear_update(Launcher &L, const LinearArgs &a, const StepScalars &sc, UpdateScratch &us,
                                const uint32_t *d_sorted_key, const uint2 *d_sorted_pay,
                                const uint32_t *d_seg_off, int seg, const float *d_dloss, int64_t nnz_hint);
-hm_status launch_predict_linear(Launcher &L, const float *w, int w_stride, int64_t dims, int64_t n_rows, const int64_t *d_rowptr,
+hm_status launch_predict_linear(Launcher &L, const WeightView &wv, int64_t dims, int64_t n_rows, const int64_t *d_rowptr,
                                 const uint32_t *d_feature, const float *d_value, float *d_out, uint32_t *d_bad);
 // model table: features with w != 0, ascending
 struct ExportScratch { uint32_t *counts = nullptr; int64_t cap = 0; };
-hm_status launch_export_count(Launcher &L, ExportScratch &es, const float *w, int w_stride, const uint8_t *touched,
+hm_status launch_export_count(Launcher &L, ExportScratch &es, const WeightView &wv, const uint8_t *touched,
                               int64_t dims, int64_t *d_total);
-hm_status launch_export_write(Launcher &L, ExportScratch &es, const float *w, int w_stride, const uint8_t *touched,
+hm_status launch_export_write(Launcher &L, ExportScratch &es, const WeightView &wv, const uint8_t *touched,
                               int64_t dims, int32_t *d_feature, float *d_weight);
 hm_status launch_scale(Launcher &L, float *p, int64_t n, float scale);
 hm_status launch_fill_u32(Launcher &L, uint32_t *p, int64_t n, uint32_t v);
+hm_status launch_dense_weights(Launcher &L, const WeightView &wv, int64_t dims, float *d_out);
 hm_status launch_strided_copy(Launcher &L, float *dense, float *strided, int64_t n, int stride, int off, int width,
                               bool gather);
 

@@ -236,9 +236,16 @@ FmArgs fm_args(const hm_udtf *u)
     return a;
 }
 
-// what the model table is read from: (weights, stride, touched bitmap or NULL)
-const float *table_w(const hm_udtf *u) { return u->fm ? u->wrec : u->rec; }
-int table_stride(const hm_udtf *u) { return u->fm ? u->ww : u->rec_width; }
+// where the weights are read from (forward, prediction, model table)
+WeightView weight_view(const hm_udtf *u)
+{
+    WeightView v;
+    v.base = u->fm ? u->wrec : u->rec;
+    v.stride = u->fm ? u->ww : u->rec_width;
+    v.ftrl = (!u->fm && u->cfg.opt == HM_OPT_FTRL) ? 1 : 0;
+    v.alpha = u->cfg.alpha; v.beta = u->cfg.beta; v.lambda1 = u->cfg.lambda1; v.lambda2 = u->cfg.lambda2;
+    return v;
+}
 
 // Train rows [row0, row0+n_rows) of a chunk.  mb_abs[i] is the chunk rowptr value at
 // row0 + min(i*B, n_rows), i = 0..n_mb.
@@ -253,7 +260,7 @@ hm_status train_rows(hm_udtf *u, const Chunk &c, int64_t row0, int64_t n_rows, c
     const int32_t B = u->cfg.mini_batch;
     const int key_bits = bits_for(u->cfg.dims);
     LinearArgs a;
-    a.cfg = u->cfg; a.rec = u->rec; a.rec_width = u->rec_width;
+    a.cfg = u->cfg; a.rec = u->rec; a.rec_width = u->rec_width; a.wv = weight_view(u);
     struct Plan { int64_t m0, m1, row0, rows, nnz; int n_segs; };
     std::vector<Plan> plan;
     for (int64_t m0 = 0; m0 < n_mb;) {
@@ -521,7 +528,8 @@ hm_status create_impl(const hm_config &cfg, int device, hm_udtf **out)
             HM_CUDA(cudaMemsetAsync(u->touched, 0, tb, u->compute));
             HM_TRY(launch_fm_init_v(u->L, fm_args(u)));
         } else {
-            u->rec_width = u->state_width == 0 ? 1 : (u->state_width == 1 ? 2 : 4);
+            // FTRL keeps (z, n) only: the weight is derived (see WeightView)
+            u->rec_width = u->state_width == 0 ? 1 : ((u->state_width == 1 || cfg.opt == HM_OPT_FTRL) ? 2 : 4);
             HM_CUDA(cudaMalloc(&u->rec, (size_t)cfg.dims * u->rec_width * sizeof(float)));
             HM_CUDA(cudaMemsetAsync(u->rec, 0, (size_t)cfg.dims * u->rec_width * sizeof(float), u->compute));
         }
@@ -768,7 +776,7 @@ hm_status hm_udtf_close(hm_udtf *u, int64_t *n_model_rows)
         u->closed = true;
     }
     HM_TRY(check_bad(u));
-    HM_TRY(launch_export_count(u->L, u->exp, table_w(u), table_stride(u), u->touched, u->cfg.dims, u->d_total));
+    HM_TRY(launch_export_count(u->L, u->exp, weight_view(u), u->touched, u->cfg.dims, u->d_total));
     HM_CUDA(cudaMemcpyAsync(u->h_small, u->d_total, sizeof(int64_t), cudaMemcpyDeviceToHost, u->compute));
     HM_CUDA(cudaStreamSynchronize(u->compute));
     u->stats.d2h_bytes += 8;
@@ -787,7 +795,7 @@ hm_status hm_udtf_forward(hm_udtf *u, int32_t *feature, float *weight, float *vi
     if (u->fm && cap > 0 && !vif) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "train_fm forward() needs a vif buffer");
     DeviceGuard g(u->device);
     // recount: the replica may have been averaged since close()
-    HM_TRY(launch_export_count(u->L, u->exp, table_w(u), table_stride(u), u->touched, u->cfg.dims, u->d_total));
+    HM_TRY(launch_export_count(u->L, u->exp, weight_view(u), u->touched, u->cfg.dims, u->d_total));
     HM_CUDA(cudaMemcpyAsync(u->h_small, u->d_total, sizeof(int64_t), cudaMemcpyDeviceToHost, u->compute));
     HM_CUDA(cudaStreamSynchronize(u->compute));
     const int64_t n = u->h_small[0];
@@ -802,7 +810,7 @@ hm_status hm_udtf_forward(hm_udtf *u, int32_t *feature, float *weight, float *vi
     if (n > 0) {
         HM_TRY(u->exp_feat.reserve((size_t)n * 4));
         HM_TRY(u->exp_weight.reserve((size_t)n * 4));
-        HM_TRY(launch_export_write(u->L, u->exp, table_w(u), table_stride(u), u->touched, u->cfg.dims,
+        HM_TRY(launch_export_write(u->L, u->exp, weight_view(u), u->touched, u->cfg.dims,
                                    u->exp_feat.as<int32_t>(), u->exp_weight.as<float>()));
         HM_CUDA(cudaMemcpyAsync(feature + head, u->exp_feat.p, (size_t)n * 4, cudaMemcpyDeviceToHost, u->compute));
         HM_CUDA(cudaMemcpyAsync(weight + head, u->exp_weight.p, (size_t)n * 4, cudaMemcpyDeviceToHost, u->compute));
@@ -888,7 +896,22 @@ static hm_status array_copy(hm_udtf *u, int which, float *host, const float *hos
 {
     float *base = nullptr; int64_t rows = u->cfg.dims; int stride = 1, off = 0, width = 1;
     const bool ada = u->cfg.opt == HM_OPT_ADAGRAD;
+    const bool ftrl = !u->fm && u->cfg.opt == HM_OPT_FTRL;
+    if (ftrl && which == 0) {
+        // the weight is not stored: evaluate it (reads only; a warm start writes (z, n) instead)
+        if (!host) HM_FAIL(HM_ERR_UNSUPPORTED, "FTRL keeps (z, n) only: warm-start array 1 (state), the weights follow from it");
+        if (n != u->cfg.dims) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "array 0 holds %lld floats, caller passed %lld", (long long)u->cfg.dims, (long long)n);
+        DeviceGuard g(u->device);
+        HM_CUDA(cudaStreamSynchronize(u->copy));
+        HM_TRY(u->tmp_a.reserve((size_t)n * 4));
+        HM_TRY(launch_dense_weights(u->L, weight_view(u), u->cfg.dims, u->tmp_a.as<float>()));
+        HM_CUDA(cudaMemcpyAsync(host, u->tmp_a.p, (size_t)n * 4, cudaMemcpyDeviceToHost, u->compute));
+        HM_CUDA(cudaStreamSynchronize(u->compute));
+        u->stats.d2h_bytes += n * 4;
+        return HM_OK;
+    }
     if (!u->fm && which == 0) { base = u->rec; stride = u->rec_width; }
+    else if (ftrl && which == 1) { base = u->rec; stride = 2; off = 0; width = 2; }
     else if (!u->fm && which == 1 && u->state_width > 0) { base = u->rec; stride = u->rec_width; off = 1; width = u->state_width; }
     else if (u->fm && which == 0) { base = u->wrec; stride = u->ww; }
     else if (u->fm && which == 1) { base = u->vrec; stride = u->vw; width = u->k; }
@@ -980,7 +1003,7 @@ hm_status hm_udtf_predict_device(hm_udtf *u, int64_t n_rows, const int64_t *d_ro
         return launch_fm_forward(u->L, fm_args(u), d_rowptr, 0, (int32_t)n_rows, 0, reinterpret_cast<const uint32_t *>(d_feature),
                                  d_value, nullptr, d_out, nullptr, nullptr, u->d_bad, 0, false);
     }
-    return launch_predict_linear(u->L, u->rec, u->rec_width, u->cfg.dims, n_rows, d_rowptr, reinterpret_cast<const uint32_t *>(d_feature),
+    return launch_predict_linear(u->L, weight_view(u), u->cfg.dims, n_rows, d_rowptr, reinterpret_cast<const uint32_t *>(d_feature),
                                  d_value, d_out, u->d_bad);
 }
 
@@ -1009,7 +1032,7 @@ hm_status hm_udtf_predict(hm_udtf *u, int64_t n_rows, const int64_t *rowptr, con
         HM_TRY(launch_fm_forward(u->L, fm_args(u), u->tmp_a.as<int64_t>(), 0, (int32_t)n_rows, 0, u->tmp_b.as<uint32_t>(),
                                  u->tmp_c.as<float>(), nullptr, u->tmp_d.as<float>(), nullptr, nullptr, u->d_bad, nnz, false));
     } else {
-        HM_TRY(launch_predict_linear(u->L, u->rec, u->rec_width, u->cfg.dims, n_rows, u->tmp_a.as<int64_t>(), u->tmp_b.as<uint32_t>(),
+        HM_TRY(launch_predict_linear(u->L, weight_view(u), u->cfg.dims, n_rows, u->tmp_a.as<int64_t>(), u->tmp_b.as<uint32_t>(),
                                      u->tmp_c.as<float>(), u->tmp_d.as<float>(), u->d_bad));
     }
     HM_CUDA(cudaMemcpyAsync(out, u->tmp_d.p, (size_t)n_rows * 4, cudaMemcpyDeviceToHost, u->compute));

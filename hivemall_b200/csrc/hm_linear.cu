@@ -50,6 +50,23 @@ __device__ __forceinline__ float dloss_of(int loss, float m, float y)
     return __fsub_rn(m, y);
 }
 
+// FTRL-Proximal closed form; the same operation sequence as the update step.
+__device__ __forceinline__ float ftrl_weight(float z, float n, float alpha, float beta, float l1, float l2)
+{
+    if (fabsf(z) <= l1) return 0.0f;
+    const float sgn = z < 0.0f ? -1.0f : 1.0f;
+    const float num = __fsub_rn(z, __fmul_rn(sgn, l1));
+    const float den = __fadd_rn(__fdiv_rn(__fadd_rn(beta, __fsqrt_rn(n)), alpha), l2);
+    return -__fdiv_rn(num, den);
+}
+
+__device__ __forceinline__ float weight_at(const WeightView &v, size_t j)
+{
+    if (!v.ftrl) return __ldg(v.base + j * v.stride);
+    const float2 zn = __ldg(reinterpret_cast<const float2 *>(v.base) + j);
+    return ftrl_weight(zn.x, zn.y, v.alpha, v.beta, v.lambda1, v.lambda2);
+}
+
 __device__ __forceinline__ double warp_sum(double v)
 {
 #pragma unroll
@@ -60,8 +77,7 @@ __device__ __forceinline__ double warp_sum(double v)
 // ---- forward ---------------------------------------------------------------------
 
 struct FwdParams {
-    const float *w;          // weight of feature f is w[f * w_stride] (records are interleaved)
-    int32_t w_stride;
+    WeightView wv;           // where the weight of a feature is read from
     const int64_t *rowptr;   // chunk row pointer (absolute element positions in the chunk)
     const uint32_t *feature;
     const float *value;
@@ -88,7 +104,7 @@ __global__ void __launch_bounds__(kFwdThreads) linear_forward_kernel(FwdParams P
         for (int64_t p = p0 + lane; p < p1; p += 32) {
             const uint32_t f = __ldcs(P.feature + p);
             const float x = __ldcs(P.value + p);
-            if (f < P.dims) acc += (double)__fmul_rn(__ldg(P.w + (size_t)f * P.w_stride), x);
+            if (f < P.dims) acc += (double)__fmul_rn(weight_at(P.wv, f), x);
             else atomicOr(P.bad, 1u);
         }
         acc = warp_sum(acc);
@@ -126,6 +142,7 @@ struct BoundaryRecs {
 struct UpdParams {
     float *rec;              // replica: rec_width floats per feature = (w[, slot1[, slot2, unused]])
     int32_t rec_width;       // 1, 2 or 4
+    int32_t ftrl_derived;    // records are (z, n); the weight is derived
     uint8_t *touched;        // nullable
     const uint32_t *skey;    // sorted features of the block
     const uint2 *spay;       // sorted (row in mini-batch, value bits)
@@ -149,6 +166,11 @@ __device__ __forceinline__ Rec load_rec(const UpdParams &P, uint32_t j)
 {
     Rec r; r.s1 = 0.f; r.s2 = 0.f;
     if (P.rec_width == 4) { const float4 v = reinterpret_cast<const float4 *>(P.rec)[j]; r.w = v.x; r.s1 = v.y; r.s2 = v.z; }
+    else if (P.ftrl_derived) {
+        const float2 v = reinterpret_cast<const float2 *>(P.rec)[j];
+        r.s1 = v.x; r.s2 = v.y;
+        r.w = ftrl_weight(v.x, v.y, P.alpha, P.beta, P.lambda1, P.lambda2);
+    }
     else if (P.rec_width == 2) { const float2 v = reinterpret_cast<const float2 *>(P.rec)[j]; r.w = v.x; r.s1 = v.y; }
     else r.w = P.rec[j];
     return r;
@@ -157,6 +179,7 @@ __device__ __forceinline__ Rec load_rec(const UpdParams &P, uint32_t j)
 __device__ __forceinline__ void store_rec(const UpdParams &P, uint32_t j, const Rec &r)
 {
     if (P.rec_width == 4) reinterpret_cast<float4 *>(P.rec)[j] = make_float4(r.w, r.s1, r.s2, 0.f);
+    else if (P.ftrl_derived) reinterpret_cast<float2 *>(P.rec)[j] = make_float2(r.s1, r.s2);
     else if (P.rec_width == 2) reinterpret_cast<float2 *>(P.rec)[j] = make_float2(r.w, r.s1);
     else P.rec[j] = r.w;
     if (P.touched) P.touched[j] = 1;
@@ -495,13 +518,13 @@ __global__ void __launch_bounds__(kUpdThreads, 3) linear_update_kernel(UpdParams
 constexpr int kExpThreads = 256;
 constexpr int kExpTile = 4096;
 
-__device__ __forceinline__ bool emit(const float *w, int stride, const uint8_t *touched, int64_t j)
+__device__ __forceinline__ bool emit(const WeightView &wv, const uint8_t *touched, int64_t j)
 {
-    return touched ? touched[j] != 0 : w[j * stride] != 0.0f;
+    return touched ? touched[j] != 0 : weight_at(wv, (size_t)j) != 0.0f;
 }
 
 __global__ void __launch_bounds__(kExpThreads)
-export_count_kernel(const float *__restrict__ w, int stride, const uint8_t *__restrict__ touched, int64_t dims,
+export_count_kernel(WeightView wv, const uint8_t *__restrict__ touched, int64_t dims,
                     uint32_t *__restrict__ counts)
 {
     __shared__ uint32_t s_tot;
@@ -511,7 +534,7 @@ export_count_kernel(const float *__restrict__ w, int stride, const uint8_t *__re
     uint32_t c = 0;
     for (int i = 0; i < kExpTile / kExpThreads; i++) {
         const int64_t j = j0 + i * kExpThreads + threadIdx.x;
-        if (j < dims && emit(w, stride, touched, j)) c++;
+        if (j < dims && emit(wv, touched, j)) c++;
     }
     c = __reduce_add_sync(0xffffffffu, c);
     if ((threadIdx.x & 31) == 0 && c) atomicAdd(&s_tot, c);
@@ -546,7 +569,7 @@ __global__ void __launch_bounds__(1024) export_scan_kernel(uint32_t *__restrict_
 }
 
 __global__ void __launch_bounds__(kExpThreads)
-export_write_kernel(const float *__restrict__ w, int stride, const uint8_t *__restrict__ touched, int64_t dims,
+export_write_kernel(WeightView wv, const uint8_t *__restrict__ touched, int64_t dims,
                     const uint32_t *__restrict__ offsets, int32_t *__restrict__ feature, float *__restrict__ weight)
 {
     __shared__ uint32_t warp_tot[kExpThreads / 32];
@@ -558,7 +581,7 @@ export_write_kernel(const float *__restrict__ w, int stride, const uint8_t *__re
     uint32_t flags = 0;
     for (int i = 0; i < per; i++) {
         const int64_t j = j0 + (int64_t)threadIdx.x * per + i;
-        if (j < dims && emit(w, stride, touched, j)) flags |= 1u << i;
+        if (j < dims && emit(wv, touched, j)) flags |= 1u << i;
     }
     const uint32_t c = __popc(flags);
     uint32_t inc = c;
@@ -573,7 +596,7 @@ export_write_kernel(const float *__restrict__ w, int stride, const uint8_t *__re
         if (flags & (1u << i)) {
             const int64_t j = j0 + (int64_t)threadIdx.x * per + i;
             feature[pos] = (int32_t)j;
-            weight[pos] = w[j * stride];
+            weight[pos] = weight_at(wv, (size_t)j);
             pos++;
         }
     }
@@ -598,6 +621,12 @@ __global__ void strided_copy_kernel(float *__restrict__ dense, float *__restrict
     }
 }
 
+__global__ void dense_weights_kernel(WeightView wv, int64_t dims, float *__restrict__ out)
+{
+    for (int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; j < dims; j += (int64_t)gridDim.x * blockDim.x)
+        out[j] = weight_at(wv, (size_t)j);
+}
+
 __global__ void fill_u32_kernel(uint32_t *__restrict__ p, int64_t n, uint32_t v)
 {
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
@@ -620,7 +649,7 @@ hm_status launch_linear_forward(Launcher &L, const LinearArgs &a, const int64_t 
 {
     if (n_rows <= 0) return HM_OK;
     FwdParams P;
-    P.w = a.rec; P.w_stride = a.rec_width; P.rowptr = d_rowptr; P.feature = d_feature; P.value = d_value; P.label = d_label;
+    P.wv = a.wv; P.rowptr = d_rowptr; P.feature = d_feature; P.value = d_value; P.label = d_label;
     P.margin = d_margin; P.dloss = d_dloss;
     P.block_row0 = block_row0; P.row0 = row0; P.n_rows = n_rows;
     P.task = a.cfg.task; P.loss = a.cfg.loss; P.train = 1;
@@ -633,13 +662,13 @@ hm_status launch_linear_forward(Launcher &L, const LinearArgs &a, const int64_t 
     return HM_OK;
 }
 
-hm_status launch_predict_linear(Launcher &L, const float *w, int w_stride, int64_t dims, int64_t n_rows, const int64_t *d_rowptr,
+hm_status launch_predict_linear(Launcher &L, const WeightView &wv, int64_t dims, int64_t n_rows, const int64_t *d_rowptr,
                                 const uint32_t *d_feature, const float *d_value, float *d_out, uint32_t *d_bad)
 {
     if (n_rows <= 0) return HM_OK;
     if (n_rows > 0x7fffffff) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "predict: too many rows in one call");
     FwdParams P;
-    P.w = w; P.w_stride = w_stride; P.rowptr = d_rowptr; P.feature = d_feature; P.value = d_value; P.label = nullptr;
+    P.wv = wv; P.rowptr = d_rowptr; P.feature = d_feature; P.value = d_value; P.label = nullptr;
     P.margin = d_out; P.dloss = nullptr;
     P.block_row0 = 0; P.row0 = 0; P.n_rows = (int32_t)n_rows;
     P.task = 0; P.loss = 0; P.train = 0;
@@ -673,7 +702,7 @@ hm_status launch_linear_update(Launcher &L, const LinearArgs &a, const StepScala
                                const uint32_t *d_seg_off, int seg, const float *d_dloss, int64_t nnz_hint)
 {
     UpdParams P;
-    P.rec = a.rec; P.rec_width = a.rec_width; P.touched = nullptr;
+    P.rec = a.rec; P.rec_width = a.rec_width; P.ftrl_derived = a.wv.ftrl; P.touched = nullptr;
     P.skey = d_sorted_key; P.spay = d_sorted_pay; P.dloss = d_dloss; P.seg_off = d_seg_off;
     P.br.first = reinterpret_cast<uint4 *>(us.boundary);
     P.br.last = P.br.first + us.grid;
@@ -698,7 +727,7 @@ hm_status launch_linear_update(Launcher &L, const LinearArgs &a, const StepScala
     return HM_OK;
 }
 
-hm_status launch_export_count(Launcher &L, ExportScratch &es, const float *w, int w_stride, const uint8_t *touched,
+hm_status launch_export_count(Launcher &L, ExportScratch &es, const WeightView &wv, const uint8_t *touched,
                               int64_t dims, int64_t *d_total)
 {
     const int64_t ctas = (dims + kExpTile - 1) / kExpTile;
@@ -709,18 +738,18 @@ hm_status launch_export_count(Launcher &L, ExportScratch &es, const float *w, in
         es.cap = ctas + 1;
     }
     HM_LAUNCH(L, K_EXPORT, 4.0 * (double)dims,
-              (export_count_kernel<<<(unsigned)ctas, kExpThreads, 0, L.stream>>>(w, w_stride, touched, dims, es.counts)));
+              (export_count_kernel<<<(unsigned)ctas, kExpThreads, 0, L.stream>>>(wv, touched, dims, es.counts)));
     HM_LAUNCH(L, K_EXPORT, 0.0, (export_scan_kernel<<<1, 1024, 0, L.stream>>>(es.counts, (int)ctas, d_total)));
     HM_CUDA(cudaGetLastError());
     return HM_OK;
 }
 
-hm_status launch_export_write(Launcher &L, ExportScratch &es, const float *w, int w_stride, const uint8_t *touched,
+hm_status launch_export_write(Launcher &L, ExportScratch &es, const WeightView &wv, const uint8_t *touched,
                               int64_t dims, int32_t *d_feature, float *d_weight)
 {
     const int64_t ctas = (dims + kExpTile - 1) / kExpTile;
     HM_LAUNCH(L, K_EXPORT, 4.0 * (double)dims,
-              (export_write_kernel<<<(unsigned)ctas, kExpThreads, 0, L.stream>>>(w, w_stride, touched, dims, es.counts,
+              (export_write_kernel<<<(unsigned)ctas, kExpThreads, 0, L.stream>>>(wv, touched, dims, es.counts,
                                                                                  d_feature, d_weight)));
     HM_CUDA(cudaGetLastError());
     return HM_OK;
@@ -742,6 +771,14 @@ hm_status launch_strided_copy(Launcher &L, float *dense, float *strided, int64_t
     HM_LAUNCH(L, K_MISC, 8.0 * (double)n * width,
               (strided_copy_kernel<<<grid_for((n * width + 1023) / 1024, 8), 256, 0, L.stream>>>(dense, strided, n, stride,
                                                                                                 off, width, gather)));
+    HM_CUDA(cudaGetLastError());
+    return HM_OK;
+}
+
+hm_status launch_dense_weights(Launcher &L, const WeightView &wv, int64_t dims, float *d_out)
+{
+    HM_LAUNCH(L, K_MISC, 12.0 * (double)dims,
+              (dense_weights_kernel<<<grid_for((dims + 1023) / 1024, 8), 256, 0, L.stream>>>(wv, dims, d_out)));
     HM_CUDA(cudaGetLastError());
     return HM_OK;
 }
@@ -848,7 +885,9 @@ extern "C" hm_status hm_model_table_noalloc(const float *d_w, int64_t dims, int3
     const uint32_t cap32 = (uint32_t)std::min<int64_t>(cap, 0xffffffffLL);
     // counts[0 .. tiles) are all rewritten by the first kernel before anything reads them, and
     // *d_n_rows is written by the second: nothing left over from an earlier call is ever read.
-    export_count_kernel<<<tiles, kExpThreads, 0, st>>>(d_w, 1, nullptr, dims, counts);
+    WeightView plain;
+    plain.base = d_w; plain.stride = 1; plain.ftrl = 0; plain.alpha = plain.beta = plain.lambda1 = plain.lambda2 = 0.f;
+    export_count_kernel<<<tiles, kExpThreads, 0, st>>>(plain, nullptr, dims, counts);
     export_scan_kernel<<<1, 1024, 0, st>>>(counts, tiles, d_n_rows);
     export_write_capped_kernel<<<tiles, kExpThreads, 0, st>>>(d_w, dims, counts, d_feature, d_weight, cap32);
     HM_CUDA(cudaGetLastError());

@@ -162,8 +162,8 @@ hm_status hm_udtf_destroy(hm_udtf *u);
 /* Device memory that makes up the replica (what MIX averaging all-reduces).  which = 0..n-1.
  * A linear learner has ONE array, "replica": `width` floats per feature, interleaved so that
  * a feature's weight and optimizer slots share a memory sector: width 1 = (w) for SGD,
- * 2 = (w, G) for AdaGrad, 4 = (w, slot1, slot2, unused) for AdaDelta (E[g^2], E[dx^2]),
- * Adam (m, v) and FTRL (z, n).  n_floats = dims * width.  train_fm has four: "w0" (w0 and its
+ * 2 = (w, G) for AdaGrad and (z, n) for FTRL -- FTRL stores no weight, it is the closed form of
+ * (z, n) --, 4 = (w, slot1, slot2, unused) for AdaDelta (E[g^2], E[dx^2]) and Adam (m, v).  n_floats = dims * width.  train_fm has four: "w0" (w0 and its
  * AdaGrad accumulator), "w" (width 1 or 2: (w[, acc]) per feature), "V" (width k or 2k: the k
  * factors of a feature, then their accumulators) and "touched" (width 0: a byte per feature,
  * 1 = seen in training; combine it with MAX, not with a sum, and do not scale it).  The
@@ -176,7 +176,8 @@ hm_status hm_udtf_array(hm_udtf *u, int which, const char **name, void **d_ptr,
  * which = 0 is the dense weight vector w (n = dims); 1 is the optimizer state (n = dims *
  * slots, the slots of a feature adjacent).  train_fm: 0 = w (dims), 1 = V (dims * factors,
  * one row per feature), 2 = w0 (1), and with -opt adagrad 3 / 4 / 5 = the accumulators of
- * w / V / w0.  Synchronous.  write_array is the warm-start path. */
+ * w / V / w0.  Synchronous.  write_array is the warm-start path (for FTRL write the state:
+ * its weights are derived, array 0 is read-only). */
 hm_status hm_udtf_read_array(hm_udtf *u, int which, float *host, int64_t n);
 hm_status hm_udtf_write_array(hm_udtf *u, int which, const float *host, int64_t n);
 /* Update counter t (mini-batches applied so far); settable for warm start / MIX. */
