@@ -165,3 +165,65 @@ def test_process_device_matches_host_path():
     assert_weights_close(w_dev, ref.w)
     torch.cuda.synchronize()
     u.destroy()
+
+
+def _csr_from_lengths(lens, dims, seed):
+    import torch
+    lens = np.asarray(lens, dtype=np.int64)
+    rowptr = np.zeros(len(lens) + 1, np.int64)
+    rowptr[1:] = np.cumsum(lens)
+    rng = np.random.default_rng(seed)
+    nnz = int(rowptr[-1])
+    feat = (rng.random(nnz) ** 2 * dims).astype(np.int32)
+    val = ((rng.random(nnz) - 0.5) * 2).astype(np.float32)
+    label = (rng.random(len(lens)) < 0.5).astype(np.float32)
+    return synth.Csr(torch.from_numpy(rowptr), torch.from_numpy(feat), torch.from_numpy(val), torch.from_numpy(label))
+
+
+def test_rows_longer_than_a_sort_tile_and_runs_of_empty_rows():
+    """Rows of 5,000-20,000 elements (longer than the 4096-element sort tile), next to thousands of
+    empty and 1-2 element rows (more than 1024 rows inside one tile: the row lookup's slow path)."""
+    rng = np.random.default_rng(7)
+    lens = []
+    for _ in range(6):
+        lens += [int(rng.integers(5000, 20000))]
+        lens += list(rng.integers(0, 3, size=3000))
+        lens += [0] * 2500
+    data = _csr_from_lengths(lens, dims=50000, seed=8)
+    options = "-opt adagrad -mini_batch 4096 -dims 50000"
+    u, w, state = run_gpu_linear("train_classifier", options, data, pushes=[7000, 9000, 20000])
+    ref, ref_state = run_oracle_linear("train_classifier", options, data)
+    assert u.step == ref.t
+    assert_weights_close(w, ref.w)
+    assert_weights_close(state, ref_state, "state")
+    u.destroy()
+
+
+def test_mini_batch_of_one_row():
+    data = synth.ragged(300, dims=200, max_nnz=12, seed=12)
+    options = "-opt sgd -mini_batch 1 -dims 200 -eta0 0.05"
+    u, w, _ = run_gpu_linear("train_classifier", options, data)
+    ref, _ = run_oracle_linear("train_classifier", options, data)
+    assert u.step == ref.t == 300
+    assert_weights_close(w, ref.w)
+    u.destroy()
+
+
+def test_one_mini_batch_larger_than_the_block_cap():
+    """A single mini-batch of 2^21 rows x 39 = 82 M elements exceeds the 2^26-element block cap:
+    it becomes a block of its own and every update CTA walks many tiles."""
+    import torch
+    n = (1 << 21) + 12345
+    parts = [synth.criteo_like(min(1 << 20, n - r), dims=1 << 22, seed=9, device="cuda", row0=r) for r in range(0, n, 1 << 20)]
+    data = synth.Csr(torch.arange(n + 1, device="cuda", dtype=torch.int64) * 39, torch.cat([p.feature for p in parts]),
+                     torch.cat([p.value for p in parts]), torch.cat([p.label for p in parts]))
+    options = f"-opt adagrad -mini_batch {1 << 21} -dims {1 << 22}"
+    u = hm.train_classifier(options)
+    u.process_device(n, data.nnz, data.rowptr, data.feature, data.value, data.label)
+    u.close()
+    assert u.step == 2
+    host = synth.Csr(data.rowptr.cpu(), data.feature.cpu(), data.value.cpu(), data.label.cpu())
+    ref = _oracle.train_linear_mt(_oracle.config_from(hm.parse_options("train_classifier", options)), *host.numpy(), 8)
+    assert_weights_close(u.array_to_host("w"), ref.w)
+    assert_weights_close(u.array_to_host("state"), ref.s1, "state")
+    u.destroy()
