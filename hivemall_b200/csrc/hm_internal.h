@@ -118,6 +118,15 @@ void update_scratch_free(UpdateScratch &u);
 hm_status launch_linear_update(Launcher &L, const LinearArgs &a, const StepScalars &sc, UpdateScratch &us,
                                const uint32_t *d_sorted_key, const uint2 *d_sorted_pay,
                                const uint32_t *d_seg_off, int seg, const float *d_dloss, int64_t nnz_hint);
+// small mini-batches (<= 1024 rows and <= one update tile of elements): up to 64 consecutive
+// mini-batches of a sorted block trained by one persistent CTA
+bool small_batch_eligible(int32_t mini_batch, int64_t max_mb_elems);
+hm_status launch_linear_small_batches(Launcher &L, const LinearArgs &a, const int64_t *d_rowptr, int64_t block_row0,
+                                      int first_seg, int n_segs, const int32_t *rows, const float *eta,
+                                      const float *adam_alpha, const uint32_t *d_feature, const float *d_value,
+                                      const float *d_label, float *d_margin, float *d_dloss, uint32_t *d_bad,
+                                      const uint32_t *d_sorted_key, const uint2 *d_sorted_pay, const uint32_t *d_seg_off,
+                                      int64_t nnz_hint);
 hm_status launch_predict_linear(Launcher &L, const WeightView &wv, int64_t dims, int64_t n_rows, const int64_t *d_rowptr,
                                 const uint32_t *d_feature, const float *d_value, float *d_out, uint32_t *d_bad);
 // model table: features with w != 0, ascending

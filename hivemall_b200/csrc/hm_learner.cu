@@ -326,6 +326,28 @@ hm_status train_rows(hm_udtf *u, const Chunk &c, int64_t row0, int64_t n_rows, c
             HM_TRY(fm_scratch_reserve(u->fms, max_mb, u->k));
             HM_TRY(u->stab.reserve((size_t)std::min<int64_t>(p.rows, B) * u->k * sizeof(float)));
         }
+        int64_t max_mb = 0;
+        for (int64_t m = p.m0; m < p.m1; m++) max_mb = std::max(max_mb, mb_abs[m + 1] - mb_abs[m]);
+        if (!u->fm && small_batch_eligible(B, max_mb)) {
+            // a few hundred rows per mini-batch: up to 64 mini-batches per launch of one persistent CTA
+            for (int s0 = 0; s0 < p.n_segs; s0 += 64) {
+                const int ns = std::min(64, p.n_segs - s0);
+                int32_t rows[64]; float eta[64], adam[64];
+                for (int s = 0; s < ns; s++) {
+                    const int64_t mrow0 = p.row0 + (int64_t)(s0 + s) * B;
+                    rows[s] = (int32_t)std::min<int64_t>(B, row0 + n_rows - mrow0);
+                    u->t += 1;
+                    eta[s] = eta_at(u->cfg, u->t);
+                    adam[s] = u->cfg.opt == HM_OPT_ADAM ? adam_alpha_at(u->cfg, eta[s], u->t) : 0.f;
+                    u->stats.mini_batches++;
+                    u->last_margin_off = mrow0 - p.row0;
+                    u->last_margin_n = rows[s];
+                }
+                HM_TRY(launch_linear_small_batches(u->L, a, c.rp(), p.row0, s0, ns, rows, eta, adam, c.ft(), c.vl(), c.lb(),
+                                                   u->margin.as<float>(), u->dloss.as<float>(), u->d_bad, ss.key[buf],
+                                                   ss.pay[buf], ss.seg_off, mb_abs[p.m0 + s0 + ns] - mb_abs[p.m0 + s0]));
+            }
+        } else
         for (int s = 0; s < p.n_segs; s++) {
             const int64_t mrow0 = p.row0 + (int64_t)s * B;
             const int32_t mrows = (int32_t)std::min<int64_t>(B, row0 + n_rows - mrow0);

@@ -14,6 +14,7 @@
 //   predict / export / scale helpers
 #include "hm_internal.h"
 #include <algorithm>
+#include <cstring>
 #include <mutex>
 
 namespace hm {
@@ -60,10 +61,13 @@ __device__ __forceinline__ float ftrl_weight(float z, float n, float alpha, floa
     return -__fdiv_rn(num, den);
 }
 
+// RO: the replica is not written by the running kernel, so the read-only path may be used.
+template <bool RO = true>
 __device__ __forceinline__ float weight_at(const WeightView &v, size_t j)
 {
-    if (!v.ftrl) return __ldg(v.base + j * v.stride);
-    const float2 zn = __ldg(reinterpret_cast<const float2 *>(v.base) + j);
+    if (!v.ftrl) return RO ? __ldg(v.base + j * v.stride) : v.base[j * v.stride];
+    const float2 *p = reinterpret_cast<const float2 *>(v.base) + j;
+    const float2 zn = RO ? __ldg(p) : *p;
     return ftrl_weight(zn.x, zn.y, v.alpha, v.beta, v.lambda1, v.lambda2);
 }
 
@@ -93,18 +97,20 @@ struct FwdParams {
     uint32_t *bad;           // set to 1 when a feature index >= dims is met (that element scores 0)
 };
 
-__global__ void __launch_bounds__(kFwdThreads) linear_forward_kernel(FwdParams P)
+// Margins (and dloss) of rows r = warp_first, warp_first + warp_stride, ... of the mini-batch: one
+// warp per row, lanes over the row's elements, fp64 shuffle reduction.
+template <bool RO>
+__device__ __forceinline__ void forward_rows(const FwdParams &P, int warp_first, int warp_stride)
 {
     const int lane = threadIdx.x & 31;
-    const int warps_per_cta = kFwdThreads / 32;
-    for (int r = blockIdx.x * warps_per_cta + (threadIdx.x >> 5); r < P.n_rows; r += gridDim.x * warps_per_cta) {
+    for (int r = warp_first; r < P.n_rows; r += warp_stride) {
         const int64_t row = P.row0 + r;
         const int64_t p0 = P.rowptr[row], p1 = P.rowptr[row + 1];
         double acc = 0.0;
         for (int64_t p = p0 + lane; p < p1; p += 32) {
             const uint32_t f = __ldcs(P.feature + p);
             const float x = __ldcs(P.value + p);
-            if (f < P.dims) acc += (double)__fmul_rn(weight_at(P.wv, f), x);
+            if (f < P.dims) acc += (double)__fmul_rn(weight_at<RO>(P.wv, f), x);
             else atomicOr(P.bad, 1u);
         }
         acc = warp_sum(acc);
@@ -118,6 +124,65 @@ __global__ void __launch_bounds__(kFwdThreads) linear_forward_kernel(FwdParams P
             }
         }
     }
+}
+
+// Forward for a small mini-batch inside one CTA: 8 lanes per row and four rows in flight per group,
+// so that the three dependent loads of a row (row pointer -> feature/value -> weight) overlap
+// across rows instead of queueing behind each other.  Same fp64 sums, other (fixed) tree order.
+__device__ __forceinline__ void forward_rows_small(const FwdParams &P)
+{
+    constexpr int G = 8, R = 4;
+    const int sub = threadIdx.x & (G - 1);
+    const int group = threadIdx.x / G, n_groups = blockDim.x / G;
+    const uint32_t gmask = 0xffu << ((threadIdx.x & 31) & ~(G - 1));
+    for (int r0 = group * R; r0 < P.n_rows; r0 += n_groups * R) {
+        int64_t p0[R], p1[R];
+#pragma unroll
+        for (int u = 0; u < R; u++) {
+            const bool ok = r0 + u < P.n_rows;
+            p0[u] = ok ? P.rowptr[P.row0 + r0 + u] : 0;
+            p1[u] = ok ? P.rowptr[P.row0 + r0 + u + 1] : 0;
+        }
+        double acc[R];
+#pragma unroll
+        for (int u = 0; u < R; u++) acc[u] = 0.0;
+        int64_t longest = 0;
+#pragma unroll
+        for (int u = 0; u < R; u++) longest = max(longest, p1[u] - p0[u]);
+        for (int64_t o = sub; o < longest; o += G) {
+            uint32_t f[R]; float x[R]; bool in[R];
+#pragma unroll
+            for (int u = 0; u < R; u++) {
+                in[u] = p0[u] + o < p1[u];
+                f[u] = in[u] ? __ldcs(P.feature + p0[u] + o) : 0u;
+                x[u] = in[u] ? __ldcs(P.value + p0[u] + o) : 0.0f;
+            }
+#pragma unroll
+            for (int u = 0; u < R; u++)
+                if (in[u]) {
+                    if (f[u] < P.dims) acc[u] += (double)__fmul_rn(weight_at<false>(P.wv, f[u]), x[u]);
+                    else atomicOr(P.bad, 1u);
+                }
+        }
+#pragma unroll
+        for (int u = 0; u < R; u++) {
+#pragma unroll
+            for (int o = G / 2; o > 0; o >>= 1) acc[u] += __shfl_xor_sync(gmask, acc[u], o);
+            if (sub == 0 && r0 + u < P.n_rows) {
+                const int64_t row = P.row0 + r0 + u;
+                const float m = (float)acc[u];
+                P.margin[row - P.block_row0] = m;
+                const float lab = P.label[row];
+                const float y = P.task == HM_TASK_CLASSIFIER ? (lab > 0.0f ? 1.0f : -1.0f) : lab;
+                P.dloss[r0 + u] = dloss_of(P.loss, m, y);
+            }
+        }
+    }
+}
+
+__global__ void __launch_bounds__(kFwdThreads) linear_forward_kernel(FwdParams P)
+{
+    forward_rows<true>(P, blockIdx.x * (kFwdThreads / 32) + (threadIdx.x >> 5), gridDim.x * (kFwdThreads / 32));
 }
 
 // ---- update ------------------------------------------------------------------------
@@ -299,6 +364,139 @@ __device__ __forceinline__ uint4 rec_bits(const SegRec &r)
     return make_uint4((uint32_t)__double2loint(r.sum), (uint32_t)__double2hiint(r.sum), r.key, r.cnt);
 }
 
+// Shared-memory working set of one CTA of the update kernels.
+struct UpdShared {
+    uint32_t *s_key; float *s_val;       // the tile: features and contributions (padded)
+    uint32_t *l_key; float *l_g;         // finished features of the tile, in feature order
+    Scan *s_warp;
+    SegRec *s_carry;                     // open trailing segment of the previous tile
+    SegRec *s_first;                     // the CTA's piece of a segment that began before its range
+    uint32_t *s_carry_open;
+    const uint32_t *s_edge;              // does the CTA's range start / end on a true segment boundary?
+    int *s_nlist;
+};
+
+// Reduce-by-feature of one tile [base, base + n_tile) of the sorted mini-batch: contributions, fp64
+// segmented scan in a fixed order, finished features compacted into S.l_key / S.l_g (*S.s_nlist
+// entries, to be stepped by apply_list), open segments left in S.s_carry / S.s_first.  Ends on a
+// barrier.  RO: dloss was written by an earlier kernel and may use the read-only path.
+template <bool RO>
+__device__ __forceinline__ void reduce_tile(const UpdParams &P, const UpdShared &S, uint32_t base, int n_tile,
+                                            bool first_tile, bool last_tile)
+{
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    // ---- coalesced striped load; contribution = dloss[row] * value (fp32 product)
+    uint32_t k[kUpdItems]; uint2 pv[kUpdItems];
+#pragma unroll
+    for (int i = 0; i < kUpdItems; i++) {
+        const int q = i * kUpdThreads + tid;
+        if (q < n_tile) { k[i] = __ldcs(P.skey + base + q); pv[i] = __ldcs(P.spay + base + q); }
+    }
+#pragma unroll
+    for (int i = 0; i < kUpdItems; i++) {
+        const int q = i * kUpdThreads + tid;
+        if (q < n_tile) {
+            S.s_key[pad_idx(q)] = k[i];
+            S.s_val[pad_idx(q)] = __fmul_rn((RO ? __ldg(P.dloss + pv[i].x) : P.dloss[pv[i].x]), __uint_as_float(pv[i].y));
+        }
+    }
+    __syncthreads();
+    const bool left_closed = S.s_edge[0] != 0, right_closed = S.s_edge[1] != 0;
+    const SegRec carry = *S.s_carry;
+    const uint32_t carry_open = *S.s_carry_open;
+            const uint32_t key0 = S.s_key[pad_idx(0)];
+    const bool edge_continues = carry.cnt != 0 && carry.key == key0;
+    // does a segment touching this tile's left edge reach past the CTA's left edge?
+    const bool edge_open = first_tile ? !left_closed : (edge_continues && carry_open != 0);
+    // the carried segment ended exactly at the tile edge and is complete: thread 0 lists it
+    const bool retire_carry = carry.cnt != 0 && !edge_continues && !carry_open;
+    // the tile's last item closes its segment when the CTA's range ends on a true boundary
+    const bool close_tail = last_tile && right_closed;
+    __syncthreads();  // everyone has read the carry before it is overwritten below
+
+    // ---- pass 1: thread summaries (items [8*tid, 8*tid+8)).  A "head" is an item at tile
+    // position >= 1 whose feature differs from its predecessor; position 0 is never a head:
+    // it either continues the carried segment or starts afresh with an empty running sum.
+    // An item "closes" its segment when the next item has another feature.
+    const int q0 = tid * kUpdItems;
+    Scan mine; mine.v = 0.0; mine.c = 0; mine.f = 0; mine.k = (tid == 0 && retire_carry) ? 1u : 0u;
+    if (tid == 0 && edge_continues) { mine.v = carry.sum; mine.c = carry.cnt; }
+    uint32_t kk[kUpdItems + 1]; float vv[kUpdItems];
+    const uint32_t prev_key = (q0 > 0 && q0 < n_tile) ? S.s_key[pad_idx(q0 - 1)] : 0u;
+#pragma unroll
+    for (int i = 0; i <= kUpdItems; i++) kk[i] = q0 + i < n_tile ? S.s_key[pad_idx(q0 + i)] : 0u;
+#pragma unroll
+    for (int i = 0; i < kUpdItems; i++) {
+        const int q = q0 + i;
+        if (q < n_tile) {
+            vv[i] = S.s_val[pad_idx(q)];
+            const bool head = q > 0 && kk[i] != (i == 0 ? prev_key : kk[i - 1]);
+            if (head) { mine.v = 0.0; mine.c = 0; mine.f = 1; }
+            mine.v += (double)vv[i]; mine.c += 1;
+            const bool closes = q < n_tile - 1 ? kk[i + 1] != kk[i] : close_tail;
+            if (closes) mine.k += 1;
+        }
+    }
+    // ---- exclusive segmented scan of the summaries over the CTA
+    Scan inc = mine;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        Scan up;
+        up.v = __shfl_up_sync(0xffffffffu, inc.v, o);
+        up.c = __shfl_up_sync(0xffffffffu, inc.c, o);
+        up.f = __shfl_up_sync(0xffffffffu, inc.f, o);
+        up.k = __shfl_up_sync(0xffffffffu, inc.k, o);
+        if (lane >= o) inc = combine(up, inc);
+    }
+    if (lane == 31) S.s_warp[warp] = inc;
+    Scan ex;
+    ex.v = __shfl_up_sync(0xffffffffu, inc.v, 1);
+    ex.c = __shfl_up_sync(0xffffffffu, inc.c, 1);
+    ex.f = __shfl_up_sync(0xffffffffu, inc.f, 1);
+    ex.k = __shfl_up_sync(0xffffffffu, inc.k, 1);
+    if (lane == 0) { ex.v = 0.0; ex.c = 0; ex.f = 0; ex.k = 0; }
+    __syncthreads();
+    Scan wp; wp.v = 0.0; wp.c = 0; wp.f = 0; wp.k = 0;
+    for (int w2 = 0; w2 < warp; w2++) wp = combine(wp, S.s_warp[w2]);
+    const Scan cin = combine(wp, ex);
+    if (tid == kUpdThreads - 1) *S.s_nlist = (int)(cin.k + mine.k);
+
+    // ---- pass 2: walk again; every closed segment goes to the list, in feature order
+    double run = cin.v; uint32_t cnt = cin.c; bool seen_head = cin.f != 0;
+    int slot = (int)cin.k;
+    if (tid == 0 && edge_continues) { run = carry.sum; cnt = carry.cnt; }
+    if (tid == 0 && carry.cnt != 0 && !edge_continues) {
+        if (carry_open) *S.s_first = carry;
+        else { S.l_key[slot] = carry.key; S.l_g[slot] = grad_of(P, carry.sum, carry.cnt); slot++; }
+    }
+#pragma unroll
+    for (int i = 0; i < kUpdItems; i++) {
+        const int q = q0 + i;
+        if (q < n_tile) {
+            const bool head = q > 0 && kk[i] != (i == 0 ? prev_key : kk[i - 1]);
+            if (head) { run = 0.0; cnt = 0; seen_head = true; }
+            run += (double)vv[i]; cnt += 1;
+            // open: the segment reaches the tile's left edge and, through it, past the CTA's left edge
+            const bool open = !seen_head && edge_open;
+            const bool closes = q < n_tile - 1 ? kk[i + 1] != kk[i] : close_tail;
+            if (closes) {
+                if (open) {     // at most one such segment per CTA
+                    S.s_first->sum = run; S.s_first->key = kk[i]; S.s_first->cnt = cnt;
+                    S.l_key[slot] = 0xffffffffu; S.l_g[slot] = 0.f;   // placeholder: skipped by apply_list
+                } else {
+                    S.l_key[slot] = kk[i]; S.l_g[slot] = grad_of(P, run, cnt);
+                }
+                slot++;
+                if (q == n_tile - 1) { S.s_carry->cnt = 0; *S.s_carry_open = 0; }
+            } else if (q == n_tile - 1) {
+                S.s_carry->sum = run; S.s_carry->key = kk[i]; S.s_carry->cnt = cnt;
+                *S.s_carry_open = open ? 1u : 0u;
+            }
+        }
+    }
+    __syncthreads();
+}
+
 __global__ void __launch_bounds__(kUpdThreads, 3) linear_update_kernel(UpdParams P)
 {
     __shared__ __align__(16) unsigned char smem_raw[kUpdSmem];
@@ -314,7 +512,7 @@ __global__ void __launch_bounds__(kUpdThreads, 3) linear_update_kernel(UpdParams
     __shared__ uint32_t s_edge[2];   // does the CTA's range start / end on a true segment boundary?
     __shared__ int s_nlist;
 
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int tid = threadIdx.x;
     const uint32_t s0 = P.seg_off[P.seg], s1 = P.seg_off[P.seg + 1];
     const uint32_t n = s1 - s0;
     // contiguous split of the sorted mini-batch over the grid, in whole tiles
@@ -336,120 +534,13 @@ __global__ void __launch_bounds__(kUpdThreads, 3) linear_update_kernel(UpdParams
     }
     if (lo >= hi) __syncthreads();   // (the tile loop below has its own barriers)
 
+    UpdShared S;
+    S.s_key = s_key; S.s_val = s_val; S.l_key = l_key; S.l_g = l_g; S.s_warp = s_warp; S.s_carry = &s_carry;
+    S.s_first = &s_first; S.s_carry_open = &s_carry_open; S.s_edge = s_edge; S.s_nlist = &s_nlist;
     for (uint32_t t0 = lo; t0 < hi; t0 += kUpdTile) {
         const int n_tile = (int)min((uint32_t)kUpdTile, hi - t0);
-        // ---- coalesced striped load; contribution = dloss[row] * value (fp32 product)
-        uint32_t k[kUpdItems]; uint2 pv[kUpdItems];
-#pragma unroll
-        for (int i = 0; i < kUpdItems; i++) {
-            const int q = i * kUpdThreads + tid;
-            if (q < n_tile) { k[i] = __ldcs(P.skey + s0 + t0 + q); pv[i] = __ldcs(P.spay + s0 + t0 + q); }
-        }
-#pragma unroll
-        for (int i = 0; i < kUpdItems; i++) {
-            const int q = i * kUpdThreads + tid;
-            if (q < n_tile) {
-                s_key[pad_idx(q)] = k[i];
-                s_val[pad_idx(q)] = __fmul_rn(__ldg(P.dloss + pv[i].x), __uint_as_float(pv[i].y));
-            }
-        }
-        __syncthreads();
-        const bool left_closed = s_edge[0] != 0, right_closed = s_edge[1] != 0;
-        const SegRec carry = s_carry;
-        const uint32_t carry_open = s_carry_open;
-        const bool first_tile = t0 == lo;
         const bool last_tile = t0 + kUpdTile >= hi;
-        const uint32_t key0 = s_key[pad_idx(0)];
-        const bool edge_continues = carry.cnt != 0 && carry.key == key0;
-        // does a segment touching this tile's left edge reach past the CTA's left edge?
-        const bool edge_open = first_tile ? !left_closed : (edge_continues && carry_open != 0);
-        // the carried segment ended exactly at the tile edge and is complete: thread 0 lists it
-        const bool retire_carry = carry.cnt != 0 && !edge_continues && !carry_open;
-        // the tile's last item closes its segment when the CTA's range ends on a true boundary
-        const bool close_tail = last_tile && right_closed;
-        __syncthreads();  // everyone has read the carry before it is overwritten below
-
-        // ---- pass 1: thread summaries (items [8*tid, 8*tid+8)).  A "head" is an item at tile
-        // position >= 1 whose feature differs from its predecessor; position 0 is never a head:
-        // it either continues the carried segment or starts afresh with an empty running sum.
-        // An item "closes" its segment when the next item has another feature.
-        const int q0 = tid * kUpdItems;
-        Scan mine; mine.v = 0.0; mine.c = 0; mine.f = 0; mine.k = (tid == 0 && retire_carry) ? 1u : 0u;
-        if (tid == 0 && edge_continues) { mine.v = carry.sum; mine.c = carry.cnt; }
-        uint32_t kk[kUpdItems + 1]; float vv[kUpdItems];
-        const uint32_t prev_key = (q0 > 0 && q0 < n_tile) ? s_key[pad_idx(q0 - 1)] : 0u;
-#pragma unroll
-        for (int i = 0; i <= kUpdItems; i++) kk[i] = q0 + i < n_tile ? s_key[pad_idx(q0 + i)] : 0u;
-#pragma unroll
-        for (int i = 0; i < kUpdItems; i++) {
-            const int q = q0 + i;
-            if (q < n_tile) {
-                vv[i] = s_val[pad_idx(q)];
-                const bool head = q > 0 && kk[i] != (i == 0 ? prev_key : kk[i - 1]);
-                if (head) { mine.v = 0.0; mine.c = 0; mine.f = 1; }
-                mine.v += (double)vv[i]; mine.c += 1;
-                const bool closes = q < n_tile - 1 ? kk[i + 1] != kk[i] : close_tail;
-                if (closes) mine.k += 1;
-            }
-        }
-        // ---- exclusive segmented scan of the summaries over the CTA
-        Scan inc = mine;
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            Scan up;
-            up.v = __shfl_up_sync(0xffffffffu, inc.v, o);
-            up.c = __shfl_up_sync(0xffffffffu, inc.c, o);
-            up.f = __shfl_up_sync(0xffffffffu, inc.f, o);
-            up.k = __shfl_up_sync(0xffffffffu, inc.k, o);
-            if (lane >= o) inc = combine(up, inc);
-        }
-        if (lane == 31) s_warp[warp] = inc;
-        Scan ex;
-        ex.v = __shfl_up_sync(0xffffffffu, inc.v, 1);
-        ex.c = __shfl_up_sync(0xffffffffu, inc.c, 1);
-        ex.f = __shfl_up_sync(0xffffffffu, inc.f, 1);
-        ex.k = __shfl_up_sync(0xffffffffu, inc.k, 1);
-        if (lane == 0) { ex.v = 0.0; ex.c = 0; ex.f = 0; ex.k = 0; }
-        __syncthreads();
-        Scan wp; wp.v = 0.0; wp.c = 0; wp.f = 0; wp.k = 0;
-        for (int w2 = 0; w2 < warp; w2++) wp = combine(wp, s_warp[w2]);
-        const Scan cin = combine(wp, ex);
-        if (tid == kUpdThreads - 1) s_nlist = (int)(cin.k + mine.k);
-
-        // ---- pass 2: walk again; every closed segment goes to the list, in feature order
-        double run = cin.v; uint32_t cnt = cin.c; bool seen_head = cin.f != 0;
-        int slot = (int)cin.k;
-        if (tid == 0 && edge_continues) { run = carry.sum; cnt = carry.cnt; }
-        if (tid == 0 && carry.cnt != 0 && !edge_continues) {
-            if (carry_open) s_first = carry;
-            else { l_key[slot] = carry.key; l_g[slot] = grad_of(P, carry.sum, carry.cnt); slot++; }
-        }
-#pragma unroll
-        for (int i = 0; i < kUpdItems; i++) {
-            const int q = q0 + i;
-            if (q < n_tile) {
-                const bool head = q > 0 && kk[i] != (i == 0 ? prev_key : kk[i - 1]);
-                if (head) { run = 0.0; cnt = 0; seen_head = true; }
-                run += (double)vv[i]; cnt += 1;
-                // open: the segment reaches the tile's left edge and, through it, past the CTA's left edge
-                const bool open = !seen_head && edge_open;
-                const bool closes = q < n_tile - 1 ? kk[i + 1] != kk[i] : close_tail;
-                if (closes) {
-                    if (open) {     // at most one such segment per CTA
-                        s_first.sum = run; s_first.key = kk[i]; s_first.cnt = cnt;
-                        l_key[slot] = 0xffffffffu; l_g[slot] = 0.f;   // placeholder: skipped by apply_list
-                    } else {
-                        l_key[slot] = kk[i]; l_g[slot] = grad_of(P, run, cnt);
-                    }
-                    slot++;
-                    if (q == n_tile - 1) { s_carry.cnt = 0; s_carry_open = 0; }
-                } else if (q == n_tile - 1) {
-                    s_carry.sum = run; s_carry.key = kk[i]; s_carry.cnt = cnt;
-                    s_carry_open = open ? 1u : 0u;
-                }
-            }
-        }
-        __syncthreads();
+        reduce_tile<true>(P, S, s0 + t0, n_tile, t0 == lo, last_tile);
         // ---- after the last tile the CTA's boundary pieces are final: publish them and take the
         // completion ticket now, so that both round trips overlap the optimizer step below
         if (last_tile && tid == 0) {
@@ -511,6 +602,58 @@ __global__ void __launch_bounds__(kUpdThreads, 3) linear_update_kernel(UpdParams
     __syncthreads();
     apply_list(P, ml_key, ml_g, s_nlist, tid);
     if (tid == 0) *P.br.ticket = 0;   // ready for the next launch on this stream
+}
+
+// ---- small mini-batches: one persistent CTA ----------------------------------------
+//
+// When a mini-batch is a few hundred rows (-mini_batch 128 is BASELINE.json's configs[0]) two
+// launches per mini-batch are all latency.  This kernel runs up to kSmallSegs consecutive
+// mini-batches of a sorted block in ONE CTA: forward of mini-batch s, barrier, reduce-by-feature and
+// optimizer step of mini-batch s (a single tile, so no piece ever leaves the CTA), barrier, s+1.
+// Same arithmetic, same order as the two-kernel path: the results are bit-identical.
+constexpr int kSmallSegs = 64;
+
+struct SmallParams {
+    FwdParams F;             // row0 / n_rows are filled per mini-batch
+    UpdParams U;             // seg / eta / adam_alpha / inv_rows are filled per mini-batch
+    int32_t first_seg, n_segs, mini_batch;
+    float eta[kSmallSegs], adam_alpha[kSmallSegs];
+    int32_t rows[kSmallSegs];
+};
+
+__global__ void __launch_bounds__(kUpdThreads, 1) linear_small_batch_kernel(const __grid_constant__ SmallParams P)
+{
+    __shared__ __align__(16) unsigned char smem_raw[kUpdSmemTile];
+    __shared__ Scan s_warp[kUpdThreads / 32];
+    __shared__ SegRec s_carry, s_first;
+    __shared__ uint32_t s_carry_open, s_edge[2];
+    __shared__ int s_nlist;
+    UpdShared S;
+    S.s_key = reinterpret_cast<uint32_t *>(smem_raw);
+    S.s_val = reinterpret_cast<float *>(smem_raw + (size_t)kUpdPadded * 4);
+    S.l_key = reinterpret_cast<uint32_t *>(smem_raw + (size_t)kUpdPadded * 8);
+    S.l_g = reinterpret_cast<float *>(smem_raw + (size_t)kUpdPadded * 8 + (size_t)kUpdList * 4);
+    S.s_warp = s_warp; S.s_carry = &s_carry; S.s_first = &s_first; S.s_carry_open = &s_carry_open;
+    S.s_edge = s_edge; S.s_nlist = &s_nlist;
+    const int tid = threadIdx.x;
+    for (int s = 0; s < P.n_segs; s++) {
+        FwdParams F = P.F;
+        F.row0 = P.F.block_row0 + (int64_t)(P.first_seg + s) * P.mini_batch;
+        F.n_rows = P.rows[s];
+        forward_rows_small(F);
+        if (tid == 0) { s_carry.cnt = 0; s_carry_open = 0; s_first.cnt = 0; s_edge[0] = 1; s_edge[1] = 1; s_nlist = 0; }
+        __syncthreads();     // dloss of every row is written; the whole mini-batch is one closed range
+        UpdParams U = P.U;
+        U.seg = P.first_seg + s; U.eta = P.eta[s]; U.adam_alpha = P.adam_alpha[s];
+        U.inv_rows = 1.0 / (double)P.rows[s];
+        const uint32_t s0 = U.seg_off[U.seg];
+        const int n = (int)(U.seg_off[U.seg + 1] - s0);       // <= kUpdTile, checked by the host
+        if (n > 0) {
+            reduce_tile<false>(U, S, s0, n, true, true);
+            apply_list(U, S.l_key, S.l_g, s_nlist, tid);
+        }
+        __syncthreads();     // the step is complete before the next forward reads the replica
+    }
 }
 
 // ---- model table --------------------------------------------------------------------
@@ -723,6 +866,36 @@ hm_status launch_linear_update(Launcher &L, const LinearArgs &a, const StepScala
     // state traffic (number of distinct features is data dependent) are not counted
     const double bytes = 12.0 * (double)nnz_hint;
     HM_LAUNCH(L, K_LIN_UPDATE, bytes, (linear_update_kernel<<<grid, kUpdThreads, 0, L.stream>>>(P)));
+    HM_CUDA(cudaGetLastError());
+    return HM_OK;
+}
+
+bool small_batch_eligible(int32_t mini_batch, int64_t max_mb_elems)
+{
+    return mini_batch <= 1024 && max_mb_elems <= kUpdTile;
+}
+
+hm_status launch_linear_small_batches(Launcher &L, const LinearArgs &a, const int64_t *d_rowptr, int64_t block_row0,
+                                      int first_seg, int n_segs, const int32_t *rows, const float *eta,
+                                      const float *adam_alpha, const uint32_t *d_feature, const float *d_value,
+                                      const float *d_label, float *d_margin, float *d_dloss, uint32_t *d_bad,
+                                      const uint32_t *d_sorted_key, const uint2 *d_sorted_pay, const uint32_t *d_seg_off,
+                                      int64_t nnz_hint)
+{
+    if (n_segs < 1 || n_segs > kSmallSegs) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "small-batch launch of %d mini-batches", n_segs);
+    SmallParams P;
+    std::memset(&P, 0, sizeof(P));
+    P.F.wv = a.wv; P.F.rowptr = d_rowptr; P.F.feature = d_feature; P.F.value = d_value; P.F.label = d_label;
+    P.F.margin = d_margin; P.F.dloss = d_dloss; P.F.block_row0 = block_row0;
+    P.F.task = a.cfg.task; P.F.loss = a.cfg.loss; P.F.train = 1; P.F.dims = (uint32_t)a.cfg.dims; P.F.bad = d_bad;
+    P.U.rec = a.rec; P.U.rec_width = a.rec_width; P.U.ftrl_derived = a.wv.ftrl; P.U.touched = nullptr;
+    P.U.skey = d_sorted_key; P.U.spay = d_sorted_pay; P.U.dloss = d_dloss; P.U.seg_off = d_seg_off;
+    P.U.dims = (uint32_t)a.cfg.dims; P.U.opt = a.cfg.opt; P.U.reg = a.cfg.reg; P.U.grad_norm = a.cfg.grad_norm;
+    P.U.lambda = a.cfg.lambda; P.U.eps = a.cfg.eps; P.U.rho = a.cfg.rho; P.U.beta1 = a.cfg.beta1; P.U.beta2 = a.cfg.beta2;
+    P.U.alpha = a.cfg.alpha; P.U.beta = a.cfg.beta; P.U.lambda1 = a.cfg.lambda1; P.U.lambda2 = a.cfg.lambda2;
+    P.first_seg = first_seg; P.n_segs = n_segs; P.mini_batch = a.cfg.mini_batch;
+    for (int s = 0; s < n_segs; s++) { P.eta[s] = eta[s]; P.adam_alpha[s] = adam_alpha[s]; P.rows[s] = rows[s]; }
+    HM_LAUNCH(L, K_LIN_UPDATE, 24.0 * (double)nnz_hint, (linear_small_batch_kernel<<<1, kUpdThreads, 0, L.stream>>>(P)));
     HM_CUDA(cudaGetLastError());
     return HM_OK;
 }
