@@ -149,23 +149,34 @@ def measured_peaks() -> tuple[float, str]:
         return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
+_CPU_DATA = {}
+
+
+def _cpu_rows(rows: int):
+    """First `rows` rows of the synthetic stream as host arrays (generated once per process)."""
+    from hivemall_b200 import synth
+    import numpy as np
+    have = _CPU_DATA.get("rows", 0)
+    if have < rows:
+        pieces = [synth.criteo_like(min(1 << 20, rows - r0), dims=DIMS, seed=SEED, row0=r0) for r0 in range(0, rows, 1 << 20)]
+        _CPU_DATA.update(rows=rows,
+                         feature=np.concatenate([p.feature.numpy() for p in pieces]),
+                         value=np.concatenate([p.value.numpy() for p in pieces]),
+                         label=np.concatenate([p.label.numpy() for p in pieces]))
+    d = _CPU_DATA
+    return (np.arange(rows + 1, dtype=np.int64) * NNZ_PER_ROW, d["feature"][: rows * NNZ_PER_ROW],
+            d["value"][: rows * NNZ_PER_ROW], d["label"][:rows])
+
+
 def cpu_baseline(rows: int, threads: int, workload: str = "ftrl") -> dict:
     """Oracle (OpenMP for the linear learner, scalar for train_fm) on the first `rows` rows of
-    the same synthetic stream."""
+    the same synthetic stream; only the training call is timed."""
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     import hivemall_b200 as hm
-    from hivemall_b200 import synth
     import _oracle
     fn, options, _ = WORKLOADS[workload]
     cfg = _oracle.config_from(hm.parse_options(fn, options))
-    pieces = []
-    for r0 in range(0, rows, 1 << 20):
-        pieces.append(synth.criteo_like(min(1 << 20, rows - r0), dims=DIMS, seed=SEED, row0=r0))
-    import numpy as np
-    feature = np.concatenate([p.feature.numpy() for p in pieces])
-    value = np.concatenate([p.value.numpy() for p in pieces])
-    label = np.concatenate([p.label.numpy() for p in pieces])
-    rowptr = np.arange(rows + 1, dtype=np.int64) * NNZ_PER_ROW
+    rowptr, feature, value, label = _cpu_rows(rows)
     if fn == "train_fm":
         threads = 1
         t0 = time.perf_counter()
@@ -173,7 +184,6 @@ def cpu_baseline(rows: int, threads: int, workload: str = "ftrl") -> dict:
         dt = time.perf_counter() - t0
         what = "hmo_train_fm (scalar)"
     else:
-        _oracle.train_linear_mt(cfg, rowptr[: MINI_BATCH + 1], feature, value, label[:MINI_BATCH], threads)  # page in
         t0 = time.perf_counter()
         _oracle.train_linear_mt(cfg, rowptr, feature, value, label, threads)
         dt = time.perf_counter() - t0
@@ -189,9 +199,11 @@ def run_reference_arm(args) -> None:
     if rank != 0:
         return
     threads = os.cpu_count() or 1
-    # calibrate so that each step is a bounded sample (~5 s), whole run within a few minutes
-    probe = cpu_baseline(2 * MINI_BATCH, threads, args.workload)
-    rows = int(max(2 * MINI_BATCH, min(probe["value"] * 5.0, 16 * MINI_BATCH)))
+    # each step is a bounded sample of the stream sized for about 3 s of CPU work (so that the
+    # one-off allocation cost of a call does not dominate), whole run within a few minutes
+    probe = cpu_baseline(4 * MINI_BATCH, threads, args.workload)
+    budget = max(0.5, min(3.0, 150.0 / max(1, args.steps + args.warmup)))
+    rows = int(max(4 * MINI_BATCH, min(probe["value"] * budget, 512 * MINI_BATCH)))
     rows = rows // MINI_BATCH * MINI_BATCH
     times = []
     for i in range(args.warmup + args.steps):
@@ -208,8 +220,8 @@ def run_reference_arm(args) -> None:
         "config": {"workload": WORKLOADS[args.workload][2],
                    "options": WORKLOADS[args.workload][1], "mini_batch": MINI_BATCH, "rows_per_step": rows,
                    "note": "CPU arm; each step is a bounded sample of the stream"},
-        "cpu_baseline": {"value": value, "unit": "examples/s", "cores": threads, "kind": "port",
-                         "sample": f"{rows} rows per step, OpenMP oracle; the reference mount holds no code to run"},
+        "cpu_baseline": {"value": value, "unit": "examples/s", "cores": r["cores"], "kind": "port",
+                         "sample": f"{rows} rows per step, {r['sample']}"},
         "e2e": {"value": value, "unit": "examples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -402,7 +414,7 @@ def main():
         rows = args.cpu_sample_rows
         if rows <= 0:
             probe = cpu_baseline(2 * MINI_BATCH, threads, args.workload)
-            rows = int(max(2 * MINI_BATCH, min(probe["value"] * 15.0, 1024 * MINI_BATCH)))
+            rows = int(max(2 * MINI_BATCH, min(probe["value"] * 15.0, 512 * MINI_BATCH)))
         rows = max(MINI_BATCH, rows // MINI_BATCH * MINI_BATCH)
         cpu = cpu_baseline(rows, threads, args.workload)
         cpu.pop("seconds", None)
