@@ -6,11 +6,14 @@
 // (README.md:20-22); the arithmetic contract is DESIGN.md section 3 and the CPU oracle
 // (oracle/hm_oracle.c) restates the same contract independently.
 //
-//   linear_forward_kernel   warp per row: gather w, margin in fp64, dloss[row]
-//   linear_update_kernel    streams the feature-sorted mini-batch (feature, row, value), forms
-//                           dloss[row]*value, reduce-by-feature in fp64 in a fixed order (no float
-//                           atomics) fused with the optimizer update; only segments that really
-//                           straddle two CTAs are left to the last CTA to finish
+//   linear_forward_kernel      warp per row: gather the weight out of the feature's record (FTRL:
+//                              derive it from (z, n)), margin in fp64, dloss[row]
+//   linear_update_kernel       one tile of the feature-sorted mini-batch per CTA: dloss[row]*value,
+//                              reduce-by-feature in fp64 in a fixed order (no float atomics), finished
+//                              features stepped in batches; only segments that really straddle CTAs
+//                              leave records, summed by the last CTA to finish (reduce_tile, apply_list)
+//   linear_small_batch_kernel  mini-batches of a few hundred rows: one persistent CTA runs forward and
+//                              reduce+step for up to 64 mini-batches per launch
 //   predict / export / scale helpers
 #include "hm_internal.h"
 #include <algorithm>
