@@ -262,124 +262,288 @@ __device__ __forceinline__ void fm_apply_pending(const FmUpdParams &P, int npend
     }
 }
 
-template <int NF>
-__global__ void __launch_bounds__(kFmWarps * 32) fm_update_kernel(FmUpdParams P)
+// ---- update: one 1024-element chunk of the feature-sorted mini-batch per CTA ------------
+//
+// Every thread owns four consecutive elements.  The segment structure (where a feature's run
+// starts and ends, which list slot a finished feature gets, whether a run continues outside the
+// chunk) is computed once; then the per-feature fp64 sums are formed kFmNV values at a time with
+// the same thread-serial + warp-shuffle + cross-warp segmented scan as the linear learner: group
+// 0 carries (A1, A2), the following groups four factors each (GS_f).  After each group the
+// finished features' parameters are stepped (loads batched per thread).  Runs that straddle
+// chunks leave their piece in first_* / last_* for fm_merge_kernel, exactly as before.
+constexpr int kFmThreads = 256;
+constexpr int kFmItems = kFmChunk / kFmThreads;     // 4
+constexpr int kFmNV = 4;                            // values reduced per pass
+constexpr int kFmPad = kFmChunk + kFmChunk / 32 + 2;
+__device__ __forceinline__ int fm_pad(int q) { return q + (q >> 5); }
+
+struct FmScan { double v[kFmNV]; uint32_t c; uint32_t f; };
+__device__ __forceinline__ FmScan fm_combine(const FmScan &a, const FmScan &b)
+{
+    FmScan r;
+    r.f = a.f | b.f;
+    r.c = b.f ? b.c : a.c + b.c;
+#pragma unroll
+    for (int v = 0; v < kFmNV; v++) r.v[v] = b.f ? b.v[v] : a.v[v] + b.v[v];
+    return r;
+}
+
+constexpr size_t kFmSmem =
+    (size_t)kFmPad * 4 * 4                       // key, row, c1, c2
+    + (size_t)kFmChunk * (4 + 4 + 8 + 8)         // list: key, cnt, A1, A2
+    + (size_t)kFmChunk * kFmNV * 8;              // list: the current group's sums
+
+__global__ void __launch_bounds__(kFmThreads) fm_update_kernel(FmUpdParams P)
 {
     extern __shared__ __align__(16) unsigned char fm_smem[];
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int k = P.k;
-    // per warp: kFmBatch headers + kFmBatch * k sums
-    const size_t per_warp = (size_t)kFmBatch * (sizeof(FmPieceHdr) + (size_t)k * sizeof(double));
-    FmPieceHdr *ph = reinterpret_cast<FmPieceHdr *>(fm_smem + per_warp * warp);
-    double *pgs = reinterpret_cast<double *>(fm_smem + per_warp * warp + kFmBatch * sizeof(FmPieceHdr));
+    uint32_t *s_key = reinterpret_cast<uint32_t *>(fm_smem);
+    uint32_t *s_row = s_key + kFmPad;
+    float *s_c1 = reinterpret_cast<float *>(s_row + kFmPad);
+    float *s_c2 = s_c1 + kFmPad;
+    uint32_t *l_key = reinterpret_cast<uint32_t *>(s_c2 + kFmPad);
+    uint32_t *l_cnt = l_key + kFmChunk;
+    double *l_a1 = reinterpret_cast<double *>(l_cnt + kFmChunk);
+    double *l_a2 = l_a1 + kFmChunk;
+    double *l_gs = l_a2 + kFmChunk;              // [kFmNV][kFmChunk]
+    __shared__ FmScan s_warp[kFmThreads / 32];
+    __shared__ int s_wk[kFmThreads / 32];
+    __shared__ uint32_t s_edge[2];
 
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int k = P.k;
     const uint32_t s0 = P.seg_off[P.seg], n = P.seg_off[P.seg + 1] - s0;
-    const int chunk = blockIdx.x * kFmWarps + warp;
-    if (chunk >= P.n_chunks) return;
-    const uint32_t c0 = (uint32_t)chunk * kFmChunk, c1 = min(n, c0 + (uint32_t)kFmChunk);
+    const int chunk = blockIdx.x;
+    const uint32_t c0 = (uint32_t)chunk * kFmChunk, c1e = min(n, c0 + (uint32_t)kFmChunk);
     FmPieceHdr none; none.a1 = 0; none.a2 = 0; none.key = 0; none.cnt = 0; none.pad[0] = none.pad[1] = 0;
-    if (c0 >= c1) {
-        if (lane == 0) { P.first_hdr[chunk] = none; P.last_hdr[chunk] = none; }
+    if (c0 >= c1e) {
+        if (tid == 0) { P.first_hdr[chunk] = none; P.last_hdr[chunk] = none; }
         return;
     }
-    // does the chunk's first / last feature run continue outside the chunk?
-    const bool left_open = c0 > 0 && __ldg(P.skey + s0 + c0 - 1) == __ldg(P.skey + s0 + c0);
-    const bool right_open = c1 < n && __ldg(P.skey + s0 + c1) == __ldg(P.skey + s0 + c1 - 1);
-
-    uint32_t cur_key = 0, cnt = 0;
-    bool have = false, cur_open_left = false, wrote_first = false;
-    double a1 = 0.0, a2 = 0.0, gs[NF];
+    const int nt = (int)(c1e - c0);
+    // does the chunk's first / last feature run continue outside the chunk?  (consumed after the barrier)
+    if (tid == 32) {
+        s_edge[0] = c0 > 0 && __ldg(P.skey + s0 + c0 - 1) == __ldg(P.skey + s0 + c0);
+        s_edge[1] = c1e < n && __ldg(P.skey + s0 + c1e) == __ldg(P.skey + s0 + c1e - 1);
+    }
+    // ---- load: coalesced, striped; c1 = dloss*x, c2 = c1*x (fp32 products)
+    {
+        uint32_t kx[kFmItems]; uint2 pv[kFmItems];
 #pragma unroll
-    for (int q = 0; q < NF; q++) gs[q] = 0.0;
-    int npend = 0;
-
-    // a finished feature: to the `first` piece if its run began before the chunk, else to the list
-    auto close_segment = [&]() {
-        if (cur_open_left) {
-            if (lane == 0) { FmPieceHdr h = none; h.a1 = a1; h.a2 = a2; h.key = cur_key; h.cnt = cnt; P.first_hdr[chunk] = h; }
-#pragma unroll
-            for (int q = 0; q < NF; q++) { const int fi = lane + 32 * q; if (fi < k) P.first_gs[(size_t)chunk * k + fi] = gs[q]; }
-            wrote_first = true;
-        } else {
-            if (lane == 0) { ph[npend].a1 = a1; ph[npend].a2 = a2; ph[npend].key = cur_key; ph[npend].cnt = cnt; }
-#pragma unroll
-            for (int q = 0; q < NF; q++) { const int fi = lane + 32 * q; if (fi < k) pgs[npend * k + fi] = gs[q]; }
-            npend++;
+        for (int i = 0; i < kFmItems; i++) {
+            const int q = i * kFmThreads + tid;
+            if (q < nt) { kx[i] = __ldcs(P.skey + s0 + c0 + q); pv[i] = __ldcs(P.spay + s0 + c0 + q); }
         }
-    };
-
-    for (uint32_t b0 = c0; b0 < c1; b0 += kFmBatch) {
-        // headers of the batch: lanes 0..15 take one element each
-        const uint32_t e = b0 + lane;
-        const bool valid = lane < kFmBatch && e < c1;
-        uint32_t key_l = 0xffffffffu, row_l = 0;
-        float c1_l = 0.0f, c2_l = 0.0f;
-        if (valid) {
-            key_l = __ldcs(P.skey + s0 + e);
-            const uint2 pv = __ldcs(P.spay + s0 + e);
-            row_l = pv.x;
-            const float x = __uint_as_float(pv.y);
-            c1_l = __fmul_rn(__ldg(P.dloss + row_l), x);
-            c2_l = __fmul_rn(c1_l, x);
-        }
-        // S rows of all elements of the batch, requested together
-        float srow[kFmBatch][NF];
-        const int nb = (int)min((uint32_t)kFmBatch, c1 - b0);
 #pragma unroll
-        for (int u = 0; u < kFmBatch; u++) {
-            const uint32_t row_u = __shfl_sync(0xffffffffu, row_l, u);
-#pragma unroll
-            for (int q = 0; q < NF; q++) {
-                const int fi = lane + 32 * q;
-                srow[u][q] = (u < nb && fi < k) ? __ldg(P.stab + (size_t)row_u * k + fi) : 0.0f;
+        for (int i = 0; i < kFmItems; i++) {
+            const int q = i * kFmThreads + tid;
+            if (q < nt) {
+                const float x = __uint_as_float(pv[i].y);
+                const float c1 = __fmul_rn(__ldg(P.dloss + pv[i].x), x);
+                s_key[fm_pad(q)] = kx[i]; s_row[fm_pad(q)] = pv[i].x;
+                s_c1[fm_pad(q)] = c1; s_c2[fm_pad(q)] = __fmul_rn(c1, x);
             }
         }
-        // elements in sorted order (warp-uniform control flow)
+    }
+    __syncthreads();
+    const bool left_open = s_edge[0] != 0, right_open = s_edge[1] != 0;
+
+    // ---- structure of this thread's items [4*tid, 4*tid+4)
+    const int q0 = tid * kFmItems;
+    uint32_t kk[kFmItems + 1], rr[kFmItems];
+    const uint32_t prev_key = (q0 > 0 && q0 < nt) ? s_key[fm_pad(q0 - 1)] : 0u;
 #pragma unroll
-        for (int u = 0; u < kFmBatch; u++) {
-            const uint32_t key_u = __shfl_sync(0xffffffffu, key_l, u);
-            const float c1_u = __shfl_sync(0xffffffffu, c1_l, u);
-            const float c2_u = __shfl_sync(0xffffffffu, c2_l, u);
-            if (u < nb) {
-                if (!have || key_u != cur_key) {
-                    if (have) close_segment();
-                    cur_open_left = !have && left_open;     // only the chunk's first run can be open to the left
-                    have = true; cur_key = key_u; cnt = 0; a1 = 0.0; a2 = 0.0;
+    for (int i = 0; i <= kFmItems; i++) kk[i] = q0 + i < nt ? s_key[fm_pad(q0 + i)] : 0u;
 #pragma unroll
-                    for (int q = 0; q < NF; q++) gs[q] = 0.0;
+    for (int i = 0; i < kFmItems; i++) rr[i] = q0 + i < nt ? s_row[fm_pad(q0 + i)] : 0u;
+    bool head[kFmItems], closes[kFmItems];
+    int my_closes = 0; uint32_t my_head = 0;
+#pragma unroll
+    for (int i = 0; i < kFmItems; i++) {
+        const int q = q0 + i;
+        head[i] = q < nt && q > 0 && kk[i] != (i == 0 ? prev_key : kk[i - 1]);
+        closes[i] = q < nt && (q < nt - 1 ? kk[i + 1] != kk[i] : !right_open);
+        my_closes += closes[i]; my_head |= head[i];
+    }
+    // exclusive scans over threads: list slot base, and "is there a head before my first item"
+    __shared__ uint32_t s_anyhead[kFmThreads / 32];
+    int inc = my_closes;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const int v = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += v; }
+    const uint32_t warp_heads = __ballot_sync(0xffffffffu, my_head != 0);
+    if (lane == 31) s_wk[warp] = inc;
+    if (lane == 0) s_anyhead[warp] = warp_heads != 0;
+    __syncthreads();
+    int slot0 = inc - my_closes;
+    bool seen_head_before = (warp_heads & ((1u << lane) - 1u)) != 0;
+    for (int w2 = 0; w2 < warp; w2++) { slot0 += s_wk[w2]; seen_head_before = seen_head_before || s_anyhead[w2] != 0; }
+    int n_list = 0;
+    for (int w2 = 0; w2 < kFmThreads / 32; w2++) n_list += s_wk[w2];
+
+    const int n_groups = 1 + (k + kFmNV - 1) / kFmNV;
+    for (int g = 0; g < n_groups; g++) {
+        const int f0 = (g - 1) * kFmNV;          // first factor of the group (g >= 1)
+        // ---- values of my items
+        float val[kFmItems][kFmNV];
+#pragma unroll
+        for (int i = 0; i < kFmItems; i++) {
+            const int q = q0 + i;
+#pragma unroll
+            for (int v = 0; v < kFmNV; v++) val[i][v] = 0.0f;
+            if (q < nt) {
+                if (g == 0) { val[i][0] = s_c1[fm_pad(q)]; val[i][1] = s_c2[fm_pad(q)]; }
+                else {
+                    const float c1 = s_c1[fm_pad(q)];
+#pragma unroll
+                    for (int v = 0; v < kFmNV; v++)
+                        if (f0 + v < k) val[i][v] = __fmul_rn(c1, __ldg(P.stab + (size_t)rr[i] * k + f0 + v));
                 }
-                a1 += (double)c1_u; a2 += (double)c2_u; cnt += 1;
-#pragma unroll
-                for (int q = 0; q < NF; q++) gs[q] += (double)__fmul_rn(c1_u, srow[u][q]);
             }
         }
-        __syncwarp();
-        if (npend > 0) { fm_apply_pending<NF>(P, npend, ph, pgs, lane); npend = 0; }
-        __syncwarp();
-    }
-    // the chunk's trailing run is finished here only if it really ends at the chunk's end
-    if (have && !right_open) {
-        close_segment(); have = false;
-        __syncwarp();
-        if (npend > 0) { fm_apply_pending<NF>(P, npend, ph, pgs, lane); npend = 0; }
-        __syncwarp();
-    }
-    // publish the pieces (every chunk writes both headers, so nothing stale is ever read)
-    if (have) {   // trailing run continues in the next chunk
-        if (cur_open_left) {        // the whole chunk lies inside one run: it is a `first` piece
-            if (lane == 0) { FmPieceHdr h = none; h.a1 = a1; h.a2 = a2; h.key = cur_key; h.cnt = cnt; P.first_hdr[chunk] = h; P.last_hdr[chunk] = none; }
+        // ---- thread summary, exclusive segmented scan over the CTA
+        FmScan mine; mine.c = 0; mine.f = 0;
 #pragma unroll
-            for (int q = 0; q < NF; q++) { const int fi = lane + 32 * q; if (fi < k) P.first_gs[(size_t)chunk * k + fi] = gs[q]; }
-            wrote_first = true;
-        } else {
-            if (lane == 0) { FmPieceHdr h = none; h.a1 = a1; h.a2 = a2; h.key = cur_key; h.cnt = cnt; P.last_hdr[chunk] = h; }
+        for (int v = 0; v < kFmNV; v++) mine.v[v] = 0.0;
 #pragma unroll
-            for (int q = 0; q < NF; q++) { const int fi = lane + 32 * q; if (fi < k) P.last_gs[(size_t)chunk * k + fi] = gs[q]; }
+        for (int i = 0; i < kFmItems; i++)
+            if (q0 + i < nt) {
+                if (head[i]) { mine.f = 1; mine.c = 0;
+#pragma unroll
+                    for (int v = 0; v < kFmNV; v++) mine.v[v] = 0.0; }
+                mine.c += 1;
+#pragma unroll
+                for (int v = 0; v < kFmNV; v++) mine.v[v] += (double)val[i][v];
+            }
+        FmScan sc = mine;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            FmScan up;
+            up.c = __shfl_up_sync(0xffffffffu, sc.c, o);
+            up.f = __shfl_up_sync(0xffffffffu, sc.f, o);
+#pragma unroll
+            for (int v = 0; v < kFmNV; v++) up.v[v] = __shfl_up_sync(0xffffffffu, sc.v[v], o);
+            if (lane >= o) sc = fm_combine(up, sc);
         }
-    } else if (lane == 0) {
-        P.last_hdr[chunk] = none;
+        __syncthreads();                           // s_warp / l_gs of the previous group are free
+        if (lane == 31) s_warp[warp] = sc;
+        FmScan ex;
+        ex.c = __shfl_up_sync(0xffffffffu, sc.c, 1);
+        ex.f = __shfl_up_sync(0xffffffffu, sc.f, 1);
+#pragma unroll
+        for (int v = 0; v < kFmNV; v++) ex.v[v] = __shfl_up_sync(0xffffffffu, sc.v[v], 1);
+        if (lane == 0) { ex.c = 0; ex.f = 0;
+#pragma unroll
+            for (int v = 0; v < kFmNV; v++) ex.v[v] = 0.0; }
+        __syncthreads();
+        FmScan wp; wp.c = 0; wp.f = 0;
+#pragma unroll
+        for (int v = 0; v < kFmNV; v++) wp.v[v] = 0.0;
+        for (int w2 = 0; w2 < warp; w2++) wp = fm_combine(wp, s_warp[w2]);
+        const FmScan cin = fm_combine(wp, ex);
+        // ---- second walk: totals of the runs that end in my items
+        double run[kFmNV]; uint32_t cnt = cin.c;
+#pragma unroll
+        for (int v = 0; v < kFmNV; v++) run[v] = cin.v[v];
+        bool seen_head = seen_head_before;
+        int slot = slot0;
+#pragma unroll
+        for (int i = 0; i < kFmItems; i++) {
+            const int q = q0 + i;
+            if (q < nt) {
+                if (head[i]) { seen_head = true; cnt = 0;
+#pragma unroll
+                    for (int v = 0; v < kFmNV; v++) run[v] = 0.0; }
+                cnt += 1;
+#pragma unroll
+                for (int v = 0; v < kFmNV; v++) run[v] += (double)val[i][v];
+                const bool open_left = !seen_head && left_open;      // the run began before the chunk
+                const bool tail_piece = q == nt - 1 && right_open;   // the run continues after the chunk
+                if (closes[i] || tail_piece) {
+                    // a piece for fm_merge_kernel (first: open to the left, or the whole chunk; last: open to the right)
+                    const bool to_first = open_left, to_last = !open_left && tail_piece;
+                    if (to_first || to_last) {
+                        FmPieceHdr *hd = to_first ? P.first_hdr : P.last_hdr;
+                        double *gsp = to_first ? P.first_gs : P.last_gs;
+                        if (g == 0) { FmPieceHdr h = none; h.a1 = run[0]; h.a2 = run[1]; h.key = kk[i]; h.cnt = cnt; hd[chunk] = h; }
+                        else {
+#pragma unroll
+                            for (int v = 0; v < kFmNV; v++) if (f0 + v < k) gsp[(size_t)chunk * k + f0 + v] = run[v];
+                        }
+                    }
+                    if (closes[i]) {
+                        if (to_first) { if (g == 0) { l_key[slot] = 0xffffffffu; l_cnt[slot] = 0; } }
+                        else if (g == 0) { l_key[slot] = kk[i]; l_cnt[slot] = cnt; l_a1[slot] = run[0]; l_a2[slot] = run[1]; }
+                        else {
+#pragma unroll
+                            for (int v = 0; v < kFmNV; v++) l_gs[v * kFmChunk + slot] = run[v];
+                        }
+                        slot++;
+                    }
+                }
+            }
+        }
+        __syncthreads();
+        // ---- step the finished features: group 0 -> w (and touched), group g -> factors f0..f0+3
+        constexpr int kPerT = kFmChunk / kFmThreads;
+        if (g == 0) {
+            float wv[kPerT], wa[kPerT]; bool ok[kPerT];
+#pragma unroll
+            for (int u = 0; u < kPerT; u++) {
+                const int e = u * kFmThreads + tid;
+                ok[u] = e < n_list && l_key[e] < P.dims;
+                if (ok[u]) { const uint32_t j = l_key[e]; wv[u] = P.wrec[(size_t)j * P.ww]; wa[u] = P.adagrad ? P.wrec[(size_t)j * P.ww + 1] : 0.0f; }
+            }
+#pragma unroll
+            for (int u = 0; u < kPerT; u++)
+                if (ok[u]) {
+                    const int e = u * kFmThreads + tid;
+                    const uint32_t j = l_key[e];
+                    fm_step(P, fm_grad(P, l_a1[e], l_cnt[e]), P.lambda_w, wv[u], wa[u]);
+                    P.wrec[(size_t)j * P.ww] = wv[u];
+                    if (P.adagrad) P.wrec[(size_t)j * P.ww + 1] = wa[u];
+                    P.touched[j] = 1;
+                }
+        } else {
+            float vv[kPerT][kFmNV], va[kPerT][kFmNV]; bool ok[kPerT];
+#pragma unroll
+            for (int u = 0; u < kPerT; u++) {
+                const int e = u * kFmThreads + tid;
+                ok[u] = e < n_list && l_key[e] < P.dims;
+                if (ok[u]) {
+                    const uint32_t j = l_key[e];
+#pragma unroll
+                    for (int v = 0; v < kFmNV; v++)
+                        if (f0 + v < k) {
+                            vv[u][v] = P.vrec[(size_t)j * P.vw + f0 + v];
+                            va[u][v] = P.adagrad ? P.vrec[(size_t)j * P.vw + k + f0 + v] : 0.0f;
+                        }
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < kPerT; u++)
+                if (ok[u]) {
+                    const int e = u * kFmThreads + tid;
+                    const uint32_t j = l_key[e];
+                    const double a2 = l_a2[e]; const uint32_t cn = l_cnt[e];
+#pragma unroll
+                    for (int v = 0; v < kFmNV; v++)
+                        if (f0 + v < k) {
+                            const double G = l_gs[v * kFmChunk + e] - (double)vv[u][v] * a2;
+                            fm_step(P, fm_grad(P, G, cn), P.lambda_v, vv[u][v], va[u][v]);
+                            P.vrec[(size_t)j * P.vw + f0 + v] = vv[u][v];
+                            if (P.adagrad) P.vrec[(size_t)j * P.vw + k + f0 + v] = va[u][v];
+                        }
+                }
+        }
     }
-    if (!wrote_first && lane == 0) P.first_hdr[chunk] = none;
+    // a chunk without a piece on one side says so (group 0 wrote the headers that exist)
+    __syncthreads();
+    if (tid == 0) {
+        // first piece exists iff the first run is open to the left; last piece iff the trailing run is
+        // open to the right and did not begin before the chunk
+        const bool whole = left_open && right_open && s_key[fm_pad(0)] == s_key[fm_pad(nt - 1)];
+        if (!left_open) P.first_hdr[chunk] = none;
+        if (!right_open || whole) P.last_hdr[chunk] = none;
+    }
 }
 
 // One warp per chunk: a non-empty `last` piece starts a run that continues through the `first`
@@ -467,7 +631,6 @@ int fm_grid(int64_t ctas_wanted, int per_sm)
     return (int)(ctas_wanted < cap ? ctas_wanted : cap);
 }
 
-size_t fm_update_smem(int k) { return (size_t)kFmWarps * kFmBatch * (sizeof(FmPieceHdr) + (size_t)k * sizeof(double)); }
 
 }  // namespace
 
@@ -526,8 +689,7 @@ hm_status launch_fm_update(Launcher &L, const FmArgs &a, const StepScalars &sc, 
 {
     static bool attr_set = false;
     if (!attr_set) {
-        HM_CUDA(cudaFuncSetAttribute(fm_update_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fm_update_smem(32)));
-        HM_CUDA(cudaFuncSetAttribute(fm_update_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fm_update_smem(64)));
+        HM_CUDA(cudaFuncSetAttribute(fm_update_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kFmSmem));
         attr_set = true;
     }
     const int n_chunks = (int)std::max<int64_t>((nnz + kFmChunk - 1) / kFmChunk, 1);
@@ -546,14 +708,9 @@ hm_status launch_fm_update(Launcher &L, const FmArgs &a, const StepScalars &sc, 
     const int ctas = (n_chunks + kFmWarps - 1) / kFmWarps;
     // algorithmic bytes: sorted stream, S row per element (the per-feature record traffic is data dependent)
     const double bytes = (12.0 + 4.0 * a.k) * (double)nnz;
-    const size_t smem = fm_update_smem(a.k);
-    if (a.k <= 32) {
-        HM_LAUNCH(L, K_FM_UPDATE, bytes, (fm_update_kernel<1><<<ctas, kFmWarps * 32, smem, L.stream>>>(P)));
-        HM_LAUNCH(L, K_FM_UPDATE, 0.0, (fm_merge_kernel<1><<<ctas + 1, kFmWarps * 32, 0, L.stream>>>(P)));
-    } else {
-        HM_LAUNCH(L, K_FM_UPDATE, bytes, (fm_update_kernel<2><<<ctas, kFmWarps * 32, smem, L.stream>>>(P)));
-        HM_LAUNCH(L, K_FM_UPDATE, 0.0, (fm_merge_kernel<2><<<ctas + 1, kFmWarps * 32, 0, L.stream>>>(P)));
-    }
+    HM_LAUNCH(L, K_FM_UPDATE, bytes, (fm_update_kernel<<<n_chunks, kFmThreads, kFmSmem, L.stream>>>(P)));
+    if (a.k <= 32) HM_LAUNCH(L, K_FM_UPDATE, 0.0, (fm_merge_kernel<1><<<ctas + 1, kFmWarps * 32, 0, L.stream>>>(P)));
+    else HM_LAUNCH(L, K_FM_UPDATE, 0.0, (fm_merge_kernel<2><<<ctas + 1, kFmWarps * 32, 0, L.stream>>>(P)));
     HM_CUDA(cudaGetLastError());
     return HM_OK;
 }
