@@ -393,9 +393,15 @@ __global__ void __launch_bounds__(kFmThreads) fm_update_kernel(FmUpdParams P)
                 if (g == 0) { val[i][0] = s_c1[fm_pad(q)]; val[i][1] = s_c2[fm_pad(q)]; }
                 else {
                     const float c1 = s_c1[fm_pad(q)];
+                    if ((k & 3) == 0) {     // rows of S are 16-byte aligned: one load for the four factors
+                        const float4 sv = __ldg(reinterpret_cast<const float4 *>(P.stab + (size_t)rr[i] * k + f0));
+                        val[i][0] = __fmul_rn(c1, sv.x); val[i][1] = __fmul_rn(c1, sv.y);
+                        val[i][2] = __fmul_rn(c1, sv.z); val[i][3] = __fmul_rn(c1, sv.w);
+                    } else {
 #pragma unroll
-                    for (int v = 0; v < kFmNV; v++)
-                        if (f0 + v < k) val[i][v] = __fmul_rn(c1, __ldg(P.stab + (size_t)rr[i] * k + f0 + v));
+                        for (int v = 0; v < kFmNV; v++)
+                            if (f0 + v < k) val[i][v] = __fmul_rn(c1, __ldg(P.stab + (size_t)rr[i] * k + f0 + v));
+                    }
                 }
             }
         }
@@ -504,18 +510,28 @@ __global__ void __launch_bounds__(kFmThreads) fm_update_kernel(FmUpdParams P)
                 }
         } else {
             float vv[kPerT][kFmNV], va[kPerT][kFmNV]; bool ok[kPerT];
+            const bool vec = (k & 3) == 0;          // factor records are 16-byte aligned: one load / store per four factors
 #pragma unroll
             for (int u = 0; u < kPerT; u++) {
                 const int e = u * kFmThreads + tid;
                 ok[u] = e < n_list && l_key[e] < P.dims;
                 if (ok[u]) {
                     const uint32_t j = l_key[e];
+                    if (vec) {
+                        const float4 a4 = *reinterpret_cast<const float4 *>(P.vrec + (size_t)j * P.vw + f0);
+                        vv[u][0] = a4.x; vv[u][1] = a4.y; vv[u][2] = a4.z; vv[u][3] = a4.w;
+                        if (P.adagrad) {
+                            const float4 b4 = *reinterpret_cast<const float4 *>(P.vrec + (size_t)j * P.vw + k + f0);
+                            va[u][0] = b4.x; va[u][1] = b4.y; va[u][2] = b4.z; va[u][3] = b4.w;
+                        } else { va[u][0] = va[u][1] = va[u][2] = va[u][3] = 0.0f; }
+                    } else {
 #pragma unroll
-                    for (int v = 0; v < kFmNV; v++)
-                        if (f0 + v < k) {
-                            vv[u][v] = P.vrec[(size_t)j * P.vw + f0 + v];
-                            va[u][v] = P.adagrad ? P.vrec[(size_t)j * P.vw + k + f0 + v] : 0.0f;
-                        }
+                        for (int v = 0; v < kFmNV; v++)
+                            if (f0 + v < k) {
+                                vv[u][v] = P.vrec[(size_t)j * P.vw + f0 + v];
+                                va[u][v] = P.adagrad ? P.vrec[(size_t)j * P.vw + k + f0 + v] : 0.0f;
+                            }
+                    }
                 }
             }
 #pragma unroll
@@ -529,9 +545,19 @@ __global__ void __launch_bounds__(kFmThreads) fm_update_kernel(FmUpdParams P)
                         if (f0 + v < k) {
                             const double G = l_gs[v * kFmChunk + e] - (double)vv[u][v] * a2;
                             fm_step(P, fm_grad(P, G, cn), P.lambda_v, vv[u][v], va[u][v]);
-                            P.vrec[(size_t)j * P.vw + f0 + v] = vv[u][v];
-                            if (P.adagrad) P.vrec[(size_t)j * P.vw + k + f0 + v] = va[u][v];
                         }
+                    if (vec) {
+                        *reinterpret_cast<float4 *>(P.vrec + (size_t)j * P.vw + f0) = make_float4(vv[u][0], vv[u][1], vv[u][2], vv[u][3]);
+                        if (P.adagrad)
+                            *reinterpret_cast<float4 *>(P.vrec + (size_t)j * P.vw + k + f0) = make_float4(va[u][0], va[u][1], va[u][2], va[u][3]);
+                    } else {
+#pragma unroll
+                        for (int v = 0; v < kFmNV; v++)
+                            if (f0 + v < k) {
+                                P.vrec[(size_t)j * P.vw + f0 + v] = vv[u][v];
+                                if (P.adagrad) P.vrec[(size_t)j * P.vw + k + f0 + v] = va[u][v];
+                            }
+                    }
                 }
         }
     }
