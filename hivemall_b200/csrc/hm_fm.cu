@@ -89,23 +89,28 @@ struct FmFwdParams {
     uint32_t *bad;
 };
 
-template <int NF>
+// LPR = lanes per row: 32 (a warp per row, NF factors per lane) or 16 (k <= 16: two rows per warp,
+// so that no lane idles).
+template <int NF, int LPR>
 __global__ void __launch_bounds__(256) fm_forward_kernel(FmFwdParams P)
 {
+    constexpr int RPW = 32 / LPR;                 // rows per warp
     const int lane = threadIdx.x & 31;
+    const int sub = lane & (LPR - 1), half = lane / LPR;
     const int k = P.k;
     const float w0 = P.w0rec[0];
-    for (int r = blockIdx.x * 8 + (threadIdx.x >> 5); r < P.n_rows; r += gridDim.x * 8) {
-        const int64_t row = P.row0 + r;
-        const int64_t p0 = P.rowptr[row], p1 = P.rowptr[row + 1];
-        // linear term: lanes over elements, fp64 tree
+    for (int rb = (blockIdx.x * 8 + (threadIdx.x >> 5)) * RPW; rb < P.n_rows; rb += gridDim.x * 8 * RPW) {
+        const int r = rb + half;
+        const bool live = r < P.n_rows;
+        const int64_t row = P.row0 + (live ? r : rb);
+        const int64_t p0 = live ? P.rowptr[row] : 0, p1 = live ? P.rowptr[row + 1] : 0;
+        // linear term: lanes of the row over its elements, fp64 tree
         double lin = 0.0;
-        for (int64_t p = p0 + lane; p < p1; p += 32) {
+        for (int64_t p = p0 + sub; p < p1; p += LPR) {
             const uint32_t f = P.feature[p];
             if (f < P.dims) lin += (double)__fmul_rn(__ldg(P.wrec + (size_t)f * P.ww), P.value[p]);
             else atomicOr(P.bad, 1u);
         }
-        lin = warp_sum(lin);
         // factor sums: lanes over f, elements in row order (4 factor-row loads in flight)
         double S[NF], Q[NF];
 #pragma unroll
@@ -120,7 +125,7 @@ __global__ void __launch_bounds__(256) fm_forward_kernel(FmFwdParams P)
                 const bool in = ok && f < P.dims;
 #pragma unroll
                 for (int q = 0; q < NF; q++) {
-                    const int fi = lane + 32 * q;
+                    const int fi = sub + LPR * q;
                     v[u][q] = (in && fi < k) ? __ldg(P.vrec + (size_t)f * P.vw + fi) : 0.0f;
                 }
             }
@@ -138,16 +143,21 @@ __global__ void __launch_bounds__(256) fm_forward_kernel(FmFwdParams P)
         double inter = 0.0;
 #pragma unroll
         for (int q = 0; q < NF; q++) {
-            const int fi = lane + 32 * q;
+            const int fi = sub + LPR * q;
             const float s32 = (float)S[q];
-            if (fi < k) {
+            if (live && fi < k) {
                 inter += (double)__fmul_rn(s32, s32) - Q[q];
                 if (P.train) P.stab[(size_t)r * k + fi] = s32;
             }
         }
-        inter = warp_sum(inter);
+        // sums over the lanes of the row (the warp has reconverged here)
+#pragma unroll
+        for (int o = LPR / 2; o > 0; o >>= 1) {
+            lin += __shfl_xor_sync(0xffffffffu, lin, o);
+            inter += __shfl_xor_sync(0xffffffffu, inter, o);
+        }
         const float yhat = (float)((double)w0 + lin + 0.5 * inter);
-        if (lane == 0) {
+        if (live && sub == 0) {
             P.margin[row - P.block_row0] = yhat;
             if (P.train) {
                 const float lab = P.label[row];
@@ -686,8 +696,9 @@ hm_status launch_fm_forward(Launcher &L, const FmArgs &a, const int64_t *d_rowpt
     // algorithmic bytes: feature+value, w and the k factors per element; S table row + scalars per row
     const double bytes = (12.0 + 4.0 * a.k) * (double)nnz_hint + (20.0 + 4.0 * a.k) * (double)n_rows;
     const int id = train ? K_FM_FORWARD : K_PREDICT;
-    if (a.k <= 32) HM_LAUNCH(L, id, bytes, (fm_forward_kernel<1><<<grid, 256, 0, L.stream>>>(P)));
-    else HM_LAUNCH(L, id, bytes, (fm_forward_kernel<2><<<grid, 256, 0, L.stream>>>(P)));
+    if (a.k <= 16) HM_LAUNCH(L, id, bytes, (fm_forward_kernel<1, 16><<<fm_grid(((int64_t)n_rows + 15) / 16, 8), 256, 0, L.stream>>>(P)));
+    else if (a.k <= 32) HM_LAUNCH(L, id, bytes, (fm_forward_kernel<1, 32><<<grid, 256, 0, L.stream>>>(P)));
+    else HM_LAUNCH(L, id, bytes, (fm_forward_kernel<2, 32><<<grid, 256, 0, L.stream>>>(P)));
     HM_CUDA(cudaGetLastError());
     return HM_OK;
 }
