@@ -47,7 +47,7 @@ class HmConfig(C.Structure):
 class HmStats(C.Structure):
     _fields_ = [("rows", C.c_int64), ("nnz", C.c_int64), ("mini_batches", C.c_int64),
                 ("kernel_launches", C.c_int64), ("h2d_bytes", C.c_int64), ("d2h_bytes", C.c_int64),
-                ("loss_sum_last_epoch", C.c_double)]
+                ("reserved0", C.c_double)]
 
 
 # name -> (restype, argtypes).  tests/test_abi.py checks this table against the header.

@@ -67,7 +67,8 @@ typedef struct hm_config {
     float   sigma;
     float   lambda_w0, lambda_w, lambda_v;
     uint32_t seed;
-    int32_t mix_interval;    /* mini-batches between model averaging; 0 = end of epoch */
+    int32_t mix_interval;    /* mini-batches between model averagings, for the CALLER's MIX loop (0 = its choice):
+                              * the library itself never communicates, see hm_udtf_array / hm_udtf_scale_replica */
     uint32_t hash_seed;      /* MurmurHash3 seed used by feature hashing */
     int32_t reserved[8];
 } hm_config;
@@ -78,7 +79,7 @@ typedef struct hm_udtf hm_udtf; /* opaque learner = one UDTF instance on one GPU
 typedef struct hm_stats {
     int64_t rows, nnz, mini_batches, kernel_launches;
     int64_t h2d_bytes, d2h_bytes;
-    double  loss_sum_last_epoch;  /* filled by hm_udtf_close when -track_loss is set */
+    double  reserved0;            /* always 0 in this version */
 } hm_stats;
 
 /* ---- library ------------------------------------------------------------- */
