@@ -1,0 +1,119 @@
+"""Entry points around the training loop: warm start, replica scaling (the 1/P step of MIX),
+device-side prediction and hashing, last-mini-batch margins, counters."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+import hivemall_b200 as hm
+from hivemall_b200 import _lib, synth
+
+import _oracle
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("opt", ["adagrad", "adam", "ftrl"])
+def test_warm_start_round_trip(opt):
+    """Save (arrays, step) after half of the rows, load them into a fresh learner, continue:
+    bit-identical to the uninterrupted run."""
+    data = synth.criteo_like(8192, dims=1 << 16, seed=21)
+    rp, f, v, y = data.numpy()
+    opts = f"-opt {opt} -mini_batch 1024 -dims {1 << 16} -eta inverse"
+    full = hm.train_classifier(opts)
+    full.process_batch(rp, f, v, y)
+    full.close()
+    a = hm.train_classifier(opts)
+    a.process_batch(rp[:4097], f, v, y[:4096])
+    a.sync()
+    saved = {"state": a.array_to_host("state"), "step": a.step}
+    if opt != "ftrl":
+        saved["w"] = a.array_to_host("w")
+    b = hm.train_classifier(opts)
+    if opt != "ftrl":
+        b.array_from_host("w", saved["w"])
+    else:
+        with pytest.raises(hm.HivemallError):        # FTRL weights are derived: only the state can be written
+            b.array_from_host("w", np.zeros(1 << 16, np.float32))
+    b.array_from_host("state", saved["state"])
+    b.step = saved["step"]
+    b.process_batch(rp[4096:], f, v, y[4096:])
+    b.close()
+    assert b.step == full.step == 8
+    assert np.array_equal(b.array_to_host("w"), full.array_to_host("w"))
+    assert np.array_equal(b.array_to_host("state"), full.array_to_host("state"))
+    for u in (full, a, b):
+        u.destroy()
+
+
+def test_scale_replica_and_device_arrays():
+    import torch
+    data = synth.criteo_like(4096, dims=1 << 14, seed=22)
+    u = hm.train_classifier(f"-opt adagrad -mini_batch 512 -dims {1 << 14}")
+    u.process_batch(*data.numpy())
+    u.sync()
+    w0, s0 = u.array_to_host("w"), u.array_to_host("state")
+    arrays = u.arrays()
+    assert list(arrays) == ["replica"] and arrays["replica"][1:] == ((1 << 14) * 2, 2)
+    t = torch.as_tensor(u.array_view("replica"), device="cuda")          # zero-copy view of the library's memory
+    assert np.array_equal(t.cpu().numpy().reshape(-1, 2)[:, 0], w0)
+    u.scale_replica(0.5)
+    u.sync()
+    assert np.array_equal(u.array_to_host("w"), w0 * np.float32(0.5))
+    assert np.array_equal(u.array_to_host("state"), s0 * np.float32(0.5))
+    u.destroy()
+
+
+def test_predict_device_and_last_margins():
+    import torch
+    data = synth.criteo_like(3000, dims=1 << 14, seed=23, device="cuda")
+    u = hm.train_classifier(f"-opt sgd -mini_batch 1000 -dims {1 << 14} -eta0 0.05")
+    u.process_device(data.rows, data.nnz, data.rowptr, data.feature, data.value, data.label)
+    u.sync()
+    # margins of the LAST mini-batch as they were when it was scored = prediction with the model
+    # of two mini-batches, which the oracle can reproduce
+    host = synth.Csr(data.rowptr.cpu(), data.feature.cpu(), data.value.cpu(), data.label.cpu())
+    rp, f, v, y = host.numpy()
+    cfg = _oracle.config_from(hm.parse_options("train_classifier", f"-opt sgd -mini_batch 1000 -dims {1 << 14} -eta0 0.05"))
+    two = _oracle.train_linear(cfg, rp[:2001], f, v, y[:2000])
+    want = _oracle.predict_linear(rp[2000:] - rp[2000], f[rp[2000]:], v[rp[2000]:], two.w)
+    got = u.last_margins()
+    assert len(got) == 1000
+    np.testing.assert_allclose(got, want, rtol=1e-5, atol=1e-6)
+    # device-side prediction equals host-side prediction
+    out = torch.empty(data.rows, dtype=torch.float32, device="cuda")
+    u.predict_device(data.rows, data.rowptr, data.feature, data.value, out)
+    u.sync()
+    assert np.array_equal(out.cpu().numpy(), u.predict(rp, f, v))
+    st = u.stats()
+    assert (st.rows, st.nnz, st.mini_batches) == (3000, 3000 * 39, 3) and st.kernel_launches > 0
+    u.destroy()
+
+
+def test_mhash_device_matches_host_entry_point():
+    import torch
+    names = [f"field{i % 37}=v{i * 7919 % 100003}" for i in range(5000)]
+    data, off = hm.udtf._pack_strings(names)
+    d_data, d_off = torch.from_numpy(data).cuda(), torch.from_numpy(off).cuda()
+    d_out = torch.empty(len(names), dtype=torch.int32, device="cuda")
+    torch.cuda.synchronize()
+    _lib.check(_lib.load().hm_mhash_device(C.c_void_p(d_data.data_ptr()), C.c_void_p(d_off.data_ptr()), len(names),
+                                           hm.DEFAULT_HASH_SEED, 1 << 24, C.c_void_p(d_out.data_ptr()), C.c_void_p(0)))
+    torch.cuda.synchronize()
+    assert np.array_equal(d_out.cpu().numpy(), hm.mhash(names))
+    assert np.array_equal(d_out.cpu().numpy(), _oracle.mhash(names, 1 << 24, hm.DEFAULT_HASH_SEED))
+
+
+def test_profiling_counters_cover_every_launch():
+    data = synth.criteo_like(4096, dims=1 << 14, seed=24)
+    u = hm.train_classifier(f"-opt adagrad -mini_batch 2048 -dims {1 << 14}")
+    u.set_profiling(True)
+    u.process_batch(*data.numpy())
+    u.sync()
+    u.set_profiling(False)
+    kt = {k: v for k, v in u.kernel_times().items() if v["launches"]}
+    assert kt["linear_forward"]["launches"] == 2 and kt["linear_update"]["launches"] == 2
+    assert kt["sort_scatter"]["launches"] == 2           # 14-bit keys: two digit passes, one block
+    assert all(v["ms"] > 0 for v in kt.values())
+    assert sum(v["launches"] for v in kt.values()) == u.stats().kernel_launches
+    u.destroy()
