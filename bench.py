@@ -35,22 +35,51 @@ import time
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-DIMS = 1 << 24
 MINI_BATCH = 65536
 ROWS_PER_STEP = 1 << 22
 TOTAL_ROWS = 24 * ROWS_PER_STEP          # 100,663,296 rows >= the 100M of configs[1]
-OPTIONS = f"-loss logloss -opt ftrl -mini_batch {MINI_BATCH} -dims {DIMS} -alpha 0.05 -lambda1 0.0001"
-NNZ_PER_ROW = 39
 SEED = 1
-# name -> (UDTF, options, label).  The default is BASELINE.json configs[1]; "fm16" is configs[2]
-# (a secondary measurement: `python bench.py --workload fm16`).
+
+
+def _wl(fn, options, label, metric, dims=1 << 24, gen="criteo", nnz=39, regression=False, mix_every=1, total_rows=TOTAL_ROWS):
+    return {"fn": fn, "options": options, "label": label, "metric": metric, "dims": dims, "gen": gen, "nnz": nnz,
+            "regression": regression, "mix_every": mix_every, "total_rows": total_rows}
+
+
+# The default is BASELINE.json configs[1]; the others are secondary measurements
+# (`python bench.py --workload NAME`): "adagrad" is the optimizer north_star's target sentence names,
+# "fm16" configs[2], "adam26" configs[3] and "fm64" configs[4] (both meant for --gpus 2/4/8).
 WORKLOADS = {
-    "ftrl": ("train_classifier", OPTIONS,
-             "configs[1]: train_classifier logistic+FTRL, 2^24 hashed dims, Criteo-shaped synthetic (39 feats/row), "
-             "100M rows per GPU"),
-    "fm16": ("train_fm", f"-factors 16 -classification -opt adagrad -mini_batch {MINI_BATCH} -dims {DIMS} -eta0 0.05",
-             "configs[2]: train_fm k=16 AdaGrad, 2^24 hashed dims, Criteo-shaped synthetic (39 feats/row)"),
+    "ftrl": _wl("train_classifier", f"-loss logloss -opt ftrl -mini_batch {MINI_BATCH} -dims {1 << 24} -alpha 0.05 -lambda1 0.0001",
+                "configs[1]: train_classifier logistic+FTRL, 2^24 hashed dims, Criteo-shaped synthetic (39 feats/row), "
+                "100M rows per GPU",
+                "examples/sec (train_classifier logloss+FTRL, 2^24 hashed dims, Criteo-shaped)"),
+    "adagrad": _wl("train_classifier", f"-loss logloss -opt adagrad -mini_batch {MINI_BATCH} -dims {1 << 24} -eta0 0.05",
+                   "north_star target: train_classifier logistic+AdaGrad, 2^24 hashed dims, Criteo-shaped synthetic "
+                   "(39 feats/row), 100M rows per GPU",
+                   "examples/sec (train_classifier logloss+AdaGrad, 2^24 hashed dims, Criteo-shaped)"),
+    "fm16": _wl("train_fm", f"-factors 16 -classification -opt adagrad -mini_batch {MINI_BATCH} -dims {1 << 24} -eta0 0.05",
+                "configs[2]: train_fm k=16 AdaGrad, 2^24 hashed dims, Criteo-shaped synthetic (39 feats/row)",
+                "examples/sec (train_fm k=16 AdaGrad, 2^24 hashed dims, Criteo-shaped)"),
+    "adam26": _wl("train_regressor", f"-loss squared -opt adam -mini_batch {MINI_BATCH} -dims {1 << 26} -eta0 0.001",
+                  "configs[3]: train_regressor squared loss + Adam, 2^26 hashed dims, Criteo-shaped synthetic "
+                  "(39 feats/row; nnz/row is not fixed by BASELINE.json), 100M rows per GPU (1B rows = 10 GPUs' worth)",
+                  "examples/sec (train_regressor squared+Adam, 2^26 hashed dims, Criteo-shaped)",
+                  dims=1 << 26, regression=True),
+    "fm64": _wl("train_fm", f"-factors 64 -classification -opt adagrad -mini_batch {MINI_BATCH} -dims {1 << 24} -eta0 0.05",
+                "configs[4]: train_fm k=64 AdaGrad, 2^24 hashed dims, KDD12-shaped synthetic (11 feats/row), "
+                "16.8M rows per GPU (134M rows over 8 GPUs), replicas averaged once per pass over them",
+                "examples/sec (train_fm k=64 AdaGrad, 2^24 hashed dims, KDD12-shaped)",
+                gen="kdd12", nnz=11, mix_every=4, total_rows=4 * ROWS_PER_STEP),
 }
+
+
+def make_rows(wl: dict, n_rows: int, row0: int, device="cpu"):
+    """Rows [row0, row0 + n_rows) of the workload's synthetic stream."""
+    from hivemall_b200 import synth
+    if wl["gen"] == "kdd12":
+        return synth.kdd12_like(n_rows, dims=wl["dims"], seed=SEED, device=device, row0=row0)
+    return synth.criteo_like(n_rows, dims=wl["dims"], seed=SEED, device=device, row0=row0, regression=wl["regression"])
 
 
 def parse_args():
@@ -60,7 +89,7 @@ def parse_args():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--rows-per-step", type=int, default=ROWS_PER_STEP)
-    ap.add_argument("--total-rows", type=int, default=TOTAL_ROWS)
+    ap.add_argument("--total-rows", type=int, default=0, help="0 = the workload's own")
     ap.add_argument("--cpu-sample-rows", type=int, default=0, help="0 = sized for ~15 s")
     ap.add_argument("--workload", default="ftrl", choices=sorted(WORKLOADS))
     ap.add_argument("--no-e2e", action="store_true")
@@ -152,20 +181,19 @@ def measured_peaks() -> tuple[float, str]:
 _CPU_DATA = {}
 
 
-def _cpu_rows(rows: int):
+def _cpu_rows(rows: int, workload: str):
     """First `rows` rows of the synthetic stream as host arrays (generated once per process)."""
-    from hivemall_b200 import synth
     import numpy as np
-    have = _CPU_DATA.get("rows", 0)
-    if have < rows:
-        pieces = [synth.criteo_like(min(1 << 20, rows - r0), dims=DIMS, seed=SEED, row0=r0) for r0 in range(0, rows, 1 << 20)]
-        _CPU_DATA.update(rows=rows,
-                         feature=np.concatenate([p.feature.numpy() for p in pieces]),
-                         value=np.concatenate([p.value.numpy() for p in pieces]),
-                         label=np.concatenate([p.label.numpy() for p in pieces]))
-    d = _CPU_DATA
-    return (np.arange(rows + 1, dtype=np.int64) * NNZ_PER_ROW, d["feature"][: rows * NNZ_PER_ROW],
-            d["value"][: rows * NNZ_PER_ROW], d["label"][:rows])
+    wl = WORKLOADS[workload]
+    d = _CPU_DATA.setdefault(workload, {"rows": 0})
+    if d["rows"] < rows:
+        pieces = [make_rows(wl, min(1 << 20, rows - r0), r0) for r0 in range(0, rows, 1 << 20)]
+        d.update(rows=rows,
+                 feature=np.concatenate([p.feature.numpy() for p in pieces]),
+                 value=np.concatenate([p.value.numpy() for p in pieces]),
+                 label=np.concatenate([p.label.numpy() for p in pieces]))
+    n = wl["nnz"]
+    return (np.arange(rows + 1, dtype=np.int64) * n, d["feature"][: rows * n], d["value"][: rows * n], d["label"][:rows])
 
 
 def cpu_baseline(rows: int, threads: int, workload: str = "ftrl") -> dict:
@@ -174,9 +202,9 @@ def cpu_baseline(rows: int, threads: int, workload: str = "ftrl") -> dict:
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     import hivemall_b200 as hm
     import _oracle
-    fn, options, _ = WORKLOADS[workload]
+    fn, options = WORKLOADS[workload]["fn"], WORKLOADS[workload]["options"]
     cfg = _oracle.config_from(hm.parse_options(fn, options))
-    rowptr, feature, value, label = _cpu_rows(rows)
+    rowptr, feature, value, label = _cpu_rows(rows, workload)
     if fn == "train_fm":
         threads = 1
         t0 = time.perf_counter()
@@ -213,12 +241,12 @@ def run_reference_arm(args) -> None:
     dt = sum(times) / len(times)
     value = rows / dt
     out = {
-        "impl": "reference", "metric": METRIC[args.workload],
+        "impl": "reference", "metric": WORKLOADS[args.workload]["metric"],
         "value": value, "unit": "examples/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32 (fp64 sums)", "data": "synthetic",
-        "config": {"workload": WORKLOADS[args.workload][2],
-                   "options": WORKLOADS[args.workload][1], "mini_batch": MINI_BATCH, "rows_per_step": rows,
+        "config": {"workload": WORKLOADS[args.workload]["label"],
+                   "options": WORKLOADS[args.workload]["options"], "mini_batch": MINI_BATCH, "rows_per_step": rows,
                    "note": "CPU arm; each step is a bounded sample of the stream"},
         "cpu_baseline": {"value": value, "unit": "examples/s", "cores": r["cores"], "kind": "port",
                          "sample": f"{rows} rows per step, {r['sample']}"},
@@ -227,9 +255,6 @@ def run_reference_arm(args) -> None:
     }
     print(json.dumps(out))
 
-
-METRIC = {"ftrl": "examples/sec (train_classifier logloss+FTRL, 2^24 hashed dims, Criteo-shaped)",
-          "fm16": "examples/sec (train_fm k=16 AdaGrad, 2^24 hashed dims, Criteo-shaped)"}
 
 # ------------------------------------------------------------------------- GPU arm
 
@@ -255,22 +280,24 @@ def main():
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
 
+    wl = WORKLOADS[args.workload]
+    nnz_per_row = wl["nnz"]
+    total_rows = args.total_rows or wl["total_rows"]
     K, W = args.steps, args.warmup
     rps = args.rows_per_step // MINI_BATCH * MINI_BATCH
-    n_blocks = max(1, min(args.total_rows // rps, K + W))
+    n_blocks = max(1, min(total_rows // rps, K + W))
     # ---- synthetic rows of this rank's shard, resident in HBM
-    row_base = rank * args.total_rows
+    row_base = rank * total_rows
     blocks = []
     for b in range(n_blocks):
-        parts = [synth.criteo_like(min(1 << 20, rps - r), dims=DIMS, seed=SEED, device=dev, row0=row_base + b * rps + r)
-                 for r in range(0, rps, 1 << 20)]
+        parts = [make_rows(wl, min(1 << 20, rps - r), row_base + b * rps + r, device=dev) for r in range(0, rps, 1 << 20)]
         feature = torch.cat([p.feature for p in parts])
         value = torch.cat([p.value for p in parts])
         label = torch.cat([p.label for p in parts])
-        rowptr = torch.arange(rps + 1, device=dev, dtype=torch.int64) * NNZ_PER_ROW
+        rowptr = torch.arange(rps + 1, device=dev, dtype=torch.int64) * nnz_per_row
         blocks.append((rowptr, feature, value, label))
         del parts
-    nnz_step = rps * NNZ_PER_ROW
+    nnz_step = rps * nnz_per_row
     torch.cuda.synchronize()
 
     def barrier():
@@ -279,7 +306,8 @@ def main():
         torch.cuda.synchronize()
 
     # ---- device-resident arm ------------------------------------------------------
-    fn, options, wl_label = WORKLOADS[args.workload]
+    fn, options, wl_label = wl["fn"], wl["options"], wl["label"]
+    mix_every = wl["mix_every"]
     u = hm.UDTF(options, local_rank, function_name=fn)
     mixer = mix.ReplicaMixer(u, world) if world > 1 else None
     stream = torch.cuda.ExternalStream(u.stream, device=dev)
@@ -287,8 +315,8 @@ def main():
     def step_device(i):
         rowptr, feature, value, label = blocks[i % n_blocks]
         u.process_device(rps, nnz_step, rowptr, feature, value, label)
-        if mixer:
-            mixer.mix()     # MIX averaging at the step boundary (every 64 mini-batches)
+        if mixer and (i + 1) % mix_every == 0:
+            mixer.mix()     # MIX averaging at a step boundary (a step = 64 mini-batches)
 
     for i in range(W):
         step_device(i)
@@ -378,11 +406,14 @@ def main():
         def step_host(i):
             (rp, _), (ft, _), (vl, _), (lb, lbt) = host[i % n_host]
             v.process_pointers(rps, rp, ft, vl, lb)
-            if mixer2:
+            if mixer2 and (i + 1) % mix_every == 0:
                 mixer2.mix()
             m = v.last_margins(margins)                      # D2H read of the step's result, waits
-            y = lbt[rps - len(m):].numpy() * 2 - 1
-            losses.append(float(np.mean(np.logaddexp(0.0, -y * m))))
+            t = lbt[rps - len(m):].numpy()
+            if wl["regression"]:
+                losses.append(float(np.mean(0.5 * (m - t) ** 2)))
+            else:
+                losses.append(float(np.mean(np.logaddexp(0.0, -(t * 2 - 1) * m))))
 
         for i in range(W):
             step_host(i)
@@ -400,7 +431,7 @@ def main():
         h2d = (rps + 1) * 8 + nnz_step * 8 + rps * 4
         e2e = {"value": world * rps * K / dt, "unit": "examples/s", "h2d_bytes_per_step": h2d,
                "d2h_bytes_per_step": MINI_BATCH * 4, "ms_per_step": dt / K * 1e3,
-               "last_minibatch_logloss": losses[-1], "pcie_GBps": h2d * K / dt / 1e9,
+               "last_minibatch_loss": losses[-1], "loss": "squared/2" if wl["regression"] else "logloss", "pcie_GBps": h2d * K / dt / 1e9,
                "timing": "host wall clock around K calls, each ending in a blocking D2H read"}
         v.destroy()
         for arrs in host:
@@ -421,17 +452,18 @@ def main():
 
     if rank == 0:
         out = {
-            "metric": METRIC[args.workload],
+            "metric": wl["metric"],
             "value": rows_per_s, "unit": "examples/s", "n_gpus": world, "steps": K, "warmup": W,
             "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32 (fp64 sums)", "data": "synthetic",
-            "nnz_per_sec": rows_per_s * NNZ_PER_ROW,
+            "nnz_per_sec": rows_per_s * nnz_per_row,
             "config": {
                 "workload": wl_label,
                 "options": options, "mini_batch": MINI_BATCH, "rows_per_step": rps,
                 "mini_batches_per_step": rps // MINI_BATCH, "rows_resident_per_gpu": n_blocks * rps,
-                "l2": "inputs larger than L2 (1.3 GB streamed per step)",
-                "mix": "all-reduce of every replica array every step (64 mini-batches)" if world > 1 else "none (1 GPU)",
+                "l2": f"inputs larger than L2 ({(nnz_step * 8 + rps * 12) / 1e9:.2f} GB streamed per step)",
+                "mix": (f"all-reduce of every replica array every {mix_every} step(s) of 64 mini-batches"
+                        if world > 1 else "none (1 GPU)"),
                 "parallelism": f"dp{world}: row shards, full replica per GPU",
             },
             "roofline": roofline,
