@@ -81,6 +81,16 @@ __device__ __forceinline__ double warp_sum(double v)
     return v;
 }
 
+// ---- per-CTA timeline stamps: compiled in with -DHM_STAMP only (scripts/upd_timeline.py, scripts/build_variant.sh) ---------
+#ifdef HM_STAMP
+__device__ unsigned long long hm_dbg_stamps[4096 * 8];
+__device__ __forceinline__ unsigned long long gtime() { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
+#define STAMP(i) do { if (threadIdx.x == 0 && blockIdx.x < 4096) hm_dbg_stamps[blockIdx.x * 8 + (i)] = gtime(); } while (0)
+#else
+#define STAMP(i) do { } while (0)
+#endif
+#define USTAMP(i) STAMP(i)
+
 // ---- forward ---------------------------------------------------------------------
 
 struct FwdParams {
@@ -404,6 +414,7 @@ __device__ __forceinline__ void reduce_tile(const UpdParams &P, const UpdShared 
         }
     }
     __syncthreads();
+    USTAMP(1);
     const bool left_closed = S.s_edge[0] != 0, right_closed = S.s_edge[1] != 0;
     const SegRec carry = *S.s_carry;
     const uint32_t carry_open = *S.s_carry_open;
@@ -424,20 +435,21 @@ __device__ __forceinline__ void reduce_tile(const UpdParams &P, const UpdShared 
     const int q0 = tid * kUpdItems;
     Scan mine; mine.v = 0.0; mine.c = 0; mine.f = 0; mine.k = (tid == 0 && retire_carry) ? 1u : 0u;
     if (tid == 0 && edge_continues) { mine.v = carry.sum; mine.c = carry.cnt; }
-    uint32_t kk[kUpdItems + 1]; float vv[kUpdItems];
-    const uint32_t prev_key = (q0 > 0 && q0 < n_tile) ? S.s_key[pad_idx(q0 - 1)] : 0u;
+    {
+        uint32_t kk[kUpdItems + 1];
+        const uint32_t prev_key = (q0 > 0 && q0 < n_tile) ? S.s_key[pad_idx(q0 - 1)] : 0u;
 #pragma unroll
-    for (int i = 0; i <= kUpdItems; i++) kk[i] = q0 + i < n_tile ? S.s_key[pad_idx(q0 + i)] : 0u;
+        for (int i = 0; i <= kUpdItems; i++) kk[i] = q0 + i < n_tile ? S.s_key[pad_idx(q0 + i)] : 0u;
 #pragma unroll
-    for (int i = 0; i < kUpdItems; i++) {
-        const int q = q0 + i;
-        if (q < n_tile) {
-            vv[i] = S.s_val[pad_idx(q)];
-            const bool head = q > 0 && kk[i] != (i == 0 ? prev_key : kk[i - 1]);
-            if (head) { mine.v = 0.0; mine.c = 0; mine.f = 1; }
-            mine.v += (double)vv[i]; mine.c += 1;
-            const bool closes = q < n_tile - 1 ? kk[i + 1] != kk[i] : close_tail;
-            if (closes) mine.k += 1;
+        for (int i = 0; i < kUpdItems; i++) {
+            const int q = q0 + i;
+            if (q < n_tile) {
+                const bool head = q > 0 && kk[i] != (i == 0 ? prev_key : kk[i - 1]);
+                if (head) { mine.v = 0.0; mine.c = 0; mine.f = 1; }
+                mine.v += (double)S.s_val[pad_idx(q)]; mine.c += 1;
+                const bool closes = q < n_tile - 1 ? kk[i + 1] != kk[i] : close_tail;
+                if (closes) mine.k += 1;
+            }
         }
     }
     // ---- exclusive segmented scan of the summaries over the CTA
@@ -459,6 +471,7 @@ __device__ __forceinline__ void reduce_tile(const UpdParams &P, const UpdShared 
     ex.k = __shfl_up_sync(0xffffffffu, inc.k, 1);
     if (lane == 0) { ex.v = 0.0; ex.c = 0; ex.f = 0; ex.k = 0; }
     __syncthreads();
+    USTAMP(2);
     Scan wp; wp.v = 0.0; wp.c = 0; wp.f = 0; wp.k = 0;
     for (int w2 = 0; w2 < warp; w2++) wp = combine(wp, S.s_warp[w2]);
     const Scan cin = combine(wp, ex);
@@ -472,35 +485,41 @@ __device__ __forceinline__ void reduce_tile(const UpdParams &P, const UpdShared 
         if (carry_open) *S.s_first = carry;
         else { S.l_key[slot] = carry.key; S.l_g[slot] = grad_of(P, carry.sum, carry.cnt); slot++; }
     }
+    // (the tile is read again from shared memory: keeping sixteen values in registers across the
+    // scan costs a fourth resident CTA per SM)
+    uint32_t kprev = (q0 > 0 && q0 < n_tile) ? S.s_key[pad_idx(q0 - 1)] : 0u;
+    uint32_t kcur = q0 < n_tile ? S.s_key[pad_idx(q0)] : 0u;
 #pragma unroll
     for (int i = 0; i < kUpdItems; i++) {
         const int q = q0 + i;
         if (q < n_tile) {
-            const bool head = q > 0 && kk[i] != (i == 0 ? prev_key : kk[i - 1]);
+            const uint32_t knext = q + 1 < n_tile ? S.s_key[pad_idx(q + 1)] : 0u;
+            const bool head = q > 0 && kcur != kprev;
             if (head) { run = 0.0; cnt = 0; seen_head = true; }
-            run += (double)vv[i]; cnt += 1;
+            run += (double)S.s_val[pad_idx(q)]; cnt += 1;
             // open: the segment reaches the tile's left edge and, through it, past the CTA's left edge
             const bool open = !seen_head && edge_open;
-            const bool closes = q < n_tile - 1 ? kk[i + 1] != kk[i] : close_tail;
+            const bool closes = q < n_tile - 1 ? knext != kcur : close_tail;
             if (closes) {
                 if (open) {     // at most one such segment per CTA
-                    S.s_first->sum = run; S.s_first->key = kk[i]; S.s_first->cnt = cnt;
+                    S.s_first->sum = run; S.s_first->key = kcur; S.s_first->cnt = cnt;
                     S.l_key[slot] = 0xffffffffu; S.l_g[slot] = 0.f;   // placeholder: skipped by apply_list
                 } else {
-                    S.l_key[slot] = kk[i]; S.l_g[slot] = grad_of(P, run, cnt);
+                    S.l_key[slot] = kcur; S.l_g[slot] = grad_of(P, run, cnt);
                 }
                 slot++;
                 if (q == n_tile - 1) { S.s_carry->cnt = 0; *S.s_carry_open = 0; }
             } else if (q == n_tile - 1) {
-                S.s_carry->sum = run; S.s_carry->key = kk[i]; S.s_carry->cnt = cnt;
+                S.s_carry->sum = run; S.s_carry->key = kcur; S.s_carry->cnt = cnt;
                 *S.s_carry_open = open ? 1u : 0u;
             }
+            kprev = kcur; kcur = knext;
         }
     }
     __syncthreads();
 }
 
-__global__ void __launch_bounds__(kUpdThreads, 3) linear_update_kernel(UpdParams P)
+__global__ void __launch_bounds__(kUpdThreads, 4) linear_update_kernel(UpdParams P)
 {
     __shared__ __align__(16) unsigned char smem_raw[kUpdSmem];
     uint32_t *s_key = reinterpret_cast<uint32_t *>(smem_raw);
@@ -516,6 +535,7 @@ __global__ void __launch_bounds__(kUpdThreads, 3) linear_update_kernel(UpdParams
     __shared__ int s_nlist;
 
     const int tid = threadIdx.x;
+    USTAMP(0);
     const uint32_t s0 = P.seg_off[P.seg], s1 = P.seg_off[P.seg + 1];
     const uint32_t n = s1 - s0;
     // contiguous split of the sorted mini-batch over the grid, in whole tiles
@@ -544,6 +564,7 @@ __global__ void __launch_bounds__(kUpdThreads, 3) linear_update_kernel(UpdParams
         const int n_tile = (int)min((uint32_t)kUpdTile, hi - t0);
         const bool last_tile = t0 + kUpdTile >= hi;
         reduce_tile<true>(P, S, s0 + t0, n_tile, t0 == lo, last_tile);
+        USTAMP(3);
         // ---- after the last tile the CTA's boundary pieces are final: publish them and take the
         // completion ticket now, so that both round trips overlap the optimizer step below
         if (last_tile && tid == 0) {
@@ -555,8 +576,10 @@ __global__ void __launch_bounds__(kUpdThreads, 3) linear_update_kernel(UpdParams
             s_is_last = atomicAdd(P.br.ticket, 1u) == gridDim.x - 1;
         }
         // ---- optimizer step for the listed features, latencies overlapped
+        USTAMP(4);
         apply_list(P, l_key, l_g, s_nlist, tid);
         __syncthreads();
+        USTAMP(5);
     }
     if (lo >= hi) {   // a CTA without elements leaves empty records and still takes its ticket
         if (tid == 0) {
@@ -604,6 +627,7 @@ __global__ void __launch_bounds__(kUpdThreads, 3) linear_update_kernel(UpdParams
     }
     __syncthreads();
     apply_list(P, ml_key, ml_g, s_nlist, tid);
+    USTAMP(6);
     if (tid == 0) *P.br.ticket = 0;   // ready for the next launch on this stream
 }
 
@@ -1069,3 +1093,11 @@ extern "C" hm_status hm_model_table_noalloc(const float *d_w, int64_t dims, int3
     HM_CUDA(cudaGetLastError());
     return HM_OK;
 }
+
+#ifdef HM_STAMP
+extern "C" int hm_debug_read_stamps(unsigned long long *host, size_t n)
+{
+    cudaDeviceSynchronize();
+    return (int)cudaMemcpyFromSymbol(host, hm::hm_dbg_stamps, n * sizeof(unsigned long long));
+}
+#endif
