@@ -247,6 +247,12 @@ sort_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint2 *__restric
         // payloads are requested now and consumed after the ranking
         uint2 pay[kScatItems];
         if (FIRST) {
+            // the values are requested before the row search, so that their latency hides behind it
+#pragma unroll
+            for (int i = 0; i < kScatItems; i++) {
+                const uint32_t e = ew + i * 32;
+                if (e < e1) pay[i].y = __float_as_uint(__ldcs(val_in + e));
+            }
             const int64_t base = rl.rowptr[rl.block_row0];
             const int64_t mb_row0 = rl.block_row0 + (int64_t)seg * rl.mini_batch;
             const int mb_rows = (int)min((int64_t)rl.mini_batch, rl.block_rows - (int64_t)seg * rl.mini_batch);
@@ -299,7 +305,7 @@ sort_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint2 *__restric
                         while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if ((uint32_t)(rp[mid] - base) <= e) lo = mid; else hi = mid; }
                         row = lo;
                     }
-                    pay[i] = make_uint2((uint32_t)row, __float_as_uint(__ldcs(val_in + e)));
+                    pay[i].x = (uint32_t)row;
                 }
             }
         } else {
@@ -318,6 +324,19 @@ sort_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint2 *__restric
             const uint32_t d = (key[i] >> shift) & (kRadix - 1);
             const uint32_t active = __ballot_sync(0xffffffffu, valid);
             uint32_t peers = 0, prev = 0;
+            if (FIRST) {
+                // match.any costs time in proportion to the number of distinct values in the warp.  In the
+                // first pass the elements are still in row order (32 consecutive elements = 32 different
+                // hashed features): eight ballots -- lanes that agree with mine in every bit -- are
+                // cheaper there.  Later passes see long runs of equal digits and keep match.any.
+                peers = active;
+#pragma unroll
+                for (int b = 0; b < 8; b++) {
+                    const uint32_t m = __ballot_sync(0xffffffffu, valid && ((d >> b) & 1u));
+                    peers &= ((d >> b) & 1u) ? m : ~m;
+                }
+                if (valid) prev = wcnt[warp][d];
+            } else
             if (valid) { peers = __match_any_sync(active, d); prev = wcnt[warp][d]; }
             __syncwarp();
             if (valid) {
