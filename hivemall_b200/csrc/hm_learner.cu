@@ -73,10 +73,12 @@ void Launcher::release()
 namespace {
 
 constexpr int64_t kBlockElemCap = (int64_t)1 << 26;   // elements sorted per launch set
-// Host rows copied per H2D slice.  Small enough that the training of the last slice of a call
-// (which cannot overlap a copy) is short, large enough for >= 4 mini-batches per sort block:
-// measured on B200 (bench.py e2e, mini-batch 65536): 2^21 -> 127 M rows/s, 2^20 -> 142, 2^19 -> 151, 2^18 -> 154.
-constexpr int64_t kSliceRows = (int64_t)1 << 19;
+// Host rows copied per H2D slice: the first slices of a call are kSliceRows long, the last ones shrink
+// to kMinSliceRows (see hm_udtf_process).  With one fixed size, measured on B200 (bench.py e2e,
+// mini-batch 65536): 2^21 -> 127 M rows/s, 2^20 -> 142, 2^19 -> 151, 2^18 -> 154; with the descending
+// schedule 159 M for (2^20 | 2^21, 2^16 | 2^17), 157.5 M for (2^20, 2^18), 155.5 M for (2^22, 2^17).
+constexpr int64_t kSliceRows = (int64_t)1 << 20;
+constexpr int64_t kMinSliceRows = (int64_t)1 << 17;
 
 struct DevBuf {
     void *p = nullptr;
@@ -427,6 +429,15 @@ hm_status process_slice(hm_udtf *u, int64_t n, const int64_t *rowptr, const int3
     HM_TRY(c->val.reserve((size_t)std::max<int64_t>(elems, 1) * sizeof(float)));
     HM_TRY(c->label.reserve((size_t)std::max<int64_t>(rows, 1) * sizeof(float)));
 
+    // new rows: host-to-device on the copy stream, queued before the host-side loop below so that the
+    // bus is busy while it runs
+    const int64_t base = rowptr[0];
+    if (nnz) {
+        HM_CUDA(cudaMemcpyAsync(c->feat.as<uint32_t>() + t_nnz, feature + base, (size_t)nnz * 4, cudaMemcpyHostToDevice, u->copy));
+        HM_CUDA(cudaMemcpyAsync(c->val.as<float>() + t_nnz, value + base, (size_t)nnz * 4, cudaMemcpyHostToDevice, u->copy));
+    }
+    HM_CUDA(cudaMemcpyAsync(c->label.as<float>() + t_rows, label, (size_t)n * 4, cudaMemcpyHostToDevice, u->copy));
+
     // rowptr of the new chunk, rebased on the host into pinned staging
     const int turn = u->stage_turn;
     u->stage_turn ^= 1;
@@ -439,7 +450,6 @@ hm_status process_slice(hm_udtf *u, int64_t n, const int64_t *rowptr, const int3
     }
     int64_t *st = u->h_stage[turn];
     for (int64_t i = 0; i < t_rows; i++) st[i] = u->tail_rp[i];
-    const int64_t base = rowptr[0];
     for (int64_t i = 0; i <= n; i++) {
         const int64_t v = rowptr[i] - base;
         if (i > 0 && rowptr[i] < rowptr[i - 1]) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "rowptr decreases at row %lld", (long long)i);
@@ -461,13 +471,8 @@ hm_status process_slice(hm_udtf *u, int64_t n, const int64_t *rowptr, const int3
         HM_TRY(retire_chunk(u, o, u->cfg.iters > 1 && o->rows > 0));
         if (u->cfg.iters > 1 && o->rows == 0) { /* nothing trained from it: already pooled */ }
     }
-    // new rows: host-to-device on the copy stream
+    // the row pointer last: it is the only copy that needs the host loop above
     HM_CUDA(cudaMemcpyAsync(c->rowptr.p, st, (size_t)(rows + 1) * 8, cudaMemcpyHostToDevice, u->copy));
-    if (nnz) {
-        HM_CUDA(cudaMemcpyAsync(c->feat.as<uint32_t>() + t_nnz, feature + base, (size_t)nnz * 4, cudaMemcpyHostToDevice, u->copy));
-        HM_CUDA(cudaMemcpyAsync(c->val.as<float>() + t_nnz, value + base, (size_t)nnz * 4, cudaMemcpyHostToDevice, u->copy));
-    }
-    HM_CUDA(cudaMemcpyAsync(c->label.as<float>() + t_rows, label, (size_t)n * 4, cudaMemcpyHostToDevice, u->copy));
     if (!u->stage_ev[turn]) HM_CUDA(cudaEventCreateWithFlags(&u->stage_ev[turn], cudaEventDisableTiming));
     HM_CUDA(cudaEventRecord(u->stage_ev[turn], u->copy));
     HM_CUDA(cudaStreamWaitEvent(u->compute, u->stage_ev[turn], 0));
@@ -691,12 +696,18 @@ hm_status hm_udtf_process(hm_udtf *u, int64_t n_rows, const int64_t *rowptr, con
     if (n_rows == 0) return HM_OK;
     if (rowptr[n_rows] > rowptr[0] && (!feature || !value)) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "NULL feature/value buffer");
     DeviceGuard g(u->device);
-    // slices sized to whole mini-batches so that copies and training overlap
+    // Slices of whole mini-batches, so that copies and training overlap.  The bus is the bottleneck of
+    // this entry point (the device trains three times faster than PCIe delivers), so the call takes
+    // (bytes / bus speed) + (training of the LAST slice, which no copy overlaps): large slices first,
+    // because copies of >= 160 MB run at the full 55 GB/s, then halving, so that the tail is short.
     const int64_t B = u->cfg.mini_batch;
-    int64_t slice = std::max<int64_t>(kSliceRows / B * B, 4 * B);
-    for (int64_t r = 0; r < n_rows; r += slice) {
+    const int64_t smallest = std::max<int64_t>(kMinSliceRows / B * B, 2 * B);
+    int64_t slice = std::max<int64_t>(kSliceRows / B * B, smallest);
+    for (int64_t r = 0; r < n_rows;) {
+        while (slice > smallest && n_rows - r <= 2 * slice) slice = std::max<int64_t>((slice / 2) / B * B, smallest);
         const int64_t n = std::min(slice, n_rows - r);
         HM_TRY(process_slice(u, n, rowptr + r, feature, value, label + r));
+        r += n;
     }
     return HM_OK;
 }
