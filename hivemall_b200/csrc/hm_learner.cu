@@ -147,7 +147,7 @@ using namespace hm;
 struct hm_udtf {
     hm_config cfg;
     int device = 0;
-    Launcher L, Ls;                  // compute stream / sort stream
+    Launcher L, Ls, Lc;              // compute stream / sort stream / copy stream (fills only)
     cudaStream_t compute = nullptr, copy = nullptr, sorter = nullptr;
     cudaEvent_t sorted_ev[2] = {nullptr, nullptr}, trained_ev[2] = {nullptr, nullptr}, ready_ev = nullptr;
     bool trained_valid[2] = {false, false};
@@ -434,7 +434,8 @@ hm_status process_slice(hm_udtf *u, int64_t n, const int64_t *rowptr, const int3
     const int64_t base = rowptr[0];
     if (nnz) {
         HM_CUDA(cudaMemcpyAsync(c->feat.as<uint32_t>() + t_nnz, feature + base, (size_t)nnz * 4, cudaMemcpyHostToDevice, u->copy));
-        HM_CUDA(cudaMemcpyAsync(c->val.as<float>() + t_nnz, value + base, (size_t)nnz * 4, cudaMemcpyHostToDevice, u->copy));
+        if (value) HM_CUDA(cudaMemcpyAsync(c->val.as<float>() + t_nnz, value + base, (size_t)nnz * 4, cudaMemcpyHostToDevice, u->copy));
+        else HM_TRY(launch_fill_u32(u->Lc, c->val.as<uint32_t>() + t_nnz, nnz, 0x3f800000u));   // index-only features: 1.0f
     }
     HM_CUDA(cudaMemcpyAsync(c->label.as<float>() + t_rows, label, (size_t)n * 4, cudaMemcpyHostToDevice, u->copy));
 
@@ -476,7 +477,7 @@ hm_status process_slice(hm_udtf *u, int64_t n, const int64_t *rowptr, const int3
     if (!u->stage_ev[turn]) HM_CUDA(cudaEventCreateWithFlags(&u->stage_ev[turn], cudaEventDisableTiming));
     HM_CUDA(cudaEventRecord(u->stage_ev[turn], u->copy));
     HM_CUDA(cudaStreamWaitEvent(u->compute, u->stage_ev[turn], 0));
-    u->stats.h2d_bytes += (rows + 1) * 8 + nnz * 8 + n * 4;
+    u->stats.h2d_bytes += (rows + 1) * 8 + nnz * (value ? 8 : 4) + n * 4;
 
     // full mini-batches
     const int64_t n_mb = rows / B;
@@ -532,6 +533,7 @@ hm_status create_impl(const hm_config &cfg, int device, hm_udtf **out)
         HM_CUDA(cudaStreamCreateWithFlags(&u->sorter, cudaStreamNonBlocking));
         u->L.stream = u->compute;
         u->Ls.stream = u->sorter;
+        u->Lc.stream = u->copy;
         for (int i = 0; i < 2; i++) {
             HM_CUDA(cudaEventCreateWithFlags(&u->sorted_ev[i], cudaEventDisableTiming));
             HM_CUDA(cudaEventCreateWithFlags(&u->trained_ev[i], cudaEventDisableTiming));
@@ -694,7 +696,7 @@ hm_status hm_udtf_process(hm_udtf *u, int64_t n_rows, const int64_t *rowptr, con
     if (u->device_rows_short) HM_FAIL(HM_ERR_STATE, "process() after a device call that ended on a short mini-batch");
     if (n_rows < 0 || (n_rows > 0 && (!rowptr || !label))) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "NULL buffer passed to process()");
     if (n_rows == 0) return HM_OK;
-    if (rowptr[n_rows] > rowptr[0] && (!feature || !value)) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "NULL feature/value buffer");
+    if (rowptr[n_rows] > rowptr[0] && !feature) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "NULL feature buffer");
     DeviceGuard g(u->device);
     // Slices of whole mini-batches, so that copies and training overlap.  The bus is the bottleneck of
     // this entry point (the device trains three times faster than PCIe delivers), so the call takes
@@ -869,6 +871,7 @@ hm_status hm_udtf_destroy(hm_udtf *u)
     if (u->sorter) cudaStreamSynchronize(u->sorter);
     u->L.release();
     u->Ls.release();
+    u->Lc.release();
     for (Chunk *c : u->retained) { c->release(); delete c; }
     for (Chunk *c : u->pool) { c->release(); delete c; }
     if (u->tail) { u->tail->release(); delete u->tail; }
@@ -1096,7 +1099,7 @@ hm_status hm_udtf_stats(const hm_udtf *u, hm_stats *out)
 {
     if (!u || !out) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "NULL argument");
     *out = u->stats;
-    out->kernel_launches = u->L.launches + u->Ls.launches;
+    out->kernel_launches = u->L.launches + u->Ls.launches + u->Lc.launches;
     return HM_OK;
 }
 

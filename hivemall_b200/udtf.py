@@ -157,22 +157,23 @@ class UDTF:
 
     def process_batch(self, rowptr, feature, value, label) -> None:
         """process() of many rows at once from host CSR arrays (int64 rowptr, int32
-        feature, float32 value, float32 label).  Asynchronous: keep the arrays alive and
-        unmodified until sync()/close()."""
+        feature, float32 value, float32 label).  `value=None` means every value is 1.0
+        (index-only features).  Asynchronous: keep the arrays alive and unmodified until
+        sync()/close()."""
         rowptr = np.ascontiguousarray(rowptr, dtype=np.int64)
         feature = np.ascontiguousarray(feature, dtype=np.int32)
-        value = np.ascontiguousarray(value, dtype=np.float32)
+        value = None if value is None else np.ascontiguousarray(value, dtype=np.float32)
         label = np.ascontiguousarray(label, dtype=np.float32)
         n = len(rowptr) - 1
         if len(label) != n:
             raise UDFArgumentError(1, f"label has {len(label)} entries for {n} rows")
-        if n and (rowptr[-1] > len(feature) or rowptr[-1] > len(value)):
+        if n and (rowptr[-1] > len(feature) or (value is not None and rowptr[-1] > len(value))):
             raise UDFArgumentError(1, "rowptr points past the end of feature/value")
         self._keep.append((rowptr, feature, value, label))
         check(self._lib.hm_udtf_process(self._h, n, _ptr(rowptr), _ptr(feature), _ptr(value), _ptr(label)))
 
-    def process_pointers(self, n_rows: int, rowptr: int, feature: int, value: int, label: int) -> None:
-        """process() from raw HOST addresses (pinned buffers from host_alloc)."""
+    def process_pointers(self, n_rows: int, rowptr: int, feature: int, value: int | None, label: int) -> None:
+        """process() from raw HOST addresses (pinned buffers from host_alloc); value None/0 = all 1.0."""
         check(self._lib.hm_udtf_process(self._h, n_rows, _ptr(rowptr), _ptr(feature), _ptr(value), _ptr(label)))
 
     def process_device(self, n_rows: int, nnz: int, rowptr, feature, value, label) -> None:

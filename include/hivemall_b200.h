@@ -132,6 +132,8 @@ hm_status hm_udtf_create_from_config(const hm_config *cfg, int device, hm_udtf *
  * feature[rowptr[i] .. rowptr[i+1]) / value[...]; rowptr[0] may be non-zero.
  * Rows are consumed in order; a mini-batch is trained as soon as -mini_batch rows
  * are buffered, exactly as if process() had been called row by row.
+ * `value` may be NULL: every value is then 1.0 (Hivemall's index-only features,
+ * "name" without ":value") and half of the feature bytes stay off the bus.
  * Copies host->device inside the call (asynchronously when the buffers are pinned). */
 hm_status hm_udtf_process(hm_udtf *u, int64_t n_rows, const int64_t *rowptr,
                           const int32_t *feature, const float *value, const float *label);

@@ -117,3 +117,21 @@ def test_profiling_counters_cover_every_launch():
     assert all(v["ms"] > 0 for v in kt.values())
     assert sum(v["launches"] for v in kt.values()) == u.stats().kernel_launches
     u.destroy()
+
+
+def test_null_values_mean_one():
+    """value == NULL on the host path: index-only features, every value 1.0 (nothing but the indices crosses the bus)."""
+    data = synth.kdd12_like(5000, dims=1 << 16, seed=25)
+    rp, f, v, y = data.numpy()
+    assert np.all(v == 1.0)
+    opts = f"-opt adagrad -mini_batch 512 -dims {1 << 16}"
+    a = hm.train_classifier(opts)
+    a.process_batch(rp, f, v, y)
+    a.close()
+    b = hm.train_classifier(opts)
+    b.process_batch(rp[:1234], f, None, y[:1233])        # ragged pushes: carried tails keep their ones
+    b.process_batch(rp[1233:], f, None, y[1233:])
+    b.close()
+    assert np.array_equal(a.array_to_host("w"), b.array_to_host("w"))
+    assert b.stats().h2d_bytes < a.stats().h2d_bytes
+    a.destroy(); b.destroy()
