@@ -283,7 +283,11 @@ __device__ __forceinline__ void fm_apply_pending(const FmUpdParams &P, int npend
 // chunks leave their piece in first_* / last_* for fm_merge_kernel, exactly as before.
 constexpr int kFmThreads = 256;
 constexpr int kFmItems = kFmChunk / kFmThreads;     // 4
-constexpr int kFmNV = 4;                            // values reduced per pass
+#ifndef HM_FM_NV
+#define HM_FM_NV 4
+#endif
+constexpr int kFmNV = HM_FM_NV;                     // values reduced per pass (a multiple of 4)
+static_assert(kFmNV % 4 == 0, "factor groups are moved as 16-byte vectors");
 constexpr int kFmPad = kFmChunk + kFmChunk / 32 + 2;
 __device__ __forceinline__ int fm_pad(int q) { return q + (q >> 5); }
 
@@ -303,7 +307,10 @@ constexpr size_t kFmSmem =
     + (size_t)kFmChunk * (4 + 4 + 8 + 8)         // list: key, cnt, A1, A2
     + (size_t)kFmChunk * kFmNV * 8;              // list: the current group's sums
 
-__global__ void __launch_bounds__(kFmThreads) fm_update_kernel(FmUpdParams P)
+#ifndef HM_FM_MINB
+#define HM_FM_MINB 1
+#endif
+__global__ void __launch_bounds__(kFmThreads, HM_FM_MINB) fm_update_kernel(FmUpdParams P)
 {
     extern __shared__ __align__(16) unsigned char fm_smem[];
     uint32_t *s_key = reinterpret_cast<uint32_t *>(fm_smem);
@@ -403,10 +410,14 @@ __global__ void __launch_bounds__(kFmThreads) fm_update_kernel(FmUpdParams P)
                 if (g == 0) { val[i][0] = s_c1[fm_pad(q)]; val[i][1] = s_c2[fm_pad(q)]; }
                 else {
                     const float c1 = s_c1[fm_pad(q)];
-                    if ((k & 3) == 0) {     // rows of S are 16-byte aligned: one load for the four factors
-                        const float4 sv = __ldg(reinterpret_cast<const float4 *>(P.stab + (size_t)rr[i] * k + f0));
-                        val[i][0] = __fmul_rn(c1, sv.x); val[i][1] = __fmul_rn(c1, sv.y);
-                        val[i][2] = __fmul_rn(c1, sv.z); val[i][3] = __fmul_rn(c1, sv.w);
+                    if ((k & 3) == 0) {     // rows of S are 16-byte aligned: one load per four factors
+#pragma unroll
+                        for (int h = 0; h < kFmNV / 4; h++)
+                            if (f0 + 4 * h < k) {
+                                const float4 sv = __ldg(reinterpret_cast<const float4 *>(P.stab + (size_t)rr[i] * k + f0 + 4 * h));
+                                val[i][4 * h + 0] = __fmul_rn(c1, sv.x); val[i][4 * h + 1] = __fmul_rn(c1, sv.y);
+                                val[i][4 * h + 2] = __fmul_rn(c1, sv.z); val[i][4 * h + 3] = __fmul_rn(c1, sv.w);
+                            }
                     } else {
 #pragma unroll
                         for (int v = 0; v < kFmNV; v++)
@@ -528,12 +539,18 @@ __global__ void __launch_bounds__(kFmThreads) fm_update_kernel(FmUpdParams P)
                 if (ok[u]) {
                     const uint32_t j = l_key[e];
                     if (vec) {
-                        const float4 a4 = *reinterpret_cast<const float4 *>(P.vrec + (size_t)j * P.vw + f0);
-                        vv[u][0] = a4.x; vv[u][1] = a4.y; vv[u][2] = a4.z; vv[u][3] = a4.w;
-                        if (P.adagrad) {
-                            const float4 b4 = *reinterpret_cast<const float4 *>(P.vrec + (size_t)j * P.vw + k + f0);
-                            va[u][0] = b4.x; va[u][1] = b4.y; va[u][2] = b4.z; va[u][3] = b4.w;
-                        } else { va[u][0] = va[u][1] = va[u][2] = va[u][3] = 0.0f; }
+#pragma unroll
+                        for (int h = 0; h < kFmNV / 4; h++) {
+                            va[u][4 * h] = va[u][4 * h + 1] = va[u][4 * h + 2] = va[u][4 * h + 3] = 0.0f;
+                            if (f0 + 4 * h < k) {
+                                const float4 a4 = *reinterpret_cast<const float4 *>(P.vrec + (size_t)j * P.vw + f0 + 4 * h);
+                                vv[u][4 * h] = a4.x; vv[u][4 * h + 1] = a4.y; vv[u][4 * h + 2] = a4.z; vv[u][4 * h + 3] = a4.w;
+                                if (P.adagrad) {
+                                    const float4 b4 = *reinterpret_cast<const float4 *>(P.vrec + (size_t)j * P.vw + k + f0 + 4 * h);
+                                    va[u][4 * h] = b4.x; va[u][4 * h + 1] = b4.y; va[u][4 * h + 2] = b4.z; va[u][4 * h + 3] = b4.w;
+                                }
+                            }
+                        }
                     } else {
 #pragma unroll
                         for (int v = 0; v < kFmNV; v++)
@@ -557,9 +574,15 @@ __global__ void __launch_bounds__(kFmThreads) fm_update_kernel(FmUpdParams P)
                             fm_step(P, fm_grad(P, G, cn), P.lambda_v, vv[u][v], va[u][v]);
                         }
                     if (vec) {
-                        *reinterpret_cast<float4 *>(P.vrec + (size_t)j * P.vw + f0) = make_float4(vv[u][0], vv[u][1], vv[u][2], vv[u][3]);
-                        if (P.adagrad)
-                            *reinterpret_cast<float4 *>(P.vrec + (size_t)j * P.vw + k + f0) = make_float4(va[u][0], va[u][1], va[u][2], va[u][3]);
+#pragma unroll
+                        for (int h = 0; h < kFmNV / 4; h++)
+                            if (f0 + 4 * h < k) {
+                                *reinterpret_cast<float4 *>(P.vrec + (size_t)j * P.vw + f0 + 4 * h) =
+                                    make_float4(vv[u][4 * h], vv[u][4 * h + 1], vv[u][4 * h + 2], vv[u][4 * h + 3]);
+                                if (P.adagrad)
+                                    *reinterpret_cast<float4 *>(P.vrec + (size_t)j * P.vw + k + f0 + 4 * h) =
+                                        make_float4(va[u][4 * h], va[u][4 * h + 1], va[u][4 * h + 2], va[u][4 * h + 3]);
+                            }
                     } else {
 #pragma unroll
                         for (int v = 0; v < kFmNV; v++)
