@@ -209,7 +209,13 @@ sort_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint2 *__restric
     __shared__ uint32_t wcnt[kScatWarps][kRadix];
     __shared__ uint32_t dig_base[kRadix], gofs[kRadix], warp_tot[kRadix / 32];
     __shared__ uint32_t s_rows[FIRST ? kRowSlice + 1 : 1];
+    __shared__ uint32_t s_mark[FIRST ? kSortTile / 32 : 1];   // bit p: a row starts at tile position p
+    __shared__ uint32_t s_dup;                                // two rows start at one position (an empty row)
     __shared__ int s_nr;
+    if (FIRST) {
+        for (int q = threadIdx.x; q < kSortTile / 32; q += kScatThreads) s_mark[q] = 0;
+        if (threadIdx.x == 0) s_dup = 0;
+    }
     for (int s = threadIdx.x; s <= n_segs; s += kScatThreads) { s_off[s] = seg_off[s]; s_toff[s] = seg_tile_off[s]; }
     __syncthreads();
     const uint32_t total = s_toff[n_segs];
@@ -246,6 +252,7 @@ sort_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint2 *__restric
         const uint32_t ew = e0 + warp * (32 * kScatItems) + lane;
         // payloads are requested now and consumed after the ranking
         uint2 pay[kScatItems];
+        int nr = 0; bool covered = false;
         if (FIRST) {
             // the values are requested before the row search, so that their latency hides behind it
 #pragma unroll
@@ -253,17 +260,25 @@ sort_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint2 *__restric
                 const uint32_t e = ew + i * 32;
                 if (e < e1) pay[i].y = __float_as_uint(__ldcs(val_in + e));
             }
-            const int64_t base = rl.rowptr[rl.block_row0];
-            const int64_t mb_row0 = rl.block_row0 + (int64_t)seg * rl.mini_batch;
             const int mb_rows = (int)min((int64_t)rl.mini_batch, rl.block_rows - (int64_t)seg * rl.mini_batch);
-            const int64_t *rp = rl.rowptr + mb_row0;
-            const int ra = cur_ra;
             // stage rp[ra ..] - base.  The first kScatThreads entries were prefetched into `slice_v`
             // with the keys and almost always cover the tile (one barrier); otherwise keep loading.
-            int nr = min(kScatThreads - 1, mb_rows - ra);
+            nr = min(kScatThreads - 1, mb_rows - cur_ra);
             if ((int)threadIdx.x <= nr) s_rows[threadIdx.x] = slice_v;
             __syncthreads();
-            if (s_rows[nr] < e1) {            // uniform: the prefetched part does not reach the tile's end
+            covered = s_rows[nr] >= e1;       // uniform
+            if (covered) {
+                // Fast path: every row that starts inside the tile sets the bit of its start position; the row
+                // of an element is then (tile's first row) + (bits at or below its position).  Two rows on one
+                // position -- an empty row -- cannot be told apart that way: the tile takes the search path.
+                if (threadIdx.x >= 1 && (int)threadIdx.x <= nr && slice_v > e0 && slice_v < e1) {
+                    const uint32_t p = slice_v - e0, bit = 1u << (p & 31);
+                    if (atomicOr(&s_mark[p >> 5], bit) & bit) s_dup = 1;
+                }
+            } else {
+                const int64_t base = rl.rowptr[rl.block_row0];
+                const int64_t *rp = rl.rowptr + rl.block_row0 + (int64_t)seg * rl.mini_batch;
+                const int ra = cur_ra;
                 nr = -1;
                 for (int i0 = kScatThreads; i0 <= kRowSlice; i0 += kScatThreads) {
                     if (threadIdx.x == 0) s_nr = 0x7fffffff;
@@ -283,31 +298,6 @@ sort_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint2 *__restric
                     if (got != 0x7fffffff) { nr = got; break; }
                 }
             }
-            // a thread's elements are 32 apart and ascending: search once, then walk forward
-            int idx = 0;
-            bool searched = false;
-#pragma unroll
-            for (int i = 0; i < kScatItems; i++) {
-                const uint32_t e = ew + i * 32;
-                if (e < e1) {
-                    int row;
-                    if (nr >= 0) {
-                        if (!searched) {
-                            int lo = 0, hi = nr;        // s_rows[lo] <= e < s_rows[hi]
-                            while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (s_rows[mid] <= e) lo = mid; else hi = mid; }
-                            idx = lo; searched = true;
-                        } else {
-                            while (s_rows[idx + 1] <= e) idx++;     // s_rows[nr] >= e1 > e bounds the walk
-                        }
-                        row = ra + idx;
-                    } else {
-                        int lo = ra, hi = mb_rows;  // slice too small (very short rows): search the row pointer itself
-                        while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if ((uint32_t)(rp[mid] - base) <= e) lo = mid; else hi = mid; }
-                        row = lo;
-                    }
-                    pay[i].x = (uint32_t)row;
-                }
-            }
         } else {
 #pragma unroll
             for (int i = 0; i < kScatItems; i++) {
@@ -317,6 +307,55 @@ sort_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint2 *__restric
         }
         for (int q = threadIdx.x; q < kScatWarps * kRadix; q += kScatThreads) (&wcnt[0][0])[q] = 0;
         __syncthreads();
+        if (FIRST) {
+            const int ra = cur_ra;
+            if (covered && !s_dup) {
+                // rows that start before this warp's 256 positions, then one word of marks per round
+                uint32_t before = 0;
+#pragma unroll
+                for (int j = 0; j < kSortTile / 32 / 32; j++) {
+                    const int wd = lane + 32 * j;
+                    if (wd < warp * kScatItems) before += __popc(s_mark[wd]);
+                }
+                before = __reduce_add_sync(0xffffffffu, before);
+                const uint32_t le_mask = 0xffffffffu >> (31 - lane);
+#pragma unroll
+                for (int i = 0; i < kScatItems; i++) {
+                    const uint32_t m = s_mark[warp * kScatItems + i];
+                    pay[i].x = (uint32_t)ra + before + __popc(m & le_mask);
+                    before += __popc(m);
+                }
+            } else {
+                const int64_t base = rl.rowptr[rl.block_row0];
+                const int mb_rows = (int)min((int64_t)rl.mini_batch, rl.block_rows - (int64_t)seg * rl.mini_batch);
+                const int64_t *rp = rl.rowptr + rl.block_row0 + (int64_t)seg * rl.mini_batch;
+                // a thread's elements are 32 apart and ascending: search once, then walk forward
+                int idx = 0;
+                bool searched = false;
+#pragma unroll
+                for (int i = 0; i < kScatItems; i++) {
+                    const uint32_t e = ew + i * 32;
+                    if (e < e1) {
+                        int row;
+                        if (nr >= 0) {
+                            if (!searched) {
+                                int lo = 0, hi = nr;        // s_rows[lo] <= e < s_rows[hi]
+                                while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (s_rows[mid] <= e) lo = mid; else hi = mid; }
+                                idx = lo; searched = true;
+                            } else {
+                                while (s_rows[idx + 1] <= e) idx++;     // s_rows[nr] >= e1 > e bounds the walk
+                            }
+                            row = ra + idx;
+                        } else {
+                            int lo = ra, hi = mb_rows;  // slice too small (very short rows): search the row pointer itself
+                            while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if ((uint32_t)(rp[mid] - base) <= e) lo = mid; else hi = mid; }
+                            row = lo;
+                        }
+                        pay[i].x = (uint32_t)row;
+                    }
+                }
+            }
+        }
         // stable rank of every element among equal digits inside its warp
 #pragma unroll
         for (int i = 0; i < kScatItems; i++) {
@@ -385,6 +424,10 @@ sort_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint2 *__restric
             }
         }
         __syncthreads();
+        if (FIRST) {      // marks are consumed: clear them for the next tile (its marks come after its slice barrier)
+            for (int q = threadIdx.x; q < kSortTile / 32; q += kScatThreads) s_mark[q] = 0;
+            if (threadIdx.x == 0) s_dup = 0;
+        }
         const uint32_t n_tile = e1 - e0;
         // next tile's coordinates and keys (the key registers are free from here on)
         const uint32_t next = tile + gridDim.x;
