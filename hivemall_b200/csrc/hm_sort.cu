@@ -29,7 +29,8 @@ namespace {
 constexpr int kSortThreads = 256;
 constexpr int kSortWarps = kSortThreads / 32;
 constexpr int kSortItems = kSortTile / kSortThreads;  // 16
-constexpr int kRadix = 256;
+constexpr int kMaxRadixBits = 9;          // digits are 8 bits wide, or 9 where that saves a pass (17-18, 25-27 key bits)
+constexpr int kMaxRadix = 1 << kMaxRadixBits;
 // the scatter kernel covers the same 4096-element tile with twice the threads: more warps per SM
 constexpr int kScatThreads = 512;
 constexpr int kScatWarps = kScatThreads / 32;
@@ -91,13 +92,15 @@ __global__ void tile_row0_kernel(const int64_t *__restrict__ rowptr, int64_t blo
     }
 }
 
+template <int RB>
 __global__ void __launch_bounds__(kSortThreads)
 sort_hist_kernel(const uint32_t *__restrict__ keys, const uint32_t *__restrict__ seg_off,
                  const uint32_t *__restrict__ seg_tile_off, int n_segs, int shift,
                  uint32_t *__restrict__ tile_hist, uint32_t *__restrict__ row_sum)
 {
+    constexpr int R = 1 << RB;
     __shared__ uint32_t s_off[kMaxSegs + 1], s_toff[kMaxSegs + 1];
-    __shared__ uint32_t hist[kSortWarps][kRadix];
+    __shared__ uint32_t hist[kSortWarps][R];
     for (int s = threadIdx.x; s <= n_segs; s += kSortThreads) { s_off[s] = seg_off[s]; s_toff[s] = seg_tile_off[s]; }
     __syncthreads();
     const uint32_t total = s_toff[n_segs];
@@ -107,8 +110,7 @@ sort_hist_kernel(const uint32_t *__restrict__ keys, const uint32_t *__restrict__
         const uint32_t tis = tile - s_toff[seg], nt = s_toff[seg + 1] - s_toff[seg];
         const uint32_t e0 = s_off[seg] + tis * kSortTile;
         const uint32_t e1 = min(e0 + (uint32_t)kSortTile, s_off[seg + 1]);
-#pragma unroll
-        for (int w = 0; w < kSortWarps; w++) hist[w][threadIdx.x] = 0;
+        for (int q = threadIdx.x; q < kSortWarps * R; q += kSortThreads) (&hist[0][0])[q] = 0;
         __syncthreads();
         uint32_t k[kSortItems];
 #pragma unroll
@@ -119,14 +121,16 @@ sort_hist_kernel(const uint32_t *__restrict__ keys, const uint32_t *__restrict__
 #pragma unroll
         for (int i = 0; i < kSortItems; i++) {
             const uint32_t e = e0 + i * kSortThreads + threadIdx.x;
-            if (e < e1) atomicAdd(&hist[warp][(k[i] >> shift) & (kRadix - 1)], 1u);
+            if (e < e1) atomicAdd(&hist[warp][(k[i] >> shift) & (R - 1)], 1u);
         }
         __syncthreads();
-        uint32_t c = 0;
+        for (int d = threadIdx.x; d < R; d += kSortThreads) {
+            uint32_t c = 0;
 #pragma unroll
-        for (int w = 0; w < kSortWarps; w++) c += hist[w][threadIdx.x];
-        tile_hist[(size_t)s_toff[seg] * kRadix + (size_t)threadIdx.x * nt + tis] = c;
-        if (c) atomicAdd(&row_sum[seg * kRadix + threadIdx.x], c);
+            for (int w = 0; w < kSortWarps; w++) c += hist[w][d];
+            tile_hist[(size_t)s_toff[seg] * R + (size_t)d * nt + tis] = c;
+            if (c) atomicAdd(&row_sum[seg * R + d], c);
+        }
         __syncthreads();
     }
 }
@@ -159,14 +163,14 @@ __global__ void __launch_bounds__(1024) scan_rows_kernel(uint32_t *__restrict__ 
 // One warp per (segment, digit) row of tile_hist: exclusive scan along the row, plus row base.
 __global__ void __launch_bounds__(kSortThreads)
 scan_tiles_kernel(uint32_t *__restrict__ tile_hist, const uint32_t *__restrict__ row_base,
-                  const uint32_t *__restrict__ seg_tile_off, int n_segs)
+                  const uint32_t *__restrict__ seg_tile_off, int n_segs, int radix)
 {
     const int lane = threadIdx.x & 31;
     const int row = blockIdx.x * kSortWarps + (threadIdx.x >> 5);
-    if (row >= n_segs * kRadix) return;
-    const int seg = row / kRadix, d = row % kRadix;
+    if (row >= n_segs * radix) return;
+    const int seg = row / radix, d = row % radix;
     const uint32_t t0 = seg_tile_off[seg], nt = seg_tile_off[seg + 1] - t0;
-    uint32_t *p = tile_hist + (size_t)t0 * kRadix + (size_t)d * nt;
+    uint32_t *p = tile_hist + (size_t)t0 * radix + (size_t)d * nt;
     uint32_t run = row_base[row];
     for (uint32_t k0 = 0; k0 < nt; k0 += 32) {
         const uint32_t k = k0 + lane;
@@ -194,7 +198,7 @@ constexpr int kRowSlice = 1024;   // staged row-pointer entries; tiles that need
 
 constexpr size_t kScatterSmem = (size_t)kSortTile * 4 + (size_t)kSortTile * 8;   // keys + payloads
 
-template <bool FIRST>
+template <bool FIRST, int RB>
 __global__ void __launch_bounds__(kScatThreads, kScatCtasPerSm)
 sort_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint2 *__restrict__ pay_in,
                     RowLookup rl, const float *__restrict__ val_in,
@@ -202,12 +206,13 @@ sort_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint2 *__restric
                     const uint32_t *__restrict__ seg_off, const uint32_t *__restrict__ seg_tile_off,
                     int n_segs, int shift, const uint32_t *__restrict__ tile_hist)
 {
+    constexpr int R = 1 << RB;
     extern __shared__ __align__(16) unsigned char dyn_smem[];
     uint32_t *s_key = reinterpret_cast<uint32_t *>(dyn_smem);
     uint2 *s_pay = reinterpret_cast<uint2 *>(dyn_smem + (size_t)kSortTile * 4);
     __shared__ uint32_t s_off[kMaxSegs + 1], s_toff[kMaxSegs + 1];
-    __shared__ uint32_t wcnt[kScatWarps][kRadix];
-    __shared__ uint32_t dig_base[kRadix], gofs[kRadix], warp_tot[kRadix / 32];
+    __shared__ uint32_t wcnt[kScatWarps][R];
+    __shared__ uint32_t dig_base[R], gofs[R], warp_tot[R / 32];
     __shared__ uint32_t s_rows[FIRST ? kRowSlice + 1 : 1];
     __shared__ uint32_t s_mark[FIRST ? kSortTile / 32 : 1];   // bit p: a row starts at tile position p
     __shared__ uint32_t s_dup;                                // two rows start at one position (an empty row)
@@ -305,7 +310,7 @@ sort_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint2 *__restric
                 if (e < e1) pay[i] = __ldcs(pay_in + e);
             }
         }
-        for (int q = threadIdx.x; q < kScatWarps * kRadix; q += kScatThreads) (&wcnt[0][0])[q] = 0;
+        for (int q = threadIdx.x; q < kScatWarps * R; q += kScatThreads) (&wcnt[0][0])[q] = 0;
         __syncthreads();
         if (FIRST) {
             const int ra = cur_ra;
@@ -360,17 +365,17 @@ sort_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint2 *__restric
 #pragma unroll
         for (int i = 0; i < kScatItems; i++) {
             const bool valid = ew + i * 32 < e1;
-            const uint32_t d = (key[i] >> shift) & (kRadix - 1);
+            const uint32_t d = (key[i] >> shift) & (R - 1);
             const uint32_t active = __ballot_sync(0xffffffffu, valid);
             uint32_t peers = 0, prev = 0;
             if (FIRST) {
                 // match.any costs time in proportion to the number of distinct values in the warp.  In the
                 // first pass the elements are still in row order (32 consecutive elements = 32 different
-                // hashed features): eight ballots -- lanes that agree with mine in every bit -- are
+                // hashed features): one ballot per digit bit -- lanes that agree with mine in every bit -- is
                 // cheaper there.  Later passes see long runs of equal digits and keep match.any.
                 peers = active;
 #pragma unroll
-                for (int b = 0; b < 8; b++) {
+                for (int b = 0; b < RB; b++) {
                     const uint32_t m = __ballot_sync(0xffffffffu, valid && ((d >> b) & 1u));
                     peers &= ((d >> b) & 1u) ? m : ~m;
                 }
@@ -388,9 +393,9 @@ sort_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint2 *__restric
         __syncthreads();
         // per-digit: exclusive scan over warps, then exclusive scan over digits
         {
-            // the first kRadix threads own one digit each
+            // the first R threads own one digit each
             const int d = threadIdx.x;
-            const bool owner = d < kRadix;
+            const bool owner = d < R;
             uint32_t run = 0;
             if (owner) {
 #pragma unroll
@@ -404,10 +409,10 @@ sort_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint2 *__restric
             if (owner) {
                 uint32_t wbase = 0;
 #pragma unroll
-                for (int w = 0; w < kRadix / 32; w++) if (w < warp) wbase += warp_tot[w];
+                for (int w = 0; w < R / 32; w++) if (w < warp) wbase += warp_tot[w];
                 const uint32_t ex = wbase + inc - run;
                 dig_base[d] = ex;
-                gofs[d] = tile_hist[(size_t)s_toff[seg] * kRadix + (size_t)d * nt + tis] - ex;
+                gofs[d] = tile_hist[(size_t)s_toff[seg] * R + (size_t)d * nt + tis] - ex;
             }
         }
         __syncthreads();
@@ -417,7 +422,7 @@ sort_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint2 *__restric
         for (int i = 0; i < kScatItems; i++) {
             const uint32_t e = ew + i * 32;
             if (e < e1) {
-                const uint32_t d = (key[i] >> shift) & (kRadix - 1);
+                const uint32_t d = (key[i] >> shift) & (R - 1);
                 const uint32_t pos = dig_base[d] + wcnt[warp][d] + rank[i];
                 s_key[pos] = key[i];
                 s_pay[pos] = pay[i];
@@ -446,7 +451,7 @@ sort_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint2 *__restric
         }
         for (uint32_t p = threadIdx.x; p < n_tile; p += kScatThreads) {
             const uint32_t k = s_key[p];
-            const uint32_t g = gofs[(k >> shift) & (kRadix - 1)] + p;
+            const uint32_t g = gofs[(k >> shift) & (R - 1)] + p;
             keys_out[g] = k;
             pay_out[g] = s_pay[p];
         }
@@ -470,7 +475,7 @@ hm_status sort_scratch_reserve(SortScratch &s, int64_t elems)
     if (!s.seg_off) {
         HM_CUDA(cudaMalloc(&s.seg_off, (kMaxSegs + 1) * sizeof(uint32_t)));
         HM_CUDA(cudaMalloc(&s.seg_tile_off, (kMaxSegs + 1) * sizeof(uint32_t)));
-        HM_CUDA(cudaMalloc(&s.row_sum, (size_t)kMaxSegs * kRadix * sizeof(uint32_t)));
+        HM_CUDA(cudaMalloc(&s.row_sum, (size_t)kMaxSegs * kMaxRadix * sizeof(uint32_t)));
     }
     if (elems > s.cap_elems) {
         for (int b = 0; b < 2; b++) {
@@ -488,7 +493,7 @@ hm_status sort_scratch_reserve(SortScratch &s, int64_t elems)
             HM_CUDA(cudaMalloc(&s.pay[b], (size_t)cap * sizeof(uint2)));
         }
         s.cap_tiles = cap / kSortTile + kMaxSegs + 1;
-        HM_CUDA(cudaMalloc(&s.tile_hist, (size_t)s.cap_tiles * kRadix * sizeof(uint32_t)));
+        HM_CUDA(cudaMalloc(&s.tile_hist, (size_t)s.cap_tiles * kMaxRadix * sizeof(uint32_t)));
         HM_CUDA(cudaMalloc(&s.tile_row0, (size_t)s.cap_tiles * sizeof(int32_t)));
         s.cap_elems = cap;
     }
@@ -524,48 +529,62 @@ hm_status launch_segmented_sort(Launcher &L, SortScratch &s, const uint32_t *d_f
                                 int64_t block_rows, int32_t mini_batch, int64_t n_elems, int n_segs, int key_bits,
                                 int *out_buf, int ctas_per_sm)
 {
-    static bool attr_set = false;   // > 48 KB of dynamic shared memory needs opting in, once per process
-    if (!attr_set) {
-        HM_CUDA(cudaFuncSetAttribute(sort_scatter_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kScatterSmem));
-        HM_CUDA(cudaFuncSetAttribute(sort_scatter_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kScatterSmem));
-        attr_set = true;
+    // > 48 KB of dynamic shared memory needs opting in, once per device
+    static bool attr_set[64] = {false};
+    int dev = 0;
+    HM_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64 || !attr_set[dev]) {
+        HM_CUDA(cudaFuncSetAttribute(sort_scatter_kernel<true, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kScatterSmem));
+        HM_CUDA(cudaFuncSetAttribute(sort_scatter_kernel<false, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kScatterSmem));
+        HM_CUDA(cudaFuncSetAttribute(sort_scatter_kernel<true, 9>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kScatterSmem));
+        HM_CUDA(cudaFuncSetAttribute(sort_scatter_kernel<false, 9>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kScatterSmem));
+        if (dev >= 0 && dev < 64) attr_set[dev] = true;
     }
     if (n_elems > s.cap_elems) HM_FAIL(HM_ERR_STATE, "sort scratch too small (%lld > %lld)", (long long)n_elems,
                                        (long long)s.cap_elems);
+    // 8-bit digits, or 9-bit ones where that saves a whole pass (17-18 and 25-27 key bits)
+    if (key_bits < 1) key_bits = 1;
     int passes = (key_bits + 7) / 8;
-    if (passes < 1) passes = 1;
+    int wide = 0;                        // how many of the passes use 9 bits
+    if ((key_bits + 8) / 9 < passes) { passes = (key_bits + 8) / 9; wide = std::max(0, key_bits - 8 * passes); }
     const int64_t max_tiles = n_elems / kSortTile + n_segs;
     // ctas_per_sm == 0: take the whole GPU; otherwise leave room for kernels of another stream
     const int grid = persistent_grid(max_tiles, ctas_per_sm > 0 ? ctas_per_sm : 6);
     const int hist_grid = persistent_grid(max_tiles, ctas_per_sm > 0 ? 2 * ctas_per_sm : 6);
-    const int rows = n_segs * kRadix;
     RowLookup rl;
     rl.rowptr = d_rowptr; rl.block_row0 = block_row0; rl.block_rows = block_rows; rl.mini_batch = mini_batch;
     rl.tile_row0 = s.tile_row0;
+    int shift = 0;
     for (int p = 0; p < passes; p++) {
-        const int shift = 8 * p;
+        const int rb = p < wide ? 9 : 8;
+        const int rows = n_segs << rb;
         const uint32_t *kin = p == 0 ? d_feature_block : s.key[(p - 1) & 1];
         const uint2 *pin = p == 0 ? nullptr : s.pay[(p - 1) & 1];
         uint32_t *kout = s.key[p & 1];
         uint2 *pout = s.pay[p & 1];
         HM_CUDA(cudaMemsetAsync(s.row_sum, 0, (size_t)rows * sizeof(uint32_t), L.stream));
-        HM_LAUNCH(L, K_SORT_HIST, 4.0 * (double)n_elems,
-                  (sort_hist_kernel<<<hist_grid, kSortThreads, 0, L.stream>>>(kin, s.seg_off, s.seg_tile_off, n_segs, shift,
-                                                                         s.tile_hist, s.row_sum)));
+        if (rb == 9)
+            HM_LAUNCH(L, K_SORT_HIST, 4.0 * (double)n_elems,
+                      (sort_hist_kernel<9><<<hist_grid, kSortThreads, 0, L.stream>>>(kin, s.seg_off, s.seg_tile_off, n_segs, shift,
+                                                                                s.tile_hist, s.row_sum)));
+        else
+            HM_LAUNCH(L, K_SORT_HIST, 4.0 * (double)n_elems,
+                      (sort_hist_kernel<8><<<hist_grid, kSortThreads, 0, L.stream>>>(kin, s.seg_off, s.seg_tile_off, n_segs, shift,
+                                                                                s.tile_hist, s.row_sum)));
         HM_LAUNCH(L, K_SORT_SCAN, 0.0, (scan_rows_kernel<<<1, 1024, 0, L.stream>>>(s.row_sum, rows)));
         HM_LAUNCH(L, K_SORT_SCAN, 0.0,
                   (scan_tiles_kernel<<<(rows + kSortWarps - 1) / kSortWarps, kSortThreads, 0, L.stream>>>(
-                      s.tile_hist, s.row_sum, s.seg_tile_off, n_segs)));
-        if (p == 0)
-            HM_LAUNCH(L, K_SORT_SCATTER, 20.0 * (double)n_elems + 8.0 * (double)block_rows,
-                      (sort_scatter_kernel<true><<<grid, kScatThreads, kScatterSmem, L.stream>>>(
-                          kin, pin, rl, d_value_block, kout, pout, s.seg_off, s.seg_tile_off, n_segs, shift,
-                          s.tile_hist)));
-        else
-            HM_LAUNCH(L, K_SORT_SCATTER, 24.0 * (double)n_elems,
-                      (sort_scatter_kernel<false><<<grid, kScatThreads, kScatterSmem, L.stream>>>(
-                          kin, pin, rl, nullptr, kout, pout, s.seg_off, s.seg_tile_off, n_segs, shift,
-                          s.tile_hist)));
+                      s.tile_hist, s.row_sum, s.seg_tile_off, n_segs, 1 << rb)));
+        const double bytes = p == 0 ? 20.0 * (double)n_elems + 8.0 * (double)block_rows : 24.0 * (double)n_elems;
+#define HM_SCATTER(FIRST_, RB_)                                                                                        \
+    HM_LAUNCH(L, K_SORT_SCATTER, bytes,                                                                                 \
+              (sort_scatter_kernel<FIRST_, RB_><<<grid, kScatThreads, kScatterSmem, L.stream>>>(                        \
+                  kin, pin, rl, p == 0 ? d_value_block : nullptr, kout, pout, s.seg_off, s.seg_tile_off, n_segs, shift, \
+                  s.tile_hist)))
+        if (p == 0) { if (rb == 9) HM_SCATTER(true, 9); else HM_SCATTER(true, 8); }
+        else { if (rb == 9) HM_SCATTER(false, 9); else HM_SCATTER(false, 8); }
+#undef HM_SCATTER
+        shift += rb;
     }
     HM_CUDA(cudaGetLastError());
     *out_buf = (passes - 1) & 1;

@@ -83,6 +83,19 @@ def test_criteo_shaped_hashed_dims(opt):
     u.destroy()
 
 
+@pytest.mark.parametrize("dims", [300, 511, (1 << 17) - 3, 1 << 18, (1 << 24) + 1, 1 << 25, (1 << 27) - 1])
+def test_key_widths_that_use_nine_bit_digits(dims):
+    """The sort takes 9-bit digits where that saves a pass (9, 17-18, 25-27 key bits): 1, 2 or 3 passes
+    of mixed widths must group features exactly like 8-bit digits do."""
+    data = synth.criteo_like(12000, dims=dims, seed=5)
+    options = f"-opt adagrad -mini_batch 4096 -dims {dims} -eta0 0.05"
+    u, w, state = run_gpu_linear("train_classifier", options, data)
+    ref, ref_state = run_oracle_linear("train_classifier", options, data)
+    assert_weights_close(w, ref.w)
+    assert_weights_close(state, ref_state, "state")
+    u.destroy()
+
+
 def test_push_boundaries_do_not_matter():
     """Mini-batch boundaries belong to the row stream, not to the process() calls."""
     data = synth.criteo_like(5000, dims=1 << 16, seed=2)
