@@ -117,7 +117,8 @@ hm_status update_scratch_reserve(UpdateScratch &u);
 void update_scratch_free(UpdateScratch &u);
 hm_status launch_linear_update(Launcher &L, const LinearArgs &a, const StepScalars &sc, UpdateScratch &us,
                                const uint32_t *d_sorted_key, const uint2 *d_sorted_pay,
-                               const uint32_t *d_seg_off, int seg, const float *d_dloss, int64_t nnz_hint);
+                               const uint32_t *d_seg_off, int seg, int64_t seg_begin, const float *d_dloss,
+                               int64_t nnz_hint);
 // small mini-batches (<= 1024 rows and <= one update tile of elements): up to 64 consecutive
 // mini-batches of a sorted block trained by one persistent CTA
 bool small_batch_eligible(int32_t mini_batch, int64_t max_mb_elems);

@@ -370,7 +370,7 @@ hm_status train_rows(hm_udtf *u, const Chunk &c, int64_t row0, int64_t n_rows, c
                 HM_TRY(launch_linear_forward(u->L, a, c.rp(), mrow0, mrows, p.row0, c.ft(), c.vl(), c.lb(),
                                              u->margin.as<float>(), u->dloss.as<float>(), u->d_bad, mnnz));
                 HM_TRY(launch_linear_update(u->L, a, sc, u->upd, ss.key[buf], ss.pay[buf], ss.seg_off, s,
-                                            u->dloss.as<float>(), mnnz));
+                                            mb_abs[p.m0 + s] - mb_abs[p.m0], u->dloss.as<float>(), mnnz));
             }
             u->stats.mini_batches++;
             u->last_margin_off = mrow0 - p.row0;

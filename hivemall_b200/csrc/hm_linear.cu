@@ -233,6 +233,9 @@ struct UpdParams {
     float eta, adam_alpha, lambda, eps, rho, beta1, beta2, alpha, beta, lambda1, lambda2;
     double inv_rows;         // 1 / rows of the mini-batch, computed on the host in fp64
     int32_t n_active;        // CTAs launched (all own at least one tile unless the segment is empty)
+    uint32_t seg_begin;      // linear_update_kernel: first element of the mini-batch in the sorted block and
+    uint32_t seg_elems;      // its element count (= seg_off[seg], seg_off[seg+1] - seg_off[seg]: the host knows
+                             // both, so the kernel does not start with a dependent load)
 };
 
 // Replica record of one feature while it is being updated.
@@ -342,7 +345,10 @@ __device__ __forceinline__ Scan combine(const Scan &a, const Scan &b)
 
 constexpr int kUpdPadded = kUpdTile + kUpdTile / 32 + 2;
 constexpr int kUpdList = kUpdTile + 8;
-constexpr int kUpdBatch = 4;         // independent record updates in flight per thread
+// independent record updates in flight per thread.  (The kernel sits at the 64-register limit of four CTAs
+// per SM: 4 in flight spilled 12 bytes and measured 48.8 us per mini-batch, 2 with the segment bounds
+// passed as parameters spills nothing: 44.6 us.)
+constexpr int kUpdBatch = 2;
 // shared memory is used twice: tile + closed-segment list while streaming, record buffers in the merge
 constexpr size_t kUpdSmemTile = (size_t)kUpdPadded * 8 + (size_t)kUpdList * 8;
 constexpr size_t kUpdSmemMerge = (size_t)kUpdMaxGrid * 24;   // staged `first` records + output list
@@ -536,8 +542,7 @@ __global__ void __launch_bounds__(kUpdThreads, 4) linear_update_kernel(UpdParams
 
     const int tid = threadIdx.x;
     USTAMP(0);
-    const uint32_t s0 = P.seg_off[P.seg], s1 = P.seg_off[P.seg + 1];
-    const uint32_t n = s1 - s0;
+    const uint32_t s0 = P.seg_begin, n = P.seg_elems;
     // contiguous split of the sorted mini-batch over the grid, in whole tiles
     const uint32_t tiles = (n + kUpdTile - 1) / kUpdTile;
     const uint32_t tiles_per_cta = (tiles + gridDim.x - 1) / gridDim.x;
@@ -869,9 +874,10 @@ void update_scratch_free(UpdateScratch &u)
 
 hm_status launch_linear_update(Launcher &L, const LinearArgs &a, const StepScalars &sc, UpdateScratch &us,
                                const uint32_t *d_sorted_key, const uint2 *d_sorted_pay,
-                               const uint32_t *d_seg_off, int seg, const float *d_dloss, int64_t nnz_hint)
+                               const uint32_t *d_seg_off, int seg, int64_t seg_begin, const float *d_dloss, int64_t nnz_hint)
 {
     UpdParams P;
+    P.seg_begin = (uint32_t)seg_begin; P.seg_elems = (uint32_t)nnz_hint;
     P.rec = a.rec; P.rec_width = a.rec_width; P.ftrl_derived = a.wv.ftrl; P.touched = nullptr;
     P.skey = d_sorted_key; P.spay = d_sorted_pay; P.dloss = d_dloss; P.seg_off = d_seg_off;
     P.br.first = reinterpret_cast<uint4 *>(us.boundary);
@@ -917,6 +923,7 @@ hm_status launch_linear_small_batches(Launcher &L, const LinearArgs &a, const in
     P.F.task = a.cfg.task; P.F.loss = a.cfg.loss; P.F.train = 1; P.F.dims = (uint32_t)a.cfg.dims; P.F.bad = d_bad;
     P.U.rec = a.rec; P.U.rec_width = a.rec_width; P.U.ftrl_derived = a.wv.ftrl; P.U.touched = nullptr;
     P.U.skey = d_sorted_key; P.U.spay = d_sorted_pay; P.U.dloss = d_dloss; P.U.seg_off = d_seg_off;
+    P.U.seg_begin = 0; P.U.seg_elems = 0;   // (the small-batch kernel reads seg_off itself)
     P.U.dims = (uint32_t)a.cfg.dims; P.U.opt = a.cfg.opt; P.U.reg = a.cfg.reg; P.U.grad_norm = a.cfg.grad_norm;
     P.U.lambda = a.cfg.lambda; P.U.eps = a.cfg.eps; P.U.rho = a.cfg.rho; P.U.beta1 = a.cfg.beta1; P.U.beta2 = a.cfg.beta2;
     P.U.alpha = a.cfg.alpha; P.U.beta = a.cfg.beta; P.U.lambda1 = a.cfg.lambda1; P.U.lambda2 = a.cfg.lambda2;
