@@ -747,10 +747,13 @@ hm_status launch_fm_update(Launcher &L, const FmArgs &a, const StepScalars &sc, 
                            const uint32_t *d_sorted_key, const uint2 *d_sorted_pay, const uint32_t *d_seg_off, int seg,
                            const float *d_dloss, const float *d_stab, int64_t nnz)
 {
-    static bool attr_set = false;
-    if (!attr_set) {
+    // > 48 KB of dynamic shared memory needs opting in, once per device
+    static bool attr_set[64] = {false};
+    int dev = 0;
+    HM_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64 || !attr_set[dev]) {
         HM_CUDA(cudaFuncSetAttribute(fm_update_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kFmSmem));
-        attr_set = true;
+        if (dev >= 0 && dev < 64) attr_set[dev] = true;
     }
     const int n_chunks = (int)std::max<int64_t>((nnz + kFmChunk - 1) / kFmChunk, 1);
     if (n_chunks > fs.cap_chunks) HM_FAIL(HM_ERR_STATE, "fm scratch too small");
