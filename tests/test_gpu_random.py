@@ -1,0 +1,50 @@
+"""Randomised differential test of the linear learner: option strings, shapes and push patterns drawn
+from a seeded generator, CUDA path vs. CPU oracle on identical rows (ragged rows with empty ones,
+mini-batches from 1 row to larger than the input, dims from 17 to 2^20, every loss / optimizer /
+regulariser / learning-rate schedule / gradient normalisation, one or two passes)."""
+import numpy as np
+import pytest
+
+from hivemall_b200 import synth
+
+from _util import assert_weights_close, run_gpu_linear, run_oracle_linear
+
+pytestmark = pytest.mark.gpu
+
+
+def draw_case(seed: int):
+    r = np.random.default_rng(seed)
+    fn = r.choice(["train_classifier", "train_regressor"])
+    loss = r.choice(["logloss", "hinge", "squared"]) if fn == "train_classifier" else "squared"
+    opt = r.choice(["sgd", "adagrad", "adadelta", "adam", "ftrl"])
+    dims = int(r.choice([17, 300, 5000, (1 << 17) + 1, 1 << 20]))
+    rows = int(r.integers(1, 6000))
+    mb = int(r.choice([1, 7, 64, 333, 1024, 2500, 8192]))
+    if mb == 1:
+        rows = min(rows, 300)
+    max_nnz = int(r.choice([1, 3, 20, 60]))
+    opts = [f"-loss {loss}", f"-opt {opt}", f"-mini_batch {mb}", f"-dims {dims}", f"-iters {int(r.choice([1, 1, 2]))}"]
+    opts.append(f"-eta {r.choice(['fixed', 'inverse', 'simple'])} -eta0 {r.choice([0.01, 0.05, 0.2])} -total_steps 100")
+    if opt != "ftrl":
+        reg = r.choice(["no", "l1", "l2"])
+        opts.append(f"-reg {reg} -lambda {r.choice([1e-4, 1e-2])}")
+    else:
+        opts.append(f"-alpha {r.choice([0.05, 0.5])} -lambda1 {r.choice([0.0, 1e-3])} -lambda2 {r.choice([0.0, 1e-2])}")
+    opts.append(f"-grad_norm {r.choice(['batch', 'count', 'sum'])}")
+    pushes = None
+    if r.random() < 0.5:       # ragged pushes: mini-batch boundaries must not depend on them
+        cuts = np.sort(r.integers(0, rows + 1, size=int(r.integers(1, 5))))
+        pushes = [int(b - a) for a, b in zip(np.concatenate([[0], cuts]), np.concatenate([cuts, [rows]])) if b > a]
+    return fn, " ".join(opts), dims, rows, max_nnz, pushes
+
+
+@pytest.mark.parametrize("seed", range(40))
+def test_random_configuration_matches_the_oracle(seed):
+    fn, options, dims, rows, max_nnz, pushes = draw_case(seed)
+    data = synth.ragged(rows, dims, max_nnz, seed=100 + seed, regression=(fn == "train_regressor"))
+    u, w, state = run_gpu_linear(fn, options, data, pushes=pushes)
+    ref, ref_state = run_oracle_linear(fn, options, data)
+    assert u.step == ref.t, options
+    assert_weights_close(w, ref.w, f"w [{fn} {options}]")
+    assert_weights_close(state, ref_state, f"state [{fn} {options}]")
+    u.destroy()
