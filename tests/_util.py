@@ -18,8 +18,12 @@ def assert_weights_close(got: np.ndarray, want: np.ndarray, what: str = "w", rto
     got = np.asarray(got, dtype=np.float64)
     want = np.asarray(want, dtype=np.float64)
     assert got.shape == want.shape, f"{what}: shape {got.shape} vs {want.shape}"
-    err = np.abs(got - want)
-    tol = rtol * np.maximum(np.abs(got), np.abs(want)) + atol
+    # a diverged run (inf / nan) must diverge in the same places, with the same sign
+    fin = np.isfinite(got) & np.isfinite(want)
+    same_nonfinite = (np.isnan(got) & np.isnan(want)) | ((got == want) & ~fin)
+    with np.errstate(invalid="ignore"):
+        err = np.where(fin, np.abs(got - want), np.where(same_nonfinite, 0.0, np.inf))
+        tol = np.where(fin, rtol * np.maximum(np.abs(got), np.abs(want)) + atol, 0.0)
     bad = err > tol
     if bad.any():
         i = int(np.argmax(err - tol))

@@ -48,3 +48,37 @@ def test_random_configuration_matches_the_oracle(seed):
     assert_weights_close(w, ref.w, f"w [{fn} {options}]")
     assert_weights_close(state, ref_state, f"state [{fn} {options}]")
     u.destroy()
+
+
+def draw_fm_case(seed: int):
+    r = np.random.default_rng(1000 + seed)
+    k = int(r.choice([1, 3, 4, 5, 8, 16, 33, 64]))
+    opt = r.choice(["sgd", "adagrad"])
+    cls = bool(r.random() < 0.5)
+    dims = int(r.choice([50, 3000, (1 << 16) + 7]))
+    rows = int(r.integers(1, 2500))
+    mb = int(r.choice([1, 16, 200, 1024, 4096]))
+    if mb == 1:
+        rows = min(rows, 150)
+    max_nnz = int(r.choice([1, 4, 30]))
+    opts = [f"-factors {k}", f"-opt {opt}", f"-mini_batch {mb}", f"-dims {dims}", f"-iters {int(r.choice([1, 1, 2]))}",
+            f"-eta0 {r.choice([0.01, 0.05])}", f"-sigma {r.choice([0.05, 0.3])}", f"-seed {int(r.integers(0, 99))}",
+            f"-lambda0 {r.choice([0.0, 0.01])} -lambdaW {r.choice([0.0, 0.01])} -lambdaV {r.choice([0.0, 0.01])}",
+            f"-grad_norm {r.choice(['batch', 'count', 'sum'])}"]
+    if cls:
+        opts.append("-classification")
+    pushes = None
+    if r.random() < 0.5:
+        cuts = np.sort(r.integers(0, rows + 1, size=int(r.integers(1, 4))))
+        pushes = [int(b - a) for a, b in zip(np.concatenate([[0], cuts]), np.concatenate([cuts, [rows]])) if b > a]
+    return " ".join(opts), dims, rows, max_nnz, pushes, cls, opt == "adagrad"
+
+
+@pytest.mark.parametrize("seed", range(24))
+def test_random_fm_configuration_matches_the_oracle(seed):
+    from test_gpu_fm import check, run_both
+    options, dims, rows, max_nnz, pushes, cls, adagrad = draw_fm_case(seed)
+    data = synth.ragged(rows, dims, max_nnz, seed=200 + seed, regression=not cls)
+    u, ref, _ = run_both(options, data, pushes=pushes)
+    check(u, ref, adagrad)
+    u.destroy()
