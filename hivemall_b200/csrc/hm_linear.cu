@@ -157,8 +157,12 @@ __device__ __forceinline__ void forward_rows_small(const FwdParams &P)
             p1[u] = ok ? P.rowptr[P.row0 + r0 + u + 1] : 0;
         }
         double acc[R];
+        float lab[R];   // requested now, used after the sums
 #pragma unroll
-        for (int u = 0; u < R; u++) acc[u] = 0.0;
+        for (int u = 0; u < R; u++) {
+            acc[u] = 0.0;
+            lab[u] = (sub == 0 && r0 + u < P.n_rows) ? P.label[P.row0 + r0 + u] : 0.0f;
+        }
         int64_t longest = 0;
 #pragma unroll
         for (int u = 0; u < R; u++) longest = max(longest, p1[u] - p0[u]);
@@ -185,8 +189,7 @@ __device__ __forceinline__ void forward_rows_small(const FwdParams &P)
                 const int64_t row = P.row0 + r0 + u;
                 const float m = (float)acc[u];
                 P.margin[row - P.block_row0] = m;
-                const float lab = P.label[row];
-                const float y = P.task == HM_TASK_CLASSIFIER ? (lab > 0.0f ? 1.0f : -1.0f) : lab;
+                const float y = P.task == HM_TASK_CLASSIFIER ? (lab[u] > 0.0f ? 1.0f : -1.0f) : lab[u];
                 P.dloss[r0 + u] = dloss_of(P.loss, m, y);
             }
         }
@@ -645,10 +648,14 @@ __global__ void __launch_bounds__(kUpdThreads, 4) linear_update_kernel(UpdParams
 // Same arithmetic, same order as the two-kernel path: the results are bit-identical.
 constexpr int kSmallSegs = 64;
 
+constexpr int kSmallMaxRows = 1024;                 // rows per mini-batch on this path
+constexpr size_t kSmallModelMax = 128 * 1024;       // a replica up to this size lives in shared memory for the launch
+
 struct SmallParams {
     FwdParams F;             // row0 / n_rows are filled per mini-batch
     UpdParams U;             // seg / eta / adam_alpha / inv_rows are filled per mini-batch
     int32_t first_seg, n_segs, mini_batch;
+    uint32_t model_floats;   // > 0: the replica (dims * rec_width floats) is staged in shared memory
     float eta[kSmallSegs], adam_alpha[kSmallSegs];
     int32_t rows[kSmallSegs];
 };
@@ -668,16 +675,31 @@ __global__ void __launch_bounds__(kUpdThreads, 1) linear_small_batch_kernel(cons
     S.s_warp = s_warp; S.s_carry = &s_carry; S.s_first = &s_first; S.s_carry_open = &s_carry_open;
     S.s_edge = s_edge; S.s_nlist = &s_nlist;
     const int tid = threadIdx.x;
+    // The dloss table of a mini-batch (<= 1024 rows) never leaves shared memory, and neither does a small
+    // replica (a9a-shaped models are a kilobyte): every mini-batch of the launch then costs three dependent
+    // global round trips (row pointer, features/values, sorted tile) instead of six.
+    __shared__ float s_dloss[kSmallMaxRows];
+    extern __shared__ __align__(16) float s_model[];
+    float *const g_rec = P.U.rec;
+    const bool staged = P.model_floats != 0;
+    if (staged) {
+        for (uint32_t i = tid; i < P.model_floats; i += kUpdThreads) s_model[i] = g_rec[i];
+        __syncthreads();
+    }
     for (int s = 0; s < P.n_segs; s++) {
         FwdParams F = P.F;
         F.row0 = P.F.block_row0 + (int64_t)(P.first_seg + s) * P.mini_batch;
         F.n_rows = P.rows[s];
+        F.dloss = s_dloss;
+        if (staged) F.wv.base = s_model;
         forward_rows_small(F);
         if (tid == 0) { s_carry.cnt = 0; s_carry_open = 0; s_first.cnt = 0; s_edge[0] = 1; s_edge[1] = 1; s_nlist = 0; }
         __syncthreads();     // dloss of every row is written; the whole mini-batch is one closed range
         UpdParams U = P.U;
         U.seg = P.first_seg + s; U.eta = P.eta[s]; U.adam_alpha = P.adam_alpha[s];
         U.inv_rows = 1.0 / (double)P.rows[s];
+        U.dloss = s_dloss;
+        if (staged) U.rec = s_model;
         const uint32_t s0 = U.seg_off[U.seg];
         const int n = (int)(U.seg_off[U.seg + 1] - s0);       // <= kUpdTile, checked by the host
         if (n > 0) {
@@ -686,6 +708,8 @@ __global__ void __launch_bounds__(kUpdThreads, 1) linear_small_batch_kernel(cons
         }
         __syncthreads();     // the step is complete before the next forward reads the replica
     }
+    if (staged)
+        for (uint32_t i = tid; i < P.model_floats; i += kUpdThreads) g_rec[i] = s_model[i];
 }
 
 // ---- model table --------------------------------------------------------------------
@@ -929,7 +953,20 @@ hm_status launch_linear_small_batches(Launcher &L, const LinearArgs &a, const in
     P.U.alpha = a.cfg.alpha; P.U.beta = a.cfg.beta; P.U.lambda1 = a.cfg.lambda1; P.U.lambda2 = a.cfg.lambda2;
     P.first_seg = first_seg; P.n_segs = n_segs; P.mini_batch = a.cfg.mini_batch;
     for (int s = 0; s < n_segs; s++) { P.eta[s] = eta[s]; P.adam_alpha[s] = adam_alpha[s]; P.rows[s] = rows[s]; }
-    HM_LAUNCH(L, K_LIN_UPDATE, 24.0 * (double)nnz_hint, (linear_small_batch_kernel<<<1, kUpdThreads, 0, L.stream>>>(P)));
+    const size_t model_bytes = (size_t)a.cfg.dims * a.rec_width * sizeof(float);
+    size_t dyn = 0;
+    if (model_bytes <= kSmallModelMax) {
+        static bool attr_set[64] = {false};   // > 48 KB of dynamic shared memory needs opting in, once per device
+        int dev = 0;
+        HM_CUDA(cudaGetDevice(&dev));
+        if (dev < 0 || dev >= 64 || !attr_set[dev]) {
+            HM_CUDA(cudaFuncSetAttribute(linear_small_batch_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmallModelMax));
+            if (dev >= 0 && dev < 64) attr_set[dev] = true;
+        }
+        P.model_floats = (uint32_t)(model_bytes / sizeof(float));
+        dyn = model_bytes;
+    }
+    HM_LAUNCH(L, K_LIN_UPDATE, 24.0 * (double)nnz_hint, (linear_small_batch_kernel<<<1, kUpdThreads, dyn, L.stream>>>(P)));
     HM_CUDA(cudaGetLastError());
     return HM_OK;
 }
