@@ -94,6 +94,7 @@ def parse_args():
     ap.add_argument("--workload", default="ftrl", choices=sorted(WORKLOADS))
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-numa", action="store_true", help="do not bind ranks to their GPU's NUMA node (N > 1)")
     return ap.parse_args()
 
 
@@ -277,6 +278,8 @@ def main():
         raise SystemExit("bench.py needs a CUDA device: hivemall_b200 has no CPU fallback")
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
+    # one process per GPU: run next to it and allocate the pinned host buffers in its NUMA node
+    host_cpus = hm.bind_host_to_gpu(local_rank) if world > 1 and not args.no_numa else None
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
 
@@ -437,6 +440,8 @@ def main():
                "d2h_bytes_per_step": MINI_BATCH * 4, "ms_per_step": dt / K * 1e3,
                "last_minibatch_loss": losses[-1], "loss": "squared/2" if wl["regression"] else "logloss", "pcie_GBps": h2d * K / dt / 1e9,
                "timing": "host wall clock around K calls, each ending in a blocking D2H read",
+               "host_binding": (f"rank bound to {len(host_cpus)} CPUs next to its GPU (NVML affinity)" if host_cpus
+                                else "none"),
                "values": "NULL (index-only features, 1.0 implied)" if index_only else "f32 per element"}
         v.destroy()
         for arrs in host:

@@ -10,11 +10,11 @@ from ._lib import HivemallError, UDFArgumentError, LIB_PATH  # noqa: F401
 from .udtf import (  # noqa: F401
     UDTF, TrainClassifierUDTF, TrainRegressorUDTF, FactorizationMachineUDTF,
     train_classifier, train_regressor, train_fm, mhash, feature_hashing, parse_options,
-    host_alloc, host_free, DEFAULT_NUM_FEATURES, DEFAULT_HASH_SEED,
+    host_alloc, host_free, bind_host_to_gpu, DEFAULT_NUM_FEATURES, DEFAULT_HASH_SEED,
 )
 
 __all__ = [
     "UDTF", "TrainClassifierUDTF", "TrainRegressorUDTF", "FactorizationMachineUDTF",
     "train_classifier", "train_regressor", "train_fm", "mhash", "feature_hashing",
-    "parse_options", "host_alloc", "host_free", "HivemallError", "UDFArgumentError",
+    "parse_options", "host_alloc", "host_free", "bind_host_to_gpu", "HivemallError", "UDFArgumentError",
 ]

@@ -85,6 +85,34 @@ def host_free(address: int) -> None:
     check(_lib.load().hm_host_free(C.c_void_p(address)))
 
 
+def bind_host_to_gpu(device: int) -> list[int] | None:
+    """Pin the calling process to the CPUs NVML names as closest to GPU `device`, so that host buffers
+    allocated afterwards (host_alloc: pinned, placed by first touch) land in that GPU's NUMA node and the
+    thread that feeds the GPU runs next to it.  With one process per GPU and eight GPUs copying at once, buffers
+    that all sit in one socket's memory cap the end-to-end rate.  Returns the CPU list, or None when NVML or
+    the affinity call is unavailable (nothing is changed then)."""
+    import os
+    try:
+        import pynvml
+        import torch
+        pynvml.nvmlInit()
+        try:
+            uuid = str(torch.cuda.get_device_properties(device).uuid)
+            handle = pynvml.nvmlDeviceGetHandleByUUID(uuid if uuid.startswith("GPU-") else "GPU-" + uuid)
+        except Exception:
+            handle = pynvml.nvmlDeviceGetHandleByIndex(device)
+        words = ((os.cpu_count() or 64) + 63) // 64
+        mask = pynvml.nvmlDeviceGetCpuAffinity(handle, words)
+        cpus = {i * 64 + b for i, w in enumerate(mask) for b in range(64) if (int(w) >> b) & 1}
+        cpus = sorted(cpus & os.sched_getaffinity(0))
+        if not cpus:
+            return None
+        os.sched_setaffinity(0, cpus)
+        return cpus
+    except Exception:
+        return None
+
+
 NOALLOC_MAX_DIMS = 1 << 26
 
 
