@@ -307,8 +307,11 @@ constexpr size_t kFmSmem =
     + (size_t)kFmChunk * (4 + 4 + 8 + 8)         // list: key, cnt, A1, A2
     + (size_t)kFmChunk * kFmNV * 8;              // list: the current group's sums
 
+#ifndef HM_FM_STEPB
+#define HM_FM_STEPB 2
+#endif
 #ifndef HM_FM_MINB
-#define HM_FM_MINB 1
+#define HM_FM_MINB 2
 #endif
 __global__ void __launch_bounds__(kFmThreads, HM_FM_MINB) fm_update_kernel(FmUpdParams P)
 {
@@ -322,7 +325,8 @@ __global__ void __launch_bounds__(kFmThreads, HM_FM_MINB) fm_update_kernel(FmUpd
     double *l_a1 = reinterpret_cast<double *>(l_cnt + kFmChunk);
     double *l_a2 = l_a1 + kFmChunk;
     double *l_gs = l_a2 + kFmChunk;              // [kFmNV][kFmChunk]
-    __shared__ FmScan s_warp[kFmThreads / 32];
+    __shared__ double s_warp_v[kFmThreads / 32][kFmNV];
+    __shared__ uint32_t s_warp_c[kFmThreads / 32];
     __shared__ int s_wk[kFmThreads / 32];
     __shared__ uint32_t s_edge[2];
 
@@ -391,12 +395,41 @@ __global__ void __launch_bounds__(kFmThreads, HM_FM_MINB) fm_update_kernel(FmUpd
     if (lane == 0) s_anyhead[warp] = warp_heads != 0;
     __syncthreads();
     int slot0 = inc - my_closes;
-    bool seen_head_before = (warp_heads & ((1u << lane) - 1u)) != 0;
-    for (int w2 = 0; w2 < warp; w2++) { slot0 += s_wk[w2]; seen_head_before = seen_head_before || s_anyhead[w2] != 0; }
+    // The segment structure does not depend on the factor group, so the flags of the segmented scans are
+    // worked out once: `reach` = how many lanes to my left belong to the run that is open at my last item
+    // (the inclusive scan adds lane - o iff o <= reach), `head_in_warp_before` = a run starts in a lower lane
+    // of my warp (then nothing is carried in from earlier warps), `carry_from` = first warp whose total is
+    // carried into mine (the last earlier warp that holds a head, or warp 0).
+    const uint32_t heads_le = warp_heads & (0xffffffffu >> (31 - lane));
+    const int reach = heads_le ? lane - (31 - __clz(heads_le)) : lane;
+    const bool head_in_warp_before = (warp_heads & ((1u << lane) - 1u)) != 0;
+    bool seen_head_before = head_in_warp_before;
+    int carry_from = 0;
+    for (int w2 = 0; w2 < warp; w2++) {
+        slot0 += s_wk[w2];
+        if (s_anyhead[w2] != 0) { seen_head_before = true; carry_from = w2; }
+    }
     int n_list = 0;
     for (int w2 = 0; w2 < kFmThreads / 32; w2++) n_list += s_wk[w2];
+    // length of the run that is open when my first item begins (the same segmented scan, on counts)
+    uint32_t cnt_in = 0;
+    {
+        uint32_t c = 0;
+#pragma unroll
+        for (int i = 0; i < kFmItems; i++)
+            if (q0 + i < nt) { if (head[i]) c = 0; c += 1; }
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const uint32_t uc = __shfl_up_sync(0xffffffffu, c, o); if (o <= reach) c += uc; }
+        if (lane == 31) s_warp_c[warp] = c;
+        cnt_in = __shfl_up_sync(0xffffffffu, c, 1);
+        if (lane == 0) cnt_in = 0;
+        __syncthreads();
+        if (!head_in_warp_before)
+            for (int w2 = carry_from; w2 < warp; w2++) cnt_in += s_warp_c[w2];
+    }
 
     const int n_groups = 1 + (k + kFmNV - 1) / kFmNV;
+#pragma unroll 1
     for (int g = 0; g < n_groups; g++) {
         const int f0 = (g - 1) * kFmNV;          // first factor of the group (g >= 1)
         // ---- values of my items
@@ -426,50 +459,50 @@ __global__ void __launch_bounds__(kFmThreads, HM_FM_MINB) fm_update_kernel(FmUpd
                 }
             }
         }
-        // ---- thread summary, exclusive segmented scan over the CTA
-        FmScan mine; mine.c = 0; mine.f = 0;
+        // ---- thread summary (sum and count of my trailing run), inclusive segmented scan over the warp with
+        // the precomputed flags, carry from the earlier warps
+        double sc[kFmNV];
 #pragma unroll
-        for (int v = 0; v < kFmNV; v++) mine.v[v] = 0.0;
+        for (int v = 0; v < kFmNV; v++) sc[v] = 0.0;
 #pragma unroll
         for (int i = 0; i < kFmItems; i++)
             if (q0 + i < nt) {
-                if (head[i]) { mine.f = 1; mine.c = 0;
+                if (head[i]) {
 #pragma unroll
-                    for (int v = 0; v < kFmNV; v++) mine.v[v] = 0.0; }
-                mine.c += 1;
+                    for (int v = 0; v < kFmNV; v++) sc[v] = 0.0; }
 #pragma unroll
-                for (int v = 0; v < kFmNV; v++) mine.v[v] += (double)val[i][v];
+                for (int v = 0; v < kFmNV; v++) sc[v] += (double)val[i][v];
             }
-        FmScan sc = mine;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
-            FmScan up;
-            up.c = __shfl_up_sync(0xffffffffu, sc.c, o);
-            up.f = __shfl_up_sync(0xffffffffu, sc.f, o);
+            const bool take = o <= reach;
 #pragma unroll
-            for (int v = 0; v < kFmNV; v++) up.v[v] = __shfl_up_sync(0xffffffffu, sc.v[v], o);
-            if (lane >= o) sc = fm_combine(up, sc);
+            for (int v = 0; v < kFmNV; v++) {
+                const double up = __shfl_up_sync(0xffffffffu, sc[v], o);
+                if (take) sc[v] = up + sc[v];
+            }
         }
-        __syncthreads();                           // s_warp / l_gs of the previous group are free
-        if (lane == 31) s_warp[warp] = sc;
-        FmScan ex;
-        ex.c = __shfl_up_sync(0xffffffffu, sc.c, 1);
-        ex.f = __shfl_up_sync(0xffffffffu, sc.f, 1);
+        __syncthreads();                           // s_warp_v / l_gs of the previous group are free
+        if (lane == 31) {
 #pragma unroll
-        for (int v = 0; v < kFmNV; v++) ex.v[v] = __shfl_up_sync(0xffffffffu, sc.v[v], 1);
-        if (lane == 0) { ex.c = 0; ex.f = 0;
+            for (int v = 0; v < kFmNV; v++) s_warp_v[warp][v] = sc[v];
+        }
+        double run[kFmNV]; uint32_t cnt = cnt_in;  // the run that is open when my first item begins
 #pragma unroll
-            for (int v = 0; v < kFmNV; v++) ex.v[v] = 0.0; }
+        for (int v = 0; v < kFmNV; v++) { run[v] = __shfl_up_sync(0xffffffffu, sc[v], 1); if (lane == 0) run[v] = 0.0; }
         __syncthreads();
-        FmScan wp; wp.c = 0; wp.f = 0;
+        if (!head_in_warp_before && warp > 0) {
+            double wp[kFmNV];
 #pragma unroll
-        for (int v = 0; v < kFmNV; v++) wp.v[v] = 0.0;
-        for (int w2 = 0; w2 < warp; w2++) wp = fm_combine(wp, s_warp[w2]);
-        const FmScan cin = fm_combine(wp, ex);
+            for (int v = 0; v < kFmNV; v++) wp[v] = 0.0;
+            for (int w2 = carry_from; w2 < warp; w2++) {
+#pragma unroll
+                for (int v = 0; v < kFmNV; v++) wp[v] += s_warp_v[w2][v];
+            }
+#pragma unroll
+            for (int v = 0; v < kFmNV; v++) run[v] = wp[v] + run[v];
+        }
         // ---- second walk: totals of the runs that end in my items
-        double run[kFmNV]; uint32_t cnt = cin.c;
-#pragma unroll
-        for (int v = 0; v < kFmNV; v++) run[v] = cin.v[v];
         bool seen_head = seen_head_before;
         int slot = slot0;
 #pragma unroll
@@ -530,68 +563,73 @@ __global__ void __launch_bounds__(kFmThreads, HM_FM_MINB) fm_update_kernel(FmUpd
                     P.touched[j] = 1;
                 }
         } else {
-            float vv[kPerT][kFmNV], va[kPerT][kFmNV]; bool ok[kPerT];
-            const bool vec = (k & 3) == 0;          // factor records are 16-byte aligned: one load / store per four factors
-#pragma unroll
-            for (int u = 0; u < kPerT; u++) {
-                const int e = u * kFmThreads + tid;
-                ok[u] = e < n_list && l_key[e] < P.dims;
-                if (ok[u]) {
-                    const uint32_t j = l_key[e];
-                    if (vec) {
-#pragma unroll
-                        for (int h = 0; h < kFmNV / 4; h++) {
-                            va[u][4 * h] = va[u][4 * h + 1] = va[u][4 * h + 2] = va[u][4 * h + 3] = 0.0f;
-                            if (f0 + 4 * h < k) {
-                                const float4 a4 = *reinterpret_cast<const float4 *>(P.vrec + (size_t)j * P.vw + f0 + 4 * h);
-                                vv[u][4 * h] = a4.x; vv[u][4 * h + 1] = a4.y; vv[u][4 * h + 2] = a4.z; vv[u][4 * h + 3] = a4.w;
-                                if (P.adagrad) {
-                                    const float4 b4 = *reinterpret_cast<const float4 *>(P.vrec + (size_t)j * P.vw + k + f0 + 4 * h);
-                                    va[u][4 * h] = b4.x; va[u][4 * h + 1] = b4.y; va[u][4 * h + 2] = b4.z; va[u][4 * h + 3] = b4.w;
+            // two list entries per thread at a time: all four would hold 32 more registers across the step
+            constexpr int kStepB = HM_FM_STEPB;
+#pragma unroll 1
+            for (int ub = 0; ub < kPerT; ub += kStepB) {
+                float vv[kStepB][kFmNV], va[kStepB][kFmNV]; bool ok[kStepB];
+                const bool vec = (k & 3) == 0;          // factor records are 16-byte aligned: one load / store per four factors
+    #pragma unroll
+                for (int u = 0; u < kStepB; u++) {
+                    const int e = (ub + u) * kFmThreads + tid;
+                    ok[u] = e < n_list && l_key[e] < P.dims;
+                    if (ok[u]) {
+                        const uint32_t j = l_key[e];
+                        if (vec) {
+    #pragma unroll
+                            for (int h = 0; h < kFmNV / 4; h++) {
+                                va[u][4 * h] = va[u][4 * h + 1] = va[u][4 * h + 2] = va[u][4 * h + 3] = 0.0f;
+                                if (f0 + 4 * h < k) {
+                                    const float4 a4 = *reinterpret_cast<const float4 *>(P.vrec + (size_t)j * P.vw + f0 + 4 * h);
+                                    vv[u][4 * h] = a4.x; vv[u][4 * h + 1] = a4.y; vv[u][4 * h + 2] = a4.z; vv[u][4 * h + 3] = a4.w;
+                                    if (P.adagrad) {
+                                        const float4 b4 = *reinterpret_cast<const float4 *>(P.vrec + (size_t)j * P.vw + k + f0 + 4 * h);
+                                        va[u][4 * h] = b4.x; va[u][4 * h + 1] = b4.y; va[u][4 * h + 2] = b4.z; va[u][4 * h + 3] = b4.w;
+                                    }
                                 }
                             }
+                        } else {
+    #pragma unroll
+                            for (int v = 0; v < kFmNV; v++)
+                                if (f0 + v < k) {
+                                    vv[u][v] = P.vrec[(size_t)j * P.vw + f0 + v];
+                                    va[u][v] = P.adagrad ? P.vrec[(size_t)j * P.vw + k + f0 + v] : 0.0f;
+                                }
                         }
-                    } else {
-#pragma unroll
-                        for (int v = 0; v < kFmNV; v++)
-                            if (f0 + v < k) {
-                                vv[u][v] = P.vrec[(size_t)j * P.vw + f0 + v];
-                                va[u][v] = P.adagrad ? P.vrec[(size_t)j * P.vw + k + f0 + v] : 0.0f;
-                            }
                     }
                 }
-            }
-#pragma unroll
-            for (int u = 0; u < kPerT; u++)
-                if (ok[u]) {
-                    const int e = u * kFmThreads + tid;
-                    const uint32_t j = l_key[e];
-                    const double a2 = l_a2[e]; const uint32_t cn = l_cnt[e];
-#pragma unroll
-                    for (int v = 0; v < kFmNV; v++)
-                        if (f0 + v < k) {
-                            const double G = l_gs[v * kFmChunk + e] - (double)vv[u][v] * a2;
-                            fm_step(P, fm_grad(P, G, cn), P.lambda_v, vv[u][v], va[u][v]);
-                        }
-                    if (vec) {
-#pragma unroll
-                        for (int h = 0; h < kFmNV / 4; h++)
-                            if (f0 + 4 * h < k) {
-                                *reinterpret_cast<float4 *>(P.vrec + (size_t)j * P.vw + f0 + 4 * h) =
-                                    make_float4(vv[u][4 * h], vv[u][4 * h + 1], vv[u][4 * h + 2], vv[u][4 * h + 3]);
-                                if (P.adagrad)
-                                    *reinterpret_cast<float4 *>(P.vrec + (size_t)j * P.vw + k + f0 + 4 * h) =
-                                        make_float4(va[u][4 * h], va[u][4 * h + 1], va[u][4 * h + 2], va[u][4 * h + 3]);
-                            }
-                    } else {
-#pragma unroll
+    #pragma unroll
+                for (int u = 0; u < kStepB; u++)
+                    if (ok[u]) {
+                        const int e = (ub + u) * kFmThreads + tid;
+                        const uint32_t j = l_key[e];
+                        const double a2 = l_a2[e]; const uint32_t cn = l_cnt[e];
+    #pragma unroll
                         for (int v = 0; v < kFmNV; v++)
                             if (f0 + v < k) {
-                                P.vrec[(size_t)j * P.vw + f0 + v] = vv[u][v];
-                                if (P.adagrad) P.vrec[(size_t)j * P.vw + k + f0 + v] = va[u][v];
+                                const double G = l_gs[v * kFmChunk + e] - (double)vv[u][v] * a2;
+                                fm_step(P, fm_grad(P, G, cn), P.lambda_v, vv[u][v], va[u][v]);
                             }
+                        if (vec) {
+    #pragma unroll
+                            for (int h = 0; h < kFmNV / 4; h++)
+                                if (f0 + 4 * h < k) {
+                                    *reinterpret_cast<float4 *>(P.vrec + (size_t)j * P.vw + f0 + 4 * h) =
+                                        make_float4(vv[u][4 * h], vv[u][4 * h + 1], vv[u][4 * h + 2], vv[u][4 * h + 3]);
+                                    if (P.adagrad)
+                                        *reinterpret_cast<float4 *>(P.vrec + (size_t)j * P.vw + k + f0 + 4 * h) =
+                                            make_float4(va[u][4 * h], va[u][4 * h + 1], va[u][4 * h + 2], va[u][4 * h + 3]);
+                                }
+                        } else {
+    #pragma unroll
+                            for (int v = 0; v < kFmNV; v++)
+                                if (f0 + v < k) {
+                                    P.vrec[(size_t)j * P.vw + f0 + v] = vv[u][v];
+                                    if (P.adagrad) P.vrec[(size_t)j * P.vw + k + f0 + v] = va[u][v];
+                                }
+                        }
                     }
-                }
+        }
         }
     }
     // a chunk without a piece on one side says so (group 0 wrote the headers that exist)
