@@ -77,7 +77,7 @@ constexpr int64_t kBlockElemCap = (int64_t)1 << 26;   // elements sorted per lau
 // to kMinSliceRows (see hm_udtf_process).  With one fixed size, measured on B200 (bench.py e2e,
 // mini-batch 65536): 2^21 -> 127 M rows/s, 2^20 -> 142, 2^19 -> 151, 2^18 -> 154; with the descending
 // schedule 159 M for (2^20 | 2^21, 2^16 | 2^17), 157.5 M for (2^20, 2^18), 155.5 M for (2^22, 2^17).
-constexpr int64_t kSliceRows = (int64_t)1 << 20;
+constexpr int64_t kSliceRows = (int64_t)1 << 19;
 constexpr int64_t kMinSliceRows = (int64_t)1 << 17;
 
 struct DevBuf {
@@ -148,6 +148,7 @@ struct hm_udtf {
     hm_config cfg;
     int device = 0;
     Launcher L, Ls, Lc;              // compute stream / sort stream / copy stream (fills only)
+    int64_t hint_rows = 0, hint_elems = 0;   // largest slice of the running process() call: chunk buffers are sized once
     cudaStream_t compute = nullptr, copy = nullptr, sorter = nullptr;
     cudaEvent_t sorted_ev[2] = {nullptr, nullptr}, trained_ev[2] = {nullptr, nullptr}, ready_ev = nullptr;
     bool trained_valid[2] = {false, false};
@@ -424,10 +425,12 @@ hm_status process_slice(hm_udtf *u, int64_t n, const int64_t *rowptr, const int3
     // A recycled chunk may still be read by queued compute work: make the copy stream wait for it.
     if (c->free_ev) HM_CUDA(cudaStreamWaitEvent(u->copy, c->free_ev, 0));
     // (growing a buffer frees the old one; cudaFree itself waits for outstanding work)
-    HM_TRY(c->rowptr.reserve((size_t)(rows + 1) * sizeof(int64_t)));
-    HM_TRY(c->feat.reserve((size_t)std::max<int64_t>(elems, 1) * sizeof(uint32_t)));
-    HM_TRY(c->val.reserve((size_t)std::max<int64_t>(elems, 1) * sizeof(float)));
-    HM_TRY(c->label.reserve((size_t)std::max<int64_t>(rows, 1) * sizeof(float)));
+    // (the slices of a call grow: size the buffers for the largest one right away)
+    const int64_t cap_rows = std::max(rows, u->hint_rows), cap_elems = std::max(elems, u->hint_elems);
+    HM_TRY(c->rowptr.reserve((size_t)(cap_rows + 1) * sizeof(int64_t)));
+    HM_TRY(c->feat.reserve((size_t)std::max<int64_t>(cap_elems, 1) * sizeof(uint32_t)));
+    HM_TRY(c->val.reserve((size_t)std::max<int64_t>(cap_elems, 1) * sizeof(float)));
+    HM_TRY(c->label.reserve((size_t)std::max<int64_t>(cap_rows, 1) * sizeof(float)));
 
     // new rows: host-to-device on the copy stream, queued before the host-side loop below so that the
     // bus is busy while it runs
@@ -457,13 +460,16 @@ hm_status process_slice(hm_udtf *u, int64_t n, const int64_t *rowptr, const int3
         st[t_rows + i] = t_nnz + v;
     }
 
-    // carried rows: device-to-device on the compute stream (ordered after their producer)
+    // carried rows: device-to-device, also on the copy stream.  Their source is input data that this very
+    // stream copied in earlier (and the old chunk is only overwritten by a later copy on this stream), so
+    // nothing here waits for the compute stream: the sort of this slice can run while the previous slice
+    // is still training.
     if (t_rows) {
         const Chunk *o = u->tail;
         const int64_t o_e0 = o->mb_abs.empty() ? 0 : o->mb_abs.back();
-        HM_CUDA(cudaMemcpyAsync(c->feat.p, o->ft() + o_e0, (size_t)t_nnz * 4, cudaMemcpyDeviceToDevice, u->compute));
-        HM_CUDA(cudaMemcpyAsync(c->val.p, o->vl() + o_e0, (size_t)t_nnz * 4, cudaMemcpyDeviceToDevice, u->compute));
-        HM_CUDA(cudaMemcpyAsync(c->label.p, o->lb() + u->tail_row0, (size_t)t_rows * 4, cudaMemcpyDeviceToDevice, u->compute));
+        HM_CUDA(cudaMemcpyAsync(c->feat.p, o->ft() + o_e0, (size_t)t_nnz * 4, cudaMemcpyDeviceToDevice, u->copy));
+        HM_CUDA(cudaMemcpyAsync(c->val.p, o->vl() + o_e0, (size_t)t_nnz * 4, cudaMemcpyDeviceToDevice, u->copy));
+        HM_CUDA(cudaMemcpyAsync(c->label.p, o->lb() + u->tail_row0, (size_t)t_rows * 4, cudaMemcpyDeviceToDevice, u->copy));
     }
     if (u->tail) {
         // the old tail chunk is finished once the copies above have run
@@ -477,6 +483,7 @@ hm_status process_slice(hm_udtf *u, int64_t n, const int64_t *rowptr, const int3
     if (!u->stage_ev[turn]) HM_CUDA(cudaEventCreateWithFlags(&u->stage_ev[turn], cudaEventDisableTiming));
     HM_CUDA(cudaEventRecord(u->stage_ev[turn], u->copy));
     HM_CUDA(cudaStreamWaitEvent(u->compute, u->stage_ev[turn], 0));
+    HM_CUDA(cudaStreamWaitEvent(u->sorter, u->stage_ev[turn], 0));     // the sort needs the rows, not the model
     u->stats.h2d_bytes += (rows + 1) * 8 + nnz * (value ? 8 : 4) + n * 4;
 
     // full mini-batches
@@ -485,7 +492,7 @@ hm_status process_slice(hm_udtf *u, int64_t n, const int64_t *rowptr, const int3
     c->rows = train;
     c->mb_abs.resize((size_t)n_mb + 1);
     for (int64_t i = 0; i <= n_mb; i++) c->mb_abs[(size_t)i] = st[i * B];
-    HM_TRY(train_rows(u, *c, 0, train, c->mb_abs.data(), n_mb));
+    HM_TRY(train_rows(u, *c, 0, train, c->mb_abs.data(), n_mb, true));
 
     // what is left waits in this chunk
     u->tail = c;
@@ -698,19 +705,32 @@ hm_status hm_udtf_process(hm_udtf *u, int64_t n_rows, const int64_t *rowptr, con
     if (n_rows == 0) return HM_OK;
     if (rowptr[n_rows] > rowptr[0] && !feature) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "NULL feature buffer");
     DeviceGuard g(u->device);
-    // Slices of whole mini-batches, so that copies and training overlap.  The bus is the bottleneck of
-    // this entry point (the device trains three times faster than PCIe delivers), so the call takes
-    // (bytes / bus speed) + (training of the LAST slice, which no copy overlaps): large slices first,
-    // because copies of >= 160 MB run at the full 55 GB/s, then halving, so that the tail is short.
+    // Slices of whole mini-batches, so that copies and training overlap (copy of slice k+1 beside the training
+    // of slice k, two chunk buffers).  A call takes
+    //   (copy of the FIRST slice, during which the device idles) + sum over slices of max(copy, training)
+    //   + (training of the LAST slice, which no copy overlaps):
+    // one small slice first (short fill), then slices of kSliceRows (copies of >= 160 MB reach the full
+    // 55 GB/s; equal sizes keep the two stages in step when training is as slow as the bus, as for train_fm),
+    // halving towards the end of the call (short drain: matters when the bus is the bottleneck).
     const int64_t B = u->cfg.mini_batch;
     const int64_t smallest = std::max<int64_t>(kMinSliceRows / B * B, 2 * B);
-    int64_t slice = std::max<int64_t>(kSliceRows / B * B, smallest);
+    const int64_t largest = std::max<int64_t>(kSliceRows / B * B, smallest);
+    int64_t ramp = smallest;
+    {
+        const int64_t big = std::min(n_rows, largest);
+        const double per_row = (double)(rowptr[n_rows] - rowptr[0]) / (double)n_rows;
+        u->hint_rows = big + B;
+        u->hint_elems = (int64_t)((double)(big + B) * per_row * 1.05) + 1024;
+    }
     for (int64_t r = 0; r < n_rows;) {
+        int64_t slice = ramp;
         while (slice > smallest && n_rows - r <= 2 * slice) slice = std::max<int64_t>((slice / 2) / B * B, smallest);
         const int64_t n = std::min(slice, n_rows - r);
         HM_TRY(process_slice(u, n, rowptr + r, feature, value, label + r));
         r += n;
+        ramp = largest;
     }
+    u->hint_rows = 0; u->hint_elems = 0;
     return HM_OK;
 }
 
