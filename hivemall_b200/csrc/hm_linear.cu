@@ -437,6 +437,34 @@ __device__ __forceinline__ void reduce_tile(const UpdParams &P, const UpdShared 
     const bool close_tail = last_tile && right_closed;
     __syncthreads();  // everyone has read the carry before it is overwritten below
 
+    // ---- a tile that holds ONE feature (a hot feature's run spans dozens of tiles: a third of the tiles of a
+    // Criteo-shaped mini-batch) needs no segmented scan: a plain fixed-order reduction, and one piece.
+    if (first_tile && last_tile && key0 == S.s_key[pad_idx(n_tile - 1)]) {
+        double part = 0.0;
+#pragma unroll
+        for (int i = 0; i < kUpdItems; i++) {
+            const int q = i * kUpdThreads + tid;
+            if (q < n_tile) part += (double)S.s_val[pad_idx(q)];
+        }
+        part = warp_sum(part);
+        if (lane == 0) S.s_warp[warp].v = part;
+        __syncthreads();
+        if (tid == 0) {
+            double sum = 0.0;
+#pragma unroll
+            for (int w2 = 0; w2 < kUpdThreads / 32; w2++) sum += S.s_warp[w2].v;
+            SegRec r; r.sum = sum; r.key = key0; r.cnt = (uint32_t)n_tile;
+            *S.s_nlist = 0;
+            S.s_carry->cnt = 0; *S.s_carry_open = 0;
+            if (!left_closed && !right_closed) { *S.s_carry = r; *S.s_carry_open = 1; }   // piece of a longer run
+            else if (!left_closed) *S.s_first = r;                                          // the run's last piece
+            else if (!right_closed) *S.s_carry = r;                                         // the run's first piece
+            else { S.l_key[0] = key0; S.l_g[0] = grad_of(P, sum, r.cnt); *S.s_nlist = 1; }  // the whole run
+        }
+        __syncthreads();
+        return;
+    }
+
     // ---- pass 1: thread summaries (items [8*tid, 8*tid+8)).  A "head" is an item at tile
     // position >= 1 whose feature differs from its predecessor; position 0 is never a head:
     // it either continues the carried segment or starts afresh with an empty running sum.
