@@ -175,7 +175,8 @@ struct hm_udtf {
     int64_t *d_total = nullptr;
     // data
     std::vector<Chunk *> retained;   // pass-1 chunks kept for -iters > 1
-    std::vector<Chunk *> pool;       // recycled chunk storage
+    std::vector<Chunk *> pool;       // recycled chunk storage (oldest first)
+    int chunks_alive = 0;            // owned chunks in circulation (pool + tail + in flight)
     Chunk *tail = nullptr;           // chunk whose last rows do not fill a mini-batch yet
     int64_t tail_row0 = 0;           // first untrained row of `tail`
     std::vector<int64_t> tail_rp;    // host copy of the untrained rows' rowptr, 0-based (size tail_rows+1)
@@ -386,14 +387,30 @@ hm_status train_rows(hm_udtf *u, const Chunk &c, int64_t row0, int64_t n_rows, c
     return HM_OK;
 }
 
+// A chunk for the next slice of host rows.  Prefer a recycled chunk the device is already done with;
+// otherwise open another one while fewer than kMaxChunks circulate (so that the copy stream can run
+// ahead of training by more than one slice when the two are equally fast); otherwise take the one
+// that was retired first (the copy stream will wait for its free_ev).
+constexpr int kMaxChunks = 4;
+
 Chunk *acquire_chunk(hm_udtf *u)
 {
-    if (!u->pool.empty()) {
-        Chunk *c = u->pool.back();
-        u->pool.pop_back();
+    for (size_t i = 0; i < u->pool.size(); i++) {
+        Chunk *c = u->pool[i];
+        if (!c->free_ev || cudaEventQuery(c->free_ev) == cudaSuccess) {
+            u->pool.erase(u->pool.begin() + (long)i);
+            return c;
+        }
+    }
+    cudaGetLastError();   // (cudaErrorNotReady from the queries is not an error)
+    if (u->pool.empty() || u->chunks_alive < kMaxChunks) {
+        Chunk *c = new (std::nothrow) Chunk();
+        if (c) u->chunks_alive++;
         return c;
     }
-    return new (std::nothrow) Chunk();
+    Chunk *c = u->pool.front();
+    u->pool.erase(u->pool.begin());
+    return c;
 }
 
 // The compute stream is (or will be, in stream order) done with `c`: recycle or retain it.
