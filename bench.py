@@ -410,17 +410,25 @@ def main():
         margins = np.empty(MINI_BATCH, dtype=np.float32)
         losses = []
 
+        pending = []     # (margins, labels) of the previous step: its loss is worked out on the host while the
+                         # device is busy with the current one (the blocking D2H read itself stays in every step)
+
+        def host_loss():
+            if pending:
+                m, t = pending.pop()
+                if wl["regression"]:
+                    losses.append(float(np.mean(0.5 * (m - t) ** 2)))
+                else:
+                    losses.append(float(np.mean(np.logaddexp(0.0, -(t * 2 - 1) * m))))
+
         def step_host(i):
             (rp, _), (ft, _), (vl, _), (lb, lbt) = host[i % n_host]
             v.process_pointers(rps, rp, ft, vl, lb)
             if mixer2 and (i + 1) % mix_every == 0:
                 mixer2.mix()
+            host_loss()
             m = v.last_margins(margins)                      # D2H read of the step's result, waits
-            t = lbt[rps - len(m):].numpy()
-            if wl["regression"]:
-                losses.append(float(np.mean(0.5 * (m - t) ** 2)))
-            else:
-                losses.append(float(np.mean(np.logaddexp(0.0, -(t * 2 - 1) * m))))
+            pending.append((m.copy(), lbt[rps - len(m):].numpy()))
 
         for i in range(W):
             step_host(i)
@@ -428,6 +436,7 @@ def main():
         t0 = time.perf_counter()
         for i in range(W, W + K):
             step_host(i)
+        host_loss()
         v.sync()
         barrier()
         dt = time.perf_counter() - t0
