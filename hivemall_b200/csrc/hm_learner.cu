@@ -105,6 +105,7 @@ struct Chunk {
     bool view = false;
     int64_t rows = 0;                   // rows whose mini-batches are listed in mb_abs
     DevBuf rowptr, feat, val, label;    // owned storage
+    DevBuf sq_rp, sc_rp, sq_feat, sq_val, sc_feat;   // split pushes: the two groups as they arrive, merged on the device
     const int64_t *v_rowptr = nullptr;  // view storage
     const uint32_t *v_feat = nullptr;
     const float *v_val = nullptr, *v_label = nullptr;
@@ -117,10 +118,57 @@ struct Chunk {
     void release()
     {
         rowptr.release(); feat.release(); val.release(); label.release();
+        sq_rp.release(); sc_rp.release(); sq_feat.release(); sq_val.release(); sc_feat.release();
         if (free_ev) cudaEventDestroy(free_ev);
         free_ev = nullptr;
     }
 };
+
+// One slice of host rows: plain CSR (value may be NULL = all ones), or split into a quantitative group
+// (index and value) and an index-only group (value 1.0); row i = its quantitative elements, then its
+// index-only elements.
+struct HostRows {
+    int64_t n = 0;
+    const int64_t *rowptr = nullptr; const int32_t *feature = nullptr; const float *value = nullptr;
+    bool split = false;
+    const int64_t *q_rowptr = nullptr, *c_rowptr = nullptr;
+    const int32_t *q_feature = nullptr, *c_feature = nullptr;
+    const float *q_value = nullptr;
+    const float *label = nullptr;
+    int64_t nnz() const
+    {
+        return split ? (q_rowptr[n] - q_rowptr[0]) + (c_rowptr[n] - c_rowptr[0]) : rowptr[n] - rowptr[0];
+    }
+    int64_t row_end(int64_t i) const   // elements before row i, relative to the slice
+    {
+        return split ? (q_rowptr[i] - q_rowptr[0]) + (c_rowptr[i] - c_rowptr[0]) : rowptr[i] - rowptr[0];
+    }
+};
+
+// Split rows -> one CSR on the device: a warp per row copies the quantitative elements, then the
+// index-only ones with value 1.0, and writes the row pointer.  Only the bytes that carry information
+// crossed the bus.
+__global__ void __launch_bounds__(256)
+merge_split_kernel(int64_t n, const int64_t *__restrict__ q_rp, int64_t q_base, const int64_t *__restrict__ c_rp,
+                   int64_t c_base, const uint32_t *__restrict__ q_feat, const float *__restrict__ q_val,
+                   const uint32_t *__restrict__ c_feat, int64_t out_base, int64_t *__restrict__ out_rp,
+                   uint32_t *__restrict__ out_feat, float *__restrict__ out_val)
+{
+    const int lane = threadIdx.x & 31;
+    const int64_t warps = (int64_t)gridDim.x * (blockDim.x >> 5);
+    for (int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); row < n; row += warps) {
+        const int64_t q0 = q_rp[row] - q_base, q1 = q_rp[row + 1] - q_base;
+        const int64_t c0 = c_rp[row] - c_base, c1 = c_rp[row + 1] - c_base;
+        const int64_t o = out_base + q0 + c0;
+        for (int64_t i = lane; i < q1 - q0; i += 32) { out_feat[o + i] = q_feat[q0 + i]; out_val[o + i] = q_val[q0 + i]; }
+        const int64_t o2 = o + (q1 - q0);
+        for (int64_t i = lane; i < c1 - c0; i += 32) { out_feat[o2 + i] = c_feat[c0 + i]; out_val[o2 + i] = 1.0f; }
+        if (lane == 0) {
+            out_rp[row] = o;
+            if (row == n - 1) out_rp[n] = out_base + q1 + c1;
+        }
+    }
+}
 
 __global__ void gather_rowptr_kernel(const int64_t *__restrict__ rowptr, int64_t n_rows, int32_t step,
                                      int64_t n_out, int64_t *__restrict__ out)
@@ -148,7 +196,7 @@ struct hm_udtf {
     hm_config cfg;
     int device = 0;
     Launcher L, Ls, Lc;              // compute stream / sort stream / copy stream (fills only)
-    int64_t hint_rows = 0, hint_elems = 0;   // largest slice of the running process() call: chunk buffers are sized once
+    int64_t hint_rows = 0, hint_elems = 0, hint_q = 0, hint_c = 0;   // largest slice of the running process() call: chunk buffers are sized once
     cudaStream_t compute = nullptr, copy = nullptr, sorter = nullptr;
     cudaEvent_t sorted_ev[2] = {nullptr, nullptr}, trained_ev[2] = {nullptr, nullptr}, ready_ev = nullptr;
     bool trained_valid[2] = {false, false};
@@ -427,13 +475,13 @@ hm_status retire_chunk(hm_udtf *u, Chunk *c, bool retain)
 }
 
 // One slice of host rows: build [tail | slice] on the device, train the full mini-batches.
-hm_status process_slice(hm_udtf *u, int64_t n, const int64_t *rowptr, const int32_t *feature, const float *value,
-                        const float *label)
+hm_status process_slice(hm_udtf *u, const HostRows &h)
 {
     const int32_t B = u->cfg.mini_batch;
+    const int64_t n = h.n;
     const int64_t t_rows = u->tail_rows();
     const int64_t t_nnz = t_rows ? u->tail_rp.back() : 0;
-    const int64_t nnz = rowptr[n] - rowptr[0];
+    const int64_t nnz = h.nnz();
     const int64_t rows = t_rows + n, elems = t_nnz + nnz;
     if (nnz < 0) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "rowptr is not non-decreasing");
 
@@ -451,13 +499,39 @@ hm_status process_slice(hm_udtf *u, int64_t n, const int64_t *rowptr, const int3
 
     // new rows: host-to-device on the copy stream, queued before the host-side loop below so that the
     // bus is busy while it runs
-    const int64_t base = rowptr[0];
-    if (nnz) {
-        HM_CUDA(cudaMemcpyAsync(c->feat.as<uint32_t>() + t_nnz, feature + base, (size_t)nnz * 4, cudaMemcpyHostToDevice, u->copy));
-        if (value) HM_CUDA(cudaMemcpyAsync(c->val.as<float>() + t_nnz, value + base, (size_t)nnz * 4, cudaMemcpyHostToDevice, u->copy));
-        else HM_TRY(launch_fill_u32(u->Lc, c->val.as<uint32_t>() + t_nnz, nnz, 0x3f800000u));   // index-only features: 1.0f
+    if (!h.split) {
+        const int64_t base = h.rowptr[0];
+        if (nnz) {
+            HM_CUDA(cudaMemcpyAsync(c->feat.as<uint32_t>() + t_nnz, h.feature + base, (size_t)nnz * 4, cudaMemcpyHostToDevice, u->copy));
+            if (h.value) HM_CUDA(cudaMemcpyAsync(c->val.as<float>() + t_nnz, h.value + base, (size_t)nnz * 4, cudaMemcpyHostToDevice, u->copy));
+            else HM_TRY(launch_fill_u32(u->Lc, c->val.as<uint32_t>() + t_nnz, nnz, 0x3f800000u));   // index-only features: 1.0f
+        }
+    } else {
+        const int64_t qb = h.q_rowptr[0], cb = h.c_rowptr[0];
+        const int64_t qn = h.q_rowptr[n] - qb, cn = h.c_rowptr[n] - cb;
+        if (qn < 0 || cn < 0) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "rowptr is not non-decreasing");
+        const int64_t hr = std::max(n, u->hint_rows);
+        HM_TRY(c->sq_rp.reserve((size_t)(hr + 1) * 8));
+        HM_TRY(c->sc_rp.reserve((size_t)(hr + 1) * 8));
+        HM_TRY(c->sq_feat.reserve((size_t)std::max<int64_t>(std::max(qn, u->hint_q), 1) * 4));
+        HM_TRY(c->sq_val.reserve((size_t)std::max<int64_t>(std::max(qn, u->hint_q), 1) * 4));
+        HM_TRY(c->sc_feat.reserve((size_t)std::max<int64_t>(std::max(cn, u->hint_c), 1) * 4));
+        HM_CUDA(cudaMemcpyAsync(c->sq_rp.p, h.q_rowptr, (size_t)(n + 1) * 8, cudaMemcpyHostToDevice, u->copy));
+        HM_CUDA(cudaMemcpyAsync(c->sc_rp.p, h.c_rowptr, (size_t)(n + 1) * 8, cudaMemcpyHostToDevice, u->copy));
+        if (qn) {
+            HM_CUDA(cudaMemcpyAsync(c->sq_feat.p, h.q_feature + qb, (size_t)qn * 4, cudaMemcpyHostToDevice, u->copy));
+            HM_CUDA(cudaMemcpyAsync(c->sq_val.p, h.q_value + qb, (size_t)qn * 4, cudaMemcpyHostToDevice, u->copy));
+        }
+        if (cn) HM_CUDA(cudaMemcpyAsync(c->sc_feat.p, h.c_feature + cb, (size_t)cn * 4, cudaMemcpyHostToDevice, u->copy));
+        const int grid = (int)std::min<int64_t>((n + 7) / 8, (int64_t)kNumSMs * 8);
+        merge_split_kernel<<<grid, 256, 0, u->copy>>>(n, c->sq_rp.as<int64_t>(), qb, c->sc_rp.as<int64_t>(), cb,
+                                                      c->sq_feat.as<uint32_t>(), c->sq_val.as<float>(),
+                                                      c->sc_feat.as<uint32_t>(), t_nnz, c->rowptr.as<int64_t>() + t_rows,
+                                                      c->feat.as<uint32_t>(), c->val.as<float>());
+        u->Lc.launches++;
+        HM_CUDA(cudaGetLastError());
     }
-    HM_CUDA(cudaMemcpyAsync(c->label.as<float>() + t_rows, label, (size_t)n * 4, cudaMemcpyHostToDevice, u->copy));
+    HM_CUDA(cudaMemcpyAsync(c->label.as<float>() + t_rows, h.label, (size_t)n * 4, cudaMemcpyHostToDevice, u->copy));
 
     // rowptr of the new chunk, rebased on the host into pinned staging
     const int turn = u->stage_turn;
@@ -471,10 +545,19 @@ hm_status process_slice(hm_udtf *u, int64_t n, const int64_t *rowptr, const int3
     }
     int64_t *st = u->h_stage[turn];
     for (int64_t i = 0; i < t_rows; i++) st[i] = u->tail_rp[i];
-    for (int64_t i = 0; i <= n; i++) {
-        const int64_t v = rowptr[i] - base;
-        if (i > 0 && rowptr[i] < rowptr[i - 1]) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "rowptr decreases at row %lld", (long long)i);
-        st[t_rows + i] = t_nnz + v;
+    if (!h.split) {
+        const int64_t base = h.rowptr[0];
+        for (int64_t i = 0; i <= n; i++) {
+            if (i > 0 && h.rowptr[i] < h.rowptr[i - 1]) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "rowptr decreases at row %lld", (long long)i);
+            st[t_rows + i] = t_nnz + (h.rowptr[i] - base);
+        }
+    } else {
+        const int64_t qb = h.q_rowptr[0], cb = h.c_rowptr[0];
+        for (int64_t i = 0; i <= n; i++) {
+            if (i > 0 && (h.q_rowptr[i] < h.q_rowptr[i - 1] || h.c_rowptr[i] < h.c_rowptr[i - 1]))
+                HM_FAIL(HM_ERR_INVALID_ARGUMENT, "rowptr decreases at row %lld", (long long)i);
+            st[t_rows + i] = t_nnz + (h.q_rowptr[i] - qb) + (h.c_rowptr[i] - cb);
+        }
     }
 
     // carried rows: device-to-device, also on the copy stream.  Their source is input data that this very
@@ -495,13 +578,16 @@ hm_status process_slice(hm_udtf *u, int64_t n, const int64_t *rowptr, const int3
         HM_TRY(retire_chunk(u, o, u->cfg.iters > 1 && o->rows > 0));
         if (u->cfg.iters > 1 && o->rows == 0) { /* nothing trained from it: already pooled */ }
     }
-    // the row pointer last: it is the only copy that needs the host loop above
-    HM_CUDA(cudaMemcpyAsync(c->rowptr.p, st, (size_t)(rows + 1) * 8, cudaMemcpyHostToDevice, u->copy));
+    // the row pointer last: it is the only copy that needs the host loop above (split rows: the merge
+    // kernel has written the new rows' part, only the carried rows' part is copied)
+    const int64_t rp_copy = h.split ? t_rows : rows + 1;
+    if (rp_copy) HM_CUDA(cudaMemcpyAsync(c->rowptr.p, st, (size_t)rp_copy * 8, cudaMemcpyHostToDevice, u->copy));
     if (!u->stage_ev[turn]) HM_CUDA(cudaEventCreateWithFlags(&u->stage_ev[turn], cudaEventDisableTiming));
     HM_CUDA(cudaEventRecord(u->stage_ev[turn], u->copy));
     HM_CUDA(cudaStreamWaitEvent(u->compute, u->stage_ev[turn], 0));
     HM_CUDA(cudaStreamWaitEvent(u->sorter, u->stage_ev[turn], 0));     // the sort needs the rows, not the model
-    u->stats.h2d_bytes += (rows + 1) * 8 + nnz * (value ? 8 : 4) + n * 4;
+    if (!h.split) u->stats.h2d_bytes += (rows + 1) * 8 + nnz * (h.value ? 8 : 4) + n * 4;
+    else u->stats.h2d_bytes += (n + 1) * 16 + (h.q_rowptr[n] - h.q_rowptr[0]) * 8 + (h.c_rowptr[n] - h.c_rowptr[0]) * 4 + n * 4 + t_rows * 8;
 
     // full mini-batches
     const int64_t n_mb = rows / B;
@@ -518,6 +604,39 @@ hm_status process_slice(hm_udtf *u, int64_t n, const int64_t *rowptr, const int3
     for (int64_t i = 0; i <= rows - train; i++) u->tail_rp[(size_t)i] = st[train + i] - st[train];
     if (rows == train) u->tail_rp.clear();
     return HM_OK;
+}
+
+// The slices of one process() call (see hm_udtf_process for the schedule).
+hm_status process_host_rows(hm_udtf *u, const HostRows &all)
+{
+    const int64_t n_rows = all.n;
+    const int64_t B = u->cfg.mini_batch;
+    const int64_t smallest = std::max<int64_t>(kMinSliceRows / B * B, 2 * B);
+    const int64_t largest = std::max<int64_t>(kSliceRows / B * B, smallest);
+    int64_t ramp = smallest;
+    {
+        const int64_t big = std::min(n_rows, largest);
+        const double frac = (double)(big + B) / (double)n_rows * 1.05;
+        u->hint_rows = big + B;
+        u->hint_elems = (int64_t)((double)all.nnz() * frac) + 1024;
+        u->hint_q = all.split ? (int64_t)((double)(all.q_rowptr[n_rows] - all.q_rowptr[0]) * frac) + 1024 : 0;
+        u->hint_c = all.split ? (int64_t)((double)(all.c_rowptr[n_rows] - all.c_rowptr[0]) * frac) + 1024 : 0;
+    }
+    hm_status st = HM_OK;
+    for (int64_t r = 0; r < n_rows && st == HM_OK;) {
+        int64_t slice = ramp;
+        while (slice > smallest && n_rows - r <= 2 * slice) slice = std::max<int64_t>((slice / 2) / B * B, smallest);
+        HostRows h = all;
+        h.n = std::min(slice, n_rows - r);
+        if (all.split) { h.q_rowptr = all.q_rowptr + r; h.c_rowptr = all.c_rowptr + r; }
+        else h.rowptr = all.rowptr + r;
+        h.label = all.label + r;
+        st = process_slice(u, h);
+        r += h.n;
+        ramp = largest;
+    }
+    u->hint_rows = 0; u->hint_elems = 0; u->hint_q = 0; u->hint_c = 0;
+    return st;
 }
 
 hm_status check_bad(hm_udtf *u)
@@ -729,26 +848,29 @@ hm_status hm_udtf_process(hm_udtf *u, int64_t n_rows, const int64_t *rowptr, con
     // one small slice first (short fill), then slices of kSliceRows (copies of >= 160 MB reach the full
     // 55 GB/s; equal sizes keep the two stages in step when training is as slow as the bus, as for train_fm),
     // halving towards the end of the call (short drain: matters when the bus is the bottleneck).
-    const int64_t B = u->cfg.mini_batch;
-    const int64_t smallest = std::max<int64_t>(kMinSliceRows / B * B, 2 * B);
-    const int64_t largest = std::max<int64_t>(kSliceRows / B * B, smallest);
-    int64_t ramp = smallest;
-    {
-        const int64_t big = std::min(n_rows, largest);
-        const double per_row = (double)(rowptr[n_rows] - rowptr[0]) / (double)n_rows;
-        u->hint_rows = big + B;
-        u->hint_elems = (int64_t)((double)(big + B) * per_row * 1.05) + 1024;
-    }
-    for (int64_t r = 0; r < n_rows;) {
-        int64_t slice = ramp;
-        while (slice > smallest && n_rows - r <= 2 * slice) slice = std::max<int64_t>((slice / 2) / B * B, smallest);
-        const int64_t n = std::min(slice, n_rows - r);
-        HM_TRY(process_slice(u, n, rowptr + r, feature, value, label + r));
-        r += n;
-        ramp = largest;
-    }
-    u->hint_rows = 0; u->hint_elems = 0;
-    return HM_OK;
+    HostRows all;
+    all.n = n_rows; all.rowptr = rowptr; all.feature = feature; all.value = value; all.label = label;
+    return process_host_rows(u, all);
+}
+
+hm_status hm_udtf_process_split(hm_udtf *u, int64_t n_rows, const int64_t *q_rowptr, const int32_t *q_feature,
+                                const float *q_value, const int64_t *c_rowptr, const int32_t *c_feature,
+                                const float *label)
+{
+    if (!u) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "NULL learner");
+    if (u->closed) HM_FAIL(HM_ERR_STATE, "process() after close()");
+    if (u->device_rows_short) HM_FAIL(HM_ERR_STATE, "process() after a device call that ended on a short mini-batch");
+    if (n_rows < 0 || (n_rows > 0 && (!q_rowptr || !c_rowptr || !label)))
+        HM_FAIL(HM_ERR_INVALID_ARGUMENT, "NULL buffer passed to process_split()");
+    if (n_rows == 0) return HM_OK;
+    if (q_rowptr[n_rows] > q_rowptr[0] && (!q_feature || !q_value)) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "NULL quantitative feature/value buffer");
+    if (c_rowptr[n_rows] > c_rowptr[0] && !c_feature) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "NULL index-only feature buffer");
+    DeviceGuard g(u->device);
+    HostRows all;
+    all.n = n_rows; all.split = true;
+    all.q_rowptr = q_rowptr; all.q_feature = q_feature; all.q_value = q_value;
+    all.c_rowptr = c_rowptr; all.c_feature = c_feature; all.label = label;
+    return process_host_rows(u, all);
 }
 
 hm_status hm_udtf_process_strings(hm_udtf *u, int64_t n_rows, const int64_t *rowptr, const uint8_t *bytes,

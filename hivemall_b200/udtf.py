@@ -204,6 +204,32 @@ class UDTF:
         """process() from raw HOST addresses (pinned buffers from host_alloc); value None/0 = all 1.0."""
         check(self._lib.hm_udtf_process(self._h, n_rows, _ptr(rowptr), _ptr(feature), _ptr(value), _ptr(label)))
 
+    def process_split(self, q_rowptr, q_feature, q_value, c_rowptr, c_feature, label) -> None:
+        """process() of many rows whose features come in two groups: quantitative (index, value) and
+        index-only (value 1.0).  Row i = its quantitative elements, then its index-only ones.  numpy arrays
+        (kept alive until sync()/close()) or raw host addresses with `label` giving the row count via
+        process_split_pointers."""
+        q_rowptr = np.ascontiguousarray(q_rowptr, dtype=np.int64)
+        c_rowptr = np.ascontiguousarray(c_rowptr, dtype=np.int64)
+        q_feature = np.ascontiguousarray(q_feature, dtype=np.int32)
+        q_value = np.ascontiguousarray(q_value, dtype=np.float32)
+        c_feature = np.ascontiguousarray(c_feature, dtype=np.int32)
+        label = np.ascontiguousarray(label, dtype=np.float32)
+        n = len(label)
+        if len(q_rowptr) != n + 1 or len(c_rowptr) != n + 1:
+            raise UDFArgumentError(1, f"row pointers must have {n + 1} entries for {n} rows")
+        if n and (q_rowptr[-1] > len(q_feature) or q_rowptr[-1] > len(q_value) or c_rowptr[-1] > len(c_feature)):
+            raise UDFArgumentError(1, "a row pointer points past the end of its feature/value array")
+        self._keep.append((q_rowptr, q_feature, q_value, c_rowptr, c_feature, label))
+        check(self._lib.hm_udtf_process_split(self._h, n, _ptr(q_rowptr), _ptr(q_feature), _ptr(q_value),
+                                              _ptr(c_rowptr), _ptr(c_feature), _ptr(label)))
+
+    def process_split_pointers(self, n_rows: int, q_rowptr: int, q_feature: int, q_value: int, c_rowptr: int,
+                               c_feature: int, label: int) -> None:
+        """process_split() from raw HOST addresses (pinned buffers from host_alloc)."""
+        check(self._lib.hm_udtf_process_split(self._h, n_rows, _ptr(q_rowptr), _ptr(q_feature), _ptr(q_value),
+                                              _ptr(c_rowptr), _ptr(c_feature), _ptr(label)))
+
     def process_device(self, n_rows: int, nnz: int, rowptr, feature, value, label) -> None:
         """process() of rows already in device memory (torch CUDA tensors or raw
         addresses): int64 rowptr, int32 feature, float32 value/label."""

@@ -137,6 +137,17 @@ hm_status hm_udtf_create_from_config(const hm_config *cfg, int device, hm_udtf *
  * Copies host->device inside the call (asynchronously when the buffers are pinned). */
 hm_status hm_udtf_process(hm_udtf *u, int64_t n_rows, const int64_t *rowptr,
                           const int32_t *feature, const float *value, const float *label);
+/* process() for rows whose features arrive in two groups, the way Hivemall's feature
+ * engineering produces them: a quantitative group (index and value, as from
+ * quantitative_features) and an index-only group (value 1.0 implied, as from
+ * categorical_features).  Row i is its quantitative elements
+ * q_feature/q_value[q_rowptr[i] .. q_rowptr[i+1]) followed by its index-only elements
+ * c_feature[c_rowptr[i] .. c_rowptr[i+1]); the two groups are merged into one CSR on the
+ * device, so the implied 1.0s never cross the bus.  Otherwise exactly hm_udtf_process
+ * (same mini-batch boundaries, same result as pushing the merged rows). */
+hm_status hm_udtf_process_split(hm_udtf *u, int64_t n_rows,
+                                const int64_t *q_rowptr, const int32_t *q_feature, const float *q_value,
+                                const int64_t *c_rowptr, const int32_t *c_feature, const float *label);
 /* process() for rows whose features are still strings ("name:value"); hashes on
  * the GPU with the learner's hash_seed into [0, dims) and then behaves as above.
  * rowptr indexes strings; string s is bytes[offsets[s] .. offsets[s+1]). */

@@ -135,3 +135,48 @@ def test_null_values_mean_one():
     assert np.array_equal(a.array_to_host("w"), b.array_to_host("w"))
     assert b.stats().h2d_bytes < a.stats().h2d_bytes
     a.destroy(); b.destroy()
+
+
+def _split(rp, f, v, rng):
+    """Cut every row of a CSR into a quantitative group (a random-length prefix) and an index-only group (the
+    rest, whose values are forced to 1.0); returns the split arrays and the merged CSR they stand for."""
+    n = len(rp) - 1
+    q_rp, c_rp = np.zeros(n + 1, np.int64), np.zeros(n + 1, np.int64)
+    qf, qv, cf, mv = [], [], [], v.copy()
+    for i in range(n):
+        a, b = int(rp[i]), int(rp[i + 1])
+        k = int(rng.integers(0, b - a + 1))           # 0 = no quantitative element, b - a = no index-only element
+        qf.append(f[a:a + k]); qv.append(v[a:a + k]); cf.append(f[a + k:b])
+        mv[a + k:b] = 1.0
+        q_rp[i + 1] = q_rp[i] + k
+        c_rp[i + 1] = c_rp[i] + (b - a - k)
+    cat = lambda xs, dt: np.concatenate(xs).astype(dt) if xs else np.zeros(0, dt)
+    return q_rp, cat(qf, np.int32), cat(qv, np.float32), c_rp, cat(cf, np.int32), mv
+
+
+@pytest.mark.parametrize("fn,opts", [
+    ("train_classifier", f"-opt ftrl -mini_batch 700 -dims {1 << 16}"),
+    ("train_regressor", f"-loss squared -opt adam -mini_batch 64 -dims 5000"),
+    ("train_fm", f"-factors 8 -classification -opt adagrad -mini_batch 512 -dims 5000"),
+])
+def test_split_rows_equal_merged_rows(fn, opts):
+    """hm_udtf_process_split: quantitative + index-only groups merged on the device == the merged CSR pushed
+    through hm_udtf_process, bit for bit, whatever the push boundaries (rows with an empty group included)."""
+    dims = 5000 if "5000" in opts else 1 << 16
+    rng = np.random.default_rng(7)
+    data = synth.ragged(4000, dims, 30, seed=41, regression=(fn == "train_regressor"))
+    rp, f, v, y = data.numpy()
+    q_rp, qf, qv, c_rp, cf, mv = _split(rp, f, v, rng)
+    a = hm.UDTF(opts, 0, function_name=fn)
+    a.process_batch(rp, f, mv, y)
+    a.close()
+    b = hm.UDTF(opts, 0, function_name=fn)
+    cuts = [0, 1, 1234, 1235, 3000, 4000]
+    for lo, hi in zip(cuts, cuts[1:]):
+        b.process_split(q_rp[lo:hi + 1], qf, qv, c_rp[lo:hi + 1], cf, y[lo:hi])
+    b.close()
+    assert a.step == b.step
+    for name in (("w", "state") if fn != "train_fm" else ("w0", "w", "V", "gV")):
+        assert np.array_equal(a.array_to_host(name), b.array_to_host(name)), name
+    assert b.stats().h2d_bytes < a.stats().h2d_bytes
+    a.destroy(); b.destroy()
