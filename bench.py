@@ -93,6 +93,8 @@ def parse_args():
     ap.add_argument("--cpu-sample-rows", type=int, default=0, help="0 = sized for ~15 s")
     ap.add_argument("--workload", default="ftrl", choices=sorted(WORKLOADS))
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--e2e-format", default="split", choices=["split", "csr"],
+                    help="host format of the end-to-end arm for Criteo-shaped rows")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-numa", action="store_true", help="do not bind ranks to their GPU's NUMA node (N > 1)")
     return ap.parse_args()
@@ -386,30 +388,41 @@ def main():
     pipeline_bytes = sum(v["bytes"] for v in kt.values()) / K
     roofline["pipeline_GBps"] = pipeline_bytes / (ms / K * 1e-3) / 1e9
 
-    # ---- end-to-end arm: host buffers through hm_udtf_process ----------------------
-    e2e = None
-    if not args.no_e2e:
+    # ---- end-to-end arm: host buffers through the C-ABI --------------------------------
+    # Formats: "csr" = hm_udtf_process with a value per element; "index_only" = hm_udtf_process(value = NULL)
+    # for rows whose values are all 1.0 (KDD12-shaped); "split" = hm_udtf_process_split for Criteo-shaped rows
+    # (13 quantitative columns with values + 26 index-only columns), merged on the device: the same rows in
+    # the same element order, without the implied 1.0s on the bus.
+    def pin(t):
+        addr, view = hm.host_alloc(t.numel() * t.element_size())
+        pinned = torch.frombuffer(view, dtype=t.dtype)
+        pinned.copy_(t)
+        return addr, pinned
+
+    def run_e2e(fmt):
         n_host = min(n_blocks, 4)
-        index_only = wl["gen"] == "kdd12"      # KDD12-shaped rows are categorical: hm_udtf_process(value = NULL)
-        host = []
+        n_q = 13
+        host, addrs = [], []
         for b in range(n_host):
             rowptr, feature, value, label = blocks[b]
-            arrs = []
-            for t in (rowptr, feature, value, label):
-                if t is value and index_only:      # every value is 1.0: the values never cross the bus
-                    arrs.append((None, None))
-                    continue
-                addr, view = hm.host_alloc(t.numel() * t.element_size())
-                pinned = torch.frombuffer(view, dtype=t.dtype)
-                pinned.copy_(t)
-                arrs.append((addr, pinned))
+            if fmt == "split":
+                f2, v2 = feature.view(rps, nnz_per_row), value.view(rps, nnz_per_row)
+                steps = torch.arange(rps + 1, device=dev, dtype=torch.int64)
+                parts = [steps * n_q, f2[:, :n_q].contiguous().view(-1), v2[:, :n_q].contiguous().view(-1),
+                         steps * (nnz_per_row - n_q), f2[:, n_q:].contiguous().view(-1), label]
+            elif fmt == "index_only":
+                parts = [rowptr, feature, label]
+            else:
+                parts = [rowptr, feature, value, label]
+            arrs = [pin(t) for t in parts]
+            del parts
+            addrs += [a for a, _ in arrs]
             host.append(arrs)
         torch.cuda.synchronize()
         v = hm.UDTF(options, local_rank, function_name=fn)
         mixer2 = mix.ReplicaMixer(v, world) if world > 1 else None
         margins = np.empty(MINI_BATCH, dtype=np.float32)
         losses = []
-
         pending = []     # (margins, labels) of the previous step: its loss is worked out on the host while the
                          # device is busy with the current one (the blocking D2H read itself stays in every step)
 
@@ -422,8 +435,14 @@ def main():
                     losses.append(float(np.mean(np.logaddexp(0.0, -(t * 2 - 1) * m))))
 
         def step_host(i):
-            (rp, _), (ft, _), (vl, _), (lb, lbt) = host[i % n_host]
-            v.process_pointers(rps, rp, ft, vl, lb)
+            arrs = host[i % n_host]
+            lbt = arrs[-1][1]
+            if fmt == "split":
+                v.process_split_pointers(rps, *[a for a, _ in arrs])
+            elif fmt == "index_only":
+                v.process_pointers(rps, arrs[0][0], arrs[1][0], None, arrs[2][0])
+            else:
+                v.process_pointers(rps, *[a for a, _ in arrs])
             if mixer2 and (i + 1) % mix_every == 0:
                 mixer2.mix()
             host_loss()
@@ -444,19 +463,36 @@ def main():
             tdt = torch.tensor([dt], device=dev)
             dist.all_reduce(tdt, op=dist.ReduceOp.MAX)
             dt = float(tdt)
-        h2d = (rps + 1) * 8 + nnz_step * (4 if index_only else 8) + rps * 4
-        e2e = {"value": world * rps * K / dt, "unit": "examples/s", "h2d_bytes_per_step": h2d,
-               "d2h_bytes_per_step": MINI_BATCH * 4, "ms_per_step": dt / K * 1e3,
-               "last_minibatch_loss": losses[-1], "loss": "squared/2" if wl["regression"] else "logloss", "pcie_GBps": h2d * K / dt / 1e9,
+        if fmt == "split":
+            h2d = 2 * (rps + 1) * 8 + rps * n_q * 8 + rps * (nnz_per_row - n_q) * 4 + rps * 4
+        else:
+            h2d = (rps + 1) * 8 + nnz_step * (4 if fmt == "index_only" else 8) + rps * 4
+        v.destroy()
+        for a in addrs:
+            hm.host_free(a)
+        return {"value": world * rps * K / dt, "ms_per_step": dt / K * 1e3, "h2d_bytes_per_step": h2d,
+                "pcie_GBps": h2d * K / dt / 1e9, "last_minibatch_loss": losses[-1]}
+
+    e2e = None
+    if not args.no_e2e:
+        fmt = "index_only" if wl["gen"] == "kdd12" else ("csr" if args.e2e_format == "csr" else "split")
+        main_run = run_e2e(fmt)
+        e2e = {"value": main_run["value"], "unit": "examples/s", "h2d_bytes_per_step": main_run["h2d_bytes_per_step"],
+               "d2h_bytes_per_step": MINI_BATCH * 4, "ms_per_step": main_run["ms_per_step"],
+               "last_minibatch_loss": main_run["last_minibatch_loss"],
+               "loss": "squared/2" if wl["regression"] else "logloss", "pcie_GBps": main_run["pcie_GBps"],
                "timing": "host wall clock around K calls, each ending in a blocking D2H read",
                "host_binding": (f"rank bound to {len(host_cpus)} CPUs next to its GPU (NVML affinity)" if host_cpus
                                 else "none"),
-               "values": "NULL (index-only features, 1.0 implied)" if index_only else "f32 per element"}
-        v.destroy()
-        for arrs in host:
-            for addr, _ in arrs:
-                if addr is not None:
-                    hm.host_free(addr)
+               "format": {"split": "hm_udtf_process_split: 13 quantitative columns (index, value) + 26 index-only "
+                                   "columns per row, merged on the device (the implied 1.0s stay off the bus)",
+                          "index_only": "hm_udtf_process with value = NULL (every value is 1.0)",
+                          "csr": "hm_udtf_process: plain CSR, one f32 value per element"}[fmt]}
+        if fmt == "split":      # the same rows as plain CSR, for comparison
+            plain = run_e2e("csr")
+            e2e["plain_csr"] = {"value": plain["value"], "ms_per_step": plain["ms_per_step"],
+                                "h2d_bytes_per_step": plain["h2d_bytes_per_step"], "pcie_GBps": plain["pcie_GBps"],
+                                "last_minibatch_loss": plain["last_minibatch_loss"]}
 
     # ---- CPU baseline (rank 0, N=1 only) -------------------------------------------
     cpu = None
