@@ -156,7 +156,7 @@ def _split(rp, f, v, rng):
 
 @pytest.mark.parametrize("fn,opts", [
     ("train_classifier", f"-opt ftrl -mini_batch 700 -dims {1 << 16}"),
-    ("train_regressor", f"-loss squared -opt adam -mini_batch 64 -dims 5000"),
+    ("train_regressor", f"-loss squared -opt adam -mini_batch 64 -dims 5000 -iters 2"),
     ("train_fm", f"-factors 8 -classification -opt adagrad -mini_batch 512 -dims 5000"),
 ])
 def test_split_rows_equal_merged_rows(fn, opts):
