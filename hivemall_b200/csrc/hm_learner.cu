@@ -684,9 +684,15 @@ hm_status create_impl(const hm_config &cfg, int device, hm_udtf **out)
     u->device = device;
     std::memset(&u->stats, 0, sizeof(u->stats));
     hm_status s = [&]() -> hm_status {
-        HM_CUDA(cudaStreamCreateWithFlags(&u->compute, cudaStreamNonBlocking));
-        HM_CUDA(cudaStreamCreateWithFlags(&u->copy, cudaStreamNonBlocking));
-        HM_CUDA(cudaStreamCreateWithFlags(&u->sorter, cudaStreamNonBlocking));
+        {
+            // the training stream's short kernels go first whenever both streams have CTAs to place
+            // (measured: +0.35 %; the sort above training: -1.7 %)
+            int lo = 0, hi = 0;
+            HM_CUDA(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+            HM_CUDA(cudaStreamCreateWithPriority(&u->compute, cudaStreamNonBlocking, hi));
+            HM_CUDA(cudaStreamCreateWithFlags(&u->copy, cudaStreamNonBlocking));
+            HM_CUDA(cudaStreamCreateWithPriority(&u->sorter, cudaStreamNonBlocking, lo));
+        }
         u->L.stream = u->compute;
         u->Ls.stream = u->sorter;
         u->Lc.stream = u->copy;
