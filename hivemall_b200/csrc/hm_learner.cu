@@ -72,7 +72,15 @@ void Launcher::release()
 
 namespace {
 
-constexpr int64_t kBlockElemCap = (int64_t)1 << 26;   // elements sorted per launch set
+constexpr int64_t kBlockElemCap = (int64_t)1 << 26;   // hard limit of elements sorted per launch set (scratch size)
+// Elements per block aimed at.  The sort of block k+1 and the training of block k share the SMs by taking
+// turns, and they interleave better in short turns: measured on configs[1] (64 mini-batches of 2.56 M elements
+// per call): 67 M (26 mini-batches per block) 489 M examples/s, 33 M 500 M, 26 M 505 M, 21 M (8 per block) 513 M,
+// 16.8 M 509 M, 8.4 M 457 M.
+#ifndef HM_BLOCK_TARGET
+#define HM_BLOCK_TARGET 21000000
+#endif
+constexpr int64_t kBlockElemTarget = HM_BLOCK_TARGET;
 // Host rows copied per H2D slice: the first slices of a call are kSliceRows long, the last ones shrink
 // to kMinSliceRows (see hm_udtf_process).  With one fixed size, measured on B200 (bench.py e2e,
 // mini-batch 65536): 2^21 -> 127 M rows/s, 2^20 -> 142, 2^19 -> 151, 2^18 -> 154; with the descending
@@ -316,10 +324,19 @@ hm_status train_rows(hm_udtf *u, const Chunk &c, int64_t row0, int64_t n_rows, c
     a.cfg = u->cfg; a.rec = u->rec; a.rec_width = u->rec_width; a.wv = weight_view(u);
     struct Plan { int64_t m0, m1, row0, rows, nnz; int n_segs; };
     std::vector<Plan> plan;
+    // Blocks of about kBlockElemTarget elements, evenly sized: the call's elements are cut into
+    // ceil(total / target) blocks at the mini-batch boundaries nearest to equal shares (never more than
+    // kMaxSegs mini-batches or kBlockElemCap elements, at least one mini-batch).
+    const int64_t total_elems = mb_abs[n_mb] - mb_abs[0];
+    const int64_t n_blocks = std::max<int64_t>(1, (total_elems + kBlockElemTarget - 1) / kBlockElemTarget);
+    int64_t block_no = 0;
     for (int64_t m0 = 0; m0 < n_mb;) {
-        // greedy block: <= kMaxSegs mini-batches and <= kBlockElemCap elements (at least one)
+        block_no++;
+        const int64_t share_end = mb_abs[0] + (int64_t)((double)total_elems * (double)block_no / (double)n_blocks);
         int64_t m1 = m0 + 1;
-        while (m1 < n_mb && m1 - m0 < kMaxSegs && mb_abs[m1 + 1] - mb_abs[m0] <= kBlockElemCap) m1++;
+        while (m1 < n_mb && m1 - m0 < kMaxSegs && mb_abs[m1 + 1] - mb_abs[m0] <= kBlockElemCap &&
+               (block_no >= n_blocks || mb_abs[m1 + 1] <= share_end + (mb_abs[m1 + 1] - mb_abs[m1]) / 2))
+            m1++;
         Plan p;
         p.m0 = m0; p.m1 = m1; p.n_segs = (int)(m1 - m0);
         p.row0 = row0 + m0 * B;
