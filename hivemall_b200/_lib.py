@@ -84,6 +84,7 @@ SIGNATURES = {
     "hm_udtf_predict": (C.c_int, [_P, C.c_int64, _P, _P, _P, _P]),
     "hm_udtf_predict_device": (C.c_int, [_P, C.c_int64, _P, _P, _P, _P]),
     "hm_udtf_last_margins": (C.c_int, [_P, _P, C.c_int64, C.POINTER(C.c_int64)]),
+    "hm_udtf_dense_columns": (C.c_int, [_P, _P, C.c_int32, C.POINTER(C.c_int32)]),
     "hm_model_table_noalloc": (C.c_int, [_P, C.c_int64, _P, _P, C.c_int64, _P, _P]),
     "hm_udtf_stats": (C.c_int, [_P, C.POINTER(HmStats)]),
     "hm_udtf_set_profiling": (C.c_int, [_P, C.c_int]),

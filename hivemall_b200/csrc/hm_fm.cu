@@ -21,6 +21,7 @@
 // With k = 16 and AdaGrad a feature's factor record is exactly one 128-byte line.
 #include "hm_internal.h"
 #include <algorithm>
+#include <atomic>
 
 namespace hm {
 
@@ -723,7 +724,7 @@ __global__ void fm_gather_vif_kernel(const float *__restrict__ vrec, int vw, int
 
 int fm_grid(int64_t ctas_wanted, int per_sm)
 {
-    const int64_t cap = (int64_t)kNumSMs * per_sm;
+    const int64_t cap = (int64_t)num_sms() * per_sm;
     if (ctas_wanted < 1) ctas_wanted = 1;
     return (int)(ctas_wanted < cap ? ctas_wanted : cap);
 }
@@ -786,12 +787,12 @@ hm_status launch_fm_update(Launcher &L, const FmArgs &a, const StepScalars &sc, 
                            const float *d_dloss, const float *d_stab, int64_t nnz)
 {
     // > 48 KB of dynamic shared memory needs opting in, once per device
-    static bool attr_set[64] = {false};
+    static std::atomic<bool> attr_set[64];
     int dev = 0;
     HM_CUDA(cudaGetDevice(&dev));
-    if (dev < 0 || dev >= 64 || !attr_set[dev]) {
+    if (dev < 0 || dev >= 64 || !attr_set[dev].load(std::memory_order_acquire)) {
         HM_CUDA(cudaFuncSetAttribute(fm_update_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kFmSmem));
-        if (dev >= 0 && dev < 64) attr_set[dev] = true;
+        if (dev >= 0 && dev < 64) attr_set[dev].store(true, std::memory_order_release);
     }
     const int n_chunks = (int)std::max<int64_t>((nnz + kFmChunk - 1) / kFmChunk, 1);
     if (n_chunks > fs.cap_chunks) HM_FAIL(HM_ERR_STATE, "fm scratch too small");

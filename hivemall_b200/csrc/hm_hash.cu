@@ -165,7 +165,7 @@ hash_kernel(const uint8_t *__restrict__ bytes, const int64_t *__restrict__ offse
 int hash_grid(int64_t n)
 {
     int64_t tiles = (n + kHashThreads - 1) / kHashThreads;
-    int64_t cap = (int64_t)kNumSMs * 4;
+    int64_t cap = (int64_t)num_sms() * 4;
     return (int)(tiles < 1 ? 1 : (tiles < cap ? tiles : cap));
 }
 
@@ -183,10 +183,10 @@ hm_status launch_mhash(Launcher &L, const uint8_t *d_bytes, const int64_t *d_off
 }
 
 hm_status launch_feature_hashing(Launcher &L, const uint8_t *d_bytes, const int64_t *d_offsets, int64_t n,
-                                 uint32_t seed, int32_t num_features, int32_t *d_index, float *d_value)
+                                 uint32_t seed, int32_t num_features, int32_t *d_index, float *d_value, double alg_bytes)
 {
     if (n == 0) return HM_OK;
-    HM_LAUNCH(L, K_HASH, 0.0,
+    HM_LAUNCH(L, K_HASH, alg_bytes,
               (hash_kernel<1><<<hash_grid(n), kHashThreads, 0, L.stream>>>(d_bytes, d_offsets, n, seed, num_features,
                                                                            d_index, d_value)));
     HM_CUDA(cudaGetLastError());

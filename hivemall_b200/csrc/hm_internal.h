@@ -45,7 +45,23 @@ struct Launcher {
 
 #define HM_LAUNCH(L, id, alg_bytes, ...) do { (L).begin((id), (alg_bytes)); __VA_ARGS__; (L).end(id); } while (0)
 
-constexpr int kNumSMs = 148;
+// SMs of the current device (cudaDevAttrMultiProcessorCount, cached per device); grids of the
+// persistent kernels are sized in multiples of it.
+int num_sms();
+
+// ---- dense prefix columns (hm_sort.cu: dense_check_kernel) -------------------------
+// Feature engineering puts the quantitative features ("name:value" with a fixed name) at the
+// front of every row: position i of every row then holds the same feature.  Such a column needs
+// no sort -- its gradient is a plain column sum -- and no gather.  Per ingest block the check
+// kernel proves, for up to 32 leading positions: every row of the block has the position, it
+// holds the same in-range feature in every row, and that feature occurs nowhere else in the
+// block (so skipping it in the sort by KEY is the same as skipping it by position).
+struct DenseInfo {
+    uint32_t mask;        // bit i: position i is a dense column of this block
+    uint32_t count;       // popcount(mask)
+    uint32_t key[32];     // feature of position i (valid where the bit is set)
+    uint32_t noteq, collide, ticket, pad;   // work area of the check kernel (left zeroed)
+};
 
 // ---- segmented radix sort (hm_sort.cu) ----------------------------------------
 constexpr int kMaxSegs = 256;          // mini-batches sorted per launch
@@ -57,8 +73,14 @@ struct SortScratch {
     uint32_t *tile_hist = nullptr;     // [seg][digit][tile_in_seg]
     int32_t *tile_row0 = nullptr;      // first row (inside its mini-batch) of every tile
     uint32_t *row_sum = nullptr;       // [seg*256 + digit] (+1)
-    uint32_t *seg_off = nullptr;       // [kMaxSegs+1] element offset of each mini-batch in the block
+    // Two coordinate systems.  in_*: the block's CSR as it lies in the chunk (what the first pass
+    // reads).  seg_*: the SORTED arrays, from which dense-column and out-of-range elements are
+    // gone; written on the device after the first pass's histogram (the host never learns them).
+    uint32_t *in_off = nullptr;        // [kMaxSegs+1] element offset of each mini-batch in the block's CSR
+    uint32_t *in_tile_off = nullptr;   // [kMaxSegs+1]
+    uint32_t *seg_off = nullptr;       // [kMaxSegs+1] element offset of each mini-batch in the sorted arrays
     uint32_t *seg_tile_off = nullptr;  // [kMaxSegs+1]
+    DenseInfo *dense = nullptr;        // dense columns of the block (mask 0: none)
     int64_t cap_elems = 0;
     int64_t cap_tiles = 0;
 };
@@ -67,18 +89,22 @@ void sort_scratch_free(SortScratch &s);
 // Fill seg_off / seg_tile_off for rows [row0, row0+n_rows) split every `mini_batch` rows.
 hm_status launch_seg_prep(Launcher &L, SortScratch &s, const int64_t *d_rowptr, int64_t row0,
                           int64_t n_rows, int64_t n_elems, int32_t mini_batch, int n_segs);
+// Find the dense columns of rows [row0, row0+n_rows) (s.dense); `enable` false: none.
+hm_status launch_dense_check(Launcher &L, SortScratch &s, const int64_t *d_rowptr, int64_t row0, int64_t n_rows,
+                             const uint32_t *d_feature, int64_t n_elems, int64_t dims, bool enable);
 // Stable sort of each segment by the low `key_bits` bits of the feature id.
 // Result: s.key[*out_buf], s.pay[*out_buf] hold (feature, (row, value)) sorted per segment.
 hm_status launch_segmented_sort(Launcher &L, SortScratch &s, const uint32_t *d_feature_block,
                                 const float *d_value_block, const int64_t *d_rowptr, int64_t block_row0,
                                 int64_t block_rows, int32_t mini_batch, int64_t n_elems, int n_segs, int key_bits,
-                                int *out_buf, int ctas_per_sm);
+                                int64_t dims, uint32_t *d_bad, int *out_buf, int ctas_per_sm);
 
 // ---- hashing (hm_hash.cu) -----------------------------------------------------
 hm_status launch_mhash(Launcher &L, const uint8_t *d_bytes, const int64_t *d_offsets, int64_t n,
                        uint32_t seed, int32_t num_features, int32_t *d_out);
 hm_status launch_feature_hashing(Launcher &L, const uint8_t *d_bytes, const int64_t *d_offsets, int64_t n,
-                                 uint32_t seed, int32_t num_features, int32_t *d_index, float *d_value);
+                                 uint32_t seed, int32_t num_features, int32_t *d_index, float *d_value,
+                                 double alg_bytes = 0.0);   // bytes + 8 (offset) + 8 (index, value) per string
 
 // ---- linear learner kernels (hm_linear.cu) ------------------------------------
 struct StepScalars {      // per mini-batch scalars computed on the host in double
@@ -102,23 +128,33 @@ struct LinearArgs {
     int rec_width;        // 1 (SGD: w), 2 (AdaGrad: w, G; FTRL: z, n), 4 (AdaDelta, Adam: w, s1, s2, unused)
     WeightView wv;
 };
+// Dense columns of the block being trained, and where their column sums travel from the forward
+// kernel to the update kernel.  info == NULL: the block was sorted whole (no dense handling).
+struct DenseCols {
+    const DenseInfo *info = nullptr;
+    double *partial = nullptr;    // [32][stride]
+    int stride = 0;
+};
+int linear_forward_grid(int32_t n_rows);
 // margin (per block row) and dloss (per mini-batch row) for rows [row0, row0+n) of the chunk
 hm_status launch_linear_forward(Launcher &L, const LinearArgs &a, const int64_t *d_rowptr, int64_t row0,
                                 int32_t n_rows, int64_t block_row0, const uint32_t *d_feature,
                                 const float *d_value, const float *d_label, float *d_margin,
-                                float *d_dloss, uint32_t *d_bad, int64_t nnz_hint);
+                                float *d_dloss, uint32_t *d_bad, int64_t nnz_hint, const DenseCols &dc);
 // reduce-by-feature over the sorted segment `seg` and apply the optimizer
 struct UpdateScratch {
     void *boundary = nullptr;     // per-CTA open-segment summaries
     uint32_t *done_counter = nullptr;
     int grid = 0;
+    double *dense_partial = nullptr;   // see DenseCols
+    int dense_stride = 0;
 };
 hm_status update_scratch_reserve(UpdateScratch &u);
 void update_scratch_free(UpdateScratch &u);
 hm_status launch_linear_update(Launcher &L, const LinearArgs &a, const StepScalars &sc, UpdateScratch &us,
                                const uint32_t *d_sorted_key, const uint2 *d_sorted_pay,
                                const uint32_t *d_seg_off, int seg, int64_t seg_begin, const float *d_dloss,
-                               int64_t nnz_hint);
+                               int64_t nnz_hint, const DenseCols &dc);
 // small mini-batches (<= 1024 rows and <= one update tile of elements): up to 64 consecutive
 // mini-batches of a sorted block trained by one persistent CTA
 bool small_batch_eligible(int32_t mini_batch, int64_t max_mb_elems);

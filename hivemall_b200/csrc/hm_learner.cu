@@ -114,6 +114,7 @@ struct Chunk {
     int64_t rows = 0;                   // rows whose mini-batches are listed in mb_abs
     DevBuf rowptr, feat, val, label;    // owned storage
     DevBuf sq_rp, sc_rp, sq_feat, sq_val, sc_feat;   // split pushes: the two groups as they arrive, merged on the device
+    DevBuf str_bytes, str_off;                       // string pushes: the feature strings as they arrive, hashed on the device
     const int64_t *v_rowptr = nullptr;  // view storage
     const uint32_t *v_feat = nullptr;
     const float *v_val = nullptr, *v_label = nullptr;
@@ -127,6 +128,7 @@ struct Chunk {
     {
         rowptr.release(); feat.release(); val.release(); label.release();
         sq_rp.release(); sc_rp.release(); sq_feat.release(); sq_val.release(); sc_feat.release();
+        str_bytes.release(); str_off.release();
         if (free_ev) cudaEventDestroy(free_ev);
         free_ev = nullptr;
     }
@@ -134,10 +136,13 @@ struct Chunk {
 
 // One slice of host rows: plain CSR (value may be NULL = all ones), or split into a quantitative group
 // (index and value) and an index-only group (value 1.0); row i = its quantitative elements, then its
-// index-only elements.
+// index-only elements; or feature STRINGS ("name:value"), one per element, hashed on the device:
+// rowptr then indexes strings, string s is s_bytes[s_offsets[s] .. s_offsets[s+1]).
 struct HostRows {
     int64_t n = 0;
     const int64_t *rowptr = nullptr; const int32_t *feature = nullptr; const float *value = nullptr;
+    bool strings = false;
+    const uint8_t *s_bytes = nullptr; const int64_t *s_offsets = nullptr;
     bool split = false;
     const int64_t *q_rowptr = nullptr, *c_rowptr = nullptr;
     const int32_t *q_feature = nullptr, *c_feature = nullptr;
@@ -205,7 +210,7 @@ struct hm_udtf {
     int device = 0;
     Launcher L, Ls, Lc;              // compute stream / sort stream / copy stream (fills only)
     cudaEvent_t merged_ev = nullptr;        // split pushes: the merge kernel of the latest slice has run
-    int64_t hint_rows = 0, hint_elems = 0, hint_q = 0, hint_c = 0;   // largest slice of the running process() call: chunk buffers are sized once
+    int64_t hint_rows = 0, hint_elems = 0, hint_q = 0, hint_c = 0, hint_bytes = 0;   // largest slice of the running process() call: chunk buffers are sized once
     cudaStream_t compute = nullptr, copy = nullptr, sorter = nullptr;
     cudaEvent_t sorted_ev[2] = {nullptr, nullptr}, trained_ev[2] = {nullptr, nullptr}, ready_ev = nullptr;
     bool trained_valid[2] = {false, false};
@@ -244,6 +249,7 @@ struct hm_udtf {
     int64_t h_small_cap = 0;
     int64_t last_margin_off = 0, last_margin_n = 0;   // last mini-batch's slice of `margin`
     bool device_rows_short = false;  // a process_device call ended on a short mini-batch
+    bool dense_enabled = true;       // HM_DENSE_COLUMNS=0 in the environment sorts every element (A/B measurements)
     hm_stats stats;
     bool closed = false;
     int64_t model_rows = -1;
@@ -356,15 +362,21 @@ hm_status train_rows(hm_udtf *u, const Chunk &c, int64_t row0, int64_t n_rows, c
         HM_CUDA(cudaStreamWaitEvent(u->sorter, u->ready_ev, 0));
     }
     int out_buf[2] = {0, 0};
+    int64_t call_max_mb = 0;
+    for (int64_t m = 0; m < n_mb; m++) call_max_mb = std::max(call_max_mb, mb_abs[m + 1] - mb_abs[m]);
+    // Dense columns (quantitative features at the front of every row) are taken out of the sort and reduced as
+    // column sums by the forward kernel: linear learners on the two-kernel path only.
+    const bool dense_on = !u->fm && u->dense_enabled && !small_batch_eligible(B, call_max_mb);
     auto enqueue_sort = [&](size_t bi) -> hm_status {
         const Plan &p = plan[bi];
         const int set = (int)((u->sort_turn + bi) & 1);
         // the scratch set is free once the block that used it last has been trained
         if (u->trained_valid[set]) HM_CUDA(cudaStreamWaitEvent(u->sorter, u->trained_ev[set], 0));
         HM_TRY(sort_scratch_reserve(u->sort[set], p.nnz));
+        HM_TRY(launch_dense_check(u->Ls, u->sort[set], c.rp(), p.row0, p.rows, c.ft(), p.nnz, u->cfg.dims, dense_on));
         HM_TRY(launch_seg_prep(u->Ls, u->sort[set], c.rp(), p.row0, p.rows, p.nnz, B, p.n_segs));
         HM_TRY(launch_segmented_sort(u->Ls, u->sort[set], c.ft() + mb_abs[p.m0], c.vl() + mb_abs[p.m0], c.rp(), p.row0,
-                                     p.rows, B, p.nnz, p.n_segs, key_bits, &out_buf[set], 0));
+                                     p.rows, B, p.nnz, p.n_segs, key_bits, u->cfg.dims, u->d_bad, &out_buf[set], 0));
         HM_CUDA(cudaEventRecord(u->sorted_ev[set], u->sorter));
         return HM_OK;
     };
@@ -396,9 +408,9 @@ hm_status train_rows(hm_udtf *u, const Chunk &c, int64_t row0, int64_t n_rows, c
             HM_TRY(fm_scratch_reserve(u->fms, max_mb, u->k));
             HM_TRY(u->stab.reserve((size_t)std::min<int64_t>(p.rows, B) * u->k * sizeof(float)));
         }
-        int64_t max_mb = 0;
-        for (int64_t m = p.m0; m < p.m1; m++) max_mb = std::max(max_mb, mb_abs[m + 1] - mb_abs[m]);
-        if (!u->fm && small_batch_eligible(B, max_mb)) {
+        DenseCols dc;
+        if (dense_on) { dc.info = ss.dense; dc.partial = u->upd.dense_partial; dc.stride = u->upd.dense_stride; }
+        if (!u->fm && small_batch_eligible(B, call_max_mb)) {
             // a few hundred rows per mini-batch: up to 64 mini-batches per launch of one persistent CTA
             for (int s0 = 0; s0 < p.n_segs; s0 += 64) {
                 const int ns = std::min(64, p.n_segs - s0);
@@ -436,9 +448,9 @@ hm_status train_rows(hm_udtf *u, const Chunk &c, int64_t row0, int64_t n_rows, c
                                         u->dloss.as<float>(), u->stab.as<float>(), mnnz));
             } else {
                 HM_TRY(launch_linear_forward(u->L, a, c.rp(), mrow0, mrows, p.row0, c.ft(), c.vl(), c.lb(),
-                                             u->margin.as<float>(), u->dloss.as<float>(), u->d_bad, mnnz));
+                                             u->margin.as<float>(), u->dloss.as<float>(), u->d_bad, mnnz, dc));
                 HM_TRY(launch_linear_update(u->L, a, sc, u->upd, ss.key[buf], ss.pay[buf], ss.seg_off, s,
-                                            mb_abs[p.m0 + s] - mb_abs[p.m0], u->dloss.as<float>(), mnnz));
+                                            mb_abs[p.m0 + s] - mb_abs[p.m0], u->dloss.as<float>(), mnnz, dc));
             }
             u->stats.mini_batches++;
             u->last_margin_off = mrow0 - p.row0;
@@ -492,6 +504,17 @@ hm_status retire_chunk(hm_udtf *u, Chunk *c, bool retain)
     return HM_OK;
 }
 
+// A chunk that was acquired for a slice which then turned out to be malformed: nothing was trained
+// from it, copies into it may be queued.  Back to the pool; its next user waits on the copy stream.
+void abandon_chunk(hm_udtf *u, Chunk *c)
+{
+    if (!c->free_ev && cudaEventCreateWithFlags(&c->free_ev, cudaEventDisableTiming) != cudaSuccess) { cudaGetLastError(); c->free_ev = nullptr; }
+    if (c->free_ev) cudaEventRecord(c->free_ev, u->copy);
+    c->rows = 0;
+    c->mb_abs.clear();
+    u->pool.push_back(c);
+}
+
 // One slice of host rows: build [tail | slice] on the device, train the full mini-batches.
 hm_status process_slice(hm_udtf *u, const HostRows &h)
 {
@@ -517,7 +540,21 @@ hm_status process_slice(hm_udtf *u, const HostRows &h)
 
     // new rows: host-to-device on the copy stream, queued before the host-side loop below so that the
     // bus is busy while it runs
-    if (!h.split) {
+    int64_t str_b0 = 0, str_nbytes = 0;
+    if (h.strings) {
+        // the strings of the slice: their bytes and their (absolute) offsets; the hash kernel writes the
+        // chunk's feature / value arrays (below, on the sort stream)
+        const int64_t s0 = h.rowptr[0];
+        str_b0 = h.s_offsets[s0];
+        str_nbytes = h.s_offsets[s0 + nnz] - str_b0;
+        if (str_nbytes < 0) { abandon_chunk(u, c); HM_FAIL(HM_ERR_INVALID_ARGUMENT, "string offsets are not non-decreasing"); }
+        HM_TRY(c->str_bytes.reserve((size_t)std::max<int64_t>(std::max(str_nbytes, u->hint_bytes), 1) + 64));
+        HM_TRY(c->str_off.reserve((size_t)(std::max<int64_t>(nnz, u->hint_elems) + 1) * 8));
+        if (nnz) {
+            if (str_nbytes) HM_CUDA(cudaMemcpyAsync(c->str_bytes.p, h.s_bytes + str_b0, (size_t)str_nbytes, cudaMemcpyHostToDevice, u->copy));
+            HM_CUDA(cudaMemcpyAsync(c->str_off.p, h.s_offsets + s0, (size_t)(nnz + 1) * 8, cudaMemcpyHostToDevice, u->copy));
+        }
+    } else if (!h.split) {
         const int64_t base = h.rowptr[0];
         if (nnz) {
             HM_CUDA(cudaMemcpyAsync(c->feat.as<uint32_t>() + t_nnz, h.feature + base, (size_t)nnz * 4, cudaMemcpyHostToDevice, u->copy));
@@ -527,7 +564,7 @@ hm_status process_slice(hm_udtf *u, const HostRows &h)
     } else {
         const int64_t qb = h.q_rowptr[0], cb = h.c_rowptr[0];
         const int64_t qn = h.q_rowptr[n] - qb, cn = h.c_rowptr[n] - cb;
-        if (qn < 0 || cn < 0) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "rowptr is not non-decreasing");
+        if (qn < 0 || cn < 0) { abandon_chunk(u, c); HM_FAIL(HM_ERR_INVALID_ARGUMENT, "rowptr is not non-decreasing"); }
         const int64_t hr = std::max(n, u->hint_rows);
         HM_TRY(c->sq_rp.reserve((size_t)(hr + 1) * 8));
         HM_TRY(c->sc_rp.reserve((size_t)(hr + 1) * 8));
@@ -561,14 +598,19 @@ hm_status process_slice(hm_udtf *u, const HostRows &h)
     if (!h.split) {
         const int64_t base = h.rowptr[0];
         for (int64_t i = 0; i <= n; i++) {
-            if (i > 0 && h.rowptr[i] < h.rowptr[i - 1]) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "rowptr decreases at row %lld", (long long)i);
+            if (i > 0 && h.rowptr[i] < h.rowptr[i - 1]) {
+                abandon_chunk(u, c);
+                HM_FAIL(HM_ERR_INVALID_ARGUMENT, "rowptr decreases at row %lld (rows pushed by earlier slices of this call were trained)", (long long)i);
+            }
             st[t_rows + i] = t_nnz + (h.rowptr[i] - base);
         }
     } else {
         const int64_t qb = h.q_rowptr[0], cb = h.c_rowptr[0];
         for (int64_t i = 0; i <= n; i++) {
-            if (i > 0 && (h.q_rowptr[i] < h.q_rowptr[i - 1] || h.c_rowptr[i] < h.c_rowptr[i - 1]))
-                HM_FAIL(HM_ERR_INVALID_ARGUMENT, "rowptr decreases at row %lld", (long long)i);
+            if (i > 0 && (h.q_rowptr[i] < h.q_rowptr[i - 1] || h.c_rowptr[i] < h.c_rowptr[i - 1])) {
+                abandon_chunk(u, c);
+                HM_FAIL(HM_ERR_INVALID_ARGUMENT, "rowptr decreases at row %lld (rows pushed by earlier slices of this call were trained)", (long long)i);
+            }
             st[t_rows + i] = t_nnz + (h.q_rowptr[i] - qb) + (h.c_rowptr[i] - cb);
         }
     }
@@ -602,7 +644,7 @@ hm_status process_slice(hm_udtf *u, const HostRows &h)
     if (h.split) {
         // the two groups -> the chunk's CSR, on the sort stream (its first consumer); training waits for it too
         const int64_t qb = h.q_rowptr[0], cb = h.c_rowptr[0];
-        const int grid = (int)std::min<int64_t>((n + 7) / 8, (int64_t)kNumSMs * 8);
+        const int grid = (int)std::min<int64_t>((n + 7) / 8, (int64_t)num_sms() * 8);
         merge_split_kernel<<<grid, 256, 0, u->sorter>>>(n, c->sq_rp.as<int64_t>(), qb, c->sc_rp.as<int64_t>(), cb,
                                                         c->sq_feat.as<uint32_t>(), c->sq_val.as<float>(),
                                                         c->sc_feat.as<uint32_t>(), t_nnz, c->rowptr.as<int64_t>() + t_rows,
@@ -613,7 +655,18 @@ hm_status process_slice(hm_udtf *u, const HostRows &h)
         HM_CUDA(cudaEventRecord(u->merged_ev, u->sorter));
         HM_CUDA(cudaStreamWaitEvent(u->compute, u->merged_ev, 0));
     }
-    if (!h.split) u->stats.h2d_bytes += (rows + 1) * 8 + nnz * (h.value ? 8 : 4) + n * 4;
+    if (h.strings && nnz) {
+        // feature strings -> the chunk's feature / value arrays, on the sort stream (their first consumer);
+        // training waits for it too.  The kernel takes absolute offsets: the byte buffer is passed shifted.
+        HM_TRY(launch_feature_hashing(u->Ls, c->str_bytes.as<uint8_t>() - str_b0, c->str_off.as<int64_t>(), nnz,
+                                      u->cfg.hash_seed, (int32_t)u->cfg.dims, reinterpret_cast<int32_t *>(c->feat.as<uint32_t>() + t_nnz),
+                                      c->val.as<float>() + t_nnz, (double)str_nbytes + 16.0 * (double)nnz));
+        if (!u->merged_ev) HM_CUDA(cudaEventCreateWithFlags(&u->merged_ev, cudaEventDisableTiming));
+        HM_CUDA(cudaEventRecord(u->merged_ev, u->sorter));
+        HM_CUDA(cudaStreamWaitEvent(u->compute, u->merged_ev, 0));
+    }
+    if (h.strings) u->stats.h2d_bytes += (rows + 1) * 8 + str_nbytes + (nnz + 1) * 8 + n * 4;
+    else if (!h.split) u->stats.h2d_bytes += (rows + 1) * 8 + nnz * (h.value ? 8 : 4) + n * 4;
     else u->stats.h2d_bytes += (n + 1) * 16 + (h.q_rowptr[n] - h.q_rowptr[0]) * 8 + (h.c_rowptr[n] - h.c_rowptr[0]) * 4 + n * 4 + t_rows * 8;
 
     // full mini-batches
@@ -651,6 +704,7 @@ hm_status process_host_rows(hm_udtf *u, const HostRows &all)
         u->hint_elems = (int64_t)((double)all.nnz() * frac) + 1024;
         u->hint_q = all.split ? (int64_t)((double)(all.q_rowptr[n_rows] - all.q_rowptr[0]) * frac) + 1024 : 0;
         u->hint_c = all.split ? (int64_t)((double)(all.c_rowptr[n_rows] - all.c_rowptr[0]) * frac) + 1024 : 0;
+        u->hint_bytes = all.strings ? (int64_t)((double)(all.s_offsets[all.rowptr[n_rows]] - all.s_offsets[all.rowptr[0]]) * frac) + 4096 : 0;
     }
     hm_status st = HM_OK;
     for (int64_t r = 0; r < n_rows && st == HM_OK;) {
@@ -665,7 +719,7 @@ hm_status process_host_rows(hm_udtf *u, const HostRows &all)
         r += h.n;
         ramp = largest;
     }
-    u->hint_rows = 0; u->hint_elems = 0; u->hint_q = 0; u->hint_c = 0;
+    u->hint_rows = 0; u->hint_elems = 0; u->hint_q = 0; u->hint_c = 0; u->hint_bytes = 0;
     return st;
 }
 
@@ -700,6 +754,7 @@ hm_status create_impl(const hm_config &cfg, int device, hm_udtf **out)
     u->cfg = cfg;
     u->device = device;
     std::memset(&u->stats, 0, sizeof(u->stats));
+    if (const char *e = std::getenv("HM_DENSE_COLUMNS")) u->dense_enabled = std::atoi(e) != 0;
     hm_status s = [&]() -> hm_status {
         {
             // the training stream's short kernels go first whenever both streams have CTAs to place
@@ -914,24 +969,19 @@ hm_status hm_udtf_process_strings(hm_udtf *u, int64_t n_rows, const int64_t *row
 {
     if (!u) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "NULL learner");
     if (u->closed) HM_FAIL(HM_ERR_STATE, "process() after close()");
+    if (u->device_rows_short) HM_FAIL(HM_ERR_STATE, "process() after a device call that ended on a short mini-batch");
     if (n_rows < 0 || (n_rows > 0 && (!rowptr || !label || !offsets))) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "NULL buffer passed to process_strings()");
     if (n_rows == 0) return HM_OK;
-    const int64_t s0 = rowptr[0], s1 = rowptr[n_rows];
-    const int64_t n = s1 - s0;
+    const int64_t n = rowptr[n_rows] - rowptr[0];
     if (n < 0) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "rowptr is not non-decreasing");
-    std::vector<int32_t> idx((size_t)std::max<int64_t>(n, 1));
-    std::vector<float> val((size_t)std::max<int64_t>(n, 1));
-    std::vector<int64_t> off((size_t)n + 1), rp((size_t)n_rows + 1);
-    const int64_t b0 = offsets[s0];
-    for (int64_t i = 0; i <= n; i++) off[(size_t)i] = offsets[s0 + i] - b0;
-    for (int64_t i = 0; i <= n_rows; i++) rp[(size_t)i] = rowptr[i] - s0;
-    if (n > 0) {
-        if (!bytes) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "NULL bytes buffer");
-        if (u->cfg.dims > 0x7fffffffLL) HM_FAIL(HM_ERR_UNSUPPORTED, "feature hashing needs dims < 2^31");
-        HM_TRY(hash_host(bytes + b0, off.data(), n, u->cfg.hash_seed, (int32_t)u->cfg.dims, idx.data(), val.data(),
-                         u->device, true));
-    }
-    return hm_udtf_process(u, n_rows, rp.data(), idx.data(), val.data(), label);
+    if (n > 0 && !bytes) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "NULL bytes buffer");
+    if (u->cfg.dims > 0x7fffffffLL) HM_FAIL(HM_ERR_UNSUPPORTED, "feature hashing needs dims < 2^31");
+    DeviceGuard g(u->device);
+    // The same slices as hm_udtf_process: the strings' bytes and offsets cross the bus on the copy stream and
+    // are hashed on the device straight into the chunk's CSR (no index ever visits the host).
+    HostRows all;
+    all.n = n_rows; all.rowptr = rowptr; all.strings = true; all.s_bytes = bytes; all.s_offsets = offsets; all.label = label;
+    return process_host_rows(u, all);
 }
 
 hm_status hm_udtf_process_device(hm_udtf *u, int64_t n_rows, int64_t nnz, const int64_t *d_rowptr,
@@ -1286,6 +1336,24 @@ hm_status hm_udtf_last_margins(hm_udtf *u, float *host, int64_t cap, int64_t *n)
     }
     HM_CUDA(cudaStreamSynchronize(u->compute));
     *n = m;
+    return HM_OK;
+}
+
+hm_status hm_udtf_dense_columns(hm_udtf *u, int32_t *feature, int32_t cap, int32_t *n)
+{
+    if (!u || !n || cap < 0 || (cap > 0 && !feature)) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "bad arguments to dense_columns");
+    *n = 0;
+    if (u->sort_turn == 0) return HM_OK;
+    DeviceGuard g(u->device);
+    const SortScratch &ss = u->sort[(u->sort_turn - 1) & 1];
+    if (!ss.dense) return HM_OK;
+    HM_CUDA(cudaStreamSynchronize(u->sorter));
+    DenseInfo di;
+    HM_CUDA(cudaMemcpy(&di, ss.dense, sizeof(di), cudaMemcpyDeviceToHost));
+    int32_t m = 0;
+    for (int i = 0; i < 32; i++)
+        if ((di.mask >> i) & 1u) { if (m < cap) feature[m] = (int32_t)di.key[i]; m++; }
+    *n = std::min(m, cap);
     return HM_OK;
 }
 

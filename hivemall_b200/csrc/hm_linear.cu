@@ -17,6 +17,7 @@
 //   predict / export / scale helpers
 #include "hm_internal.h"
 #include <algorithm>
+#include <atomic>
 #include <cstring>
 #include <mutex>
 
@@ -108,6 +109,12 @@ struct FwdParams {
     int32_t train;           // 0: prediction only
     uint32_t dims;
     uint32_t *bad;           // set to 1 when a feature index >= dims is met (that element scores 0)
+    // dense columns of the block (training only; NULL: none).  Lane i of a warp owns position i of
+    // its rows: the weight of a dense column sits in a register instead of being gathered, and the
+    // column's gradient sum is accumulated right here, in a fixed order, instead of being sorted.
+    const DenseInfo *dense;
+    double *dense_partial;   // [32][dense_stride]: per forward CTA, the column sums of its rows
+    int32_t dense_stride;
 };
 
 // Margins (and dloss) of rows r = warp_first, warp_first + warp_stride, ... of the mini-batch: one
@@ -136,6 +143,59 @@ __device__ __forceinline__ void forward_rows(const FwdParams &P, int warp_first,
                 P.dloss[r] = dloss_of(P.loss, m, y);
             }
         }
+    }
+}
+
+// The same with dense columns (DenseInfo).  Every row of the block has the block's dense
+// positions, so `p0 + lane < p1` holds for their lanes.  The margin adds the same products in
+// the same order as forward_rows: only the source of a dense column's weight differs.
+__device__ __forceinline__ void forward_rows_dense(const FwdParams &P, int warp_first, int warp_stride, double *s_part)
+{
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t dmask = P.dense->mask;
+    const bool mine = (dmask >> lane) & 1u;
+    const float wd = mine ? weight_at<true>(P.wv, P.dense->key[lane]) : 0.0f;
+    double dacc = 0.0;
+    for (int r = warp_first; r < P.n_rows; r += warp_stride) {
+        const int64_t row = P.row0 + r;
+        const int64_t p0 = P.rowptr[row], p1 = P.rowptr[row + 1];
+        double acc = 0.0;
+        float x0 = 0.0f;
+        int64_t p = p0 + lane;
+        if (p < p1) {
+            const uint32_t f = __ldcs(P.feature + p);
+            x0 = __ldcs(P.value + p);
+            if (mine) acc += (double)__fmul_rn(wd, x0);
+            else if (f < P.dims) acc += (double)__fmul_rn(weight_at<true>(P.wv, f), x0);
+            else atomicOr(P.bad, 1u);
+        }
+        for (p += 32; p < p1; p += 32) {
+            const uint32_t f = __ldcs(P.feature + p);
+            const float x = __ldcs(P.value + p);
+            if (f < P.dims) acc += (double)__fmul_rn(weight_at<true>(P.wv, f), x);
+            else atomicOr(P.bad, 1u);
+        }
+        acc = warp_sum(acc);
+        const float m = (float)acc;
+        float dl = 0.0f;
+        if (lane == 0) {
+            P.margin[row - P.block_row0] = m;
+            const float lab = P.label[row];
+            const float y = P.task == HM_TASK_CLASSIFIER ? (lab > 0.0f ? 1.0f : -1.0f) : lab;
+            dl = dloss_of(P.loss, m, y);
+            P.dloss[r] = dl;
+        }
+        dl = __shfl_sync(0xffffffffu, dl, 0);
+        if (mine) dacc += (double)__fmul_rn(dl, x0);      // the contribution the update kernel would have sorted
+    }
+    // column sums of this CTA's rows: warps added in a fixed order
+    s_part[warp * 32 + lane] = dacc;
+    __syncthreads();
+    if (warp == 0) {
+        double sum = 0.0;
+#pragma unroll
+        for (int w2 = 0; w2 < kFwdThreads / 32; w2++) sum += s_part[w2 * 32 + lane];
+        P.dense_partial[(size_t)lane * P.dense_stride + blockIdx.x] = sum;
     }
 }
 
@@ -198,7 +258,10 @@ __device__ __forceinline__ void forward_rows_small(const FwdParams &P)
 
 __global__ void __launch_bounds__(kFwdThreads) linear_forward_kernel(FwdParams P)
 {
-    forward_rows<true>(P, blockIdx.x * (kFwdThreads / 32) + (threadIdx.x >> 5), gridDim.x * (kFwdThreads / 32));
+    __shared__ double s_part[kFwdThreads];
+    const int warp_first = blockIdx.x * (kFwdThreads / 32) + (threadIdx.x >> 5), warp_stride = gridDim.x * (kFwdThreads / 32);
+    if (P.dense && P.dense->mask != 0u) forward_rows_dense(P, warp_first, warp_stride, s_part);
+    else forward_rows<true>(P, warp_first, warp_stride);
 }
 
 // ---- update ------------------------------------------------------------------------
@@ -236,9 +299,13 @@ struct UpdParams {
     float eta, adam_alpha, lambda, eps, rho, beta1, beta2, alpha, beta, lambda1, lambda2;
     double inv_rows;         // 1 / rows of the mini-batch, computed on the host in fp64
     int32_t n_active;        // CTAs launched (all own at least one tile unless the segment is empty)
-    uint32_t seg_begin;      // linear_update_kernel: first element of the mini-batch in the sorted block and
-    uint32_t seg_elems;      // its element count (= seg_off[seg], seg_off[seg+1] - seg_off[seg]: the host knows
-                             // both, so the kernel does not start with a dependent load)
+    // (the mini-batch's bounds in the sorted arrays are read from seg_off: the sorted arrays are shorter
+    // than the CSR by the dense-column and out-of-range elements, a number only the device knows)
+    // dense columns of the block (NULL: the block was sorted whole)
+    const DenseInfo *dense;
+    const double *dense_partial;   // [32][dense_stride] column sums left by the forward kernel's CTAs
+    int32_t dense_stride, fwd_grid;
+    int32_t n_rows;          // rows of the mini-batch (= occurrences of every dense column)
 };
 
 // Replica record of one feature while it is being updated.
@@ -556,7 +623,29 @@ __device__ __forceinline__ void reduce_tile(const UpdParams &P, const UpdShared 
     __syncthreads();
 }
 
-__global__ void __launch_bounds__(kUpdThreads, 4) linear_update_kernel(UpdParams P)
+// Optimizer step of the block's dense columns: one warp per column adds the forward CTAs' partial
+// sums in a fixed order.  Runs as one extra CTA of the update kernel; the features are disjoint
+// from everything the sorted stream holds (dense_check_kernel), so nothing else touches their records.
+__device__ __noinline__ void dense_columns_step(const UpdParams &P)
+{
+    const uint32_t dmask = P.dense->mask;
+    const int lane = threadIdx.x & 31;
+    for (int i = threadIdx.x >> 5; i < 32; i += kUpdThreads / 32) {
+        if (!((dmask >> i) & 1u)) continue;
+        const double *col = P.dense_partial + (size_t)i * P.dense_stride;
+        double sum = 0.0;
+        for (int c = lane; c < P.fwd_grid; c += 32) sum += col[c];
+        sum = warp_sum(sum);
+        if (lane == 0) {
+            const uint32_t j = P.dense->key[i];
+            Rec r = load_rec(P, j);
+            step_rec(P, r, grad_of(P, sum, (uint32_t)P.n_rows));
+            store_rec(P, j, r);
+        }
+    }
+}
+
+__global__ void __launch_bounds__(kUpdThreads, 4) linear_update_kernel(const __grid_constant__ UpdParams P)
 {
     __shared__ __align__(16) unsigned char smem_raw[kUpdSmem];
     uint32_t *s_key = reinterpret_cast<uint32_t *>(smem_raw);
@@ -573,10 +662,11 @@ __global__ void __launch_bounds__(kUpdThreads, 4) linear_update_kernel(UpdParams
 
     const int tid = threadIdx.x;
     USTAMP(0);
-    const uint32_t s0 = P.seg_begin, n = P.seg_elems;
+    if (P.dense && (int)blockIdx.x == P.n_active) { dense_columns_step(P); return; }
+    const uint32_t s0 = P.seg_off[P.seg], n = P.seg_off[P.seg + 1] - s0;
     // contiguous split of the sorted mini-batch over the grid, in whole tiles
     const uint32_t tiles = (n + kUpdTile - 1) / kUpdTile;
-    const uint32_t tiles_per_cta = (tiles + gridDim.x - 1) / gridDim.x;
+    const uint32_t tiles_per_cta = (tiles + P.n_active - 1) / P.n_active;
     const uint32_t lo = min(n, blockIdx.x * tiles_per_cta * kUpdTile);
     const uint32_t hi = min(n, lo + tiles_per_cta * kUpdTile);
 
@@ -609,7 +699,7 @@ __global__ void __launch_bounds__(kUpdThreads, 4) linear_update_kernel(UpdParams
             P.br.first[blockIdx.x] = whole ? rec_bits(s_carry) : (s_first.cnt != 0 ? rec_bits(s_first) : none);
             P.br.last[blockIdx.x] = (!whole && s_carry.cnt != 0) ? rec_bits(s_carry) : none;
             __threadfence();
-            s_is_last = atomicAdd(P.br.ticket, 1u) == gridDim.x - 1;
+            s_is_last = atomicAdd(P.br.ticket, 1u) == (uint32_t)P.n_active - 1;
         }
         // ---- optimizer step for the listed features, latencies overlapped
         USTAMP(4);
@@ -622,7 +712,7 @@ __global__ void __launch_bounds__(kUpdThreads, 4) linear_update_kernel(UpdParams
             P.br.first[blockIdx.x] = make_uint4(0u, 0u, 0u, 0u);
             P.br.last[blockIdx.x] = make_uint4(0u, 0u, 0u, 0u);
             __threadfence();
-            s_is_last = atomicAdd(P.br.ticket, 1u) == gridDim.x - 1;
+            s_is_last = atomicAdd(P.br.ticket, 1u) == (uint32_t)P.n_active - 1;
         }
         __syncthreads();
     }
@@ -632,7 +722,7 @@ __global__ void __launch_bounds__(kUpdThreads, 4) linear_update_kernel(UpdParams
     // in shared memory; the thread that owns CTA c starts a run at last[c] and walks first[c+1],
     // first[c+2], ... while the feature matches (fixed order, fp64).  No sorting is needed.
     __threadfence();
-    const int G = (int)gridDim.x;
+    const int G = P.n_active;
     uint4 *f_sm = reinterpret_cast<uint4 *>(smem_raw);
     uint32_t *ml_key = reinterpret_cast<uint32_t *>(smem_raw + (size_t)kUpdMaxGrid * 16);
     float *ml_g = reinterpret_cast<float *>(ml_key + kUpdMaxGrid);
@@ -862,26 +952,30 @@ __global__ void fill_u32_kernel(uint32_t *__restrict__ p, int64_t n, uint32_t v)
 
 int grid_for(int64_t ctas_wanted, int per_sm)
 {
-    const int64_t cap = (int64_t)kNumSMs * per_sm;
+    const int64_t cap = (int64_t)num_sms() * per_sm;
     if (ctas_wanted < 1) ctas_wanted = 1;
     return (int)(ctas_wanted < cap ? ctas_wanted : cap);
 }
 
 }  // namespace
 
+int linear_forward_grid(int32_t n_rows) { return grid_for(((int64_t)n_rows + 7) / 8, 8); }
+
 hm_status launch_linear_forward(Launcher &L, const LinearArgs &a, const int64_t *d_rowptr, int64_t row0,
                                 int32_t n_rows, int64_t block_row0, const uint32_t *d_feature,
                                 const float *d_value, const float *d_label, float *d_margin,
-                                float *d_dloss, uint32_t *d_bad, int64_t nnz_hint)
+                                float *d_dloss, uint32_t *d_bad, int64_t nnz_hint, const DenseCols &dc)
 {
     if (n_rows <= 0) return HM_OK;
     FwdParams P;
+    P.dense = dc.info; P.dense_partial = dc.partial; P.dense_stride = dc.stride;
     P.wv = a.wv; P.rowptr = d_rowptr; P.feature = d_feature; P.value = d_value; P.label = d_label;
     P.margin = d_margin; P.dloss = d_dloss;
     P.block_row0 = block_row0; P.row0 = row0; P.n_rows = n_rows;
     P.task = a.cfg.task; P.loss = a.cfg.loss; P.train = 1;
     P.dims = (uint32_t)a.cfg.dims; P.bad = d_bad;
-    const int grid = grid_for(((int64_t)n_rows + 7) / 8, 8);
+    const int grid = linear_forward_grid(n_rows);
+    if (dc.info && grid > dc.stride) HM_FAIL(HM_ERR_STATE, "dense-column scratch too small (%d > %d)", grid, dc.stride);
     // algorithmic bytes: feature+value read, w gather per element; rowptr, label, margin, dloss per row
     const double bytes = 12.0 * (double)nnz_hint + 20.0 * (double)n_rows;
     HM_LAUNCH(L, K_LIN_FORWARD, bytes, (linear_forward_kernel<<<grid, kFwdThreads, 0, L.stream>>>(P)));
@@ -900,6 +994,7 @@ hm_status launch_predict_linear(Launcher &L, const WeightView &wv, int64_t dims,
     P.block_row0 = 0; P.row0 = 0; P.n_rows = (int32_t)n_rows;
     P.task = 0; P.loss = 0; P.train = 0;
     P.dims = (uint32_t)dims; P.bad = d_bad;
+    P.dense = nullptr; P.dense_partial = nullptr; P.dense_stride = 0;
     const int grid = grid_for((n_rows + 7) / 8, 8);
     HM_LAUNCH(L, K_PREDICT, 0.0, (linear_forward_kernel<<<grid, kFwdThreads, 0, L.stream>>>(P)));
     HM_CUDA(cudaGetLastError());
@@ -915,21 +1010,29 @@ hm_status update_scratch_reserve(UpdateScratch &u)
     HM_CUDA(cudaMalloc(&u.boundary, bytes));
     HM_CUDA(cudaMemset(u.boundary, 0, bytes));
     u.done_counter = reinterpret_cast<uint32_t *>(static_cast<char *>(u.boundary) + (size_t)2 * u.grid * 16);
+    // column sums of the dense columns: one double per (column, forward CTA)
+    u.dense_stride = num_sms() * 8;
+    HM_CUDA(cudaMalloc(&u.dense_partial, (size_t)32 * u.dense_stride * sizeof(double)));
+    HM_CUDA(cudaMemset(u.dense_partial, 0, (size_t)32 * u.dense_stride * sizeof(double)));
     return HM_OK;
 }
 
 void update_scratch_free(UpdateScratch &u)
 {
     cudaFree(u.boundary);
-    u.boundary = nullptr; u.done_counter = nullptr; u.grid = 0;
+    cudaFree(u.dense_partial);
+    u.boundary = nullptr; u.done_counter = nullptr; u.grid = 0; u.dense_partial = nullptr; u.dense_stride = 0;
 }
 
 hm_status launch_linear_update(Launcher &L, const LinearArgs &a, const StepScalars &sc, UpdateScratch &us,
                                const uint32_t *d_sorted_key, const uint2 *d_sorted_pay,
-                               const uint32_t *d_seg_off, int seg, int64_t seg_begin, const float *d_dloss, int64_t nnz_hint)
+                               const uint32_t *d_seg_off, int seg, int64_t seg_begin, const float *d_dloss, int64_t nnz_hint,
+                               const DenseCols &dc)
 {
     UpdParams P;
-    P.seg_begin = (uint32_t)seg_begin; P.seg_elems = (uint32_t)nnz_hint;
+    (void)seg_begin;
+    P.dense = dc.info; P.dense_partial = dc.partial; P.dense_stride = dc.stride;
+    P.fwd_grid = linear_forward_grid(sc.n_rows); P.n_rows = sc.n_rows;
     P.rec = a.rec; P.rec_width = a.rec_width; P.ftrl_derived = a.wv.ftrl; P.touched = nullptr;
     P.skey = d_sorted_key; P.spay = d_sorted_pay; P.dloss = d_dloss; P.seg_off = d_seg_off;
     P.br.first = reinterpret_cast<uint4 *>(us.boundary);
@@ -950,7 +1053,9 @@ hm_status launch_linear_update(Launcher &L, const LinearArgs &a, const StepScala
     // algorithmic bytes: sorted feature + (row, value) stream; dloss table and the per-feature
     // state traffic (number of distinct features is data dependent) are not counted
     const double bytes = 12.0 * (double)nnz_hint;
-    HM_LAUNCH(L, K_LIN_UPDATE, bytes, (linear_update_kernel<<<grid, kUpdThreads, 0, L.stream>>>(P)));
+    // (with dense columns: nnz_hint bounds the sorted mini-batch from above, CTAs past its end find nothing
+    // to do; one more CTA steps the dense columns)
+    HM_LAUNCH(L, K_LIN_UPDATE, bytes, (linear_update_kernel<<<grid + (dc.info ? 1 : 0), kUpdThreads, 0, L.stream>>>(P)));
     HM_CUDA(cudaGetLastError());
     return HM_OK;
 }
@@ -975,7 +1080,6 @@ hm_status launch_linear_small_batches(Launcher &L, const LinearArgs &a, const in
     P.F.task = a.cfg.task; P.F.loss = a.cfg.loss; P.F.train = 1; P.F.dims = (uint32_t)a.cfg.dims; P.F.bad = d_bad;
     P.U.rec = a.rec; P.U.rec_width = a.rec_width; P.U.ftrl_derived = a.wv.ftrl; P.U.touched = nullptr;
     P.U.skey = d_sorted_key; P.U.spay = d_sorted_pay; P.U.dloss = d_dloss; P.U.seg_off = d_seg_off;
-    P.U.seg_begin = 0; P.U.seg_elems = 0;   // (the small-batch kernel reads seg_off itself)
     P.U.dims = (uint32_t)a.cfg.dims; P.U.opt = a.cfg.opt; P.U.reg = a.cfg.reg; P.U.grad_norm = a.cfg.grad_norm;
     P.U.lambda = a.cfg.lambda; P.U.eps = a.cfg.eps; P.U.rho = a.cfg.rho; P.U.beta1 = a.cfg.beta1; P.U.beta2 = a.cfg.beta2;
     P.U.alpha = a.cfg.alpha; P.U.beta = a.cfg.beta; P.U.lambda1 = a.cfg.lambda1; P.U.lambda2 = a.cfg.lambda2;
@@ -984,12 +1088,12 @@ hm_status launch_linear_small_batches(Launcher &L, const LinearArgs &a, const in
     const size_t model_bytes = (size_t)a.cfg.dims * a.rec_width * sizeof(float);
     size_t dyn = 0;
     if (model_bytes <= kSmallModelMax) {
-        static bool attr_set[64] = {false};   // > 48 KB of dynamic shared memory needs opting in, once per device
+        static std::atomic<bool> attr_set[64];   // > 48 KB of dynamic shared memory needs opting in, once per device
         int dev = 0;
         HM_CUDA(cudaGetDevice(&dev));
-        if (dev < 0 || dev >= 64 || !attr_set[dev]) {
+        if (dev < 0 || dev >= 64 || !attr_set[dev].load(std::memory_order_acquire)) {
             HM_CUDA(cudaFuncSetAttribute(linear_small_batch_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmallModelMax));
-            if (dev >= 0 && dev < 64) attr_set[dev] = true;
+            if (dev >= 0 && dev < 64) attr_set[dev].store(true, std::memory_order_release);
         }
         P.model_floats = (uint32_t)(model_bytes / sizeof(float));
         dyn = model_bytes;

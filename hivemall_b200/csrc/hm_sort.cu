@@ -16,9 +16,30 @@
 // scatter (reads key+payload, writes key+payload, 24 B/elem).  The first pass reads the
 // CSR feature/value arrays directly and looks the row ids up in the row pointer (20 B/elem),
 // so no copy of the input is made.  Integer counting only; atomics are integer (order-independent).
+//
+// Two kinds of element never enter the sort: those of the block's dense columns (DenseInfo:
+// their gradient is a column sum taken by the forward kernel, see hm_linear.cu) and those whose
+// feature index is out of range (they are flagged and ignored everywhere).  Both are dropped by
+// key in the first pass and its histogram, so the sorted arrays are shorter than the block's CSR:
+// in_off / in_tile_off describe the CSR, seg_off / seg_tile_off the sorted arrays, and the latter
+// are written on the device from the first histogram (scan_rows_kernel).
 #include "hm_internal.h"
+#include <algorithm>
+#include <atomic>
 
 namespace hm {
+
+int num_sms()
+{
+    static std::atomic<int> cache[64];
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) { cudaGetLastError(); return 148; }
+    if (dev >= 0 && dev < 64) { const int c = cache[dev].load(std::memory_order_relaxed); if (c > 0) return c; }
+    int n = 0;
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n < 1) { cudaGetLastError(); n = 148; }
+    if (dev >= 0 && dev < 64) cache[dev].store(n, std::memory_order_relaxed);
+    return n;
+}
 
 const char *const kKernelNames[K_NUM_KERNELS] = {
     "hash", "seg_prep", "sort_hist", "sort_scan", "sort_scatter", "linear_forward",
@@ -37,6 +58,7 @@ constexpr int kScatWarps = kScatThreads / 32;
 constexpr int kScatItems = kSortTile / kScatThreads;  // 8
 constexpr int kScatCtasPerSm = 2;
 
+// Offsets of the block's mini-batches in its CSR (the first pass's coordinates).
 __global__ void seg_prep_kernel(const int64_t *__restrict__ rowptr, int64_t row0, int64_t n_rows,
                                 int32_t mini_batch, int n_segs, uint32_t *__restrict__ seg_off,
                                 uint32_t *__restrict__ seg_tile_off)
@@ -72,6 +94,110 @@ __device__ __forceinline__ int find_seg(const uint32_t *tile_off, int n_segs, ui
     return lo;
 }
 
+// ---- dense columns --------------------------------------------------------------------
+constexpr uint32_t kDenseEmpty = 0xffffffffu;
+constexpr int kDenseSlots = 128;       // open-addressing table of at most 32 keys
+
+__device__ __forceinline__ uint32_t dense_hash(uint32_t key) { return (key * 0x9E3779B1u) >> 25; }
+
+// Index (0..31) of `key` among the table's keys, or -1.
+__device__ __forceinline__ int dense_find(const uint32_t *tab, const uint32_t *tab_idx, uint32_t key)
+{
+    uint32_t h = dense_hash(key);
+    while (true) {
+        const uint32_t v = tab[h];
+        if (v == key) return (int)tab_idx[h];
+        if (v == kDenseEmpty) return -1;
+        h = (h + 1) & (kDenseSlots - 1);
+    }
+}
+__device__ __forceinline__ bool dense_hit(const uint32_t *tab, uint32_t key)
+{
+    uint32_t h = dense_hash(key);
+    while (true) {
+        const uint32_t v = tab[h];
+        if (v == key) return true;
+        if (v == kDenseEmpty) return false;
+        h = (h + 1) & (kDenseSlots - 1);
+    }
+}
+// Called by every thread of the CTA (two barriers).  Lane i of warp 0 inserts key i.
+__device__ __forceinline__ void dense_tab_build(uint32_t *tab, uint32_t *tab_idx, uint32_t mask, uint32_t my_key, int nthreads)
+{
+    for (int q = threadIdx.x; q < kDenseSlots; q += nthreads) tab[q] = kDenseEmpty;
+    __syncthreads();
+    if (threadIdx.x < 32 && ((mask >> threadIdx.x) & 1u)) {
+        uint32_t h = dense_hash(my_key);
+        while (atomicCAS(&tab[h], kDenseEmpty, my_key) != kDenseEmpty) h = (h + 1) & (kDenseSlots - 1);
+        if (tab_idx) tab_idx[h] = threadIdx.x;
+    }
+    __syncthreads();
+}
+
+constexpr int kChkThreads = 256;
+
+// Which of the first 32 positions of the block's rows are dense columns (see DenseInfo)?  A warp
+// per row reads the whole row once (4 B per element): position i stays a candidate while every
+// row holds the first row's feature there, and loses the bit as soon as that feature turns up
+// anywhere else.  The last CTA to finish publishes the result.
+__global__ void __launch_bounds__(kChkThreads)
+dense_check_kernel(const int64_t *__restrict__ rowptr, int64_t row0, int64_t n_rows,
+                   const uint32_t *__restrict__ feature, uint32_t dims, DenseInfo *__restrict__ out)
+{
+    __shared__ uint32_t s_ref[32], s_tab[kDenseSlots], s_tab_idx[kDenseSlots];
+    __shared__ uint32_t s_init, s_noteq, s_collide;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (warp == 0) {
+        const int64_t p0 = rowptr[row0], p1 = rowptr[row0 + 1];
+        const bool have = p0 + lane < p1;
+        const uint32_t f = have ? __ldg(feature + p0 + lane) : kDenseEmpty;
+        const uint32_t peers = __match_any_sync(0xffffffffu, f);
+        const bool ok = have && f < dims && __popc(peers) == 1;     // in range, and once in the row
+        const uint32_t init = __ballot_sync(0xffffffffu, ok);
+        s_ref[lane] = f;
+        if (lane == 0) { s_init = init; s_noteq = 0; s_collide = 0; }
+    }
+    __syncthreads();
+    const uint32_t init = s_init;
+    dense_tab_build(s_tab, s_tab_idx, init, s_ref[lane], kChkThreads);
+    if (init != 0) {
+        const uint32_t ref = s_ref[lane];
+        uint32_t noteq = 0, coll = 0;
+        const int64_t stride = (int64_t)gridDim.x * (kChkThreads / 32);
+        for (int64_t r = (int64_t)blockIdx.x * (kChkThreads / 32) + warp; r < n_rows; r += stride) {
+            const int64_t p0 = rowptr[row0 + r], p1 = rowptr[row0 + r + 1];
+            {
+                const int64_t p = p0 + lane;
+                const bool in = p < p1;
+                const uint32_t f = in ? __ldg(feature + p) : kDenseEmpty;
+                const bool eq = in && f == ref;
+                noteq |= init & ~__ballot_sync(0xffffffffu, eq);
+                if (in && !eq) { const int j = dense_find(s_tab, s_tab_idx, f); if (j >= 0) coll |= 1u << j; }
+            }
+            for (int64_t p = p0 + 32 + lane; p < p1; p += 32) {
+                const int j = dense_find(s_tab, s_tab_idx, __ldg(feature + p));
+                if (j >= 0) coll |= 1u << j;
+            }
+        }
+        coll = __reduce_or_sync(0xffffffffu, coll);
+        if (lane == 0) { if (noteq) atomicOr(&s_noteq, noteq); if (coll) atomicOr(&s_collide, coll); }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        if (s_noteq) atomicOr(&out->noteq, s_noteq);
+        if (s_collide) atomicOr(&out->collide, s_collide);
+        __threadfence();
+        if (atomicAdd(&out->ticket, 1u) == gridDim.x - 1) {
+            __threadfence();
+            const uint32_t mask = init & ~atomicOr(&out->noteq, 0u) & ~atomicOr(&out->collide, 0u);
+            for (int i = 0; i < 32; i++) out->key[i] = s_ref[i];
+            out->mask = mask;
+            out->count = (uint32_t)__popc(mask);
+            out->noteq = 0; out->collide = 0; out->ticket = 0;      // ready for the next block
+        }
+    }
+}
+
 // One thread per sort tile: the row of the mini-batch that holds the tile's first element.
 __global__ void tile_row0_kernel(const int64_t *__restrict__ rowptr, int64_t block_row0, int64_t block_rows,
                                  int32_t mini_batch, const uint32_t *__restrict__ seg_off,
@@ -92,15 +218,23 @@ __global__ void tile_row0_kernel(const int64_t *__restrict__ rowptr, int64_t blo
     }
 }
 
-template <int RB>
+// FIRST: the keys are the block's CSR features; dense-column and out-of-range elements are not counted.
+template <int RB, bool FIRST>
 __global__ void __launch_bounds__(kSortThreads)
 sort_hist_kernel(const uint32_t *__restrict__ keys, const uint32_t *__restrict__ seg_off,
                  const uint32_t *__restrict__ seg_tile_off, int n_segs, int shift,
-                 uint32_t *__restrict__ tile_hist, uint32_t *__restrict__ row_sum)
+                 uint32_t *__restrict__ tile_hist, uint32_t *__restrict__ row_sum,
+                 uint32_t dims, const DenseInfo *__restrict__ dense)
 {
     constexpr int R = 1 << RB;
     __shared__ uint32_t s_off[kMaxSegs + 1], s_toff[kMaxSegs + 1];
     __shared__ uint32_t hist[kSortWarps][R];
+    __shared__ uint32_t s_dtab[FIRST ? kDenseSlots : 1];
+    uint32_t dmask = 0;
+    if (FIRST) {
+        dmask = dense->mask;
+        dense_tab_build(s_dtab, nullptr, dmask, dense->key[threadIdx.x & 31], kSortThreads);
+    }
     for (int s = threadIdx.x; s <= n_segs; s += kSortThreads) { s_off[s] = seg_off[s]; s_toff[s] = seg_tile_off[s]; }
     __syncthreads();
     const uint32_t total = s_toff[n_segs];
@@ -121,7 +255,9 @@ sort_hist_kernel(const uint32_t *__restrict__ keys, const uint32_t *__restrict__
 #pragma unroll
         for (int i = 0; i < kSortItems; i++) {
             const uint32_t e = e0 + i * kSortThreads + threadIdx.x;
-            if (e < e1) atomicAdd(&hist[warp][(k[i] >> shift) & (R - 1)], 1u);
+            bool count = e < e1;
+            if (FIRST) count = count && k[i] < dims && !(dmask && dense_hit(s_dtab, k[i]));
+            if (count) atomicAdd(&hist[warp][(k[i] >> shift) & (R - 1)], 1u);
         }
         __syncthreads();
         for (int d = threadIdx.x; d < R; d += kSortThreads) {
@@ -135,10 +271,15 @@ sort_hist_kernel(const uint32_t *__restrict__ keys, const uint32_t *__restrict__
     }
 }
 
-// In-place exclusive scan of row_sum[0..n) by one CTA of 1024 threads.
-__global__ void __launch_bounds__(1024) scan_rows_kernel(uint32_t *__restrict__ row_sum, int n)
+// In-place exclusive scan of row_sum[0..n) by one CTA of 1024 threads.  After the first pass's
+// histogram (seg_off != NULL) the scan also yields where every mini-batch starts in the sorted
+// arrays: row_sum[s * radix] = elements counted before mini-batch s.
+__global__ void __launch_bounds__(1024) scan_rows_kernel(uint32_t *__restrict__ row_sum, int n,
+                                                         uint32_t *__restrict__ seg_off, uint32_t *__restrict__ seg_tile_off,
+                                                         int n_segs, int radix)
 {
     __shared__ uint32_t warp_tot[32];
+    __shared__ uint32_t s_total, s_so[kMaxSegs + 1];
     const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
     const int per = (n + 1023) / 1024;
     const int lo = t * per, hi = min(lo + per, n);
@@ -158,6 +299,23 @@ __global__ void __launch_bounds__(1024) scan_rows_kernel(uint32_t *__restrict__ 
     __syncthreads();
     uint32_t run = warp_tot[warp] + inc - s;
     for (int i = lo; i < hi; i++) { uint32_t v = row_sum[i]; row_sum[i] = run; run += v; }
+    if (!seg_off) return;
+    if (t == 1023) s_total = run;       // (threads past the end carry the grand total)
+    __syncthreads();
+    for (int sg = t; sg <= n_segs; sg += 1024) {
+        const uint32_t o = sg < n_segs ? row_sum[sg * radix] : s_total;
+        s_so[sg] = o;
+        seg_off[sg] = o;
+    }
+    __syncthreads();
+    if (t == 0) {
+        uint32_t tiles = 0;
+        for (int sg = 0; sg < n_segs; sg++) {
+            seg_tile_off[sg] = tiles;
+            tiles += (s_so[sg + 1] - s_so[sg] + kSortTile - 1) / kSortTile;
+        }
+        seg_tile_off[n_segs] = tiles;
+    }
 }
 
 // One warp per (segment, digit) row of tile_hist: exclusive scan along the row, plus row base.
@@ -204,8 +362,11 @@ sort_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint2 *__restric
                     RowLookup rl, const float *__restrict__ val_in,
                     uint32_t *__restrict__ keys_out, uint2 *__restrict__ pay_out,
                     const uint32_t *__restrict__ seg_off, const uint32_t *__restrict__ seg_tile_off,
-                    int n_segs, int shift, const uint32_t *__restrict__ tile_hist)
+                    int n_segs, int shift, const uint32_t *__restrict__ tile_hist,
+                    uint32_t dims, const DenseInfo *__restrict__ dense, uint32_t *__restrict__ bad)
 {
+    // FIRST: seg_off / seg_tile_off are the CSR's (in_off / in_tile_off); elements of dense columns and
+    // out-of-range features take no part (the histogram did not count them either).
     constexpr int R = 1 << RB;
     extern __shared__ __align__(16) unsigned char dyn_smem[];
     uint32_t *s_key = reinterpret_cast<uint32_t *>(dyn_smem);
@@ -217,7 +378,12 @@ sort_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint2 *__restric
     __shared__ uint32_t s_mark[FIRST ? kSortTile / 32 : 1];   // bit p: a row starts at tile position p
     __shared__ uint32_t s_dup;                                // two rows start at one position (an empty row)
     __shared__ int s_nr;
+    __shared__ uint32_t s_ntile;                              // elements of the tile that are sorted
+    __shared__ uint32_t s_dtab[FIRST ? kDenseSlots : 1];
+    uint32_t dmask = 0;
     if (FIRST) {
+        dmask = dense->mask;
+        dense_tab_build(s_dtab, nullptr, dmask, dense->key[threadIdx.x & 31], kScatThreads);
         for (int q = threadIdx.x; q < kSortTile / 32; q += kScatThreads) s_mark[q] = 0;
         if (threadIdx.x == 0) s_dup = 0;
     }
@@ -362,9 +528,15 @@ sort_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint2 *__restric
             }
         }
         // stable rank of every element among equal digits inside its warp
+        uint32_t vbits = 0;      // bit i: item i takes part in the sort
 #pragma unroll
         for (int i = 0; i < kScatItems; i++) {
-            const bool valid = ew + i * 32 < e1;
+            bool valid = ew + i * 32 < e1;
+            if (FIRST && valid) {
+                if (key[i] >= dims) { valid = false; atomicOr(bad, 1u); }
+                else if (dmask && dense_hit(s_dtab, key[i])) valid = false;
+            }
+            if (valid) vbits |= 1u << i;
             const uint32_t d = (key[i] >> shift) & (R - 1);
             const uint32_t active = __ballot_sync(0xffffffffu, valid);
             uint32_t peers = 0, prev = 0;
@@ -413,6 +585,7 @@ sort_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint2 *__restric
                 const uint32_t ex = wbase + inc - run;
                 dig_base[d] = ex;
                 gofs[d] = tile_hist[(size_t)s_toff[seg] * R + (size_t)d * nt + tis] - ex;
+                if (d == R - 1) s_ntile = ex + run;
             }
         }
         __syncthreads();
@@ -420,8 +593,7 @@ sort_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint2 *__restric
         // sixteen independent loads in flight per thread, no registers held across the ranking)
 #pragma unroll
         for (int i = 0; i < kScatItems; i++) {
-            const uint32_t e = ew + i * 32;
-            if (e < e1) {
+            if ((vbits >> i) & 1u) {
                 const uint32_t d = (key[i] >> shift) & (R - 1);
                 const uint32_t pos = dig_base[d] + wcnt[warp][d] + rank[i];
                 s_key[pos] = key[i];
@@ -433,7 +605,7 @@ sort_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint2 *__restric
             for (int q = threadIdx.x; q < kSortTile / 32; q += kScatThreads) s_mark[q] = 0;
             if (threadIdx.x == 0) s_dup = 0;
         }
-        const uint32_t n_tile = e1 - e0;
+        const uint32_t n_tile = s_ntile;
         // next tile's coordinates and keys (the key registers are free from here on)
         const uint32_t next = tile + gridDim.x;
         int nseg = 0; uint32_t ntis = 0, nnt = 0, ne0 = 0, ne1 = 0;
@@ -462,7 +634,7 @@ sort_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint2 *__restric
 
 int persistent_grid(int64_t work_items, int per_sm)
 {
-    int64_t cap = (int64_t)kNumSMs * per_sm;
+    int64_t cap = (int64_t)num_sms() * per_sm;
     if (work_items < 1) work_items = 1;
     return (int)(work_items < cap ? work_items : cap);
 }
@@ -473,9 +645,13 @@ hm_status sort_scratch_reserve(SortScratch &s, int64_t elems)
 {
     if (elems < 1) elems = 1;
     if (!s.seg_off) {
+        HM_CUDA(cudaMalloc(&s.in_off, (kMaxSegs + 1) * sizeof(uint32_t)));
+        HM_CUDA(cudaMalloc(&s.in_tile_off, (kMaxSegs + 1) * sizeof(uint32_t)));
         HM_CUDA(cudaMalloc(&s.seg_off, (kMaxSegs + 1) * sizeof(uint32_t)));
         HM_CUDA(cudaMalloc(&s.seg_tile_off, (kMaxSegs + 1) * sizeof(uint32_t)));
         HM_CUDA(cudaMalloc(&s.row_sum, (size_t)kMaxSegs * kMaxRadix * sizeof(uint32_t)));
+        HM_CUDA(cudaMalloc(&s.dense, sizeof(DenseInfo)));
+        HM_CUDA(cudaMemset(s.dense, 0, sizeof(DenseInfo)));
     }
     if (elems > s.cap_elems) {
         for (int b = 0; b < 2; b++) {
@@ -504,7 +680,9 @@ void sort_scratch_free(SortScratch &s)
 {
     for (int b = 0; b < 2; b++) { cudaFree(s.key[b]); cudaFree(s.pay[b]); s.key[b] = nullptr; s.pay[b] = nullptr; }
     cudaFree(s.tile_hist); cudaFree(s.row_sum); cudaFree(s.seg_off); cudaFree(s.seg_tile_off); cudaFree(s.tile_row0);
-    s.tile_hist = s.row_sum = s.seg_off = s.seg_tile_off = nullptr; s.tile_row0 = nullptr;
+    cudaFree(s.in_off); cudaFree(s.in_tile_off); cudaFree(s.dense);
+    s.tile_hist = s.row_sum = s.seg_off = s.seg_tile_off = s.in_off = s.in_tile_off = nullptr; s.tile_row0 = nullptr;
+    s.dense = nullptr;
     s.cap_elems = s.cap_tiles = 0;
 }
 
@@ -513,32 +691,57 @@ hm_status launch_seg_prep(Launcher &L, SortScratch &s, const int64_t *d_rowptr, 
 {
     if (n_segs < 1 || n_segs > kMaxSegs) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "segment count %d out of range", n_segs);
     HM_LAUNCH(L, K_SEG_PREP, 0.0,
-              (seg_prep_kernel<<<1, 256, 0, L.stream>>>(d_rowptr, row0, n_rows, mini_batch, n_segs, s.seg_off,
-                                                        s.seg_tile_off)));
-    // first row of every sort tile (one thread per tile; used by the first scatter pass)
+              (seg_prep_kernel<<<1, 256, 0, L.stream>>>(d_rowptr, row0, n_rows, mini_batch, n_segs, s.in_off,
+                                                        s.in_tile_off)));
+    // first row of every sort tile of the CSR (one thread per tile; used by the first scatter pass)
     const int64_t max_tiles = n_elems / kSortTile + n_segs;
     HM_LAUNCH(L, K_SEG_PREP, 0.0,
               (tile_row0_kernel<<<persistent_grid((max_tiles + 127) / 128, 8), 128, 0, L.stream>>>(
-                  d_rowptr, row0, n_rows, mini_batch, s.seg_off, s.seg_tile_off, n_segs, s.tile_row0)));
+                  d_rowptr, row0, n_rows, mini_batch, s.in_off, s.in_tile_off, n_segs, s.tile_row0)));
     HM_CUDA(cudaGetLastError());
     return HM_OK;
 }
 
+hm_status launch_dense_check(Launcher &L, SortScratch &s, const int64_t *d_rowptr, int64_t row0, int64_t n_rows,
+                             const uint32_t *d_feature, int64_t n_elems, int64_t dims, bool enable)
+{
+    if (!enable || n_rows < 1) {
+        HM_CUDA(cudaMemsetAsync(s.dense, 0, sizeof(DenseInfo), L.stream));
+        return HM_OK;
+    }
+    const int grid = persistent_grid((n_rows + kChkThreads / 32 - 1) / (kChkThreads / 32), 8);
+    HM_LAUNCH(L, K_SEG_PREP, 4.0 * (double)n_elems + 8.0 * (double)n_rows,
+              (dense_check_kernel<<<grid, kChkThreads, 0, L.stream>>>(d_rowptr, row0, n_rows, d_feature,
+                                                                     (uint32_t)std::min<int64_t>(dims, 0xffffffffLL), s.dense)));
+    HM_CUDA(cudaGetLastError());
+    return HM_OK;
+}
+
+namespace {
+template <class K>
+hm_status opt_in_smem(K kernel, size_t bytes)
+{
+    HM_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+    return HM_OK;
+}
+}  // namespace
+
 hm_status launch_segmented_sort(Launcher &L, SortScratch &s, const uint32_t *d_feature_block,
                                 const float *d_value_block, const int64_t *d_rowptr, int64_t block_row0,
                                 int64_t block_rows, int32_t mini_batch, int64_t n_elems, int n_segs, int key_bits,
-                                int *out_buf, int ctas_per_sm)
+                                int64_t dims, uint32_t *d_bad, int *out_buf, int ctas_per_sm)
 {
-    // > 48 KB of dynamic shared memory needs opting in, once per device
-    static bool attr_set[64] = {false};
+    // > 48 KB of dynamic shared memory needs opting in, once per device (the attribute is per
+    // device; the flags are atomics because learners on different threads may get here together)
+    static std::atomic<bool> attr_set[64];
     int dev = 0;
     HM_CUDA(cudaGetDevice(&dev));
-    if (dev < 0 || dev >= 64 || !attr_set[dev]) {
-        HM_CUDA(cudaFuncSetAttribute(sort_scatter_kernel<true, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kScatterSmem));
-        HM_CUDA(cudaFuncSetAttribute(sort_scatter_kernel<false, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kScatterSmem));
-        HM_CUDA(cudaFuncSetAttribute(sort_scatter_kernel<true, 9>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kScatterSmem));
-        HM_CUDA(cudaFuncSetAttribute(sort_scatter_kernel<false, 9>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kScatterSmem));
-        if (dev >= 0 && dev < 64) attr_set[dev] = true;
+    if (dev < 0 || dev >= 64 || !attr_set[dev].load(std::memory_order_acquire)) {
+        HM_TRY(opt_in_smem(sort_scatter_kernel<true, 8>, kScatterSmem));
+        HM_TRY(opt_in_smem(sort_scatter_kernel<false, 8>, kScatterSmem));
+        HM_TRY(opt_in_smem(sort_scatter_kernel<true, 9>, kScatterSmem));
+        HM_TRY(opt_in_smem(sort_scatter_kernel<false, 9>, kScatterSmem));
+        if (dev >= 0 && dev < 64) attr_set[dev].store(true, std::memory_order_release);
     }
     if (n_elems > s.cap_elems) HM_FAIL(HM_ERR_STATE, "sort scratch too small (%lld > %lld)", (long long)n_elems,
                                        (long long)s.cap_elems);
@@ -551,6 +754,7 @@ hm_status launch_segmented_sort(Launcher &L, SortScratch &s, const uint32_t *d_f
     // ctas_per_sm == 0: take the whole GPU; otherwise leave room for kernels of another stream
     const int grid = persistent_grid(max_tiles, ctas_per_sm > 0 ? ctas_per_sm : 6);
     const int hist_grid = persistent_grid(max_tiles, ctas_per_sm > 0 ? 2 * ctas_per_sm : 6);
+    const uint32_t dims32 = (uint32_t)std::min<int64_t>(dims, 0xffffffffLL);
     RowLookup rl;
     rl.rowptr = d_rowptr; rl.block_row0 = block_row0; rl.block_rows = block_rows; rl.mini_batch = mini_batch;
     rl.tile_row0 = s.tile_row0;
@@ -562,25 +766,29 @@ hm_status launch_segmented_sort(Launcher &L, SortScratch &s, const uint32_t *d_f
         const uint2 *pin = p == 0 ? nullptr : s.pay[(p - 1) & 1];
         uint32_t *kout = s.key[p & 1];
         uint2 *pout = s.pay[p & 1];
+        // the first pass walks the block's CSR, later passes the (shorter) sorted arrays
+        const uint32_t *off = p == 0 ? s.in_off : s.seg_off;
+        const uint32_t *toff = p == 0 ? s.in_tile_off : s.seg_tile_off;
         HM_CUDA(cudaMemsetAsync(s.row_sum, 0, (size_t)rows * sizeof(uint32_t), L.stream));
-        if (rb == 9)
-            HM_LAUNCH(L, K_SORT_HIST, 4.0 * (double)n_elems,
-                      (sort_hist_kernel<9><<<hist_grid, kSortThreads, 0, L.stream>>>(kin, s.seg_off, s.seg_tile_off, n_segs, shift,
-                                                                                s.tile_hist, s.row_sum)));
-        else
-            HM_LAUNCH(L, K_SORT_HIST, 4.0 * (double)n_elems,
-                      (sort_hist_kernel<8><<<hist_grid, kSortThreads, 0, L.stream>>>(kin, s.seg_off, s.seg_tile_off, n_segs, shift,
-                                                                                s.tile_hist, s.row_sum)));
-        HM_LAUNCH(L, K_SORT_SCAN, 0.0, (scan_rows_kernel<<<1, 1024, 0, L.stream>>>(s.row_sum, rows)));
+#define HM_HIST(RB_, FIRST_)                                                                                            \
+    HM_LAUNCH(L, K_SORT_HIST, 4.0 * (double)n_elems,                                                                     \
+              (sort_hist_kernel<RB_, FIRST_><<<hist_grid, kSortThreads, 0, L.stream>>>(kin, off, toff, n_segs, shift,  \
+                                                                                       s.tile_hist, s.row_sum, dims32, s.dense)))
+        if (p == 0) { if (rb == 9) HM_HIST(9, true); else HM_HIST(8, true); }
+        else { if (rb == 9) HM_HIST(9, false); else HM_HIST(8, false); }
+#undef HM_HIST
+        // (the first scan also writes the sorted arrays' mini-batch and tile offsets)
+        HM_LAUNCH(L, K_SORT_SCAN, 0.0, (scan_rows_kernel<<<1, 1024, 0, L.stream>>>(
+                                           s.row_sum, rows, p == 0 ? s.seg_off : nullptr, s.seg_tile_off, n_segs, 1 << rb)));
         HM_LAUNCH(L, K_SORT_SCAN, 0.0,
                   (scan_tiles_kernel<<<(rows + kSortWarps - 1) / kSortWarps, kSortThreads, 0, L.stream>>>(
-                      s.tile_hist, s.row_sum, s.seg_tile_off, n_segs, 1 << rb)));
+                      s.tile_hist, s.row_sum, toff, n_segs, 1 << rb)));
         const double bytes = p == 0 ? 20.0 * (double)n_elems + 8.0 * (double)block_rows : 24.0 * (double)n_elems;
 #define HM_SCATTER(FIRST_, RB_)                                                                                        \
     HM_LAUNCH(L, K_SORT_SCATTER, bytes,                                                                                 \
               (sort_scatter_kernel<FIRST_, RB_><<<grid, kScatThreads, kScatterSmem, L.stream>>>(                        \
-                  kin, pin, rl, p == 0 ? d_value_block : nullptr, kout, pout, s.seg_off, s.seg_tile_off, n_segs, shift, \
-                  s.tile_hist)))
+                  kin, pin, rl, p == 0 ? d_value_block : nullptr, kout, pout, off, toff, n_segs, shift,                 \
+                  s.tile_hist, dims32, s.dense, d_bad)))
         if (p == 0) { if (rb == 9) HM_SCATTER(true, 9); else HM_SCATTER(true, 8); }
         else { if (rb == 9) HM_SCATTER(false, 9); else HM_SCATTER(false, 8); }
 #undef HM_SCATTER

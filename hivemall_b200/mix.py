@@ -61,18 +61,38 @@ class ReplicaMixer:
                           for name, a in arrays.items() if a[2] == 0]
         self.bytes_per_mix = sum(t.numel() * 4 for t in self.tensors) + sum(t.numel() for t in self.byte_maps)
         self.mixes = 0
+        self._events = []      # (start, end) CUDA events of the timed mixes
 
-    def mix(self) -> None:
+    def mix(self, timed: bool = False) -> None:
         """All-reduce every replica array, then scale by 1/P with the library's own kernel.
-        Ordered after all training already queued on the learner's stream."""
+        Ordered after all training already queued on the learner's stream.  timed: bracket the
+        exchange (all-reduce + scale) with its own CUDA event pair on that stream (timed_ms)."""
         import torch
         import torch.distributed as dist
         if self.world == 1:
             return
+        ev = None
+        if timed:
+            ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+            with torch.cuda.stream(self.stream):
+                ev[0].record()
         with torch.cuda.stream(self.stream):
             for t in self.tensors:
                 dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.group)
             for t in self.byte_maps:
                 dist.all_reduce(t, op=dist.ReduceOp.MAX, group=self.group)
         self.udtf.scale_replica(1.0 / self.world)
+        if ev:
+            with torch.cuda.stream(self.stream):
+                ev[1].record()
+            self._events.append(ev)
         self.mixes += 1
+
+    def timed_ms(self) -> list:
+        """Durations (ms) of the mixes run with timed=True so far; waits for them, then forgets them."""
+        out = []
+        for a, b in self._events:
+            b.synchronize()
+            out.append(a.elapsed_time(b))
+        self._events = []
+        return out

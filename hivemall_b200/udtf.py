@@ -174,8 +174,7 @@ class UDTF:
         flat = [f for r in rows for f in r]
         if flat and isinstance(flat[0], (str, bytes)):
             data, offsets = _pack_strings(flat)
-            check(self._lib.hm_udtf_process_strings(self._h, len(rows), _ptr(rowptr), _ptr(data), _ptr(offsets),
-                                                    _ptr(labels)))
+            self.process_strings(rowptr, data, offsets, labels)
             self.sync()
         else:
             idx = np.asarray([f[0] for f in flat], dtype=np.int32)
@@ -229,6 +228,26 @@ class UDTF:
         """process_split() from raw HOST addresses (pinned buffers from host_alloc)."""
         check(self._lib.hm_udtf_process_split(self._h, n_rows, _ptr(q_rowptr), _ptr(q_feature), _ptr(q_value),
                                               _ptr(c_rowptr), _ptr(c_feature), _ptr(label)))
+
+    def process_strings(self, rowptr, data, offsets, label) -> None:
+        """process() of many rows whose features are still strings ("name:value" / "name"): int64 rowptr
+        over strings, uint8 `data` holding the strings back to back, int64 offsets (len = strings + 1).
+        The strings are hashed on the GPU straight into the learner's CSR.  Asynchronous like process_batch."""
+        rowptr = np.ascontiguousarray(rowptr, dtype=np.int64)
+        data = np.ascontiguousarray(data, dtype=np.uint8)
+        offsets = np.ascontiguousarray(offsets, dtype=np.int64)
+        label = np.ascontiguousarray(label, dtype=np.float32)
+        n = len(rowptr) - 1
+        if len(label) != n:
+            raise UDFArgumentError(1, f"label has {len(label)} entries for {n} rows")
+        if n and (rowptr[-1] >= len(offsets) or offsets[rowptr[-1]] > len(data)):
+            raise UDFArgumentError(1, "rowptr / offsets point past the end of the strings")
+        self._keep.append((rowptr, data, offsets, label))
+        check(self._lib.hm_udtf_process_strings(self._h, n, _ptr(rowptr), _ptr(data), _ptr(offsets), _ptr(label)))
+
+    def process_strings_pointers(self, n_rows: int, rowptr: int, data: int, offsets: int, label: int) -> None:
+        """process_strings() from raw HOST addresses (pinned buffers from host_alloc)."""
+        check(self._lib.hm_udtf_process_strings(self._h, n_rows, _ptr(rowptr), _ptr(data), _ptr(offsets), _ptr(label)))
 
     def process_device(self, n_rows: int, nnz: int, rowptr, feature, value, label) -> None:
         """process() of rows already in device memory (torch CUDA tensors or raw
@@ -363,6 +382,13 @@ class UDTF:
             out = np.empty(self.config.mini_batch, dtype=np.float32)
         n = C.c_int64()
         check(self._lib.hm_udtf_last_margins(self._h, _ptr(out), len(out), C.byref(n)))
+        return out[: n.value]
+
+    def dense_columns(self) -> np.ndarray:
+        """Features of the dense columns found in the most recently sorted block (int32, at most 32)."""
+        out = np.empty(32, dtype=np.int32)
+        n = C.c_int32()
+        check(self._lib.hm_udtf_dense_columns(self._h, _ptr(out), 32, C.byref(n)))
         return out[: n.value]
 
     # ---- measurement ---------------------------------------------------------------

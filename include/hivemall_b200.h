@@ -218,6 +218,15 @@ hm_status hm_udtf_predict_device(hm_udtf *u, int64_t n_rows, const int64_t *d_ro
  * into a loss.  Copies min(cap, rows) floats to `host`, waits for the GPU, sets *n. */
 hm_status hm_udtf_last_margins(hm_udtf *u, float *host, int64_t cap, int64_t *n);
 
+/* Dense columns of the most recently sorted ingest block (diagnostics, tests).  Rows usually
+ * start with their quantitative features ("name:value" with a fixed name), so position i of every
+ * row holds the same feature; the linear learners reduce such a column as a plain column sum
+ * instead of sorting it (same arithmetic contract, other -- fixed -- summation order).  Writes up
+ * to `cap` (at most 32) feature indices and sets *n to the number of dense columns; waits for the
+ * GPU.  Setting HM_DENSE_COLUMNS=0 in the environment before hm_udtf_create turns the detection
+ * off (every element is then sorted).  Stands in for nothing in the reference. */
+hm_status hm_udtf_dense_columns(hm_udtf *u, int32_t *feature, int32_t cap, int32_t *n);
+
 /* ---- model table without device allocation ---------------------------------- */
 
 /* Largest model hm_model_table_noalloc accepts (its built-in scratch is 64 KiB per GPU). */

@@ -85,6 +85,87 @@ def config_from(hm_cfg) -> HmoConfig:
     return c
 
 
+# Option strings without the product library: the same grammar and defaults as
+# hivemall_b200/csrc/hm_options.cpp, restated so that the CPU arm of bench.py (and nothing else)
+# can build an oracle config while its process maps only oracle/.  tests/test_options.py checks
+# the two parsers against each other.
+_ENUMS = {
+    "loss": {"logloss": 0, "logistic": 0, "log": 0, "hinge": 1, "hingeloss": 1, "squared": 2, "squaredloss": 2,
+             "squared_loss": 2},
+    "opt": {"sgd": 0, "adagrad": 1, "adadelta": 2, "adam": 3, "ftrl": 4},
+    "eta_sched": {"fixed": 0, "inverse": 1, "inv": 1, "invscaling": 1, "simple": 2},
+    "reg": {"no": 0, "none": 0, "l1": 1, "l2": 2},
+    "grad_norm": {"batch": 0, "count": 1, "sum": 2},
+}
+_OPTION_FIELDS = {
+    "-loss": ("loss", "enum"), "-loss_function": ("loss", "enum"), "-opt": ("opt", "enum"), "-optimizer": ("opt", "enum"),
+    "-mini_batch": ("mini_batch", int), "-mini_batch_size": ("mini_batch", int),
+    "-iters": ("iters", int), "-iter": ("iters", int), "-iterations": ("iters", int),
+    "-dims": ("dims", int), "-feature_dimensions": ("dims", int), "-p": ("dims", int), "-num_features": ("dims", int),
+    "-eta0": ("eta0", float), "-eta_0": ("eta0", float), "-eta": ("eta_sched", "enum"), "-power_t": ("power_t", float),
+    "-total_steps": ("total_steps", float), "-t": ("total_steps", float),
+    "-reg": ("reg", "enum"), "-regularization": ("reg", "enum"), "-lambda": ("lambda_", float), "-eps": ("eps", float),
+    "-rho": ("rho", float), "-decay": ("rho", float), "-beta1": ("beta1", float), "-beta2": ("beta2", float),
+    "-alpha": ("alpha", float), "-beta": ("beta", float), "-lambda1": ("lambda1", float), "-l1": ("lambda1", float),
+    "-lambda2": ("lambda2", float), "-l2": ("lambda2", float), "-grad_norm": ("grad_norm", "enum"),
+    "-factors": ("factors", int), "-factor": ("factors", int), "-f": ("factors", int), "-k": ("factors", int),
+    "-sigma": ("sigma", float), "-lambda0": ("lambda_w0", float), "-lambda_w0": ("lambda_w0", float),
+    "-lambdaW": ("lambda_w", float), "-lambda_w": ("lambda_w", float), "-lambdaV": ("lambda_v", float),
+    "-lambda_v": ("lambda_v", float), "-seed": ("seed", int),
+    "-hash_seed": (None, int), "-mix_interval": (None, int),     # not oracle fields
+}
+
+
+def config_from_options(function_name: str, options: str = "") -> HmoConfig:
+    """Oracle config of a UDTF option string (no product code involved)."""
+    task = {"train_classifier": 0, "train_regressor": 1, "train_fm": 2}[function_name]
+    c = HmoConfig()
+    c.task = task
+    c.loss = 2 if task == 1 else 0
+    c.opt = 0 if task == 2 else 1
+    c.eta_sched, c.reg, c.grad_norm, c.mini_batch, c.iters = 0, 0, 0, 1, 1
+    c.dims, c.total_steps = 1 << 24, 10000.0
+    c.eta0, c.power_t, c.lambda_, c.eps, c.rho = (0.05 if task == 2 else 0.1), 0.1, 1e-4, 1e-6, 0.95
+    c.beta1, c.beta2, c.alpha, c.beta, c.lambda1, c.lambda2 = 0.9, 0.999, 0.1, 1.0, 0.001, 0.0
+    c.factors, c.fm_classification, c.sigma = 5, 0, 0.1
+    c.lambda_w0 = c.lambda_w = c.lambda_v = 0.01
+    c.seed = 31
+    tok = options.split()
+    i = 0
+    while i < len(tok):
+        name = tok[i]
+        i += 1
+        if name in ("-classification", "-c"):
+            if task != 2:
+                raise ValueError(f"{name} is a train_fm option")
+            c.fm_classification = 1
+            continue
+        if name in ("-dense", "-densemodel"):
+            continue
+        if name not in _OPTION_FIELDS:
+            raise ValueError(f"unknown option {name!r}")
+        if i >= len(tok):
+            raise ValueError(f"option {name!r} needs a value")
+        field, kind = _OPTION_FIELDS[name]
+        v = tok[i]
+        i += 1
+        if field is None:
+            continue
+        if kind == "enum":
+            table = _ENUMS[field]
+            if v.lower() not in table:
+                raise ValueError(f"option {name}: unknown value {v!r}")
+            setattr(c, field, table[v.lower()])
+        else:
+            setattr(c, field, kind(v))
+    if task == 1 and c.loss != 2:
+        raise ValueError("train_regressor supports -loss squared only")
+    if task == 2:
+        c.loss = 0 if c.fm_classification else 2
+        c.task = 1          # (as config_from: the FM entry points do not read it)
+    return c
+
+
 def murmur3(data: bytes, seed: int) -> int:
     return lib().hmo_murmur3_x86_32(data, len(data), seed & 0xFFFFFFFF)
 

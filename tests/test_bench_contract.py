@@ -24,6 +24,25 @@ def test_reference_arm_prints_the_contract_line():
     e = j["e2e"]
     assert e["value"] == j["value"] and e["h2d_bytes_per_step"] == 0 and e["d2h_bytes_per_step"] == 0
     assert j["gpu_launches"] == 0
+    # the same config object as the GPU arm prints for these arguments (vs_reference.same_config)
+    sys.path.insert(0, ROOT)
+    import bench
+    wl = bench.WORKLOADS["ftrl"]
+    assert j["config"] == bench.config_of(wl, bench.MINI_BATCH, bench.ROWS_PER_STEP, 1, 1, 0, wl["total_rows"])
+    assert j["config"]["rows_per_step"] == bench.ROWS_PER_STEP
+
+
+def test_reference_arm_does_not_load_the_product():
+    """The CPU arm's process maps oracle/ only: importing bench and building its oracle config must not
+    import hivemall_b200 (synth.py is loaded by path)."""
+    code = ("import sys; sys.argv=['bench.py']; import bench; sys.path.insert(0, 'tests'); import _oracle; "
+            "bench.make_rows(bench.WORKLOADS['ftrl'], 8, 0); "
+            "_oracle.config_from_options('train_classifier', bench.options_of(bench.WORKLOADS['ftrl'])); "
+            "assert 'hivemall_b200' not in sys.modules, sorted(m for m in sys.modules if 'hivemall' in m); "
+            "print(open('/proc/self/maps').read().count('libhivemall_b200'))")
+    out = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=300, cwd=ROOT)
+    assert out.returncode == 0, out.stderr[-2000:]
+    assert out.stdout.strip() == "0"
 
 
 def test_workload_table():
@@ -32,10 +51,14 @@ def test_workload_table():
     import hivemall_b200 as hm
     assert set(bench.WORKLOADS) == {"ftrl", "adagrad", "fm16", "adam26", "fm64"}
     for name, wl in bench.WORKLOADS.items():
-        cfg = hm.parse_options(wl["fn"], wl["options"])          # every option string parses
+        cfg = hm.parse_options(wl["fn"], bench.options_of(wl))   # every option string parses
         assert cfg.dims == wl["dims"] and cfg.mini_batch == bench.MINI_BATCH, name
+        assert hm.parse_options(wl["fn"], bench.options_of(wl, 128)).mini_batch == 128
+        bpe = bench.bytes_per_example(wl)
+        assert bpe["bytes"] == bpe["ingest"] + bpe["forward"] + bpe["update"]
         rows = bench.make_rows(wl, 64, 0)
         rp, f, v, y = rows.numpy()
         assert len(y) == 64 and rp[-1] == 64 * wl["nnz"] and f.max() < wl["dims"]
         if wl["gen"] == "kdd12":
             assert (v == 1.0).all()
+    assert bench.bytes_per_example(bench.WORKLOADS["ftrl"])["bytes"] == 1412

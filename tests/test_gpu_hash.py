@@ -69,3 +69,41 @@ def test_process_strings_equals_process_indices():
     b.close()
     assert np.array_equal(a.array_to_host("w"), b.array_to_host("w"))
     assert np.count_nonzero(a.array_to_host("w")) > 0
+
+
+def test_process_strings_many_slices_bit_identical():
+    """Rows pushed as feature strings are hashed on the device straight into the learner's CSR.  Several
+    H2D slices, two pushes, a tail that carries over: the model is bit-identical to pushing the
+    indices / values that the feature_hashing UDF returns for the same strings."""
+    n_rows, per_row, dims = 300_000, 7, 1 << 18
+    rng = np.random.default_rng(5)
+    cat = (rng.random((n_rows, per_row)) ** 3 * 50_000).astype(np.int64)
+    val = np.round(rng.random((n_rows, per_row)) * 4, 3)
+    cols = []
+    for j in range(per_row):
+        if j < 2:
+            cols.append(np.char.add(f"q{j}:", val[:, j].astype(str)))
+        else:
+            cols.append(np.char.add(f"c{j}=", cat[:, j].astype(str)))
+    enc = np.char.encode(np.stack(cols, axis=1).reshape(-1), "ascii")
+    lens = np.char.str_len(enc).astype(np.int64)
+    offsets = np.zeros(len(enc) + 1, dtype=np.int64)
+    offsets[1:] = np.cumsum(lens)
+    data = np.frombuffer(b"".join(enc.tolist()), dtype=np.uint8)
+    rowptr = np.arange(n_rows + 1, dtype=np.int64) * per_row
+    label = (rng.random(n_rows) < 0.3).astype(np.float32)
+    opts = f"-loss logloss -opt ftrl -mini_batch 4096 -dims {dims} -alpha 0.05"
+    cut = 170_001
+    a = hm.train_classifier(opts)
+    a.process_strings(rowptr[: cut + 1], data, offsets, label[:cut])
+    a.process_strings(rowptr[cut:], data, offsets, label[cut:])
+    a.close()
+    idx, v = hm.feature_hashing([bytes(e) for e in enc.tolist()], num_features=dims)
+    assert np.array_equal(v.reshape(n_rows, per_row)[:, :2], val[:, :2].astype(np.float32))
+    b = hm.train_classifier(opts)
+    b.process_batch(rowptr, idx, v, label)
+    b.close()
+    assert np.array_equal(a.array_to_host("state"), b.array_to_host("state"))
+    assert np.count_nonzero(a.array_to_host("w")) > 1000
+    a.destroy()
+    b.destroy()

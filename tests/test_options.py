@@ -58,3 +58,23 @@ def test_error_names_the_offending_token():
     with pytest.raises(hm.UDFArgumentError) as e:
         hm.parse_options("train_classifier", "-opt adagrad -frobnicate 3")
     assert "-frobnicate" in str(e.value)
+
+
+@pytest.mark.parametrize("fn,opts", [
+    ("train_classifier", "-loss logloss -opt AdaGrad -mini_batch 128"),
+    ("train_classifier", "-loss logloss -opt ftrl -mini_batch 65536 -dims 16777216 -alpha 0.05 -lambda1 0.0001"),
+    ("train_classifier", "-loss hinge -opt adadelta -rho 0.9 -eps 1e-7 -reg l1 -lambda 0.001 -grad_norm sum"),
+    ("train_regressor", "-loss squared -opt adam -mini_batch 65536 -dims 67108864 -eta0 0.001 -beta1 0.8"),
+    ("train_regressor", "-eta inverse -eta0 0.3 -power_t 0.2 -total_steps 500 -iters 3 -mix_interval 64 -hash_seed 7"),
+    ("train_fm", "-factors 16 -classification -opt adagrad -mini_batch 65536 -dims 16777216 -eta0 0.05"),
+    ("train_fm", "-factors 8 -sigma 0.2 -lambda0 0.1 -lambdaW 0.2 -lambdaV 0.3 -seed 5"),
+    ("train_fm", ""),
+])
+def test_oracle_side_parser_agrees_with_the_library(fn, opts):
+    """bench.py's CPU arm builds its oracle config with tests/_oracle.config_from_options so that its
+    process never loads the product library; the two parsers must agree field by field."""
+    import _oracle
+    a = _oracle.config_from(hm.parse_options(fn, opts))
+    b = _oracle.config_from_options(fn, opts)
+    for name, _ in _oracle.HmoConfig._fields_:
+        assert getattr(a, name) == getattr(b, name), name

@@ -95,6 +95,9 @@ def np_train(cfg, rowptr, feat, val, label):
                     cnts[j] = cnts.get(j, 0) + 1
             t += 1
             eta = F(_oracle.lib().hmo_eta(cfg, t))
+            # Adam's bias-corrected step size, in fp64 on the host side of both implementations
+            alpha_t = F(float(eta) * np.sqrt(1.0 - float(F(cfg.beta2)) ** t) / (1.0 - float(F(cfg.beta1)) ** t)) \
+                if cfg.opt == 3 else F(0.0)
             for j, sm in sums.items():
                 g = F(sm * (1.0 / float(b1 - b0))) if cfg.grad_norm == 0 else (F(sm / float(cnts[j])) if cfg.grad_norm == 1 else F(sm))
                 wv = w[j]
@@ -116,8 +119,25 @@ def np_train(cfg, rowptr, feat, val, label):
                         sg = F(-1.0) if z < 0 else F(1.0)
                         wv = F(-F(F(z - F(sg * F(cfg.lambda1))) /
                                   F(F(F(F(cfg.beta) + np.sqrt(n1)) / F(cfg.alpha)) + F(cfg.lambda2))))
+                elif cfg.opt == 2:      # AdaDelta: (s1, s2) = (E[g^2], E[dx^2])
+                    rho, eps = F(cfg.rho), F(cfg.eps)
+                    omr = F(F(1.0) - rho)
+                    E = F(F(rho * s1[j]) + F(F(omr * g) * g))
+                    dx = F(F(np.sqrt(F(s2[j] + eps)) / np.sqrt(F(E + eps))) * g)
+                    s2[j] = F(F(rho * s2[j]) + F(F(omr * dx) * dx))
+                    s1[j] = E
+                    wv = F(wv - dx)
+                elif cfg.opt == 3:      # Adam: (s1, s2) = (m, v)
+                    be1, be2 = F(cfg.beta1), F(cfg.beta2)
+                    m = F(F(be1 * s1[j]) + F(F(F(1.0) - be1) * g))
+                    v = F(F(be2 * s2[j]) + F(F(F(F(1.0) - be2) * g) * g))
+                    s1[j], s2[j] = m, v
+                    wv = F(wv - F(F(alpha_t * m) / F(np.sqrt(v) + F(cfg.eps))))
                 else:
                     raise NotImplementedError
+                if cfg.reg == 1 and cfg.opt != 4:      # L1: soft threshold by eta * lambda after the step
+                    a = F(abs(wv) - F(eta * F(cfg.lambda_)))
+                    wv = F(np.copysign(a, wv)) if a > 0 else F(0.0)
                 w[j] = wv
     return w, s1, s2, t
 
@@ -128,6 +148,11 @@ def np_train(cfg, rowptr, feat, val, label):
     ("-loss hinge -opt adagrad -mini_batch 5 -dims 50 -grad_norm count", "train_classifier"),
     ("-loss logloss -opt ftrl -mini_batch 11 -dims 50 -alpha 0.5 -lambda1 0.01 -lambda2 0.1", "train_classifier"),
     ("-loss squared -opt adagrad -mini_batch 9 -dims 50 -reg l2 -lambda 0.1 -eta inverse", "train_regressor"),
+    ("-loss logloss -opt adadelta -mini_batch 8 -dims 50 -rho 0.9 -eps 1e-5 -iters 2", "train_classifier"),
+    ("-loss squared -opt adadelta -mini_batch 13 -dims 50 -grad_norm sum", "train_regressor"),
+    ("-loss logloss -opt adam -mini_batch 6 -dims 50 -eta0 0.05 -iters 3", "train_classifier"),
+    ("-loss squared -opt adam -mini_batch 10 -dims 50 -eta0 0.01 -beta1 0.8 -beta2 0.99 -eta simple -total_steps 30", "train_regressor"),
+    ("-loss hinge -opt sgd -mini_batch 7 -dims 50 -reg l1 -lambda 0.01 -eta0 0.3", "train_classifier"),
 ])
 def test_oracle_matches_numpy_restatement(options, fn):
     data = synth.ragged(120, dims=50, max_nnz=9, seed=2, regression=(fn == "train_regressor"))

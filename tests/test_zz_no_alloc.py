@@ -13,6 +13,8 @@ import pytest
 import hivemall_b200 as hm
 from hivemall_b200 import synth, udtf
 
+import _oracle
+
 pytestmark = pytest.mark.gpu
 
 
@@ -52,6 +54,10 @@ def test_two_calls_in_a_row_match_the_allocating_entry_point():
         assert np.array_equal(got_f[:n], want_f)           # bit-exact feature order
         assert np.array_equal(got_w[:n], want_w)           # weights are copies: bit-exact too
         assert (got_f[n:] == -7).all()                     # nothing written past the table
+        # and against the CPU oracle's model table of the same dense weights (not only against the
+        # library's own allocating path)
+        ora_f, ora_w = _oracle.model_table(u.array_to_host("w"))
+        assert np.array_equal(got_f[:n], ora_f) and np.array_equal(got_w[:n], ora_w)
     # and once more on the first model: leftovers of a smaller call do not leak into a larger one
     want_f, want_w = a.forward()
     n, got_f, got_w = _noalloc_table(a, cap=len(want_f))
