@@ -16,7 +16,7 @@ LIB = os.path.join(ROOT, "hivemall_b200", "libhivemall_b200.so")
 ORACLE_DIR = os.path.join(ROOT, "oracle")
 ORACLE_LIB = os.path.join(ORACLE_DIR, "_build", "libhm_oracle.so")
 
-SOURCES = ["hm_options.cpp", "hm_hash.cu", "hm_sort.cu", "hm_linear.cu", "hm_fm.cu", "hm_learner.cu"]
+SOURCES = ["hm_options.cpp", "hm_table.cpp", "hm_hash.cu", "hm_sort.cu", "hm_linear.cu", "hm_fm.cu", "hm_learner.cu"]
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",

@@ -20,7 +20,7 @@ void set_error(const char *fmt, ...);
 enum KernelId {
     K_HASH = 0, K_SEG_PREP, K_SORT_HIST, K_SORT_SCAN, K_SORT_SCATTER,
     K_LIN_FORWARD, K_LIN_UPDATE, K_FM_FORWARD, K_FM_UPDATE, K_PREDICT,
-    K_EXPORT, K_MISC, K_NUM_KERNELS
+    K_EXPORT, K_MISC, K_DENSE_CHECK, K_NUM_KERNELS
 };
 extern const char *const kKernelNames[K_NUM_KERNELS];
 
@@ -60,7 +60,10 @@ struct DenseInfo {
     uint32_t mask;        // bit i: position i is a dense column of this block
     uint32_t count;       // popcount(mask)
     uint32_t key[32];     // feature of position i (valid where the bit is set)
-    uint32_t noteq, collide, ticket, pad;   // work area of the check kernel (left zeroed)
+    uint32_t unit;        // 1: every element that IS sorted has value 1.0 (index-only features): the sort then
+                          // moves packed (feature, row) records of 8 bytes and no value at all
+    uint32_t noteq, collide, ticket, nonunit_pos, nonunit_other;   // work area of the check kernel (left zeroed)
+    uint32_t pad[2];
 };
 
 // ---- segmented radix sort (hm_sort.cu) ----------------------------------------
@@ -68,8 +71,9 @@ constexpr int kMaxSegs = 256;          // mini-batches sorted per launch
 constexpr int kSortTile = 4096;        // elements per sort tile
 struct SortScratch {
     // device
-    uint32_t *key[2] = {nullptr, nullptr};   // feature ids, ping-pong
-    uint2 *pay[2] = {nullptr, nullptr};      // (row inside the mini-batch, value bits), ping-pong
+    uint32_t *key[2] = {nullptr, nullptr};   // feature ids, ping-pong (unused when the block's values are all 1.0)
+    uint2 *pay[2] = {nullptr, nullptr};      // (row inside the mini-batch, value bits), ping-pong; DenseInfo::unit:
+                                             // packed (feature, row inside the mini-batch) records instead
     uint32_t *tile_hist = nullptr;     // [seg][digit][tile_in_seg]
     int32_t *tile_row0 = nullptr;      // first row (inside its mini-batch) of every tile
     uint32_t *row_sum = nullptr;       // [seg*256 + digit] (+1)
@@ -91,7 +95,7 @@ hm_status launch_seg_prep(Launcher &L, SortScratch &s, const int64_t *d_rowptr, 
                           int64_t n_rows, int64_t n_elems, int32_t mini_batch, int n_segs);
 // Find the dense columns of rows [row0, row0+n_rows) (s.dense); `enable` false: none.
 hm_status launch_dense_check(Launcher &L, SortScratch &s, const int64_t *d_rowptr, int64_t row0, int64_t n_rows,
-                             const uint32_t *d_feature, int64_t n_elems, int64_t dims, bool enable);
+                             const uint32_t *d_feature, const float *d_value, int64_t n_elems, int64_t dims, bool enable);
 // Stable sort of each segment by the low `key_bits` bits of the feature id.
 // Result: s.key[*out_buf], s.pay[*out_buf] hold (feature, (row, value)) sorted per segment.
 hm_status launch_segmented_sort(Launcher &L, SortScratch &s, const uint32_t *d_feature_block,

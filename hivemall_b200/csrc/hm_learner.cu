@@ -107,10 +107,22 @@ struct DevBuf {
     template <class T> T *as() const { return reinterpret_cast<T *>(p); }
 };
 
+// The sort result of one ingest block, kept for the later passes of -iters > 1: the sort depends
+// on the rows only, so a replay of retained rows needs no sort_* launch at all.
+struct SortedBlock {
+    int64_t row0 = 0, rows = 0, nnz = 0;
+    int n_segs = 0;
+    void *mem = nullptr;                // one allocation: key | pay | seg_off | dense
+    uint32_t *key = nullptr; uint2 *pay = nullptr; uint32_t *seg_off = nullptr; DenseInfo *dense = nullptr;
+    bool dense_on = false;
+};
+
 // A run of rows resident on the device.  Owned chunks hold copies of host data (rowptr is
 // 0-based inside the chunk); views alias caller memory (hm_udtf_process_device).
 struct Chunk {
     bool view = false;
+    std::vector<SortedBlock> sorted;    // -iters > 1: the blocks of the first pass, in row order
+    bool sorted_valid = true;           // false: a block could not be kept (memory): replays sort again
     int64_t rows = 0;                   // rows whose mini-batches are listed in mb_abs
     DevBuf rowptr, feat, val, label;    // owned storage
     DevBuf sq_rp, sc_rp, sq_feat, sq_val, sc_feat;   // split pushes: the two groups as they arrive, merged on the device
@@ -124,11 +136,17 @@ struct Chunk {
     const uint32_t *ft() const { return view ? v_feat : feat.as<uint32_t>(); }
     const float *vl() const { return view ? v_val : val.as<float>(); }
     const float *lb() const { return view ? v_label : label.as<float>(); }
+    void drop_sorted()
+    {
+        for (SortedBlock &b : sorted) if (b.mem) cudaFree(b.mem);
+        sorted.clear();
+    }
     void release()
     {
         rowptr.release(); feat.release(); val.release(); label.release();
         sq_rp.release(); sc_rp.release(); sq_feat.release(); sq_val.release(); sc_feat.release();
         str_bytes.release(); str_off.release();
+        drop_sorted();
         if (free_ev) cudaEventDestroy(free_ev);
         free_ev = nullptr;
     }
@@ -233,7 +251,7 @@ struct hm_udtf {
     UpdateScratch upd;
     ExportScratch exp;
     DevBuf margin, dloss, mb_gather, exp_feat, exp_weight, tmp_a, tmp_b, tmp_c, tmp_d;
-    uint32_t *d_bad = nullptr;
+    uint32_t *d_bad = nullptr;       // [0]: a training row held an index outside [0, dims); [1]: a scored row did
     int64_t *d_total = nullptr;
     // data
     std::vector<Chunk *> retained;   // pass-1 chunks kept for -iters > 1
@@ -320,8 +338,15 @@ WeightView weight_view(const hm_udtf *u)
 // The rows are cut into blocks (<= kMaxSegs mini-batches, <= kBlockElemCap elements).  Sorting a
 // block needs only the data, so block k+1 is sorted on the sort stream while block k trains on
 // the compute stream (two scratch sets, two events each way).
-hm_status train_rows(hm_udtf *u, const Chunk &c, int64_t row0, int64_t n_rows, const int64_t *mb_abs, int64_t n_mb,
-                     bool rows_ready = false)
+//
+// -iters > 1: the first pass keeps every block's sort result with the chunk (kTrainKeep) when device memory
+// allows, and the later passes (kTrainReplay, rows [0, c.rows) with the chunk's own mb_abs) train straight
+// from those: no sort_* kernel is launched again.
+enum TrainMode { kTrainPlain = 0, kTrainKeep = 1, kTrainReplay = 2 };
+constexpr size_t kKeepFreeFloor = (size_t)6 << 30;     // stop keeping sort results when less than this stays free
+
+hm_status train_rows(hm_udtf *u, Chunk &c, int64_t row0, int64_t n_rows, const int64_t *mb_abs, int64_t n_mb,
+                     bool rows_ready = false, TrainMode mode = kTrainPlain)
 {
     if (n_rows <= 0) return HM_OK;
     const int32_t B = u->cfg.mini_batch;
@@ -330,6 +355,24 @@ hm_status train_rows(hm_udtf *u, const Chunk &c, int64_t row0, int64_t n_rows, c
     a.cfg = u->cfg; a.rec = u->rec; a.rec_width = u->rec_width; a.wv = weight_view(u);
     struct Plan { int64_t m0, m1, row0, rows, nnz; int n_segs; };
     std::vector<Plan> plan;
+    // A replay trains from the kept blocks when they tile the chunk's rows, in the first pass's order.
+    bool replay = false;
+    if (mode == kTrainReplay && c.sorted_valid && !c.sorted.empty() && row0 == 0) {
+        int64_t next = 0;
+        for (const SortedBlock &b : c.sorted) { if (b.row0 != next) { next = -1; break; } next += b.rows; }
+        replay = next == n_rows;
+    }
+    if (replay) {
+        for (const SortedBlock &b : c.sorted) {
+            Plan p;
+            p.m0 = b.row0 / B; p.m1 = p.m0 + b.n_segs; p.n_segs = b.n_segs;     // (only a chunk's last mini-batch is short)
+            p.row0 = b.row0; p.rows = b.rows; p.nnz = b.nnz;
+            plan.push_back(p);
+        }
+        // the kept blocks were written by copies on the sort stream
+        HM_CUDA(cudaEventRecord(u->ready_ev, u->sorter));
+        HM_CUDA(cudaStreamWaitEvent(u->compute, u->ready_ev, 0));
+    } else {
     // Blocks of about kBlockElemTarget elements, evenly sized: the call's elements are cut into
     // ceil(total / target) blocks at the mini-batch boundaries nearest to equal shares (never more than
     // kMaxSegs mini-batches or kBlockElemCap elements, at least one mini-batch).
@@ -353,6 +396,7 @@ hm_status train_rows(hm_udtf *u, const Chunk &c, int64_t row0, int64_t n_rows, c
         plan.push_back(p);
         m0 = m1;
     }
+    }
     // Rows that were copied in by this library: everything queued on the compute stream so far
     // (their copies included) precedes the sorts.  Rows that are already resident (device views,
     // replays of retained chunks) need no such wait: the sort only reads data, so it may start
@@ -373,21 +417,50 @@ hm_status train_rows(hm_udtf *u, const Chunk &c, int64_t row0, int64_t n_rows, c
         // the scratch set is free once the block that used it last has been trained
         if (u->trained_valid[set]) HM_CUDA(cudaStreamWaitEvent(u->sorter, u->trained_ev[set], 0));
         HM_TRY(sort_scratch_reserve(u->sort[set], p.nnz));
-        HM_TRY(launch_dense_check(u->Ls, u->sort[set], c.rp(), p.row0, p.rows, c.ft(), p.nnz, u->cfg.dims, dense_on));
+        HM_TRY(launch_dense_check(u->Ls, u->sort[set], c.rp(), p.row0, p.rows, c.ft(), c.vl(), p.nnz, u->cfg.dims, dense_on));
         HM_TRY(launch_seg_prep(u->Ls, u->sort[set], c.rp(), p.row0, p.rows, p.nnz, B, p.n_segs));
         HM_TRY(launch_segmented_sort(u->Ls, u->sort[set], c.ft() + mb_abs[p.m0], c.vl() + mb_abs[p.m0], c.rp(), p.row0,
                                      p.rows, B, p.nnz, p.n_segs, key_bits, u->cfg.dims, u->d_bad, &out_buf[set], 0));
         HM_CUDA(cudaEventRecord(u->sorted_ev[set], u->sorter));
+        if (mode == kTrainKeep && c.sorted_valid) {
+            // keep the result for the later passes (device-to-device, on the sort stream, behind the event
+            // training waits for)
+            const size_t key_b = ((size_t)p.nnz * 4 + 255) & ~(size_t)255, pay_b = ((size_t)p.nnz * 8 + 255) & ~(size_t)255;
+            const size_t off_b = ((size_t)(p.n_segs + 1) * 4 + 255) & ~(size_t)255;
+            const size_t need = key_b + pay_b + off_b + sizeof(DenseInfo);
+            size_t free_b = 0, total_b = 0;
+            SortedBlock sb;
+            if (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess && free_b > need + kKeepFreeFloor &&
+                cudaMalloc(&sb.mem, need) == cudaSuccess) {
+                char *base = static_cast<char *>(sb.mem);
+                sb.key = reinterpret_cast<uint32_t *>(base);
+                sb.pay = reinterpret_cast<uint2 *>(base + key_b);
+                sb.seg_off = reinterpret_cast<uint32_t *>(base + key_b + pay_b);
+                sb.dense = reinterpret_cast<DenseInfo *>(base + key_b + pay_b + off_b);
+                sb.row0 = p.row0; sb.rows = p.rows; sb.nnz = p.nnz; sb.n_segs = p.n_segs; sb.dense_on = dense_on;
+                const SortScratch &ss = u->sort[set];
+                // (the sorted arrays are at most nnz long; the tail past the sorted length is never read)
+                HM_CUDA(cudaMemcpyAsync(sb.key, ss.key[out_buf[set]], (size_t)p.nnz * 4, cudaMemcpyDeviceToDevice, u->sorter));
+                HM_CUDA(cudaMemcpyAsync(sb.pay, ss.pay[out_buf[set]], (size_t)p.nnz * 8, cudaMemcpyDeviceToDevice, u->sorter));
+                HM_CUDA(cudaMemcpyAsync(sb.seg_off, ss.seg_off, (size_t)(p.n_segs + 1) * 4, cudaMemcpyDeviceToDevice, u->sorter));
+                HM_CUDA(cudaMemcpyAsync(sb.dense, ss.dense, sizeof(DenseInfo), cudaMemcpyDeviceToDevice, u->sorter));
+                c.sorted.push_back(sb);
+            } else {
+                cudaGetLastError();
+                c.sorted_valid = false;      // not enough memory: this chunk's replays sort again
+                c.drop_sorted();
+            }
+        }
         return HM_OK;
     };
     // While per-kernel profiling is on, the two streams are serialised so that every kernel is
     // timed alone (overlapped kernels stretch each other's event-to-event time).
     const bool overlap = !u->L.profiling;
-    HM_TRY(enqueue_sort(0));
+    if (!replay) HM_TRY(enqueue_sort(0));
     for (size_t bi = 0; bi < plan.size(); bi++) {
         const Plan &p = plan[bi];
         const int set = (int)((u->sort_turn + bi) & 1);
-        if (bi + 1 < plan.size()) {
+        if (!replay && bi + 1 < plan.size()) {
             if (!overlap) {     // the next sort starts only after everything queued for training so far
                 HM_CUDA(cudaEventRecord(u->ready_ev, u->compute));
                 HM_CUDA(cudaStreamWaitEvent(u->sorter, u->ready_ev, 0));
@@ -397,9 +470,16 @@ hm_status train_rows(hm_udtf *u, const Chunk &c, int64_t row0, int64_t n_rows, c
                 HM_CUDA(cudaStreamWaitEvent(u->compute, u->sorted_ev[(u->sort_turn + bi + 1) & 1], 0));
             }
         }
-        HM_CUDA(cudaStreamWaitEvent(u->compute, u->sorted_ev[set], 0));
-        SortScratch &ss = u->sort[set];
-        const int buf = out_buf[set];
+        if (!replay) HM_CUDA(cudaStreamWaitEvent(u->compute, u->sorted_ev[set], 0));
+        // where this block's sorted arrays are: the scratch set, or the block kept by the first pass
+        SortScratch view;
+        const int buf = replay ? 0 : out_buf[set];
+        if (replay) {
+            const SortedBlock &sb = c.sorted[bi];
+            view.key[0] = sb.key; view.pay[0] = sb.pay; view.seg_off = sb.seg_off; view.dense = sb.dense;
+        }
+        SortScratch &ss = replay ? view : u->sort[set];
+        const bool block_dense = replay ? c.sorted[bi].dense_on : dense_on;
         HM_TRY(u->margin.reserve((size_t)p.rows * sizeof(float)));
         HM_TRY(u->dloss.reserve((size_t)std::min<int64_t>(p.rows, B) * sizeof(float)));
         if (u->fm) {
@@ -409,7 +489,7 @@ hm_status train_rows(hm_udtf *u, const Chunk &c, int64_t row0, int64_t n_rows, c
             HM_TRY(u->stab.reserve((size_t)std::min<int64_t>(p.rows, B) * u->k * sizeof(float)));
         }
         DenseCols dc;
-        if (dense_on) { dc.info = ss.dense; dc.partial = u->upd.dense_partial; dc.stride = u->upd.dense_stride; }
+        if (block_dense) { dc.info = ss.dense; dc.partial = u->upd.dense_partial; dc.stride = u->upd.dense_stride; }
         if (!u->fm && small_batch_eligible(B, call_max_mb)) {
             // a few hundred rows per mini-batch: up to 64 mini-batches per launch of one persistent CTA
             for (int s0 = 0; s0 < p.n_segs; s0 += 64) {
@@ -456,12 +536,14 @@ hm_status train_rows(hm_udtf *u, const Chunk &c, int64_t row0, int64_t n_rows, c
             u->last_margin_off = mrow0 - p.row0;
             u->last_margin_n = mrows;
         }
-        HM_CUDA(cudaEventRecord(u->trained_ev[set], u->compute));
-        u->trained_valid[set] = true;
+        if (!replay) {
+            HM_CUDA(cudaEventRecord(u->trained_ev[set], u->compute));
+            u->trained_valid[set] = true;
+        }
         u->stats.rows += p.rows;
         u->stats.nnz += p.nnz;
     }
-    u->sort_turn += plan.size();
+    if (!replay) u->sort_turn += plan.size();
     return HM_OK;
 }
 
@@ -500,6 +582,8 @@ hm_status retire_chunk(hm_udtf *u, Chunk *c, bool retain)
     HM_CUDA(cudaEventRecord(c->free_ev, u->compute));
     c->rows = 0;
     c->mb_abs.clear();
+    c->drop_sorted();          // (cudaFree waits for the device: only ever non-empty with -iters > 1)
+    c->sorted_valid = true;
     u->pool.push_back(c);
     return HM_OK;
 }
@@ -675,7 +759,7 @@ hm_status process_slice(hm_udtf *u, const HostRows &h)
     c->rows = train;
     c->mb_abs.resize((size_t)n_mb + 1);
     for (int64_t i = 0; i <= n_mb; i++) c->mb_abs[(size_t)i] = st[i * B];
-    HM_TRY(train_rows(u, *c, 0, train, c->mb_abs.data(), n_mb, true));
+    HM_TRY(train_rows(u, *c, 0, train, c->mb_abs.data(), n_mb, true, u->cfg.iters > 1 ? kTrainKeep : kTrainPlain));
 
     // what is left waits in this chunk
     u->tail = c;
@@ -729,8 +813,8 @@ hm_status check_bad(hm_udtf *u)
     HM_CUDA(cudaMemcpyAsync(u->h_small, u->d_bad, sizeof(uint32_t), cudaMemcpyDeviceToHost, u->compute));
     HM_CUDA(cudaStreamSynchronize(u->compute));
     std::memcpy(&bad, u->h_small, sizeof(bad));
-    if (bad) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "a feature index was negative or >= dims (%lld); those elements were ignored",
-                     (long long)u->cfg.dims);
+    if (bad) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "a training row held a feature index that was negative or >= dims (%lld); "
+                     "those elements took no part in the margins or the updates", (long long)u->cfg.dims);
     return HM_OK;
 }
 
@@ -796,8 +880,8 @@ hm_status create_impl(const hm_config &cfg, int device, hm_udtf **out)
             HM_CUDA(cudaMalloc(&u->rec, (size_t)cfg.dims * u->rec_width * sizeof(float)));
             HM_CUDA(cudaMemsetAsync(u->rec, 0, (size_t)cfg.dims * u->rec_width * sizeof(float), u->compute));
         }
-        HM_CUDA(cudaMalloc(&u->d_bad, sizeof(uint32_t)));
-        HM_CUDA(cudaMemsetAsync(u->d_bad, 0, sizeof(uint32_t), u->compute));
+        HM_CUDA(cudaMalloc(&u->d_bad, 2 * sizeof(uint32_t)));
+        HM_CUDA(cudaMemsetAsync(u->d_bad, 0, 2 * sizeof(uint32_t), u->compute));
         HM_CUDA(cudaMalloc(&u->d_total, sizeof(int64_t)));
         HM_TRY(update_scratch_reserve(u->upd));
         HM_TRY(ensure_small(u, 1024));
@@ -1018,7 +1102,7 @@ hm_status hm_udtf_process_device(hm_udtf *u, int64_t n_rows, int64_t nnz, const 
         if (c->mb_abs.back() - c->mb_abs.front() != nnz)
             HM_FAIL(HM_ERR_INVALID_ARGUMENT, "nnz (%lld) does not match d_rowptr (%lld)", (long long)nnz,
                     (long long)(c->mb_abs.back() - c->mb_abs.front()));
-        return train_rows(u, *c, 0, n_rows, c->mb_abs.data(), n_mb, true);
+        return train_rows(u, *c, 0, n_rows, c->mb_abs.data(), n_mb, true, u->cfg.iters > 1 ? kTrainKeep : kTrainPlain);
     }();
     if (s != HM_OK) { delete c; return s; }
     if (n_rows % B) u->device_rows_short = true;
@@ -1037,7 +1121,7 @@ hm_status hm_udtf_close(hm_udtf *u, int64_t *n_model_rows)
             if (t_rows > 0) {
                 const int64_t e0 = c->mb_abs.empty() ? 0 : c->mb_abs.back();
                 int64_t mb[2] = {e0, e0 + u->tail_rp.back()};
-                HM_TRY(train_rows(u, *c, u->tail_row0, t_rows, mb, 1));
+                HM_TRY(train_rows(u, *c, u->tail_row0, t_rows, mb, 1, false, u->cfg.iters > 1 ? kTrainKeep : kTrainPlain));
                 if (c->mb_abs.empty()) c->mb_abs.push_back(e0);
                 c->mb_abs.push_back(mb[1]);
                 c->rows += t_rows;
@@ -1051,7 +1135,7 @@ hm_status hm_udtf_close(hm_udtf *u, int64_t *n_model_rows)
             for (Chunk *c : u->retained) {
                 const int64_t B = u->cfg.mini_batch;
                 const int64_t n_mb = (c->rows + B - 1) / B;
-                HM_TRY(train_rows(u, *c, 0, c->rows, c->mb_abs.data(), n_mb, true));
+                HM_TRY(train_rows(u, *c, 0, c->rows, c->mb_abs.data(), n_mb, true, kTrainReplay));
             }
         u->closed = true;
     }
@@ -1147,6 +1231,49 @@ hm_status hm_udtf_destroy(hm_udtf *u)
     if (u->sorter) cudaStreamDestroy(u->sorter);
     cudaGetLastError();
     delete u;
+    return HM_OK;
+}
+
+// ---- what hm_table.cpp needs to know about a learner ---------------------------------------
+}  // extern "C"
+
+namespace hm {
+
+hm_status learner_info(const hm_udtf *u, int *is_fm, int *factors, int64_t *dims, int *opt)
+{
+    if (!u) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "NULL learner");
+    *is_fm = u->fm ? 1 : 0; *factors = u->k; *dims = u->cfg.dims; *opt = u->cfg.opt;
+    return HM_OK;
+}
+
+__global__ void set_touched_kernel(uint8_t *__restrict__ touched, const int32_t *__restrict__ feature, int64_t n)
+{
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+        touched[feature[i]] = 1;
+}
+
+// train_fm emits the features seen in training: features restored from a model table count as seen.
+hm_status learner_set_touched(hm_udtf *u, const int32_t *feature, int64_t n)
+{
+    if (!u || !u->fm || n <= 0) return HM_OK;
+    DeviceGuard g(u->device);
+    HM_TRY(u->tmp_b.reserve((size_t)n * 4));
+    HM_CUDA(cudaMemcpyAsync(u->tmp_b.p, feature, (size_t)n * 4, cudaMemcpyHostToDevice, u->compute));
+    set_touched_kernel<<<(unsigned)std::min<int64_t>((n + 255) / 256, 1024), 256, 0, u->compute>>>(u->touched, u->tmp_b.as<int32_t>(), n);
+    u->L.launches++;
+    HM_CUDA(cudaGetLastError());
+    HM_CUDA(cudaStreamSynchronize(u->compute));
+    return HM_OK;
+}
+
+}  // namespace hm
+
+extern "C" {
+
+hm_status hm_udtf_config(const hm_udtf *u, hm_config *out)
+{
+    if (!u || !out) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "NULL argument");
+    *out = u->cfg;
     return HM_OK;
 }
 
@@ -1283,10 +1410,10 @@ hm_status hm_udtf_predict_device(hm_udtf *u, int64_t n_rows, const int64_t *d_ro
     if (u->fm) {
         if (n_rows > 0x7fffffff) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "predict: too many rows in one call");
         return launch_fm_forward(u->L, fm_args(u), d_rowptr, 0, (int32_t)n_rows, 0, reinterpret_cast<const uint32_t *>(d_feature),
-                                 d_value, nullptr, d_out, nullptr, nullptr, u->d_bad, 0, false);
+                                 d_value, nullptr, d_out, nullptr, nullptr, u->d_bad + 1, 0, false);
     }
     return launch_predict_linear(u->L, weight_view(u), u->cfg.dims, n_rows, d_rowptr, reinterpret_cast<const uint32_t *>(d_feature),
-                                 d_value, d_out, u->d_bad);
+                                 d_value, d_out, u->d_bad + 1);
 }
 
 hm_status hm_udtf_predict(hm_udtf *u, int64_t n_rows, const int64_t *rowptr, const int32_t *feature,
@@ -1312,15 +1439,22 @@ hm_status hm_udtf_predict(hm_udtf *u, int64_t n_rows, const int64_t *rowptr, con
     if (u->fm) {
         if (n_rows > 0x7fffffff) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "predict: too many rows in one call");
         HM_TRY(launch_fm_forward(u->L, fm_args(u), u->tmp_a.as<int64_t>(), 0, (int32_t)n_rows, 0, u->tmp_b.as<uint32_t>(),
-                                 u->tmp_c.as<float>(), nullptr, u->tmp_d.as<float>(), nullptr, nullptr, u->d_bad, nnz, false));
+                                 u->tmp_c.as<float>(), nullptr, u->tmp_d.as<float>(), nullptr, nullptr, u->d_bad + 1, nnz, false));
     } else {
         HM_TRY(launch_predict_linear(u->L, weight_view(u), u->cfg.dims, n_rows, u->tmp_a.as<int64_t>(), u->tmp_b.as<uint32_t>(),
-                                     u->tmp_c.as<float>(), u->tmp_d.as<float>(), u->d_bad));
+                                     u->tmp_c.as<float>(), u->tmp_d.as<float>(), u->d_bad + 1));
     }
     HM_CUDA(cudaMemcpyAsync(out, u->tmp_d.p, (size_t)n_rows * 4, cudaMemcpyDeviceToHost, u->compute));
+    // the scoring flag is this call's own: read it, clear it, report it here (never at close())
+    HM_CUDA(cudaMemcpyAsync(u->h_small, u->d_bad + 1, sizeof(uint32_t), cudaMemcpyDeviceToHost, u->compute));
+    HM_CUDA(cudaMemsetAsync(u->d_bad + 1, 0, sizeof(uint32_t), u->compute));
     HM_CUDA(cudaStreamSynchronize(u->compute));   // also keeps `rp` alive long enough
     u->stats.h2d_bytes += (n_rows + 1) * 8 + nnz * 8;
     u->stats.d2h_bytes += n_rows * 4;
+    uint32_t bad = 0;
+    std::memcpy(&bad, u->h_small, sizeof(bad));
+    if (bad) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "a scored row held a feature index that was negative or >= dims (%lld); "
+                     "those elements contributed 0 to the margins written to `out`", (long long)u->cfg.dims);
     return HM_OK;
 }
 

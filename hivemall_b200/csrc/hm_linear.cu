@@ -146,56 +146,107 @@ __device__ __forceinline__ void forward_rows(const FwdParams &P, int warp_first,
     }
 }
 
-// The same with dense columns (DenseInfo).  Every row of the block has the block's dense
-// positions, so `p0 + lane < p1` holds for their lanes.  The margin adds the same products in
-// the same order as forward_rows: only the source of a dense column's weight differs.
-__device__ __forceinline__ void forward_rows_dense(const FwdParams &P, int warp_first, int warp_stride, double *s_part)
+// Training forward of the two-kernel path: FOUR consecutive rows per warp at a time.  The kernel is
+// bound by the latency of each row's chain (row pointer -> feature/value -> weight gather), so the
+// loads of four rows (positions 0..63 of each) are all issued before the first is used.  Lane i owns
+// position i of a row.  With dense columns (DenseInfo; every row of the block then has the block's
+// dense positions) the weight of a dense column sits in a register instead of being gathered, and
+// the column's gradient sum is accumulated here.  The margin adds the same fp32 products as
+// forward_rows in the same lane order (fp64), so the two agree bit for bit.
+template <bool DENSE>
+__device__ __forceinline__ void forward_rows4(const FwdParams &P, int warp_first, int warp_stride, double *s_part)
 {
+    constexpr int RW = 4;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const uint32_t dmask = P.dense->mask;
-    const bool mine = (dmask >> lane) & 1u;
-    const float wd = mine ? weight_at<true>(P.wv, P.dense->key[lane]) : 0.0f;
-    double dacc = 0.0;
-    for (int r = warp_first; r < P.n_rows; r += warp_stride) {
-        const int64_t row = P.row0 + r;
-        const int64_t p0 = P.rowptr[row], p1 = P.rowptr[row + 1];
-        double acc = 0.0;
-        float x0 = 0.0f;
-        int64_t p = p0 + lane;
-        if (p < p1) {
-            const uint32_t f = __ldcs(P.feature + p);
-            x0 = __ldcs(P.value + p);
-            if (mine) acc += (double)__fmul_rn(wd, x0);
-            else if (f < P.dims) acc += (double)__fmul_rn(weight_at<true>(P.wv, f), x0);
-            else atomicOr(P.bad, 1u);
-        }
-        for (p += 32; p < p1; p += 32) {
-            const uint32_t f = __ldcs(P.feature + p);
-            const float x = __ldcs(P.value + p);
-            if (f < P.dims) acc += (double)__fmul_rn(weight_at<true>(P.wv, f), x);
-            else atomicOr(P.bad, 1u);
-        }
-        acc = warp_sum(acc);
-        const float m = (float)acc;
-        float dl = 0.0f;
-        if (lane == 0) {
-            P.margin[row - P.block_row0] = m;
-            const float lab = P.label[row];
-            const float y = P.task == HM_TASK_CLASSIFIER ? (lab > 0.0f ? 1.0f : -1.0f) : lab;
-            dl = dloss_of(P.loss, m, y);
-            P.dloss[r] = dl;
-        }
-        dl = __shfl_sync(0xffffffffu, dl, 0);
-        if (mine) dacc += (double)__fmul_rn(dl, x0);      // the contribution the update kernel would have sorted
+    bool mine = false;
+    float wd = 0.0f;
+    if (DENSE) {
+        const uint32_t dmask = P.dense->mask;
+        mine = (dmask >> lane) & 1u;
+        if (mine) wd = weight_at<true>(P.wv, P.dense->key[lane]);
     }
-    // column sums of this CTA's rows: warps added in a fixed order
-    s_part[warp * 32 + lane] = dacc;
-    __syncthreads();
-    if (warp == 0) {
-        double sum = 0.0;
+    double dacc = 0.0;
+    for (int r = warp_first * RW; r < P.n_rows; r += warp_stride * RW) {
+        const int64_t rp = (lane <= RW && r + lane <= P.n_rows) ? P.rowptr[P.row0 + r + lane] : 0;
+        float lab = 0.0f;
+        if (lane < RW && r + lane < P.n_rows) lab = P.label[P.row0 + r + lane];
+        int64_t p0[RW], p1[RW];
+        bool in[RW], in2[RW];
+        uint32_t f[RW], g[RW];
+        float x[RW], y2[RW];
 #pragma unroll
-        for (int w2 = 0; w2 < kFwdThreads / 32; w2++) sum += s_part[w2 * 32 + lane];
-        P.dense_partial[(size_t)lane * P.dense_stride + blockIdx.x] = sum;
+        for (int u = 0; u < RW; u++) {
+            p0[u] = __shfl_sync(0xffffffffu, rp, u);
+            p1[u] = __shfl_sync(0xffffffffu, rp, u + 1);
+            const bool row = r + u < P.n_rows;
+            in[u] = row && p0[u] + lane < p1[u];
+            in2[u] = row && p0[u] + 32 + lane < p1[u];
+        }
+#pragma unroll
+        for (int u = 0; u < RW; u++) {
+            f[u] = in[u] ? __ldcs(P.feature + p0[u] + lane) : 0u;
+            x[u] = in[u] ? __ldcs(P.value + p0[u] + lane) : 0.0f;
+        }
+#pragma unroll
+        for (int u = 0; u < RW; u++) {
+            g[u] = in2[u] ? __ldcs(P.feature + p0[u] + 32 + lane) : 0u;
+            y2[u] = in2[u] ? __ldcs(P.value + p0[u] + 32 + lane) : 0.0f;
+        }
+        // gathers of the four rows, all in flight together
+        float w1[RW], w2[RW];
+#pragma unroll
+        for (int u = 0; u < RW; u++) {
+            w1[u] = 0.0f; w2[u] = 0.0f;
+            if (in[u]) {
+                if (DENSE && mine) w1[u] = wd;
+                else if (f[u] < P.dims) w1[u] = weight_at<true>(P.wv, f[u]);
+                else { in[u] = false; atomicOr(P.bad, 1u); }
+            }
+            if (in2[u]) {
+                if (g[u] < P.dims) w2[u] = weight_at<true>(P.wv, g[u]);
+                else { in2[u] = false; atomicOr(P.bad, 1u); }
+            }
+        }
+        float dl[RW];
+#pragma unroll
+        for (int u = 0; u < RW; u++) {
+            double acc = 0.0;
+            if (in[u]) acc += (double)__fmul_rn(w1[u], x[u]);
+            if (in2[u]) acc += (double)__fmul_rn(w2[u], y2[u]);
+            if (r + u < P.n_rows) {       // (uniform over the warp) rows longer than 64 elements
+                for (int64_t p = p0[u] + 64 + lane; p < p1[u]; p += 32) {
+                    const uint32_t f3 = __ldcs(P.feature + p);
+                    const float x3 = __ldcs(P.value + p);
+                    if (f3 < P.dims) acc += (double)__fmul_rn(weight_at<true>(P.wv, f3), x3);
+                    else atomicOr(P.bad, 1u);
+                }
+            }
+            acc = warp_sum(acc);
+            dl[u] = 0.0f;
+            if (r + u < P.n_rows) {
+                const float m = (float)acc;
+                const float lb = __shfl_sync(0xffffffffu, lab, u);
+                const float yy = P.task == HM_TASK_CLASSIFIER ? (lb > 0.0f ? 1.0f : -1.0f) : lb;
+                dl[u] = dloss_of(P.loss, m, yy);
+                if (lane == 0) { P.margin[P.row0 + r + u - P.block_row0] = m; P.dloss[r + u] = dl[u]; }
+            }
+        }
+        if (DENSE && mine) {
+#pragma unroll
+            for (int u = 0; u < RW; u++)
+                if (r + u < P.n_rows) dacc += (double)__fmul_rn(dl[u], x[u]);   // the contribution the update kernel would have sorted
+        }
+    }
+    if (DENSE) {
+        // column sums of this CTA's rows: warps added in a fixed order
+        s_part[warp * 32 + lane] = dacc;
+        __syncthreads();
+        if (warp == 0) {
+            double sum = 0.0;
+#pragma unroll
+            for (int w2i = 0; w2i < kFwdThreads / 32; w2i++) sum += s_part[w2i * 32 + lane];
+            P.dense_partial[(size_t)lane * P.dense_stride + blockIdx.x] = sum;
+        }
     }
 }
 
@@ -256,12 +307,13 @@ __device__ __forceinline__ void forward_rows_small(const FwdParams &P)
     }
 }
 
-__global__ void __launch_bounds__(kFwdThreads) linear_forward_kernel(FwdParams P)
+__global__ void __launch_bounds__(kFwdThreads, 3) linear_forward_kernel(FwdParams P)
 {
     __shared__ double s_part[kFwdThreads];
     const int warp_first = blockIdx.x * (kFwdThreads / 32) + (threadIdx.x >> 5), warp_stride = gridDim.x * (kFwdThreads / 32);
-    if (P.dense && P.dense->mask != 0u) forward_rows_dense(P, warp_first, warp_stride, s_part);
-    else forward_rows<true>(P, warp_first, warp_stride);
+    if (!P.train) forward_rows<true>(P, warp_first, warp_stride);       // prediction
+    else if (P.dense && P.dense->mask != 0u) forward_rows4<true>(P, warp_first, warp_stride, s_part);
+    else forward_rows4<false>(P, warp_first, warp_stride, s_part);
 }
 
 // ---- update ------------------------------------------------------------------------
@@ -469,17 +521,26 @@ struct UpdShared {
 // segmented scan in a fixed order, finished features compacted into S.l_key / S.l_g (*S.s_nlist
 // entries, to be stepped by apply_list), open segments left in S.s_carry / S.s_first.  Ends on a
 // barrier.  RO: dloss was written by an earlier kernel and may use the read-only path.
+// unit: the block's sorted values are all 1.0 and spay holds packed (feature, row) records (DenseInfo::unit).
 template <bool RO>
 __device__ __forceinline__ void reduce_tile(const UpdParams &P, const UpdShared &S, uint32_t base, int n_tile,
-                                            bool first_tile, bool last_tile)
+                                            bool first_tile, bool last_tile, bool unit = false)
 {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     // ---- coalesced striped load; contribution = dloss[row] * value (fp32 product)
     uint32_t k[kUpdItems]; uint2 pv[kUpdItems];
+    if (unit) {
 #pragma unroll
-    for (int i = 0; i < kUpdItems; i++) {
-        const int q = i * kUpdThreads + tid;
-        if (q < n_tile) { k[i] = __ldcs(P.skey + base + q); pv[i] = __ldcs(P.spay + base + q); }
+        for (int i = 0; i < kUpdItems; i++) {
+            const int q = i * kUpdThreads + tid;
+            if (q < n_tile) { const uint2 r = __ldcs(P.spay + base + q); k[i] = r.x; pv[i] = make_uint2(r.y, 0x3f800000u); }
+        }
+    } else {
+#pragma unroll
+        for (int i = 0; i < kUpdItems; i++) {
+            const int q = i * kUpdThreads + tid;
+            if (q < n_tile) { k[i] = __ldcs(P.skey + base + q); pv[i] = __ldcs(P.spay + base + q); }
+        }
     }
 #pragma unroll
     for (int i = 0; i < kUpdItems; i++) {
@@ -645,25 +706,36 @@ __device__ __noinline__ void dense_columns_step(const UpdParams &P)
     }
 }
 
-__global__ void __launch_bounds__(kUpdThreads, 4) linear_update_kernel(const __grid_constant__ UpdParams P)
+// Shared memory of one update CTA (declared once in the kernel; the two bodies share it).
+struct UpdSmem {
+    __align__(16) unsigned char raw[kUpdSmem];
+    Scan warp[kUpdThreads / 32];
+    SegRec carry;            // open trailing segment of the previous tile
+    SegRec first;            // the CTA's piece of a segment that began before its range
+    uint32_t carry_open;
+    uint32_t is_last;
+    uint32_t edge[2];        // does the CTA's range start / end on a true segment boundary?
+    int nlist;
+};
+
+// UNIT: the block's sorted values are all 1.0; spay holds packed (feature, row) records (DenseInfo::unit).
+template <bool UNIT>
+__device__ __forceinline__ void update_body(const UpdParams &P, UpdSmem &sm, uint32_t s0, uint32_t n)
 {
-    __shared__ __align__(16) unsigned char smem_raw[kUpdSmem];
+    unsigned char *smem_raw = sm.raw;
     uint32_t *s_key = reinterpret_cast<uint32_t *>(smem_raw);
     float *s_val = reinterpret_cast<float *>(smem_raw + (size_t)kUpdPadded * 4);
     uint32_t *l_key = reinterpret_cast<uint32_t *>(smem_raw + (size_t)kUpdPadded * 8);
     float *l_g = reinterpret_cast<float *>(smem_raw + (size_t)kUpdPadded * 8 + (size_t)kUpdList * 4);
-    __shared__ Scan s_warp[kUpdThreads / 32];
-    __shared__ SegRec s_carry;       // open trailing segment of the previous tile
-    __shared__ SegRec s_first;       // the CTA's piece of a segment that began before its range
-    __shared__ uint32_t s_carry_open;
-    __shared__ uint32_t s_is_last;
-    __shared__ uint32_t s_edge[2];   // does the CTA's range start / end on a true segment boundary?
-    __shared__ int s_nlist;
-
+    Scan *s_warp = sm.warp;
+    SegRec &s_carry = sm.carry;
+    SegRec &s_first = sm.first;
+    uint32_t &s_carry_open = sm.carry_open;
+    uint32_t &s_is_last = sm.is_last;
+    uint32_t *s_edge = sm.edge;
+    int &s_nlist = sm.nlist;
+    constexpr bool unit = UNIT;
     const int tid = threadIdx.x;
-    USTAMP(0);
-    if (P.dense && (int)blockIdx.x == P.n_active) { dense_columns_step(P); return; }
-    const uint32_t s0 = P.seg_off[P.seg], n = P.seg_off[P.seg + 1] - s0;
     // contiguous split of the sorted mini-batch over the grid, in whole tiles
     const uint32_t tiles = (n + kUpdTile - 1) / kUpdTile;
     const uint32_t tiles_per_cta = (tiles + P.n_active - 1) / P.n_active;
@@ -676,20 +748,21 @@ __global__ void __launch_bounds__(kUpdThreads, 4) linear_update_kernel(const __g
     // The four loads are issued here and only consumed after the first tile's barrier, so they
     // overlap the tile loads instead of adding a round trip.
     if (tid == 32 && lo < hi) {
-        const uint32_t a0 = lo == 0 ? 0u : __ldg(P.skey + s0 + lo - 1), a1 = __ldg(P.skey + s0 + lo);
-        const uint32_t b0 = __ldg(P.skey + s0 + hi - 1), b1 = hi == n ? 0u : __ldg(P.skey + s0 + hi);
+        auto key_at = [&](uint32_t e) -> uint32_t { return unit ? __ldg(&P.spay[e].x) : __ldg(P.skey + e); };
+        const uint32_t a0 = lo == 0 ? 0u : key_at(s0 + lo - 1), a1 = key_at(s0 + lo);
+        const uint32_t b0 = key_at(s0 + hi - 1), b1 = hi == n ? 0u : key_at(s0 + hi);
         s_edge[0] = lo == 0 || a0 != a1;
         s_edge[1] = hi == n || b0 != b1;
     }
     if (lo >= hi) __syncthreads();   // (the tile loop below has its own barriers)
 
     UpdShared S;
-    S.s_key = s_key; S.s_val = s_val; S.l_key = l_key; S.l_g = l_g; S.s_warp = s_warp; S.s_carry = &s_carry;
-    S.s_first = &s_first; S.s_carry_open = &s_carry_open; S.s_edge = s_edge; S.s_nlist = &s_nlist;
+    S.s_key = s_key; S.s_val = s_val; S.l_key = l_key; S.l_g = l_g; S.s_warp = s_warp; S.s_carry = &sm.carry;
+    S.s_first = &sm.first; S.s_carry_open = &sm.carry_open; S.s_edge = s_edge; S.s_nlist = &sm.nlist;
     for (uint32_t t0 = lo; t0 < hi; t0 += kUpdTile) {
         const int n_tile = (int)min((uint32_t)kUpdTile, hi - t0);
         const bool last_tile = t0 + kUpdTile >= hi;
-        reduce_tile<true>(P, S, s0 + t0, n_tile, t0 == lo, last_tile);
+        reduce_tile<true>(P, S, s0 + t0, n_tile, t0 == lo, last_tile, unit);
         USTAMP(3);
         // ---- after the last tile the CTA's boundary pieces are final: publish them and take the
         // completion ticket now, so that both round trips overlap the optimizer step below
@@ -755,6 +828,16 @@ __global__ void __launch_bounds__(kUpdThreads, 4) linear_update_kernel(const __g
     apply_list(P, ml_key, ml_g, s_nlist, tid);
     USTAMP(6);
     if (tid == 0) *P.br.ticket = 0;   // ready for the next launch on this stream
+}
+
+__global__ void __launch_bounds__(kUpdThreads, 4) linear_update_kernel(const __grid_constant__ UpdParams P)
+{
+    __shared__ UpdSmem sm;
+    USTAMP(0);
+    if (P.dense && (int)blockIdx.x == P.n_active) { dense_columns_step(P); return; }
+    const uint32_t s0 = P.seg_off[P.seg], n = P.seg_off[P.seg + 1] - s0;
+    if (P.dense && P.dense->unit != 0u) update_body<true>(P, sm, s0, n);     // (uniform over the grid)
+    else update_body<false>(P, sm, s0, n);
 }
 
 // ---- small mini-batches: one persistent CTA ----------------------------------------
@@ -861,7 +944,7 @@ export_count_kernel(WeightView wv, const uint8_t *__restrict__ touched, int64_t 
 
 __global__ void __launch_bounds__(1024) export_scan_kernel(uint32_t *__restrict__ counts, int n, int64_t *total)
 {
-    // exclusive scan of counts[0..n) by one CTA; counts[n] and *total receive the sum
+    // exclusive scan of counts[0..n) by one CTA; *total receives the sum
     __shared__ uint32_t warp_tot[32];
     const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
     const int per = (n + 1023) / 1024;
@@ -959,7 +1042,8 @@ int grid_for(int64_t ctas_wanted, int per_sm)
 
 }  // namespace
 
-int linear_forward_grid(int32_t n_rows) { return grid_for(((int64_t)n_rows + 7) / 8, 8); }
+// (a warp takes four rows at a time, a CTA of eight warps 32)
+int linear_forward_grid(int32_t n_rows) { return grid_for(((int64_t)n_rows + 31) / 32, 8); }
 
 hm_status launch_linear_forward(Launcher &L, const LinearArgs &a, const int64_t *d_rowptr, int64_t row0,
                                 int32_t n_rows, int64_t block_row0, const uint32_t *d_feature,

@@ -278,6 +278,21 @@ class UDTF:
             return feat[: m.value], wt[: m.value], vif[: m.value]
         return feat[: m.value], wt[: m.value]
 
+    def save_model_table(self, path: str, binary: bool = False, delimiter: str = "\t") -> int:
+        """close() + forward() into a file (text: feature<delim>weight[<delim>v1,...,vk] per line; or binary).
+        Returns the number of rows written."""
+        self._flush_rows()
+        n = C.c_int64()
+        check(self._lib.hm_udtf_save_model_table(self._h, path.encode(), int(binary), delimiter.encode()[:1], C.byref(n)))
+        self._keep.clear()
+        return n.value
+
+    def load_model_table(self, path: str, binary: bool = False, delimiter: str = "\t") -> int:
+        """Warm start from a model-table file: weights (train_fm: w0, w, V) exactly, optimizer slots from zero."""
+        n = C.c_int64()
+        check(self._lib.hm_udtf_load_model_table(self._h, path.encode(), int(binary), delimiter.encode()[:1], C.byref(n)))
+        return n.value
+
     def destroy(self) -> None:
         if getattr(self, "_h", None) is not None and self._h:
             self._lib.hm_udtf_destroy(self._h)

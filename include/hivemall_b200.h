@@ -134,7 +134,13 @@ hm_status hm_udtf_create_from_config(const hm_config *cfg, int device, hm_udtf *
  * are buffered, exactly as if process() had been called row by row.
  * `value` may be NULL: every value is then 1.0 (Hivemall's index-only features,
  * "name" without ":value") and half of the feature bytes stay off the bus.
- * Copies host->device inside the call (asynchronously when the buffers are pinned). */
+ * Copies host->device inside the call (asynchronously when the buffers are pinned).
+ * LIFETIME: with pinned buffers (hm_host_alloc) the call returns while DMA is still reading
+ * them -- rowptr, feature, value and label must stay valid AND unmodified until hm_udtf_sync,
+ * hm_udtf_last_margins or hm_udtf_close returns (a JNI caller must not refill a direct
+ * ByteBuffer before that).  The same holds for hm_udtf_process_split and
+ * hm_udtf_process_strings.  A malformed row pointer is HM_ERR_INVALID_ARGUMENT; slices of the
+ * call that were consumed before the bad row was met have been trained. */
 hm_status hm_udtf_process(hm_udtf *u, int64_t n_rows, const int64_t *rowptr,
                           const int32_t *feature, const float *value, const float *label);
 /* process() for rows whose features arrive in two groups, the way Hivemall's feature
@@ -155,7 +161,12 @@ hm_status hm_udtf_process_strings(hm_udtf *u, int64_t n_rows, const int64_t *row
                                   const uint8_t *bytes, const int64_t *offsets, const float *label);
 /* process() for rows already resident in device memory (no copies).  n_rows must
  * be a multiple of -mini_batch unless this is the last call before close(), and
- * no host-buffered remainder may be pending.  nnz = d_rowptr[n_rows]-d_rowptr[0]. */
+ * no host-buffered remainder may be pending.  nnz = d_rowptr[n_rows]-d_rowptr[0].
+ * LIFETIME / ORDER: the arrays are used in place, by kernels on the learner's own streams
+ * that do not wait for the caller's streams: finish writing them (and synchronise the stream
+ * that wrote them) before the call, and keep them alive and unmodified until hm_udtf_sync or
+ * hm_udtf_close returns; with -iters > 1 they are read again by close() (the later passes
+ * replay them), so keep them until close() has returned. */
 hm_status hm_udtf_process_device(hm_udtf *u, int64_t n_rows, int64_t nnz, const int64_t *d_rowptr,
                                  const int32_t *d_feature, const float *d_value, const float *d_label);
 
@@ -182,7 +193,14 @@ hm_status hm_udtf_destroy(hm_udtf *u);
  * factors of a feature, then their accumulators) and "touched" (width 0: a byte per feature,
  * 1 = seen in training; combine it with MAX, not with a sum, and do not scale it).  The
  * pointers stay valid until destroy; call hm_udtf_sync before touching them from another
- * stream. */
+ * stream.
+ * MIX semantics: averaging means averaging THESE arrays.  For every optimizer but FTRL that
+ * is the mean of the ranks' weights (and of their slots).  FTRL's replica is (z, n): the
+ * mean of (z, n) is taken and the weight is then derived from it -- because the closed form
+ * holds a soft threshold and 1/sqrt(n), that is NOT the mean of the ranks' weights (it can
+ * zero or un-zero a feature); it is the usual way to combine FTRL replicas and keeps them
+ * consistent state-wise, but a MIX server that averages weights would differ.  What the
+ * reference averages is unknown (no source is mounted). */
 int hm_udtf_num_arrays(const hm_udtf *u);
 hm_status hm_udtf_array(hm_udtf *u, int which, const char **name, void **d_ptr,
                         int64_t *n_floats, int32_t *width);
@@ -207,9 +225,14 @@ hm_status hm_udtf_scale_replica(hm_udtf *u, float scale);
 
 /* ---- prediction (held-out AUC / logloss for parity) ----------------------- */
 
-/* out[i] = margin of row i under the current model (linear: w.x ; fm: y_hat). */
+/* out[i] = margin of row i under the current model (linear: w.x ; fm: y_hat).  Host buffers;
+ * waits for the result.  An element whose index is outside [0, dims) contributes 0 and makes the
+ * call return HM_ERR_INVALID_ARGUMENT (after writing `out`); it does not taint close(). */
 hm_status hm_udtf_predict(hm_udtf *u, int64_t n_rows, const int64_t *rowptr,
                           const int32_t *feature, const float *value, float *out);
+/* Same for device buffers: ASYNCHRONOUS on hm_udtf_stream -- the call returns before d_out is
+ * written; order your reads after that stream or call hm_udtf_sync.  Out-of-range indices
+ * contribute 0 and are not reported by this variant. */
 hm_status hm_udtf_predict_device(hm_udtf *u, int64_t n_rows, const int64_t *d_rowptr,
                                  const int32_t *d_feature, const float *d_value, float *d_out);
 
@@ -217,6 +240,29 @@ hm_status hm_udtf_predict_device(hm_udtf *u, int64_t n_rows, const int64_t *d_ro
  * (before that mini-batch's update): the per-step training signal a caller logs or turns
  * into a loss.  Copies min(cap, rows) floats to `host`, waits for the GPU, sets *n. */
 hm_status hm_udtf_last_margins(hm_udtf *u, float *host, int64_t cap, int64_t *n);
+
+/* ---- the model table as a file, warm start from one ------------------------------- */
+
+enum { HM_TABLE_TEXT = 0, HM_TABLE_BINARY = 1 };
+
+/* close() + forward() into a file: what a Hive job does with the rows a training UDTF forwards
+ * (INSERT into a table (feature, weight[, Vif])).  HM_TABLE_TEXT: one row per line,
+ * feature <delimiter> weight [<delimiter> v1,v2,...,vk], numbers printed so that they read back
+ * bit for bit; delimiter 0 means TAB (Hive's text tables use \t or ^A: the reference's own
+ * choice is unknown, hence the parameter).  HM_TABLE_BINARY: a 32-byte header ("HMTABLE1",
+ * factors, dims, rows) followed by feature int32[rows], weight f32[rows], vif f32[rows*factors],
+ * little endian.  Rows are in forward() order (ascending feature; train_fm: the w0 row, feature
+ * -1, first).  *n_rows (nullable) receives the row count. */
+hm_status hm_udtf_save_model_table(hm_udtf *u, const char *path, int format, char delimiter, int64_t *n_rows);
+/* Warm start: set the replica of a fresh (or running) learner from such a file.  Weights (and
+ * train_fm's w0 and factor rows; factors of features absent from the file keep their initial
+ * values) are restored exactly.  Optimizer slots are NOT in a model table: they restart from
+ * zero, so continuing is exact for -opt sgd and approximate for the others; for -opt ftrl, which
+ * stores (z, n) and derives the weight, z is rebuilt from the weight with n = 0.  Call
+ * hm_udtf_set_step to continue a learning-rate schedule. */
+hm_status hm_udtf_load_model_table(hm_udtf *u, const char *path, int format, char delimiter, int64_t *n_rows);
+/* The learner's numeric configuration (what hm_parse_options made of its option string). */
+hm_status hm_udtf_config(const hm_udtf *u, hm_config *out);
 
 /* Dense columns of the most recently sorted ingest block (diagnostics, tests).  Rows usually
  * start with their quantitative features ("name:value" with a fixed name), so position i of every

@@ -12,7 +12,7 @@ lib = _lib.load()
 buf = np.zeros(4096 * 8, dtype=np.uint64)
 rc = lib.hm_debug_read_stamps(buf.ctypes.data_as(C.c_void_p), C.c_size_t(buf.size)); assert rc == 0
 s = buf.reshape(4096, 8).astype(np.int64)
-act = s[:, 0] > 0
+act = (s[:, 0] > 0) & (s[:, 5] > 0)     # (the dense-column CTA leaves stamp 0 only)
 s = s[act]; print("CTAs", len(s))
 t0 = s[:, 0].min()
 end = max(s[:, 5].max(), s[:, 6].max())

@@ -180,3 +180,22 @@ def test_split_rows_equal_merged_rows(fn, opts):
         assert np.array_equal(a.array_to_host(name), b.array_to_host(name)), name
     assert b.stats().h2d_bytes < a.stats().h2d_bytes
     a.destroy(); b.destroy()
+
+
+def test_predict_reports_out_of_range_indices_itself():
+    """Scoring rows with an index >= dims is the predict call's own error; it must not make a later
+    close() complain about training data that was fine, and a clean predict afterwards succeeds."""
+    data = synth.a9a_like(1024, seed=0)
+    rp, f, v, y = data.numpy()
+    u = hm.train_classifier("-opt adagrad -mini_batch 128 -dims 124")
+    u.process_batch(rp, f, v, y)
+    u.sync()
+    bad_f = f.copy()
+    bad_f[5] = 124
+    with pytest.raises(hm.UDFArgumentError) as e:
+        u.predict(rp[:9], bad_f, v)
+    assert "scored row" in str(e.value)
+    m = u.predict(rp[:9], f, v)
+    assert np.isfinite(m).all()
+    assert u.close() > 0
+    u.destroy()

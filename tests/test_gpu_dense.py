@@ -57,6 +57,7 @@ def to_csr(rows_f, rows_v, rng, regression=False):
 
 
 def check(fn, options, data, want_dense, pushes=None):
+    """want_dense: the dense columns of the LAST ingest block (that is what dense_columns() reports)."""
     u, w, state = run_gpu_linear(fn, options, data, pushes=pushes)
     got = sorted(int(x) for x in u.dense_columns())
     assert got == sorted(want_dense), f"dense columns {got}, expected {sorted(want_dense)}"
@@ -85,16 +86,16 @@ def test_gradient_normalisations(norm):
 def test_feature_again_later_in_a_row():
     """Feature PREFIX[2] also turns up in the tail of one row: it is not a dense column (its
     occurrences must meet in ONE optimizer step), the others still are."""
-    rows_f, rows_v, rng = prefix_rows(5000, seed=7)
-    rows_f[4321] = np.concatenate([rows_f[4321], [PREFIX[2]]])
-    rows_v[4321] = np.concatenate([rows_v[4321], [0.75]])
+    rows_f, rows_v, rng = prefix_rows(4096, seed=7)      # two whole mini-batches: one ingest block
+    rows_f[3321] = np.concatenate([rows_f[3321], [PREFIX[2]]])
+    rows_v[3321] = np.concatenate([rows_v[3321], [0.75]])
     data = to_csr(rows_f, rows_v, rng)
     check("train_classifier", f"-loss logloss -opt adagrad -mini_batch 2048 -dims {DIMS} -eta0 0.05", data,
           [p for p in PREFIX if p != PREFIX[2]])
 
 
 def test_row_that_breaks_the_pattern_and_short_rows():
-    rows_f, rows_v, rng = prefix_rows(5000, seed=9)
+    rows_f, rows_v, rng = prefix_rows(4096, seed=9)
     rows_f[17][1] = 555                      # position 1 holds another feature in one row
     rows_f[2500] = rows_f[2500][:5]          # a row with only positions 0..4
     rows_v[2500] = rows_v[2500][:5]
@@ -106,13 +107,13 @@ def test_row_that_breaks_the_pattern_and_short_rows():
 
 def test_same_feature_twice_in_the_prefix():
     prefix = [5, 9, 5, 11]
-    rows_f, rows_v, rng = prefix_rows(5000, prefix=prefix, seed=11)
+    rows_f, rows_v, rng = prefix_rows(4096, prefix=prefix, seed=11)
     data = to_csr(rows_f, rows_v, rng)
     check("train_classifier", f"-loss logloss -opt adam -mini_batch 2048 -dims {DIMS} -eta0 0.01", data, [9, 11])
 
 
 def test_empty_row_disables_all():
-    rows_f, rows_v, rng = prefix_rows(5000, seed=13)
+    rows_f, rows_v, rng = prefix_rows(4096, seed=13)
     rows_f[100] = rows_f[100][:0]
     rows_v[100] = rows_v[100][:0]
     data = to_csr(rows_f, rows_v, rng)

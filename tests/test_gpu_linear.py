@@ -118,6 +118,34 @@ def test_iters_and_schedules():
         u.destroy()
 
 
+def test_replays_do_not_sort_again():
+    """-iters 3: the later passes train from the sort results the first pass kept: sort kernels are
+    launched in pass 1 only, results match the oracle, and host pushes in several pieces (a carried tail,
+    a short last mini-batch) replay in the same order."""
+    data = synth.criteo_like(20000 + 333, dims=1 << 16, seed=4)
+    rowptr, feature, value, label = data.numpy()
+    base = f"-opt adagrad -mini_batch 4096 -dims {1 << 16} -eta0 0.05"
+    counts = {}
+    for iters in (1, 3):
+        u = hm.UDTF(f"{base} -iters {iters}", 0, function_name="train_classifier")
+        u.set_profiling(True)
+        r0 = 0
+        for cnt in (9000, 11333):
+            u.process_batch(rowptr[r0:r0 + cnt + 1], feature, value, label[r0:r0 + cnt])
+            r0 += cnt
+        u.close()
+        kt = u.kernel_times()
+        counts[iters] = (kt["sort_scatter"]["launches"], kt["sort_hist"]["launches"], kt["linear_update"]["launches"])
+        if iters == 3:
+            w, state = u.array_to_host("w"), u.array_to_host("state")
+        u.destroy()
+    assert counts[3][0] == counts[1][0] > 0 and counts[3][1] == counts[1][1]
+    assert counts[3][2] == 3 * counts[1][2]
+    ref, ref_state = run_oracle_linear("train_classifier", f"{base} -iters 3", data)
+    assert_weights_close(w, ref.w)
+    assert_weights_close(state, ref_state, "state")
+
+
 def test_deterministic_rerun():
     """No float atomics anywhere: two runs are bit-identical."""
     data = synth.criteo_like(30000, dims=1 << 18, seed=7)
