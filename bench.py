@@ -7,7 +7,7 @@ dims, Criteo-shaped synthetic rows (39 features/row), 100M rows per GPU, -mini_b
 changes it, and the N=1 line carries a sweep over 128 / 1024 / 8192 / 65536).
 
 A "step" is one pass of the hot path over one ingest call of ROWS_PER_STEP rows (64
-mini-batches of 65536): dense-column check and segmented sort-by-feature of its blocks, then
+mini-batches of 65536): hot-feature selection and segmented sort-by-feature of its blocks, then
 per mini-batch the forward and the fused reduce+update kernels.  Inputs are far larger than
 L2 (1.3 GB per step).
 
@@ -498,7 +498,7 @@ def main():
 
     main_run = arm.run(clock_index=local_rank)
     ms, rows_per_s, launches = main_run["ms"], main_run["value"], main_run["launches"]
-    dense_cols = [int(x) for x in arm.u.dense_columns()]
+    hot_feats = [int(x) for x in arm.u.hot_features()]
 
     # ---- same steps again with per-kernel CUDA events (roofline of the dominant kernel)
     kt, ms_prof_step = arm.profile()
@@ -751,9 +751,9 @@ def main():
             "dtype": "f32 (fp64 sums)", "data": "synthetic",
             "nnz_per_sec": rows_per_s * nnz_per_row,
             "config": config_of(wl, mb, rps, world, K, W, total_rows),
-            "dense_columns": {"count": len(dense_cols),
-                              "note": "leading row positions that hold the same feature in every row of a block: reduced "
-                                      "as column sums by the forward kernel, not sorted"},
+            "hot_features": {"count": len(hot_feats),
+                             "note": "features picked per ingest block by their frequency in a sample of its rows: reduced by "
+                                     "the forward kernel, not sorted (the choice affects speed only)"},
             "roofline": roofline,
             "cpu_baseline": cpu,
             "e2e": e2e,

@@ -87,7 +87,7 @@ SIGNATURES = {
     "hm_udtf_save_model_table": (C.c_int, [_P, C.c_char_p, C.c_int, C.c_char, C.POINTER(C.c_int64)]),
     "hm_udtf_load_model_table": (C.c_int, [_P, C.c_char_p, C.c_int, C.c_char, C.POINTER(C.c_int64)]),
     "hm_udtf_config": (C.c_int, [_P, C.POINTER(HmConfig)]),
-    "hm_udtf_dense_columns": (C.c_int, [_P, _P, C.c_int32, C.POINTER(C.c_int32)]),
+    "hm_udtf_hot_features": (C.c_int, [_P, _P, C.c_int32, C.POINTER(C.c_int32)]),
     "hm_model_table_noalloc": (C.c_int, [_P, C.c_int64, _P, _P, C.c_int64, _P, _P]),
     "hm_udtf_stats": (C.c_int, [_P, C.POINTER(HmStats)]),
     "hm_udtf_set_profiling": (C.c_int, [_P, C.c_int]),

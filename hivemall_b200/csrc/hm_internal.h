@@ -20,7 +20,7 @@ void set_error(const char *fmt, ...);
 enum KernelId {
     K_HASH = 0, K_SEG_PREP, K_SORT_HIST, K_SORT_SCAN, K_SORT_SCATTER,
     K_LIN_FORWARD, K_LIN_UPDATE, K_FM_FORWARD, K_FM_UPDATE, K_PREDICT,
-    K_EXPORT, K_MISC, K_DENSE_CHECK, K_NUM_KERNELS
+    K_EXPORT, K_MISC, K_HOT_SELECT, K_NUM_KERNELS
 };
 extern const char *const kKernelNames[K_NUM_KERNELS];
 
@@ -49,21 +49,28 @@ struct Launcher {
 // persistent kernels are sized in multiples of it.
 int num_sms();
 
-// ---- dense prefix columns (hm_sort.cu: dense_check_kernel) -------------------------
-// Feature engineering puts the quantitative features ("name:value" with a fixed name) at the
-// front of every row: position i of every row then holds the same feature.  Such a column needs
-// no sort -- its gradient is a plain column sum -- and no gather.  Per ingest block the check
-// kernel proves, for up to 32 leading positions: every row of the block has the position, it
-// holds the same in-range feature in every row, and that feature occurs nowhere else in the
-// block (so skipping it in the sort by KEY is the same as skipping it by position).
-struct DenseInfo {
-    uint32_t mask;        // bit i: position i is a dense column of this block
-    uint32_t count;       // popcount(mask)
-    uint32_t key[32];     // feature of position i (valid where the bit is set)
-    uint32_t unit;        // 1: every element that IS sorted has value 1.0 (index-only features): the sort then
-                          // moves packed (feature, row) records of 8 bytes and no value at all
-    uint32_t noteq, collide, ticket, nonunit_pos, nonunit_other;   // work area of the check kernel (left zeroed)
-    uint32_t pad[2];
+// ---- hot features (hm_sort.cu: hot_select_kernel) -----------------------------------
+// A handful of features carry a large share of a mini-batch's elements: the quantitative features
+// ("name:value" with a fixed name) that every row has, and the head of each categorical field.
+// Sorting them is wasted work -- their gradient is a long plain sum -- and so is gathering their
+// weight.  Per ingest block up to kMaxHot features are picked by their frequency in a sample of
+// the block's rows.  Their elements never enter the sort (dropped by KEY in the first pass and its
+// histogram); the forward kernel reads their weights from shared memory and accumulates their
+// gradient sums itself, in a fixed order; extra CTAs of the update kernel step them.  The choice
+// only affects speed: whatever set is picked, every occurrence of a picked feature goes one way
+// and every other element the other, so no property of the rows has to be verified.
+constexpr int kMaxHot = 64;
+// The kernels test "is this feature hot?" once per element, so the test is one multiply, one shift, one
+// shared-memory load and one compare: a direct-mapped table, index = hot_index(feature), entry = the
+// feature.  The selection kernel only picks features whose indices are pairwise different.
+constexpr int kHotSlotBits = 11;
+constexpr int kHotSlots = 1 << kHotSlotBits;
+constexpr uint32_t kHotEmpty = 0xffffffffu;
+__host__ __device__ inline uint32_t hot_index(uint32_t key) { return (key * 0x9E3779B1u) >> (32 - kHotSlotBits); }
+struct HotInfo {
+    uint32_t count;                    // hot features of this block (0: none)
+    uint32_t pad[3];
+    uint32_t key[kMaxHot];             // ordered by (sample count descending, feature ascending)
 };
 
 // ---- segmented radix sort (hm_sort.cu) ----------------------------------------
@@ -71,20 +78,19 @@ constexpr int kMaxSegs = 256;          // mini-batches sorted per launch
 constexpr int kSortTile = 4096;        // elements per sort tile
 struct SortScratch {
     // device
-    uint32_t *key[2] = {nullptr, nullptr};   // feature ids, ping-pong (unused when the block's values are all 1.0)
-    uint2 *pay[2] = {nullptr, nullptr};      // (row inside the mini-batch, value bits), ping-pong; DenseInfo::unit:
-                                             // packed (feature, row inside the mini-batch) records instead
+    uint32_t *key[2] = {nullptr, nullptr};   // feature ids, ping-pong
+    uint2 *pay[2] = {nullptr, nullptr};      // (row inside the mini-batch, value bits), ping-pong
     uint32_t *tile_hist = nullptr;     // [seg][digit][tile_in_seg]
     int32_t *tile_row0 = nullptr;      // first row (inside its mini-batch) of every tile
     uint32_t *row_sum = nullptr;       // [seg*256 + digit] (+1)
     // Two coordinate systems.  in_*: the block's CSR as it lies in the chunk (what the first pass
-    // reads).  seg_*: the SORTED arrays, from which dense-column and out-of-range elements are
+    // reads).  seg_*: the SORTED arrays, from which hot-feature and out-of-range elements are
     // gone; written on the device after the first pass's histogram (the host never learns them).
     uint32_t *in_off = nullptr;        // [kMaxSegs+1] element offset of each mini-batch in the block's CSR
     uint32_t *in_tile_off = nullptr;   // [kMaxSegs+1]
     uint32_t *seg_off = nullptr;       // [kMaxSegs+1] element offset of each mini-batch in the sorted arrays
     uint32_t *seg_tile_off = nullptr;  // [kMaxSegs+1]
-    DenseInfo *dense = nullptr;        // dense columns of the block (mask 0: none)
+    HotInfo *hot = nullptr;            // hot features of the block (count 0: none)
     int64_t cap_elems = 0;
     int64_t cap_tiles = 0;
 };
@@ -93,9 +99,9 @@ void sort_scratch_free(SortScratch &s);
 // Fill seg_off / seg_tile_off for rows [row0, row0+n_rows) split every `mini_batch` rows.
 hm_status launch_seg_prep(Launcher &L, SortScratch &s, const int64_t *d_rowptr, int64_t row0,
                           int64_t n_rows, int64_t n_elems, int32_t mini_batch, int n_segs);
-// Find the dense columns of rows [row0, row0+n_rows) (s.dense); `enable` false: none.
-hm_status launch_dense_check(Launcher &L, SortScratch &s, const int64_t *d_rowptr, int64_t row0, int64_t n_rows,
-                             const uint32_t *d_feature, const float *d_value, int64_t n_elems, int64_t dims, bool enable);
+// Pick the hot features of rows [row0, row0+n_rows) (s.hot); `enable` false: none.
+hm_status launch_hot_select(Launcher &L, SortScratch &s, const int64_t *d_rowptr, int64_t row0, int64_t n_rows,
+                            const uint32_t *d_feature, int64_t dims, bool enable);
 // Stable sort of each segment by the low `key_bits` bits of the feature id.
 // Result: s.key[*out_buf], s.pay[*out_buf] hold (feature, (row, value)) sorted per segment.
 hm_status launch_segmented_sort(Launcher &L, SortScratch &s, const uint32_t *d_feature_block,
@@ -132,11 +138,12 @@ struct LinearArgs {
     int rec_width;        // 1 (SGD: w), 2 (AdaGrad: w, G; FTRL: z, n), 4 (AdaDelta, Adam: w, s1, s2, unused)
     WeightView wv;
 };
-// Dense columns of the block being trained, and where their column sums travel from the forward
-// kernel to the update kernel.  info == NULL: the block was sorted whole (no dense handling).
-struct DenseCols {
-    const DenseInfo *info = nullptr;
-    double *partial = nullptr;    // [32][stride]
+// Hot features of the block being trained, and where their gradient sums travel from the forward
+// kernel to the update kernel.  info == NULL: the block was sorted whole.
+struct HotCols {
+    const HotInfo *info = nullptr;
+    double *sum = nullptr;        // [kMaxHot][stride]: per forward CTA, the sum of dloss * value over its rows
+    uint32_t *cnt = nullptr;      // [kMaxHot][stride]: ... and the number of occurrences
     int stride = 0;
 };
 int linear_forward_grid(int32_t n_rows);
@@ -144,21 +151,22 @@ int linear_forward_grid(int32_t n_rows);
 hm_status launch_linear_forward(Launcher &L, const LinearArgs &a, const int64_t *d_rowptr, int64_t row0,
                                 int32_t n_rows, int64_t block_row0, const uint32_t *d_feature,
                                 const float *d_value, const float *d_label, float *d_margin,
-                                float *d_dloss, uint32_t *d_bad, int64_t nnz_hint, const DenseCols &dc);
+                                float *d_dloss, uint32_t *d_bad, int64_t nnz_hint, const HotCols &hc);
 // reduce-by-feature over the sorted segment `seg` and apply the optimizer
 struct UpdateScratch {
     void *boundary = nullptr;     // per-CTA open-segment summaries
     uint32_t *done_counter = nullptr;
     int grid = 0;
-    double *dense_partial = nullptr;   // see DenseCols
-    int dense_stride = 0;
+    double *hot_sum = nullptr;         // see HotCols
+    uint32_t *hot_cnt = nullptr;
+    int hot_stride = 0;
 };
 hm_status update_scratch_reserve(UpdateScratch &u);
 void update_scratch_free(UpdateScratch &u);
 hm_status launch_linear_update(Launcher &L, const LinearArgs &a, const StepScalars &sc, UpdateScratch &us,
                                const uint32_t *d_sorted_key, const uint2 *d_sorted_pay,
                                const uint32_t *d_seg_off, int seg, int64_t seg_begin, const float *d_dloss,
-                               int64_t nnz_hint, const DenseCols &dc);
+                               int64_t nnz_hint, const HotCols &hc);
 // small mini-batches (<= 1024 rows and <= one update tile of elements): up to 64 consecutive
 // mini-batches of a sorted block trained by one persistent CTA
 bool small_batch_eligible(int32_t mini_batch, int64_t max_mb_elems);

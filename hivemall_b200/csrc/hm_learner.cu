@@ -112,9 +112,9 @@ struct DevBuf {
 struct SortedBlock {
     int64_t row0 = 0, rows = 0, nnz = 0;
     int n_segs = 0;
-    void *mem = nullptr;                // one allocation: key | pay | seg_off | dense
-    uint32_t *key = nullptr; uint2 *pay = nullptr; uint32_t *seg_off = nullptr; DenseInfo *dense = nullptr;
-    bool dense_on = false;
+    void *mem = nullptr;                // one allocation: key | pay | seg_off | hot
+    uint32_t *key = nullptr; uint2 *pay = nullptr; uint32_t *seg_off = nullptr; HotInfo *hot = nullptr;
+    bool hot_on = false;
 };
 
 // A run of rows resident on the device.  Owned chunks hold copies of host data (rowptr is
@@ -267,7 +267,7 @@ struct hm_udtf {
     int64_t h_small_cap = 0;
     int64_t last_margin_off = 0, last_margin_n = 0;   // last mini-batch's slice of `margin`
     bool device_rows_short = false;  // a process_device call ended on a short mini-batch
-    bool dense_enabled = true;       // HM_DENSE_COLUMNS=0 in the environment sorts every element (A/B measurements)
+    bool hot_enabled = true;         // HM_HOT_FEATURES=0 in the environment sorts every element (A/B measurements)
     hm_stats stats;
     bool closed = false;
     int64_t model_rows = -1;
@@ -408,16 +408,16 @@ hm_status train_rows(hm_udtf *u, Chunk &c, int64_t row0, int64_t n_rows, const i
     int out_buf[2] = {0, 0};
     int64_t call_max_mb = 0;
     for (int64_t m = 0; m < n_mb; m++) call_max_mb = std::max(call_max_mb, mb_abs[m + 1] - mb_abs[m]);
-    // Dense columns (quantitative features at the front of every row) are taken out of the sort and reduced as
-    // column sums by the forward kernel: linear learners on the two-kernel path only.
-    const bool dense_on = !u->fm && u->dense_enabled && !small_batch_eligible(B, call_max_mb);
+    // Hot features (the quantitative features every row has, the head of each categorical field) are taken out
+    // of the sort and reduced by the forward kernel: linear learners on the two-kernel path only.
+    const bool hot_on = !u->fm && u->hot_enabled && !small_batch_eligible(B, call_max_mb);
     auto enqueue_sort = [&](size_t bi) -> hm_status {
         const Plan &p = plan[bi];
         const int set = (int)((u->sort_turn + bi) & 1);
         // the scratch set is free once the block that used it last has been trained
         if (u->trained_valid[set]) HM_CUDA(cudaStreamWaitEvent(u->sorter, u->trained_ev[set], 0));
         HM_TRY(sort_scratch_reserve(u->sort[set], p.nnz));
-        HM_TRY(launch_dense_check(u->Ls, u->sort[set], c.rp(), p.row0, p.rows, c.ft(), c.vl(), p.nnz, u->cfg.dims, dense_on));
+        HM_TRY(launch_hot_select(u->Ls, u->sort[set], c.rp(), p.row0, p.rows, c.ft(), u->cfg.dims, hot_on));
         HM_TRY(launch_seg_prep(u->Ls, u->sort[set], c.rp(), p.row0, p.rows, p.nnz, B, p.n_segs));
         HM_TRY(launch_segmented_sort(u->Ls, u->sort[set], c.ft() + mb_abs[p.m0], c.vl() + mb_abs[p.m0], c.rp(), p.row0,
                                      p.rows, B, p.nnz, p.n_segs, key_bits, u->cfg.dims, u->d_bad, &out_buf[set], 0));
@@ -427,7 +427,7 @@ hm_status train_rows(hm_udtf *u, Chunk &c, int64_t row0, int64_t n_rows, const i
             // training waits for)
             const size_t key_b = ((size_t)p.nnz * 4 + 255) & ~(size_t)255, pay_b = ((size_t)p.nnz * 8 + 255) & ~(size_t)255;
             const size_t off_b = ((size_t)(p.n_segs + 1) * 4 + 255) & ~(size_t)255;
-            const size_t need = key_b + pay_b + off_b + sizeof(DenseInfo);
+            const size_t need = key_b + pay_b + off_b + sizeof(HotInfo);
             size_t free_b = 0, total_b = 0;
             SortedBlock sb;
             if (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess && free_b > need + kKeepFreeFloor &&
@@ -436,14 +436,14 @@ hm_status train_rows(hm_udtf *u, Chunk &c, int64_t row0, int64_t n_rows, const i
                 sb.key = reinterpret_cast<uint32_t *>(base);
                 sb.pay = reinterpret_cast<uint2 *>(base + key_b);
                 sb.seg_off = reinterpret_cast<uint32_t *>(base + key_b + pay_b);
-                sb.dense = reinterpret_cast<DenseInfo *>(base + key_b + pay_b + off_b);
-                sb.row0 = p.row0; sb.rows = p.rows; sb.nnz = p.nnz; sb.n_segs = p.n_segs; sb.dense_on = dense_on;
+                sb.hot = reinterpret_cast<HotInfo *>(base + key_b + pay_b + off_b);
+                sb.row0 = p.row0; sb.rows = p.rows; sb.nnz = p.nnz; sb.n_segs = p.n_segs; sb.hot_on = hot_on;
                 const SortScratch &ss = u->sort[set];
                 // (the sorted arrays are at most nnz long; the tail past the sorted length is never read)
                 HM_CUDA(cudaMemcpyAsync(sb.key, ss.key[out_buf[set]], (size_t)p.nnz * 4, cudaMemcpyDeviceToDevice, u->sorter));
                 HM_CUDA(cudaMemcpyAsync(sb.pay, ss.pay[out_buf[set]], (size_t)p.nnz * 8, cudaMemcpyDeviceToDevice, u->sorter));
                 HM_CUDA(cudaMemcpyAsync(sb.seg_off, ss.seg_off, (size_t)(p.n_segs + 1) * 4, cudaMemcpyDeviceToDevice, u->sorter));
-                HM_CUDA(cudaMemcpyAsync(sb.dense, ss.dense, sizeof(DenseInfo), cudaMemcpyDeviceToDevice, u->sorter));
+                HM_CUDA(cudaMemcpyAsync(sb.hot, ss.hot, sizeof(HotInfo), cudaMemcpyDeviceToDevice, u->sorter));
                 c.sorted.push_back(sb);
             } else {
                 cudaGetLastError();
@@ -476,10 +476,10 @@ hm_status train_rows(hm_udtf *u, Chunk &c, int64_t row0, int64_t n_rows, const i
         const int buf = replay ? 0 : out_buf[set];
         if (replay) {
             const SortedBlock &sb = c.sorted[bi];
-            view.key[0] = sb.key; view.pay[0] = sb.pay; view.seg_off = sb.seg_off; view.dense = sb.dense;
+            view.key[0] = sb.key; view.pay[0] = sb.pay; view.seg_off = sb.seg_off; view.hot = sb.hot;
         }
         SortScratch &ss = replay ? view : u->sort[set];
-        const bool block_dense = replay ? c.sorted[bi].dense_on : dense_on;
+        const bool block_hot = replay ? c.sorted[bi].hot_on : hot_on;
         HM_TRY(u->margin.reserve((size_t)p.rows * sizeof(float)));
         HM_TRY(u->dloss.reserve((size_t)std::min<int64_t>(p.rows, B) * sizeof(float)));
         if (u->fm) {
@@ -488,8 +488,8 @@ hm_status train_rows(hm_udtf *u, Chunk &c, int64_t row0, int64_t n_rows, const i
             HM_TRY(fm_scratch_reserve(u->fms, max_mb, u->k));
             HM_TRY(u->stab.reserve((size_t)std::min<int64_t>(p.rows, B) * u->k * sizeof(float)));
         }
-        DenseCols dc;
-        if (block_dense) { dc.info = ss.dense; dc.partial = u->upd.dense_partial; dc.stride = u->upd.dense_stride; }
+        HotCols hc;
+        if (block_hot) { hc.info = ss.hot; hc.sum = u->upd.hot_sum; hc.cnt = u->upd.hot_cnt; hc.stride = u->upd.hot_stride; }
         if (!u->fm && small_batch_eligible(B, call_max_mb)) {
             // a few hundred rows per mini-batch: up to 64 mini-batches per launch of one persistent CTA
             for (int s0 = 0; s0 < p.n_segs; s0 += 64) {
@@ -528,9 +528,9 @@ hm_status train_rows(hm_udtf *u, Chunk &c, int64_t row0, int64_t n_rows, const i
                                         u->dloss.as<float>(), u->stab.as<float>(), mnnz));
             } else {
                 HM_TRY(launch_linear_forward(u->L, a, c.rp(), mrow0, mrows, p.row0, c.ft(), c.vl(), c.lb(),
-                                             u->margin.as<float>(), u->dloss.as<float>(), u->d_bad, mnnz, dc));
+                                             u->margin.as<float>(), u->dloss.as<float>(), u->d_bad, mnnz, hc));
                 HM_TRY(launch_linear_update(u->L, a, sc, u->upd, ss.key[buf], ss.pay[buf], ss.seg_off, s,
-                                            mb_abs[p.m0 + s] - mb_abs[p.m0], u->dloss.as<float>(), mnnz, dc));
+                                            mb_abs[p.m0 + s] - mb_abs[p.m0], u->dloss.as<float>(), mnnz, hc));
             }
             u->stats.mini_batches++;
             u->last_margin_off = mrow0 - p.row0;
@@ -838,7 +838,7 @@ hm_status create_impl(const hm_config &cfg, int device, hm_udtf **out)
     u->cfg = cfg;
     u->device = device;
     std::memset(&u->stats, 0, sizeof(u->stats));
-    if (const char *e = std::getenv("HM_DENSE_COLUMNS")) u->dense_enabled = std::atoi(e) != 0;
+    if (const char *e = std::getenv("HM_HOT_FEATURES")) u->hot_enabled = std::atoi(e) != 0;
     hm_status s = [&]() -> hm_status {
         {
             // the training stream's short kernels go first whenever both streams have CTAs to place
@@ -1473,20 +1473,19 @@ hm_status hm_udtf_last_margins(hm_udtf *u, float *host, int64_t cap, int64_t *n)
     return HM_OK;
 }
 
-hm_status hm_udtf_dense_columns(hm_udtf *u, int32_t *feature, int32_t cap, int32_t *n)
+hm_status hm_udtf_hot_features(hm_udtf *u, int32_t *feature, int32_t cap, int32_t *n)
 {
-    if (!u || !n || cap < 0 || (cap > 0 && !feature)) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "bad arguments to dense_columns");
+    if (!u || !n || cap < 0 || (cap > 0 && !feature)) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "bad arguments to hot_features");
     *n = 0;
     if (u->sort_turn == 0) return HM_OK;
     DeviceGuard g(u->device);
     const SortScratch &ss = u->sort[(u->sort_turn - 1) & 1];
-    if (!ss.dense) return HM_OK;
+    if (!ss.hot) return HM_OK;
     HM_CUDA(cudaStreamSynchronize(u->sorter));
-    DenseInfo di;
-    HM_CUDA(cudaMemcpy(&di, ss.dense, sizeof(di), cudaMemcpyDeviceToHost));
-    int32_t m = 0;
-    for (int i = 0; i < 32; i++)
-        if ((di.mask >> i) & 1u) { if (m < cap) feature[m] = (int32_t)di.key[i]; m++; }
+    HotInfo hi;
+    HM_CUDA(cudaMemcpy(&hi, ss.hot, sizeof(hi), cudaMemcpyDeviceToHost));
+    const int32_t m = (int32_t)std::min<uint32_t>(hi.count, (uint32_t)kMaxHot);
+    for (int32_t i = 0; i < m && i < cap; i++) feature[i] = (int32_t)hi.key[i];
     *n = std::min(m, cap);
     return HM_OK;
 }

@@ -109,12 +109,13 @@ struct FwdParams {
     int32_t train;           // 0: prediction only
     uint32_t dims;
     uint32_t *bad;           // set to 1 when a feature index >= dims is met (that element scores 0)
-    // dense columns of the block (training only; NULL: none).  Lane i of a warp owns position i of
-    // its rows: the weight of a dense column sits in a register instead of being gathered, and the
-    // column's gradient sum is accumulated right here, in a fixed order, instead of being sorted.
-    const DenseInfo *dense;
-    double *dense_partial;   // [32][dense_stride]: per forward CTA, the column sums of its rows
-    int32_t dense_stride;
+    // hot features of the block (training only; NULL: none): their weights are read from shared memory
+    // instead of being gathered, and their gradient sums are accumulated right here, in a fixed order,
+    // instead of being sorted.
+    const HotInfo *hot;
+    double *hot_sum;         // [kMaxHot][hot_stride]: per forward CTA, sum of dloss * value over its rows
+    uint32_t *hot_cnt;       // [kMaxHot][hot_stride]: ... and the number of occurrences
+    int32_t hot_stride;
 };
 
 // Margins (and dloss) of rows r = warp_first, warp_first + warp_stride, ... of the mini-batch: one
@@ -146,107 +147,115 @@ __device__ __forceinline__ void forward_rows(const FwdParams &P, int warp_first,
     }
 }
 
-// Training forward of the two-kernel path: FOUR consecutive rows per warp at a time.  The kernel is
-// bound by the latency of each row's chain (row pointer -> feature/value -> weight gather), so the
-// loads of four rows (positions 0..63 of each) are all issued before the first is used.  Lane i owns
-// position i of a row.  With dense columns (DenseInfo; every row of the block then has the block's
-// dense positions) the weight of a dense column sits in a register instead of being gathered, and
-// the column's gradient sum is accumulated here.  The margin adds the same fp32 products as
-// forward_rows in the same lane order (fp64), so the two agree bit for bit.
-template <bool DENSE>
-__device__ __forceinline__ void forward_rows4(const FwdParams &P, int warp_first, int warp_stride, double *s_part)
+// ---- hot features in the forward kernel ------------------------------------------------------
+constexpr uint32_t kHotNone = 0xffffffffu;
+
+struct HotShared {                          // shared memory of a forward CTA that handles hot features
+    uint32_t tab_key[kHotSlots];            // direct-mapped (hot_index): key -> slot (index into HotInfo::key)
+    uint8_t tab_slot[kHotSlots];
+    float w[kMaxHot];                       // the hot features' weights at the start of the mini-batch
+    double acc[kFwdThreads / 32][kMaxHot];  // per warp: sum of dloss * value per hot feature
+    uint32_t cnt[kFwdThreads / 32][kMaxHot];
+    uint32_t claim[kFwdThreads / 32][kMaxHot];
+};
+
+__device__ __forceinline__ uint32_t hot_slot_of(const HotShared &H, uint32_t key)
 {
-    constexpr int RW = 4;
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    bool mine = false;
-    float wd = 0.0f;
-    if (DENSE) {
-        const uint32_t dmask = P.dense->mask;
-        mine = (dmask >> lane) & 1u;
-        if (mine) wd = weight_at<true>(P.wv, P.dense->key[lane]);
-    }
-    double dacc = 0.0;
-    for (int r = warp_first * RW; r < P.n_rows; r += warp_stride * RW) {
-        const int64_t rp = (lane <= RW && r + lane <= P.n_rows) ? P.rowptr[P.row0 + r + lane] : 0;
-        float lab = 0.0f;
-        if (lane < RW && r + lane < P.n_rows) lab = P.label[P.row0 + r + lane];
-        int64_t p0[RW], p1[RW];
-        bool in[RW], in2[RW];
-        uint32_t f[RW], g[RW];
-        float x[RW], y2[RW];
-#pragma unroll
-        for (int u = 0; u < RW; u++) {
-            p0[u] = __shfl_sync(0xffffffffu, rp, u);
-            p1[u] = __shfl_sync(0xffffffffu, rp, u + 1);
-            const bool row = r + u < P.n_rows;
-            in[u] = row && p0[u] + lane < p1[u];
-            in2[u] = row && p0[u] + 32 + lane < p1[u];
-        }
-#pragma unroll
-        for (int u = 0; u < RW; u++) {
-            f[u] = in[u] ? __ldcs(P.feature + p0[u] + lane) : 0u;
-            x[u] = in[u] ? __ldcs(P.value + p0[u] + lane) : 0.0f;
-        }
-#pragma unroll
-        for (int u = 0; u < RW; u++) {
-            g[u] = in2[u] ? __ldcs(P.feature + p0[u] + 32 + lane) : 0u;
-            y2[u] = in2[u] ? __ldcs(P.value + p0[u] + 32 + lane) : 0.0f;
-        }
-        // gathers of the four rows, all in flight together
-        float w1[RW], w2[RW];
-#pragma unroll
-        for (int u = 0; u < RW; u++) {
-            w1[u] = 0.0f; w2[u] = 0.0f;
-            if (in[u]) {
-                if (DENSE && mine) w1[u] = wd;
-                else if (f[u] < P.dims) w1[u] = weight_at<true>(P.wv, f[u]);
-                else { in[u] = false; atomicOr(P.bad, 1u); }
-            }
-            if (in2[u]) {
-                if (g[u] < P.dims) w2[u] = weight_at<true>(P.wv, g[u]);
-                else { in2[u] = false; atomicOr(P.bad, 1u); }
-            }
-        }
-        float dl[RW];
-#pragma unroll
-        for (int u = 0; u < RW; u++) {
-            double acc = 0.0;
-            if (in[u]) acc += (double)__fmul_rn(w1[u], x[u]);
-            if (in2[u]) acc += (double)__fmul_rn(w2[u], y2[u]);
-            if (r + u < P.n_rows) {       // (uniform over the warp) rows longer than 64 elements
-                for (int64_t p = p0[u] + 64 + lane; p < p1[u]; p += 32) {
-                    const uint32_t f3 = __ldcs(P.feature + p);
-                    const float x3 = __ldcs(P.value + p);
-                    if (f3 < P.dims) acc += (double)__fmul_rn(weight_at<true>(P.wv, f3), x3);
-                    else atomicOr(P.bad, 1u);
-                }
-            }
-            acc = warp_sum(acc);
-            dl[u] = 0.0f;
-            if (r + u < P.n_rows) {
-                const float m = (float)acc;
-                const float lb = __shfl_sync(0xffffffffu, lab, u);
-                const float yy = P.task == HM_TASK_CLASSIFIER ? (lb > 0.0f ? 1.0f : -1.0f) : lb;
-                dl[u] = dloss_of(P.loss, m, yy);
-                if (lane == 0) { P.margin[P.row0 + r + u - P.block_row0] = m; P.dloss[r + u] = dl[u]; }
-            }
-        }
-        if (DENSE && mine) {
-#pragma unroll
-            for (int u = 0; u < RW; u++)
-                if (r + u < P.n_rows) dacc += (double)__fmul_rn(dl[u], x[u]);   // the contribution the update kernel would have sorted
+    const uint32_t h = hot_index(key);
+    return H.tab_key[h] == key ? (uint32_t)H.tab_slot[h] : kHotNone;
+}
+
+// Add this warp's contributions c (lanes with slot != kHotNone) to the warp's accumulators.  Lanes that
+// hit DIFFERENT slots add at once; when two lanes hit the same slot (a feature twice in one row) the adds
+// are done one lane at a time in lane order, so that the sum's order is fixed.
+__device__ __forceinline__ void hot_accumulate(HotShared &H, int warp, int lane, uint32_t slot, float c)
+{
+    const bool hot = slot != kHotNone;
+    const uint32_t hot_lanes = __ballot_sync(0xffffffffu, hot);
+    if (hot_lanes == 0u) return;
+    if (hot) H.claim[warp][slot] = (uint32_t)lane;
+    __syncwarp();
+    const bool lost = hot && H.claim[warp][slot] != (uint32_t)lane;
+    if (!__any_sync(0xffffffffu, lost)) {
+        if (hot) { H.acc[warp][slot] += (double)c; H.cnt[warp][slot] += 1u; }
+    } else {
+        for (uint32_t m = hot_lanes; m != 0u; m &= m - 1u) {
+            if (lane == __ffs(m) - 1) { H.acc[warp][slot] += (double)c; H.cnt[warp][slot] += 1u; }
+            __syncwarp();
         }
     }
-    if (DENSE) {
-        // column sums of this CTA's rows: warps added in a fixed order
-        s_part[warp * 32 + lane] = dacc;
-        __syncthreads();
-        if (warp == 0) {
-            double sum = 0.0;
-#pragma unroll
-            for (int w2i = 0; w2i < kFwdThreads / 32; w2i++) sum += s_part[w2i * 32 + lane];
-            P.dense_partial[(size_t)lane * P.dense_stride + blockIdx.x] = sum;
+    __syncwarp();
+}
+
+// forward_rows with hot features.  The margin adds the same fp32 products in the same lane order as
+// forward_rows: only the source of a hot feature's weight differs (shared memory instead of the gather;
+// it is the same number).  After a row's dloss is known, the contributions dloss * value of its hot
+// elements (what the update kernel would otherwise have found in the sorted stream) go to the warp's
+// accumulators; rows longer than 64 elements re-read their tail for that.
+__device__ __forceinline__ void forward_rows_hot(const FwdParams &P, int warp_first, int warp_stride, HotShared &H)
+{
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const uint32_t n_hot = P.hot->count;
+    for (int q = tid; q < kHotSlots; q += kFwdThreads) H.tab_key[q] = kHotNone;
+    for (int q = tid; q < (kFwdThreads / 32) * kMaxHot; q += kFwdThreads) { (&H.acc[0][0])[q] = 0.0; (&H.cnt[0][0])[q] = 0u; }
+    __syncthreads();
+    if (tid < (int)n_hot) {
+        const uint32_t key = P.hot->key[tid];
+        H.w[tid] = key < P.dims ? weight_at<true>(P.wv, key) : 0.0f;
+        const uint32_t h = hot_index(key);     // (pairwise different for the keys of a HotInfo)
+        H.tab_key[h] = key;
+        H.tab_slot[h] = (uint8_t)tid;
+    }
+    __syncthreads();
+    for (int r = warp_first; r < P.n_rows; r += warp_stride) {
+        const int64_t row = P.row0 + r;
+        const int64_t p0 = P.rowptr[row], p1 = P.rowptr[row + 1];
+        double acc = 0.0;
+        uint32_t slot_a = kHotNone, slot_b = kHotNone;     // this lane's elements at positions lane and 32 + lane
+        float x_a = 0.0f, x_b = 0.0f;
+        for (int64_t p = p0 + lane; p < p1; p += 32) {
+            const uint32_t f = __ldcs(P.feature + p);
+            const float x = __ldcs(P.value + p);
+            if (f < P.dims) {
+                const uint32_t sl = hot_slot_of(H, f);
+                const float w = sl != kHotNone ? H.w[sl] : weight_at<true>(P.wv, f);
+                acc += (double)__fmul_rn(w, x);
+                if (p == p0 + lane) { slot_a = sl; x_a = x; }
+                else if (p == p0 + 32 + lane) { slot_b = sl; x_b = x; }
+            } else atomicOr(P.bad, 1u);
         }
+        acc = warp_sum(acc);
+        const float m = (float)acc;
+        float dl = 0.0f;
+        if (lane == 0) {
+            P.margin[row - P.block_row0] = m;
+            const float lab = P.label[row];
+            const float y = P.task == HM_TASK_CLASSIFIER ? (lab > 0.0f ? 1.0f : -1.0f) : lab;
+            dl = dloss_of(P.loss, m, y);
+            P.dloss[r] = dl;
+        }
+        dl = __shfl_sync(0xffffffffu, dl, 0);
+        hot_accumulate(H, warp, lane, slot_a, __fmul_rn(dl, x_a));
+        if (p1 - p0 > 32) hot_accumulate(H, warp, lane, slot_b, __fmul_rn(dl, x_b));
+        for (int64_t q0 = p0 + 64; q0 < p1; q0 += 32) {       // (uniform over the warp)
+            const int64_t p = q0 + lane;
+            uint32_t sl = kHotNone; float x = 0.0f;
+            if (p < p1) {
+                const uint32_t f = __ldcs(P.feature + p);
+                x = __ldcs(P.value + p);
+                if (f < P.dims) sl = hot_slot_of(H, f);
+            }
+            hot_accumulate(H, warp, lane, sl, __fmul_rn(dl, x));
+        }
+    }
+    // this CTA's sums: warps added in a fixed order
+    __syncthreads();
+    if (tid < (int)n_hot) {
+        double sum = 0.0; uint32_t cnt = 0;
+#pragma unroll
+        for (int w2 = 0; w2 < kFwdThreads / 32; w2++) { sum += H.acc[w2][tid]; cnt += H.cnt[w2][tid]; }
+        P.hot_sum[(size_t)tid * P.hot_stride + blockIdx.x] = sum;
+        P.hot_cnt[(size_t)tid * P.hot_stride + blockIdx.x] = cnt;
     }
 }
 
@@ -307,13 +316,12 @@ __device__ __forceinline__ void forward_rows_small(const FwdParams &P)
     }
 }
 
-__global__ void __launch_bounds__(kFwdThreads, 3) linear_forward_kernel(FwdParams P)
+__global__ void __launch_bounds__(kFwdThreads, 8) linear_forward_kernel(FwdParams P)
 {
-    __shared__ double s_part[kFwdThreads];
+    __shared__ HotShared H;
     const int warp_first = blockIdx.x * (kFwdThreads / 32) + (threadIdx.x >> 5), warp_stride = gridDim.x * (kFwdThreads / 32);
-    if (!P.train) forward_rows<true>(P, warp_first, warp_stride);       // prediction
-    else if (P.dense && P.dense->mask != 0u) forward_rows4<true>(P, warp_first, warp_stride, s_part);
-    else forward_rows4<false>(P, warp_first, warp_stride, s_part);
+    if (P.hot && P.hot->count != 0u) forward_rows_hot(P, warp_first, warp_stride, H);
+    else forward_rows<true>(P, warp_first, warp_stride);
 }
 
 // ---- update ------------------------------------------------------------------------
@@ -324,7 +332,10 @@ struct SegRec {           // a (feature, partial sum) record; cnt == 0 means emp
 };
 static_assert(sizeof(SegRec) == 16, "boundary records travel as 16-byte vectors");
 
-constexpr int kUpdMaxGrid = 1536;     // CTAs per launch; beyond that each CTA walks consecutive tiles
+#ifndef HM_UPD_MAXGRID
+#define HM_UPD_MAXGRID 1536
+#endif
+constexpr int kUpdMaxGrid = HM_UPD_MAXGRID;     // CTAs per launch; beyond that each CTA walks consecutive tiles
 
 // Segments that really straddle CTAs are the hot features' long runs.  Each CTA leaves two
 // 16-byte records: `first` = its piece of a segment that began in an earlier CTA (or the
@@ -352,12 +363,12 @@ struct UpdParams {
     double inv_rows;         // 1 / rows of the mini-batch, computed on the host in fp64
     int32_t n_active;        // CTAs launched (all own at least one tile unless the segment is empty)
     // (the mini-batch's bounds in the sorted arrays are read from seg_off: the sorted arrays are shorter
-    // than the CSR by the dense-column and out-of-range elements, a number only the device knows)
-    // dense columns of the block (NULL: the block was sorted whole)
-    const DenseInfo *dense;
-    const double *dense_partial;   // [32][dense_stride] column sums left by the forward kernel's CTAs
-    int32_t dense_stride, fwd_grid;
-    int32_t n_rows;          // rows of the mini-batch (= occurrences of every dense column)
+    // than the CSR by the hot-feature and out-of-range elements, a number only the device knows)
+    // hot features of the block (NULL: the block was sorted whole)
+    const HotInfo *hot;
+    const double *hot_sum;   // [kMaxHot][hot_stride] gradient sums left by the forward kernel's CTAs
+    const uint32_t *hot_cnt; // ... and occurrence counts
+    int32_t hot_stride, fwd_grid;
 };
 
 // Replica record of one feature while it is being updated.
@@ -521,26 +532,17 @@ struct UpdShared {
 // segmented scan in a fixed order, finished features compacted into S.l_key / S.l_g (*S.s_nlist
 // entries, to be stepped by apply_list), open segments left in S.s_carry / S.s_first.  Ends on a
 // barrier.  RO: dloss was written by an earlier kernel and may use the read-only path.
-// unit: the block's sorted values are all 1.0 and spay holds packed (feature, row) records (DenseInfo::unit).
 template <bool RO>
 __device__ __forceinline__ void reduce_tile(const UpdParams &P, const UpdShared &S, uint32_t base, int n_tile,
-                                            bool first_tile, bool last_tile, bool unit = false)
+                                            bool first_tile, bool last_tile)
 {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     // ---- coalesced striped load; contribution = dloss[row] * value (fp32 product)
     uint32_t k[kUpdItems]; uint2 pv[kUpdItems];
-    if (unit) {
 #pragma unroll
-        for (int i = 0; i < kUpdItems; i++) {
-            const int q = i * kUpdThreads + tid;
-            if (q < n_tile) { const uint2 r = __ldcs(P.spay + base + q); k[i] = r.x; pv[i] = make_uint2(r.y, 0x3f800000u); }
-        }
-    } else {
-#pragma unroll
-        for (int i = 0; i < kUpdItems; i++) {
-            const int q = i * kUpdThreads + tid;
-            if (q < n_tile) { k[i] = __ldcs(P.skey + base + q); pv[i] = __ldcs(P.spay + base + q); }
-        }
+    for (int i = 0; i < kUpdItems; i++) {
+        const int q = i * kUpdThreads + tid;
+        if (q < n_tile) { k[i] = __ldcs(P.skey + base + q); pv[i] = __ldcs(P.spay + base + q); }
     }
 #pragma unroll
     for (int i = 0; i < kUpdItems; i++) {
@@ -684,58 +686,50 @@ __device__ __forceinline__ void reduce_tile(const UpdParams &P, const UpdShared 
     __syncthreads();
 }
 
-// Optimizer step of the block's dense columns: one warp per column adds the forward CTAs' partial
-// sums in a fixed order.  Runs as one extra CTA of the update kernel; the features are disjoint
-// from everything the sorted stream holds (dense_check_kernel), so nothing else touches their records.
-__device__ __noinline__ void dense_columns_step(const UpdParams &P)
+// Optimizer step of the block's hot features: one warp per feature adds the forward CTAs' partial sums
+// in a fixed order.  Runs in kHotCtas extra CTAs of the update kernel; the features are disjoint from
+// everything the sorted stream holds (the sort dropped them by key), so nothing else touches their
+// records.  A hot feature that does not occur in this mini-batch is left alone, like any other.
+constexpr int kHotCtas = kMaxHot / (kUpdThreads / 32);
+
+__device__ __noinline__ void hot_features_step(const UpdParams &P, int part)
 {
-    const uint32_t dmask = P.dense->mask;
     const int lane = threadIdx.x & 31;
-    for (int i = threadIdx.x >> 5; i < 32; i += kUpdThreads / 32) {
-        if (!((dmask >> i) & 1u)) continue;
-        const double *col = P.dense_partial + (size_t)i * P.dense_stride;
-        double sum = 0.0;
-        for (int c = lane; c < P.fwd_grid; c += 32) sum += col[c];
-        sum = warp_sum(sum);
-        if (lane == 0) {
-            const uint32_t j = P.dense->key[i];
-            Rec r = load_rec(P, j);
-            step_rec(P, r, grad_of(P, sum, (uint32_t)P.n_rows));
-            store_rec(P, j, r);
-        }
+    const int i = part * (kUpdThreads / 32) + (threadIdx.x >> 5);
+    if (i >= (int)P.hot->count) return;
+    const double *col = P.hot_sum + (size_t)i * P.hot_stride;
+    const uint32_t *ccol = P.hot_cnt + (size_t)i * P.hot_stride;
+    double sum = 0.0; uint32_t cnt = 0;
+    for (int c = lane; c < P.fwd_grid; c += 32) { sum += col[c]; cnt += ccol[c]; }
+    sum = warp_sum(sum);
+    cnt = __reduce_add_sync(0xffffffffu, cnt);
+    if (lane == 0 && cnt != 0u) {
+        const uint32_t j = P.hot->key[i];
+        Rec r = load_rec(P, j);
+        step_rec(P, r, grad_of(P, sum, cnt));
+        store_rec(P, j, r);
     }
 }
 
-// Shared memory of one update CTA (declared once in the kernel; the two bodies share it).
-struct UpdSmem {
-    __align__(16) unsigned char raw[kUpdSmem];
-    Scan warp[kUpdThreads / 32];
-    SegRec carry;            // open trailing segment of the previous tile
-    SegRec first;            // the CTA's piece of a segment that began before its range
-    uint32_t carry_open;
-    uint32_t is_last;
-    uint32_t edge[2];        // does the CTA's range start / end on a true segment boundary?
-    int nlist;
-};
-
-// UNIT: the block's sorted values are all 1.0; spay holds packed (feature, row) records (DenseInfo::unit).
-template <bool UNIT>
-__device__ __forceinline__ void update_body(const UpdParams &P, UpdSmem &sm, uint32_t s0, uint32_t n)
+__global__ void __launch_bounds__(kUpdThreads, 4) linear_update_kernel(const __grid_constant__ UpdParams P)
 {
-    unsigned char *smem_raw = sm.raw;
+    __shared__ __align__(16) unsigned char smem_raw[kUpdSmem];
     uint32_t *s_key = reinterpret_cast<uint32_t *>(smem_raw);
     float *s_val = reinterpret_cast<float *>(smem_raw + (size_t)kUpdPadded * 4);
     uint32_t *l_key = reinterpret_cast<uint32_t *>(smem_raw + (size_t)kUpdPadded * 8);
     float *l_g = reinterpret_cast<float *>(smem_raw + (size_t)kUpdPadded * 8 + (size_t)kUpdList * 4);
-    Scan *s_warp = sm.warp;
-    SegRec &s_carry = sm.carry;
-    SegRec &s_first = sm.first;
-    uint32_t &s_carry_open = sm.carry_open;
-    uint32_t &s_is_last = sm.is_last;
-    uint32_t *s_edge = sm.edge;
-    int &s_nlist = sm.nlist;
-    constexpr bool unit = UNIT;
+    __shared__ Scan s_warp[kUpdThreads / 32];
+    __shared__ SegRec s_carry;       // open trailing segment of the previous tile
+    __shared__ SegRec s_first;       // the CTA's piece of a segment that began before its range
+    __shared__ uint32_t s_carry_open;
+    __shared__ uint32_t s_is_last;
+    __shared__ uint32_t s_edge[2];   // does the CTA's range start / end on a true segment boundary?
+    __shared__ int s_nlist;
+
     const int tid = threadIdx.x;
+    USTAMP(0);
+    if ((int)blockIdx.x >= P.n_active) { hot_features_step(P, (int)blockIdx.x - P.n_active); return; }
+    const uint32_t s0 = P.seg_off[P.seg], n = P.seg_off[P.seg + 1] - s0;
     // contiguous split of the sorted mini-batch over the grid, in whole tiles
     const uint32_t tiles = (n + kUpdTile - 1) / kUpdTile;
     const uint32_t tiles_per_cta = (tiles + P.n_active - 1) / P.n_active;
@@ -748,21 +742,20 @@ __device__ __forceinline__ void update_body(const UpdParams &P, UpdSmem &sm, uin
     // The four loads are issued here and only consumed after the first tile's barrier, so they
     // overlap the tile loads instead of adding a round trip.
     if (tid == 32 && lo < hi) {
-        auto key_at = [&](uint32_t e) -> uint32_t { return unit ? __ldg(&P.spay[e].x) : __ldg(P.skey + e); };
-        const uint32_t a0 = lo == 0 ? 0u : key_at(s0 + lo - 1), a1 = key_at(s0 + lo);
-        const uint32_t b0 = key_at(s0 + hi - 1), b1 = hi == n ? 0u : key_at(s0 + hi);
+        const uint32_t a0 = lo == 0 ? 0u : __ldg(P.skey + s0 + lo - 1), a1 = __ldg(P.skey + s0 + lo);
+        const uint32_t b0 = __ldg(P.skey + s0 + hi - 1), b1 = hi == n ? 0u : __ldg(P.skey + s0 + hi);
         s_edge[0] = lo == 0 || a0 != a1;
         s_edge[1] = hi == n || b0 != b1;
     }
     if (lo >= hi) __syncthreads();   // (the tile loop below has its own barriers)
 
     UpdShared S;
-    S.s_key = s_key; S.s_val = s_val; S.l_key = l_key; S.l_g = l_g; S.s_warp = s_warp; S.s_carry = &sm.carry;
-    S.s_first = &sm.first; S.s_carry_open = &sm.carry_open; S.s_edge = s_edge; S.s_nlist = &sm.nlist;
+    S.s_key = s_key; S.s_val = s_val; S.l_key = l_key; S.l_g = l_g; S.s_warp = s_warp; S.s_carry = &s_carry;
+    S.s_first = &s_first; S.s_carry_open = &s_carry_open; S.s_edge = s_edge; S.s_nlist = &s_nlist;
     for (uint32_t t0 = lo; t0 < hi; t0 += kUpdTile) {
         const int n_tile = (int)min((uint32_t)kUpdTile, hi - t0);
         const bool last_tile = t0 + kUpdTile >= hi;
-        reduce_tile<true>(P, S, s0 + t0, n_tile, t0 == lo, last_tile, unit);
+        reduce_tile<true>(P, S, s0 + t0, n_tile, t0 == lo, last_tile);
         USTAMP(3);
         // ---- after the last tile the CTA's boundary pieces are final: publish them and take the
         // completion ticket now, so that both round trips overlap the optimizer step below
@@ -828,16 +821,6 @@ __device__ __forceinline__ void update_body(const UpdParams &P, UpdSmem &sm, uin
     apply_list(P, ml_key, ml_g, s_nlist, tid);
     USTAMP(6);
     if (tid == 0) *P.br.ticket = 0;   // ready for the next launch on this stream
-}
-
-__global__ void __launch_bounds__(kUpdThreads, 4) linear_update_kernel(const __grid_constant__ UpdParams P)
-{
-    __shared__ UpdSmem sm;
-    USTAMP(0);
-    if (P.dense && (int)blockIdx.x == P.n_active) { dense_columns_step(P); return; }
-    const uint32_t s0 = P.seg_off[P.seg], n = P.seg_off[P.seg + 1] - s0;
-    if (P.dense && P.dense->unit != 0u) update_body<true>(P, sm, s0, n);     // (uniform over the grid)
-    else update_body<false>(P, sm, s0, n);
 }
 
 // ---- small mini-batches: one persistent CTA ----------------------------------------
@@ -944,7 +927,7 @@ export_count_kernel(WeightView wv, const uint8_t *__restrict__ touched, int64_t 
 
 __global__ void __launch_bounds__(1024) export_scan_kernel(uint32_t *__restrict__ counts, int n, int64_t *total)
 {
-    // exclusive scan of counts[0..n) by one CTA; *total receives the sum
+    // exclusive scan of counts[0..n) by one CTA; counts[n] and *total receive the sum
     __shared__ uint32_t warp_tot[32];
     const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
     const int per = (n + 1023) / 1024;
@@ -1042,24 +1025,23 @@ int grid_for(int64_t ctas_wanted, int per_sm)
 
 }  // namespace
 
-// (a warp takes four rows at a time, a CTA of eight warps 32)
-int linear_forward_grid(int32_t n_rows) { return grid_for(((int64_t)n_rows + 31) / 32, 8); }
+int linear_forward_grid(int32_t n_rows) { return grid_for(((int64_t)n_rows + 7) / 8, 8); }
 
 hm_status launch_linear_forward(Launcher &L, const LinearArgs &a, const int64_t *d_rowptr, int64_t row0,
                                 int32_t n_rows, int64_t block_row0, const uint32_t *d_feature,
                                 const float *d_value, const float *d_label, float *d_margin,
-                                float *d_dloss, uint32_t *d_bad, int64_t nnz_hint, const DenseCols &dc)
+                                float *d_dloss, uint32_t *d_bad, int64_t nnz_hint, const HotCols &hc)
 {
     if (n_rows <= 0) return HM_OK;
     FwdParams P;
-    P.dense = dc.info; P.dense_partial = dc.partial; P.dense_stride = dc.stride;
+    P.hot = hc.info; P.hot_sum = hc.sum; P.hot_cnt = hc.cnt; P.hot_stride = hc.stride;
     P.wv = a.wv; P.rowptr = d_rowptr; P.feature = d_feature; P.value = d_value; P.label = d_label;
     P.margin = d_margin; P.dloss = d_dloss;
     P.block_row0 = block_row0; P.row0 = row0; P.n_rows = n_rows;
     P.task = a.cfg.task; P.loss = a.cfg.loss; P.train = 1;
     P.dims = (uint32_t)a.cfg.dims; P.bad = d_bad;
     const int grid = linear_forward_grid(n_rows);
-    if (dc.info && grid > dc.stride) HM_FAIL(HM_ERR_STATE, "dense-column scratch too small (%d > %d)", grid, dc.stride);
+    if (hc.info && grid > hc.stride) HM_FAIL(HM_ERR_STATE, "hot-feature scratch too small (%d > %d)", grid, hc.stride);
     // algorithmic bytes: feature+value read, w gather per element; rowptr, label, margin, dloss per row
     const double bytes = 12.0 * (double)nnz_hint + 20.0 * (double)n_rows;
     HM_LAUNCH(L, K_LIN_FORWARD, bytes, (linear_forward_kernel<<<grid, kFwdThreads, 0, L.stream>>>(P)));
@@ -1078,7 +1060,7 @@ hm_status launch_predict_linear(Launcher &L, const WeightView &wv, int64_t dims,
     P.block_row0 = 0; P.row0 = 0; P.n_rows = (int32_t)n_rows;
     P.task = 0; P.loss = 0; P.train = 0;
     P.dims = (uint32_t)dims; P.bad = d_bad;
-    P.dense = nullptr; P.dense_partial = nullptr; P.dense_stride = 0;
+    P.hot = nullptr; P.hot_sum = nullptr; P.hot_cnt = nullptr; P.hot_stride = 0;
     const int grid = grid_for((n_rows + 7) / 8, 8);
     HM_LAUNCH(L, K_PREDICT, 0.0, (linear_forward_kernel<<<grid, kFwdThreads, 0, L.stream>>>(P)));
     HM_CUDA(cudaGetLastError());
@@ -1094,29 +1076,31 @@ hm_status update_scratch_reserve(UpdateScratch &u)
     HM_CUDA(cudaMalloc(&u.boundary, bytes));
     HM_CUDA(cudaMemset(u.boundary, 0, bytes));
     u.done_counter = reinterpret_cast<uint32_t *>(static_cast<char *>(u.boundary) + (size_t)2 * u.grid * 16);
-    // column sums of the dense columns: one double per (column, forward CTA)
-    u.dense_stride = num_sms() * 8;
-    HM_CUDA(cudaMalloc(&u.dense_partial, (size_t)32 * u.dense_stride * sizeof(double)));
-    HM_CUDA(cudaMemset(u.dense_partial, 0, (size_t)32 * u.dense_stride * sizeof(double)));
+    // gradient sums of the hot features: one double and one count per (feature, forward CTA)
+    u.hot_stride = num_sms() * 8;
+    HM_CUDA(cudaMalloc(&u.hot_sum, (size_t)kMaxHot * u.hot_stride * sizeof(double)));
+    HM_CUDA(cudaMalloc(&u.hot_cnt, (size_t)kMaxHot * u.hot_stride * sizeof(uint32_t)));
+    HM_CUDA(cudaMemset(u.hot_sum, 0, (size_t)kMaxHot * u.hot_stride * sizeof(double)));
+    HM_CUDA(cudaMemset(u.hot_cnt, 0, (size_t)kMaxHot * u.hot_stride * sizeof(uint32_t)));
     return HM_OK;
 }
 
 void update_scratch_free(UpdateScratch &u)
 {
     cudaFree(u.boundary);
-    cudaFree(u.dense_partial);
-    u.boundary = nullptr; u.done_counter = nullptr; u.grid = 0; u.dense_partial = nullptr; u.dense_stride = 0;
+    cudaFree(u.hot_sum); cudaFree(u.hot_cnt);
+    u.boundary = nullptr; u.done_counter = nullptr; u.grid = 0; u.hot_sum = nullptr; u.hot_cnt = nullptr; u.hot_stride = 0;
 }
 
 hm_status launch_linear_update(Launcher &L, const LinearArgs &a, const StepScalars &sc, UpdateScratch &us,
                                const uint32_t *d_sorted_key, const uint2 *d_sorted_pay,
                                const uint32_t *d_seg_off, int seg, int64_t seg_begin, const float *d_dloss, int64_t nnz_hint,
-                               const DenseCols &dc)
+                               const HotCols &hc)
 {
     UpdParams P;
     (void)seg_begin;
-    P.dense = dc.info; P.dense_partial = dc.partial; P.dense_stride = dc.stride;
-    P.fwd_grid = linear_forward_grid(sc.n_rows); P.n_rows = sc.n_rows;
+    P.hot = hc.info; P.hot_sum = hc.sum; P.hot_cnt = hc.cnt; P.hot_stride = hc.stride;
+    P.fwd_grid = linear_forward_grid(sc.n_rows);
     P.rec = a.rec; P.rec_width = a.rec_width; P.ftrl_derived = a.wv.ftrl; P.touched = nullptr;
     P.skey = d_sorted_key; P.spay = d_sorted_pay; P.dloss = d_dloss; P.seg_off = d_seg_off;
     P.br.first = reinterpret_cast<uint4 *>(us.boundary);
@@ -1137,9 +1121,9 @@ hm_status launch_linear_update(Launcher &L, const LinearArgs &a, const StepScala
     // algorithmic bytes: sorted feature + (row, value) stream; dloss table and the per-feature
     // state traffic (number of distinct features is data dependent) are not counted
     const double bytes = 12.0 * (double)nnz_hint;
-    // (with dense columns: nnz_hint bounds the sorted mini-batch from above, CTAs past its end find nothing
-    // to do; one more CTA steps the dense columns)
-    HM_LAUNCH(L, K_LIN_UPDATE, bytes, (linear_update_kernel<<<grid + (dc.info ? 1 : 0), kUpdThreads, 0, L.stream>>>(P)));
+    // (nnz_hint bounds the sorted mini-batch from above: CTAs past its end find nothing to do; kHotCtas
+    // more CTAs step the hot features)
+    HM_LAUNCH(L, K_LIN_UPDATE, bytes, (linear_update_kernel<<<grid + (hc.info ? kHotCtas : 0), kUpdThreads, 0, L.stream>>>(P)));
     HM_CUDA(cudaGetLastError());
     return HM_OK;
 }

@@ -17,10 +17,10 @@
 // CSR feature/value arrays directly and looks the row ids up in the row pointer (20 B/elem),
 // so no copy of the input is made.  Integer counting only; atomics are integer (order-independent).
 //
-// Two kinds of element never enter the sort: those of the block's dense columns (DenseInfo:
-// their gradient is a column sum taken by the forward kernel, see hm_linear.cu) and those whose
-// feature index is out of range (they are flagged and ignored everywhere).  Both are dropped by
-// key in the first pass and its histogram, so the sorted arrays are shorter than the block's CSR:
+// Two kinds of element never enter the sort: those of the block's hot features (HotInfo: their
+// gradient sums are taken by the forward kernel, see hm_linear.cu) and those whose feature index
+// is out of range (they are flagged and ignored everywhere).  Both are dropped by key in the
+// first pass and its histogram, so the sorted arrays are shorter than the block's CSR:
 // in_off / in_tile_off describe the CSR, seg_off / seg_tile_off the sorted arrays, and the latter
 // are written on the device from the first histogram (scan_rows_kernel).
 #include "hm_internal.h"
@@ -43,7 +43,7 @@ int num_sms()
 
 const char *const kKernelNames[K_NUM_KERNELS] = {
     "hash", "seg_prep", "sort_hist", "sort_scan", "sort_scatter", "linear_forward",
-    "linear_update", "fm_forward", "fm_update", "predict", "export", "misc", "dense_check"};
+    "linear_update", "fm_forward", "fm_update", "predict", "export", "misc", "hot_select"};
 
 namespace {
 
@@ -56,10 +56,7 @@ constexpr int kMaxRadix = 1 << kMaxRadixBits;
 constexpr int kScatThreads = 512;
 constexpr int kScatWarps = kScatThreads / 32;
 constexpr int kScatItems = kSortTile / kScatThreads;  // 8
-#ifndef HM_SCAT_CTAS
-#define HM_SCAT_CTAS 2
-#endif
-constexpr int kScatCtasPerSm = HM_SCAT_CTAS;
+constexpr int kScatCtasPerSm = 2;
 
 // Offsets of the block's mini-batches in its CSR (the first pass's coordinates).
 __global__ void seg_prep_kernel(const int64_t *__restrict__ rowptr, int64_t row0, int64_t n_rows,
@@ -97,151 +94,101 @@ __device__ __forceinline__ int find_seg(const uint32_t *tile_off, int n_segs, ui
     return lo;
 }
 
-// ---- dense columns --------------------------------------------------------------------
-constexpr uint32_t kDenseEmpty = 0xffffffffu;
-constexpr int kDenseSlots = 128;       // open-addressing table of at most 32 keys
+// ---- hot features -----------------------------------------------------------------------
+__device__ __forceinline__ bool hot_hit(const uint32_t *tab, uint32_t key) { return tab[hot_index(key)] == key; }
 
-__device__ __forceinline__ uint32_t dense_hash(uint32_t key) { return (key * 0x9E3779B1u) >> 25; }
-
-// Index (0..31) of `key` among the table's keys, or -1.
-__device__ __forceinline__ int dense_find(const uint32_t *tab, const uint32_t *tab_idx, uint32_t key)
+// Called by every thread of the CTA (two barriers): the block's hot keys into the direct-mapped table.
+__device__ __forceinline__ uint32_t hot_tab_build(uint32_t *tab, const HotInfo *hot, int nthreads)
 {
-    uint32_t h = dense_hash(key);
-    while (true) {
-        const uint32_t v = tab[h];
-        if (v == key) return (int)tab_idx[h];
-        if (v == kDenseEmpty) return -1;
-        h = (h + 1) & (kDenseSlots - 1);
-    }
-}
-__device__ __forceinline__ bool dense_hit(const uint32_t *tab, uint32_t key)
-{
-    uint32_t h = dense_hash(key);
-    while (true) {
-        const uint32_t v = tab[h];
-        if (v == key) return true;
-        if (v == kDenseEmpty) return false;
-        h = (h + 1) & (kDenseSlots - 1);
-    }
-}
-// Called by every thread of the CTA (two barriers).  Lane i of warp 0 inserts key i.
-__device__ __forceinline__ void dense_tab_build(uint32_t *tab, uint32_t *tab_idx, uint32_t mask, uint32_t my_key, int nthreads)
-{
-    for (int q = threadIdx.x; q < kDenseSlots; q += nthreads) tab[q] = kDenseEmpty;
+    const uint32_t n = hot->count;
+    for (int q = threadIdx.x; q < kHotSlots; q += nthreads) tab[q] = kHotEmpty;
     __syncthreads();
-    if (threadIdx.x < 32 && ((mask >> threadIdx.x) & 1u)) {
-        uint32_t h = dense_hash(my_key);
-        while (atomicCAS(&tab[h], kDenseEmpty, my_key) != kDenseEmpty) h = (h + 1) & (kDenseSlots - 1);
-        if (tab_idx) tab_idx[h] = threadIdx.x;
-    }
+    if (threadIdx.x < n) { const uint32_t key = hot->key[threadIdx.x]; tab[hot_index(key)] = key; }
     __syncthreads();
+    return n;
 }
 
-constexpr int kChkThreads = 256;
+// Pick the block's hot features: count the features of a sample of its rows (kSelRows rows spread
+// evenly over the block, the first kSelPerRow elements of each) in a shared-memory hash table
+// (integer atomics: the counts do not depend on the order), keep those seen in at least 1/32 of the
+// sampled rows, order them by (count descending, feature ascending), drop those whose table index
+// (hot_index) is taken by a better-placed one, and keep the first kMaxHot.
+// One CTA; a few microseconds on the sort stream.
+constexpr int kSelThreads = 1024;
+constexpr int kSelRows = 256, kSelPerRow = 32;
+constexpr int kSelSlots = 16384;                       // >= 2 x the sample
+constexpr int kSelCand = 1024;
+constexpr size_t kSelSmem = (size_t)kSelSlots * 8 + (size_t)kSelCand * 12;
 
-// Which of the first 32 positions of the block's rows are dense columns (see DenseInfo)?  A warp
-// per row reads the whole row once (4 B per element): position i stays a candidate while every
-// row holds the first row's feature there, and loses the bit as soon as that feature turns up
-// anywhere else.  The last CTA to finish publishes the result.
-__global__ void __launch_bounds__(kChkThreads)
-dense_check_kernel(const int64_t *__restrict__ rowptr, int64_t row0, int64_t n_rows,
-                   const uint32_t *__restrict__ feature, const float *__restrict__ value, uint32_t dims,
-                   DenseInfo *__restrict__ out)
+__global__ void __launch_bounds__(kSelThreads)
+hot_select_kernel(const int64_t *__restrict__ rowptr, int64_t row0, int64_t n_rows,
+                  const uint32_t *__restrict__ feature, uint32_t dims, HotInfo *__restrict__ out)
 {
-    __shared__ uint32_t s_ref[32], s_tab[kDenseSlots], s_tab_idx[kDenseSlots];
-    __shared__ uint32_t s_init, s_noteq, s_collide, s_nupos, s_nuother;
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    if (warp == 0) {
-        const int64_t p0 = rowptr[row0], p1 = rowptr[row0 + 1];
-        const bool have = p0 + lane < p1;
-        const uint32_t f = have ? __ldg(feature + p0 + lane) : kDenseEmpty;
-        const uint32_t peers = __match_any_sync(0xffffffffu, f);
-        const bool ok = have && f < dims && __popc(peers) == 1;     // in range, and once in the row
-        const uint32_t init = __ballot_sync(0xffffffffu, ok);
-        s_ref[lane] = f;
-        if (lane == 0) { s_init = init; s_noteq = 0; s_collide = 0; s_nupos = 0; s_nuother = 0; }
-    }
+    extern __shared__ __align__(16) unsigned char sel_smem[];
+    uint32_t *t_key = reinterpret_cast<uint32_t *>(sel_smem);
+    uint32_t *t_cnt = t_key + kSelSlots;
+    uint32_t *c_key = t_cnt + kSelSlots;
+    uint32_t *c_cnt = c_key + kSelCand;
+    uint32_t *c_rank = c_cnt + kSelCand;     // rank by (count descending, feature ascending); 0xffffffff: dropped
+    __shared__ int s_ncand, s_nhot;
+    const int tid = threadIdx.x;
+    for (int q = tid; q < kSelSlots; q += kSelThreads) { t_key[q] = kHotEmpty; t_cnt[q] = 0; }
+    if (tid == 0) { s_ncand = 0; s_nhot = 0; }
     __syncthreads();
-    const uint32_t init = s_init;
-    dense_tab_build(s_tab, s_tab_idx, init, s_ref[lane], kChkThreads);
-    // (a block without a candidate column still learns whether its values are all 1.0)
-    {
-        const uint32_t ref = s_ref[lane];
-        const bool cand = (init >> lane) & 1u;
-        uint32_t noteq = 0, coll = 0;
-        bool nu_pos = false, nu_other = false;     // a value != 1.0 at my candidate position / anywhere else
-        // Four consecutive rows per warp at a time: their loads are all issued before any is used (the
-        // kernel is bound by the latency of the rowptr -> feature chain, not by bytes).
-        constexpr int RW = 4;
-        const int64_t stride = (int64_t)gridDim.x * (kChkThreads / 32) * RW;
-        for (int64_t r = ((int64_t)blockIdx.x * (kChkThreads / 32) + warp) * RW; r < n_rows; r += stride) {
-            const int64_t rp = (lane <= RW && r + lane <= n_rows) ? rowptr[row0 + r + lane] : 0;
-            int64_t p0[RW], p1[RW];
-            bool in[RW], in2[RW];
-            uint32_t f[RW], g[RW];
-            float xv[RW], xg[RW];
-#pragma unroll
-            for (int u = 0; u < RW; u++) {
-                p0[u] = __shfl_sync(0xffffffffu, rp, u);
-                p1[u] = __shfl_sync(0xffffffffu, rp, u + 1);
-                const bool row = r + u < n_rows;
-                in[u] = row && p0[u] + lane < p1[u];
-                in2[u] = row && p0[u] + 32 + lane < p1[u];
-            }
-#pragma unroll
-            for (int u = 0; u < RW; u++) {
-                f[u] = in[u] ? __ldg(feature + p0[u] + lane) : kDenseEmpty;
-                xv[u] = in[u] ? __ldg(value + p0[u] + lane) : 1.0f;
-            }
-#pragma unroll
-            for (int u = 0; u < RW; u++) {
-                g[u] = in2[u] ? __ldg(feature + p0[u] + 32 + lane) : kDenseEmpty;
-                xg[u] = in2[u] ? __ldg(value + p0[u] + 32 + lane) : 1.0f;
-            }
-#pragma unroll
-            for (int u = 0; u < RW; u++) {
-                if (r + u < n_rows) {      // (uniform over the warp)
-                    const bool eq = in[u] && f[u] == ref;
-                    noteq |= init & ~__ballot_sync(0xffffffffu, eq);
-                    if (xv[u] != 1.0f) { if (eq && cand) nu_pos = true; else nu_other = true; }
-                    if (xg[u] != 1.0f) nu_other = true;
-                    if (init != 0) {
-                        if (in[u] && !eq) { const int j = dense_find(s_tab, s_tab_idx, f[u]); if (j >= 0) coll |= 1u << j; }
-                        if (in2[u]) { const int j = dense_find(s_tab, s_tab_idx, g[u]); if (j >= 0) coll |= 1u << j; }
-                    }
-                    for (int64_t p = p0[u] + 64 + lane; p < p1[u]; p += 32) {
-                        if (init != 0) { const int j = dense_find(s_tab, s_tab_idx, __ldg(feature + p)); if (j >= 0) coll |= 1u << j; }
-                        if (__ldg(value + p) != 1.0f) nu_other = true;
-                    }
+    const int rows = (int)min((int64_t)kSelRows, n_rows);
+    for (int q = tid; q < rows * kSelPerRow; q += kSelThreads) {
+        const int i = q / kSelPerRow, e = q % kSelPerRow;
+        const int64_t r = row0 + (n_rows * i) / rows;            // evenly spaced rows of the block
+        const int64_t p = rowptr[r] + e;
+        if (p < rowptr[r + 1]) {
+            const uint32_t key = __ldg(feature + p);
+            if (key < dims) {
+                uint32_t h = (key * 0x9E3779B1u) >> 18;          // kSelSlots = 2^14
+                while (true) {
+                    const uint32_t prev = atomicCAS(&t_key[h], kHotEmpty, key);
+                    if (prev == kHotEmpty || prev == key) { atomicAdd(&t_cnt[h], 1u); break; }
+                    h = (h + 1) & (kSelSlots - 1);
                 }
             }
         }
-        const uint32_t nupos = __ballot_sync(0xffffffffu, nu_pos);
-        const bool nuother = __any_sync(0xffffffffu, nu_other);
-        if (lane == 0) { if (nupos) atomicOr(&s_nupos, nupos); if (nuother) atomicOr(&s_nuother, 1u); }
-        coll = __reduce_or_sync(0xffffffffu, coll);
-        if (lane == 0) { if (noteq) atomicOr(&s_noteq, noteq); if (coll) atomicOr(&s_collide, coll); }
     }
     __syncthreads();
-    if (threadIdx.x == 0) {
-        if (s_noteq) atomicOr(&out->noteq, s_noteq);
-        if (s_collide) atomicOr(&out->collide, s_collide);
-        if (s_nupos) atomicOr(&out->nonunit_pos, s_nupos);
-        if (s_nuother) atomicOr(&out->nonunit_other, 1u);
-        __threadfence();
-        if (atomicAdd(&out->ticket, 1u) == gridDim.x - 1) {
-            __threadfence();
-            const uint32_t mask = init & ~atomicOr(&out->noteq, 0u) & ~atomicOr(&out->collide, 0u);
-            for (int i = 0; i < 32; i++) out->key[i] = s_ref[i];
-            out->mask = mask;
-            out->count = (uint32_t)__popc(mask);
-            // all ones among what is sorted: nothing != 1.0 outside the candidate columns, and none in a
-            // candidate column that did not become a dense column after all
-            out->unit = (atomicOr(&out->nonunit_other, 0u) == 0u &&
-                         ((init & ~mask) & atomicOr(&out->nonunit_pos, 0u)) == 0u) ? 1u : 0u;
-            out->noteq = 0; out->collide = 0; out->ticket = 0; out->nonunit_pos = 0; out->nonunit_other = 0;   // ready for the next block
+    const uint32_t threshold = (uint32_t)max(2, rows / 32);
+    for (int q = tid; q < kSelSlots; q += kSelThreads) {
+        if (t_key[q] != kHotEmpty && t_cnt[q] >= threshold) {
+            const int c = atomicAdd(&s_ncand, 1);
+            if (c < kSelCand) { c_key[c] = t_key[q]; c_cnt[c] = t_cnt[q]; }
         }
     }
+    __syncthreads();
+    const int nc = min(s_ncand, kSelCand);      // (more than kSelCand candidates cannot happen: 8192 / 8)
+    for (int c = tid; c < nc; c += kSelThreads) {
+        const uint32_t k = c_key[c], n = c_cnt[c];
+        uint32_t rank = 0;
+        for (int o = 0; o < nc; o++) rank += (c_cnt[o] > n || (c_cnt[o] == n && c_key[o] < k)) ? 1u : 0u;
+        c_rank[c] = rank;
+    }
+    __syncthreads();
+    // a candidate whose table index belongs to a better-ranked candidate is dropped (the hot test is a
+    // single probe); decided against ALL better-ranked candidates, so the outcome needs no ordering
+    bool keep = false;
+    uint32_t my_rank = 0;
+    if (tid < nc) {
+        my_rank = c_rank[tid];
+        const uint32_t idx = hot_index(c_key[tid]);
+        keep = true;
+        for (int o = 0; o < nc; o++) if (c_rank[o] < my_rank && hot_index(c_key[o]) == idx) keep = false;
+    }
+    __syncthreads();
+    if (tid < nc && !keep) c_rank[tid] = 0xffffffffu;
+    __syncthreads();
+    if (tid < nc && keep) {
+        int pos = 0;
+        for (int o = 0; o < nc; o++) pos += (c_rank[o] < my_rank) ? 1 : 0;      // kept candidates ahead of me
+        if (pos < kMaxHot) { out->key[pos] = c_key[tid]; atomicAdd(&s_nhot, 1); }
+    }
+    __syncthreads();
+    if (tid == 0) out->count = (uint32_t)s_nhot;
 }
 
 // One thread per sort tile: the row of the mini-batch that holds the tile's first element.
@@ -264,26 +211,20 @@ __global__ void tile_row0_kernel(const int64_t *__restrict__ rowptr, int64_t blo
     }
 }
 
-// FIRST: the keys are the block's CSR features; dense-column and out-of-range elements are not counted.
+// FIRST: the keys are the block's CSR features; hot-feature and out-of-range elements are not counted.
 template <int RB, bool FIRST>
 __global__ void __launch_bounds__(kSortThreads)
-sort_hist_kernel(const uint32_t *__restrict__ keys, const uint2 *__restrict__ recs,
-                 const uint32_t *__restrict__ seg_off,
+sort_hist_kernel(const uint32_t *__restrict__ keys, const uint32_t *__restrict__ seg_off,
                  const uint32_t *__restrict__ seg_tile_off, int n_segs, int shift,
                  uint32_t *__restrict__ tile_hist, uint32_t *__restrict__ row_sum,
-                 uint32_t dims, const DenseInfo *__restrict__ dense)
+                 uint32_t dims, const HotInfo *__restrict__ hot)
 {
-    // later passes of a block whose sorted values are all 1.0: the keys sit in packed (feature, row) records
-    const bool unit = !FIRST && dense->unit != 0u;
     constexpr int R = 1 << RB;
     __shared__ uint32_t s_off[kMaxSegs + 1], s_toff[kMaxSegs + 1];
     __shared__ uint32_t hist[kSortWarps][R];
-    __shared__ uint32_t s_dtab[FIRST ? kDenseSlots : 1];
-    uint32_t dmask = 0;
-    if (FIRST) {
-        dmask = dense->mask;
-        dense_tab_build(s_dtab, nullptr, dmask, dense->key[threadIdx.x & 31], kSortThreads);
-    }
+    __shared__ uint32_t s_htab[FIRST ? kHotSlots : 1];
+    uint32_t n_hot = 0;
+    if (FIRST) n_hot = hot_tab_build(s_htab, hot, kSortThreads);
     for (int s = threadIdx.x; s <= n_segs; s += kSortThreads) { s_off[s] = seg_off[s]; s_toff[s] = seg_tile_off[s]; }
     __syncthreads();
     const uint32_t total = s_toff[n_segs];
@@ -299,13 +240,13 @@ sort_hist_kernel(const uint32_t *__restrict__ keys, const uint2 *__restrict__ re
 #pragma unroll
         for (int i = 0; i < kSortItems; i++) {
             const uint32_t e = e0 + i * kSortThreads + threadIdx.x;
-            k[i] = e < e1 ? (unit ? __ldg(&recs[e].x) : __ldg(keys + e)) : 0u;
+            k[i] = e < e1 ? __ldg(keys + e) : 0u;
         }
 #pragma unroll
         for (int i = 0; i < kSortItems; i++) {
             const uint32_t e = e0 + i * kSortThreads + threadIdx.x;
             bool count = e < e1;
-            if (FIRST) count = count && k[i] < dims && !(dmask && dense_hit(s_dtab, k[i]));
+            if (FIRST) count = count && k[i] < dims && !(n_hot && hot_hit(s_htab, k[i]));
             if (count) atomicAdd(&hist[warp][(k[i] >> shift) & (R - 1)], 1u);
         }
         __syncthreads();
@@ -405,44 +346,43 @@ constexpr int kRowSlice = 1024;   // staged row-pointer entries; tiles that need
 
 constexpr size_t kScatterSmem = (size_t)kSortTile * 4 + (size_t)kSortTile * 8;   // keys + payloads
 
-// Shared memory of one scatter CTA (declared once in the kernel; the two bodies below share it).
 template <bool FIRST, int RB>
-struct ScatSmem {
-    static constexpr int R = 1 << RB;
-    uint32_t off[kMaxSegs + 1], toff[kMaxSegs + 1];
-    uint32_t wcnt[kScatWarps][R];
-    uint32_t dig_base[R], gofs[R], warp_tot[R / 32];
-    uint32_t rows[FIRST ? kRowSlice + 1 : 1];
-    uint32_t mark[FIRST ? kSortTile / 32 : 1];   // bit p: a row starts at tile position p
-    uint32_t dup;                                // two rows start at one position (an empty row)
-    int nr;
-    uint32_t ntile;                              // elements of the tile that are sorted
-    uint32_t dtab[FIRST ? kDenseSlots : 1];
-};
-
-// One digit pass over the tiles of a block.
-//   FIRST: the input is the block's CSR (features in keys_in, values in val_in, rows looked up in the row
-//          pointer); seg_off / seg_tile_off are the CSR's (in_off / in_tile_off); elements of dense columns and
-//          out-of-range features take no part (the histogram did not count them either).
-//   UNIT : every sorted element has value 1.0 (DenseInfo::unit): input and output of the later passes are packed
-//          (feature, row) records of 8 bytes in the payload arrays; the key arrays and the values are not touched.
-template <bool FIRST, int RB, bool UNIT>
-__device__ __forceinline__ void
-scatter_body(ScatSmem<FIRST, RB> &sm, unsigned char *dyn_smem, const uint32_t *__restrict__ keys_in,
-             const uint2 *__restrict__ pay_in, const RowLookup &rl, const float *__restrict__ val_in,
-             uint32_t *__restrict__ keys_out, uint2 *__restrict__ pay_out, int n_segs, int shift,
-             const uint32_t *__restrict__ tile_hist, uint32_t dims, uint32_t dmask, uint32_t *__restrict__ bad)
+__global__ void __launch_bounds__(kScatThreads, kScatCtasPerSm)
+sort_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint2 *__restrict__ pay_in,
+                    RowLookup rl, const float *__restrict__ val_in,
+                    uint32_t *__restrict__ keys_out, uint2 *__restrict__ pay_out,
+                    const uint32_t *__restrict__ seg_off, const uint32_t *__restrict__ seg_tile_off,
+                    int n_segs, int shift, const uint32_t *__restrict__ tile_hist,
+                    uint32_t dims, const HotInfo *__restrict__ hot, uint32_t *__restrict__ bad)
 {
+    // FIRST: seg_off / seg_tile_off are the CSR's (in_off / in_tile_off); elements of hot features and
+    // out-of-range features take no part (the histogram did not count them either).
     constexpr int R = 1 << RB;
-    // staging of the tile in sorted order: keys + payloads, or packed records
+    extern __shared__ __align__(16) unsigned char dyn_smem[];
     uint32_t *s_key = reinterpret_cast<uint32_t *>(dyn_smem);
-    uint2 *s_pay = reinterpret_cast<uint2 *>(dyn_smem + (UNIT ? 0 : (size_t)kSortTile * 4));
-    const uint32_t total = sm.toff[n_segs];
+    uint2 *s_pay = reinterpret_cast<uint2 *>(dyn_smem + (size_t)kSortTile * 4);
+    __shared__ uint32_t s_off[kMaxSegs + 1], s_toff[kMaxSegs + 1];
+    __shared__ uint32_t wcnt[kScatWarps][R];
+    __shared__ uint32_t dig_base[R], gofs[R], warp_tot[R / 32];
+    __shared__ uint32_t s_rows[FIRST ? kRowSlice + 1 : 1];
+    __shared__ uint32_t s_mark[FIRST ? kSortTile / 32 : 1];   // bit p: a row starts at tile position p
+    __shared__ uint32_t s_dup;                                // two rows start at one position (an empty row)
+    __shared__ int s_nr;
+    __shared__ uint32_t s_ntile;                              // elements of the tile that are sorted
+    uint32_t *s_htab = reinterpret_cast<uint32_t *>(dyn_smem + kScatterSmem);     // (first pass only: kHotSlots entries)
+    uint32_t n_hot = 0;
+    if (FIRST) {
+        n_hot = hot_tab_build(s_htab, hot, kScatThreads);
+        for (int q = threadIdx.x; q < kSortTile / 32; q += kScatThreads) s_mark[q] = 0;
+        if (threadIdx.x == 0) s_dup = 0;
+    }
+    for (int s = threadIdx.x; s <= n_segs; s += kScatThreads) { s_off[s] = seg_off[s]; s_toff[s] = seg_tile_off[s]; }
+    __syncthreads();
+    const uint32_t total = s_toff[n_segs];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint32_t lt_mask = (1u << lane) - 1u;
     // keys of the first tile; later tiles are prefetched while the previous one is written out
     uint32_t key[kScatItems], rank[kScatItems];
-    uint2 pay[kScatItems];      // (row, value bits); UNIT: .x = row only
     uint32_t tile = blockIdx.x;
     int seg = 0; uint32_t tis = 0, nt = 0, e0 = 0, e1 = 0;
     int cur_ra = 0; uint32_t slice_v = 0;   // first pass: the tile's first row and one row-pointer entry per thread
@@ -455,54 +395,45 @@ scatter_body(ScatSmem<FIRST, RB> &sm, unsigned char *dyn_smem, const uint32_t *_
         if (r > mb_rows) return 0xffffffffu;
         return (uint32_t)(rl.rowptr[rl.block_row0 + (int64_t)sg * rl.mini_batch + r] - rl.rowptr[rl.block_row0]);
     };
-    // keys of a tile (UNIT, later passes: the whole record -- its row comes along)
-    auto load_keys = [&](uint32_t a0, uint32_t a1) {
+    if (tile < total) {
+        seg = find_seg(s_toff, n_segs, tile);
+        tis = tile - s_toff[seg]; nt = s_toff[seg + 1] - s_toff[seg];
+        e0 = s_off[seg] + tis * kSortTile;
+        e1 = min(e0 + (uint32_t)kSortTile, s_off[seg + 1]);
+        if (FIRST) slice_v = load_slice(seg, tile, &cur_ra);
 #pragma unroll
         for (int i = 0; i < kScatItems; i++) {
-            const uint32_t e = a0 + warp * (32 * kScatItems) + lane + i * 32;
-            if (UNIT && !FIRST) {
-                const uint2 r = e < a1 ? __ldcs(pay_in + e) : make_uint2(0xffffffffu, 0u);
-                key[i] = r.x; pay[i].x = r.y;
-            } else {
-                key[i] = e < a1 ? __ldcs(keys_in + e) : 0xffffffffu;
-            }
+            const uint32_t e = e0 + warp * (32 * kScatItems) + lane + i * 32;
+            key[i] = e < e1 ? __ldcs(keys_in + e) : 0xffffffffu;
         }
-    };
-    if (tile < total) {
-        seg = find_seg(sm.toff, n_segs, tile);
-        tis = tile - sm.toff[seg]; nt = sm.toff[seg + 1] - sm.toff[seg];
-        e0 = sm.off[seg] + tis * kSortTile;
-        e1 = min(e0 + (uint32_t)kSortTile, sm.off[seg + 1]);
-        if (FIRST) slice_v = load_slice(seg, tile, &cur_ra);
-        load_keys(e0, e1);
     }
     for (; tile < total; tile += gridDim.x) {
         // warp-striped: warp w owns tile positions [w*256, (w+1)*256), round i, lane
         const uint32_t ew = e0 + warp * (32 * kScatItems) + lane;
+        // payloads are requested now and consumed after the ranking
+        uint2 pay[kScatItems];
         int nr = 0; bool covered = false;
         if (FIRST) {
             // the values are requested before the row search, so that their latency hides behind it
-            if (!UNIT) {
 #pragma unroll
-                for (int i = 0; i < kScatItems; i++) {
-                    const uint32_t e = ew + i * 32;
-                    if (e < e1) pay[i].y = __float_as_uint(__ldcs(val_in + e));
-                }
+            for (int i = 0; i < kScatItems; i++) {
+                const uint32_t e = ew + i * 32;
+                if (e < e1) pay[i].y = __float_as_uint(__ldcs(val_in + e));
             }
             const int mb_rows = (int)min((int64_t)rl.mini_batch, rl.block_rows - (int64_t)seg * rl.mini_batch);
             // stage rp[ra ..] - base.  The first kScatThreads entries were prefetched into `slice_v`
             // with the keys and almost always cover the tile (one barrier); otherwise keep loading.
             nr = min(kScatThreads - 1, mb_rows - cur_ra);
-            if ((int)threadIdx.x <= nr) sm.rows[threadIdx.x] = slice_v;
+            if ((int)threadIdx.x <= nr) s_rows[threadIdx.x] = slice_v;
             __syncthreads();
-            covered = sm.rows[nr] >= e1;       // uniform
+            covered = s_rows[nr] >= e1;       // uniform
             if (covered) {
                 // Fast path: every row that starts inside the tile sets the bit of its start position; the row
                 // of an element is then (tile's first row) + (bits at or below its position).  Two rows on one
                 // position -- an empty row -- cannot be told apart that way: the tile takes the search path.
                 if (threadIdx.x >= 1 && (int)threadIdx.x <= nr && slice_v > e0 && slice_v < e1) {
                     const uint32_t p = slice_v - e0, bit = 1u << (p & 31);
-                    if (atomicOr(&sm.mark[p >> 5], bit) & bit) sm.dup = 1;
+                    if (atomicOr(&s_mark[p >> 5], bit) & bit) s_dup = 1;
                 }
             } else {
                 const int64_t base = rl.rowptr[rl.block_row0];
@@ -510,48 +441,47 @@ scatter_body(ScatSmem<FIRST, RB> &sm, unsigned char *dyn_smem, const uint32_t *_
                 const int ra = cur_ra;
                 nr = -1;
                 for (int i0 = kScatThreads; i0 <= kRowSlice; i0 += kScatThreads) {
-                    if (threadIdx.x == 0) sm.nr = 0x7fffffff;
+                    if (threadIdx.x == 0) s_nr = 0x7fffffff;
                     __syncthreads();
                     const int i = i0 + threadIdx.x;
                     int hit = 0x7fffffff;
                     if (i <= kRowSlice && ra + i <= mb_rows) {
                         const uint32_t v = (uint32_t)(rp[ra + i] - base);
-                        sm.rows[i] = v;
+                        s_rows[i] = v;
                         if (v >= e1) hit = i;
                     }
                     const int wmin = __reduce_min_sync(0xffffffffu, hit);
-                    if (lane == 0 && wmin != 0x7fffffff) atomicMin(&sm.nr, wmin);
+                    if (lane == 0 && wmin != 0x7fffffff) atomicMin(&s_nr, wmin);
                     __syncthreads();
-                    const int got = sm.nr;
+                    const int got = s_nr;
                     __syncthreads();
                     if (got != 0x7fffffff) { nr = got; break; }
                 }
             }
-        } else if (!UNIT) {
-            // payloads are requested now and consumed after the ranking
+        } else {
 #pragma unroll
             for (int i = 0; i < kScatItems; i++) {
                 const uint32_t e = ew + i * 32;
                 if (e < e1) pay[i] = __ldcs(pay_in + e);
             }
         }
-        for (int q = threadIdx.x; q < kScatWarps * R; q += kScatThreads) (&sm.wcnt[0][0])[q] = 0;
+        for (int q = threadIdx.x; q < kScatWarps * R; q += kScatThreads) (&wcnt[0][0])[q] = 0;
         __syncthreads();
         if (FIRST) {
             const int ra = cur_ra;
-            if (covered && !sm.dup) {
+            if (covered && !s_dup) {
                 // rows that start before this warp's 256 positions, then one word of marks per round
                 uint32_t before = 0;
 #pragma unroll
                 for (int j = 0; j < kSortTile / 32 / 32; j++) {
                     const int wd = lane + 32 * j;
-                    if (wd < warp * kScatItems) before += __popc(sm.mark[wd]);
+                    if (wd < warp * kScatItems) before += __popc(s_mark[wd]);
                 }
                 before = __reduce_add_sync(0xffffffffu, before);
                 const uint32_t le_mask = 0xffffffffu >> (31 - lane);
 #pragma unroll
                 for (int i = 0; i < kScatItems; i++) {
-                    const uint32_t m = sm.mark[warp * kScatItems + i];
+                    const uint32_t m = s_mark[warp * kScatItems + i];
                     pay[i].x = (uint32_t)ra + before + __popc(m & le_mask);
                     before += __popc(m);
                 }
@@ -569,11 +499,11 @@ scatter_body(ScatSmem<FIRST, RB> &sm, unsigned char *dyn_smem, const uint32_t *_
                         int row;
                         if (nr >= 0) {
                             if (!searched) {
-                                int lo = 0, hi = nr;        // rows[lo] <= e < rows[hi]
-                                while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (sm.rows[mid] <= e) lo = mid; else hi = mid; }
+                                int lo = 0, hi = nr;        // s_rows[lo] <= e < s_rows[hi]
+                                while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (s_rows[mid] <= e) lo = mid; else hi = mid; }
                                 idx = lo; searched = true;
                             } else {
-                                while (sm.rows[idx + 1] <= e) idx++;     // rows[nr] >= e1 > e bounds the walk
+                                while (s_rows[idx + 1] <= e) idx++;     // s_rows[nr] >= e1 > e bounds the walk
                             }
                             row = ra + idx;
                         } else {
@@ -593,7 +523,7 @@ scatter_body(ScatSmem<FIRST, RB> &sm, unsigned char *dyn_smem, const uint32_t *_
             bool valid = ew + i * 32 < e1;
             if (FIRST && valid) {
                 if (key[i] >= dims) { valid = false; atomicOr(bad, 1u); }
-                else if (dmask && dense_hit(sm.dtab, key[i])) valid = false;
+                else if (n_hot && hot_hit(s_htab, key[i])) valid = false;
             }
             if (valid) vbits |= 1u << i;
             const uint32_t d = (key[i] >> shift) & (R - 1);
@@ -610,13 +540,13 @@ scatter_body(ScatSmem<FIRST, RB> &sm, unsigned char *dyn_smem, const uint32_t *_
                     const uint32_t m = __ballot_sync(0xffffffffu, valid && ((d >> b) & 1u));
                     peers &= ((d >> b) & 1u) ? m : ~m;
                 }
-                if (valid) prev = sm.wcnt[warp][d];
+                if (valid) prev = wcnt[warp][d];
             } else
-            if (valid) { peers = __match_any_sync(active, d); prev = sm.wcnt[warp][d]; }
+            if (valid) { peers = __match_any_sync(active, d); prev = wcnt[warp][d]; }
             __syncwarp();
             if (valid) {
                 const uint32_t r = __popc(peers & lt_mask);
-                if (r == 0) sm.wcnt[warp][d] = prev + __popc(peers);
+                if (r == 0) wcnt[warp][d] = prev + __popc(peers);
                 rank[i] = prev + r;
             }
             __syncwarp();
@@ -630,92 +560,65 @@ scatter_body(ScatSmem<FIRST, RB> &sm, unsigned char *dyn_smem, const uint32_t *_
             uint32_t run = 0;
             if (owner) {
 #pragma unroll
-                for (int w = 0; w < kScatWarps; w++) { uint32_t c = sm.wcnt[w][d]; sm.wcnt[w][d] = run; run += c; }
+                for (int w = 0; w < kScatWarps; w++) { uint32_t c = wcnt[w][d]; wcnt[w][d] = run; run += c; }
             }
             uint32_t inc = run;
 #pragma unroll
             for (int o = 1; o < 32; o <<= 1) { uint32_t v = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += v; }
-            if (lane == 31 && owner) sm.warp_tot[warp] = inc;
+            if (lane == 31 && owner) warp_tot[warp] = inc;
             __syncthreads();
             if (owner) {
                 uint32_t wbase = 0;
 #pragma unroll
-                for (int w = 0; w < R / 32; w++) if (w < warp) wbase += sm.warp_tot[w];
+                for (int w = 0; w < R / 32; w++) if (w < warp) wbase += warp_tot[w];
                 const uint32_t ex = wbase + inc - run;
-                sm.dig_base[d] = ex;
-                sm.gofs[d] = tile_hist[(size_t)sm.toff[seg] * R + (size_t)d * nt + tis] - ex;
-                if (d == R - 1) sm.ntile = ex + run;
+                dig_base[d] = ex;
+                gofs[d] = tile_hist[(size_t)s_toff[seg] * R + (size_t)d * nt + tis] - ex;
+                if (d == R - 1) s_ntile = ex + run;
             }
         }
         __syncthreads();
-        // place keys and payloads (or packed records) at their tile-local sorted position
+        // place keys and payloads at their tile-local sorted position (payload loaded only now:
+        // sixteen independent loads in flight per thread, no registers held across the ranking)
 #pragma unroll
         for (int i = 0; i < kScatItems; i++) {
             if ((vbits >> i) & 1u) {
                 const uint32_t d = (key[i] >> shift) & (R - 1);
-                const uint32_t pos = sm.dig_base[d] + sm.wcnt[warp][d] + rank[i];
-                if (UNIT) s_pay[pos] = make_uint2(key[i], pay[i].x);
-                else { s_key[pos] = key[i]; s_pay[pos] = pay[i]; }
+                const uint32_t pos = dig_base[d] + wcnt[warp][d] + rank[i];
+                s_key[pos] = key[i];
+                s_pay[pos] = pay[i];
             }
         }
         __syncthreads();
         if (FIRST) {      // marks are consumed: clear them for the next tile (its marks come after its slice barrier)
-            for (int q = threadIdx.x; q < kSortTile / 32; q += kScatThreads) sm.mark[q] = 0;
-            if (threadIdx.x == 0) sm.dup = 0;
+            for (int q = threadIdx.x; q < kSortTile / 32; q += kScatThreads) s_mark[q] = 0;
+            if (threadIdx.x == 0) s_dup = 0;
         }
-        const uint32_t n_tile = sm.ntile;
+        const uint32_t n_tile = s_ntile;
         // next tile's coordinates and keys (the key registers are free from here on)
         const uint32_t next = tile + gridDim.x;
         int nseg = 0; uint32_t ntis = 0, nnt = 0, ne0 = 0, ne1 = 0;
         if (next < total) {
-            nseg = find_seg(sm.toff, n_segs, next);
-            ntis = next - sm.toff[nseg]; nnt = sm.toff[nseg + 1] - sm.toff[nseg];
-            ne0 = sm.off[nseg] + ntis * kSortTile;
-            ne1 = min(ne0 + (uint32_t)kSortTile, sm.off[nseg + 1]);
+            nseg = find_seg(s_toff, n_segs, next);
+            ntis = next - s_toff[nseg]; nnt = s_toff[nseg + 1] - s_toff[nseg];
+            ne0 = s_off[nseg] + ntis * kSortTile;
+            ne1 = min(ne0 + (uint32_t)kSortTile, s_off[nseg + 1]);
             if (FIRST) slice_v = load_slice(nseg, next, &cur_ra);
-            load_keys(ne0, ne1);
+#pragma unroll
+            for (int i = 0; i < kScatItems; i++) {
+                const uint32_t e = ne0 + warp * (32 * kScatItems) + lane + i * 32;
+                key[i] = e < ne1 ? __ldcs(keys_in + e) : 0xffffffffu;
+            }
         }
         for (uint32_t p = threadIdx.x; p < n_tile; p += kScatThreads) {
-            if (UNIT) {
-                const uint2 r = s_pay[p];
-                pay_out[sm.gofs[(r.x >> shift) & (R - 1)] + p] = r;
-            } else {
-                const uint32_t k = s_key[p];
-                const uint32_t g = sm.gofs[(k >> shift) & (R - 1)] + p;
-                keys_out[g] = k;
-                pay_out[g] = s_pay[p];
-            }
+            const uint32_t k = s_key[p];
+            const uint32_t g = gofs[(k >> shift) & (R - 1)] + p;
+            keys_out[g] = k;
+            pay_out[g] = s_pay[p];
         }
         __syncthreads();
         seg = nseg; tis = ntis; nt = nnt; e0 = ne0; e1 = ne1;
     }
-}
-
-template <bool FIRST, int RB>
-__global__ void __launch_bounds__(kScatThreads, kScatCtasPerSm)
-sort_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint2 *__restrict__ pay_in,
-                    RowLookup rl, const float *__restrict__ val_in,
-                    uint32_t *__restrict__ keys_out, uint2 *__restrict__ pay_out,
-                    const uint32_t *__restrict__ seg_off, const uint32_t *__restrict__ seg_tile_off,
-                    int n_segs, int shift, const uint32_t *__restrict__ tile_hist,
-                    uint32_t dims, const DenseInfo *__restrict__ dense, uint32_t *__restrict__ bad)
-{
-    extern __shared__ __align__(16) unsigned char dyn_smem[];
-    __shared__ ScatSmem<FIRST, RB> sm;
-    uint32_t dmask = 0;
-    if (FIRST) {
-        dmask = dense->mask;
-        dense_tab_build(sm.dtab, nullptr, dmask, dense->key[threadIdx.x & 31], kScatThreads);
-        for (int q = threadIdx.x; q < kSortTile / 32; q += kScatThreads) sm.mark[q] = 0;
-        if (threadIdx.x == 0) sm.dup = 0;
-    }
-    for (int s = threadIdx.x; s <= n_segs; s += kScatThreads) { sm.off[s] = seg_off[s]; sm.toff[s] = seg_tile_off[s]; }
-    const bool unit = dense->unit != 0u;     // uniform over the grid
-    __syncthreads();
-    if (unit) scatter_body<FIRST, RB, true>(sm, dyn_smem, keys_in, pay_in, rl, val_in, keys_out, pay_out, n_segs, shift,
-                                            tile_hist, dims, dmask, bad);
-    else scatter_body<FIRST, RB, false>(sm, dyn_smem, keys_in, pay_in, rl, val_in, keys_out, pay_out, n_segs, shift,
-                                        tile_hist, dims, dmask, bad);
 }
 
 int persistent_grid(int64_t work_items, int per_sm)
@@ -736,8 +639,8 @@ hm_status sort_scratch_reserve(SortScratch &s, int64_t elems)
         HM_CUDA(cudaMalloc(&s.seg_off, (kMaxSegs + 1) * sizeof(uint32_t)));
         HM_CUDA(cudaMalloc(&s.seg_tile_off, (kMaxSegs + 1) * sizeof(uint32_t)));
         HM_CUDA(cudaMalloc(&s.row_sum, (size_t)kMaxSegs * kMaxRadix * sizeof(uint32_t)));
-        HM_CUDA(cudaMalloc(&s.dense, sizeof(DenseInfo)));
-        HM_CUDA(cudaMemset(s.dense, 0, sizeof(DenseInfo)));
+        HM_CUDA(cudaMalloc(&s.hot, sizeof(HotInfo)));
+        HM_CUDA(cudaMemset(s.hot, 0, sizeof(HotInfo)));
     }
     if (elems > s.cap_elems) {
         for (int b = 0; b < 2; b++) {
@@ -766,9 +669,9 @@ void sort_scratch_free(SortScratch &s)
 {
     for (int b = 0; b < 2; b++) { cudaFree(s.key[b]); cudaFree(s.pay[b]); s.key[b] = nullptr; s.pay[b] = nullptr; }
     cudaFree(s.tile_hist); cudaFree(s.row_sum); cudaFree(s.seg_off); cudaFree(s.seg_tile_off); cudaFree(s.tile_row0);
-    cudaFree(s.in_off); cudaFree(s.in_tile_off); cudaFree(s.dense);
+    cudaFree(s.in_off); cudaFree(s.in_tile_off); cudaFree(s.hot);
     s.tile_hist = s.row_sum = s.seg_off = s.seg_tile_off = s.in_off = s.in_tile_off = nullptr; s.tile_row0 = nullptr;
-    s.dense = nullptr;
+    s.hot = nullptr;
     s.cap_elems = s.cap_tiles = 0;
 }
 
@@ -788,17 +691,23 @@ hm_status launch_seg_prep(Launcher &L, SortScratch &s, const int64_t *d_rowptr, 
     return HM_OK;
 }
 
-hm_status launch_dense_check(Launcher &L, SortScratch &s, const int64_t *d_rowptr, int64_t row0, int64_t n_rows,
-                             const uint32_t *d_feature, const float *d_value, int64_t n_elems, int64_t dims, bool enable)
+hm_status launch_hot_select(Launcher &L, SortScratch &s, const int64_t *d_rowptr, int64_t row0, int64_t n_rows,
+                            const uint32_t *d_feature, int64_t dims, bool enable)
 {
     if (!enable || n_rows < 1) {
-        HM_CUDA(cudaMemsetAsync(s.dense, 0, sizeof(DenseInfo), L.stream));
+        HM_CUDA(cudaMemsetAsync(s.hot, 0, sizeof(HotInfo), L.stream));
         return HM_OK;
     }
-    const int grid = persistent_grid((n_rows + kChkThreads / 8 - 1) / (kChkThreads / 8), 8);
-    HM_LAUNCH(L, K_DENSE_CHECK, 8.0 * (double)n_elems + 8.0 * (double)n_rows,
-              (dense_check_kernel<<<grid, kChkThreads, 0, L.stream>>>(d_rowptr, row0, n_rows, d_feature, d_value,
-                                                                     (uint32_t)std::min<int64_t>(dims, 0xffffffffLL), s.dense)));
+    static std::atomic<bool> attr_set[64];   // > 48 KB of dynamic shared memory needs opting in, once per device
+    int dev = 0;
+    HM_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64 || !attr_set[dev].load(std::memory_order_acquire)) {
+        HM_CUDA(cudaFuncSetAttribute(hot_select_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSelSmem));
+        if (dev >= 0 && dev < 64) attr_set[dev].store(true, std::memory_order_release);
+    }
+    HM_LAUNCH(L, K_HOT_SELECT, 0.0,
+              (hot_select_kernel<<<1, kSelThreads, kSelSmem, L.stream>>>(d_rowptr, row0, n_rows, d_feature,
+                                                                          (uint32_t)std::min<int64_t>(dims, 0xffffffffLL), s.hot)));
     HM_CUDA(cudaGetLastError());
     return HM_OK;
 }
@@ -823,9 +732,9 @@ hm_status launch_segmented_sort(Launcher &L, SortScratch &s, const uint32_t *d_f
     int dev = 0;
     HM_CUDA(cudaGetDevice(&dev));
     if (dev < 0 || dev >= 64 || !attr_set[dev].load(std::memory_order_acquire)) {
-        HM_TRY(opt_in_smem(sort_scatter_kernel<true, 8>, kScatterSmem));
+        HM_TRY(opt_in_smem(sort_scatter_kernel<true, 8>, kScatterSmem + kHotSlots * 4));
         HM_TRY(opt_in_smem(sort_scatter_kernel<false, 8>, kScatterSmem));
-        HM_TRY(opt_in_smem(sort_scatter_kernel<true, 9>, kScatterSmem));
+        HM_TRY(opt_in_smem(sort_scatter_kernel<true, 9>, kScatterSmem + kHotSlots * 4));
         HM_TRY(opt_in_smem(sort_scatter_kernel<false, 9>, kScatterSmem));
         if (dev >= 0 && dev < 64) attr_set[dev].store(true, std::memory_order_release);
     }
@@ -858,8 +767,8 @@ hm_status launch_segmented_sort(Launcher &L, SortScratch &s, const uint32_t *d_f
         HM_CUDA(cudaMemsetAsync(s.row_sum, 0, (size_t)rows * sizeof(uint32_t), L.stream));
 #define HM_HIST(RB_, FIRST_)                                                                                            \
     HM_LAUNCH(L, K_SORT_HIST, 4.0 * (double)n_elems,                                                                     \
-              (sort_hist_kernel<RB_, FIRST_><<<hist_grid, kSortThreads, 0, L.stream>>>(kin, pin, off, toff, n_segs, shift, \
-                                                                                       s.tile_hist, s.row_sum, dims32, s.dense)))
+              (sort_hist_kernel<RB_, FIRST_><<<hist_grid, kSortThreads, 0, L.stream>>>(kin, off, toff, n_segs, shift,  \
+                                                                                       s.tile_hist, s.row_sum, dims32, s.hot)))
         if (p == 0) { if (rb == 9) HM_HIST(9, true); else HM_HIST(8, true); }
         else { if (rb == 9) HM_HIST(9, false); else HM_HIST(8, false); }
 #undef HM_HIST
@@ -872,9 +781,9 @@ hm_status launch_segmented_sort(Launcher &L, SortScratch &s, const uint32_t *d_f
         const double bytes = p == 0 ? 20.0 * (double)n_elems + 8.0 * (double)block_rows : 24.0 * (double)n_elems;
 #define HM_SCATTER(FIRST_, RB_)                                                                                        \
     HM_LAUNCH(L, K_SORT_SCATTER, bytes,                                                                                 \
-              (sort_scatter_kernel<FIRST_, RB_><<<grid, kScatThreads, kScatterSmem, L.stream>>>(                        \
+              (sort_scatter_kernel<FIRST_, RB_><<<grid, kScatThreads, kScatterSmem + (FIRST_ ? kHotSlots * 4 : 0), L.stream>>>( \
                   kin, pin, rl, p == 0 ? d_value_block : nullptr, kout, pout, off, toff, n_segs, shift,                 \
-                  s.tile_hist, dims32, s.dense, d_bad)))
+                  s.tile_hist, dims32, s.hot, d_bad)))
         if (p == 0) { if (rb == 9) HM_SCATTER(true, 9); else HM_SCATTER(true, 8); }
         else { if (rb == 9) HM_SCATTER(false, 9); else HM_SCATTER(false, 8); }
 #undef HM_SCATTER

@@ -399,11 +399,11 @@ class UDTF:
         check(self._lib.hm_udtf_last_margins(self._h, _ptr(out), len(out), C.byref(n)))
         return out[: n.value]
 
-    def dense_columns(self) -> np.ndarray:
-        """Features of the dense columns found in the most recently sorted block (int32, at most 32)."""
-        out = np.empty(32, dtype=np.int32)
+    def hot_features(self) -> np.ndarray:
+        """Hot features picked for the most recently sorted block (int32, at most 64, most frequent first)."""
+        out = np.empty(64, dtype=np.int32)
         n = C.c_int32()
-        check(self._lib.hm_udtf_dense_columns(self._h, _ptr(out), 32, C.byref(n)))
+        check(self._lib.hm_udtf_hot_features(self._h, _ptr(out), 64, C.byref(n)))
         return out[: n.value]
 
     # ---- measurement ---------------------------------------------------------------

@@ -264,14 +264,15 @@ hm_status hm_udtf_load_model_table(hm_udtf *u, const char *path, int format, cha
 /* The learner's numeric configuration (what hm_parse_options made of its option string). */
 hm_status hm_udtf_config(const hm_udtf *u, hm_config *out);
 
-/* Dense columns of the most recently sorted ingest block (diagnostics, tests).  Rows usually
- * start with their quantitative features ("name:value" with a fixed name), so position i of every
- * row holds the same feature; the linear learners reduce such a column as a plain column sum
- * instead of sorting it (same arithmetic contract, other -- fixed -- summation order).  Writes up
- * to `cap` (at most 32) feature indices and sets *n to the number of dense columns; waits for the
- * GPU.  Setting HM_DENSE_COLUMNS=0 in the environment before hm_udtf_create turns the detection
- * off (every element is then sorted).  Stands in for nothing in the reference. */
-hm_status hm_udtf_dense_columns(hm_udtf *u, int32_t *feature, int32_t cap, int32_t *n);
+/* Hot features of the most recently sorted ingest block (diagnostics, tests).  A few features carry
+ * a large share of a mini-batch's elements: the quantitative features every row has, the head of
+ * each categorical field.  Per ingest block the linear learners pick up to 64 of them by their
+ * frequency in a sample of the block's rows and reduce them in the forward kernel instead of sorting
+ * them (same arithmetic contract, other -- fixed -- summation order).  The choice affects speed
+ * only.  Writes up to `cap` feature indices, most frequent first, sets *n; waits for the GPU.
+ * HM_HOT_FEATURES=0 in the environment before hm_udtf_create turns the mechanism off (every
+ * element is then sorted).  Stands in for nothing in the reference. */
+hm_status hm_udtf_hot_features(hm_udtf *u, int32_t *feature, int32_t cap, int32_t *n);
 
 /* ---- model table without device allocation ---------------------------------- */
 

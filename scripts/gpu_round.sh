@@ -12,12 +12,12 @@ for v in "$@"; do
   echo -n "$v: "; timeout 300 python bench.py $B 2>&1 | python scripts/benchline.py
 done
 cp /tmp/lib_base.so hivemall_b200/libhivemall_b200.so
-echo -n "dense off: "; HM_DENSE_COLUMNS=0 timeout 300 python bench.py $B 2>&1 | python scripts/benchline.py
+echo -n "hot off: "; HM_HOT_FEATURES=0 timeout 300 python bench.py $B 2>&1 | python scripts/benchline.py
 echo -n "base again: "; timeout 300 python bench.py $B 2>&1 | python scripts/benchline.py
-timeout 300 ncu --metrics gpu__time_duration.sum --clock-control none -c 260 --csv --log-file gpurun_out/launches.csv \
+timeout 300 ncu -k regex:"sort_|linear_|hot_|seg_|scan_|tile_" --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches.csv \
   python bench.py --steps 1 --warmup 1 --no-e2e --no-cpu --no-sweep > gpurun_out/ncu.log 2>&1; echo "ncu rc=$?"
 if [ -f variants/lib_stamp.so ]; then
   cp variants/lib_stamp.so hivemall_b200/libhivemall_b200.so
-  timeout 120 python scripts/upd_timeline.py ftrl 2>&1 | tee gpurun_out/timeline.txt
+  timeout 120 env PYTHONPATH=. python scripts/upd_timeline.py ftrl 2>&1 | tee gpurun_out/timeline.txt
   cp /tmp/lib_base.so hivemall_b200/libhivemall_b200.so
 fi

@@ -1,9 +1,10 @@
-"""Dense columns: features that sit at the same position of every row of an ingest block
-(quantitative features at the front of the row) are reduced as column sums by the forward
-kernel and never enter the sort (hm_sort.cu: dense_check_kernel, hm_linear.cu:
-forward_rows_dense / dense_columns_step).  The result must be what the oracle computes for the
-plain rows -- the oracle knows nothing about dense columns -- whatever the block looks like:
-clean prefix, the same feature again later in a row, a row that breaks the pattern, short rows.
+"""Hot features: the few features that carry a large share of a mini-batch's elements (the
+quantitative features every row has, the head of a categorical field) are picked per ingest block
+from a sample of its rows, reduced by the forward kernel and never enter the sort (hm_sort.cu:
+hot_select_kernel, hm_linear.cu: forward_rows_hot / hot_features_step).  The result must be what
+the oracle computes for the plain rows -- the oracle knows nothing about hot features -- whatever
+the rows look like: a clean prefix, the same feature again later in a row or twice in one row,
+rows without it, empty rows, long rows.
 
 PARITY UNPINNED w.r.t. Hivemall (no reference source is mounted); checked against oracle/.
 """
@@ -56,11 +57,11 @@ def to_csr(rows_f, rows_v, rng, regression=False):
                      torch.from_numpy(label))
 
 
-def check(fn, options, data, want_dense, pushes=None):
-    """want_dense: the dense columns of the LAST ingest block (that is what dense_columns() reports)."""
+def check(fn, options, data, want_hot, pushes=None):
+    """want_hot: the hot features of the LAST ingest block (that is what hot_features() reports)."""
     u, w, state = run_gpu_linear(fn, options, data, pushes=pushes)
-    got = sorted(int(x) for x in u.dense_columns())
-    assert got == sorted(want_dense), f"dense columns {got}, expected {sorted(want_dense)}"
+    got = sorted(int(x) for x in u.hot_features())
+    assert got == sorted(want_hot), f"hot features {got}, expected {sorted(want_hot)}"
     ref, ref_state = run_oracle_linear(fn, options, data)
     assert u.step == ref.t
     assert_weights_close(w, ref.w)
@@ -84,14 +85,13 @@ def test_gradient_normalisations(norm):
 
 
 def test_feature_again_later_in_a_row():
-    """Feature PREFIX[2] also turns up in the tail of one row: it is not a dense column (its
-    occurrences must meet in ONE optimizer step), the others still are."""
+    """Feature PREFIX[2] also turns up in the tail of one row: every occurrence of a hot feature, wherever
+    it sits, is reduced in the forward kernel, so that they all meet in ONE optimizer step."""
     rows_f, rows_v, rng = prefix_rows(4096, seed=7)      # two whole mini-batches: one ingest block
     rows_f[3321] = np.concatenate([rows_f[3321], [PREFIX[2]]])
     rows_v[3321] = np.concatenate([rows_v[3321], [0.75]])
     data = to_csr(rows_f, rows_v, rng)
-    check("train_classifier", f"-loss logloss -opt adagrad -mini_batch 2048 -dims {DIMS} -eta0 0.05", data,
-          [p for p in PREFIX if p != PREFIX[2]])
+    check("train_classifier", f"-loss logloss -opt adagrad -mini_batch 2048 -dims {DIMS} -eta0 0.05", data, PREFIX)
 
 
 def test_row_that_breaks_the_pattern_and_short_rows():
@@ -100,28 +100,35 @@ def test_row_that_breaks_the_pattern_and_short_rows():
     rows_f[2500] = rows_f[2500][:5]          # a row with only positions 0..4
     rows_v[2500] = rows_v[2500][:5]
     data = to_csr(rows_f, rows_v, rng)
-    # position 1 is out (and its feature 40000 is no dense column); positions 5, 6 are missing in one row
-    check("train_classifier", f"-loss logloss -opt ftrl -mini_batch 2048 -dims {DIMS} -alpha 0.05", data,
-          [PREFIX[0], PREFIX[2], PREFIX[3], PREFIX[4]])
+    # (a feature is hot by its frequency, not by sitting at the same place in every row)
+    check("train_classifier", f"-loss logloss -opt ftrl -mini_batch 2048 -dims {DIMS} -alpha 0.05", data, PREFIX)
 
 
-def test_same_feature_twice_in_the_prefix():
+def test_same_feature_twice_in_a_row():
+    """Two lanes of a warp hit the same accumulator: the adds are serialised in lane order."""
     prefix = [5, 9, 5, 11]
     rows_f, rows_v, rng = prefix_rows(4096, prefix=prefix, seed=11)
     data = to_csr(rows_f, rows_v, rng)
-    check("train_classifier", f"-loss logloss -opt adam -mini_batch 2048 -dims {DIMS} -eta0 0.01", data, [9, 11])
+    check("train_classifier", f"-loss logloss -opt adam -mini_batch 2048 -dims {DIMS} -eta0 0.01", data, [5, 9, 11])
 
 
-def test_empty_row_disables_all():
+def test_empty_rows_and_long_rows():
+    """Empty rows, and rows of more than 64 elements whose tail holds hot features again (the forward kernel
+    keeps a lane's first two elements in registers and re-reads longer tails)."""
     rows_f, rows_v, rng = prefix_rows(4096, seed=13)
     rows_f[100] = rows_f[100][:0]
     rows_v[100] = rows_v[100][:0]
+    for r in (7, 1000, 3000, 4095):
+        extra = rng.integers(0, DIMS, 90)
+        extra[[40, 70, 88]] = [PREFIX[0], PREFIX[3], PREFIX[0]]
+        rows_f[r] = np.concatenate([rows_f[r], extra])
+        rows_v[r] = np.concatenate([rows_v[r], rng.normal(0, 1, 90)])
     data = to_csr(rows_f, rows_v, rng)
-    check("train_classifier", f"-loss hinge -opt sgd -mini_batch 2048 -dims {DIMS} -eta0 0.05", data, [])
+    check("train_classifier", f"-loss hinge -opt sgd -mini_batch 2048 -dims {DIMS} -eta0 0.05", data, PREFIX)
 
 
 def test_blocks_with_different_columns():
-    """Two pushes whose rows start differently: the columns are found per ingest block."""
+    """Two pushes whose rows start differently: hot features are picked per ingest block."""
     a_f, a_v, rng = prefix_rows(4096, seed=15)
     b_f, b_v, _ = prefix_rows(4096, prefix=[3, 8], seed=16)
     data = to_csr(a_f + b_f, a_v + b_v, rng)
@@ -132,18 +139,20 @@ def test_blocks_with_different_columns():
 def test_switched_off_by_environment():
     rows_f, rows_v, rng = prefix_rows(5000, seed=17)
     data = to_csr(rows_f, rows_v, rng)
-    os.environ["HM_DENSE_COLUMNS"] = "0"
+    os.environ["HM_HOT_FEATURES"] = "0"
     try:
         check("train_classifier", f"-loss logloss -opt adagrad -mini_batch 2048 -dims {DIMS} -eta0 0.05", data, [])
     finally:
-        del os.environ["HM_DENSE_COLUMNS"]
+        del os.environ["HM_HOT_FEATURES"]
 
 
-def test_criteo_shaped_rows_have_13_dense_columns():
+def test_criteo_shaped_rows():
+    """The 13 quantitative columns and the head of the small categorical fields are hot."""
     data = synth.criteo_like(20000, dims=1 << 20, seed=1)
     options = f"-loss logloss -opt ftrl -mini_batch 4096 -dims {1 << 20} -alpha 0.05"
     u, w, state = run_gpu_linear("train_classifier", options, data)
-    assert len(u.dense_columns()) == 13
+    hot = set(int(x) for x in u.hot_features())
+    assert set(int(x) for x in data.feature[:13]) <= hot and 20 <= len(hot) <= 64
     ref, ref_state = run_oracle_linear("train_classifier", options, data)
     assert_weights_close(w, ref.w)
     assert_weights_close(state, ref_state, "state")
