@@ -59,7 +59,10 @@ int num_sms();
 // gradient sums itself, in a fixed order; extra CTAs of the update kernel step them.  The choice
 // only affects speed: whatever set is picked, every occurrence of a picked feature goes one way
 // and every other element the other, so no property of the rows has to be verified.
-constexpr int kMaxHot = 64;
+#ifndef HM_MAX_HOT
+#define HM_MAX_HOT 64
+#endif
+constexpr int kMaxHot = HM_MAX_HOT;
 // The kernels test "is this feature hot?" once per element, so the test is one multiply, one shift, one
 // shared-memory load and one compare: a direct-mapped table, index = hot_index(feature), entry = the
 // feature.  The selection kernel only picks features whose indices are pairwise different.
@@ -107,7 +110,8 @@ hm_status launch_hot_select(Launcher &L, SortScratch &s, const int64_t *d_rowptr
 hm_status launch_segmented_sort(Launcher &L, SortScratch &s, const uint32_t *d_feature_block,
                                 const float *d_value_block, const int64_t *d_rowptr, int64_t block_row0,
                                 int64_t block_rows, int32_t mini_batch, int64_t n_elems, int n_segs, int key_bits,
-                                int64_t dims, uint32_t *d_bad, int *out_buf, int ctas_per_sm);
+                                int64_t dims, uint32_t *d_bad, int *out_buf, int ctas_per_sm,
+                                std::vector<uint32_t> *seg_off_host = nullptr);   // filled while profiling
 
 // ---- hashing (hm_hash.cu) -----------------------------------------------------
 hm_status launch_mhash(Launcher &L, const uint8_t *d_bytes, const int64_t *d_offsets, int64_t n,
@@ -157,6 +161,7 @@ struct UpdateScratch {
     void *boundary = nullptr;     // per-CTA open-segment summaries
     uint32_t *done_counter = nullptr;
     int grid = 0;
+    uint32_t *barrier = nullptr;       // arrival counter of the persistent block kernel
     double *hot_sum = nullptr;         // see HotCols
     uint32_t *hot_cnt = nullptr;
     int hot_stride = 0;
@@ -166,7 +171,16 @@ void update_scratch_free(UpdateScratch &u);
 hm_status launch_linear_update(Launcher &L, const LinearArgs &a, const StepScalars &sc, UpdateScratch &us,
                                const uint32_t *d_sorted_key, const uint2 *d_sorted_pay,
                                const uint32_t *d_seg_off, int seg, int64_t seg_begin, const float *d_dloss,
-                               int64_t nnz_hint, const HotCols &hc);
+                               int64_t nnz_hint, const HotCols &hc, int64_t sorted_elems = -1);   // (byte accounting)
+// mid-size mini-batches (not small, <= 2^20 elements): up to 64 consecutive mini-batches of a sorted block
+// trained by one persistent, co-resident grid (forward, grid barrier, reduce + step, grid barrier)
+bool block_kernel_eligible(int32_t mini_batch, int64_t max_mb_elems);
+hm_status launch_linear_block(Launcher &L, const LinearArgs &a, UpdateScratch &us, const int64_t *d_rowptr,
+                              int64_t block_row0, int first_seg, int n_segs, const int32_t *rows, const float *eta,
+                              const float *adam_alpha, const uint32_t *d_feature, const float *d_value,
+                              const float *d_label, float *d_margin, float *d_dloss, uint32_t *d_bad,
+                              const uint32_t *d_sorted_key, const uint2 *d_sorted_pay, const uint32_t *d_seg_off,
+                              int64_t nnz_hint, int64_t max_mb_elems, const HotCols &hc);
 // small mini-batches (<= 1024 rows and <= one update tile of elements): up to 64 consecutive
 // mini-batches of a sorted block trained by one persistent CTA
 bool small_batch_eligible(int32_t mini_batch, int64_t max_mb_elems);

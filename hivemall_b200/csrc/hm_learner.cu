@@ -268,6 +268,7 @@ struct hm_udtf {
     int64_t last_margin_off = 0, last_margin_n = 0;   // last mini-batch's slice of `margin`
     bool device_rows_short = false;  // a process_device call ended on a short mini-batch
     bool hot_enabled = true;         // HM_HOT_FEATURES=0 in the environment sorts every element (A/B measurements)
+    bool block_kernel_enabled = true;   // HM_BLOCK_KERNEL=0: mid-size mini-batches take the two-kernel path (A/B measurements)
     hm_stats stats;
     bool closed = false;
     int64_t model_rows = -1;
@@ -406,6 +407,7 @@ hm_status train_rows(hm_udtf *u, Chunk &c, int64_t row0, int64_t n_rows, const i
         HM_CUDA(cudaStreamWaitEvent(u->sorter, u->ready_ev, 0));
     }
     int out_buf[2] = {0, 0};
+    std::vector<uint32_t> seg_host[2];      // while profiling: the sorted arrays' mini-batch offsets (byte accounting)
     int64_t call_max_mb = 0;
     for (int64_t m = 0; m < n_mb; m++) call_max_mb = std::max(call_max_mb, mb_abs[m + 1] - mb_abs[m]);
     // Hot features (the quantitative features every row has, the head of each categorical field) are taken out
@@ -420,7 +422,8 @@ hm_status train_rows(hm_udtf *u, Chunk &c, int64_t row0, int64_t n_rows, const i
         HM_TRY(launch_hot_select(u->Ls, u->sort[set], c.rp(), p.row0, p.rows, c.ft(), u->cfg.dims, hot_on));
         HM_TRY(launch_seg_prep(u->Ls, u->sort[set], c.rp(), p.row0, p.rows, p.nnz, B, p.n_segs));
         HM_TRY(launch_segmented_sort(u->Ls, u->sort[set], c.ft() + mb_abs[p.m0], c.vl() + mb_abs[p.m0], c.rp(), p.row0,
-                                     p.rows, B, p.nnz, p.n_segs, key_bits, u->cfg.dims, u->d_bad, &out_buf[set], 0));
+                                     p.rows, B, p.nnz, p.n_segs, key_bits, u->cfg.dims, u->d_bad, &out_buf[set], 0,
+                                     &seg_host[set]));
         HM_CUDA(cudaEventRecord(u->sorted_ev[set], u->sorter));
         if (mode == kTrainKeep && c.sorted_valid) {
             // keep the result for the later passes (device-to-device, on the sort stream, behind the event
@@ -509,6 +512,25 @@ hm_status train_rows(hm_udtf *u, Chunk &c, int64_t row0, int64_t n_rows, const i
                                                    u->margin.as<float>(), u->dloss.as<float>(), u->d_bad, ss.key[buf],
                                                    ss.pay[buf], ss.seg_off, mb_abs[p.m0 + s0 + ns] - mb_abs[p.m0 + s0]));
             }
+        } else if (!u->fm && u->block_kernel_enabled && block_kernel_eligible(B, call_max_mb)) {
+            // mid-size mini-batches: up to 64 per launch of one persistent grid (forward, grid barrier, reduce + step)
+            for (int s0 = 0; s0 < p.n_segs; s0 += 64) {
+                const int ns = std::min(64, p.n_segs - s0);
+                int32_t rows[64]; float eta[64], adam[64];
+                for (int s = 0; s < ns; s++) {
+                    const int64_t mrow0 = p.row0 + (int64_t)(s0 + s) * B;
+                    rows[s] = (int32_t)std::min<int64_t>(B, row0 + n_rows - mrow0);
+                    u->t += 1;
+                    eta[s] = eta_at(u->cfg, u->t);
+                    adam[s] = u->cfg.opt == HM_OPT_ADAM ? adam_alpha_at(u->cfg, eta[s], u->t) : 0.f;
+                    u->stats.mini_batches++;
+                    u->last_margin_off = mrow0 - p.row0;
+                    u->last_margin_n = rows[s];
+                }
+                HM_TRY(launch_linear_block(u->L, a, u->upd, c.rp(), p.row0, s0, ns, rows, eta, adam, c.ft(), c.vl(), c.lb(),
+                                           u->margin.as<float>(), u->dloss.as<float>(), u->d_bad, ss.key[buf], ss.pay[buf],
+                                           ss.seg_off, mb_abs[p.m0 + s0 + ns] - mb_abs[p.m0 + s0], call_max_mb, hc));
+            }
         } else
         for (int s = 0; s < p.n_segs; s++) {
             const int64_t mrow0 = p.row0 + (int64_t)s * B;
@@ -530,7 +552,9 @@ hm_status train_rows(hm_udtf *u, Chunk &c, int64_t row0, int64_t n_rows, const i
                 HM_TRY(launch_linear_forward(u->L, a, c.rp(), mrow0, mrows, p.row0, c.ft(), c.vl(), c.lb(),
                                              u->margin.as<float>(), u->dloss.as<float>(), u->d_bad, mnnz, hc));
                 HM_TRY(launch_linear_update(u->L, a, sc, u->upd, ss.key[buf], ss.pay[buf], ss.seg_off, s,
-                                            mb_abs[p.m0 + s] - mb_abs[p.m0], u->dloss.as<float>(), mnnz, hc));
+                                            mb_abs[p.m0 + s] - mb_abs[p.m0], u->dloss.as<float>(), mnnz, hc,
+                                            (!replay && (int)seg_host[set].size() == p.n_segs + 1)
+                                                ? (int64_t)(seg_host[set][s + 1] - seg_host[set][s]) : -1));
             }
             u->stats.mini_batches++;
             u->last_margin_off = mrow0 - p.row0;
@@ -839,6 +863,7 @@ hm_status create_impl(const hm_config &cfg, int device, hm_udtf **out)
     u->device = device;
     std::memset(&u->stats, 0, sizeof(u->stats));
     if (const char *e = std::getenv("HM_HOT_FEATURES")) u->hot_enabled = std::atoi(e) != 0;
+    if (const char *e = std::getenv("HM_BLOCK_KERNEL")) u->block_kernel_enabled = std::atoi(e) != 0;
     hm_status s = [&]() -> hm_status {
         {
             // the training stream's short kernels go first whenever both streams have CTAs to place

@@ -27,7 +27,10 @@ namespace {
 
 constexpr int kFwdThreads = 256;
 constexpr int kUpdThreads = 256;
-constexpr int kUpdItems = 8;
+#ifndef HM_UPD_ITEMS
+#define HM_UPD_ITEMS 8
+#endif
+constexpr int kUpdItems = HM_UPD_ITEMS;
 constexpr int kUpdTile = kUpdThreads * kUpdItems;  // 2048
 
 // ---- scalar math of DESIGN.md section 3 (every fp32 op rounded on its own) ------
@@ -187,26 +190,57 @@ __device__ __forceinline__ void hot_accumulate(HotShared &H, int warp, int lane,
     __syncwarp();
 }
 
+// The block's hot keys into the CTA's direct-mapped table (two barriers).  The keys of a block do not change,
+// so the persistent block kernel does this once per launch.
+__device__ __forceinline__ void hot_table_build(HotShared &H, const HotInfo *hot)
+{
+    const int tid = threadIdx.x;
+    for (int q = tid; q < kHotSlots; q += kFwdThreads) H.tab_key[q] = kHotNone;
+    __syncthreads();
+    if (tid < (int)hot->count) {
+        const uint32_t h = hot_index(hot->key[tid]);     // (pairwise different for the keys of a HotInfo)
+        H.tab_key[h] = hot->key[tid];
+        H.tab_slot[h] = (uint8_t)tid;
+    }
+    __syncthreads();
+}
+
+// Before the forward pass of a mini-batch: the hot features' current weights, cleared accumulators (one barrier).
+template <bool RO>
+__device__ __forceinline__ void hot_begin(const FwdParams &P, HotShared &H)
+{
+    const int tid = threadIdx.x;
+    for (int q = tid; q < (kFwdThreads / 32) * kMaxHot; q += kFwdThreads) { (&H.acc[0][0])[q] = 0.0; (&H.cnt[0][0])[q] = 0u; }
+    if (tid < (int)P.hot->count) {
+        const uint32_t key = P.hot->key[tid];
+        H.w[tid] = key < P.dims ? weight_at<RO>(P.wv, key) : 0.0f;
+    }
+    __syncthreads();
+}
+
+// After it: this CTA's sums (warps added in a fixed order) to slot `cta` of the per-feature arrays.
+__device__ __forceinline__ void hot_end(const FwdParams &P, HotShared &H, int cta)
+{
+    const int tid = threadIdx.x;
+    __syncthreads();
+    if (tid < (int)P.hot->count) {
+        double sum = 0.0; uint32_t cnt = 0;
+#pragma unroll
+        for (int w2 = 0; w2 < kFwdThreads / 32; w2++) { sum += H.acc[w2][tid]; cnt += H.cnt[w2][tid]; }
+        P.hot_sum[(size_t)tid * P.hot_stride + cta] = sum;
+        P.hot_cnt[(size_t)tid * P.hot_stride + cta] = cnt;
+    }
+}
+
 // forward_rows with hot features.  The margin adds the same fp32 products in the same lane order as
 // forward_rows: only the source of a hot feature's weight differs (shared memory instead of the gather;
 // it is the same number).  After a row's dloss is known, the contributions dloss * value of its hot
 // elements (what the update kernel would otherwise have found in the sorted stream) go to the warp's
 // accumulators; rows longer than 64 elements re-read their tail for that.
+template <bool RO>
 __device__ __forceinline__ void forward_rows_hot(const FwdParams &P, int warp_first, int warp_stride, HotShared &H)
 {
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const uint32_t n_hot = P.hot->count;
-    for (int q = tid; q < kHotSlots; q += kFwdThreads) H.tab_key[q] = kHotNone;
-    for (int q = tid; q < (kFwdThreads / 32) * kMaxHot; q += kFwdThreads) { (&H.acc[0][0])[q] = 0.0; (&H.cnt[0][0])[q] = 0u; }
-    __syncthreads();
-    if (tid < (int)n_hot) {
-        const uint32_t key = P.hot->key[tid];
-        H.w[tid] = key < P.dims ? weight_at<true>(P.wv, key) : 0.0f;
-        const uint32_t h = hot_index(key);     // (pairwise different for the keys of a HotInfo)
-        H.tab_key[h] = key;
-        H.tab_slot[h] = (uint8_t)tid;
-    }
-    __syncthreads();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     for (int r = warp_first; r < P.n_rows; r += warp_stride) {
         const int64_t row = P.row0 + r;
         const int64_t p0 = P.rowptr[row], p1 = P.rowptr[row + 1];
@@ -218,7 +252,7 @@ __device__ __forceinline__ void forward_rows_hot(const FwdParams &P, int warp_fi
             const float x = __ldcs(P.value + p);
             if (f < P.dims) {
                 const uint32_t sl = hot_slot_of(H, f);
-                const float w = sl != kHotNone ? H.w[sl] : weight_at<true>(P.wv, f);
+                const float w = sl != kHotNone ? H.w[sl] : weight_at<RO>(P.wv, f);
                 acc += (double)__fmul_rn(w, x);
                 if (p == p0 + lane) { slot_a = sl; x_a = x; }
                 else if (p == p0 + 32 + lane) { slot_b = sl; x_b = x; }
@@ -247,15 +281,6 @@ __device__ __forceinline__ void forward_rows_hot(const FwdParams &P, int warp_fi
             }
             hot_accumulate(H, warp, lane, sl, __fmul_rn(dl, x));
         }
-    }
-    // this CTA's sums: warps added in a fixed order
-    __syncthreads();
-    if (tid < (int)n_hot) {
-        double sum = 0.0; uint32_t cnt = 0;
-#pragma unroll
-        for (int w2 = 0; w2 < kFwdThreads / 32; w2++) { sum += H.acc[w2][tid]; cnt += H.cnt[w2][tid]; }
-        P.hot_sum[(size_t)tid * P.hot_stride + blockIdx.x] = sum;
-        P.hot_cnt[(size_t)tid * P.hot_stride + blockIdx.x] = cnt;
     }
 }
 
@@ -320,8 +345,12 @@ __global__ void __launch_bounds__(kFwdThreads, 8) linear_forward_kernel(FwdParam
 {
     __shared__ HotShared H;
     const int warp_first = blockIdx.x * (kFwdThreads / 32) + (threadIdx.x >> 5), warp_stride = gridDim.x * (kFwdThreads / 32);
-    if (P.hot && P.hot->count != 0u) forward_rows_hot(P, warp_first, warp_stride, H);
-    else forward_rows<true>(P, warp_first, warp_stride);
+    if (P.hot && P.hot->count != 0u) {
+        hot_table_build(H, P.hot);
+        hot_begin<true>(P, H);
+        forward_rows_hot<true>(P, warp_first, warp_stride, H);
+        hot_end(P, H, (int)blockIdx.x);
+    } else forward_rows<true>(P, warp_first, warp_stride);
 }
 
 // ---- update ------------------------------------------------------------------------
@@ -346,6 +375,17 @@ struct BoundaryRecs {
     uint4 *first, *last;   // SegRec as bits, one per CTA
     uint32_t *ticket;
 };
+// What changes from one mini-batch to the next.  Apart from this block an UpdParams is the same for every
+// mini-batch of an ingest block: the persistent block kernel keeps ONE UpdParams in its (constant) kernel
+// parameters and one UpdDyn per mini-batch in shared memory.
+struct UpdDyn {
+    int32_t seg;             // mini-batch of the sorted block
+    int32_t n_active;        // CTAs that own tiles (all own at least one unless the mini-batch is empty)
+    int32_t fwd_grid;        // CTAs of the forward pass (partial sums of the hot features)
+    float eta, adam_alpha;
+    double inv_rows;         // 1 / rows of the mini-batch, computed in fp64
+};
+
 struct UpdParams {
     float *rec;              // replica: rec_width floats per feature = (w[, slot1[, slot2, unused]])
     int32_t rec_width;       // 1, 2 or 4
@@ -356,19 +396,17 @@ struct UpdParams {
     const float *dloss;      // dloss of every row of this mini-batch
     const uint32_t *seg_off;
     BoundaryRecs br;
-    int32_t seg;
+    UpdDyn dyn;              // the mini-batch (kernels that train one mini-batch per launch read it from here)
     uint32_t dims;
     int32_t opt, reg, grad_norm;
-    float eta, adam_alpha, lambda, eps, rho, beta1, beta2, alpha, beta, lambda1, lambda2;
-    double inv_rows;         // 1 / rows of the mini-batch, computed on the host in fp64
-    int32_t n_active;        // CTAs launched (all own at least one tile unless the segment is empty)
+    float lambda, eps, rho, beta1, beta2, alpha, beta, lambda1, lambda2;
     // (the mini-batch's bounds in the sorted arrays are read from seg_off: the sorted arrays are shorter
     // than the CSR by the hot-feature and out-of-range elements, a number only the device knows)
     // hot features of the block (NULL: the block was sorted whole)
     const HotInfo *hot;
     const double *hot_sum;   // [kMaxHot][hot_stride] gradient sums left by the forward kernel's CTAs
     const uint32_t *hot_cnt; // ... and occurrence counts
-    int32_t hot_stride, fwd_grid;
+    int32_t hot_stride;
 };
 
 // Replica record of one feature while it is being updated.
@@ -400,26 +438,26 @@ __device__ __forceinline__ void store_rec(const UpdParams &P, uint32_t j, const 
 }
 
 // mean gradient of one feature from its fp64 sum: DESIGN.md 3.4
-__device__ __forceinline__ float grad_of(const UpdParams &P, double sum, uint32_t cnt)
+__device__ __forceinline__ float grad_of(const UpdParams &P, const UpdDyn &D, double sum, uint32_t cnt)
 {
-    if (P.grad_norm == HM_NORM_BATCH) return (float)(sum * P.inv_rows);
+    if (P.grad_norm == HM_NORM_BATCH) return (float)(sum * D.inv_rows);
     if (P.grad_norm == HM_NORM_COUNT) return (float)(sum / (double)cnt);
     return (float)sum;
 }
 
 // One coordinate step: DESIGN.md 3.5-3.6 (every fp32 operation rounded on its own).
-__device__ __forceinline__ void step_rec(const UpdParams &P, Rec &r, float g)
+__device__ __forceinline__ void step_rec(const UpdParams &P, const UpdDyn &D, Rec &r, float g)
 {
     float wv = r.w;
     if (P.reg == HM_REG_L2 && P.opt != HM_OPT_FTRL) g = __fadd_rn(g, __fmul_rn(P.lambda, wv));
     switch (P.opt) {
     case HM_OPT_SGD:
-        wv = __fsub_rn(wv, __fmul_rn(P.eta, g));
+        wv = __fsub_rn(wv, __fmul_rn(D.eta, g));
         break;
     case HM_OPT_ADAGRAD: {
         const float G = __fadd_rn(r.s1, __fmul_rn(g, g));
         r.s1 = G;
-        wv = __fsub_rn(wv, __fdiv_rn(__fmul_rn(P.eta, g), __fadd_rn(__fsqrt_rn(G), P.eps)));
+        wv = __fsub_rn(wv, __fdiv_rn(__fmul_rn(D.eta, g), __fadd_rn(__fsqrt_rn(G), P.eps)));
         break;
     }
     case HM_OPT_ADADELTA: {
@@ -435,7 +473,7 @@ __device__ __forceinline__ void step_rec(const UpdParams &P, Rec &r, float g)
         const float m = __fadd_rn(__fmul_rn(P.beta1, r.s1), __fmul_rn(__fsub_rn(1.0f, P.beta1), g));
         const float v = __fadd_rn(__fmul_rn(P.beta2, r.s2), __fmul_rn(__fmul_rn(__fsub_rn(1.0f, P.beta2), g), g));
         r.s1 = m; r.s2 = v;
-        wv = __fsub_rn(wv, __fdiv_rn(__fmul_rn(P.adam_alpha, m), __fadd_rn(__fsqrt_rn(v), P.eps)));
+        wv = __fsub_rn(wv, __fdiv_rn(__fmul_rn(D.adam_alpha, m), __fadd_rn(__fsqrt_rn(v), P.eps)));
         break;
     }
     case HM_OPT_FTRL: {   // (s1, s2) = (z, n)
@@ -455,7 +493,7 @@ __device__ __forceinline__ void step_rec(const UpdParams &P, Rec &r, float g)
     }
     }
     if (P.reg == HM_REG_L1 && P.opt != HM_OPT_FTRL) {
-        const float a = __fsub_rn(fabsf(wv), __fmul_rn(P.eta, P.lambda));
+        const float a = __fsub_rn(fabsf(wv), __fmul_rn(D.eta, P.lambda));
         wv = a > 0.0f ? copysignf(a, wv) : 0.0f;
     }
     r.w = wv;
@@ -490,7 +528,7 @@ constexpr size_t kUpdSmem = kUpdSmemTile > kUpdSmemMerge ? kUpdSmemTile : kUpdSm
 // Apply the optimizer to list entries [0, n): kUpdBatch independent read-modify-writes per thread
 // are issued together so that their DRAM latencies overlap.  Entries are distinct features;
 // 0xffffffff marks a slot to skip.
-__device__ __forceinline__ void apply_list(const UpdParams &P, const uint32_t *l_key, const float *l_g, int n, int tid)
+__device__ __forceinline__ void apply_list(const UpdParams &P, const UpdDyn &D, const uint32_t *l_key, const float *l_g, int n, int tid)
 {
     for (int i0 = 0; i0 < n; i0 += kUpdThreads * kUpdBatch) {
         uint32_t j[kUpdBatch]; float g[kUpdBatch]; Rec r[kUpdBatch]; bool ok[kUpdBatch];
@@ -505,7 +543,7 @@ __device__ __forceinline__ void apply_list(const UpdParams &P, const uint32_t *l
 #pragma unroll
         for (int u = 0; u < kUpdBatch; u++) if (ok[u]) r[u] = load_rec(P, j[u]);
 #pragma unroll
-        for (int u = 0; u < kUpdBatch; u++) if (ok[u]) step_rec(P, r[u], g[u]);
+        for (int u = 0; u < kUpdBatch; u++) if (ok[u]) step_rec(P, D, r[u], g[u]);
 #pragma unroll
         for (int u = 0; u < kUpdBatch; u++) if (ok[u]) store_rec(P, j[u], r[u]);
     }
@@ -533,7 +571,7 @@ struct UpdShared {
 // entries, to be stepped by apply_list), open segments left in S.s_carry / S.s_first.  Ends on a
 // barrier.  RO: dloss was written by an earlier kernel and may use the read-only path.
 template <bool RO>
-__device__ __forceinline__ void reduce_tile(const UpdParams &P, const UpdShared &S, uint32_t base, int n_tile,
+__device__ __forceinline__ void reduce_tile(const UpdParams &P, const UpdDyn &D, const UpdShared &S, uint32_t base, int n_tile,
                                             bool first_tile, bool last_tile)
 {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -589,7 +627,7 @@ __device__ __forceinline__ void reduce_tile(const UpdParams &P, const UpdShared 
             if (!left_closed && !right_closed) { *S.s_carry = r; *S.s_carry_open = 1; }   // piece of a longer run
             else if (!left_closed) *S.s_first = r;                                          // the run's last piece
             else if (!right_closed) *S.s_carry = r;                                         // the run's first piece
-            else { S.l_key[0] = key0; S.l_g[0] = grad_of(P, sum, r.cnt); *S.s_nlist = 1; }  // the whole run
+            else { S.l_key[0] = key0; S.l_g[0] = grad_of(P, D, sum, r.cnt); *S.s_nlist = 1; }  // the whole run
         }
         __syncthreads();
         return;
@@ -650,7 +688,7 @@ __device__ __forceinline__ void reduce_tile(const UpdParams &P, const UpdShared 
     if (tid == 0 && edge_continues) { run = carry.sum; cnt = carry.cnt; }
     if (tid == 0 && carry.cnt != 0 && !edge_continues) {
         if (carry_open) *S.s_first = carry;
-        else { S.l_key[slot] = carry.key; S.l_g[slot] = grad_of(P, carry.sum, carry.cnt); slot++; }
+        else { S.l_key[slot] = carry.key; S.l_g[slot] = grad_of(P, D, carry.sum, carry.cnt); slot++; }
     }
     // (the tile is read again from shared memory: keeping sixteen values in registers across the
     // scan costs a fourth resident CTA per SM)
@@ -672,7 +710,7 @@ __device__ __forceinline__ void reduce_tile(const UpdParams &P, const UpdShared 
                     S.s_first->sum = run; S.s_first->key = kcur; S.s_first->cnt = cnt;
                     S.l_key[slot] = 0xffffffffu; S.l_g[slot] = 0.f;   // placeholder: skipped by apply_list
                 } else {
-                    S.l_key[slot] = kcur; S.l_g[slot] = grad_of(P, run, cnt);
+                    S.l_key[slot] = kcur; S.l_g[slot] = grad_of(P, D, run, cnt);
                 }
                 slot++;
                 if (q == n_tile - 1) { S.s_carry->cnt = 0; *S.s_carry_open = 0; }
@@ -692,7 +730,7 @@ __device__ __forceinline__ void reduce_tile(const UpdParams &P, const UpdShared 
 // records.  A hot feature that does not occur in this mini-batch is left alone, like any other.
 constexpr int kHotCtas = kMaxHot / (kUpdThreads / 32);
 
-__device__ __noinline__ void hot_features_step(const UpdParams &P, int part)
+__device__ __noinline__ void hot_features_step(const UpdParams &P, const UpdDyn &D, int part)
 {
     const int lane = threadIdx.x & 31;
     const int i = part * (kUpdThreads / 32) + (threadIdx.x >> 5);
@@ -700,40 +738,53 @@ __device__ __noinline__ void hot_features_step(const UpdParams &P, int part)
     const double *col = P.hot_sum + (size_t)i * P.hot_stride;
     const uint32_t *ccol = P.hot_cnt + (size_t)i * P.hot_stride;
     double sum = 0.0; uint32_t cnt = 0;
-    for (int c = lane; c < P.fwd_grid; c += 32) { sum += col[c]; cnt += ccol[c]; }
+    for (int c = lane; c < D.fwd_grid; c += 32) { sum += col[c]; cnt += ccol[c]; }
     sum = warp_sum(sum);
     cnt = __reduce_add_sync(0xffffffffu, cnt);
     if (lane == 0 && cnt != 0u) {
         const uint32_t j = P.hot->key[i];
         Rec r = load_rec(P, j);
-        step_rec(P, r, grad_of(P, sum, cnt));
+        step_rec(P, D, r, grad_of(P, D, sum, cnt));
         store_rec(P, j, r);
     }
 }
 
-__global__ void __launch_bounds__(kUpdThreads, 4) linear_update_kernel(const __grid_constant__ UpdParams P)
+// Shared memory of one CTA of the update kernels.
+struct UpdCtaSmem {
+    __align__(16) unsigned char raw[kUpdSmem];
+    Scan warp[kUpdThreads / 32];
+    SegRec carry;            // open trailing segment of the previous tile
+    SegRec first;            // the CTA's piece of a segment that began before its range
+    uint32_t carry_open;
+    uint32_t is_last;
+    uint32_t edge[2];        // does the CTA's range start / end on a true segment boundary?
+    int nlist;
+};
+
+// Reduce-by-feature and optimizer step of mini-batch P.seg of a sorted block, as CTA `cta` of P.n_active.
+// RO: nothing this kernel writes is read here through the read-only path (false inside the persistent
+// block kernel, where dloss and the replica change between mini-batches of one launch).
+template <bool RO>
+__device__ __forceinline__ void update_segment(const UpdParams &P, const UpdDyn &D, UpdCtaSmem &sm, const int cta)
 {
-    __shared__ __align__(16) unsigned char smem_raw[kUpdSmem];
+    unsigned char *smem_raw = sm.raw;
+    Scan *s_warp = sm.warp;
+    SegRec &s_carry = sm.carry;
+    SegRec &s_first = sm.first;
+    uint32_t &s_carry_open = sm.carry_open;
+    uint32_t &s_is_last = sm.is_last;
+    uint32_t *s_edge = sm.edge;
+    int &s_nlist = sm.nlist;
     uint32_t *s_key = reinterpret_cast<uint32_t *>(smem_raw);
     float *s_val = reinterpret_cast<float *>(smem_raw + (size_t)kUpdPadded * 4);
     uint32_t *l_key = reinterpret_cast<uint32_t *>(smem_raw + (size_t)kUpdPadded * 8);
     float *l_g = reinterpret_cast<float *>(smem_raw + (size_t)kUpdPadded * 8 + (size_t)kUpdList * 4);
-    __shared__ Scan s_warp[kUpdThreads / 32];
-    __shared__ SegRec s_carry;       // open trailing segment of the previous tile
-    __shared__ SegRec s_first;       // the CTA's piece of a segment that began before its range
-    __shared__ uint32_t s_carry_open;
-    __shared__ uint32_t s_is_last;
-    __shared__ uint32_t s_edge[2];   // does the CTA's range start / end on a true segment boundary?
-    __shared__ int s_nlist;
-
     const int tid = threadIdx.x;
-    USTAMP(0);
-    if ((int)blockIdx.x >= P.n_active) { hot_features_step(P, (int)blockIdx.x - P.n_active); return; }
-    const uint32_t s0 = P.seg_off[P.seg], n = P.seg_off[P.seg + 1] - s0;
+    const uint32_t s0 = P.seg_off[D.seg], n = P.seg_off[D.seg + 1] - s0;
     // contiguous split of the sorted mini-batch over the grid, in whole tiles
     const uint32_t tiles = (n + kUpdTile - 1) / kUpdTile;
-    const uint32_t tiles_per_cta = (tiles + P.n_active - 1) / P.n_active;
-    const uint32_t lo = min(n, blockIdx.x * tiles_per_cta * kUpdTile);
+    const uint32_t tiles_per_cta = (tiles + D.n_active - 1) / D.n_active;
+    const uint32_t lo = min(n, (uint32_t)cta * tiles_per_cta * kUpdTile);
     const uint32_t hi = min(n, lo + tiles_per_cta * kUpdTile);
 
     if (tid == 0) { s_carry.cnt = 0; s_carry_open = 0; s_first.cnt = 0; s_is_last = 0; }
@@ -750,35 +801,35 @@ __global__ void __launch_bounds__(kUpdThreads, 4) linear_update_kernel(const __g
     if (lo >= hi) __syncthreads();   // (the tile loop below has its own barriers)
 
     UpdShared S;
-    S.s_key = s_key; S.s_val = s_val; S.l_key = l_key; S.l_g = l_g; S.s_warp = s_warp; S.s_carry = &s_carry;
-    S.s_first = &s_first; S.s_carry_open = &s_carry_open; S.s_edge = s_edge; S.s_nlist = &s_nlist;
+    S.s_key = s_key; S.s_val = s_val; S.l_key = l_key; S.l_g = l_g; S.s_warp = s_warp; S.s_carry = &sm.carry;
+    S.s_first = &sm.first; S.s_carry_open = &sm.carry_open; S.s_edge = s_edge; S.s_nlist = &sm.nlist;
     for (uint32_t t0 = lo; t0 < hi; t0 += kUpdTile) {
         const int n_tile = (int)min((uint32_t)kUpdTile, hi - t0);
         const bool last_tile = t0 + kUpdTile >= hi;
-        reduce_tile<true>(P, S, s0 + t0, n_tile, t0 == lo, last_tile);
+        reduce_tile<RO>(P, D, S, s0 + t0, n_tile, t0 == lo, last_tile);
         USTAMP(3);
         // ---- after the last tile the CTA's boundary pieces are final: publish them and take the
         // completion ticket now, so that both round trips overlap the optimizer step below
         if (last_tile && tid == 0) {
             const uint4 none = make_uint4(0u, 0u, 0u, 0u);
             const bool whole = s_carry.cnt != 0 && s_carry_open;     // the range lies inside one segment
-            P.br.first[blockIdx.x] = whole ? rec_bits(s_carry) : (s_first.cnt != 0 ? rec_bits(s_first) : none);
-            P.br.last[blockIdx.x] = (!whole && s_carry.cnt != 0) ? rec_bits(s_carry) : none;
+            P.br.first[cta] = whole ? rec_bits(s_carry) : (s_first.cnt != 0 ? rec_bits(s_first) : none);
+            P.br.last[cta] = (!whole && s_carry.cnt != 0) ? rec_bits(s_carry) : none;
             __threadfence();
-            s_is_last = atomicAdd(P.br.ticket, 1u) == (uint32_t)P.n_active - 1;
+            s_is_last = atomicAdd(P.br.ticket, 1u) == (uint32_t)D.n_active - 1;
         }
         // ---- optimizer step for the listed features, latencies overlapped
         USTAMP(4);
-        apply_list(P, l_key, l_g, s_nlist, tid);
+        apply_list(P, D, l_key, l_g, s_nlist, tid);
         __syncthreads();
         USTAMP(5);
     }
     if (lo >= hi) {   // a CTA without elements leaves empty records and still takes its ticket
         if (tid == 0) {
-            P.br.first[blockIdx.x] = make_uint4(0u, 0u, 0u, 0u);
-            P.br.last[blockIdx.x] = make_uint4(0u, 0u, 0u, 0u);
+            P.br.first[cta] = make_uint4(0u, 0u, 0u, 0u);
+            P.br.last[cta] = make_uint4(0u, 0u, 0u, 0u);
             __threadfence();
-            s_is_last = atomicAdd(P.br.ticket, 1u) == (uint32_t)P.n_active - 1;
+            s_is_last = atomicAdd(P.br.ticket, 1u) == (uint32_t)D.n_active - 1;
         }
         __syncthreads();
     }
@@ -788,7 +839,7 @@ __global__ void __launch_bounds__(kUpdThreads, 4) linear_update_kernel(const __g
     // in shared memory; the thread that owns CTA c starts a run at last[c] and walks first[c+1],
     // first[c+2], ... while the feature matches (fixed order, fp64).  No sorting is needed.
     __threadfence();
-    const int G = P.n_active;
+    const int G = D.n_active;
     uint4 *f_sm = reinterpret_cast<uint4 *>(smem_raw);
     uint32_t *ml_key = reinterpret_cast<uint32_t *>(smem_raw + (size_t)kUpdMaxGrid * 16);
     float *ml_g = reinterpret_cast<float *>(ml_key + kUpdMaxGrid);
@@ -814,13 +865,105 @@ __global__ void __launch_bounds__(kUpdThreads, 4) linear_update_kernel(const __g
                 sum += __hiloint2double((int)f.y, (int)f.x); cnt += f.w;
             }
             const int sl = atomicAdd(&s_nlist, 1);     // distinct features: list order is irrelevant
-            ml_key[sl] = key; ml_g[sl] = grad_of(P, sum, cnt);
+            ml_key[sl] = key; ml_g[sl] = grad_of(P, D, sum, cnt);
         }
     }
     __syncthreads();
-    apply_list(P, ml_key, ml_g, s_nlist, tid);
+    apply_list(P, D, ml_key, ml_g, s_nlist, tid);
     USTAMP(6);
     if (tid == 0) *P.br.ticket = 0;   // ready for the next launch on this stream
+}
+
+__global__ void __launch_bounds__(kUpdThreads, 4) linear_update_kernel(const __grid_constant__ UpdParams P)
+{
+    __shared__ UpdCtaSmem sm;
+    USTAMP(0);
+    if ((int)blockIdx.x >= P.dyn.n_active) { hot_features_step(P, P.dyn, (int)blockIdx.x - P.dyn.n_active); return; }
+    update_segment<true>(P, P.dyn, sm, (int)blockIdx.x);
+}
+
+// ---- mid-size mini-batches: one persistent grid per block ------------------------------------
+//
+// Between a few thousand and a few hundred thousand elements per mini-batch the two kernels above are
+// mostly launch latency, prologues and tails (measured at -mini_batch 8192 on Criteo-shaped rows: 33 us
+// per mini-batch for 10 us of work).  This kernel trains up to kBlockSegs consecutive mini-batches of a
+// sorted block in ONE launch of a grid that is resident as a whole: forward of mini-batch s over all
+// warps of the grid, grid barrier, reduce-by-feature + optimizer step of mini-batch s (the same
+// update_segment, CTA i taking the i-th range of tiles; the last one to finish merges the straddling
+// segments) and the hot features' step, grid barrier, s + 1.  Same arithmetic as the two-kernel path;
+// the order of the hot features' sums follows the grid size, as it does there.
+constexpr int kBlockSegs = 64;
+#ifndef HM_BLOCK_MINB
+#define HM_BLOCK_MINB 3
+#endif
+
+struct BlockParams {
+    FwdParams F;             // row0 / n_rows are filled per mini-batch
+    UpdParams U;             // seg / eta / adam_alpha / inv_rows / n_active / fwd_grid are filled per mini-batch
+    int32_t first_seg, n_segs, mini_batch;
+    uint32_t *barrier;       // arrival counter, zero at launch
+    float eta[kBlockSegs], adam_alpha[kBlockSegs];
+    int32_t rows[kBlockSegs];
+};
+
+// Every CTA of the (co-resident) grid arrives; `target` = arrivals expected so far.  The fences make what the
+// CTAs wrote before the barrier visible to every CTA after it.
+__device__ __forceinline__ void grid_barrier(uint32_t *counter, uint32_t target)
+{
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        atomicAdd(counter, 1u);
+        while (*reinterpret_cast<volatile uint32_t *>(counter) < target) { }
+        __threadfence();
+    }
+    __syncthreads();
+}
+
+// (out of line: each phase gets its own register allocation, as in the two kernels it replaces)
+__device__ __noinline__ void block_forward(const FwdParams &F, HotShared &H, bool hot, int warp_first, int warp_stride, int cta)
+{
+    if (hot) {
+        hot_begin<false>(F, H);
+        forward_rows_hot<false>(F, warp_first, warp_stride, H);
+        hot_end(F, H, cta);
+    } else forward_rows<false>(F, warp_first, warp_stride);
+}
+
+
+__global__ void __launch_bounds__(kUpdThreads, HM_BLOCK_MINB) linear_block_kernel(const __grid_constant__ BlockParams P)
+{
+    extern __shared__ __align__(16) unsigned char blk_smem[];
+    UpdCtaSmem &sm = *reinterpret_cast<UpdCtaSmem *>(blk_smem);
+    __shared__ HotShared H;
+    const int G = (int)gridDim.x, cta = (int)blockIdx.x;
+    const bool hot = P.F.hot != nullptr && P.F.hot->count != 0u;
+    if (hot) hot_table_build(H, P.F.hot);
+    const int warp_first = cta * (kUpdThreads / 32) + (threadIdx.x >> 5), warp_stride = G * (kUpdThreads / 32);
+    // the per-mini-batch parameter blocks live in shared memory (a private copy per thread would sit on the stack)
+    __shared__ FwdParams F;
+    __shared__ UpdDyn D;
+    uint32_t target = 0;
+    for (int s = 0; s < P.n_segs; s++) {
+        if (threadIdx.x == 0) {
+            F = P.F;
+            F.row0 = P.F.block_row0 + (int64_t)(P.first_seg + s) * P.mini_batch;
+            F.n_rows = P.rows[s];
+            D.seg = P.first_seg + s; D.eta = P.eta[s]; D.adam_alpha = P.adam_alpha[s];
+            D.inv_rows = 1.0 / (double)P.rows[s];
+            D.fwd_grid = G;
+            const uint32_t n = P.U.seg_off[D.seg + 1] - P.U.seg_off[D.seg];
+            D.n_active = min(G, max((int)((n + kUpdTile - 1) / kUpdTile), 1));
+        }
+        __syncthreads();
+        block_forward(F, H, hot, warp_first, warp_stride, cta);
+        target += (uint32_t)G;
+        grid_barrier(P.barrier, target);      // every row's dloss (and the hot sums) are written
+        if (cta < D.n_active) update_segment<false>(P.U, D, sm, cta);
+        if (hot) for (int part = G - 1 - cta; part < kHotCtas; part += G) hot_features_step(P.U, D, part);
+        target += (uint32_t)G;
+        grid_barrier(P.barrier, target);      // the step is complete before the next forward reads the replica
+    }
 }
 
 // ---- small mini-batches: one persistent CTA ----------------------------------------
@@ -831,6 +974,7 @@ __global__ void __launch_bounds__(kUpdThreads, 4) linear_update_kernel(const __g
 // optimizer step of mini-batch s (a single tile, so no piece ever leaves the CTA), barrier, s+1.
 // Same arithmetic, same order as the two-kernel path: the results are bit-identical.
 constexpr int kSmallSegs = 64;
+constexpr int64_t kBlockKernelMaxElems = (int64_t)1 << 20;   // per mini-batch; above that the two-kernel path keeps the GPU full on its own
 
 constexpr int kSmallMaxRows = 1024;                 // rows per mini-batch on this path
 constexpr size_t kSmallModelMax = 128 * 1024;       // a replica up to this size lives in shared memory for the launch
@@ -880,15 +1024,16 @@ __global__ void __launch_bounds__(kUpdThreads, 1) linear_small_batch_kernel(cons
         if (tid == 0) { s_carry.cnt = 0; s_carry_open = 0; s_first.cnt = 0; s_edge[0] = 1; s_edge[1] = 1; s_nlist = 0; }
         __syncthreads();     // dloss of every row is written; the whole mini-batch is one closed range
         UpdParams U = P.U;
-        U.seg = P.first_seg + s; U.eta = P.eta[s]; U.adam_alpha = P.adam_alpha[s];
-        U.inv_rows = 1.0 / (double)P.rows[s];
+        UpdDyn D;
+        D.seg = P.first_seg + s; D.eta = P.eta[s]; D.adam_alpha = P.adam_alpha[s];
+        D.inv_rows = 1.0 / (double)P.rows[s]; D.n_active = 1; D.fwd_grid = 0;
         U.dloss = s_dloss;
         if (staged) U.rec = s_model;
-        const uint32_t s0 = U.seg_off[U.seg];
-        const int n = (int)(U.seg_off[U.seg + 1] - s0);       // <= kUpdTile, checked by the host
+        const uint32_t s0 = U.seg_off[D.seg];
+        const int n = (int)(U.seg_off[D.seg + 1] - s0);       // <= kUpdTile, checked by the host
         if (n > 0) {
-            reduce_tile<false>(U, S, s0, n, true, true);
-            apply_list(U, S.l_key, S.l_g, s_nlist, tid);
+            reduce_tile<false>(U, D, S, s0, n, true, true);
+            apply_list(U, D, S.l_key, S.l_g, s_nlist, tid);
         }
         __syncthreads();     // the step is complete before the next forward reads the replica
     }
@@ -1070,12 +1215,16 @@ hm_status launch_predict_linear(Launcher &L, const WeightView &wv, int64_t dims,
 hm_status update_scratch_reserve(UpdateScratch &u)
 {
     if (u.boundary) return HM_OK;
-    u.grid = kUpdMaxGrid;
+    // one tile per CTA while the CTAs fit on the device at once (four per SM); beyond that each CTA walks
+    // consecutive tiles -- a second, mostly empty wave of CTAs costs more than the walk (measured)
+    u.grid = std::min(kUpdMaxGrid, num_sms() * 4);
     // [ first: grid x 16 B | last: grid x 16 B | ticket ]
     const size_t bytes = (size_t)2 * u.grid * 16 + 16;
     HM_CUDA(cudaMalloc(&u.boundary, bytes));
     HM_CUDA(cudaMemset(u.boundary, 0, bytes));
     u.done_counter = reinterpret_cast<uint32_t *>(static_cast<char *>(u.boundary) + (size_t)2 * u.grid * 16);
+    HM_CUDA(cudaMalloc(&u.barrier, sizeof(uint32_t)));
+    HM_CUDA(cudaMemset(u.barrier, 0, sizeof(uint32_t)));
     // gradient sums of the hot features: one double and one count per (feature, forward CTA)
     u.hot_stride = num_sms() * 8;
     HM_CUDA(cudaMalloc(&u.hot_sum, (size_t)kMaxHot * u.hot_stride * sizeof(double)));
@@ -1088,39 +1237,40 @@ hm_status update_scratch_reserve(UpdateScratch &u)
 void update_scratch_free(UpdateScratch &u)
 {
     cudaFree(u.boundary);
-    cudaFree(u.hot_sum); cudaFree(u.hot_cnt);
+    cudaFree(u.hot_sum); cudaFree(u.hot_cnt); cudaFree(u.barrier);
+    u.barrier = nullptr;
     u.boundary = nullptr; u.done_counter = nullptr; u.grid = 0; u.hot_sum = nullptr; u.hot_cnt = nullptr; u.hot_stride = 0;
 }
 
 hm_status launch_linear_update(Launcher &L, const LinearArgs &a, const StepScalars &sc, UpdateScratch &us,
                                const uint32_t *d_sorted_key, const uint2 *d_sorted_pay,
                                const uint32_t *d_seg_off, int seg, int64_t seg_begin, const float *d_dloss, int64_t nnz_hint,
-                               const HotCols &hc)
+                               const HotCols &hc, int64_t sorted_elems)
 {
     UpdParams P;
     (void)seg_begin;
     P.hot = hc.info; P.hot_sum = hc.sum; P.hot_cnt = hc.cnt; P.hot_stride = hc.stride;
-    P.fwd_grid = linear_forward_grid(sc.n_rows);
+    P.dyn.fwd_grid = linear_forward_grid(sc.n_rows);
     P.rec = a.rec; P.rec_width = a.rec_width; P.ftrl_derived = a.wv.ftrl; P.touched = nullptr;
     P.skey = d_sorted_key; P.spay = d_sorted_pay; P.dloss = d_dloss; P.seg_off = d_seg_off;
     P.br.first = reinterpret_cast<uint4 *>(us.boundary);
     P.br.last = P.br.first + us.grid;
     P.br.ticket = us.done_counter;
-    P.seg = seg; P.dims = (uint32_t)a.cfg.dims;
+    P.dyn.seg = seg; P.dims = (uint32_t)a.cfg.dims;
     P.opt = a.cfg.opt; P.reg = a.cfg.reg; P.grad_norm = a.cfg.grad_norm;
-    P.eta = sc.eta; P.adam_alpha = sc.adam_alpha; P.lambda = a.cfg.lambda; P.eps = a.cfg.eps; P.rho = a.cfg.rho;
+    P.dyn.eta = sc.eta; P.dyn.adam_alpha = sc.adam_alpha; P.lambda = a.cfg.lambda; P.eps = a.cfg.eps; P.rho = a.cfg.rho;
     P.beta1 = a.cfg.beta1; P.beta2 = a.cfg.beta2; P.alpha = a.cfg.alpha; P.beta = a.cfg.beta;
     P.lambda1 = a.cfg.lambda1; P.lambda2 = a.cfg.lambda2;
-    P.inv_rows = 1.0 / (double)sc.n_rows;
+    P.dyn.inv_rows = 1.0 / (double)sc.n_rows;
     // one tile per CTA up to kUpdMaxGrid CTAs; beyond that each CTA walks consecutive tiles.
     // nnz_hint is exact (the host knows rowptr at every mini-batch boundary).
     const int64_t tiles = std::max<int64_t>((nnz_hint + kUpdTile - 1) / kUpdTile, 1);
     const int64_t tiles_per_cta = (tiles + us.grid - 1) / us.grid;
     const int grid = (int)((tiles + tiles_per_cta - 1) / tiles_per_cta);
-    P.n_active = grid;
+    P.dyn.n_active = grid;
     // algorithmic bytes: sorted feature + (row, value) stream; dloss table and the per-feature
     // state traffic (number of distinct features is data dependent) are not counted
-    const double bytes = 12.0 * (double)nnz_hint;
+    const double bytes = 12.0 * (double)(sorted_elems >= 0 ? sorted_elems : nnz_hint);
     // (nnz_hint bounds the sorted mini-batch from above: CTAs past its end find nothing to do; kHotCtas
     // more CTAs step the hot features)
     HM_LAUNCH(L, K_LIN_UPDATE, bytes, (linear_update_kernel<<<grid + (hc.info ? kHotCtas : 0), kUpdThreads, 0, L.stream>>>(P)));
@@ -1167,6 +1317,67 @@ hm_status launch_linear_small_batches(Launcher &L, const LinearArgs &a, const in
         dyn = model_bytes;
     }
     HM_LAUNCH(L, K_LIN_UPDATE, 24.0 * (double)nnz_hint, (linear_small_batch_kernel<<<1, kUpdThreads, dyn, L.stream>>>(P)));
+    HM_CUDA(cudaGetLastError());
+    return HM_OK;
+}
+
+bool block_kernel_eligible(int32_t mini_batch, int64_t max_mb_elems)
+{
+    return !small_batch_eligible(mini_batch, max_mb_elems) && max_mb_elems <= kBlockKernelMaxElems;
+}
+
+hm_status launch_linear_block(Launcher &L, const LinearArgs &a, UpdateScratch &us, const int64_t *d_rowptr,
+                              int64_t block_row0, int first_seg, int n_segs, const int32_t *rows, const float *eta,
+                              const float *adam_alpha, const uint32_t *d_feature, const float *d_value,
+                              const float *d_label, float *d_margin, float *d_dloss, uint32_t *d_bad,
+                              const uint32_t *d_sorted_key, const uint2 *d_sorted_pay, const uint32_t *d_seg_off,
+                              int64_t nnz_hint, int64_t max_mb_elems, const HotCols &hc)
+{
+    if (n_segs < 1 || n_segs > kBlockSegs) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "block launch of %d mini-batches", n_segs);
+    constexpr size_t kDyn = sizeof(UpdCtaSmem);
+    // once per device: opt in to the dynamic shared memory, and how many CTAs fit on the device at once
+    static std::atomic<int> resident[64];
+    int dev = 0;
+    HM_CUDA(cudaGetDevice(&dev));
+    int fit = (dev >= 0 && dev < 64) ? resident[dev].load(std::memory_order_acquire) : 0;
+    if (fit == 0) {
+        HM_CUDA(cudaFuncSetAttribute(linear_block_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kDyn));
+        int per_sm = 0;
+        HM_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, linear_block_kernel, kUpdThreads, kDyn));
+        if (per_sm < 1) HM_FAIL(HM_ERR_CUDA, "the block kernel does not fit on this device");
+        fit = std::min(per_sm, 2) * num_sms();      // at most two per SM: the sort of the next block runs beside it
+        if (dev >= 0 && dev < 64) resident[dev].store(fit, std::memory_order_release);
+    }
+    BlockParams P;
+    std::memset(&P, 0, sizeof(P));
+    P.F.wv = a.wv; P.F.rowptr = d_rowptr; P.F.feature = d_feature; P.F.value = d_value; P.F.label = d_label;
+    P.F.margin = d_margin; P.F.dloss = d_dloss; P.F.block_row0 = block_row0;
+    P.F.task = a.cfg.task; P.F.loss = a.cfg.loss; P.F.train = 1; P.F.dims = (uint32_t)a.cfg.dims; P.F.bad = d_bad;
+    P.F.hot = hc.info; P.F.hot_sum = hc.sum; P.F.hot_cnt = hc.cnt; P.F.hot_stride = hc.stride;
+    P.U.rec = a.rec; P.U.rec_width = a.rec_width; P.U.ftrl_derived = a.wv.ftrl; P.U.touched = nullptr;
+    P.U.skey = d_sorted_key; P.U.spay = d_sorted_pay; P.U.dloss = d_dloss; P.U.seg_off = d_seg_off;
+    P.U.br.first = reinterpret_cast<uint4 *>(us.boundary);
+    P.U.br.last = P.U.br.first + us.grid;
+    P.U.br.ticket = us.done_counter;
+    P.U.dims = (uint32_t)a.cfg.dims; P.U.opt = a.cfg.opt; P.U.reg = a.cfg.reg; P.U.grad_norm = a.cfg.grad_norm;
+    P.U.lambda = a.cfg.lambda; P.U.eps = a.cfg.eps; P.U.rho = a.cfg.rho; P.U.beta1 = a.cfg.beta1; P.U.beta2 = a.cfg.beta2;
+    P.U.alpha = a.cfg.alpha; P.U.beta = a.cfg.beta; P.U.lambda1 = a.cfg.lambda1; P.U.lambda2 = a.cfg.lambda2;
+    P.U.hot = hc.info; P.U.hot_sum = hc.sum; P.U.hot_cnt = hc.cnt; P.U.hot_stride = hc.stride;
+    P.first_seg = first_seg; P.n_segs = n_segs; P.mini_batch = a.cfg.mini_batch;
+    P.barrier = us.barrier;
+    int32_t max_rows = 1;
+    for (int s = 0; s < n_segs; s++) { P.eta[s] = eta[s]; P.adam_alpha[s] = adam_alpha[s]; P.rows[s] = rows[s]; max_rows = std::max(max_rows, rows[s]); }
+    // enough warps for two rows each in the forward pass, enough CTAs for a tile each in the update, no more than fit
+    const int64_t want = std::max<int64_t>(((int64_t)max_rows + 15) / 16, (max_mb_elems + kUpdTile - 1) / kUpdTile);
+    const int grid = (int)std::max<int64_t>(1, std::min<int64_t>({want, (int64_t)fit, (int64_t)us.grid, (int64_t)hc.stride > 0 ? (int64_t)hc.stride : (int64_t)fit}));
+    HM_CUDA(cudaMemsetAsync(us.barrier, 0, sizeof(uint32_t), L.stream));
+    void *args[] = {&P};
+    L.begin(K_LIN_UPDATE, 24.0 * (double)nnz_hint);
+    // a cooperative launch: the runtime starts the grid only when all of it is resident, which the barrier needs
+    cudaError_t e = cudaLaunchCooperativeKernel(reinterpret_cast<const void *>(linear_block_kernel), dim3((unsigned)grid),
+                                                dim3(kUpdThreads), args, kDyn, L.stream);
+    L.end(K_LIN_UPDATE);
+    if (e != cudaSuccess) HM_FAIL(HM_ERR_CUDA, "cooperative launch of the block kernel failed: %s", cudaGetErrorString(e));
     HM_CUDA(cudaGetLastError());
     return HM_OK;
 }

@@ -153,7 +153,10 @@ hot_select_kernel(const int64_t *__restrict__ rowptr, int64_t row0, int64_t n_ro
         }
     }
     __syncthreads();
-    const uint32_t threshold = (uint32_t)max(2, rows / 32);
+#ifndef HM_HOT_DIV
+#define HM_HOT_DIV 32
+#endif
+    const uint32_t threshold = (uint32_t)max(2, rows / HM_HOT_DIV);
     for (int q = tid; q < kSelSlots; q += kSelThreads) {
         if (t_key[q] != kHotEmpty && t_cnt[q] >= threshold) {
             const int c = atomicAdd(&s_ncand, 1);
@@ -724,7 +727,7 @@ hm_status opt_in_smem(K kernel, size_t bytes)
 hm_status launch_segmented_sort(Launcher &L, SortScratch &s, const uint32_t *d_feature_block,
                                 const float *d_value_block, const int64_t *d_rowptr, int64_t block_row0,
                                 int64_t block_rows, int32_t mini_batch, int64_t n_elems, int n_segs, int key_bits,
-                                int64_t dims, uint32_t *d_bad, int *out_buf, int ctas_per_sm)
+                                int64_t dims, uint32_t *d_bad, int *out_buf, int ctas_per_sm, std::vector<uint32_t> *seg_off_host)
 {
     // > 48 KB of dynamic shared memory needs opting in, once per device (the attribute is per
     // device; the flags are atomics because learners on different threads may get here together)
@@ -754,6 +757,7 @@ hm_status launch_segmented_sort(Launcher &L, SortScratch &s, const uint32_t *d_f
     rl.rowptr = d_rowptr; rl.block_row0 = block_row0; rl.block_rows = block_rows; rl.mini_batch = mini_batch;
     rl.tile_row0 = s.tile_row0;
     int shift = 0;
+    double sorted_elems = (double)n_elems;     // (an upper bound unless profiling)
     for (int p = 0; p < passes; p++) {
         const int rb = p < wide ? 9 : 8;
         const int rows = n_segs << rb;
@@ -766,7 +770,7 @@ hm_status launch_segmented_sort(Launcher &L, SortScratch &s, const uint32_t *d_f
         const uint32_t *toff = p == 0 ? s.in_tile_off : s.seg_tile_off;
         HM_CUDA(cudaMemsetAsync(s.row_sum, 0, (size_t)rows * sizeof(uint32_t), L.stream));
 #define HM_HIST(RB_, FIRST_)                                                                                            \
-    HM_LAUNCH(L, K_SORT_HIST, 4.0 * (double)n_elems,                                                                     \
+    HM_LAUNCH(L, K_SORT_HIST, 4.0 * (p == 0 ? (double)n_elems : sorted_elems),                                           \
               (sort_hist_kernel<RB_, FIRST_><<<hist_grid, kSortThreads, 0, L.stream>>>(kin, off, toff, n_segs, shift,  \
                                                                                        s.tile_hist, s.row_sum, dims32, s.hot)))
         if (p == 0) { if (rb == 9) HM_HIST(9, true); else HM_HIST(8, true); }
@@ -778,7 +782,15 @@ hm_status launch_segmented_sort(Launcher &L, SortScratch &s, const uint32_t *d_f
         HM_LAUNCH(L, K_SORT_SCAN, 0.0,
                   (scan_tiles_kernel<<<(rows + kSortWarps - 1) / kSortWarps, kSortThreads, 0, L.stream>>>(
                       s.tile_hist, s.row_sum, toff, n_segs, 1 << rb)));
-        const double bytes = p == 0 ? 20.0 * (double)n_elems + 8.0 * (double)block_rows : 24.0 * (double)n_elems;
+        // While profiling, the per-kernel byte counts use the SORTED element count, which only the device knows
+        // (hot and out-of-range elements are gone): read the offsets back once the first scan has run.
+        if (p == 0 && L.profiling && seg_off_host) {
+            seg_off_host->assign((size_t)n_segs + 1, 0u);
+            HM_CUDA(cudaMemcpyAsync(seg_off_host->data(), s.seg_off, (size_t)(n_segs + 1) * sizeof(uint32_t), cudaMemcpyDeviceToHost, L.stream));
+            HM_CUDA(cudaStreamSynchronize(L.stream));
+            sorted_elems = (double)seg_off_host->back();
+        }
+        const double bytes = p == 0 ? 8.0 * (double)n_elems + 8.0 * (double)block_rows + 12.0 * sorted_elems : 24.0 * sorted_elems;
 #define HM_SCATTER(FIRST_, RB_)                                                                                        \
     HM_LAUNCH(L, K_SORT_SCATTER, bytes,                                                                                 \
               (sort_scatter_kernel<FIRST_, RB_><<<grid, kScatThreads, kScatterSmem + (FIRST_ ? kHotSlots * 4 : 0), L.stream>>>( \
