@@ -9,10 +9,11 @@
 //   fm_forward_kernel  warp per row, lanes over factors: S_f = sum_j v_jf x_j accumulated in
 //                      ROW ORDER in fp64 (bit-identical to a sequential loop), y_hat, dloss,
 //                      and the table S32[row][f] the update needs
-//   fm_update_kernel   warp per 1024-element chunk of the feature-sorted mini-batch, lanes over
-//                      factors, elements taken in order: per-feature sums A1, A2, GS_f in fp64;
-//                      finished features wait in a shared-memory list and are stepped 16 at a
-//                      time so their factor-row loads overlap
+//   fm_update_kernel   CTA per 1024-element chunk of the feature-sorted mini-batch, a segmented scan
+//                      like the linear learner's: the segment structure is worked out once, then the
+//                      per-feature fp64 sums A1, A2, GS_f are formed four factors per pass (16-byte
+//                      loads of S rows and factor records) and finished features are stepped from a
+//                      shared-memory list, two entries per thread at a time
 //   fm_merge_kernel    features whose run straddles chunks (hot features): pieces sit in
 //                      consecutive chunks, one warp walks them in order; one extra CTA sums dloss
 //                      for the w0 step
@@ -28,7 +29,6 @@ namespace hm {
 namespace {
 
 constexpr int kFmChunk = 1024;      // sorted elements per warp
-constexpr int kFmBatch = 16;        // elements (and pending feature steps) per inner batch
 constexpr int kFmWarps = 4;         // warps per CTA in update / merge
 
 __device__ __forceinline__ uint32_t fmix32(uint32_t h)
@@ -220,53 +220,29 @@ __device__ __forceinline__ void fm_step(const FmUpdParams &P, float g, float lam
     }
 }
 
-// Step the (up to kFmBatch) finished features waiting in the warp's shared-memory list:
-// all factor rows are requested first, then stepped and stored.  Lane i also steps w of entry i.
+// Step ONE finished feature (the merge kernel's: a feature whose run straddled chunks): its factor row is
+// loaded, stepped and stored by the warp, lanes over factors; lane 0 also steps w.
 template <int NF>
-__device__ __forceinline__ void fm_apply_pending(const FmUpdParams &P, int npend, const FmPieceHdr *ph,
-                                                 const double *pgs, int lane)
+__device__ __forceinline__ void fm_apply_one(const FmUpdParams &P, const FmPieceHdr &h, const double *gs, int lane)
 {
     const int k = P.k;
-    float v[kFmBatch][NF], a[kFmBatch][NF];
+    const uint32_t j = h.key;
+    if (j >= P.dims) return;
 #pragma unroll
-    for (int i = 0; i < kFmBatch; i++)
-        if (i < npend) {
-            const uint32_t j = ph[i].key;
-#pragma unroll
-            for (int q = 0; q < NF; q++) {
-                const int fi = lane + 32 * q;
-                const bool in = fi < k && j < P.dims;
-                v[i][q] = in ? P.vrec[(size_t)j * P.vw + fi] : 0.0f;
-                a[i][q] = (in && P.adagrad) ? P.vrec[(size_t)j * P.vw + k + fi] : 0.0f;
-            }
+    for (int q = 0; q < NF; q++) {
+        const int fi = lane + 32 * q;
+        if (fi < k) {
+            float v = P.vrec[(size_t)j * P.vw + fi];
+            float a = P.adagrad ? P.vrec[(size_t)j * P.vw + k + fi] : 0.0f;
+            const double G = gs[fi] - (double)v * h.a2;
+            fm_step(P, fm_grad(P, G, h.cnt), P.lambda_v, v, a);
+            P.vrec[(size_t)j * P.vw + fi] = v;
+            if (P.adagrad) P.vrec[(size_t)j * P.vw + k + fi] = a;
         }
-    float wv = 0.0f, wa = 0.0f;
-    const bool mine = lane < npend && ph[lane < kFmBatch ? lane : 0].key < P.dims;
-    if (mine) {
-        const uint32_t j = ph[lane].key;
-        wv = P.wrec[(size_t)j * P.ww];
-        if (P.adagrad) wa = P.wrec[(size_t)j * P.ww + 1];
     }
-#pragma unroll
-    for (int i = 0; i < kFmBatch; i++)
-        if (i < npend) {
-            const uint32_t j = ph[i].key;
-            const double a2 = ph[i].a2;
-            const uint32_t cnt = ph[i].cnt;
-#pragma unroll
-            for (int q = 0; q < NF; q++) {
-                const int fi = lane + 32 * q;
-                if (fi < k && j < P.dims) {
-                    const double G = pgs[i * k + fi] - (double)v[i][q] * a2;
-                    fm_step(P, fm_grad(P, G, cnt), P.lambda_v, v[i][q], a[i][q]);
-                    P.vrec[(size_t)j * P.vw + fi] = v[i][q];
-                    if (P.adagrad) P.vrec[(size_t)j * P.vw + k + fi] = a[i][q];
-                }
-            }
-        }
-    if (mine) {
-        const uint32_t j = ph[lane].key;
-        fm_step(P, fm_grad(P, ph[lane].a1, ph[lane].cnt), P.lambda_w, wv, wa);
+    if (lane == 0) {
+        float wv = P.wrec[(size_t)j * P.ww], wa = P.adagrad ? P.wrec[(size_t)j * P.ww + 1] : 0.0f;
+        fm_step(P, fm_grad(P, h.a1, h.cnt), P.lambda_w, wv, wa);
         P.wrec[(size_t)j * P.ww] = wv;
         if (P.adagrad) P.wrec[(size_t)j * P.ww + 1] = wa;
         P.touched[j] = 1;
@@ -702,14 +678,14 @@ __global__ void __launch_bounds__(kFmWarps * 32) fm_merge_kernel(FmUpdParams P)
         }
         j += 4;
     }
-    // one finished feature: reuse the batched step with a list of length 1
+    // one finished feature
     FmPieceHdr *ph = reinterpret_cast<FmPieceHdr *>(m_smem + (size_t)warp * (sizeof(FmPieceHdr) + 256 * sizeof(double)));
     double *pgs = reinterpret_cast<double *>(reinterpret_cast<unsigned char *>(ph) + sizeof(FmPieceHdr));
     if (lane == 0) { ph[0].a1 = a1; ph[0].a2 = a2; ph[0].key = start.key; ph[0].cnt = cnt; }
 #pragma unroll
     for (int q = 0; q < NF; q++) { const int fi = lane + 32 * q; if (fi < k) pgs[fi] = gs[q]; }
     __syncwarp();
-    fm_apply_pending<NF>(P, 1, ph, pgs, lane);
+    fm_apply_one<NF>(P, ph[0], pgs, lane);
 }
 
 __global__ void fm_gather_vif_kernel(const float *__restrict__ vrec, int vw, int k, const int32_t *__restrict__ feature,

@@ -161,7 +161,6 @@ struct UpdateScratch {
     void *boundary = nullptr;     // per-CTA open-segment summaries
     uint32_t *done_counter = nullptr;
     int grid = 0;
-    uint32_t *barrier = nullptr;       // arrival counter of the persistent block kernel
     double *hot_sum = nullptr;         // see HotCols
     uint32_t *hot_cnt = nullptr;
     int hot_stride = 0;
@@ -172,15 +171,6 @@ hm_status launch_linear_update(Launcher &L, const LinearArgs &a, const StepScala
                                const uint32_t *d_sorted_key, const uint2 *d_sorted_pay,
                                const uint32_t *d_seg_off, int seg, int64_t seg_begin, const float *d_dloss,
                                int64_t nnz_hint, const HotCols &hc, int64_t sorted_elems = -1);   // (byte accounting)
-// mid-size mini-batches (not small, <= 2^20 elements): up to 64 consecutive mini-batches of a sorted block
-// trained by one persistent, co-resident grid (forward, grid barrier, reduce + step, grid barrier)
-bool block_kernel_eligible(int32_t mini_batch, int64_t max_mb_elems);
-hm_status launch_linear_block(Launcher &L, const LinearArgs &a, UpdateScratch &us, const int64_t *d_rowptr,
-                              int64_t block_row0, int first_seg, int n_segs, const int32_t *rows, const float *eta,
-                              const float *adam_alpha, const uint32_t *d_feature, const float *d_value,
-                              const float *d_label, float *d_margin, float *d_dloss, uint32_t *d_bad,
-                              const uint32_t *d_sorted_key, const uint2 *d_sorted_pay, const uint32_t *d_seg_off,
-                              int64_t nnz_hint, int64_t max_mb_elems, const HotCols &hc);
 // small mini-batches (<= 1024 rows and <= one update tile of elements): up to 64 consecutive
 // mini-batches of a sorted block trained by one persistent CTA
 bool small_batch_eligible(int32_t mini_batch, int64_t max_mb_elems);

@@ -268,7 +268,6 @@ struct hm_udtf {
     int64_t last_margin_off = 0, last_margin_n = 0;   // last mini-batch's slice of `margin`
     bool device_rows_short = false;  // a process_device call ended on a short mini-batch
     bool hot_enabled = true;         // HM_HOT_FEATURES=0 in the environment sorts every element (A/B measurements)
-    bool block_kernel_enabled = true;   // HM_BLOCK_KERNEL=0: mid-size mini-batches take the two-kernel path (A/B measurements)
     hm_stats stats;
     bool closed = false;
     int64_t model_rows = -1;
@@ -511,25 +510,6 @@ hm_status train_rows(hm_udtf *u, Chunk &c, int64_t row0, int64_t n_rows, const i
                 HM_TRY(launch_linear_small_batches(u->L, a, c.rp(), p.row0, s0, ns, rows, eta, adam, c.ft(), c.vl(), c.lb(),
                                                    u->margin.as<float>(), u->dloss.as<float>(), u->d_bad, ss.key[buf],
                                                    ss.pay[buf], ss.seg_off, mb_abs[p.m0 + s0 + ns] - mb_abs[p.m0 + s0]));
-            }
-        } else if (!u->fm && u->block_kernel_enabled && block_kernel_eligible(B, call_max_mb)) {
-            // mid-size mini-batches: up to 64 per launch of one persistent grid (forward, grid barrier, reduce + step)
-            for (int s0 = 0; s0 < p.n_segs; s0 += 64) {
-                const int ns = std::min(64, p.n_segs - s0);
-                int32_t rows[64]; float eta[64], adam[64];
-                for (int s = 0; s < ns; s++) {
-                    const int64_t mrow0 = p.row0 + (int64_t)(s0 + s) * B;
-                    rows[s] = (int32_t)std::min<int64_t>(B, row0 + n_rows - mrow0);
-                    u->t += 1;
-                    eta[s] = eta_at(u->cfg, u->t);
-                    adam[s] = u->cfg.opt == HM_OPT_ADAM ? adam_alpha_at(u->cfg, eta[s], u->t) : 0.f;
-                    u->stats.mini_batches++;
-                    u->last_margin_off = mrow0 - p.row0;
-                    u->last_margin_n = rows[s];
-                }
-                HM_TRY(launch_linear_block(u->L, a, u->upd, c.rp(), p.row0, s0, ns, rows, eta, adam, c.ft(), c.vl(), c.lb(),
-                                           u->margin.as<float>(), u->dloss.as<float>(), u->d_bad, ss.key[buf], ss.pay[buf],
-                                           ss.seg_off, mb_abs[p.m0 + s0 + ns] - mb_abs[p.m0 + s0], call_max_mb, hc));
             }
         } else
         for (int s = 0; s < p.n_segs; s++) {
@@ -863,7 +843,6 @@ hm_status create_impl(const hm_config &cfg, int device, hm_udtf **out)
     u->device = device;
     std::memset(&u->stats, 0, sizeof(u->stats));
     if (const char *e = std::getenv("HM_HOT_FEATURES")) u->hot_enabled = std::atoi(e) != 0;
-    if (const char *e = std::getenv("HM_BLOCK_KERNEL")) u->block_kernel_enabled = std::atoi(e) != 0;
     hm_status s = [&]() -> hm_status {
         {
             // the training stream's short kernels go first whenever both streams have CTAs to place

@@ -190,8 +190,7 @@ __device__ __forceinline__ void hot_accumulate(HotShared &H, int warp, int lane,
     __syncwarp();
 }
 
-// The block's hot keys into the CTA's direct-mapped table (two barriers).  The keys of a block do not change,
-// so the persistent block kernel does this once per launch.
+// The block's hot keys into the CTA's direct-mapped table (two barriers).
 __device__ __forceinline__ void hot_table_build(HotShared &H, const HotInfo *hot)
 {
     const int tid = threadIdx.x;
@@ -375,9 +374,8 @@ struct BoundaryRecs {
     uint4 *first, *last;   // SegRec as bits, one per CTA
     uint32_t *ticket;
 };
-// What changes from one mini-batch to the next.  Apart from this block an UpdParams is the same for every
-// mini-batch of an ingest block: the persistent block kernel keeps ONE UpdParams in its (constant) kernel
-// parameters and one UpdDyn per mini-batch in shared memory.
+// What changes from one mini-batch to the next; apart from this block an UpdParams is the same for every
+// mini-batch of an ingest block (the small-batch kernel keeps one UpdParams and fills an UpdDyn per mini-batch).
 struct UpdDyn {
     int32_t seg;             // mini-batch of the sorted block
     int32_t n_active;        // CTAs that own tiles (all own at least one unless the mini-batch is empty)
@@ -762,8 +760,7 @@ struct UpdCtaSmem {
 };
 
 // Reduce-by-feature and optimizer step of mini-batch P.seg of a sorted block, as CTA `cta` of P.n_active.
-// RO: nothing this kernel writes is read here through the read-only path (false inside the persistent
-// block kernel, where dloss and the replica change between mini-batches of one launch).
+// RO: nothing the running kernel writes is read here through the read-only path.
 template <bool RO>
 __device__ __forceinline__ void update_segment(const UpdParams &P, const UpdDyn &D, UpdCtaSmem &sm, const int cta)
 {
@@ -882,90 +879,6 @@ __global__ void __launch_bounds__(kUpdThreads, 4) linear_update_kernel(const __g
     update_segment<true>(P, P.dyn, sm, (int)blockIdx.x);
 }
 
-// ---- mid-size mini-batches: one persistent grid per block ------------------------------------
-//
-// Between a few thousand and a few hundred thousand elements per mini-batch the two kernels above are
-// mostly launch latency, prologues and tails (measured at -mini_batch 8192 on Criteo-shaped rows: 33 us
-// per mini-batch for 10 us of work).  This kernel trains up to kBlockSegs consecutive mini-batches of a
-// sorted block in ONE launch of a grid that is resident as a whole: forward of mini-batch s over all
-// warps of the grid, grid barrier, reduce-by-feature + optimizer step of mini-batch s (the same
-// update_segment, CTA i taking the i-th range of tiles; the last one to finish merges the straddling
-// segments) and the hot features' step, grid barrier, s + 1.  Same arithmetic as the two-kernel path;
-// the order of the hot features' sums follows the grid size, as it does there.
-constexpr int kBlockSegs = 64;
-#ifndef HM_BLOCK_MINB
-#define HM_BLOCK_MINB 3
-#endif
-
-struct BlockParams {
-    FwdParams F;             // row0 / n_rows are filled per mini-batch
-    UpdParams U;             // seg / eta / adam_alpha / inv_rows / n_active / fwd_grid are filled per mini-batch
-    int32_t first_seg, n_segs, mini_batch;
-    uint32_t *barrier;       // arrival counter, zero at launch
-    float eta[kBlockSegs], adam_alpha[kBlockSegs];
-    int32_t rows[kBlockSegs];
-};
-
-// Every CTA of the (co-resident) grid arrives; `target` = arrivals expected so far.  The fences make what the
-// CTAs wrote before the barrier visible to every CTA after it.
-__device__ __forceinline__ void grid_barrier(uint32_t *counter, uint32_t target)
-{
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        __threadfence();
-        atomicAdd(counter, 1u);
-        while (*reinterpret_cast<volatile uint32_t *>(counter) < target) { }
-        __threadfence();
-    }
-    __syncthreads();
-}
-
-// (out of line: each phase gets its own register allocation, as in the two kernels it replaces)
-__device__ __noinline__ void block_forward(const FwdParams &F, HotShared &H, bool hot, int warp_first, int warp_stride, int cta)
-{
-    if (hot) {
-        hot_begin<false>(F, H);
-        forward_rows_hot<false>(F, warp_first, warp_stride, H);
-        hot_end(F, H, cta);
-    } else forward_rows<false>(F, warp_first, warp_stride);
-}
-
-
-__global__ void __launch_bounds__(kUpdThreads, HM_BLOCK_MINB) linear_block_kernel(const __grid_constant__ BlockParams P)
-{
-    extern __shared__ __align__(16) unsigned char blk_smem[];
-    UpdCtaSmem &sm = *reinterpret_cast<UpdCtaSmem *>(blk_smem);
-    __shared__ HotShared H;
-    const int G = (int)gridDim.x, cta = (int)blockIdx.x;
-    const bool hot = P.F.hot != nullptr && P.F.hot->count != 0u;
-    if (hot) hot_table_build(H, P.F.hot);
-    const int warp_first = cta * (kUpdThreads / 32) + (threadIdx.x >> 5), warp_stride = G * (kUpdThreads / 32);
-    // the per-mini-batch parameter blocks live in shared memory (a private copy per thread would sit on the stack)
-    __shared__ FwdParams F;
-    __shared__ UpdDyn D;
-    uint32_t target = 0;
-    for (int s = 0; s < P.n_segs; s++) {
-        if (threadIdx.x == 0) {
-            F = P.F;
-            F.row0 = P.F.block_row0 + (int64_t)(P.first_seg + s) * P.mini_batch;
-            F.n_rows = P.rows[s];
-            D.seg = P.first_seg + s; D.eta = P.eta[s]; D.adam_alpha = P.adam_alpha[s];
-            D.inv_rows = 1.0 / (double)P.rows[s];
-            D.fwd_grid = G;
-            const uint32_t n = P.U.seg_off[D.seg + 1] - P.U.seg_off[D.seg];
-            D.n_active = min(G, max((int)((n + kUpdTile - 1) / kUpdTile), 1));
-        }
-        __syncthreads();
-        block_forward(F, H, hot, warp_first, warp_stride, cta);
-        target += (uint32_t)G;
-        grid_barrier(P.barrier, target);      // every row's dloss (and the hot sums) are written
-        if (cta < D.n_active) update_segment<false>(P.U, D, sm, cta);
-        if (hot) for (int part = G - 1 - cta; part < kHotCtas; part += G) hot_features_step(P.U, D, part);
-        target += (uint32_t)G;
-        grid_barrier(P.barrier, target);      // the step is complete before the next forward reads the replica
-    }
-}
-
 // ---- small mini-batches: one persistent CTA ----------------------------------------
 //
 // When a mini-batch is a few hundred rows (-mini_batch 128 is BASELINE.json's configs[0]) two
@@ -974,7 +887,6 @@ __global__ void __launch_bounds__(kUpdThreads, HM_BLOCK_MINB) linear_block_kerne
 // optimizer step of mini-batch s (a single tile, so no piece ever leaves the CTA), barrier, s+1.
 // Same arithmetic, same order as the two-kernel path: the results are bit-identical.
 constexpr int kSmallSegs = 64;
-constexpr int64_t kBlockKernelMaxElems = (int64_t)1 << 20;   // per mini-batch; above that the two-kernel path keeps the GPU full on its own
 
 constexpr int kSmallMaxRows = 1024;                 // rows per mini-batch on this path
 constexpr size_t kSmallModelMax = 128 * 1024;       // a replica up to this size lives in shared memory for the launch
@@ -1223,8 +1135,6 @@ hm_status update_scratch_reserve(UpdateScratch &u)
     HM_CUDA(cudaMalloc(&u.boundary, bytes));
     HM_CUDA(cudaMemset(u.boundary, 0, bytes));
     u.done_counter = reinterpret_cast<uint32_t *>(static_cast<char *>(u.boundary) + (size_t)2 * u.grid * 16);
-    HM_CUDA(cudaMalloc(&u.barrier, sizeof(uint32_t)));
-    HM_CUDA(cudaMemset(u.barrier, 0, sizeof(uint32_t)));
     // gradient sums of the hot features: one double and one count per (feature, forward CTA)
     u.hot_stride = num_sms() * 8;
     HM_CUDA(cudaMalloc(&u.hot_sum, (size_t)kMaxHot * u.hot_stride * sizeof(double)));
@@ -1237,8 +1147,7 @@ hm_status update_scratch_reserve(UpdateScratch &u)
 void update_scratch_free(UpdateScratch &u)
 {
     cudaFree(u.boundary);
-    cudaFree(u.hot_sum); cudaFree(u.hot_cnt); cudaFree(u.barrier);
-    u.barrier = nullptr;
+    cudaFree(u.hot_sum); cudaFree(u.hot_cnt);
     u.boundary = nullptr; u.done_counter = nullptr; u.grid = 0; u.hot_sum = nullptr; u.hot_cnt = nullptr; u.hot_stride = 0;
 }
 
@@ -1317,67 +1226,6 @@ hm_status launch_linear_small_batches(Launcher &L, const LinearArgs &a, const in
         dyn = model_bytes;
     }
     HM_LAUNCH(L, K_LIN_UPDATE, 24.0 * (double)nnz_hint, (linear_small_batch_kernel<<<1, kUpdThreads, dyn, L.stream>>>(P)));
-    HM_CUDA(cudaGetLastError());
-    return HM_OK;
-}
-
-bool block_kernel_eligible(int32_t mini_batch, int64_t max_mb_elems)
-{
-    return !small_batch_eligible(mini_batch, max_mb_elems) && max_mb_elems <= kBlockKernelMaxElems;
-}
-
-hm_status launch_linear_block(Launcher &L, const LinearArgs &a, UpdateScratch &us, const int64_t *d_rowptr,
-                              int64_t block_row0, int first_seg, int n_segs, const int32_t *rows, const float *eta,
-                              const float *adam_alpha, const uint32_t *d_feature, const float *d_value,
-                              const float *d_label, float *d_margin, float *d_dloss, uint32_t *d_bad,
-                              const uint32_t *d_sorted_key, const uint2 *d_sorted_pay, const uint32_t *d_seg_off,
-                              int64_t nnz_hint, int64_t max_mb_elems, const HotCols &hc)
-{
-    if (n_segs < 1 || n_segs > kBlockSegs) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "block launch of %d mini-batches", n_segs);
-    constexpr size_t kDyn = sizeof(UpdCtaSmem);
-    // once per device: opt in to the dynamic shared memory, and how many CTAs fit on the device at once
-    static std::atomic<int> resident[64];
-    int dev = 0;
-    HM_CUDA(cudaGetDevice(&dev));
-    int fit = (dev >= 0 && dev < 64) ? resident[dev].load(std::memory_order_acquire) : 0;
-    if (fit == 0) {
-        HM_CUDA(cudaFuncSetAttribute(linear_block_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kDyn));
-        int per_sm = 0;
-        HM_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, linear_block_kernel, kUpdThreads, kDyn));
-        if (per_sm < 1) HM_FAIL(HM_ERR_CUDA, "the block kernel does not fit on this device");
-        fit = std::min(per_sm, 2) * num_sms();      // at most two per SM: the sort of the next block runs beside it
-        if (dev >= 0 && dev < 64) resident[dev].store(fit, std::memory_order_release);
-    }
-    BlockParams P;
-    std::memset(&P, 0, sizeof(P));
-    P.F.wv = a.wv; P.F.rowptr = d_rowptr; P.F.feature = d_feature; P.F.value = d_value; P.F.label = d_label;
-    P.F.margin = d_margin; P.F.dloss = d_dloss; P.F.block_row0 = block_row0;
-    P.F.task = a.cfg.task; P.F.loss = a.cfg.loss; P.F.train = 1; P.F.dims = (uint32_t)a.cfg.dims; P.F.bad = d_bad;
-    P.F.hot = hc.info; P.F.hot_sum = hc.sum; P.F.hot_cnt = hc.cnt; P.F.hot_stride = hc.stride;
-    P.U.rec = a.rec; P.U.rec_width = a.rec_width; P.U.ftrl_derived = a.wv.ftrl; P.U.touched = nullptr;
-    P.U.skey = d_sorted_key; P.U.spay = d_sorted_pay; P.U.dloss = d_dloss; P.U.seg_off = d_seg_off;
-    P.U.br.first = reinterpret_cast<uint4 *>(us.boundary);
-    P.U.br.last = P.U.br.first + us.grid;
-    P.U.br.ticket = us.done_counter;
-    P.U.dims = (uint32_t)a.cfg.dims; P.U.opt = a.cfg.opt; P.U.reg = a.cfg.reg; P.U.grad_norm = a.cfg.grad_norm;
-    P.U.lambda = a.cfg.lambda; P.U.eps = a.cfg.eps; P.U.rho = a.cfg.rho; P.U.beta1 = a.cfg.beta1; P.U.beta2 = a.cfg.beta2;
-    P.U.alpha = a.cfg.alpha; P.U.beta = a.cfg.beta; P.U.lambda1 = a.cfg.lambda1; P.U.lambda2 = a.cfg.lambda2;
-    P.U.hot = hc.info; P.U.hot_sum = hc.sum; P.U.hot_cnt = hc.cnt; P.U.hot_stride = hc.stride;
-    P.first_seg = first_seg; P.n_segs = n_segs; P.mini_batch = a.cfg.mini_batch;
-    P.barrier = us.barrier;
-    int32_t max_rows = 1;
-    for (int s = 0; s < n_segs; s++) { P.eta[s] = eta[s]; P.adam_alpha[s] = adam_alpha[s]; P.rows[s] = rows[s]; max_rows = std::max(max_rows, rows[s]); }
-    // enough warps for two rows each in the forward pass, enough CTAs for a tile each in the update, no more than fit
-    const int64_t want = std::max<int64_t>(((int64_t)max_rows + 15) / 16, (max_mb_elems + kUpdTile - 1) / kUpdTile);
-    const int grid = (int)std::max<int64_t>(1, std::min<int64_t>({want, (int64_t)fit, (int64_t)us.grid, (int64_t)hc.stride > 0 ? (int64_t)hc.stride : (int64_t)fit}));
-    HM_CUDA(cudaMemsetAsync(us.barrier, 0, sizeof(uint32_t), L.stream));
-    void *args[] = {&P};
-    L.begin(K_LIN_UPDATE, 24.0 * (double)nnz_hint);
-    // a cooperative launch: the runtime starts the grid only when all of it is resident, which the barrier needs
-    cudaError_t e = cudaLaunchCooperativeKernel(reinterpret_cast<const void *>(linear_block_kernel), dim3((unsigned)grid),
-                                                dim3(kUpdThreads), args, kDyn, L.stream);
-    L.end(K_LIN_UPDATE);
-    if (e != cudaSuccess) HM_FAIL(HM_ERR_CUDA, "cooperative launch of the block kernel failed: %s", cudaGetErrorString(e));
     HM_CUDA(cudaGetLastError());
     return HM_OK;
 }
