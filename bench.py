@@ -150,7 +150,7 @@ def parse_args():
     ap.add_argument("--cpu-sample-rows", type=int, default=0, help="0 = sized for ~15 s")
     ap.add_argument("--workload", default="ftrl", choices=sorted(WORKLOADS))
     ap.add_argument("--no-e2e", action="store_true")
-    ap.add_argument("--e2e-format", default="split", choices=["split", "csr", "strings"],
+    ap.add_argument("--e2e-format", default="columns", choices=["columns", "split", "csr", "strings"],
                     help="host format of the end-to-end arm for Criteo-shaped rows")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-sweep", action="store_true", help="skip the mini-batch sweep of the N=1 line")
@@ -536,7 +536,9 @@ def main():
     }
 
     # ---- end-to-end arm: host buffers through the C-ABI --------------------------------
-    # Formats: "csr" = hm_udtf_process with a value per element; "index_only" = hm_udtf_process(value = NULL)
+    # Formats: "columns" = hm_udtf_process_columns for Criteo-shaped rows (the 13 quantitative indices given once,
+    # a [rows][13] value matrix and a [rows][26] index matrix: no repeated index, no implied 1.0, no row pointer
+    # on the bus); "csr" = hm_udtf_process with a value per element; "index_only" = hm_udtf_process(value = NULL)
     # for rows whose values are all 1.0 (KDD12-shaped); "split" = hm_udtf_process_split for Criteo-shaped rows
     # (13 quantitative columns with values + 26 index-only columns), merged on the device: the same rows in
     # the same element order, without the implied 1.0s on the bus; "strings" = hm_udtf_process_strings, rows as a
@@ -579,7 +581,10 @@ def main():
         host, addrs = [], []
         for b in range(n_host):
             rowptr, feature, value, label = blocks[b]
-            if fmt == "split":
+            if fmt == "columns":
+                f2, v2 = feature.view(rps, nnz_per_row), value.view(rps, nnz_per_row)
+                parts = [f2[0, :n_q].contiguous(), v2[:, :n_q].contiguous().view(-1), f2[:, n_q:].contiguous().view(-1), label]
+            elif fmt == "split":
                 f2, v2 = feature.view(rps, nnz_per_row), value.view(rps, nnz_per_row)
                 steps = torch.arange(rps + 1, device=dev, dtype=torch.int64)
                 parts = [steps * n_q, f2[:, :n_q].contiguous().view(-1), v2[:, :n_q].contiguous().view(-1),
@@ -613,7 +618,9 @@ def main():
         def step_host(i):
             arrs = host[i % n_host]
             lbt = arrs[-1][1]
-            if fmt == "split":
+            if fmt == "columns":
+                v.process_columns_pointers(rows_step, n_q, arrs[0][0], arrs[1][0], nnz_per_row - n_q, arrs[2][0], arrs[3][0])
+            elif fmt == "split":
                 v.process_split_pointers(rows_step, *[a for a, _ in arrs])
             elif fmt == "index_only":
                 v.process_pointers(rows_step, arrs[0][0], arrs[1][0], None, arrs[2][0])
@@ -641,7 +648,9 @@ def main():
             tdt = torch.tensor([dt], device=dev)
             dist.all_reduce(tdt, op=dist.ReduceOp.MAX)
             dt = float(tdt)
-        if fmt == "split":
+        if fmt == "columns":
+            h2d = n_q * 4 + rps * n_q * 4 + rps * (nnz_per_row - n_q) * 4 + rps * 4
+        elif fmt == "split":
             h2d = 2 * (rps + 1) * 8 + rps * n_q * 8 + rps * (nnz_per_row - n_q) * 4 + rps * 4
         elif fmt == "strings":
             h2d = sum(t.numel() * t.element_size() for _, t in host[0])
@@ -653,7 +662,9 @@ def main():
         return {"value": world * rows_step * K / dt, "ms_per_step": dt / K * 1e3, "h2d_bytes_per_step": h2d,
                 "pcie_GBps": h2d * K / dt / 1e9, "last_minibatch_loss": losses[-1], "rows_per_step": rows_step}
 
-    FORMATS = {"split": "hm_udtf_process_split: 13 quantitative columns (index, value) + 26 index-only "
+    FORMATS = {"columns": "hm_udtf_process_columns: the 13 quantitative indices once, a [rows][13] value matrix, a [rows][26] "
+                          "index matrix; expanded into CSR on the device (160 bytes per row on the bus)",
+               "split": "hm_udtf_process_split: 13 quantitative columns (index, value) + 26 index-only "
                         "columns per row, merged on the device (the implied 1.0s stay off the bus)",
                "index_only": "hm_udtf_process with value = NULL (every value is 1.0)",
                "csr": "hm_udtf_process: plain CSR, one f32 value per element",
@@ -663,7 +674,7 @@ def main():
     if not args.no_e2e:
         fmt = args.e2e_format
         if fmt != "strings":
-            fmt = "index_only" if wl["gen"] == "kdd12" else ("csr" if fmt == "csr" else "split")
+            fmt = "index_only" if wl["gen"] == "kdd12" else fmt
         first = run_e2e(fmt)
         e2e = {"value": first["value"], "unit": "examples/s", "h2d_bytes_per_step": first["h2d_bytes_per_step"],
                "d2h_bytes_per_step": mb * 4, "ms_per_step": first["ms_per_step"],
@@ -674,7 +685,10 @@ def main():
                "host_binding": (f"rank bound to {len(host_cpus)} CPUs next to its GPU (NVML affinity)" if host_cpus
                                 else "none"),
                "format": FORMATS[fmt]}
-        if fmt == "split":      # the same rows as plain CSR, and (one GPU) as strings, for comparison
+        if fmt == "columns":      # the same rows in the other host formats, for comparison
+            sp = run_e2e("split")
+            e2e["split"] = {"value": sp["value"], "ms_per_step": sp["ms_per_step"], "h2d_bytes_per_step": sp["h2d_bytes_per_step"],
+                            "pcie_GBps": sp["pcie_GBps"], "last_minibatch_loss": sp["last_minibatch_loss"], "format": FORMATS["split"]}
             plain = run_e2e("csr")
             e2e["plain_csr"] = {"value": plain["value"], "ms_per_step": plain["ms_per_step"],
                                 "h2d_bytes_per_step": plain["h2d_bytes_per_step"], "pcie_GBps": plain["pcie_GBps"],

@@ -66,6 +66,7 @@ SIGNATURES = {
     "hm_udtf_create_from_config": (C.c_int, [C.POINTER(HmConfig), C.c_int, C.POINTER(_P)]),
     "hm_udtf_process": (C.c_int, [_P, C.c_int64, _P, _P, _P, _P]),
     "hm_udtf_process_split": (C.c_int, [_P, C.c_int64, _P, _P, _P, _P, _P, _P]),
+    "hm_udtf_process_columns": (C.c_int, [_P, C.c_int64, C.c_int32, _P, _P, C.c_int32, _P, _P]),
     "hm_udtf_process_strings": (C.c_int, [_P, C.c_int64, _P, _P, _P, _P]),
     "hm_udtf_process_device": (C.c_int, [_P, C.c_int64, C.c_int64, _P, _P, _P, _P]),
     "hm_udtf_close": (C.c_int, [_P, C.POINTER(C.c_int64)]),

@@ -161,6 +161,12 @@ struct HostRows {
     const int64_t *rowptr = nullptr; const int32_t *feature = nullptr; const float *value = nullptr;
     bool strings = false;
     const uint8_t *s_bytes = nullptr; const int64_t *s_offsets = nullptr;
+    // columns: every row = n_q quantitative features whose indices are the same in every row (q_cols[n_q], given
+    // once) with a value each (cq_value[n][n_q]), then n_c index-only features (cc_feature[n][n_c]); no row pointer
+    bool columns = false;
+    int32_t n_q = 0, n_c = 0;
+    const int32_t *q_cols = nullptr, *cc_feature = nullptr;
+    const float *cq_value = nullptr;
     bool split = false;
     const int64_t *q_rowptr = nullptr, *c_rowptr = nullptr;
     const int32_t *q_feature = nullptr, *c_feature = nullptr;
@@ -168,6 +174,7 @@ struct HostRows {
     const float *label = nullptr;
     int64_t nnz() const
     {
+        if (columns) return n * (int64_t)(n_q + n_c);
         return split ? (q_rowptr[n] - q_rowptr[0]) + (c_rowptr[n] - c_rowptr[0]) : rowptr[n] - rowptr[0];
     }
     int64_t row_end(int64_t i) const   // elements before row i, relative to the slice
@@ -199,6 +206,25 @@ merge_split_kernel(int64_t n, const int64_t *__restrict__ q_rp, int64_t q_base, 
             if (row == n - 1) out_rp[n] = out_base + q1 + c1;
         }
     }
+}
+
+// Column rows -> one CSR on the device: element e of the slice belongs to row e / (n_q + n_c); the first n_q
+// elements of a row take their index from q_cols and their value from the value matrix, the others are
+// index-only (value 1.0).  Fully regular: a thread per element, every access coalesced.
+__global__ void __launch_bounds__(256)
+expand_columns_kernel(int64_t n, int32_t n_q, int32_t n_c, const uint32_t *__restrict__ q_cols,
+                      const float *__restrict__ q_val, const uint32_t *__restrict__ c_feat, int64_t out_base,
+                      int64_t *__restrict__ out_rp, uint32_t *__restrict__ out_feat, float *__restrict__ out_val)
+{
+    const int64_t per = (int64_t)n_q + n_c, total = n * per;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += stride) {
+        const int64_t row = e / per;
+        const int32_t j = (int32_t)(e - row * per);
+        if (j < n_q) { out_feat[out_base + e] = q_cols[j]; out_val[out_base + e] = q_val[row * n_q + j]; }
+        else { out_feat[out_base + e] = c_feat[row * n_c + (j - n_q)]; out_val[out_base + e] = 1.0f; }
+    }
+    for (int64_t row = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; row <= n; row += stride) out_rp[row] = out_base + row * per;
 }
 
 __global__ void gather_rowptr_kernel(const int64_t *__restrict__ rowptr, int64_t n_rows, int32_t step,
@@ -642,6 +668,16 @@ hm_status process_slice(hm_udtf *u, const HostRows &h)
             if (str_nbytes) HM_CUDA(cudaMemcpyAsync(c->str_bytes.p, h.s_bytes + str_b0, (size_t)str_nbytes, cudaMemcpyHostToDevice, u->copy));
             HM_CUDA(cudaMemcpyAsync(c->str_off.p, h.s_offsets + s0, (size_t)(nnz + 1) * 8, cudaMemcpyHostToDevice, u->copy));
         }
+    } else if (h.columns) {
+        const int64_t hr = std::max(n, u->hint_rows);
+        HM_TRY(c->sq_feat.reserve((size_t)std::max<int32_t>(h.n_q, 1) * 4));
+        HM_TRY(c->sq_val.reserve((size_t)std::max<int64_t>(hr * h.n_q, 1) * 4));
+        HM_TRY(c->sc_feat.reserve((size_t)std::max<int64_t>(hr * h.n_c, 1) * 4));
+        if (h.n_q) {
+            HM_CUDA(cudaMemcpyAsync(c->sq_feat.p, h.q_cols, (size_t)h.n_q * 4, cudaMemcpyHostToDevice, u->copy));
+            HM_CUDA(cudaMemcpyAsync(c->sq_val.p, h.cq_value, (size_t)n * h.n_q * 4, cudaMemcpyHostToDevice, u->copy));
+        }
+        if (h.n_c) HM_CUDA(cudaMemcpyAsync(c->sc_feat.p, h.cc_feature, (size_t)n * h.n_c * 4, cudaMemcpyHostToDevice, u->copy));
     } else if (!h.split) {
         const int64_t base = h.rowptr[0];
         if (nnz) {
@@ -683,7 +719,12 @@ hm_status process_slice(hm_udtf *u, const HostRows &h)
     }
     int64_t *st = u->h_stage[turn];
     for (int64_t i = 0; i < t_rows; i++) st[i] = u->tail_rp[i];
-    if (!h.split) {
+    const int64_t per_row = (int64_t)h.n_q + h.n_c;
+    // element position of row i of [tail | slice] (column rows need no table for their own part)
+    auto st_at = [&](int64_t i) -> int64_t { return (h.columns && i >= t_rows) ? t_nnz + (i - t_rows) * per_row : st[i]; };
+    if (h.columns) {
+        // (nothing to rebase: the row pointer of the new rows is implied and written on the device)
+    } else if (!h.split) {
         const int64_t base = h.rowptr[0];
         for (int64_t i = 0; i <= n; i++) {
             if (i > 0 && h.rowptr[i] < h.rowptr[i - 1]) {
@@ -723,7 +764,7 @@ hm_status process_slice(hm_udtf *u, const HostRows &h)
     }
     // the row pointer last: it is the only copy that needs the host loop above (split rows: the merge
     // kernel has written the new rows' part, only the carried rows' part is copied)
-    const int64_t rp_copy = h.split ? t_rows : rows + 1;
+    const int64_t rp_copy = (h.split || h.columns) ? t_rows : rows + 1;
     if (rp_copy) HM_CUDA(cudaMemcpyAsync(c->rowptr.p, st, (size_t)rp_copy * 8, cudaMemcpyHostToDevice, u->copy));
     if (!u->stage_ev[turn]) HM_CUDA(cudaEventCreateWithFlags(&u->stage_ev[turn], cudaEventDisableTiming));
     HM_CUDA(cudaEventRecord(u->stage_ev[turn], u->copy));
@@ -743,6 +784,17 @@ hm_status process_slice(hm_udtf *u, const HostRows &h)
         HM_CUDA(cudaEventRecord(u->merged_ev, u->sorter));
         HM_CUDA(cudaStreamWaitEvent(u->compute, u->merged_ev, 0));
     }
+    if (h.columns) {
+        const int grid = (int)std::min<int64_t>((nnz + 1023) / 1024 + 1, (int64_t)num_sms() * 8);
+        expand_columns_kernel<<<grid, 256, 0, u->sorter>>>(n, h.n_q, h.n_c, c->sq_feat.as<uint32_t>(), c->sq_val.as<float>(),
+                                                          c->sc_feat.as<uint32_t>(), t_nnz, c->rowptr.as<int64_t>() + t_rows,
+                                                          c->feat.as<uint32_t>(), c->val.as<float>());
+        u->Ls.launches++;
+        HM_CUDA(cudaGetLastError());
+        if (!u->merged_ev) HM_CUDA(cudaEventCreateWithFlags(&u->merged_ev, cudaEventDisableTiming));
+        HM_CUDA(cudaEventRecord(u->merged_ev, u->sorter));
+        HM_CUDA(cudaStreamWaitEvent(u->compute, u->merged_ev, 0));
+    }
     if (h.strings && nnz) {
         // feature strings -> the chunk's feature / value arrays, on the sort stream (their first consumer);
         // training waits for it too.  The kernel takes absolute offsets: the byte buffer is passed shifted.
@@ -753,7 +805,8 @@ hm_status process_slice(hm_udtf *u, const HostRows &h)
         HM_CUDA(cudaEventRecord(u->merged_ev, u->sorter));
         HM_CUDA(cudaStreamWaitEvent(u->compute, u->merged_ev, 0));
     }
-    if (h.strings) u->stats.h2d_bytes += (rows + 1) * 8 + str_nbytes + (nnz + 1) * 8 + n * 4;
+    if (h.columns) u->stats.h2d_bytes += n * (per_row * 4 + 4) + (int64_t)h.n_q * 4 + t_rows * 8;
+    else if (h.strings) u->stats.h2d_bytes += (rows + 1) * 8 + str_nbytes + (nnz + 1) * 8 + n * 4;
     else if (!h.split) u->stats.h2d_bytes += (rows + 1) * 8 + nnz * (h.value ? 8 : 4) + n * 4;
     else u->stats.h2d_bytes += (n + 1) * 16 + (h.q_rowptr[n] - h.q_rowptr[0]) * 8 + (h.c_rowptr[n] - h.c_rowptr[0]) * 4 + n * 4 + t_rows * 8;
 
@@ -762,14 +815,14 @@ hm_status process_slice(hm_udtf *u, const HostRows &h)
     const int64_t train = n_mb * B;
     c->rows = train;
     c->mb_abs.resize((size_t)n_mb + 1);
-    for (int64_t i = 0; i <= n_mb; i++) c->mb_abs[(size_t)i] = st[i * B];
+    for (int64_t i = 0; i <= n_mb; i++) c->mb_abs[(size_t)i] = st_at(i * B);
     HM_TRY(train_rows(u, *c, 0, train, c->mb_abs.data(), n_mb, true, u->cfg.iters > 1 ? kTrainKeep : kTrainPlain));
 
     // what is left waits in this chunk
     u->tail = c;
     u->tail_row0 = train;
     u->tail_rp.resize((size_t)(rows - train) + 1);
-    for (int64_t i = 0; i <= rows - train; i++) u->tail_rp[(size_t)i] = st[train + i] - st[train];
+    for (int64_t i = 0; i <= rows - train; i++) u->tail_rp[(size_t)i] = st_at(train + i) - st_at(train);
     if (rows == train) u->tail_rp.clear();
     return HM_OK;
 }
@@ -783,7 +836,7 @@ hm_status process_host_rows(hm_udtf *u, const HostRows &all)
     // (split rows arrive as more, smaller arrays: twice the rows per slice keep the copies long -- for the
     // linear learners, where the bus is the bottleneck; train_fm trains about as fast as the bus delivers and
     // wants the shorter slices that keep copy and training in step: measured 131 M vs 141 M examples/s)
-    const int64_t largest = std::max<int64_t>((all.split && !u->fm ? 2 * kSliceRows : kSliceRows) / B * B, smallest);
+    const int64_t largest = std::max<int64_t>(((all.split || all.columns) && !u->fm ? 2 * kSliceRows : kSliceRows) / B * B, smallest);
     int64_t ramp = smallest;
     {
         const int64_t big = std::min(n_rows, largest);
@@ -800,7 +853,8 @@ hm_status process_host_rows(hm_udtf *u, const HostRows &all)
         while (slice > smallest && n_rows - r <= 2 * slice) slice = std::max<int64_t>((slice / 2) / B * B, smallest);
         HostRows h = all;
         h.n = std::min(slice, n_rows - r);
-        if (all.split) { h.q_rowptr = all.q_rowptr + r; h.c_rowptr = all.c_rowptr + r; }
+        if (all.columns) { h.cq_value = all.cq_value + r * all.n_q; h.cc_feature = all.cc_feature + r * all.n_c; }
+        else if (all.split) { h.q_rowptr = all.q_rowptr + r; h.c_rowptr = all.c_rowptr + r; }
         else h.rowptr = all.rowptr + r;
         h.label = all.label + r;
         st = process_slice(u, h);
@@ -1049,6 +1103,23 @@ hm_status hm_udtf_process_split(hm_udtf *u, int64_t n_rows, const int64_t *q_row
     all.n = n_rows; all.split = true;
     all.q_rowptr = q_rowptr; all.q_feature = q_feature; all.q_value = q_value;
     all.c_rowptr = c_rowptr; all.c_feature = c_feature; all.label = label;
+    return process_host_rows(u, all);
+}
+
+hm_status hm_udtf_process_columns(hm_udtf *u, int64_t n_rows, int32_t n_q, const int32_t *q_feature, const float *q_value,
+                                  int32_t n_c, const int32_t *c_feature, const float *label)
+{
+    if (!u) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "NULL learner");
+    if (u->closed) HM_FAIL(HM_ERR_STATE, "process() after close()");
+    if (u->device_rows_short) HM_FAIL(HM_ERR_STATE, "process() after a device call that ended on a short mini-batch");
+    if (n_rows < 0 || n_q < 0 || n_c < 0 || (n_rows > 0 && !label)) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "bad arguments to process_columns()");
+    if (n_rows > 0 && ((n_q > 0 && (!q_feature || !q_value)) || (n_c > 0 && !c_feature)))
+        HM_FAIL(HM_ERR_INVALID_ARGUMENT, "NULL buffer passed to process_columns()");
+    if (n_rows == 0) return HM_OK;
+    DeviceGuard g(u->device);
+    HostRows all;
+    all.n = n_rows; all.columns = true; all.n_q = n_q; all.n_c = n_c;
+    all.q_cols = q_feature; all.cq_value = q_value; all.cc_feature = c_feature; all.label = label;
     return process_host_rows(u, all);
 }
 

@@ -229,6 +229,25 @@ class UDTF:
         check(self._lib.hm_udtf_process_split(self._h, n_rows, _ptr(q_rowptr), _ptr(q_feature), _ptr(q_value),
                                               _ptr(c_rowptr), _ptr(c_feature), _ptr(label)))
 
+    def process_columns(self, q_feature, q_value, c_feature, label) -> None:
+        """process() of many rows = a quantitative block whose n_q indices are the same in every row (`q_feature`,
+        given once; `q_value` is the (rows, n_q) matrix) followed by n_c index-only features per row (`c_feature`,
+        (rows, n_c)).  Asynchronous like process_batch."""
+        q_feature = np.ascontiguousarray(q_feature, dtype=np.int32).reshape(-1)
+        label = np.ascontiguousarray(label, dtype=np.float32)
+        n = len(label)
+        q_value = np.ascontiguousarray(q_value, dtype=np.float32).reshape(n, len(q_feature))
+        c_feature = np.ascontiguousarray(c_feature, dtype=np.int32).reshape(n, -1)
+        self._keep.append((q_feature, q_value, c_feature, label))
+        check(self._lib.hm_udtf_process_columns(self._h, n, len(q_feature), _ptr(q_feature), _ptr(q_value),
+                                                c_feature.shape[1], _ptr(c_feature), _ptr(label)))
+
+    def process_columns_pointers(self, n_rows: int, n_q: int, q_feature: int, q_value: int, n_c: int, c_feature: int,
+                                 label: int) -> None:
+        """process_columns() from raw HOST addresses (pinned buffers from host_alloc)."""
+        check(self._lib.hm_udtf_process_columns(self._h, n_rows, n_q, _ptr(q_feature), _ptr(q_value), n_c,
+                                                _ptr(c_feature), _ptr(label)))
+
     def process_strings(self, rowptr, data, offsets, label) -> None:
         """process() of many rows whose features are still strings ("name:value" / "name"): int64 rowptr
         over strings, uint8 `data` holding the strings back to back, int64 offsets (len = strings + 1).

@@ -154,6 +154,18 @@ hm_status hm_udtf_process(hm_udtf *u, int64_t n_rows, const int64_t *rowptr,
 hm_status hm_udtf_process_split(hm_udtf *u, int64_t n_rows,
                                 const int64_t *q_rowptr, const int32_t *q_feature, const float *q_value,
                                 const int64_t *c_rowptr, const int32_t *c_feature, const float *label);
+/* process() for rows whose quantitative features are the same n_q indices in every row -- what
+ * quantitative_features(array("age", "height", ...), age, height, ...) produces: fixed names, one value
+ * each -- followed by n_c index-only features (categorical_features: one per field).  The indices of
+ * the quantitative block are given ONCE (q_feature[n_q]); q_value is the row-major matrix
+ * [n_rows][n_q], c_feature the row-major matrix [n_rows][n_c].  Row i = (q_feature[j], q_value[i][j])
+ * for j < n_q, then (c_feature[i][k], 1.0) for k < n_c.  Neither the repeated indices nor the implied
+ * 1.0s nor a row pointer cross the bus (Criteo-shaped rows: 160 instead of 228 bytes per row), and
+ * the rows are expanded into the learner's CSR on the device.  Otherwise exactly hm_udtf_process
+ * (same mini-batch boundaries, same result as pushing the expanded rows). */
+hm_status hm_udtf_process_columns(hm_udtf *u, int64_t n_rows, int32_t n_q, const int32_t *q_feature,
+                                  const float *q_value, int32_t n_c, const int32_t *c_feature,
+                                  const float *label);
 /* process() for rows whose features are still strings ("name:value"); hashes on
  * the GPU with the learner's hash_seed into [0, dims) and then behaves as above.
  * rowptr indexes strings; string s is bytes[offsets[s] .. offsets[s+1]). */

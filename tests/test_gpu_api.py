@@ -199,3 +199,35 @@ def test_predict_reports_out_of_range_indices_itself():
     assert np.isfinite(m).all()
     assert u.close() > 0
     u.destroy()
+
+
+@pytest.mark.parametrize("fn,opts", [
+    ("train_classifier", f"-opt ftrl -mini_batch 4096 -dims {1 << 18}"),
+    ("train_classifier", f"-opt adagrad -mini_batch 300 -dims {1 << 18} -iters 2"),
+    ("train_fm", f"-factors 8 -classification -opt adagrad -mini_batch 1000 -dims {1 << 18}"),
+])
+def test_column_rows_equal_expanded_rows(fn, opts):
+    """hm_udtf_process_columns: a quantitative block whose indices are given once + index-only columns, expanded on
+    the device == the same rows as plain CSR through hm_udtf_process, bit for bit; pushes of column rows and of
+    CSR rows may alternate (the carried tail keeps its own row pointer), several H2D slices included."""
+    n = 300_000 if "4096" in opts else 20_000
+    data = synth.criteo_like(n, dims=1 << 18, seed=13)
+    rp, f, v, y = data.numpy()
+    f2, v2 = f.reshape(n, 39), v.reshape(n, 39)
+    assert (f2[:, :13] == f2[0, :13]).all() and (v2[:, 13:] == 1.0).all()
+    a = hm.UDTF(opts, 0, function_name=fn)
+    a.process_batch(rp, f, v, y)
+    a.close()
+    b = hm.UDTF(opts, 0, function_name=fn)
+    cuts = [0, 777, 778, n // 2 + 5, n]
+    for i, (lo, hi) in enumerate(zip(cuts, cuts[1:])):
+        if i == 1:      # one push as plain CSR in between
+            b.process_batch(rp[lo:hi + 1], f, v, y[lo:hi])
+        else:
+            b.process_columns(f2[0, :13], v2[lo:hi, :13], f2[lo:hi, 13:], y[lo:hi])
+    b.close()
+    assert a.step == b.step
+    for name in (("w", "state") if fn != "train_fm" else ("w0", "w", "V", "gV")):
+        assert np.array_equal(a.array_to_host(name), b.array_to_host(name)), name
+    assert b.stats().h2d_bytes < 0.6 * a.stats().h2d_bytes
+    a.destroy(); b.destroy()
