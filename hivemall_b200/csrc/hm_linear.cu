@@ -190,28 +190,22 @@ __device__ __forceinline__ void hot_accumulate(HotShared &H, int warp, int lane,
     __syncwarp();
 }
 
-// The block's hot keys into the CTA's direct-mapped table (two barriers).
-__device__ __forceinline__ void hot_table_build(HotShared &H, const HotInfo *hot)
-{
-    const int tid = threadIdx.x;
-    for (int q = tid; q < kHotSlots; q += kFwdThreads) H.tab_key[q] = kHotNone;
-    __syncthreads();
-    if (tid < (int)hot->count) {
-        const uint32_t h = hot_index(hot->key[tid]);     // (pairwise different for the keys of a HotInfo)
-        H.tab_key[h] = hot->key[tid];
-        H.tab_slot[h] = (uint8_t)tid;
-    }
-    __syncthreads();
-}
-
-// Before the forward pass of a mini-batch: the hot features' current weights, cleared accumulators (one barrier).
+// Before the forward pass of a mini-batch: the block's hot keys into the CTA's direct-mapped table, their
+// current weights, cleared accumulators.  Two barriers and two dependent round trips (count and key are
+// loaded side by side; the weight gather needs the key).
 template <bool RO>
-__device__ __forceinline__ void hot_begin(const FwdParams &P, HotShared &H)
+__device__ __forceinline__ void hot_prologue(const FwdParams &P, HotShared &H)
 {
     const int tid = threadIdx.x;
+    const uint32_t n = P.hot->count;
+    const uint32_t key = tid < kMaxHot ? P.hot->key[tid] : 0u;
+    for (int q = tid; q < kHotSlots; q += kFwdThreads) H.tab_key[q] = kHotNone;
     for (int q = tid; q < (kFwdThreads / 32) * kMaxHot; q += kFwdThreads) { (&H.acc[0][0])[q] = 0.0; (&H.cnt[0][0])[q] = 0u; }
-    if (tid < (int)P.hot->count) {
-        const uint32_t key = P.hot->key[tid];
+    __syncthreads();
+    if (tid < (int)n) {
+        const uint32_t h = hot_index(key);     // (pairwise different for the keys of a HotInfo)
+        H.tab_key[h] = key;
+        H.tab_slot[h] = (uint8_t)tid;
         H.w[tid] = key < P.dims ? weight_at<RO>(P.wv, key) : 0.0f;
     }
     __syncthreads();
@@ -345,8 +339,7 @@ __global__ void __launch_bounds__(kFwdThreads, 8) linear_forward_kernel(FwdParam
     __shared__ HotShared H;
     const int warp_first = blockIdx.x * (kFwdThreads / 32) + (threadIdx.x >> 5), warp_stride = gridDim.x * (kFwdThreads / 32);
     if (P.hot && P.hot->count != 0u) {
-        hot_table_build(H, P.hot);
-        hot_begin<true>(P, H);
+        hot_prologue<true>(P, H);
         forward_rows_hot<true>(P, warp_first, warp_stride, H);
         hot_end(P, H, (int)blockIdx.x);
     } else forward_rows<true>(P, warp_first, warp_stride);
