@@ -532,11 +532,13 @@ sort_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint2 *__restric
             const uint32_t d = (key[i] >> shift) & (R - 1);
             const uint32_t active = __ballot_sync(0xffffffffu, valid);
             uint32_t peers = 0, prev = 0;
-            if (FIRST) {
+            if (FIRST && n_hot == 0u) {
                 // match.any costs time in proportion to the number of distinct values in the warp.  In the
                 // first pass the elements are still in row order (32 consecutive elements = 32 different
                 // hashed features): one ballot per digit bit -- lanes that agree with mine in every bit -- is
-                // cheaper there.  Later passes see long runs of equal digits and keep match.any.
+                // cheaper there.  Later passes see long runs of equal digits and keep match.any -- and so does
+                // the first pass of a block with hot features: half of its lanes are dropped before the
+                // ranking, which halves what match.any costs (measured: 134 -> 128 us per launch on average).
                 peers = active;
 #pragma unroll
                 for (int b = 0; b < RB; b++) {
