@@ -1,8 +1,8 @@
-"""BASELINE.json-sized runs (2^24 hashed dims, -mini_batch 65536, Criteo-shaped rows) checked
-through size-independent properties, since the CPU oracle would take too long at this size:
-determinism, host path == device path bit for bit, model-table order, a conserved quantity of
-the update rule, and that training actually reduces the loss.  A slice small enough for the
-oracle is still compared directly."""
+"""BASELINE.json-sized runs (2^24 / 2^26 hashed dims, -mini_batch 65536, Criteo- and KDD12-shaped rows):
+size-independent properties (determinism, host path == device path bit for bit, model-table order, a
+conserved quantity of the update rule, training reduces the loss) AND the oracle itself on the same rows --
+all 32 mini-batches of the configs[1] run, the configs[3] run (Adam, 2^26 dims), and two mini-batches of
+train_fm at the configs[2] (k = 16, Criteo-shaped) and configs[4] (k = 64, KDD12-shaped) sizes."""
 import numpy as np
 import pytest
 
@@ -62,20 +62,20 @@ def test_config1_shape_properties():
     m = torch.from_numpy(a.predict(rp, f, v))
     assert synth.logloss(m, torch.from_numpy(y)) < 0.68
     assert synth.auc(m, torch.from_numpy(y)) > 0.6
-    # (5) the first 3 mini-batches against the oracle directly
-    k = 3 * MB
-    c = hm.train_classifier(opts)
-    c.process_batch(host[0][:k + 1], host[1], host[2], host[3][:k])
-    c.close()
+    # (5) the whole run -- all 32 mini-batches, hot features and all -- against the oracle
+    import os
     ref = _oracle.train_linear_mt(_oracle.config_from(hm.parse_options("train_classifier", opts)),
-                                  host[0][:k + 1], host[1], host[2], host[3][:k], 8)
-    assert_weights_close(c.array_to_host("w"), ref.w)
-    for u in (a, b, c):
+                                  host[0], host[1], host[2], host[3], min(16, os.cpu_count() or 1))
+    assert ref.t == 32
+    assert_weights_close(wa, ref.w)
+    assert_weights_close(a.array_to_host("state"), ref.state(2), "state")
+    for u in (a, b):
         u.destroy()
 
 
 def test_config3_shape_adam_2pow26_dims():
-    """configs[3] shape on one GPU: squared loss + Adam, 2^26 dims (1 GiB replica), rerun identical."""
+    """configs[3] shape on one GPU: squared loss + Adam, 2^26 dims (1 GiB replica): rerun identical, and the
+    oracle on the same 8 mini-batches."""
     n = 8 * MB
     import torch
     data = synth.criteo_like(n, dims=1 << 26, seed=3, device="cuda", regression=True)
@@ -91,3 +91,36 @@ def test_config3_shape_adam_2pow26_dims():
         u.destroy()
     assert np.array_equal(ws[0][0], ws[1][0]) and np.array_equal(ws[0][1], ws[1][1])
     torch.cuda.synchronize()
+    import os
+    rp, f, v, y = data.numpy()
+    ref = _oracle.train_linear_mt(_oracle.config_from(hm.parse_options("train_regressor", opts)), rp, f, v, y,
+                                  min(16, os.cpu_count() or 1))
+    ofeat, owt = _oracle.model_table(ref.w)
+    assert np.array_equal(ws[0][0], ofeat)                 # the same features carry a weight, in the same order
+    assert_weights_close(ws[0][1], owt, "model table weights")
+
+
+@pytest.mark.parametrize("gen,k,nnz", [("criteo", 16, 39), ("kdd12", 64, 11)])
+def test_train_fm_at_baseline_dims(gen, k, nnz):
+    """configs[2] / configs[4] shapes: train_fm AdaGrad at 2^24 dims, -mini_batch 65536, two mini-batches against
+    the (scalar) oracle: w0, w, V and their accumulators on every feature the rows touch."""
+    n = 2 * MB
+    data = (synth.criteo_like(n, dims=DIMS, seed=2) if gen == "criteo" else synth.kdd12_like(n, dims=DIMS, seed=4))
+    rp, f, v, y = data.numpy()
+    opts = f"-factors {k} -classification -opt adagrad -mini_batch {MB} -dims {DIMS} -eta0 0.05"
+    u = hm.train_fm(opts)
+    u.process_batch(rp, f, v, y)
+    u.close()
+    ref = _oracle.train_fm(_oracle.config_from(hm.parse_options("train_fm", opts)), rp, f, v, y)
+    assert u.step == ref.t == 2
+    touched = np.unique(f)
+    assert_weights_close(u.array_to_host("w0"), ref.w0, "w0")
+    assert_weights_close(u.array_to_host("w")[touched], ref.w[touched], "w")
+    V = u.array_to_host("V").reshape(-1, k)
+    assert_weights_close(V[touched].reshape(-1), ref.V.reshape(-1, k)[touched].reshape(-1), "V")
+    gV = u.array_to_host("gV").reshape(-1, k)
+    assert_weights_close(gV[touched].reshape(-1), ref.gv.reshape(-1, k)[touched].reshape(-1), "gV")
+    # untouched features keep their initial factors bit for bit
+    rest = np.setdiff1d(np.arange(0, DIMS, 4099), touched)
+    assert np.array_equal(V[rest], ref.V.reshape(-1, k)[rest])
+    u.destroy()
