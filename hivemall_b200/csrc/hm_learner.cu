@@ -5,10 +5,13 @@
 // mount has no source to cite (README.md:20-22).  What happens between process() and the
 // kernels:
 //
-//   host CSR slice --H2D (copy stream; truly async when the caller used hm_host_alloc)--> chunk
+//   host rows slice --H2D (copy stream; truly async when the caller used hm_host_alloc)--> chunk
+//     (plain CSR; or two groups / column matrices / feature strings, which a kernel on the sort
+//      stream merges, expands or hashes into the chunk's CSR)
 //   chunk = [rows left over from the previous slice | new rows]          (device resident)
 //   full mini-batches of the chunk are grouped into blocks (<= kMaxSegs mini-batches,
-//   <= kBlockElemCap elements); per block: seg_prep + segmented sort (once, data only), then
+//   <= kBlockElemCap elements); per block, on the sort stream: hot-feature selection, seg_prep,
+//   segmented sort (once, data only; kept for the later passes of -iters > 1), then
 //   per mini-batch: linear_forward + linear_update on the compute stream.
 //   Rows that do not fill a mini-batch wait at the end of the chunk for the next slice or close().
 //

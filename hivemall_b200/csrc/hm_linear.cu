@@ -7,11 +7,15 @@
 // (oracle/hm_oracle.c) restates the same contract independently.
 //
 //   linear_forward_kernel      warp per row: gather the weight out of the feature's record (FTRL:
-//                              derive it from (z, n)), margin in fp64, dloss[row]
+//                              derive it from (z, n)), margin in fp64, dloss[row]; the block's hot features
+//                              (HotInfo) take their weight from shared memory and have their gradient sums
+//                              accumulated here, in a fixed order, instead of being sorted
 //   linear_update_kernel       one tile of the feature-sorted mini-batch per CTA: dloss[row]*value,
 //                              reduce-by-feature in fp64 in a fixed order (no float atomics), finished
 //                              features stepped in batches; only segments that really straddle CTAs
-//                              leave records, summed by the last CTA to finish (reduce_tile, apply_list)
+//                              leave records, summed by the last CTA to finish (reduce_tile, apply_list);
+//                              extra CTAs step the hot features from the forward kernel's partial sums
+//   (mini-batches up to 400 K elements launch the two as programmatic dependents: pdl_wait)
 //   linear_small_batch_kernel  mini-batches of a few hundred rows: one persistent CTA runs forward and
 //                              reduce+step for up to 64 mini-batches per launch
 //   predict / export / scale helpers
