@@ -136,6 +136,7 @@ struct FwdParams {
     int32_t n_rows;
     int32_t task, loss;
     int32_t train;           // 0: prediction only
+    int32_t lpr;             // lanes per row: 32, 16 or 8 (chosen by the host from the mean row length)
     uint32_t dims;
     uint32_t *bad;           // set to 1 when a feature index >= dims is met (that element scores 0)
     // hot features of the block (training only; NULL: none): their weights are read from shared memory
@@ -176,40 +177,88 @@ __device__ __forceinline__ void forward_rows(const FwdParams &P, int warp_first,
     }
 }
 
+// The same with LPR lanes per row (32 / LPR rows per warp side by side): rows of a few dozen elements leave
+// fewer lanes idle in the gather loop, and two (or four) rows' dloss are worked out at once.  Same fp64 sums,
+// another (fixed) tree order.
+template <int LD, int LPR>
+__device__ __forceinline__ void forward_rows_lpr(const FwdParams &P, int warp_first, int warp_stride)
+{
+    constexpr int RPW = 32 / LPR;
+    const int lane = threadIdx.x & 31, sub = lane & (LPR - 1), part = lane / LPR;
+    for (int rb = warp_first * RPW; rb < P.n_rows; rb += warp_stride * RPW) {
+        const int r = rb + part;
+        const bool live = r < P.n_rows;
+        const int64_t row = P.row0 + (live ? r : rb);
+        const int64_t p0 = live ? P.rowptr[row] : 0, p1 = live ? P.rowptr[row + 1] : 0;
+        double acc = 0.0;
+        for (int64_t p = p0 + sub; p < p1; p += LPR) {
+            const uint32_t f = __ldcs(P.feature + p);
+            const float x = __ldcs(P.value + p);
+            if (f < P.dims) acc += (double)__fmul_rn(weight_at<LD>(P.wv, f), x);
+            else atomicOr(P.bad, 1u);
+        }
+#pragma unroll
+        for (int o = LPR / 2; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+        if (live && sub == 0) {
+            const float m = (float)acc;
+            P.margin[row - P.block_row0] = m;
+            if (P.train) {
+                const float lab = P.label[row];
+                const float y = P.task == HM_TASK_CLASSIFIER ? (lab > 0.0f ? 1.0f : -1.0f) : lab;
+                P.dloss[r] = dloss_of(P.loss, m, y);
+            }
+        }
+    }
+}
+
 // ---- hot features in the forward kernel ------------------------------------------------------
 constexpr uint32_t kHotNone = 0xffffffffu;
 
-struct HotShared {                          // shared memory of a forward CTA that handles hot features
-    uint32_t tab_key[kHotSlots];            // direct-mapped (hot_index): key -> slot (index into HotInfo::key)
-    uint8_t tab_slot[kHotSlots];
+// Shared memory of a forward CTA that handles hot features (dynamic: a launch without hot features asks for
+// none and leaves the whole carve-out to L1).  UNITS = row groups per CTA: 8 with a warp per row, 16 with half.
+template <int UNITS>
+struct HotSharedT {
+    // accumulators per UNIT = group of lanes that works on one row at a time (a warp, or half a warp when rows
+    // are short): sum of dloss * value per hot feature, occurrences, and the claim bytes
+    static constexpr int kUnits = UNITS;
+    double acc[UNITS][kMaxHot];
+    uint32_t cnt[UNITS][kMaxHot];
+    uint32_t key[kMaxHot];                  // HotInfo::key
     float w[kMaxHot];                       // the hot features' weights at the start of the mini-batch
-    double acc[kFwdThreads / 32][kMaxHot];  // per warp: sum of dloss * value per hot feature
-    uint32_t cnt[kFwdThreads / 32][kMaxHot];
-    uint32_t claim[kFwdThreads / 32][kMaxHot];
+    uint8_t tab_slot[kHotSlots];            // direct-mapped (hot_index): -> index into key[], kHotFree if none
+    uint8_t claim[UNITS][kMaxHot];
 };
+// The footprint decides how much of the SM's 256 KB is left as L1 and how many CTAs of the sort stream fit beside
+// this kernel: with 27 KB per CTA (a 4-byte key per table slot, 4-byte claims) the half-warp variant ran 50 us
+// against 40 us (L1 hit rate 8 % against 17 %), and 4 KB of padding alone cost 2 % of the whole step.
+static_assert(sizeof(HotSharedT<16>) <= 16 * 1024 && sizeof(HotSharedT<8>) <= 10 * 1024, "forward CTA shared memory");
+static_assert(kMaxHot < 255, "slot numbers are bytes");
+constexpr uint8_t kHotFree = 0xff;
 
-__device__ __forceinline__ uint32_t hot_slot_of(const HotShared &H, uint32_t key)
+template <class HS>
+__device__ __forceinline__ uint32_t hot_slot_of(const HS &H, uint32_t key)
 {
-    const uint32_t h = hot_index(key);
-    return H.tab_key[h] == key ? (uint32_t)H.tab_slot[h] : kHotNone;
+    const uint32_t s = H.tab_slot[hot_index(key)];
+    return (s != kHotFree && H.key[s] == key) ? s : kHotNone;
 }
 
 // Add this warp's contributions c (lanes with slot != kHotNone) to the warp's accumulators.  Lanes that
 // hit DIFFERENT slots add at once; when two lanes hit the same slot (a feature twice in one row) the adds
 // are done one lane at a time in lane order, so that the sum's order is fixed.
-__device__ __forceinline__ void hot_accumulate(HotShared &H, int warp, int lane, uint32_t slot, float c)
+template <class HS>
+__device__ __forceinline__ void hot_accumulate(HS &H, int unit, int lane, uint32_t slot, float c)
 {
     const bool hot = slot != kHotNone;
     const uint32_t hot_lanes = __ballot_sync(0xffffffffu, hot);
     if (hot_lanes == 0u) return;
-    if (hot) H.claim[warp][slot] = (uint32_t)lane;
+    if (hot) H.claim[unit][slot] = (uint8_t)lane;
     __syncwarp();
-    const bool lost = hot && H.claim[warp][slot] != (uint32_t)lane;
+    const bool lost = hot && H.claim[unit][slot] != (uint8_t)lane;
     if (!__any_sync(0xffffffffu, lost)) {
-        if (hot) { H.acc[warp][slot] += (double)c; H.cnt[warp][slot] += 1u; }
+        if (hot) { H.acc[unit][slot] += (double)c; H.cnt[unit][slot] += 1u; }
     } else {
         for (uint32_t m = hot_lanes; m != 0u; m &= m - 1u) {
-            if (lane == __ffs(m) - 1) { H.acc[warp][slot] += (double)c; H.cnt[warp][slot] += 1u; }
+            if (lane == __ffs(m) - 1) { H.acc[unit][slot] += (double)c; H.cnt[unit][slot] += 1u; }
             __syncwarp();
         }
     }
@@ -219,87 +268,110 @@ __device__ __forceinline__ void hot_accumulate(HotShared &H, int warp, int lane,
 // Before the forward pass of a mini-batch: the block's hot keys into the CTA's direct-mapped table, their
 // current weights, cleared accumulators.  Two barriers and two dependent round trips (count and key are
 // loaded side by side; the weight gather needs the key).
-template <int LD>
-__device__ __forceinline__ void hot_prologue(const FwdParams &P, HotShared &H)
+template <int LD, class HS>
+__device__ __forceinline__ void hot_prologue(const FwdParams &P, HS &H)
 {
     const int tid = threadIdx.x;
     const uint32_t n = P.hot->count;
     const uint32_t key = tid < kMaxHot ? P.hot->key[tid] : 0u;
-    for (int q = tid; q < kHotSlots; q += kFwdThreads) H.tab_key[q] = kHotNone;
-    for (int q = tid; q < (kFwdThreads / 32) * kMaxHot; q += kFwdThreads) { (&H.acc[0][0])[q] = 0.0; (&H.cnt[0][0])[q] = 0u; }
+    for (int q = tid; q < kHotSlots / 4; q += kFwdThreads) reinterpret_cast<uint32_t *>(H.tab_slot)[q] = 0xffffffffu;
+    for (int q = tid; q < HS::kUnits * kMaxHot; q += kFwdThreads) { (&H.acc[0][0])[q] = 0.0; (&H.cnt[0][0])[q] = 0u; }
     __syncthreads();
     if (LD == kLdCG) pdl_wait();     // the weights below are the previous mini-batch's update
     if (tid < (int)n) {
-        const uint32_t h = hot_index(key);     // (pairwise different for the keys of a HotInfo)
-        H.tab_key[h] = key;
-        H.tab_slot[h] = (uint8_t)tid;
+        H.tab_slot[hot_index(key)] = (uint8_t)tid;     // (the index is pairwise different for the keys of a HotInfo)
+        H.key[tid] = key;
         H.w[tid] = key < P.dims ? weight_at<LD>(P.wv, key) : 0.0f;
     }
     __syncthreads();
 }
 
-// After it: this CTA's sums (warps added in a fixed order) to slot `cta` of the per-feature arrays.
-__device__ __forceinline__ void hot_end(const FwdParams &P, HotShared &H, int cta)
+// After it: this CTA's sums (units added in a fixed order) to slot `cta` of the per-feature arrays.
+template <class HS>
+__device__ __forceinline__ void hot_end(const FwdParams &P, HS &H, int cta)
 {
     const int tid = threadIdx.x;
     __syncthreads();
     if (tid < (int)P.hot->count) {
         double sum = 0.0; uint32_t cnt = 0;
 #pragma unroll
-        for (int w2 = 0; w2 < kFwdThreads / 32; w2++) { sum += H.acc[w2][tid]; cnt += H.cnt[w2][tid]; }
+        for (int w2 = 0; w2 < HS::kUnits; w2++) { sum += H.acc[w2][tid]; cnt += H.cnt[w2][tid]; }
         P.hot_sum[(size_t)tid * P.hot_stride + cta] = sum;
         P.hot_cnt[(size_t)tid * P.hot_stride + cta] = cnt;
     }
 }
 
-// forward_rows with hot features.  The margin adds the same fp32 products in the same lane order as
-// forward_rows: only the source of a hot feature's weight differs (shared memory instead of the gather;
-// it is the same number).  After a row's dloss is known, the contributions dloss * value of its hot
-// elements (what the update kernel would otherwise have found in the sorted stream) go to the warp's
-// accumulators; rows longer than 64 elements re-read their tail for that.
-template <int LD>
-__device__ __forceinline__ void forward_rows_hot(const FwdParams &P, int warp_first, int warp_stride, HotShared &H)
+// forward_rows_lpr with hot features: LPR lanes per row, 32 / LPR rows per warp side by side.  The margin adds
+// the same fp32 products as the plain path; only the source of a hot feature's weight differs (shared memory
+// instead of the gather; it is the same number).  After a row's dloss is known, the contributions dloss * value
+// of its hot elements (what the update kernel would otherwise have found in the sorted stream) go to the
+// accumulators of the row's unit; a lane keeps its first KEEP elements in registers for that, longer rows
+// re-read their tail.
+template <int LD, int LPR>
+__device__ __forceinline__ void forward_rows_hot(const FwdParams &P, int warp_first, int warp_stride,
+                                                 HotSharedT<256 / LPR> &H)
 {
+    constexpr int RPW = 32 / LPR;
+    constexpr int KEEP = LPR == 32 ? 2 : 3;          // 64 or 48 elements of a row stay in registers
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    for (int r = warp_first; r < P.n_rows; r += warp_stride) {
-        const int64_t row = P.row0 + r;
-        const int64_t p0 = P.rowptr[row], p1 = P.rowptr[row + 1];
+    const int sub = lane & (LPR - 1), part = lane / LPR;
+    const int unit = RPW * warp + part;
+    for (int rb = warp_first * RPW; rb < P.n_rows; rb += warp_stride * RPW) {
+        const int r = rb + part;
+        const bool live = r < P.n_rows;
+        const int64_t row = P.row0 + (live ? r : rb);
+        const int64_t p0 = live ? P.rowptr[row] : 0, p1 = live ? P.rowptr[row + 1] : 0;
         double acc = 0.0;
-        uint32_t slot_a = kHotNone, slot_b = kHotNone;     // this lane's elements at positions lane and 32 + lane
-        float x_a = 0.0f, x_b = 0.0f;
-        for (int64_t p = p0 + lane; p < p1; p += 32) {
+        uint32_t slot[KEEP]; float xk[KEEP];
+#pragma unroll
+        for (int i = 0; i < KEEP; i++) {
+            slot[i] = kHotNone; xk[i] = 0.0f;
+            const int64_t p = p0 + sub + i * LPR;
+            if (p < p1) {
+                const uint32_t f = __ldcs(P.feature + p);
+                const float x = __ldcs(P.value + p);
+                if (f < P.dims) {
+                    const uint32_t sl = hot_slot_of(H, f);
+                    const float w = sl != kHotNone ? H.w[sl] : weight_at<LD>(P.wv, f);
+                    acc += (double)__fmul_rn(w, x);
+                    slot[i] = sl; xk[i] = x;
+                } else atomicOr(P.bad, 1u);
+            }
+        }
+        for (int64_t p = p0 + sub + KEEP * LPR; p < p1; p += LPR) {
             const uint32_t f = __ldcs(P.feature + p);
             const float x = __ldcs(P.value + p);
             if (f < P.dims) {
                 const uint32_t sl = hot_slot_of(H, f);
-                const float w = sl != kHotNone ? H.w[sl] : weight_at<LD>(P.wv, f);
-                acc += (double)__fmul_rn(w, x);
-                if (p == p0 + lane) { slot_a = sl; x_a = x; }
-                else if (p == p0 + 32 + lane) { slot_b = sl; x_b = x; }
+                acc += (double)__fmul_rn(sl != kHotNone ? H.w[sl] : weight_at<LD>(P.wv, f), x);
             } else atomicOr(P.bad, 1u);
         }
-        acc = warp_sum(acc);
-        const float m = (float)acc;
+#pragma unroll
+        for (int o = LPR / 2; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
         float dl = 0.0f;
-        if (lane == 0) {
+        if (live && sub == 0) {
+            const float m = (float)acc;
             P.margin[row - P.block_row0] = m;
             const float lab = P.label[row];
             const float y = P.task == HM_TASK_CLASSIFIER ? (lab > 0.0f ? 1.0f : -1.0f) : lab;
             dl = dloss_of(P.loss, m, y);
             P.dloss[r] = dl;
         }
-        dl = __shfl_sync(0xffffffffu, dl, 0);
-        hot_accumulate(H, warp, lane, slot_a, __fmul_rn(dl, x_a));
-        if (p1 - p0 > 32) hot_accumulate(H, warp, lane, slot_b, __fmul_rn(dl, x_b));
-        for (int64_t q0 = p0 + 64; q0 < p1; q0 += 32) {       // (uniform over the warp)
-            const int64_t p = q0 + lane;
+        dl = __shfl_sync(0xffffffffu, dl, part * LPR);
+        const int len = (int)min(p1 - p0, (int64_t)0x7fffffff);
+        const int maxlen = __reduce_max_sync(0xffffffffu, len);          // (uniform over the warp)
+#pragma unroll
+        for (int i = 0; i < KEEP; i++)
+            if (maxlen > i * LPR) hot_accumulate(H, unit, lane, slot[i], __fmul_rn(dl, xk[i]));
+        for (int q0 = KEEP * LPR; q0 < maxlen; q0 += LPR) {
+            const int64_t p = p0 + q0 + sub;
             uint32_t sl = kHotNone; float x = 0.0f;
             if (p < p1) {
                 const uint32_t f = __ldcs(P.feature + p);
                 x = __ldcs(P.value + p);
                 if (f < P.dims) sl = hot_slot_of(H, f);
             }
-            hot_accumulate(H, warp, lane, sl, __fmul_rn(dl, x));
+            hot_accumulate(H, unit, lane, sl, __fmul_rn(dl, x));
         }
     }
 }
@@ -366,16 +438,28 @@ template <bool PDL>
 __global__ void __launch_bounds__(kFwdThreads, 8) linear_forward_kernel(FwdParams P)
 {
     constexpr int LD = PDL ? kLdCG : kLdRO;
-    __shared__ HotShared H;
+    extern __shared__ __align__(16) unsigned char fwd_dyn[];
     if (PDL) pdl_launch_dependents();
     const int warp_first = blockIdx.x * (kFwdThreads / 32) + (threadIdx.x >> 5), warp_stride = gridDim.x * (kFwdThreads / 32);
     if (P.hot && P.hot->count != 0u) {     // (HotInfo is the sort's output: complete before this launch)
-        hot_prologue<LD>(P, H);
-        forward_rows_hot<LD>(P, warp_first, warp_stride, H);
-        hot_end(P, H, (int)blockIdx.x);
+        if (P.lpr <= 16) {
+            auto &H = *reinterpret_cast<HotSharedT<16> *>(fwd_dyn);
+            hot_prologue<LD>(P, H);
+            forward_rows_hot<LD, 16>(P, warp_first, warp_stride, H);
+            hot_end(P, H, (int)blockIdx.x);
+        } else {
+            auto &H = *reinterpret_cast<HotSharedT<8> *>(fwd_dyn);
+            hot_prologue<LD>(P, H);
+            forward_rows_hot<LD, 32>(P, warp_first, warp_stride, H);
+            hot_end(P, H, (int)blockIdx.x);
+        }
     } else {
         if (PDL) pdl_wait();
-        forward_rows<LD>(P, warp_first, warp_stride);
+        // lanes per row by the mini-batch's mean row length (measured on 39-element rows: 32.7 us with a warp
+        // per row, 28.8 with half a warp, 27.7 with a quarter)
+        if (P.lpr == 8) forward_rows_lpr<LD, 8>(P, warp_first, warp_stride);
+        else if (P.lpr == 16) forward_rows_lpr<LD, 16>(P, warp_first, warp_stride);
+        else forward_rows<LD>(P, warp_first, warp_stride);
     }
 }
 
@@ -1135,10 +1219,11 @@ int grid_for(int64_t ctas_wanted, int per_sm)
 // with grids that fill the GPU the early CTAs take slots from the running kernel's tail (measured slower).
 constexpr int64_t kPdlMaxElems = 400000;      // elements per mini-batch (measured: +8 % at 320 K, -10 % at 640 K)
 template <class P>
-cudaError_t launch_maybe_pdl(void (*kernel)(P), int grid, int block, cudaStream_t stream, bool pdl, const P &params)
+cudaError_t launch_maybe_pdl(void (*kernel)(P), int grid, int block, cudaStream_t stream, bool pdl, const P &params,
+                             size_t dyn_smem = 0)
 {
     cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3((unsigned)grid); cfg.blockDim = dim3((unsigned)block); cfg.dynamicSmemBytes = 0; cfg.stream = stream;
+    cfg.gridDim = dim3((unsigned)grid); cfg.blockDim = dim3((unsigned)block); cfg.dynamicSmemBytes = dyn_smem; cfg.stream = stream;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[0].val.programmaticStreamSerializationAllowed = 1;
@@ -1163,6 +1248,19 @@ hm_status launch_linear_forward(Launcher &L, const LinearArgs &a, const int64_t 
     if (n_rows <= 0) return HM_OK;
     FwdParams P;
     P.hot = hc.info; P.hot_sum = hc.sum; P.hot_cnt = hc.cnt; P.hot_stride = hc.stride;
+    {
+        // Narrow row groups only when the mini-batch still fills the resident grid with them; a smaller one
+        // keeps a warp per row (more CTAs in flight matter more there than instructions per row).
+        const int64_t mean = nnz_hint / std::max<int32_t>(n_rows, 1);
+        const bool fills = (int64_t)n_rows >= (int64_t)num_sms() * 8 * 8 * 2;
+        P.lpr = (!fills || nnz_hint <= 0 || mean > 48) ? 32 : (mean <= 24 && !hc.info ? 8 : 16);
+        // HM_FWD_LPR=32|16|8 in the environment overrides the choice (A/B measurements)
+        if (const char *e = std::getenv("HM_FWD_LPR")) {
+            const int v = std::atoi(e);
+            if (v == 32 || v == 16 || (v == 8 && !hc.info)) P.lpr = v;
+        }
+    }
+    const size_t dyn = !hc.info ? 0 : (P.lpr <= 16 ? sizeof(HotSharedT<16>) : sizeof(HotSharedT<8>));
     P.wv = a.wv; P.rowptr = d_rowptr; P.feature = d_feature; P.value = d_value; P.label = d_label;
     P.margin = d_margin; P.dloss = d_dloss;
     P.block_row0 = block_row0; P.row0 = row0; P.n_rows = n_rows;
@@ -1173,9 +1271,9 @@ hm_status launch_linear_forward(Launcher &L, const LinearArgs &a, const int64_t 
     // algorithmic bytes: feature+value read, w gather per element; rowptr, label, margin, dloss per row
     const double bytes = 12.0 * (double)nnz_hint + 20.0 * (double)n_rows;
     if (pdl_enabled() && nnz_hint <= kPdlMaxElems)
-        HM_LAUNCH(L, K_LIN_FORWARD, bytes, (launch_maybe_pdl(linear_forward_kernel<true>, grid, kFwdThreads, L.stream, true, P)));
+        HM_LAUNCH(L, K_LIN_FORWARD, bytes, (launch_maybe_pdl(linear_forward_kernel<true>, grid, kFwdThreads, L.stream, true, P, dyn)));
     else
-        HM_LAUNCH(L, K_LIN_FORWARD, bytes, (linear_forward_kernel<false><<<grid, kFwdThreads, 0, L.stream>>>(P)));
+        HM_LAUNCH(L, K_LIN_FORWARD, bytes, (linear_forward_kernel<false><<<grid, kFwdThreads, dyn, L.stream>>>(P)));
     HM_CUDA(cudaGetLastError());
     return HM_OK;
 }
@@ -1191,7 +1289,7 @@ hm_status launch_predict_linear(Launcher &L, const WeightView &wv, int64_t dims,
     P.block_row0 = 0; P.row0 = 0; P.n_rows = (int32_t)n_rows;
     P.task = 0; P.loss = 0; P.train = 0;
     P.dims = (uint32_t)dims; P.bad = d_bad;
-    P.hot = nullptr; P.hot_sum = nullptr; P.hot_cnt = nullptr; P.hot_stride = 0;
+    P.hot = nullptr; P.hot_sum = nullptr; P.hot_cnt = nullptr; P.hot_stride = 0; P.lpr = 32;
     const int grid = grid_for((n_rows + 7) / 8, 8);
     HM_LAUNCH(L, K_PREDICT, 0.0, (linear_forward_kernel<false><<<grid, kFwdThreads, 0, L.stream>>>(P)));
     HM_CUDA(cudaGetLastError());

@@ -182,3 +182,30 @@ def test_out_of_range_feature_is_reported_and_ignored():
     ref, _ = run_oracle_linear("train_classifier", options, clean)
     assert_weights_close(w, ref.w)
     u.destroy()
+
+
+@pytest.mark.parametrize("hot", ["1", "0"])
+@pytest.mark.parametrize("lpr", ["16", "8"])
+def test_rows_side_by_side_in_a_warp(monkeypatch, lpr, hot):
+    """Short rows are worked on by half (or a quarter) of a warp each, two (four) rows side by side
+    (hm_linear.cu: forward_rows_lpr / forward_rows_hot<LD, 16>; the library picks this for mini-batches that
+    fill the GPU, HM_FWD_LPR forces it here).  Same data as the hard cases above: a hot feature twice in a row
+    (the row group's serial fallback), empty rows, rows longer than the 48 elements a group keeps in registers
+    with hot features in the re-read tail, a ragged last mini-batch."""
+    monkeypatch.setenv("HM_FWD_LPR", lpr)
+    monkeypatch.setenv("HM_HOT_FEATURES", hot)
+    prefix = [5, 9, 5, 11, 40000]
+    rows_f, rows_v, rng = prefix_rows(4096 + 333, prefix=prefix, seed=23)
+    rows_f[100] = rows_f[100][:0]
+    rows_v[100] = rows_v[100][:0]
+    rows_f[101] = rows_f[101][:2]
+    rows_v[101] = rows_v[101][:2]
+    for r in (6, 7, 1000, 3001, 4096, 4428):
+        extra = rng.integers(0, DIMS, 90)
+        extra[[10, 41, 70, 88]] = [9, 5, 11, 5]
+        rows_f[r] = np.concatenate([rows_f[r], extra])
+        rows_v[r] = np.concatenate([rows_v[r], rng.normal(0, 1, 90)])
+    data = to_csr(rows_f, rows_v, rng)
+    want = [5, 9, 11, 40000] if hot == "1" else []
+    check("train_classifier", f"-loss logloss -opt adagrad -mini_batch 2048 -dims {DIMS} -eta0 0.05", data, want)
+    check("train_classifier", f"-loss logloss -opt ftrl -mini_batch 2048 -dims {DIMS} -alpha 0.05", data, want)
