@@ -141,7 +141,12 @@ struct LinearArgs {
     float *rec;           // replica: rec_width floats per feature
     int rec_width;        // 1 (SGD: w), 2 (AdaGrad: w, G; FTRL: z, n), 4 (AdaDelta, Adam: w, s1, s2, unused)
     WeightView wv;
+    const float *sqnorm = nullptr;   // |x|^2 per row of the block being trained (online learners), else NULL
 };
+// |x|^2 of rows [row0, row0 + n_rows) of a chunk into out[0 .. n_rows)
+hm_status launch_row_sqnorm(Launcher &L, const int64_t *d_rowptr, int64_t row0, int64_t n_rows, const uint32_t *d_feature,
+                            const float *d_value, int64_t dims, float *d_out, int64_t nnz_hint);
+inline bool loss_needs_sqnorm(int loss) { return loss >= HM_LOSS_PA; }
 // Hot features of the block being trained, and where their gradient sums travel from the forward
 // kernel to the update kernel.  info == NULL: the block was sorted whole.
 struct HotCols {

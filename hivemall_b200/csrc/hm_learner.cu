@@ -279,6 +279,7 @@ struct hm_udtf {
     SortScratch sort[2];             // block k+1 is sorted (sort stream) while block k trains (compute stream)
     UpdateScratch upd;
     ExportScratch exp;
+    DevBuf sqnorm;        // online learners: |x|^2 per row of the block being trained
     DevBuf margin, dloss, mb_gather, exp_feat, exp_weight, tmp_a, tmp_b, tmp_c, tmp_d;
     uint32_t *d_bad = nullptr;       // [0]: a training row held an index outside [0, dims); [1]: a scored row did
     int64_t *d_total = nullptr;
@@ -512,6 +513,11 @@ hm_status train_rows(hm_udtf *u, Chunk &c, int64_t row0, int64_t n_rows, const i
         SortScratch &ss = replay ? view : u->sort[set];
         const bool block_hot = replay ? c.sorted[bi].hot_on : hot_on;
         HM_TRY(u->margin.reserve((size_t)p.rows * sizeof(float)));
+        if (!u->fm && loss_needs_sqnorm(u->cfg.loss)) {
+            HM_TRY(u->sqnorm.reserve((size_t)p.rows * sizeof(float)));
+            HM_TRY(launch_row_sqnorm(u->L, c.rp(), p.row0, p.rows, c.ft(), c.vl(), u->cfg.dims, u->sqnorm.as<float>(), p.nnz));
+            a.sqnorm = u->sqnorm.as<float>();
+        }
         HM_TRY(u->dloss.reserve((size_t)std::min<int64_t>(p.rows, B) * sizeof(float)));
         if (u->fm) {
             int64_t max_mb = 0;
@@ -1292,7 +1298,7 @@ hm_status hm_udtf_destroy(hm_udtf *u)
     if (u->merged_ev) cudaEventDestroy(u->merged_ev);
     update_scratch_free(u->upd);
     cudaFree(u->exp.counts);
-    for (DevBuf *b : {&u->margin, &u->dloss, &u->mb_gather, &u->exp_feat, &u->exp_weight, &u->tmp_a,
+    for (DevBuf *b : {&u->sqnorm, &u->margin, &u->dloss, &u->mb_gather, &u->exp_feat, &u->exp_weight, &u->tmp_a,
                       &u->tmp_b, &u->tmp_c, &u->tmp_d})
         b->release();
     cudaFree(u->rec); cudaFree(u->d_bad); cudaFree(u->d_total);

@@ -67,6 +67,34 @@ __device__ __forceinline__ float dloss_of(int loss, float m, float y)
     return __fsub_rn(m, y);
 }
 
+// Online learners on the same skeleton: the number that takes dloss's place for a row is
+// -(step size) * (direction of the correction); xx = |x|^2 of the row (row_sqnorm_kernel).  Perceptron
+// (Rosenblatt): step 1 on a mistake.  Passive-aggressive (Crammer et al. 2006): PA tau = l / xx, PA-I
+// tau = min(C, l / xx), PA-II tau = l / (xx + 1 / (2C)), with l the hinge loss (classification) or the
+// epsilon-insensitive loss (regression).  A row without valid elements (xx == 0) gives 0.
+__device__ __forceinline__ float online_coef(int loss, float m, float y, float xx, float c, float eps)
+{
+    if (loss == HM_LOSS_PERCEPTRON) return __fmul_rn(y, m) <= 0.0f ? -y : 0.0f;
+    float l, dir;
+    if (loss == HM_LOSS_PA1_REGR || loss == HM_LOSS_PA2_REGR) {
+        const float e = __fsub_rn(y, m);
+        l = __fsub_rn(fabsf(e), eps);
+        dir = e < 0.0f ? -1.0f : 1.0f;
+    } else {
+        l = __fsub_rn(1.0f, __fmul_rn(y, m));
+        dir = y;
+    }
+    if (!(l > 0.0f)) return 0.0f;
+    float tau;
+    if (loss == HM_LOSS_PA2 || loss == HM_LOSS_PA2_REGR) tau = __fdiv_rn(l, __fadd_rn(xx, __fdiv_rn(0.5f, c)));
+    else {
+        if (!(xx > 0.0f)) return 0.0f;
+        tau = __fdiv_rn(l, xx);
+        if (loss != HM_LOSS_PA) tau = fminf(c, tau);
+    }
+    return -__fmul_rn(tau, dir);
+}
+
 // FTRL-Proximal closed form; the same operation sequence as the update step.
 __device__ __forceinline__ float ftrl_weight(float z, float n, float alpha, float beta, float l1, float l2)
 {
@@ -137,6 +165,8 @@ struct FwdParams {
     int32_t task, loss;
     int32_t train;           // 0: prediction only
     int32_t lpr;             // lanes per row: 32, 16 or 8 (chosen by the host from the mean row length)
+    const float *sqnorm;     // online learners other than the perceptron: |x|^2 per row of the BLOCK, else NULL
+    float pa_c, pa_eps;
     uint32_t dims;
     uint32_t *bad;           // set to 1 when a feature index >= dims is met (that element scores 0)
     // hot features of the block (training only; NULL: none): their weights are read from shared memory
@@ -147,6 +177,37 @@ struct FwdParams {
     uint32_t *hot_cnt;       // [kMaxHot][hot_stride]: ... and the number of occurrences
     int32_t hot_stride;
 };
+
+// What the update multiplies a row's values with: the loss derivative, or an online learner's signed step.
+template <int LD>
+__device__ __forceinline__ float row_coef(const FwdParams &P, float m, float y, int64_t block_row)
+{
+    if (P.loss <= HM_LOSS_SQUARED) return dloss_of(P.loss, m, y);
+    const float xx = P.sqnorm ? ld_mode<LD>(P.sqnorm + block_row) : 0.0f;
+    return online_coef(P.loss, m, y, xx, P.pa_c, P.pa_eps);
+}
+
+// |x|^2 of every row of a block: fp32 squares, fp64 sum, rounded to fp32 once (elements with an index out of
+// range do not count, as everywhere).  One warp per row.  The rows do not change: once per block, before its
+// first mini-batch.
+__global__ void __launch_bounds__(256) row_sqnorm_kernel(const int64_t *__restrict__ rowptr, int64_t row0, int64_t n_rows,
+                                                         const uint32_t *__restrict__ feature, const float *__restrict__ value,
+                                                         uint32_t dims, float *__restrict__ out)
+{
+    const int lane = threadIdx.x & 31;
+    const int64_t warp = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), stride = (int64_t)gridDim.x * (blockDim.x >> 5);
+    for (int64_t r = warp; r < n_rows; r += stride) {
+        const int64_t p0 = rowptr[row0 + r], p1 = rowptr[row0 + r + 1];
+        double acc = 0.0;
+        for (int64_t p = p0 + lane; p < p1; p += 32) {
+            const float x = __ldcs(value + p);
+            if (__ldcs(feature + p) < dims) acc += (double)__fmul_rn(x, x);
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+        if (lane == 0) out[r] = (float)acc;
+    }
+}
 
 // Margins (and dloss) of rows r = warp_first, warp_first + warp_stride, ... of the mini-batch: one
 // warp per row, lanes over the row's elements, fp64 shuffle reduction.
@@ -171,7 +232,7 @@ __device__ __forceinline__ void forward_rows(const FwdParams &P, int warp_first,
             if (P.train) {
                 const float lab = P.label[row];
                 const float y = P.task == HM_TASK_CLASSIFIER ? (lab > 0.0f ? 1.0f : -1.0f) : lab;
-                P.dloss[r] = dloss_of(P.loss, m, y);
+                P.dloss[r] = row_coef<LD>(P, m, y, row - P.block_row0);
             }
         }
     }
@@ -205,7 +266,7 @@ __device__ __forceinline__ void forward_rows_lpr(const FwdParams &P, int warp_fi
             if (P.train) {
                 const float lab = P.label[row];
                 const float y = P.task == HM_TASK_CLASSIFIER ? (lab > 0.0f ? 1.0f : -1.0f) : lab;
-                P.dloss[r] = dloss_of(P.loss, m, y);
+                P.dloss[r] = row_coef<LD>(P, m, y, row - P.block_row0);
             }
         }
     }
@@ -354,7 +415,7 @@ __device__ __forceinline__ void forward_rows_hot(const FwdParams &P, int warp_fi
             P.margin[row - P.block_row0] = m;
             const float lab = P.label[row];
             const float y = P.task == HM_TASK_CLASSIFIER ? (lab > 0.0f ? 1.0f : -1.0f) : lab;
-            dl = dloss_of(P.loss, m, y);
+            dl = row_coef<LD>(P, m, y, row - P.block_row0);
             P.dloss[r] = dl;
         }
         dl = __shfl_sync(0xffffffffu, dl, part * LPR);
@@ -427,7 +488,7 @@ __device__ __forceinline__ void forward_rows_small(const FwdParams &P)
                 const float m = (float)acc[u];
                 P.margin[row - P.block_row0] = m;
                 const float y = P.task == HM_TASK_CLASSIFIER ? (lab[u] > 0.0f ? 1.0f : -1.0f) : lab[u];
-                P.dloss[r0 + u] = dloss_of(P.loss, m, y);
+                P.dloss[r0 + u] = row_coef<kLdPlain>(P, m, y, row - P.block_row0);
             }
         }
     }
@@ -1265,6 +1326,7 @@ hm_status launch_linear_forward(Launcher &L, const LinearArgs &a, const int64_t 
     P.margin = d_margin; P.dloss = d_dloss;
     P.block_row0 = block_row0; P.row0 = row0; P.n_rows = n_rows;
     P.task = a.cfg.task; P.loss = a.cfg.loss; P.train = 1;
+    P.sqnorm = a.sqnorm; P.pa_c = a.cfg.pa_c; P.pa_eps = a.cfg.pa_epsilon;
     P.dims = (uint32_t)a.cfg.dims; P.bad = d_bad;
     const int grid = linear_forward_grid(n_rows);
     if (hc.info && grid > hc.stride) HM_FAIL(HM_ERR_STATE, "hot-feature scratch too small (%d > %d)", grid, hc.stride);
@@ -1278,6 +1340,17 @@ hm_status launch_linear_forward(Launcher &L, const LinearArgs &a, const int64_t 
     return HM_OK;
 }
 
+hm_status launch_row_sqnorm(Launcher &L, const int64_t *d_rowptr, int64_t row0, int64_t n_rows, const uint32_t *d_feature,
+                            const float *d_value, int64_t dims, float *d_out, int64_t nnz_hint)
+{
+    if (n_rows <= 0) return HM_OK;
+    HM_LAUNCH(L, K_MISC, 8.0 * (double)nnz_hint + 12.0 * (double)n_rows,
+              (row_sqnorm_kernel<<<grid_for((n_rows + 7) / 8, 8), 256, 0, L.stream>>>(d_rowptr, row0, n_rows, d_feature, d_value,
+                                                                                       (uint32_t)dims, d_out)));
+    HM_CUDA(cudaGetLastError());
+    return HM_OK;
+}
+
 hm_status launch_predict_linear(Launcher &L, const WeightView &wv, int64_t dims, int64_t n_rows, const int64_t *d_rowptr,
                                 const uint32_t *d_feature, const float *d_value, float *d_out, uint32_t *d_bad)
 {
@@ -1287,7 +1360,7 @@ hm_status launch_predict_linear(Launcher &L, const WeightView &wv, int64_t dims,
     P.wv = wv; P.rowptr = d_rowptr; P.feature = d_feature; P.value = d_value; P.label = nullptr;
     P.margin = d_out; P.dloss = nullptr;
     P.block_row0 = 0; P.row0 = 0; P.n_rows = (int32_t)n_rows;
-    P.task = 0; P.loss = 0; P.train = 0;
+    P.task = 0; P.loss = 0; P.train = 0; P.sqnorm = nullptr; P.pa_c = 0.f; P.pa_eps = 0.f;
     P.dims = (uint32_t)dims; P.bad = d_bad;
     P.hot = nullptr; P.hot_sum = nullptr; P.hot_cnt = nullptr; P.hot_stride = 0; P.lpr = 32;
     const int grid = grid_for((n_rows + 7) / 8, 8);
@@ -1381,6 +1454,7 @@ hm_status launch_linear_small_batches(Launcher &L, const LinearArgs &a, const in
     P.F.wv = a.wv; P.F.rowptr = d_rowptr; P.F.feature = d_feature; P.F.value = d_value; P.F.label = d_label;
     P.F.margin = d_margin; P.F.dloss = d_dloss; P.F.block_row0 = block_row0;
     P.F.task = a.cfg.task; P.F.loss = a.cfg.loss; P.F.train = 1; P.F.dims = (uint32_t)a.cfg.dims; P.F.bad = d_bad;
+    P.F.sqnorm = a.sqnorm; P.F.pa_c = a.cfg.pa_c; P.F.pa_eps = a.cfg.pa_epsilon;
     P.U.rec = a.rec; P.U.rec_width = a.rec_width; P.U.ftrl_derived = a.wv.ftrl; P.U.touched = nullptr;
     P.U.skey = d_sorted_key; P.U.spay = d_sorted_pay; P.U.dloss = d_dloss; P.U.seg_off = d_seg_off;
     P.U.dims = (uint32_t)a.cfg.dims; P.U.opt = a.cfg.opt; P.U.reg = a.cfg.reg; P.U.grad_norm = a.cfg.grad_norm;

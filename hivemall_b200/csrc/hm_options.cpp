@@ -91,6 +91,8 @@ static void defaults(hm_config *c, int task)
     c->seed = 31;
     c->mix_interval = 0;
     c->hash_seed = 0x9747b28cu;
+    c->pa_c = 1.0f;
+    c->pa_epsilon = 0.1f;
 }
 
 hm_status parse_options(const char *function_name, const char *options, hm_config *out)
@@ -98,12 +100,26 @@ hm_status parse_options(const char *function_name, const char *options, hm_confi
     if (!function_name || !out) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "function_name and out must not be NULL");
     std::string fn = function_name;
     int task;
+    int online = -1;        // the loss id of an online learner (its function fixes loss and optimizer)
     if (fn == "train_classifier") task = HM_TASK_CLASSIFIER;
     else if (fn == "train_regressor") task = HM_TASK_REGRESSOR;
     else if (fn == "train_fm") task = HM_TASK_FM;
-    else HM_FAIL(HM_ERR_INVALID_ARGUMENT, "unknown function '%s' (expected train_classifier, train_regressor or train_fm)", function_name);
+    else if (fn == "train_perceptron") { task = HM_TASK_CLASSIFIER; online = HM_LOSS_PERCEPTRON; }
+    else if (fn == "train_pa") { task = HM_TASK_CLASSIFIER; online = HM_LOSS_PA; }
+    else if (fn == "train_pa1") { task = HM_TASK_CLASSIFIER; online = HM_LOSS_PA1; }
+    else if (fn == "train_pa2") { task = HM_TASK_CLASSIFIER; online = HM_LOSS_PA2; }
+    else if (fn == "train_pa1_regr") { task = HM_TASK_REGRESSOR; online = HM_LOSS_PA1_REGR; }
+    else if (fn == "train_pa2_regr") { task = HM_TASK_REGRESSOR; online = HM_LOSS_PA2_REGR; }
+    else HM_FAIL(HM_ERR_INVALID_ARGUMENT, "unknown function '%s' (expected train_classifier, train_regressor, train_fm, "
+                 "train_perceptron, train_pa, train_pa1, train_pa2, train_pa1_regr or train_pa2_regr)", function_name);
     hm_config c;
     defaults(&c, task);
+    if (online >= 0) {
+        // the step size lives in the per-row coefficient: the "optimizer" only subtracts the mean of coef * x
+        c.loss = online; c.opt = HM_OPT_SGD; c.eta_sched = HM_ETA_FIXED; c.eta0 = 1.0f; c.reg = HM_REG_NONE;
+    }
+    const bool takes_c = online == HM_LOSS_PA1 || online == HM_LOSS_PA2 || online == HM_LOSS_PA1_REGR || online == HM_LOSS_PA2_REGR;
+    const bool takes_eps = online == HM_LOSS_PA1_REGR || online == HM_LOSS_PA2_REGR;
 
     std::vector<std::string> tok;
     {
@@ -117,7 +133,7 @@ hm_status parse_options(const char *function_name, const char *options, hm_confi
         if (name.size() < 2 || name[0] != '-')
             HM_FAIL(HM_ERR_INVALID_ARGUMENT, "expected an option starting with '-', got '%s'", name.c_str());
         // ---- flags
-        if (name == "-classification" || name == "-c") {
+        if (name == "-classification" || (name == "-c" && online < 0)) {
             if (task != HM_TASK_FM) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "%s is a train_fm option", name.c_str());
             c.fm_classification = 1;
             continue;
@@ -146,7 +162,18 @@ hm_status parse_options(const char *function_name, const char *options, hm_confi
         };
 #define NEED_F(lo, hi) if (!need_f((lo), (hi))) return HM_ERR_INVALID_ARGUMENT
 #define NEED_I(lo, hi) if (!need_i((lo), (hi))) return HM_ERR_INVALID_ARGUMENT
-        if (name == "-loss" || name == "-loss_function") {
+        if (online >= 0 && (name == "-loss" || name == "-loss_function" || name == "-opt" || name == "-optimizer" ||
+                            name == "-eta" || name == "-eta0" || name == "-eta_0" || name == "-power_t" ||
+                            name == "-total_steps" || name == "-t" || name == "-reg" || name == "-regularization" ||
+                            name == "-lambda"))
+            HM_FAIL(HM_ERR_INVALID_ARGUMENT, "%s is fixed by %s", name.c_str(), function_name);
+        if (name == "-c" || name == "-aggressiveness") {
+            if (!takes_c) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "%s is an option of train_pa1, train_pa2 and their _regr forms", name.c_str());
+            NEED_F(1e-12, 1e12); c.pa_c = (float)d;
+        } else if (name == "-epsilon" || name == "-e") {
+            if (!takes_eps) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "%s is an option of train_pa1_regr and train_pa2_regr", name.c_str());
+            NEED_F(0.0, 1e12); c.pa_epsilon = (float)d;
+        } else if (name == "-loss" || name == "-loss_function") {
             if (task == HM_TASK_FM) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "-loss is not a train_fm option (use -classification)");
             if (lv == "logloss" || lv == "logistic" || lv == "log") c.loss = HM_LOSS_LOG;
             else if (lv == "hinge" || lv == "hingeloss") c.loss = HM_LOSS_HINGE;
@@ -231,7 +258,7 @@ hm_status parse_options(const char *function_name, const char *options, hm_confi
     // cross-option checks
     if (task == HM_TASK_CLASSIFIER && c.loss == HM_LOSS_SQUARED && loss_given)
         ;  // allowed: squared loss on +-1 targets
-    if (task == HM_TASK_REGRESSOR && c.loss != HM_LOSS_SQUARED)
+    if (task == HM_TASK_REGRESSOR && online < 0 && c.loss != HM_LOSS_SQUARED)
         HM_FAIL(HM_ERR_INVALID_ARGUMENT, "train_regressor supports -loss squared only");
     if (task == HM_TASK_FM && c.opt != HM_OPT_SGD && c.opt != HM_OPT_ADAGRAD)
         HM_FAIL(HM_ERR_INVALID_ARGUMENT, "train_fm supports -opt sgd or adagrad");

@@ -466,3 +466,55 @@ def train_regressor(options: str = "", device: int = 0) -> TrainRegressorUDTF:
 
 def train_fm(options: str = "", device: int = 0) -> FactorizationMachineUDTF:
     return FactorizationMachineUDTF(options, device)
+
+
+# ---- online learners that share the mini-batch skeleton -----------------------------------
+# Rosenblatt's perceptron and the passive-aggressive family of Crammer et al. (JMLR 2006): the function fixes the
+# loss, the optimizer is plain SGD with eta = 1, the step size lives in the per-row coefficient.
+
+class PerceptronUDTF(UDTF):
+    function_name = "train_perceptron"
+
+
+class PassiveAggressiveUDTF(UDTF):
+    function_name = "train_pa"
+
+
+class PassiveAggressive1UDTF(UDTF):
+    function_name = "train_pa1"
+
+
+class PassiveAggressive2UDTF(UDTF):
+    function_name = "train_pa2"
+
+
+class PassiveAggressive1RegressionUDTF(UDTF):
+    function_name = "train_pa1_regr"
+
+
+class PassiveAggressive2RegressionUDTF(UDTF):
+    function_name = "train_pa2_regr"
+
+
+def train_perceptron(options: str = "", device: int = 0) -> PerceptronUDTF:
+    return PerceptronUDTF(options, device)
+
+
+def train_pa(options: str = "", device: int = 0) -> PassiveAggressiveUDTF:
+    return PassiveAggressiveUDTF(options, device)
+
+
+def train_pa1(options: str = "", device: int = 0) -> PassiveAggressive1UDTF:
+    return PassiveAggressive1UDTF(options, device)
+
+
+def train_pa2(options: str = "", device: int = 0) -> PassiveAggressive2UDTF:
+    return PassiveAggressive2UDTF(options, device)
+
+
+def train_pa1_regr(options: str = "", device: int = 0) -> PassiveAggressive1RegressionUDTF:
+    return PassiveAggressive1RegressionUDTF(options, device)
+
+
+def train_pa2_regr(options: str = "", device: int = 0) -> PassiveAggressive2RegressionUDTF:
+    return PassiveAggressive2RegressionUDTF(options, device)

@@ -44,7 +44,12 @@ typedef enum hm_status {
 } hm_status;
 
 enum { HM_TASK_CLASSIFIER = 0, HM_TASK_REGRESSOR = 1, HM_TASK_FM = 2 };
-enum { HM_LOSS_LOG = 0, HM_LOSS_HINGE = 1, HM_LOSS_SQUARED = 2 };
+enum { HM_LOSS_LOG = 0, HM_LOSS_HINGE = 1, HM_LOSS_SQUARED = 2,
+       /* the online learners that share the mini-batch skeleton (train_perceptron, train_pa, train_pa1, train_pa2,
+        * train_pa1_regr, train_pa2_regr): the per-row coefficient is the learner's step size times the sign of
+        * the correction instead of a loss derivative, and the optimizer is plain SGD with eta = 1 */
+       HM_LOSS_PERCEPTRON = 3, HM_LOSS_PA = 4, HM_LOSS_PA1 = 5, HM_LOSS_PA2 = 6,
+       HM_LOSS_PA1_REGR = 7, HM_LOSS_PA2_REGR = 8 };
 enum { HM_OPT_SGD = 0, HM_OPT_ADAGRAD = 1, HM_OPT_ADADELTA = 2, HM_OPT_ADAM = 3, HM_OPT_FTRL = 4 };
 enum { HM_ETA_FIXED = 0, HM_ETA_INVERSE = 1, HM_ETA_SIMPLE = 2 };
 enum { HM_REG_NONE = 0, HM_REG_L1 = 1, HM_REG_L2 = 2 };
@@ -70,7 +75,9 @@ typedef struct hm_config {
     int32_t mix_interval;    /* mini-batches between model averagings, for the CALLER's MIX loop (0 = its choice):
                               * the library itself never communicates, see hm_udtf_array / hm_udtf_scale_replica */
     uint32_t hash_seed;      /* MurmurHash3 seed used by feature hashing */
-    int32_t reserved[8];
+    float   pa_c;            /* passive-aggressive learners: aggressiveness C (PA-I cap, PA-II slack) */
+    float   pa_epsilon;      /* ... regression: width of the insensitive zone */
+    int32_t reserved[6];
 } hm_config;
 
 typedef struct hm_udtf hm_udtf; /* opaque learner = one UDTF instance on one GPU */
@@ -116,7 +123,12 @@ hm_status hm_feature_hashing(const uint8_t *bytes, const int64_t *offsets, int64
 
 /* ---- option strings (stands in for the UDTF's getOptions/processOptions) --- */
 
-/* function_name: "train_classifier" | "train_regressor" | "train_fm".
+/* function_name: "train_classifier" | "train_regressor" | "train_fm", or one of the online learners on the
+ * same skeleton: "train_perceptron" | "train_pa" | "train_pa1" | "train_pa2" (labels as train_classifier) |
+ * "train_pa1_regr" | "train_pa2_regr" (targets as train_regressor).  Those fix loss, optimizer (SGD), eta (1)
+ * and regularisation (none) themselves and take -mini_batch, -iters, -dims, -grad_norm, -mix_interval,
+ * -hash_seed, plus -c / -aggressiveness (train_pa1, train_pa2, *_regr; default 1) and -epsilon / -e (*_regr;
+ * default 0.1).
  * Unknown options, missing values and out-of-range numbers are
  * HM_ERR_INVALID_ARGUMENT with the offending token in hm_last_error(). */
 hm_status hm_parse_options(const char *function_name, const char *options, hm_config *out);

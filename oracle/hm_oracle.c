@@ -100,9 +100,44 @@ float hmo_dloss(int32_t loss, float m, float y)
     }
 }
 
+float hmo_row_coef(const hmo_config *c, float m, float y, float xx)
+{
+    const int32_t loss = c->loss;
+    if (loss <= HMO_LOSS_SQUARED) return hmo_dloss(loss, m, y);
+    if (loss == HMO_LOSS_PERCEPTRON) return (y * m <= 0.0f) ? -y : 0.0f;
+    float l, dir;
+    if (loss == HMO_LOSS_PA1_REGR || loss == HMO_LOSS_PA2_REGR) {
+        const float e = y - m;                      /* epsilon-insensitive loss */
+        l = fabsf(e) - c->pa_epsilon;
+        dir = e < 0.0f ? -1.0f : 1.0f;
+    } else {
+        l = 1.0f - y * m;                           /* hinge loss */
+        dir = y;
+    }
+    if (!(l > 0.0f)) return 0.0f;
+    float tau;
+    if (loss == HMO_LOSS_PA2 || loss == HMO_LOSS_PA2_REGR) tau = l / (xx + 0.5f / c->pa_c);
+    else {
+        if (!(xx > 0.0f)) return 0.0f;
+        tau = l / xx;
+        if (loss != HMO_LOSS_PA) tau = fminf(c->pa_c, tau);
+    }
+    return -(tau * dir);
+}
+
+static inline float row_sqnorm(const int64_t *rowptr, const float *val, int64_t i)
+{
+    double acc = 0.0;
+    for (int64_t p = rowptr[i]; p < rowptr[i + 1]; p++) acc += (double)(val[p] * val[p]);
+    return (float)acc;
+}
+
 double hmo_loss(int32_t loss, float m, float y)
 {
     double z = (double)y * (double)m;
+    if (loss == HMO_LOSS_PERCEPTRON) return z <= 0.0 ? -z : 0.0;
+    if (loss == HMO_LOSS_PA || loss == HMO_LOSS_PA1 || loss == HMO_LOSS_PA2) loss = HMO_LOSS_HINGE;
+    if (loss == HMO_LOSS_PA1_REGR || loss == HMO_LOSS_PA2_REGR) return fabs((double)y - (double)m);   /* (epsilon not known here) */
     switch (loss) {
     case HMO_LOSS_LOG:   return z > 0 ? log1p(exp(-z)) : -z + log1p(exp(z));
     case HMO_LOSS_HINGE: return z < 1.0 ? 1.0 - z : 0.0;
@@ -241,7 +276,7 @@ int hmo_train_linear(const hmo_config *c, int64_t n_rows, const int64_t *rowptr,
                 }
                 float m = (float)acc;
                 float y = target_of(c, label[i]);
-                dl[i - b0] = hmo_dloss(c->loss, m, y);
+                dl[i - b0] = hmo_row_coef(c, m, y, c->loss >= HMO_LOSS_PA ? row_sqnorm(rowptr, val, i) : 0.0f);
                 lsum += hmo_loss(c->loss, m, y);
                 if (margins) margins[i] = m;
             }
@@ -328,7 +363,8 @@ int hmo_train_linear_mt(const hmo_config *c, int64_t n_rows, const int64_t *rowp
                         acc += (double)(w[idx[p]] * val[p]);
                         my[idx[p] / per_owner + 1]++;
                     }
-                    dl[i - b0] = hmo_dloss(c->loss, (float)acc, target_of(c, label[i]));
+                    dl[i - b0] = hmo_row_coef(c, (float)acc, target_of(c, label[i]),
+                                              c->loss >= HMO_LOSS_PA ? row_sqnorm(rowptr, val, i) : 0.0f);
                 }
                 /* bucket offsets inside this thread's region of `pairs` (region = its element range) */
                 const int64_t base = rowptr[r0] - e0;

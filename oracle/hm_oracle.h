@@ -23,7 +23,11 @@ extern "C" {
 #endif
 
 enum { HMO_TASK_CLASSIFIER = 0, HMO_TASK_REGRESSOR = 1 };
-enum { HMO_LOSS_LOG = 0, HMO_LOSS_HINGE = 1, HMO_LOSS_SQUARED = 2 };
+enum { HMO_LOSS_LOG = 0, HMO_LOSS_HINGE = 1, HMO_LOSS_SQUARED = 2,
+       /* online learners on the mini-batch skeleton: perceptron (Rosenblatt 1958) and the
+        * passive-aggressive family (Crammer, Dekel, Keshet, Shalev-Shwartz, Singer, JMLR 2006) */
+       HMO_LOSS_PERCEPTRON = 3, HMO_LOSS_PA = 4, HMO_LOSS_PA1 = 5, HMO_LOSS_PA2 = 6,
+       HMO_LOSS_PA1_REGR = 7, HMO_LOSS_PA2_REGR = 8 };
 enum { HMO_OPT_SGD = 0, HMO_OPT_ADAGRAD = 1, HMO_OPT_ADADELTA = 2, HMO_OPT_ADAM = 3, HMO_OPT_FTRL = 4 };
 enum { HMO_ETA_FIXED = 0, HMO_ETA_INVERSE = 1, HMO_ETA_SIMPLE = 2 };
 enum { HMO_REG_NONE = 0, HMO_REG_L1 = 1, HMO_REG_L2 = 2 };
@@ -48,6 +52,9 @@ typedef struct hmo_config {
     float   sigma;                /* V init half-width */
     float   lambda_w0, lambda_w, lambda_v;
     uint32_t seed;
+    /* passive-aggressive learners */
+    float   pa_c;                 /* aggressiveness C */
+    float   pa_epsilon;           /* regression: insensitive zone */
 } hmo_config;
 
 /* MurmurHash3_x86_32 (Appleby, public domain algorithm). */
@@ -62,6 +69,9 @@ void hmo_mhash_batch(const uint8_t *bytes, const int64_t *offsets, int64_t n,
 float hmo_exp(float x);
 /* dloss/dmargin for one row; y is +-1 for classifier losses, the target otherwise. */
 float hmo_dloss(int32_t loss, float margin, float y);
+/* The number that takes dloss's place for a row, any loss id: hmo_dloss for the three losses, else the
+ * online learner's -(step size) * (direction); xx = |x|^2 of the row (fp32 squares, fp64 sum, rounded once). */
+float hmo_row_coef(const hmo_config *c, float margin, float y, float xx);
 /* loss value in double (reporting only). */
 double hmo_loss(int32_t loss, float margin, float y);
 

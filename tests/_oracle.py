@@ -21,7 +21,7 @@ class HmoConfig(C.Structure):
         ("alpha", C.c_float), ("beta", C.c_float), ("lambda1", C.c_float), ("lambda2", C.c_float),
         ("factors", C.c_int32), ("fm_classification", C.c_int32), ("sigma", C.c_float),
         ("lambda_w0", C.c_float), ("lambda_w", C.c_float), ("lambda_v", C.c_float),
-        ("seed", C.c_uint32),
+        ("seed", C.c_uint32), ("pa_c", C.c_float), ("pa_epsilon", C.c_float),
     ]
 
 
@@ -113,14 +113,24 @@ _OPTION_FIELDS = {
     "-lambdaW": ("lambda_w", float), "-lambda_w": ("lambda_w", float), "-lambdaV": ("lambda_v", float),
     "-lambda_v": ("lambda_v", float), "-seed": ("seed", int),
     "-hash_seed": (None, int), "-mix_interval": (None, int),     # not oracle fields
+    "-aggressiveness": ("pa_c", float), "-epsilon": ("pa_epsilon", float), "-e": ("pa_epsilon", float),
 }
+# online learners on the mini-batch skeleton: function -> (task, loss id)
+_ONLINE = {"train_perceptron": (0, 3), "train_pa": (0, 4), "train_pa1": (0, 5), "train_pa2": (0, 6),
+           "train_pa1_regr": (1, 7), "train_pa2_regr": (1, 8)}
+_ONLINE_FIXED = {"-loss", "-loss_function", "-opt", "-optimizer", "-eta", "-eta0", "-eta_0", "-power_t", "-total_steps",
+                 "-t", "-reg", "-regularization", "-lambda"}
 
 
 def config_from_options(function_name: str, options: str = "") -> HmoConfig:
     """Oracle config of a UDTF option string (no product code involved)."""
-    task = {"train_classifier": 0, "train_regressor": 1, "train_fm": 2}[function_name]
+    online = _ONLINE.get(function_name)
+    task = online[0] if online else {"train_classifier": 0, "train_regressor": 1, "train_fm": 2}[function_name]
+    takes_c = bool(online) and online[1] in (5, 6, 7, 8)
+    takes_eps = bool(online) and online[1] in (7, 8)
     c = HmoConfig()
     c.task = task
+    c.pa_c, c.pa_epsilon = 1.0, 0.1
     c.loss = 2 if task == 1 else 0
     c.opt = 0 if task == 2 else 1
     c.eta_sched, c.reg, c.grad_norm, c.mini_batch, c.iters = 0, 0, 0, 1, 1
@@ -130,18 +140,28 @@ def config_from_options(function_name: str, options: str = "") -> HmoConfig:
     c.factors, c.fm_classification, c.sigma = 5, 0, 0.1
     c.lambda_w0 = c.lambda_w = c.lambda_v = 0.01
     c.seed = 31
+    if online:
+        c.loss, c.opt, c.eta0 = online[1], 0, 1.0
     tok = options.split()
     i = 0
     while i < len(tok):
         name = tok[i]
         i += 1
-        if name in ("-classification", "-c"):
+        if name == "-classification" or (name == "-c" and not online):
             if task != 2:
                 raise ValueError(f"{name} is a train_fm option")
             c.fm_classification = 1
             continue
         if name in ("-dense", "-densemodel"):
             continue
+        if online and name in _ONLINE_FIXED:
+            raise ValueError(f"{name} is fixed by {function_name}")
+        if name in ("-c", "-aggressiveness") and not takes_c:
+            raise ValueError(f"{name} is an option of train_pa1, train_pa2 and their _regr forms")
+        if name in ("-epsilon", "-e") and not takes_eps:
+            raise ValueError(f"{name} is an option of train_pa1_regr and train_pa2_regr")
+        if name == "-c":
+            name = "-aggressiveness"
         if name not in _OPTION_FIELDS:
             raise ValueError(f"unknown option {name!r}")
         if i >= len(tok):
@@ -158,7 +178,7 @@ def config_from_options(function_name: str, options: str = "") -> HmoConfig:
             setattr(c, field, table[v.lower()])
         else:
             setattr(c, field, kind(v))
-    if task == 1 and c.loss != 2:
+    if task == 1 and not online and c.loss != 2:
         raise ValueError("train_regressor supports -loss squared only")
     if task == 2:
         c.loss = 0 if c.fm_classification else 2

@@ -1,0 +1,121 @@
+"""The online learners on the CUDA path against the oracle: perceptron and the passive-aggressive family run
+through the same forward / sort / update kernels as train_classifier, with the step size in the per-row
+coefficient (hm_linear.cu: online_coef, row_sqnorm_kernel).  Every launch shape is covered: the persistent
+small-batch kernel (-mini_batch 1, 128), the two-kernel path with and without hot features, rows worked on
+by half a warp, several pushes, replays.
+
+PARITY UNPINNED w.r.t. Hivemall (no reference source is mounted); checked against oracle/.
+"""
+import numpy as np
+import pytest
+
+import hivemall_b200 as hm
+from hivemall_b200 import synth
+
+from _util import assert_weights_close, run_gpu_linear, run_oracle_linear
+
+pytestmark = pytest.mark.gpu
+
+CLASSIFIERS = ["train_perceptron", "train_pa", "train_pa1", "train_pa2"]
+REGRESSORS = ["train_pa1_regr", "train_pa2_regr"]
+
+
+def check(fn, options, data, pushes=None):
+    u, w, _ = run_gpu_linear(fn, options, data, pushes=pushes)
+    ref, _ = run_oracle_linear(fn, options, data)
+    assert u.step == ref.t
+    assert_weights_close(w, ref.w)
+    assert np.count_nonzero(ref.w) > 0
+    u.destroy()
+    return w
+
+
+@pytest.mark.parametrize("fn", CLASSIFIERS)
+@pytest.mark.parametrize("mb", [1, 128])
+def test_small_batches_a9a_shaped(fn, mb):
+    data = synth.a9a_like(2048 + 37, seed=2)
+    extra = " -c 0.1" if fn in ("train_pa1", "train_pa2") else ""
+    check(fn, f"-dims 124 -mini_batch {mb} -iters 2{extra}", data)
+
+
+@pytest.mark.parametrize("fn", REGRESSORS)
+@pytest.mark.parametrize("mb", [1, 100])
+def test_small_batches_regression(fn, mb):
+    data = synth.ragged(3000, dims=256, max_nnz=12, seed=5, regression=True)
+    check(fn, f"-dims 256 -mini_batch {mb} -c 0.5 -epsilon 0.05", data)
+
+
+@pytest.mark.parametrize("fn", CLASSIFIERS + REGRESSORS)
+@pytest.mark.parametrize("hot", ["1", "0"])
+def test_two_kernel_path_criteo_shaped(monkeypatch, fn, hot):
+    """Mini-batches of 4096 Criteo-shaped rows: quantitative columns with real values (|x|^2 is not the row
+    length), hot features reduced in the forward kernel."""
+    monkeypatch.setenv("HM_HOT_FEATURES", hot)
+    dims = 1 << 18
+    data = synth.criteo_like(3 * 4096 + 555, dims=dims, seed=7)
+    if fn in REGRESSORS:
+        rng = np.random.default_rng(1)
+        import torch
+        data.label = data.label * 2.0 + torch.from_numpy(rng.normal(0, 0.3, data.rows).astype(np.float32))
+    norm = " -grad_norm count" if fn in ("train_pa", "train_pa2_regr") else ""
+    check(fn, f"-dims {dims} -mini_batch 4096{norm}", data, pushes=[5000, 4096 * 2, 10000])
+
+
+@pytest.mark.parametrize("lpr", ["16", "8"])
+def test_rows_side_by_side(monkeypatch, lpr):
+    monkeypatch.setenv("HM_FWD_LPR", lpr)
+    dims = 1 << 16
+    data = synth.criteo_like(2 * 2048 + 100, dims=dims, seed=9)
+    check("train_pa1", f"-dims {dims} -mini_batch 2048 -c 0.2", data)
+    monkeypatch.setenv("HM_HOT_FEATURES", "0")
+    check("train_pa2", f"-dims {dims} -mini_batch 2048 -c 0.2", data)
+
+
+def test_out_of_range_elements_do_not_count_in_the_norm():
+    """An index >= dims is ignored everywhere, also in |x|^2: the model is what the oracle gets for the rows
+    without that element (and close() reports it)."""
+    data = synth.ragged(4096, dims=512, max_nnz=10, seed=11)
+    rowptr, feature, value, label = data.numpy()
+    bad_f = feature.copy()
+    r = 1234 + int(np.argmax(np.diff(rowptr[1234:]) > 1))       # a row with at least two elements
+    assert rowptr[r + 1] - rowptr[r] > 1
+    p = int(rowptr[r])
+    bad_f[p] = 512 + 9
+    options = "-dims 512 -mini_batch 2048"
+    u = hm.UDTF(options, 0, function_name="train_pa")
+    u.process_batch(rowptr, bad_f, value, label)
+    with pytest.raises(hm.UDFArgumentError):
+        u.close()
+    w = u.array_to_host("w")
+    # the same rows with that element removed
+    keep = np.ones(len(feature), bool)
+    keep[p] = False
+    rp2 = rowptr.copy()
+    rp2[r + 1:] -= 1
+    clean = synth.Csr(*(__import__("torch").from_numpy(a) for a in (rp2, feature[keep], value[keep], label)))
+    ref, _ = run_oracle_linear("train_pa", options, clean)
+    assert_weights_close(w, ref.w)
+    u.destroy()
+
+
+def test_replays_and_determinism():
+    dims = 1 << 16
+    data = synth.criteo_like(3 * 2048, dims=dims, seed=13)
+    options = f"-dims {dims} -mini_batch 2048 -iters 3 -c 0.05"
+    w1 = check("train_pa1", options, data)
+    u, w2, _ = run_gpu_linear("train_pa1", options, data)
+    assert np.array_equal(w1, w2)
+    u.destroy()
+
+
+def test_model_table_and_prediction():
+    data = synth.a9a_like(4096, seed=3)
+    rowptr, feature, value, label = data.numpy()
+    with hm.train_pa1("-dims 124 -mini_batch 64 -c 0.05") as u:
+        u.process_batch(rowptr, feature, value, label)
+        u.close()
+        feat, wt = u.forward()[:2]
+        w = u.array_to_host("w")
+        assert np.all(np.diff(feat) > 0) and np.array_equal(wt, w[feat]) and set(np.flatnonzero(w)) <= set(feat.tolist())
+        import torch
+        assert synth.auc(torch.from_numpy(u.predict(rowptr, feature, value)), torch.from_numpy(label)) > 0.7

@@ -1,0 +1,96 @@
+"""The online learners that share the mini-batch skeleton: Rosenblatt's
+perceptron and the passive-aggressive family (Crammer, Dekel, Keshet, Shalev-Shwartz, Singer, JMLR 2006) --
+the oracle's statement of them checked against what the papers promise.  CPU only.
+
+PARITY UNPINNED w.r.t. Hivemall (no reference source is mounted): which learners its base class carries,
+their option names and how they behave under -mini_batch are not known here; DESIGN.md 3.10 states
+this library's contract.
+"""
+import numpy as np
+import pytest
+
+import hivemall_b200 as hm
+from hivemall_b200 import synth
+
+import _oracle
+
+
+def one_row(fn, options, f, v, y, w0=None, dims=16):
+    cfg = _oracle.config_from(hm.parse_options(fn, f"-dims {dims} " + options))
+    rp = np.array([0, len(f)], dtype=np.int64)
+    w = np.zeros(dims, np.float32) if w0 is None else np.asarray(w0, np.float32).copy()
+    res = _oracle.train_linear(cfg, rp, np.asarray(f), np.asarray(v, np.float32), np.asarray([y], np.float32), w=w)
+    return res.w
+
+
+def test_pa_step_lands_on_the_margin():
+    """PA: after the step the row's margin is exactly 1 (the smallest change of w that removes the loss)."""
+    f, v = [1, 5, 9], [0.5, -2.0, 1.5]
+    w = one_row("train_pa", "", f, v, 1.0)
+    assert abs(float(np.dot(w[f], v)) - 1.0) < 1e-6
+    w = one_row("train_pa", "", f, v, 0.0)          # label <= 0 is the negative class
+    assert abs(float(np.dot(w[f], v)) + 1.0) < 1e-6
+
+
+def test_pa1_caps_the_step_and_pa2_softens_it():
+    f, v = [2, 3], [1.0, 1.0]                       # |x|^2 = 2, loss at w = 0 is 1: PA's tau = 0.5
+    assert np.allclose(one_row("train_pa", "", f, v, 1.0)[f], 0.5)
+    assert np.allclose(one_row("train_pa1", "-c 0.1", f, v, 1.0)[f], 0.1)          # min(C, 0.5)
+    assert np.allclose(one_row("train_pa1", "-c 10", f, v, 1.0)[f], 0.5)
+    assert np.allclose(one_row("train_pa2", "-c 1", f, v, 1.0)[f], 1.0 / (2 + 0.5))  # l / (|x|^2 + 1/(2C))
+
+
+def test_no_loss_no_step():
+    f, v = [0, 7], [1.0, 2.0]
+    w0 = np.zeros(16, np.float32)
+    w0[0], w0[7] = 1.0, 1.0                          # margin 3
+    for fn in ("train_perceptron", "train_pa", "train_pa1", "train_pa2"):
+        assert np.array_equal(one_row(fn, "", f, v, 1.0, w0), w0), fn
+    # regression: inside the insensitive zone nothing moves, outside the step stops at its edge
+    assert np.array_equal(one_row("train_pa1_regr", "-epsilon 0.5", f, v, 3.3, w0), w0)
+    w = one_row("train_pa1_regr", "-epsilon 0.5 -c 100", f, v, 5.0, w0)
+    assert abs(float(np.dot(w[f], v)) - 4.5) < 1e-6
+    w = one_row("train_pa1_regr", "-epsilon 0.5 -c 100", f, v, 1.0, w0)
+    assert abs(float(np.dot(w[f], v)) - 1.5) < 1e-6
+
+
+def test_perceptron_moves_by_the_row_on_a_mistake():
+    f, v = [4, 6], [2.0, -1.0]
+    assert np.allclose(one_row("train_perceptron", "", f, v, 1.0)[f], v)           # margin 0 counts as a mistake
+    assert np.allclose(one_row("train_perceptron", "", f, v, -1.0)[f], np.negative(v))
+
+
+def test_empty_row_and_zero_row_are_harmless():
+    for fn in ("train_pa", "train_pa1", "train_pa2", "train_pa2_regr"):
+        assert not one_row(fn, "", [], [], 1.0).any()
+        assert np.isfinite(one_row(fn, "", [3], [0.0], 1.0)).all()
+
+
+@pytest.mark.parametrize("fn", ["train_perceptron", "train_pa", "train_pa1", "train_pa2"])
+def test_classifiers_learn_a_separable_problem(fn):
+    data = synth.a9a_like(4096, seed=1)
+    rp, f, v, y = data.numpy()
+    cfg = _oracle.config_from(hm.parse_options(fn, "-dims 124 -mini_batch 1 -iters 2"))
+    res = _oracle.train_linear(cfg, rp, f, v, y)
+    import torch
+    assert synth.auc(torch.from_numpy(_oracle.predict_linear(rp, f, v, res.w)), torch.from_numpy(y)) > 0.7     # (noisy labels: the last iterate of an online learner wanders)
+
+
+@pytest.mark.parametrize("fn", ["train_pa1_regr", "train_pa2_regr"])
+def test_regressors_reduce_the_error(fn):
+    data = synth.ragged(3000, dims=64, max_nnz=8, seed=4, regression=True)
+    rp, f, v, y = data.numpy()
+    cfg = _oracle.config_from(hm.parse_options(fn, "-dims 64 -mini_batch 1 -iters 3 -epsilon 0.01"))
+    res = _oracle.train_linear(cfg, rp, f, v, y)
+    err = np.abs(_oracle.predict_linear(rp, f, v, res.w) - y).mean()
+    assert err < 0.5 * np.abs(y).mean()
+
+
+@pytest.mark.parametrize("fn", ["train_pa1", "train_pa2_regr"])
+def test_openmp_variant_is_bit_identical(fn):
+    data = synth.criteo_like(2000, dims=1 << 12, seed=3)
+    rp, f, v, y = data.numpy()
+    cfg = _oracle.config_from(hm.parse_options(fn, f"-mini_batch 128 -dims {1 << 12} -iters 2 -c 0.5"))
+    a = _oracle.train_linear(cfg, rp, f, v, y)
+    b = _oracle.train_linear_mt(cfg, rp, f, v, y, 4)
+    assert np.array_equal(a.w, b.w) and a.t == b.t

@@ -46,6 +46,14 @@ def test_numeric_options_round_trip():
     ("train_fm", "-opt adam"),
     ("train_fm", "-loss logloss"),
     ("train_everything", ""),
+    ("train_pa", "-c 1"),                       # plain PA has no aggressiveness
+    ("train_perceptron", "-eta0 0.5"),          # fixed by the function
+    ("train_pa1", "-loss hinge"),
+    ("train_pa1", "-opt adagrad"),
+    ("train_pa1", "-epsilon 0.1"),              # regression only
+    ("train_pa2", "-c 0"),
+    ("train_pa2", "-c"),
+    ("train_classifier", "-aggressiveness 1"),
     ("train_classifier", "-eta0 nan"),
     ("train_classifier", "-dims -5"),
 ])
@@ -69,6 +77,12 @@ def test_error_names_the_offending_token():
     ("train_fm", "-factors 16 -classification -opt adagrad -mini_batch 65536 -dims 16777216 -eta0 0.05"),
     ("train_fm", "-factors 8 -sigma 0.2 -lambda0 0.1 -lambdaW 0.2 -lambdaV 0.3 -seed 5"),
     ("train_fm", ""),
+    ("train_perceptron", "-mini_batch 16 -dims 1000 -iters 2"),
+    ("train_pa", "-mini_batch 1 -grad_norm count"),
+    ("train_pa1", "-c 0.25 -mini_batch 128 -dims 4096 -mix_interval 4"),
+    ("train_pa2", "-aggressiveness 3"),
+    ("train_pa1_regr", "-c 0.5 -epsilon 0.01 -mini_batch 64"),
+    ("train_pa2_regr", "-e 0.2"),
 ])
 def test_oracle_side_parser_agrees_with_the_library(fn, opts):
     """bench.py's CPU arm builds its oracle config with tests/_oracle.config_from_options so that its
@@ -78,3 +92,14 @@ def test_oracle_side_parser_agrees_with_the_library(fn, opts):
     b = _oracle.config_from_options(fn, opts)
     for name, _ in _oracle.HmoConfig._fields_:
         assert getattr(a, name) == getattr(b, name), name
+
+
+def test_online_learner_functions():
+    """The functions fix loss, optimizer and step size; C and epsilon have the stated defaults."""
+    for fn, task, loss in [("train_perceptron", 0, 3), ("train_pa", 0, 4), ("train_pa1", 0, 5), ("train_pa2", 0, 6),
+                           ("train_pa1_regr", 1, 7), ("train_pa2_regr", 1, 8)]:
+        c = hm.parse_options(fn, "")
+        assert (c.task, c.loss, c.opt, c.eta_sched, c.reg, c.mini_batch) == (task, loss, 0, 0, 0, 1), fn
+        assert c.eta0 == 1.0 and c.pa_c == 1.0 and abs(c.pa_epsilon - 0.1) < 1e-8
+    c = hm.parse_options("train_pa1_regr", "-c 0.25 -e 0.5")
+    assert c.pa_c == 0.25 and c.pa_epsilon == 0.5

@@ -73,6 +73,32 @@ def np_dloss(loss, m, y):
     return F(m - y)
 
 
+def np_row_coef(cfg, m, y, xx):
+    """The per-row coefficient for any loss id: the loss derivative, or the online learner's signed step
+    (perceptron; passive-aggressive PA / PA-I / PA-II, Crammer et al. 2006, classification and regression)."""
+    loss = cfg.loss
+    if loss <= 2:
+        return np_dloss(loss, m, y)
+    if loss == 3:
+        return F(-y) if F(y * m) <= F(0.0) else F(0.0)
+    if loss in (7, 8):
+        e = F(y - m)
+        l, d = F(abs(e) - F(cfg.pa_epsilon)), (F(-1.0) if e < 0 else F(1.0))
+    else:
+        l, d = F(F(1.0) - F(y * m)), y
+    if not l > 0:
+        return F(0.0)
+    if loss in (6, 8):
+        tau = F(l / F(xx + F(F(0.5) / F(cfg.pa_c))))
+    else:
+        if not xx > 0:
+            return F(0.0)
+        tau = F(l / xx)
+        if loss != 4:
+            tau = min(F(cfg.pa_c), tau)
+    return F(-F(tau * d))
+
+
 def np_train(cfg, rowptr, feat, val, label):
     D, B = int(cfg.dims), int(cfg.mini_batch)
     w = np.zeros(D, F); s1 = np.zeros(D, F); s2 = np.zeros(D, F)
@@ -82,11 +108,12 @@ def np_train(cfg, rowptr, feat, val, label):
             b1 = min(n, b0 + B)
             dl = []
             for i in range(b0, b1):
-                acc = 0.0
+                acc, xx = 0.0, 0.0
                 for p in range(rowptr[i], rowptr[i + 1]):
                     acc += float(F(w[feat[p]] * val[p]))
+                    xx += float(F(val[p] * val[p]))
                 y = (F(1.0) if label[i] > 0 else F(-1.0)) if cfg.task == 0 else F(label[i])
-                dl.append(np_dloss(cfg.loss, F(acc), y))
+                dl.append(np_row_coef(cfg, F(acc), y, F(xx)))
             sums, cnts = {}, {}
             for i in range(b0, b1):
                 for p in range(rowptr[i], rowptr[i + 1]):
@@ -153,9 +180,22 @@ def np_train(cfg, rowptr, feat, val, label):
     ("-loss logloss -opt adam -mini_batch 6 -dims 50 -eta0 0.05 -iters 3", "train_classifier"),
     ("-loss squared -opt adam -mini_batch 10 -dims 50 -eta0 0.01 -beta1 0.8 -beta2 0.99 -eta simple -total_steps 30", "train_regressor"),
     ("-loss hinge -opt sgd -mini_batch 7 -dims 50 -reg l1 -lambda 0.01 -eta0 0.3", "train_classifier"),
+    # online learners on the same skeleton
+    ("-mini_batch 1 -dims 50 -iters 2", "train_perceptron"),
+    ("-mini_batch 6 -dims 50", "train_perceptron"),
+    ("-mini_batch 1 -dims 50", "train_pa"),
+    ("-mini_batch 5 -dims 50 -grad_norm count -iters 2", "train_pa"),
+    ("-mini_batch 1 -dims 50 -c 0.05", "train_pa1"),
+    ("-mini_batch 9 -dims 50 -aggressiveness 0.5 -grad_norm sum", "train_pa1"),
+    ("-mini_batch 1 -dims 50 -c 0.3", "train_pa2"),
+    ("-mini_batch 4 -dims 50 -c 2", "train_pa2"),
+    ("-mini_batch 1 -dims 50 -c 0.1 -epsilon 0.05", "train_pa1_regr"),
+    ("-mini_batch 8 -dims 50 -e 0.2 -iters 2", "train_pa1_regr"),
+    ("-mini_batch 1 -dims 50 -c 0.7", "train_pa2_regr"),
+    ("-mini_batch 7 -dims 50 -c 5 -epsilon 0.01 -grad_norm count", "train_pa2_regr"),
 ])
 def test_oracle_matches_numpy_restatement(options, fn):
-    data = synth.ragged(120, dims=50, max_nnz=9, seed=2, regression=(fn == "train_regressor"))
+    data = synth.ragged(120, dims=50, max_nnz=9, seed=2, regression=fn in ("train_regressor", "train_pa1_regr", "train_pa2_regr"))
     rp, f, v, y = data.numpy()
     cfg = _oracle.config_from(hm.parse_options(fn, options))
     res = _oracle.train_linear(cfg, rp, f, v, y)
