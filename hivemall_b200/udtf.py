@@ -73,6 +73,44 @@ def feature_hashing(features: Sequence[str | bytes], num_features: int = DEFAULT
     return idx, val
 
 
+BIAS_FEATURE = 0          # the bias clause "0:1.0": feature index 0 (a name made of digits is an index already)
+BIAS_CLAUSE = "0:1.0"
+
+
+def add_bias(features: Sequence[str | bytes]) -> list:
+    """add_bias UDF: one row's feature strings with the bias clause "0:1.0" appended.  Row-level host logic
+    that stays upstream of the UDTF boundary: the rows reach process() with the bias in
+    them.  A row that already carries feature 0 gets a second one, as any repeated feature would."""
+    out = list(features)
+    out.append(BIAS_CLAUSE.encode() if out and isinstance(out[0], bytes) else BIAS_CLAUSE)
+    return out
+
+
+def add_bias_csr(rowptr, feature, value, bias_feature: int = BIAS_FEATURE, bias_value: float = 1.0):
+    """add_bias for rows that are already (index, value) pairs in CSR form: every row gets one more element
+    (bias_feature, bias_value) at its end.  value=None (index-only rows) stays None when bias_value is 1.
+    Returns (rowptr, feature, value)."""
+    rowptr = np.ascontiguousarray(rowptr, dtype=np.int64)
+    feature = np.ascontiguousarray(feature)
+    n = len(rowptr) - 1
+    base = int(rowptr[0])
+    lens = np.diff(rowptr)
+    new_rp = np.zeros(n + 1, dtype=np.int64)
+    new_rp[1:] = np.cumsum(lens + 1)
+    # position of old element p of row i: p - base + i
+    shift = np.repeat(np.arange(n, dtype=np.int64), lens)
+    src = np.arange(base, base + int(lens.sum()), dtype=np.int64)
+    new_f = np.empty(int(new_rp[-1]), dtype=feature.dtype)
+    new_f[src - base + shift] = feature[src]
+    new_f[new_rp[1:] - 1] = bias_feature
+    if value is None and bias_value == 1.0:
+        return new_rp, new_f, None
+    new_v = np.empty(int(new_rp[-1]), dtype=np.float32)
+    new_v[src - base + shift] = 1.0 if value is None else np.asarray(value, dtype=np.float32)[src]
+    new_v[new_rp[1:] - 1] = bias_value
+    return new_rp, new_f, new_v
+
+
 def host_alloc(nbytes: int) -> tuple[int, np.ndarray]:
     """Pinned host buffer (address, uint8 view).  Free with host_free(address)."""
     p = C.c_void_p()
