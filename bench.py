@@ -83,6 +83,10 @@ WORKLOADS = {
                 "16.8M rows per GPU (134M rows over 8 GPUs), replicas averaged once per pass over them",
                 "examples/sec (train_fm k=64 AdaGrad, 2^24 hashed dims, KDD12-shaped)",
                 gen="kdd12", nnz=11, mix_every=4, total_rows=4 * ROWS_PER_STEP, state_words=2, factors=64),
+    # not a BASELINE.json config: one of the online learners on the same kernels, for the record
+    "pa1": _wl("train_pa1", "-mini_batch {mb} -dims 16777216 -c 0.1",
+               "train_pa1 (passive-aggressive PA-I), 2^24 hashed dims, Criteo-shaped synthetic (39 feats/row)",
+               "examples/sec (train_pa1, 2^24 hashed dims, Criteo-shaped)", state_words=1),
 }
 
 
