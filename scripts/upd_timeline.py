@@ -4,7 +4,7 @@ import numpy as np, torch
 import hivemall_b200 as hm
 from hivemall_b200 import synth, _lib
 opt = sys.argv[1] if len(sys.argv) > 1 else "ftrl"
-mb = 65536
+mb = int(sys.argv[2]) if len(sys.argv) > 2 else 65536
 d = synth.criteo_like(mb * 6, dims=1 << 24, seed=1, device="cuda")
 u = hm.train_classifier(f"-opt {opt} -mini_batch {mb} -dims {1 << 24}")
 u.process_device(d.rows, d.nnz, d.rowptr, d.feature, d.value, d.label); u.sync()
