@@ -48,7 +48,9 @@ def main(out_dir):
     dump("options_template.json", {**mark, "cases": [
         {"function": "train_classifier", "options": "-loss logloss -opt AdaGrad -mini_batch 128",
          "fields": {"loss": 0, "opt": 1, "mini_batch": 128, "eta0": 0.1, "eps": 1e-6, "dims": 1 << 24}},
-        {"function": "train_fm", "options": "-factors 16 -classification", "fields": {"factors": 16, "loss": 0, "sigma": 0.1}}]})
+        {"function": "train_fm", "options": "-factors 16 -classification", "fields": {"factors": 16, "loss": 0, "sigma": 0.1}},
+        {"function": "train_pa1", "options": "-c 0.5 -mini_batch 4", "fields": {"loss": 5, "opt": 0, "eta0": 1.0, "pa_c": 0.5, "mini_batch": 4}},
+        {"function": "train_pa2_regr", "options": "", "fields": {"loss": 8, "pa_c": 1.0, "pa_epsilon": 0.1}}]})
     dims = 64
     for opt in ("sgd", "adagrad", "adadelta", "adam", "ftrl"):
         options = f"-loss logloss -opt {opt} -mini_batch 16 -dims {dims}"
@@ -59,6 +61,20 @@ def main(out_dir):
         dump(f"step_{opt}_template.json", {**mark, "function": "train_classifier", "options": options, "dims": dims,
                                             "rows": rows_json(rows), "before": before,
                                             "after": {"t": after["t"], **{k: _golden.sparse(after[k]) for k in ("w", "s1", "s2")}}})
+    # the online learners on the same skeleton: one mini-batch step each
+    for fn, options in (("train_perceptron", f"-mini_batch 16 -dims {dims}"),
+                        ("train_pa", f"-mini_batch 16 -dims {dims}"),
+                        ("train_pa1", f"-mini_batch 16 -dims {dims} -c 0.1"),
+                        ("train_pa2", f"-mini_batch 16 -dims {dims} -c 0.1"),
+                        ("train_pa1_regr", f"-mini_batch 16 -dims {dims} -c 0.1 -epsilon 0.05"),
+                        ("train_pa2_regr", f"-mini_batch 16 -dims {dims} -c 0.1 -epsilon 0.05")):
+        first = impl.linear(fn, options, small_rows(16, dims, 1))
+        before = {"t": first["t"], **{k: _golden.sparse(first[k]) for k in ("w", "s1", "s2")}}
+        rows = small_rows(16, dims, 2)
+        after = impl.linear(fn, options, rows, before)
+        dump(f"step_{fn}_template.json", {**mark, "function": fn, "options": options, "dims": dims,
+                                           "rows": rows_json(rows), "before": before,
+                                           "after": {"t": after["t"], **{k: _golden.sparse(after[k]) for k in ("w", "s1", "s2")}}})
     v = impl.fm_init("-factors 4 -seed 31 -sigma 0.1", dims)
     dump("fm_init_template.json", {**mark, "options": "-factors 4 -seed 31 -sigma 0.1", "dims": dims,
                                    "V": {"feature": [0, 5, 63], "rows": [[float(x) for x in v[i]] for i in (0, 5, 63)]}})
