@@ -1,15 +1,16 @@
 // hm_update.cuh -- the reduce-and-step half of a mini-batch (linear_update_kernel and what it is made of).
 //
-// Included by hm_linear.cu TWICE, inside two namespaces that differ in kUpdItems only (elements per thread of
-// a tile): the mini-batches that fill the GPU use 2048-element tiles, mid-size mini-batches (a few hundred
-// thousand elements: fewer tiles than SMs) 1024-element tiles -- every phase of a tile (load, two scans, step)
+// Included by hm_linear.cu THREE times, inside namespaces that differ in kUpdItems only (elements per thread
+// of a tile): the mini-batches that fill the GPU use 2048-element tiles, mid-size mini-batches (a few hundred
+// thousand elements: fewer tiles than SMs) 1024-element tiles, those of up to 100 K elements 512 -- every phase of a tile (load, two scans, step)
 // is a latency chain whose length grows with the elements per thread, and with few tiles nothing else hides
 // it.  Measured (examples/s, 8 / 4 elements per thread): 2048 rows per mini-batch 75 / 97 M, 4096 rows
-// 151 / 173 M, 8192 rows 261 / 295 M, 16,384 rows 395 / 372 M (profiles/r02e_update_tile_midsize.txt).
+// 151 / 173 M, 8192 rows 261 / 295 M, 16,384 rows 395 / 372 M; 4 / 2 elements per thread: 512 rows 29 / 32.5 M,
+// 2048 rows 96 / 108 M, 4096 rows 173 / 170 M, 8192 rows 300 / 278 M (profiles/r02e_update_tile_midsize.txt).
 // Needs kUpdItems (constexpr int) defined by the including namespace; everything else it uses (UpdParams,
 // step_rec, load_rec, ...) is defined before the inclusion.  Not a stand-alone header.
 
-constexpr int kUpdTile = kUpdThreads * kUpdItems;  // 2048 / 1024
+constexpr int kUpdTile = kUpdThreads * kUpdItems;  // 2048 / 1024 / 512
 
 __device__ __forceinline__ int pad_idx(int q) { return q + (q >> 5); }
 
