@@ -142,8 +142,16 @@ __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;"
 __device__ unsigned long long hm_dbg_stamps[4096 * 8];
 __device__ __forceinline__ unsigned long long gtime() { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
 #define STAMP(i) do { if (threadIdx.x == 0 && blockIdx.x < 4096) hm_dbg_stamps[blockIdx.x * 8 + (i)] = gtime(); } while (0)
+__device__ unsigned long long hm_dbg_fstamps[4096 * 8];      // the same for the forward kernel
+#define FSTAMP(i) do { if (threadIdx.x == 0 && blockIdx.x < 4096) hm_dbg_fstamps[blockIdx.x * 8 + (i)] = gtime(); } while (0)
+__device__ unsigned long long hm_dbg_seq[256 * 8];           // per mini-batch of the last block: CTA 0 of each launch
+#define SEQSTAMP(seg, i) do { if (threadIdx.x == 0 && blockIdx.x == 0) hm_dbg_seq[((seg) & 255) * 8 + (i)] = gtime(); } while (0)
+#define SEQSTAMP_ANY(seg, i) do { if (threadIdx.x == 0) hm_dbg_seq[((seg) & 255) * 8 + (i)] = gtime(); } while (0)
 #else
+#define SEQSTAMP(seg, i) do { } while (0)
+#define SEQSTAMP_ANY(seg, i) do { } while (0)
 #define STAMP(i) do { } while (0)
+#define FSTAMP(i) do { } while (0)
 #endif
 #define USTAMP(i) STAMP(i)
 
@@ -336,7 +344,10 @@ __device__ __forceinline__ void hot_prologue(const FwdParams &P, HS &H)
     for (int q = tid; q < kHotSlots / 4; q += kFwdThreads) reinterpret_cast<uint32_t *>(H.tab_slot)[q] = 0xffffffffu;
     for (int q = tid; q < HS::kUnits * kMaxHot; q += kFwdThreads) { (&H.acc[0][0])[q] = 0.0; (&H.cnt[0][0])[q] = 0u; }
     __syncthreads();
+    FSTAMP(1);
     if (LD == kLdCG) pdl_wait();     // the weights below are the previous mini-batch's update
+    FSTAMP(2);
+    SEQSTAMP((int)((P.row0 - P.block_row0) / max(P.n_rows, 1)), 1);
     if (tid < (int)n) {
         H.tab_slot[hot_index(key)] = (uint8_t)tid;     // (the index is pairwise different for the keys of a HotInfo)
         H.key[tid] = key;
@@ -498,6 +509,8 @@ __global__ void __launch_bounds__(kFwdThreads, 8) linear_forward_kernel(FwdParam
 {
     constexpr int LD = PDL ? kLdCG : kLdRO;
     extern __shared__ __align__(16) unsigned char fwd_dyn[];
+    FSTAMP(0);
+    SEQSTAMP((int)((P.row0 - P.block_row0) / max(P.n_rows, 1)), 0);
     if (PDL) pdl_launch_dependents();
     const int warp_first = blockIdx.x * (kFwdThreads / 32) + (threadIdx.x >> 5), warp_stride = gridDim.x * (kFwdThreads / 32);
     if (P.hot && P.hot->count != 0u) {     // (HotInfo is the sort's output: complete before this launch)
@@ -509,8 +522,12 @@ __global__ void __launch_bounds__(kFwdThreads, 8) linear_forward_kernel(FwdParam
         } else {
             auto &H = *reinterpret_cast<HotSharedT<8> *>(fwd_dyn);
             hot_prologue<LD>(P, H);
+            FSTAMP(3);
             forward_rows_hot<LD, 32>(P, warp_first, warp_stride, H);
+            FSTAMP(4);
             hot_end(P, H, (int)blockIdx.x);
+            FSTAMP(5);
+            SEQSTAMP((int)((P.row0 - P.block_row0) / max(P.n_rows, 1)), 2);
         }
     } else {
         if (PDL) pdl_wait();
@@ -1285,5 +1302,15 @@ extern "C" int hm_debug_read_stamps(unsigned long long *host, size_t n)
 {
     cudaDeviceSynchronize();
     return (int)cudaMemcpyFromSymbol(host, hm::hm_dbg_stamps, n * sizeof(unsigned long long));
+}
+extern "C" int hm_debug_read_seq(unsigned long long *host, size_t n)
+{
+    cudaDeviceSynchronize();
+    return (int)cudaMemcpyFromSymbol(host, hm::hm_dbg_seq, n * sizeof(unsigned long long));
+}
+extern "C" int hm_debug_read_fstamps(unsigned long long *host, size_t n)
+{
+    cudaDeviceSynchronize();
+    return (int)cudaMemcpyFromSymbol(host, hm::hm_dbg_fstamps, n * sizeof(unsigned long long));
 }
 #endif

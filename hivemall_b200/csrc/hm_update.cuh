@@ -100,6 +100,8 @@ __device__ __forceinline__ void reduce_tile(const UpdParams &P, const UpdDyn &D,
         if (q < n_tile) { k[i] = __ldcs(P.skey + base + q); pv[i] = __ldcs(P.spay + base + q); }
     }
     if (LD == kLdCG) pdl_wait();     // the sorted tile is on its way; dloss is the forward kernel's output
+    USTAMP(7);
+    SEQSTAMP(D.seg, 4);
 #pragma unroll
     for (int i = 0; i < kUpdItems; i++) {
         const int q = i * kUpdThreads + tid;
@@ -340,6 +342,7 @@ __device__ __forceinline__ void update_segment(const UpdParams &P, const UpdDyn 
         apply_list<LD == kLdCG>(P, D, l_key, l_g, s_nlist, tid);
         __syncthreads();
         USTAMP(5);
+        SEQSTAMP(D.seg, 5);
     }
     if (lo >= hi) {   // a CTA without elements leaves empty records and still takes its ticket
         if (LD == kLdCG) pdl_wait();   // (the records and the ticket belong to the previous update until it has finished)
@@ -389,6 +392,7 @@ __device__ __forceinline__ void update_segment(const UpdParams &P, const UpdDyn 
     __syncthreads();
     apply_list<LD == kLdCG>(P, D, ml_key, ml_g, s_nlist, tid);
     USTAMP(6);
+    SEQSTAMP_ANY(D.seg, 6);
     if (tid == 0) *P.br.ticket = 0;   // ready for the next launch on this stream
 }
 
@@ -397,6 +401,7 @@ __global__ void __launch_bounds__(kUpdThreads, kUpdCtasPerSm) linear_update_kern
 {
     __shared__ UpdCtaSmem sm;
     USTAMP(0);
+    SEQSTAMP(P.dyn.seg, 3);
     if (PDL) pdl_launch_dependents();
     if ((int)blockIdx.x >= P.dyn.n_active) {
         if (PDL) pdl_wait();
