@@ -124,3 +124,28 @@ def test_train_fm_at_baseline_dims(gen, k, nnz):
     rest = np.setdiff1d(np.arange(0, DIMS, 4099), touched)
     assert np.array_equal(V[rest], ref.V.reshape(-1, k)[rest])
     u.destroy()
+
+
+@pytest.mark.parametrize("fn,extra", [("train_pa1", "-c 0.05"), ("train_pa2_regr", "-c 0.05 -epsilon 0.02")])
+def test_online_learners_at_the_configs1_size(fn, extra):
+    """The online learners of DESIGN.md 3.10 on 65,536-row mini-batches of Criteo-shaped rows at 2^24 dims: the
+    launch shape of the headline (rows worked on by half a warp, hot features reduced in the forward kernel,
+    |x|^2 from the per-block kernel) against the oracle, eight mini-batches, and a bit-identical rerun."""
+    import os
+    n = 8 * MB
+    data = _device_rows(n, seed=3)
+    host = [t.cpu().numpy() for t in (data.rowptr, data.feature, data.value, data.label)]
+    opts = f"-mini_batch {MB} -dims {DIMS} {extra}"
+    ws = []
+    for _ in range(2):
+        u = hm.UDTF(opts, 0, function_name=fn)
+        u.process_device(n, data.nnz, data.rowptr, data.feature, data.value, data.label)
+        u.close()
+        assert u.step == 8 and len(u.hot_features()) >= 20
+        ws.append(u.array_to_host("w"))
+        u.destroy()
+    assert np.array_equal(ws[0], ws[1])
+    ref = _oracle.train_linear_mt(_oracle.config_from(hm.parse_options(fn, opts)), host[0], host[1], host[2], host[3],
+                                  min(16, os.cpu_count() or 1))
+    assert ref.t == 8 and np.count_nonzero(ref.w) > 100000
+    assert_weights_close(ws[0], ref.w)
