@@ -142,11 +142,17 @@ struct LinearArgs {
     int rec_width;        // 1 (SGD: w), 2 (AdaGrad: w, G; FTRL: z, n), 4 (AdaDelta, Adam: w, s1, s2, unused)
     WeightView wv;
     const float *sqnorm = nullptr;   // |x|^2 per row of the block being trained (online learners), else NULL
+    int cov_pass = 0;                // HM_OPT_COV: 1 = the update launch steps the weights, 2 = the variances
 };
+inline bool loss_keeps_variance(int loss) { return loss >= HM_LOSS_AROW; }
+// margin, variance and the two per-row coefficients of the variance-keeping learners (AROW)
+hm_status launch_linear_forward_cov(Launcher &L, const LinearArgs &a, const int64_t *d_rowptr, int64_t row0, int32_t n_rows,
+                                    int64_t block_row0, const uint32_t *d_feature, const float *d_value, const float *d_label,
+                                    float *d_margin, float *d_c1, float *d_c2, uint32_t *d_bad, int64_t nnz_hint);
 // |x|^2 of rows [row0, row0 + n_rows) of a chunk into out[0 .. n_rows)
 hm_status launch_row_sqnorm(Launcher &L, const int64_t *d_rowptr, int64_t row0, int64_t n_rows, const uint32_t *d_feature,
                             const float *d_value, int64_t dims, float *d_out, int64_t nnz_hint);
-inline bool loss_needs_sqnorm(int loss) { return loss >= HM_LOSS_PA; }
+inline bool loss_needs_sqnorm(int loss) { return loss >= HM_LOSS_PA && loss <= HM_LOSS_PA2_REGR; }
 // Hot features of the block being trained, and where their gradient sums travel from the forward
 // kernel to the update kernel.  info == NULL: the block was sorted whole.
 struct HotCols {
@@ -195,6 +201,7 @@ hm_status launch_export_write(Launcher &L, ExportScratch &es, const WeightView &
                               int64_t dims, int32_t *d_feature, float *d_weight);
 hm_status launch_scale(Launcher &L, float *p, int64_t n, float scale);
 hm_status launch_fill_u32(Launcher &L, uint32_t *p, int64_t n, uint32_t v);
+hm_status launch_fill_strided(Launcher &L, float *p, int64_t n, int stride, float v);
 hm_status launch_dense_weights(Launcher &L, const WeightView &wv, int64_t dims, float *d_out);
 hm_status launch_strided_copy(Launcher &L, float *dense, float *strided, int64_t n, int stride, int off, int width,
                               bool gather);

@@ -280,6 +280,7 @@ struct hm_udtf {
     UpdateScratch upd;
     ExportScratch exp;
     DevBuf sqnorm;        // online learners: |x|^2 per row of the block being trained
+    DevBuf dloss2;        // variance-keeping learners: the variance pass's per-row coefficients
     DevBuf margin, dloss, mb_gather, exp_feat, exp_weight, tmp_a, tmp_b, tmp_c, tmp_d;
     uint32_t *d_bad = nullptr;       // [0]: a training row held an index outside [0, dims); [1]: a scored row did
     int64_t *d_total = nullptr;
@@ -441,7 +442,10 @@ hm_status train_rows(hm_udtf *u, Chunk &c, int64_t row0, int64_t n_rows, const i
     for (int64_t m = 0; m < n_mb; m++) call_max_mb = std::max(call_max_mb, mb_abs[m + 1] - mb_abs[m]);
     // Hot features (the quantitative features every row has, the head of each categorical field) are taken out
     // of the sort and reduced by the forward kernel: linear learners on the two-kernel path only.
-    const bool hot_on = !u->fm && u->hot_enabled && !small_batch_eligible(B, call_max_mb);
+    // (the variance-keeping learners take the plain two-kernel path: no hot features, no persistent small-batch kernel)
+    const bool cov = !u->fm && loss_keeps_variance(u->cfg.loss);
+    const bool small_path = !u->fm && !cov && small_batch_eligible(B, call_max_mb);
+    const bool hot_on = !u->fm && !cov && u->hot_enabled && !small_path;
     auto enqueue_sort = [&](size_t bi) -> hm_status {
         const Plan &p = plan[bi];
         const int set = (int)((u->sort_turn + bi) & 1);
@@ -519,6 +523,7 @@ hm_status train_rows(hm_udtf *u, Chunk &c, int64_t row0, int64_t n_rows, const i
             a.sqnorm = u->sqnorm.as<float>();
         }
         HM_TRY(u->dloss.reserve((size_t)std::min<int64_t>(p.rows, B) * sizeof(float)));
+        if (cov) HM_TRY(u->dloss2.reserve((size_t)std::min<int64_t>(p.rows, B) * sizeof(float)));
         if (u->fm) {
             int64_t max_mb = 0;
             for (int64_t m = p.m0; m < p.m1; m++) max_mb = std::max(max_mb, mb_abs[m + 1] - mb_abs[m]);
@@ -527,7 +532,7 @@ hm_status train_rows(hm_udtf *u, Chunk &c, int64_t row0, int64_t n_rows, const i
         }
         HotCols hc;
         if (block_hot) { hc.info = ss.hot; hc.sum = u->upd.hot_sum; hc.cnt = u->upd.hot_cnt; hc.stride = u->upd.hot_stride; }
-        if (!u->fm && small_batch_eligible(B, call_max_mb)) {
+        if (small_path) {
             // a few hundred rows per mini-batch: up to 64 mini-batches per launch of one persistent CTA
             for (int s0 = 0; s0 < p.n_segs; s0 += 64) {
                 const int ns = std::min(64, p.n_segs - s0);
@@ -563,6 +568,19 @@ hm_status train_rows(hm_udtf *u, Chunk &c, int64_t row0, int64_t n_rows, const i
                                          true));
                 HM_TRY(launch_fm_update(u->L, fa, sc, u->fms, ss.key[buf], ss.pay[buf], ss.seg_off, s,
                                         u->dloss.as<float>(), u->stab.as<float>(), mnnz));
+            } else if (cov) {
+                // margin + variance per row, then one reduce-and-step launch for the weights and one for the
+                // variances over the same sorted mini-batch (both read the variances of its start)
+                HM_TRY(launch_linear_forward_cov(u->L, a, c.rp(), mrow0, mrows, p.row0, c.ft(), c.vl(), c.lb(),
+                                                 u->margin.as<float>(), u->dloss.as<float>(), u->dloss2.as<float>(),
+                                                 u->d_bad, mnnz));
+                for (int pass = 1; pass <= 2; pass++) {
+                    a.cov_pass = pass;
+                    HM_TRY(launch_linear_update(u->L, a, sc, u->upd, ss.key[buf], ss.pay[buf], ss.seg_off, s,
+                                                mb_abs[p.m0 + s] - mb_abs[p.m0],
+                                                pass == 1 ? u->dloss.as<float>() : u->dloss2.as<float>(), mnnz, hc, -1));
+                }
+                a.cov_pass = 0;
             } else {
                 HM_TRY(launch_linear_forward(u->L, a, c.rp(), mrow0, mrows, p.row0, c.ft(), c.vl(), c.lb(),
                                              u->margin.as<float>(), u->dloss.as<float>(), u->d_bad, mnnz, hc));
@@ -924,7 +942,7 @@ hm_status create_impl(const hm_config &cfg, int device, hm_udtf **out)
             HM_CUDA(cudaEventCreateWithFlags(&u->trained_ev[i], cudaEventDisableTiming));
         }
         HM_CUDA(cudaEventCreateWithFlags(&u->ready_ev, cudaEventDisableTiming));
-        u->state_width = cfg.opt == HM_OPT_SGD ? 0 : (cfg.opt == HM_OPT_ADAGRAD ? 1 : 2);
+        u->state_width = cfg.opt == HM_OPT_SGD ? 0 : ((cfg.opt == HM_OPT_ADAGRAD || cfg.opt == HM_OPT_COV) ? 1 : 2);
         if (cfg.task == HM_TASK_FM) {
             u->fm = true;
             u->k = cfg.factors;
@@ -946,6 +964,8 @@ hm_status create_impl(const hm_config &cfg, int device, hm_udtf **out)
             u->rec_width = u->state_width == 0 ? 1 : ((u->state_width == 1 || cfg.opt == HM_OPT_FTRL) ? 2 : 4);
             HM_CUDA(cudaMalloc(&u->rec, (size_t)cfg.dims * u->rec_width * sizeof(float)));
             HM_CUDA(cudaMemsetAsync(u->rec, 0, (size_t)cfg.dims * u->rec_width * sizeof(float), u->compute));
+            // the variance-keeping learners start from sigma = 1 for every feature (slot 1 of the (w, sigma) records)
+            if (cfg.opt == HM_OPT_COV) HM_TRY(launch_fill_strided(u->L, u->rec + 1, cfg.dims, u->rec_width, 1.0f));
         }
         HM_CUDA(cudaMalloc(&u->d_bad, 2 * sizeof(uint32_t)));
         HM_CUDA(cudaMemsetAsync(u->d_bad, 0, 2 * sizeof(uint32_t), u->compute));
@@ -1298,7 +1318,7 @@ hm_status hm_udtf_destroy(hm_udtf *u)
     if (u->merged_ev) cudaEventDestroy(u->merged_ev);
     update_scratch_free(u->upd);
     cudaFree(u->exp.counts);
-    for (DevBuf *b : {&u->sqnorm, &u->margin, &u->dloss, &u->mb_gather, &u->exp_feat, &u->exp_weight, &u->tmp_a,
+    for (DevBuf *b : {&u->sqnorm, &u->dloss2, &u->margin, &u->dloss, &u->mb_gather, &u->exp_feat, &u->exp_weight, &u->tmp_a,
                       &u->tmp_b, &u->tmp_c, &u->tmp_d})
         b->release();
     cudaFree(u->rec); cudaFree(u->d_bad); cudaFree(u->d_total);

@@ -539,6 +539,67 @@ __global__ void __launch_bounds__(kFwdThreads, 8) linear_forward_kernel(FwdParam
     }
 }
 
+// ---- learners that keep a variance per feature (AROW) -----------------------
+// Forward: margin m = sum w_j x_j AND variance v = sum sigma_j x_j^2 of a row from one 8-byte gather per
+// element (the record is (w, sigma)); then the two numbers that stand in dloss's place: c1 for the weight
+// sums (times x), c2 = beta for the variance sums (times x^2).  Crammer, Kulesza, Dredze 2009, diagonal.
+__device__ __forceinline__ void cov_coefs(int loss, float m, float y, float v, float r, float eps, float *c1, float *c2)
+{
+    *c1 = 0.0f; *c2 = 0.0f;
+    float l, dir;
+    if (loss == HM_LOSS_AROW) { l = __fsub_rn(1.0f, __fmul_rn(y, m)); dir = y; if (!(l > 0.0f)) return; }
+    else if (loss == HM_LOSS_AROW_REGR) { const float e = __fsub_rn(y, m); l = fabsf(e); dir = e < 0.0f ? -1.0f : 1.0f; }
+    else { const float e = __fsub_rn(y, m); l = __fsub_rn(fabsf(e), eps); dir = e < 0.0f ? -1.0f : 1.0f; if (!(l > 0.0f)) return; }
+    const float beta = __fdiv_rn(1.0f, __fadd_rn(v, r));
+    const float alpha = __fmul_rn(l, beta);
+    *c1 = -__fmul_rn(alpha, dir);
+    *c2 = beta;
+}
+
+struct FwdCovParams {
+    const float *rec;        // (w, sigma) per feature
+    const int64_t *rowptr;
+    const uint32_t *feature;
+    const float *value, *label;
+    float *margin, *c1, *c2;
+    int64_t block_row0, row0;
+    int32_t n_rows, task, loss;
+    float r, eps;
+    uint32_t dims;
+    uint32_t *bad;
+};
+
+__global__ void __launch_bounds__(kFwdThreads) linear_forward_cov_kernel(FwdCovParams P)
+{
+    const int lane = threadIdx.x & 31;
+    const int warp_first = blockIdx.x * (kFwdThreads / 32) + (threadIdx.x >> 5), warp_stride = gridDim.x * (kFwdThreads / 32);
+    const float2 *rec = reinterpret_cast<const float2 *>(P.rec);
+    for (int r = warp_first; r < P.n_rows; r += warp_stride) {
+        const int64_t row = P.row0 + r;
+        const int64_t p0 = P.rowptr[row], p1 = P.rowptr[row + 1];
+        double am = 0.0, av = 0.0;
+        for (int64_t p = p0 + lane; p < p1; p += 32) {
+            const uint32_t f = __ldcs(P.feature + p);
+            const float x = __ldcs(P.value + p);
+            if (f < P.dims) {
+                const float2 ws = __ldg(rec + f);
+                am += (double)__fmul_rn(ws.x, x);
+                av += (double)__fmul_rn(ws.y, __fmul_rn(x, x));
+            } else atomicOr(P.bad, 1u);
+        }
+        am = warp_sum(am); av = warp_sum(av);
+        if (lane == 0) {
+            const float m = (float)am;
+            P.margin[row - P.block_row0] = m;
+            const float lab = P.label[row];
+            const float y = P.task == HM_TASK_CLASSIFIER ? (lab > 0.0f ? 1.0f : -1.0f) : lab;
+            float c1, c2;
+            cov_coefs(P.loss, m, y, (float)av, P.r, P.eps, &c1, &c2);
+            P.c1[r] = c1; P.c2[r] = c2;
+        }
+    }
+}
+
 // ---- update ------------------------------------------------------------------------
 
 struct SegRec {           // a (feature, partial sum) record; cnt == 0 means empty
@@ -584,6 +645,7 @@ struct UpdParams {
     UpdDyn dyn;              // the mini-batch (kernels that train one mini-batch per launch read it from here)
     uint32_t dims;
     int32_t opt, reg, grad_norm;
+    int32_t square;          // HM_OPT_COV, variance pass: the sums run over dloss * value^2 and step the variance
     float lambda, eps, rho, beta1, beta2, alpha, beta, lambda1, lambda2;
     // (the mini-batch's bounds in the sorted arrays are read from seg_off: the sorted arrays are shorter
     // than the CSR by the hot-feature and out-of-range elements, a number only the device knows)
@@ -670,6 +732,11 @@ __device__ __forceinline__ void step_rec(const UpdParams &P, const UpdDyn &D, Re
         wv = __fsub_rn(wv, __fdiv_rn(__fmul_rn(D.adam_alpha, m), __fadd_rn(__fsqrt_rn(v), P.eps)));
         break;
     }
+    case HM_OPT_COV: {    // s1 = the feature's variance; both passes use its value of the start of the mini-batch
+        if (P.square) r.s1 = __fsub_rn(r.s1, __fmul_rn(__fmul_rn(r.s1, r.s1), g));
+        else wv = __fsub_rn(wv, __fmul_rn(r.s1, g));
+        break;
+    }
     case HM_OPT_FTRL: {   // (s1, s2) = (z, n)
         const float n1 = __fadd_rn(r.s2, __fmul_rn(g, g));
         const float sq1 = __fsqrt_rn(n1);
@@ -698,16 +765,24 @@ __device__ __forceinline__ void step_rec(const UpdParams &P, const UpdDyn &D, Re
 #endif
 namespace upd8 {            // 2048-element tiles: mini-batches that fill the GPU, and the small-batch kernel
 constexpr int kUpdItems = HM_UPD_ITEMS;
+constexpr bool kUpdCov = false;
 #include "hm_update.cuh"
 }  // namespace upd8
 namespace upd4 {            // 1024-element tiles: mid-size mini-batches
 constexpr int kUpdItems = HM_UPD_ITEMS_MID;
+constexpr bool kUpdCov = false;
 #include "hm_update.cuh"
 }  // namespace upd4
 namespace upd2 {            // 512-element tiles: mini-batches of up to 100 K elements
 constexpr int kUpdItems = 2;
+constexpr bool kUpdCov = false;
 #include "hm_update.cuh"
 }  // namespace upd2
+namespace updc {            // the variance-keeping learners (AROW): 1024-element tiles, sums over value or value^2
+constexpr int kUpdItems = HM_UPD_ITEMS_MID;
+constexpr bool kUpdCov = true;
+#include "hm_update.cuh"
+}  // namespace updc
 using namespace upd8;
 
 // ---- small mini-batches: one persistent CTA ----------------------------------------
@@ -904,6 +979,12 @@ __global__ void fill_u32_kernel(uint32_t *__restrict__ p, int64_t n, uint32_t v)
         p[i] = v;
 }
 
+__global__ void fill_strided_kernel(float *__restrict__ p, int64_t n, int stride, float v)
+{
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+        p[i * stride] = v;
+}
+
 int grid_for(int64_t ctas_wanted, int per_sm)
 {
     const int64_t cap = (int64_t)num_sms() * per_sm;
@@ -980,6 +1061,23 @@ hm_status launch_linear_forward(Launcher &L, const LinearArgs &a, const int64_t 
     return HM_OK;
 }
 
+hm_status launch_linear_forward_cov(Launcher &L, const LinearArgs &a, const int64_t *d_rowptr, int64_t row0, int32_t n_rows,
+                                    int64_t block_row0, const uint32_t *d_feature, const float *d_value, const float *d_label,
+                                    float *d_margin, float *d_c1, float *d_c2, uint32_t *d_bad, int64_t nnz_hint)
+{
+    if (n_rows <= 0) return HM_OK;
+    if (a.rec_width != 2) HM_FAIL(HM_ERR_STATE, "variance-keeping learners use (w, sigma) records");
+    FwdCovParams P;
+    P.rec = a.rec; P.rowptr = d_rowptr; P.feature = d_feature; P.value = d_value; P.label = d_label;
+    P.margin = d_margin; P.c1 = d_c1; P.c2 = d_c2; P.block_row0 = block_row0; P.row0 = row0; P.n_rows = n_rows;
+    P.task = a.cfg.task; P.loss = a.cfg.loss; P.r = a.cfg.cov_r; P.eps = a.cfg.pa_epsilon;
+    P.dims = (uint32_t)a.cfg.dims; P.bad = d_bad;
+    HM_LAUNCH(L, K_LIN_FORWARD, 16.0 * (double)nnz_hint + 24.0 * (double)n_rows,
+              (linear_forward_cov_kernel<<<linear_forward_grid(n_rows), kFwdThreads, 0, L.stream>>>(P)));
+    HM_CUDA(cudaGetLastError());
+    return HM_OK;
+}
+
 hm_status launch_row_sqnorm(Launcher &L, const int64_t *d_rowptr, int64_t row0, int64_t n_rows, const uint32_t *d_feature,
                             const float *d_value, int64_t dims, float *d_out, int64_t nnz_hint)
 {
@@ -1051,15 +1149,16 @@ hm_status launch_linear_update(Launcher &L, const LinearArgs &a, const StepScala
     P.br.last = P.br.first + us.grid;
     P.br.ticket = us.done_counter;
     P.dyn.seg = seg; P.dims = (uint32_t)a.cfg.dims;
-    P.opt = a.cfg.opt; P.reg = a.cfg.reg; P.grad_norm = a.cfg.grad_norm;
+    P.opt = a.cfg.opt; P.reg = a.cfg.reg; P.grad_norm = a.cfg.grad_norm; P.square = a.cov_pass == 2;
     P.dyn.eta = sc.eta; P.dyn.adam_alpha = sc.adam_alpha; P.lambda = a.cfg.lambda; P.eps = a.cfg.eps; P.rho = a.cfg.rho;
     P.beta1 = a.cfg.beta1; P.beta2 = a.cfg.beta2; P.alpha = a.cfg.alpha; P.beta = a.cfg.beta;
     P.lambda1 = a.cfg.lambda1; P.lambda2 = a.cfg.lambda2;
     P.dyn.inv_rows = 1.0 / (double)sc.n_rows;
     // Tile size by the mini-batch's element count (hm_update.cuh): 512 elements up to 100 K, 1024 up to the
     // bound for dependent launches, 2048 above.
-    const int tier = nnz_hint <= kSmallTileMaxElems ? 2 : (nnz_hint <= kPdlMaxElems ? 4 : 8);
-    const int64_t tile = tier == 2 ? upd2::kUpdTile : (tier == 4 ? upd4::kUpdTile : upd8::kUpdTile);
+    const bool cov = a.cov_pass != 0;
+    const int tier = cov ? 0 : (nnz_hint <= kSmallTileMaxElems ? 2 : (nnz_hint <= kPdlMaxElems ? 4 : 8));
+    const int64_t tile = cov ? updc::kUpdTile : (tier == 2 ? upd2::kUpdTile : (tier == 4 ? upd4::kUpdTile : upd8::kUpdTile));
     // one tile per CTA up to kUpdMaxGrid CTAs; beyond that each CTA walks consecutive tiles.
     // nnz_hint is exact (the host knows rowptr at every mini-batch boundary).
     const int64_t tiles = std::max<int64_t>((nnz_hint + tile - 1) / tile, 1);
@@ -1073,7 +1172,9 @@ hm_status launch_linear_update(Launcher &L, const LinearArgs &a, const StepScala
     // more CTAs step the hot features)
     const int ctas = grid + (hc.info ? kHotCtas : 0);
     const bool pdl = pdl_enabled();
-    if (tier == 2) {
+    if (cov) {
+        HM_LAUNCH(L, K_LIN_UPDATE, bytes, (updc::linear_update_kernel<false><<<ctas, kUpdThreads, 0, L.stream>>>(P)));
+    } else if (tier == 2) {
         if (pdl) HM_LAUNCH(L, K_LIN_UPDATE, bytes, (launch_maybe_pdl(upd2::linear_update_kernel<true>, ctas, kUpdThreads, L.stream, true, P)));
         else HM_LAUNCH(L, K_LIN_UPDATE, bytes, (upd2::linear_update_kernel<false><<<ctas, kUpdThreads, 0, L.stream>>>(P)));
     } else if (tier == 4) {
@@ -1191,6 +1292,16 @@ hm_status launch_fill_u32(Launcher &L, uint32_t *p, int64_t n, uint32_t v)
     if (n <= 0) return HM_OK;
     HM_LAUNCH(L, K_MISC, 4.0 * (double)n,
               (fill_u32_kernel<<<grid_for((n + 1023) / 1024, 8), 256, 0, L.stream>>>(p, n, v)));
+    HM_CUDA(cudaGetLastError());
+    return HM_OK;
+}
+
+// p[i * stride] = v for i in [0, n)
+hm_status launch_fill_strided(Launcher &L, float *p, int64_t n, int stride, float v)
+{
+    if (n <= 0) return HM_OK;
+    HM_LAUNCH(L, K_MISC, 4.0 * (double)n,
+              (fill_strided_kernel<<<grid_for((n + 1023) / 1024, 8), 256, 0, L.stream>>>(p, n, stride, v)));
     HM_CUDA(cudaGetLastError());
     return HM_OK;
 }

@@ -93,6 +93,7 @@ static void defaults(hm_config *c, int task)
     c->hash_seed = 0x9747b28cu;
     c->pa_c = 1.0f;
     c->pa_epsilon = 0.1f;
+    c->cov_r = 0.1f;
 }
 
 hm_status parse_options(const char *function_name, const char *options, hm_config *out)
@@ -110,16 +111,22 @@ hm_status parse_options(const char *function_name, const char *options, hm_confi
     else if (fn == "train_pa2") { task = HM_TASK_CLASSIFIER; online = HM_LOSS_PA2; }
     else if (fn == "train_pa1_regr") { task = HM_TASK_REGRESSOR; online = HM_LOSS_PA1_REGR; }
     else if (fn == "train_pa2_regr") { task = HM_TASK_REGRESSOR; online = HM_LOSS_PA2_REGR; }
+    else if (fn == "train_arow") { task = HM_TASK_CLASSIFIER; online = HM_LOSS_AROW; }
+    else if (fn == "train_arow_regr") { task = HM_TASK_REGRESSOR; online = HM_LOSS_AROW_REGR; }
+    else if (fn == "train_arowe_regr") { task = HM_TASK_REGRESSOR; online = HM_LOSS_AROWE_REGR; }
     else HM_FAIL(HM_ERR_INVALID_ARGUMENT, "unknown function '%s' (expected train_classifier, train_regressor, train_fm, "
-                 "train_perceptron, train_pa, train_pa1, train_pa2, train_pa1_regr or train_pa2_regr)", function_name);
+                 "train_perceptron, train_pa, train_pa1, train_pa2, train_pa1_regr, train_pa2_regr, train_arow, train_arow_regr "
+                 "or train_arowe_regr)", function_name);
     hm_config c;
     defaults(&c, task);
     if (online >= 0) {
         // the step size lives in the per-row coefficient: the "optimizer" only subtracts the mean of coef * x
         c.loss = online; c.opt = HM_OPT_SGD; c.eta_sched = HM_ETA_FIXED; c.eta0 = 1.0f; c.reg = HM_REG_NONE;
+        if (online >= HM_LOSS_AROW) c.opt = HM_OPT_COV;
     }
+    const bool takes_r = online >= HM_LOSS_AROW;
     const bool takes_c = online == HM_LOSS_PA1 || online == HM_LOSS_PA2 || online == HM_LOSS_PA1_REGR || online == HM_LOSS_PA2_REGR;
-    const bool takes_eps = online == HM_LOSS_PA1_REGR || online == HM_LOSS_PA2_REGR;
+    const bool takes_eps = online == HM_LOSS_PA1_REGR || online == HM_LOSS_PA2_REGR || online == HM_LOSS_AROWE_REGR;
 
     std::vector<std::string> tok;
     {
@@ -171,8 +178,11 @@ hm_status parse_options(const char *function_name, const char *options, hm_confi
             if (!takes_c) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "%s is an option of train_pa1, train_pa2 and their _regr forms", name.c_str());
             NEED_F(1e-12, 1e12); c.pa_c = (float)d;
         } else if (name == "-epsilon" || name == "-e") {
-            if (!takes_eps) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "%s is an option of train_pa1_regr and train_pa2_regr", name.c_str());
+            if (!takes_eps) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "%s is an option of train_pa1_regr, train_pa2_regr and train_arowe_regr", name.c_str());
             NEED_F(0.0, 1e12); c.pa_epsilon = (float)d;
+        } else if (name == "-r") {
+            if (!takes_r) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "-r is an option of train_arow, train_arow_regr and train_arowe_regr");
+            NEED_F(1e-12, 1e12); c.cov_r = (float)d;
         } else if (name == "-loss" || name == "-loss_function") {
             if (task == HM_TASK_FM) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "-loss is not a train_fm option (use -classification)");
             if (lv == "logloss" || lv == "logistic" || lv == "log") c.loss = HM_LOSS_LOG;

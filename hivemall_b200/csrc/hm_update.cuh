@@ -7,7 +7,9 @@
 // it.  Measured (examples/s, 8 / 4 elements per thread): 2048 rows per mini-batch 75 / 97 M, 4096 rows
 // 151 / 173 M, 8192 rows 261 / 295 M, 16,384 rows 395 / 372 M; 4 / 2 elements per thread: 512 rows 29 / 32.5 M,
 // 2048 rows 96 / 108 M, 4096 rows 173 / 170 M, 8192 rows 300 / 278 M (profiles/r02e_update_tile_midsize.txt).
-// Needs kUpdItems (constexpr int) defined by the including namespace; everything else it uses (UpdParams,
+// A fourth inclusion (kUpdCov = true) serves the learners that keep a variance per feature: its sums can run
+// over dloss * value^2 (UpdParams::square); the other three compile that choice out.
+// Needs kUpdItems (constexpr int) and kUpdCov (constexpr bool) defined by the including namespace; everything else it uses (UpdParams,
 // step_rec, load_rec, ...) is defined before the inclusion.  Not a stand-alone header.
 
 constexpr int kUpdTile = kUpdThreads * kUpdItems;  // 2048 / 1024 / 512
@@ -107,7 +109,9 @@ __device__ __forceinline__ void reduce_tile(const UpdParams &P, const UpdDyn &D,
         const int q = i * kUpdThreads + tid;
         if (q < n_tile) {
             S.s_key[pad_idx(q)] = k[i];
-            S.s_val[pad_idx(q)] = __fmul_rn(ld_mode<LD>(P.dloss + pv[i].x), __uint_as_float(pv[i].y));
+            const float x = __uint_as_float(pv[i].y);
+            // (kUpdCov: only the instance for the variance-keeping learners carries the second kind of sum)
+            S.s_val[pad_idx(q)] = __fmul_rn(ld_mode<LD>(P.dloss + pv[i].x), (kUpdCov && P.square) ? __fmul_rn(x, x) : x);
         }
     }
     __syncthreads();

@@ -404,8 +404,8 @@ class UDTF:
 
     @property
     def state_width(self) -> int:
-        """Optimizer slots per feature (0 SGD, 1 AdaGrad, 2 otherwise)."""
-        return {0: 0, 1: 1}.get(self.config.opt, 2)
+        """Optimizer slots per feature (0 SGD, 1 AdaGrad and the variance-keeping learners, 2 otherwise)."""
+        return {0: 0, 1: 1, 5: 1}.get(self.config.opt, 2)
 
     def _logical(self, name: str) -> tuple[int, int]:
         """(index, length) of a logical model array."""
@@ -556,3 +556,31 @@ def train_pa1_regr(options: str = "", device: int = 0) -> PassiveAggressive1Regr
 
 def train_pa2_regr(options: str = "", device: int = 0) -> PassiveAggressive2RegressionUDTF:
     return PassiveAggressive2RegressionUDTF(options, device)
+
+
+# ---- learners that keep a variance per feature ---------------------------------------------
+# Adaptive regularization of weights (Crammer, Kulesza, Dredze, NIPS 2009), diagonal covariance: array "state"
+# holds the variances (1 at the start).
+
+class AROWClassifierUDTF(UDTF):
+    function_name = "train_arow"
+
+
+class AROWRegressionUDTF(UDTF):
+    function_name = "train_arow_regr"
+
+
+class AROWeRegressionUDTF(UDTF):
+    function_name = "train_arowe_regr"
+
+
+def train_arow(options: str = "", device: int = 0) -> AROWClassifierUDTF:
+    return AROWClassifierUDTF(options, device)
+
+
+def train_arow_regr(options: str = "", device: int = 0) -> AROWRegressionUDTF:
+    return AROWRegressionUDTF(options, device)
+
+
+def train_arowe_regr(options: str = "", device: int = 0) -> AROWeRegressionUDTF:
+    return AROWeRegressionUDTF(options, device)

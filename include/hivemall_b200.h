@@ -49,8 +49,13 @@ enum { HM_LOSS_LOG = 0, HM_LOSS_HINGE = 1, HM_LOSS_SQUARED = 2,
         * train_pa1_regr, train_pa2_regr): the per-row coefficient is the learner's step size times the sign of
         * the correction instead of a loss derivative, and the optimizer is plain SGD with eta = 1 */
        HM_LOSS_PERCEPTRON = 3, HM_LOSS_PA = 4, HM_LOSS_PA1 = 5, HM_LOSS_PA2 = 6,
-       HM_LOSS_PA1_REGR = 7, HM_LOSS_PA2_REGR = 8 };
-enum { HM_OPT_SGD = 0, HM_OPT_ADAGRAD = 1, HM_OPT_ADADELTA = 2, HM_OPT_ADAM = 3, HM_OPT_FTRL = 4 };
+       HM_LOSS_PA1_REGR = 7, HM_LOSS_PA2_REGR = 8,
+       /* learners that keep a per-feature variance beside the weight (train_arow, train_arow_regr,
+        * train_arowe_regr): the forward pass also yields the row's variance, and a mini-batch ends in two
+        * reduce-and-step launches, one for the weights and one for the variances */
+       HM_LOSS_AROW = 9, HM_LOSS_AROW_REGR = 10, HM_LOSS_AROWE_REGR = 11 };
+enum { HM_OPT_SGD = 0, HM_OPT_ADAGRAD = 1, HM_OPT_ADADELTA = 2, HM_OPT_ADAM = 3, HM_OPT_FTRL = 4,
+       HM_OPT_COV = 5 /* set by the variance-keeping learners, not by -opt: state = one variance per feature, 1 at the start */ };
 enum { HM_ETA_FIXED = 0, HM_ETA_INVERSE = 1, HM_ETA_SIMPLE = 2 };
 enum { HM_REG_NONE = 0, HM_REG_L1 = 1, HM_REG_L2 = 2 };
 enum { HM_NORM_BATCH = 0, HM_NORM_COUNT = 1, HM_NORM_SUM = 2 };
@@ -76,8 +81,9 @@ typedef struct hm_config {
                               * the library itself never communicates, see hm_udtf_array / hm_udtf_scale_replica */
     uint32_t hash_seed;      /* MurmurHash3 seed used by feature hashing */
     float   pa_c;            /* passive-aggressive learners: aggressiveness C (PA-I cap, PA-II slack) */
-    float   pa_epsilon;      /* ... regression: width of the insensitive zone */
-    int32_t reserved[6];
+    float   pa_epsilon;      /* ... regression: width of the insensitive zone (also train_arowe_regr) */
+    float   cov_r;           /* train_arow*: regularisation r of the variance update */
+    int32_t reserved[5];
 } hm_config;
 
 typedef struct hm_udtf hm_udtf; /* opaque learner = one UDTF instance on one GPU */
@@ -125,10 +131,11 @@ hm_status hm_feature_hashing(const uint8_t *bytes, const int64_t *offsets, int64
 
 /* function_name: "train_classifier" | "train_regressor" | "train_fm", or one of the online learners on the
  * same skeleton: "train_perceptron" | "train_pa" | "train_pa1" | "train_pa2" (labels as train_classifier) |
- * "train_pa1_regr" | "train_pa2_regr" (targets as train_regressor).  Those fix loss, optimizer (SGD), eta (1)
- * and regularisation (none) themselves and take -mini_batch, -iters, -dims, -grad_norm, -mix_interval,
- * -hash_seed, plus -c / -aggressiveness (train_pa1, train_pa2, *_regr; default 1) and -epsilon / -e (*_regr;
- * default 0.1).
+ * "train_pa1_regr" | "train_pa2_regr" (targets as train_regressor) | "train_arow" (labels) |
+ * "train_arow_regr" | "train_arowe_regr" (targets).  Those fix loss, optimizer, eta (1) and regularisation
+ * (none) themselves and take -mini_batch, -iters, -dims, -grad_norm, -mix_interval, -hash_seed, plus
+ * -c / -aggressiveness (train_pa1, train_pa2, train_pa*_regr; default 1), -epsilon / -e (train_pa*_regr,
+ * train_arowe_regr; default 0.1) and -r (train_arow*; default 0.1).
  * Unknown options, missing values and out-of-range numbers are
  * HM_ERR_INVALID_ARGUMENT with the offending token in hm_last_error(). */
 hm_status hm_parse_options(const char *function_name, const char *options, hm_config *out);

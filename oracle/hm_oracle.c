@@ -125,6 +125,94 @@ float hmo_row_coef(const hmo_config *c, float m, float y, float xx)
     return -(tau * dir);
 }
 
+/* AROW (Crammer, Kulesza, Dredze 2009), diagonal: beta = 1 / (v + r); classification: l = 1 - y m, step when
+ * l > 0, alpha = l beta, w_j += alpha y sigma_j x_j, sigma_j -= beta sigma_j^2 x_j^2.  Regression: e = y - m
+ * in place of y l (every row steps); with an insensitive zone: l = |e| - epsilon, step when l > 0, along sgn(e).
+ * c1 = -(alpha * direction) so that the common "w -= sigma * mean(c1 x)" adds the step; c2 = beta. */
+void hmo_cov_coefs(const hmo_config *c, float m, float y, float v, float *c1, float *c2)
+{
+    *c1 = 0.0f; *c2 = 0.0f;
+    float l, dir;
+    if (c->loss == HMO_LOSS_AROW) { l = 1.0f - y * m; dir = y; if (!(l > 0.0f)) return; }
+    else if (c->loss == HMO_LOSS_AROW_REGR) { const float e = y - m; l = fabsf(e); dir = e < 0.0f ? -1.0f : 1.0f; }
+    else { const float e = y - m; l = fabsf(e) - c->pa_epsilon; dir = e < 0.0f ? -1.0f : 1.0f; if (!(l > 0.0f)) return; }
+    const float beta = 1.0f / (v + c->cov_r);
+    const float alpha = l * beta;
+    *c1 = -(alpha * dir);
+    *c2 = beta;
+}
+
+static inline float target_of(const hmo_config *c, float label);
+static inline float mean_grad(const hmo_config *c, double sum, uint32_t cnt, double inv_nb);
+
+static int train_cov(const hmo_config *c, int64_t n_rows, const int64_t *rowptr,
+                     const uint32_t *idx, const float *val, const float *label,
+                     float *w, float *sg, int64_t *t, float *margins, double *loss_sum)
+{
+    if (!sg) return -4;
+    const int64_t B = c->mini_batch;
+    double *g1 = (double *)calloc((size_t)c->dims, sizeof(double));
+    double *g2 = (double *)calloc((size_t)c->dims, sizeof(double));
+    uint32_t *cnt = (uint32_t *)calloc((size_t)c->dims, sizeof(uint32_t));
+    float *c1 = (float *)malloc((size_t)B * sizeof(float)), *c2 = (float *)malloc((size_t)B * sizeof(float));
+    int64_t max_touch = 1;
+    for (int64_t b0 = 0; b0 < n_rows; b0 += B) {
+        int64_t e = b0 + B < n_rows ? b0 + B : n_rows;
+        if (rowptr[e] - rowptr[b0] > max_touch) max_touch = rowptr[e] - rowptr[b0];
+    }
+    uint32_t *touch = (uint32_t *)malloc((size_t)max_touch * sizeof(uint32_t));
+    if (!g1 || !g2 || !cnt || !c1 || !c2 || !touch) return -2;
+    double lsum = 0.0;
+    int rc = 0;
+    for (int32_t it = 0; it < c->iters && rc == 0; it++) {
+        lsum = 0.0;
+        for (int64_t b0 = 0; b0 < n_rows && rc == 0; b0 += B) {
+            const int64_t b1 = b0 + B < n_rows ? b0 + B : n_rows;
+            /* margin and variance of every row with the model as it stands */
+            for (int64_t i = b0; i < b1; i++) {
+                double am = 0.0, av = 0.0;
+                for (int64_t p = rowptr[i]; p < rowptr[i + 1]; p++) {
+                    if ((int64_t)idx[p] >= c->dims) { rc = -3; break; }
+                    const float x = val[p];
+                    am += (double)(w[idx[p]] * x);
+                    const float xx = x * x;
+                    av += (double)(sg[idx[p]] * xx);
+                }
+                if (rc) break;
+                const float m = (float)am, y = target_of(c, label[i]);
+                hmo_cov_coefs(c, m, y, (float)av, &c1[i - b0], &c2[i - b0]);
+                lsum += hmo_loss(c->loss, m, y);
+                if (margins) margins[i] = m;
+            }
+            if (rc) break;
+            int64_t nt = 0;
+            for (int64_t i = b0; i < b1; i++)
+                for (int64_t p = rowptr[i]; p < rowptr[i + 1]; p++) {
+                    const uint32_t j = idx[p];
+                    if (cnt[j]++ == 0) touch[nt++] = j;
+                    const float x = val[p];
+                    g1[j] += (double)(c1[i - b0] * x);
+                    const float xx = x * x;
+                    g2[j] += (double)(c2[i - b0] * xx);
+                }
+            *t += 1;
+            const double inv_nb = 1.0 / (double)(b1 - b0);
+            for (int64_t k = 0; k < nt; k++) {
+                const uint32_t j = touch[k];
+                const float m1 = mean_grad(c, g1[j], cnt[j], inv_nb), m2 = mean_grad(c, g2[j], cnt[j], inv_nb);
+                const float s = sg[j];
+                w[j] = w[j] - s * m1;            /* both steps use the variance of the start of the mini-batch */
+                const float ss = s * s;
+                sg[j] = s - ss * m2;
+                g1[j] = 0.0; g2[j] = 0.0; cnt[j] = 0;
+            }
+        }
+    }
+    if (loss_sum) *loss_sum = lsum;
+    free(g1); free(g2); free(cnt); free(c1); free(c2); free(touch);
+    return rc;
+}
+
 static inline float row_sqnorm(const int64_t *rowptr, const float *val, int64_t i)
 {
     double acc = 0.0;
@@ -137,6 +225,8 @@ double hmo_loss(int32_t loss, float m, float y)
     double z = (double)y * (double)m;
     if (loss == HMO_LOSS_PERCEPTRON) return z <= 0.0 ? -z : 0.0;
     if (loss == HMO_LOSS_PA || loss == HMO_LOSS_PA1 || loss == HMO_LOSS_PA2) loss = HMO_LOSS_HINGE;
+    if (loss == HMO_LOSS_AROW) loss = HMO_LOSS_HINGE;
+    if (loss == HMO_LOSS_AROW_REGR || loss == HMO_LOSS_AROWE_REGR) return fabs((double)y - (double)m);
     if (loss == HMO_LOSS_PA1_REGR || loss == HMO_LOSS_PA2_REGR) return fabs((double)y - (double)m);   /* (epsilon not known here) */
     switch (loss) {
     case HMO_LOSS_LOG:   return z > 0 ? log1p(exp(-z)) : -z + log1p(exp(z));
@@ -248,6 +338,7 @@ int hmo_train_linear(const hmo_config *c, int64_t n_rows, const int64_t *rowptr,
                      float *margins, double *loss_sum)
 {
     if (c->mini_batch < 1 || c->dims < 1) return -1;
+    if (c->loss >= HMO_LOSS_AROW) return train_cov(c, n_rows, rowptr, idx, val, label, w, s1, t, margins, loss_sum);
     const int64_t B = c->mini_batch;
     double *gsum = (double *)calloc((size_t)c->dims, sizeof(double));
     uint32_t *cnt = (uint32_t *)calloc((size_t)c->dims, sizeof(uint32_t));
@@ -320,6 +411,7 @@ int hmo_train_linear_mt(const hmo_config *c, int64_t n_rows, const int64_t *rowp
                         float *w, float *s1, float *s2, int64_t *t, int threads)
 {
     if (c->mini_batch < 1 || c->dims < 1 || threads < 1) return -1;
+    if (c->loss >= HMO_LOSS_AROW) return train_cov(c, n_rows, rowptr, idx, val, label, w, s1, t, NULL, NULL);   /* (single thread) */
     if (threads > 256) threads = 256;
     const int64_t B = c->mini_batch;
     const int T = threads;

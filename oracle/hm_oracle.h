@@ -27,8 +27,12 @@ enum { HMO_LOSS_LOG = 0, HMO_LOSS_HINGE = 1, HMO_LOSS_SQUARED = 2,
        /* online learners on the mini-batch skeleton: perceptron (Rosenblatt 1958) and the
         * passive-aggressive family (Crammer, Dekel, Keshet, Shalev-Shwartz, Singer, JMLR 2006) */
        HMO_LOSS_PERCEPTRON = 3, HMO_LOSS_PA = 4, HMO_LOSS_PA1 = 5, HMO_LOSS_PA2 = 6,
-       HMO_LOSS_PA1_REGR = 7, HMO_LOSS_PA2_REGR = 8 };
-enum { HMO_OPT_SGD = 0, HMO_OPT_ADAGRAD = 1, HMO_OPT_ADADELTA = 2, HMO_OPT_ADAM = 3, HMO_OPT_FTRL = 4 };
+       HMO_LOSS_PA1_REGR = 7, HMO_LOSS_PA2_REGR = 8,
+       /* adaptive regularization of weights (Crammer, Kulesza, Dredze, NIPS 2009), diagonal covariance:
+        * classification, regression, regression with an insensitive zone */
+       HMO_LOSS_AROW = 9, HMO_LOSS_AROW_REGR = 10, HMO_LOSS_AROWE_REGR = 11 };
+enum { HMO_OPT_SGD = 0, HMO_OPT_ADAGRAD = 1, HMO_OPT_ADADELTA = 2, HMO_OPT_ADAM = 3, HMO_OPT_FTRL = 4,
+       HMO_OPT_COV = 5 /* the AROW learners: s1 = per-feature variance, 1 at the start (the CALLER fills it) */ };
 enum { HMO_ETA_FIXED = 0, HMO_ETA_INVERSE = 1, HMO_ETA_SIMPLE = 2 };
 enum { HMO_REG_NONE = 0, HMO_REG_L1 = 1, HMO_REG_L2 = 2 };
 enum { HMO_NORM_BATCH = 0, HMO_NORM_COUNT = 1, HMO_NORM_SUM = 2 };
@@ -55,6 +59,7 @@ typedef struct hmo_config {
     /* passive-aggressive learners */
     float   pa_c;                 /* aggressiveness C */
     float   pa_epsilon;           /* regression: insensitive zone */
+    float   cov_r;                /* AROW: regularisation r */
 } hmo_config;
 
 /* MurmurHash3_x86_32 (Appleby, public domain algorithm). */
@@ -72,6 +77,9 @@ float hmo_dloss(int32_t loss, float margin, float y);
 /* The number that takes dloss's place for a row, any loss id: hmo_dloss for the three losses, else the
  * online learner's -(step size) * (direction); xx = |x|^2 of the row (fp32 squares, fp64 sum, rounded once). */
 float hmo_row_coef(const hmo_config *c, float margin, float y, float xx);
+/* AROW: the two numbers that take dloss's place for a row -- c1 for the weight sums (times x), c2 for the
+ * variance sums (times x^2) -- from the margin, the target and the row's variance v = sum sigma_j x_j^2. */
+void hmo_cov_coefs(const hmo_config *c, float margin, float y, float v, float *c1, float *c2);
 /* loss value in double (reporting only). */
 double hmo_loss(int32_t loss, float margin, float y);
 

@@ -21,7 +21,7 @@ class HmoConfig(C.Structure):
         ("alpha", C.c_float), ("beta", C.c_float), ("lambda1", C.c_float), ("lambda2", C.c_float),
         ("factors", C.c_int32), ("fm_classification", C.c_int32), ("sigma", C.c_float),
         ("lambda_w0", C.c_float), ("lambda_w", C.c_float), ("lambda_v", C.c_float),
-        ("seed", C.c_uint32), ("pa_c", C.c_float), ("pa_epsilon", C.c_float),
+        ("seed", C.c_uint32), ("pa_c", C.c_float), ("pa_epsilon", C.c_float), ("cov_r", C.c_float),
     ]
 
 
@@ -114,10 +114,12 @@ _OPTION_FIELDS = {
     "-lambda_v": ("lambda_v", float), "-seed": ("seed", int),
     "-hash_seed": (None, int), "-mix_interval": (None, int),     # not oracle fields
     "-aggressiveness": ("pa_c", float), "-epsilon": ("pa_epsilon", float), "-e": ("pa_epsilon", float),
+    "-r": ("cov_r", float),
 }
 # online learners on the mini-batch skeleton: function -> (task, loss id)
 _ONLINE = {"train_perceptron": (0, 3), "train_pa": (0, 4), "train_pa1": (0, 5), "train_pa2": (0, 6),
-           "train_pa1_regr": (1, 7), "train_pa2_regr": (1, 8)}
+           "train_pa1_regr": (1, 7), "train_pa2_regr": (1, 8),
+           "train_arow": (0, 9), "train_arow_regr": (1, 10), "train_arowe_regr": (1, 11)}
 _ONLINE_FIXED = {"-loss", "-loss_function", "-opt", "-optimizer", "-eta", "-eta0", "-eta_0", "-power_t", "-total_steps",
                  "-t", "-reg", "-regularization", "-lambda"}
 
@@ -127,10 +129,11 @@ def config_from_options(function_name: str, options: str = "") -> HmoConfig:
     online = _ONLINE.get(function_name)
     task = online[0] if online else {"train_classifier": 0, "train_regressor": 1, "train_fm": 2}[function_name]
     takes_c = bool(online) and online[1] in (5, 6, 7, 8)
-    takes_eps = bool(online) and online[1] in (7, 8)
+    takes_eps = bool(online) and online[1] in (7, 8, 11)
+    takes_r = bool(online) and online[1] >= 9
     c = HmoConfig()
     c.task = task
-    c.pa_c, c.pa_epsilon = 1.0, 0.1
+    c.pa_c, c.pa_epsilon, c.cov_r = 1.0, 0.1, 0.1
     c.loss = 2 if task == 1 else 0
     c.opt = 0 if task == 2 else 1
     c.eta_sched, c.reg, c.grad_norm, c.mini_batch, c.iters = 0, 0, 0, 1, 1
@@ -141,7 +144,7 @@ def config_from_options(function_name: str, options: str = "") -> HmoConfig:
     c.lambda_w0 = c.lambda_w = c.lambda_v = 0.01
     c.seed = 31
     if online:
-        c.loss, c.opt, c.eta0 = online[1], 0, 1.0
+        c.loss, c.opt, c.eta0 = online[1], (5 if online[1] >= 9 else 0), 1.0
     tok = options.split()
     i = 0
     while i < len(tok):
@@ -159,7 +162,9 @@ def config_from_options(function_name: str, options: str = "") -> HmoConfig:
         if name in ("-c", "-aggressiveness") and not takes_c:
             raise ValueError(f"{name} is an option of train_pa1, train_pa2 and their _regr forms")
         if name in ("-epsilon", "-e") and not takes_eps:
-            raise ValueError(f"{name} is an option of train_pa1_regr and train_pa2_regr")
+            raise ValueError(f"{name} is an option of train_pa1_regr, train_pa2_regr and train_arowe_regr")
+        if name == "-r" and not takes_r:
+            raise ValueError("-r is an option of train_arow, train_arow_regr and train_arowe_regr")
         if name == "-c":
             name = "-aggressiveness"
         if name not in _OPTION_FIELDS:
@@ -222,7 +227,8 @@ def train_linear(cfg: HmoConfig, rowptr, feature, value, label, w=None, s1=None,
     n = len(rowptr) - 1
     d = int(cfg.dims)
     w = np.zeros(d, np.float32) if w is None else np.array(w, np.float32)
-    s1 = np.zeros(d, np.float32) if s1 is None else np.array(s1, np.float32)
+    # (the AROW learners' slot is a variance: 1 at the start)
+    s1 = np.full(d, 1.0 if cfg.opt == 5 else 0.0, np.float32) if s1 is None else np.array(s1, np.float32)
     s2 = np.zeros(d, np.float32) if s2 is None else np.array(s2, np.float32)
     margins = np.zeros(n, np.float32)
     tt = C.c_int64(t)
@@ -243,7 +249,7 @@ def train_linear_mt(cfg: HmoConfig, rowptr, feature, value, label, threads: int)
     value = np.ascontiguousarray(value, dtype=np.float32)
     label = np.ascontiguousarray(label, dtype=np.float32)
     d = int(cfg.dims)
-    w, s1, s2 = np.zeros(d, np.float32), np.zeros(d, np.float32), np.zeros(d, np.float32)
+    w, s1, s2 = np.zeros(d, np.float32), np.full(d, 1.0 if cfg.opt == 5 else 0.0, np.float32), np.zeros(d, np.float32)
     tt = C.c_int64(0)
     rc = lib().hmo_train_linear_mt(C.byref(cfg), len(rowptr) - 1, _p(rowptr), _p(feature), _p(value), _p(label),
                                    _p(w), _p(s1), _p(s2), C.byref(tt), threads)

@@ -56,5 +56,5 @@ def run_oracle_linear(function_name: str, options: str, data: synth.Csr):
     ocfg = _oracle.config_from(cfg)
     rowptr, feature, value, label = data.numpy()
     res = _oracle.train_linear(ocfg, rowptr, feature, value, label)
-    width = 0 if cfg.opt == 0 else (1 if cfg.opt == 1 else 2)
+    width = 0 if cfg.opt == 0 else (1 if cfg.opt in (1, 5) else 2)
     return res, res.state(width)

@@ -119,3 +119,60 @@ def test_model_table_and_prediction():
         assert np.all(np.diff(feat) > 0) and np.array_equal(wt, w[feat]) and set(np.flatnonzero(w)) <= set(feat.tolist())
         import torch
         assert synth.auc(torch.from_numpy(u.predict(rowptr, feature, value)), torch.from_numpy(label)) > 0.7
+
+
+# ---- learners that keep a variance per feature (AROW): forward with margin + variance, two update launches ---
+
+COV = ["train_arow", "train_arow_regr", "train_arowe_regr"]
+
+
+def check_cov(fn, options, data, pushes=None):
+    u, w, state = run_gpu_linear(fn, options, data, pushes=pushes)
+    ref, ref_state = run_oracle_linear(fn, options, data)
+    assert u.step == ref.t and u.state_width == 1
+    assert_weights_close(w, ref.w)
+    assert_weights_close(state, ref_state, "variance")
+    assert np.count_nonzero(ref.w) > 0 and (ref_state <= 1.0).all() and (ref_state < 1.0).any()
+    u.destroy()
+    return w, state
+
+
+@pytest.mark.parametrize("fn", COV)
+@pytest.mark.parametrize("mb", [1, 64])
+def test_cov_small_batches(fn, mb):
+    if fn == "train_arow":
+        data = synth.a9a_like(1024 + 11, seed=4)
+        check_cov(fn, f"-dims 124 -mini_batch {mb} -r 1", data)
+    else:
+        data = synth.ragged(1500, dims=256, max_nnz=12, seed=6, regression=True)
+        check_cov(fn, f"-dims 256 -mini_batch {mb} -r 2" + (" -epsilon 0.05" if fn == "train_arowe_regr" else ""), data)
+
+
+@pytest.mark.parametrize("fn", COV)
+def test_cov_criteo_shaped_every_tile_size(fn):
+    """Criteo-shaped rows with real-valued quantitative columns (x^2 matters), mini-batches of 1024, 8192 and
+    20,000 rows: the three tile sizes of the update kernel, several pushes, a ragged tail."""
+    dims = 1 << 18
+    for mb, n in ((1024, 5 * 1024 + 77), (8192, 2 * 8192 + 1000), (20000, 45000)):
+        data = synth.criteo_like(n, dims=dims, seed=8)
+        if fn != "train_arow":
+            import torch
+            rng = np.random.default_rng(2)
+            data.label = data.label * 2.0 + torch.from_numpy(rng.normal(0, 0.3, data.rows).astype(np.float32))
+        norm = " -grad_norm count" if mb == 8192 else ""
+        check_cov(fn, f"-dims {dims} -mini_batch {mb} -r 1{norm}", data, pushes=[n // 3, n])
+
+
+def test_cov_determinism_replays_and_table():
+    dims = 1 << 16
+    data = synth.criteo_like(3 * 4096, dims=dims, seed=10)
+    options = f"-dims {dims} -mini_batch 4096 -iters 2 -r 0.5"
+    w1, s1 = check_cov("train_arow", options, data)
+    u, w2, s2 = run_gpu_linear("train_arow", options, data)
+    assert np.array_equal(w1, w2) and np.array_equal(s1, s2)
+    feat, wt = u.forward()[:2]
+    assert np.all(np.diff(feat) > 0) and np.array_equal(wt, w2[feat])
+    rowptr, feature, value, label = data.numpy()
+    import torch
+    assert synth.auc(torch.from_numpy(u.predict(rowptr, feature, value)), torch.from_numpy(label)) > 0.52    # (six averaged steps: a weak model, better than chance)
+    u.destroy()

@@ -94,3 +94,55 @@ def test_openmp_variant_is_bit_identical(fn):
     a = _oracle.train_linear(cfg, rp, f, v, y)
     b = _oracle.train_linear_mt(cfg, rp, f, v, y, 4)
     assert np.array_equal(a.w, b.w) and a.t == b.t
+
+
+# ---- learners that keep a variance per feature: AROW (Crammer, Kulesza, Dredze 2009), diagonal --------------
+
+def one_row_cov(fn, options, f, v, y, dims=16):
+    cfg = _oracle.config_from(hm.parse_options(fn, f"-dims {dims} " + options))
+    rp = np.array([0, len(f)], dtype=np.int64)
+    res = _oracle.train_linear(cfg, rp, np.asarray(f), np.asarray(v, np.float32), np.asarray([y], np.float32))
+    return res.w, res.s1
+
+
+def test_arow_first_step_is_the_closed_form():
+    """From w = 0, sigma = 1: v = |x|^2, beta = 1 / (v + r), alpha = beta; w_j = alpha y x_j,
+    sigma_j = 1 - beta x_j^2; features the row does not have keep sigma = 1."""
+    f, x, r = [1, 4, 9], np.array([0.5, -2.0, 1.0], np.float32), 0.5
+    w, sg = one_row_cov("train_arow", f"-r {r}", f, x, 1.0)
+    beta = 1.0 / (float((x * x).sum()) + r)
+    assert np.allclose(w[f], beta * x, rtol=1e-6)
+    assert np.allclose(sg[f], 1.0 - beta * x * x, rtol=1e-6)
+    untouched = np.setdiff1d(np.arange(16), f)
+    assert (sg[untouched] == 1.0).all() and not w[untouched].any()
+    # the variances never grow and stay positive
+    assert (sg <= 1.0).all() and (sg > 0.0).all()
+
+
+def test_arow_no_loss_no_step_and_regression_always_steps():
+    f, x = [2, 3], [1.0, 1.0]
+    cfg = _oracle.config_from(hm.parse_options("train_arow", "-dims 8"))
+    w0 = np.zeros(8, np.float32); w0[2] = 2.0
+    res = _oracle.train_linear(cfg, np.array([0, 2]), np.asarray(f), np.asarray(x, np.float32), np.array([1.0], np.float32), w=w0,
+                               s1=np.ones(8, np.float32))
+    assert np.array_equal(res.w, w0) and (res.s1 == 1.0).all()          # margin 2 >= 1: untouched
+    w, sg = one_row_cov("train_arow_regr", "-r 1", f, x, 0.3, dims=8)
+    assert abs(float(w[2] + w[3]) - 0.3 * 2 / 3) < 1e-6 and (sg[[2, 3]] < 1.0).all()   # e beta |x|^2 = 0.3 * 2 / (2 + 1)
+    w, sg = one_row_cov("train_arowe_regr", "-r 1 -epsilon 0.5", f, x, 0.3, dims=8)
+    assert not w.any() and (sg == 1.0).all()                            # inside the insensitive zone
+
+
+def test_arow_learns_and_confidence_grows_with_evidence():
+    data = synth.a9a_like(4096, seed=1)
+    rp, f, v, y = data.numpy()
+    cfg = _oracle.config_from(hm.parse_options("train_arow", "-dims 124 -mini_batch 1 -r 1"))
+    res = _oracle.train_linear(cfg, rp, f, v, y)
+    import torch
+    assert synth.auc(torch.from_numpy(_oracle.predict_linear(rp, f, v, res.w)), torch.from_numpy(y)) > 0.8
+    counts = np.bincount(f, minlength=124)
+    seen = counts > 0
+    assert (res.s1[~seen] == 1.0).all() and (res.s1[seen] < 1.0).all() and (res.s1 > 0).all()
+    # frequent features end up with smaller variances than rare ones
+    order = np.argsort(counts[seen])
+    sg = res.s1[seen][order]
+    assert sg[: len(sg) // 4].mean() > sg[-len(sg) // 4:].mean()

@@ -54,6 +54,11 @@ def test_numeric_options_round_trip():
     ("train_pa2", "-c 0"),
     ("train_pa2", "-c"),
     ("train_classifier", "-aggressiveness 1"),
+    ("train_arow", "-c 1"),
+    ("train_arow", "-epsilon 0.1"),             # only the regression with an insensitive zone has it
+    ("train_arow", "-r 0"),
+    ("train_pa1", "-r 1"),
+    ("train_arow_regr", "-opt sgd"),
     ("train_classifier", "-eta0 nan"),
     ("train_classifier", "-dims -5"),
 ])
@@ -83,6 +88,9 @@ def test_error_names_the_offending_token():
     ("train_pa2", "-aggressiveness 3"),
     ("train_pa1_regr", "-c 0.5 -epsilon 0.01 -mini_batch 64"),
     ("train_pa2_regr", "-e 0.2"),
+    ("train_arow", "-r 0.5 -mini_batch 32"),
+    ("train_arow_regr", ""),
+    ("train_arowe_regr", "-r 2 -epsilon 0.3 -dims 1024"),
 ])
 def test_oracle_side_parser_agrees_with_the_library(fn, opts):
     """bench.py's CPU arm builds its oracle config with tests/_oracle.config_from_options so that its
@@ -103,3 +111,11 @@ def test_online_learner_functions():
         assert c.eta0 == 1.0 and c.pa_c == 1.0 and abs(c.pa_epsilon - 0.1) < 1e-8
     c = hm.parse_options("train_pa1_regr", "-c 0.25 -e 0.5")
     assert c.pa_c == 0.25 and c.pa_epsilon == 0.5
+
+
+def test_variance_keeping_learner_functions():
+    for fn, task, loss in [("train_arow", 0, 9), ("train_arow_regr", 1, 10), ("train_arowe_regr", 1, 11)]:
+        c = hm.parse_options(fn, "")
+        assert (c.task, c.loss, c.opt, c.mini_batch) == (task, loss, 5, 1), fn
+        assert abs(c.cov_r - 0.1) < 1e-8 and c.eta0 == 1.0
+    assert hm.parse_options("train_arow", "-r 3").cov_r == 3.0

@@ -99,7 +99,58 @@ def np_row_coef(cfg, m, y, xx):
     return F(-F(tau * d))
 
 
+def np_cov_coefs(cfg, m, y, v):
+    """AROW (Crammer, Kulesza, Dredze 2009), diagonal: (c1, c2) for the weight and the variance sums."""
+    if cfg.loss == 9:
+        l, d = F(F(1.0) - F(y * m)), y
+        if not l > 0:
+            return F(0.0), F(0.0)
+    else:
+        e = F(y - m)
+        d = F(-1.0) if e < 0 else F(1.0)
+        l = F(abs(e)) if cfg.loss == 10 else F(abs(e) - F(cfg.pa_epsilon))
+        if cfg.loss == 11 and not l > 0:
+            return F(0.0), F(0.0)
+    beta = F(F(1.0) / F(v + F(cfg.cov_r)))
+    alpha = F(l * beta)
+    return F(-F(alpha * d)), beta
+
+
+def np_train_cov(cfg, rowptr, feat, val, label):
+    D, B = int(cfg.dims), int(cfg.mini_batch)
+    w = np.zeros(D, F); sg = np.ones(D, F)
+    n = len(label); t = 0
+    for _ in range(cfg.iters):
+        for b0 in range(0, n, B):
+            b1 = min(n, b0 + B)
+            cs = []
+            for i in range(b0, b1):
+                am, av = 0.0, 0.0
+                for p in range(rowptr[i], rowptr[i + 1]):
+                    am += float(F(w[feat[p]] * val[p]))
+                    av += float(F(sg[feat[p]] * F(val[p] * val[p])))
+                y = (F(1.0) if label[i] > 0 else F(-1.0)) if cfg.task == 0 else F(label[i])
+                cs.append(np_cov_coefs(cfg, F(am), y, F(av)))
+            s1, s2, cnts = {}, {}, {}
+            for i in range(b0, b1):
+                for p in range(rowptr[i], rowptr[i + 1]):
+                    j = int(feat[p])
+                    s1[j] = s1.get(j, 0.0) + float(F(cs[i - b0][0] * val[p]))
+                    s2[j] = s2.get(j, 0.0) + float(F(cs[i - b0][1] * F(val[p] * val[p])))
+                    cnts[j] = cnts.get(j, 0) + 1
+            t += 1
+            for j in s1:
+                def mean(sm):
+                    return F(sm * (1.0 / float(b1 - b0))) if cfg.grad_norm == 0 else (F(sm / float(cnts[j])) if cfg.grad_norm == 1 else F(sm))
+                g1, g2, s = mean(s1[j]), mean(s2[j]), sg[j]
+                w[j] = F(w[j] - F(s * g1))
+                sg[j] = F(s - F(F(s * s) * g2))
+    return w, sg, np.zeros(D, F), t
+
+
 def np_train(cfg, rowptr, feat, val, label):
+    if cfg.loss >= 9:
+        return np_train_cov(cfg, rowptr, feat, val, label)
     D, B = int(cfg.dims), int(cfg.mini_batch)
     w = np.zeros(D, F); s1 = np.zeros(D, F); s2 = np.zeros(D, F)
     n = len(label); t = 0
@@ -193,9 +244,16 @@ def np_train(cfg, rowptr, feat, val, label):
     ("-mini_batch 8 -dims 50 -e 0.2 -iters 2", "train_pa1_regr"),
     ("-mini_batch 1 -dims 50 -c 0.7", "train_pa2_regr"),
     ("-mini_batch 7 -dims 50 -c 5 -epsilon 0.01 -grad_norm count", "train_pa2_regr"),
+    # learners that keep a variance per feature
+    ("-mini_batch 1 -dims 50 -iters 2", "train_arow"),
+    ("-mini_batch 6 -dims 50 -r 1.0 -grad_norm count", "train_arow"),
+    ("-mini_batch 1 -dims 50 -r 0.5", "train_arow_regr"),
+    ("-mini_batch 8 -dims 50 -grad_norm sum -r 10", "train_arow_regr"),
+    ("-mini_batch 1 -dims 50 -epsilon 0.05", "train_arowe_regr"),
+    ("-mini_batch 5 -dims 50 -epsilon 0.2 -r 2 -iters 2", "train_arowe_regr"),
 ])
 def test_oracle_matches_numpy_restatement(options, fn):
-    data = synth.ragged(120, dims=50, max_nnz=9, seed=2, regression=fn in ("train_regressor", "train_pa1_regr", "train_pa2_regr"))
+    data = synth.ragged(120, dims=50, max_nnz=9, seed=2, regression=fn in ("train_regressor", "train_pa1_regr", "train_pa2_regr", "train_arow_regr", "train_arowe_regr"))
     rp, f, v, y = data.numpy()
     cfg = _oracle.config_from(hm.parse_options(fn, options))
     res = _oracle.train_linear(cfg, rp, f, v, y)
