@@ -67,7 +67,11 @@ def main(out_dir):
                         ("train_pa1", f"-mini_batch 16 -dims {dims} -c 0.1"),
                         ("train_pa2", f"-mini_batch 16 -dims {dims} -c 0.1"),
                         ("train_pa1_regr", f"-mini_batch 16 -dims {dims} -c 0.1 -epsilon 0.05"),
-                        ("train_pa2_regr", f"-mini_batch 16 -dims {dims} -c 0.1 -epsilon 0.05")):
+                        ("train_pa2_regr", f"-mini_batch 16 -dims {dims} -c 0.1 -epsilon 0.05"),
+                        # (s1 = the per-feature variance, 1 where the learner has seen nothing)
+                        ("train_arow", f"-mini_batch 16 -dims {dims} -r 0.5"),
+                        ("train_arow_regr", f"-mini_batch 16 -dims {dims} -r 0.5"),
+                        ("train_arowe_regr", f"-mini_batch 16 -dims {dims} -r 0.5 -epsilon 0.05")):
         first = impl.linear(fn, options, small_rows(16, dims, 1))
         before = {"t": first["t"], **{k: _golden.sparse(first[k]) for k in ("w", "s1", "s2")}}
         rows = small_rows(16, dims, 2)
