@@ -16,11 +16,12 @@ from .udtf import (  # noqa: F401
     train_perceptron, train_pa, train_pa1, train_pa2, train_pa1_regr, train_pa2_regr,
     add_bias, add_bias_csr, BIAS_FEATURE, BIAS_CLAUSE,
     AROWClassifierUDTF, AROWRegressionUDTF, AROWeRegressionUDTF, train_arow, train_arow_regr, train_arowe_regr,
+    ConfidenceWeightedUDTF, SoftConfidenceWeighted1UDTF, SoftConfidenceWeighted2UDTF, train_cw, train_scw, train_scw2,
 )
 
 __all__ = [
     "UDTF", "TrainClassifierUDTF", "TrainRegressorUDTF", "FactorizationMachineUDTF",
     "train_classifier", "train_regressor", "train_fm", "mhash", "feature_hashing",
     "train_perceptron", "train_pa", "train_pa1", "train_pa2", "train_pa1_regr", "train_pa2_regr",
-    "train_arow", "train_arow_regr", "train_arowe_regr", "add_bias", "add_bias_csr", "parse_options", "host_alloc", "host_free", "bind_host_to_gpu", "HivemallError", "UDFArgumentError",
+    "train_arow", "train_arow_regr", "train_arowe_regr", "train_cw", "train_scw", "train_scw2", "add_bias", "add_bias_csr", "parse_options", "host_alloc", "host_free", "bind_host_to_gpu", "HivemallError", "UDFArgumentError",
 ]

@@ -543,9 +543,51 @@ __global__ void __launch_bounds__(kFwdThreads, 8) linear_forward_kernel(FwdParam
 // Forward: margin m = sum w_j x_j AND variance v = sum sigma_j x_j^2 of a row from one 8-byte gather per
 // element (the record is (w, sigma)); then the two numbers that stand in dloss's place: c1 for the weight
 // sums (times x), c2 = beta for the variance sums (times x^2).  Crammer, Kulesza, Dredze 2009, diagonal.
-__device__ __forceinline__ void cov_coefs(int loss, float m, float y, float v, float r, float eps, float *c1, float *c2)
+__device__ __forceinline__ void cov_coefs(int loss, float m, float y, float v, float r, float eps, float phi, float cc,
+                                          float *c1, float *c2)
 {
     *c1 = 0.0f; *c2 = 0.0f;
+    if (loss >= HM_LOSS_CW) {
+        // Confidence-weighted (Dredze, Crammer, Pereira 2008, variance form) and soft confidence-weighted
+        // learning (Wang, Zhao, Hoi 2012), diagonal: alpha from the closed forms, c1 = -alpha y;
+        // CW: the PRECISION grows by 2 alpha phi x^2 (c2 = 2 alpha phi); SCW: sigma -= beta sigma^2 x^2 (c2 = beta).
+        if (!(v > 0.0f)) return;
+        const float my = __fmul_rn(y, m), p2 = __fmul_rn(phi, phi);
+        float alpha;
+        if (loss == HM_LOSS_CW) {
+            const float q = __fadd_rn(1.0f, __fmul_rn(__fmul_rn(2.0f, phi), my));
+            const float rad = __fsub_rn(__fmul_rn(q, q), __fmul_rn(__fmul_rn(8.0f, phi), __fsub_rn(my, __fmul_rn(phi, v))));
+            if (!(rad >= 0.0f)) return;
+            alpha = __fdiv_rn(__fsub_rn(__fsqrt_rn(rad), q), __fmul_rn(__fmul_rn(4.0f, phi), v));
+            if (!(alpha > 0.0f)) return;
+            *c1 = -__fmul_rn(alpha, y);
+            *c2 = __fmul_rn(__fmul_rn(2.0f, alpha), phi);
+            return;
+        }
+        if (!(__fsub_rn(__fmul_rn(phi, __fsqrt_rn(v)), my) > 0.0f)) return;      // loss = phi sqrt(v) - y m
+        const float t1 = __fmul_rn(my, my);
+        if (loss == HM_LOSS_SCW1) {
+            const float psi = __fadd_rn(1.0f, __fmul_rn(p2, 0.5f)), zeta = __fadd_rn(1.0f, p2);
+            const float rad = __fadd_rn(__fmul_rn(__fmul_rn(t1, __fmul_rn(p2, p2)), 0.25f), __fmul_rn(__fmul_rn(v, p2), zeta));
+            alpha = __fdiv_rn(__fsub_rn(__fsqrt_rn(rad), __fmul_rn(my, psi)), __fmul_rn(v, zeta));
+            alpha = fminf(cc, alpha);
+        } else {
+            const float n = __fadd_rn(v, __fdiv_rn(0.5f, cc));
+            const float vp2 = __fmul_rn(v, p2);
+            const float g1 = __fmul_rn(__fmul_rn(__fmul_rn(p2, t1), v), v);
+            const float g2 = __fmul_rn(__fmul_rn(__fmul_rn(4.0f, n), v), __fadd_rn(n, vp2));
+            const float gamma = __fmul_rn(phi, __fsqrt_rn(__fadd_rn(g1, g2)));
+            const float num = __fsub_rn(gamma, __fadd_rn(__fmul_rn(__fmul_rn(2.0f, my), n), __fmul_rn(__fmul_rn(p2, my), v)));
+            const float den = __fmul_rn(2.0f, __fadd_rn(__fmul_rn(n, n), __fmul_rn(__fmul_rn(n, v), p2)));
+            alpha = __fdiv_rn(num, den);
+        }
+        if (!(alpha > 0.0f)) return;
+        const float avp = __fmul_rn(__fmul_rn(alpha, v), phi);
+        const float usq = __fmul_rn(0.5f, __fsub_rn(__fsqrt_rn(__fadd_rn(__fmul_rn(avp, avp), __fmul_rn(4.0f, v))), avp));
+        *c1 = -__fmul_rn(alpha, y);
+        *c2 = __fdiv_rn(__fmul_rn(alpha, phi), __fadd_rn(usq, avp));
+        return;
+    }
     float l, dir;
     if (loss == HM_LOSS_AROW) { l = __fsub_rn(1.0f, __fmul_rn(y, m)); dir = y; if (!(l > 0.0f)) return; }
     else if (loss == HM_LOSS_AROW_REGR) { const float e = __fsub_rn(y, m); l = fabsf(e); dir = e < 0.0f ? -1.0f : 1.0f; }
@@ -564,7 +606,7 @@ struct FwdCovParams {
     float *margin, *c1, *c2;
     int64_t block_row0, row0;
     int32_t n_rows, task, loss;
-    float r, eps;
+    float r, eps, phi, cc;
     uint32_t dims;
     uint32_t *bad;
 };
@@ -594,7 +636,7 @@ __global__ void __launch_bounds__(kFwdThreads) linear_forward_cov_kernel(FwdCovP
             const float lab = P.label[row];
             const float y = P.task == HM_TASK_CLASSIFIER ? (lab > 0.0f ? 1.0f : -1.0f) : lab;
             float c1, c2;
-            cov_coefs(P.loss, m, y, (float)av, P.r, P.eps, &c1, &c2);
+            cov_coefs(P.loss, m, y, (float)av, P.r, P.eps, P.phi, P.cc, &c1, &c2);
             P.c1[r] = c1; P.c2[r] = c2;
         }
     }
@@ -646,6 +688,7 @@ struct UpdParams {
     uint32_t dims;
     int32_t opt, reg, grad_norm;
     int32_t square;          // HM_OPT_COV, variance pass: the sums run over dloss * value^2 and step the variance
+                             // (1: sigma -= sigma^2 g; 2: 1/sigma += g, the confidence-weighted form)
     float lambda, eps, rho, beta1, beta2, alpha, beta, lambda1, lambda2;
     // (the mini-batch's bounds in the sorted arrays are read from seg_off: the sorted arrays are shorter
     // than the CSR by the hot-feature and out-of-range elements, a number only the device knows)
@@ -733,7 +776,8 @@ __device__ __forceinline__ void step_rec(const UpdParams &P, const UpdDyn &D, Re
         break;
     }
     case HM_OPT_COV: {    // s1 = the feature's variance; both passes use its value of the start of the mini-batch
-        if (P.square) r.s1 = __fsub_rn(r.s1, __fmul_rn(__fmul_rn(r.s1, r.s1), g));
+        if (P.square == 2) r.s1 = __fdiv_rn(1.0f, __fadd_rn(__fdiv_rn(1.0f, r.s1), g));     // CW: the precision grows
+        else if (P.square) r.s1 = __fsub_rn(r.s1, __fmul_rn(__fmul_rn(r.s1, r.s1), g));
         else wv = __fsub_rn(wv, __fmul_rn(r.s1, g));
         break;
     }
@@ -1070,7 +1114,7 @@ hm_status launch_linear_forward_cov(Launcher &L, const LinearArgs &a, const int6
     FwdCovParams P;
     P.rec = a.rec; P.rowptr = d_rowptr; P.feature = d_feature; P.value = d_value; P.label = d_label;
     P.margin = d_margin; P.c1 = d_c1; P.c2 = d_c2; P.block_row0 = block_row0; P.row0 = row0; P.n_rows = n_rows;
-    P.task = a.cfg.task; P.loss = a.cfg.loss; P.r = a.cfg.cov_r; P.eps = a.cfg.pa_epsilon;
+    P.task = a.cfg.task; P.loss = a.cfg.loss; P.r = a.cfg.cov_r; P.eps = a.cfg.pa_epsilon; P.phi = a.cfg.cov_phi; P.cc = a.cfg.pa_c;
     P.dims = (uint32_t)a.cfg.dims; P.bad = d_bad;
     HM_LAUNCH(L, K_LIN_FORWARD, 16.0 * (double)nnz_hint + 24.0 * (double)n_rows,
               (linear_forward_cov_kernel<<<linear_forward_grid(n_rows), kFwdThreads, 0, L.stream>>>(P)));
@@ -1149,7 +1193,7 @@ hm_status launch_linear_update(Launcher &L, const LinearArgs &a, const StepScala
     P.br.last = P.br.first + us.grid;
     P.br.ticket = us.done_counter;
     P.dyn.seg = seg; P.dims = (uint32_t)a.cfg.dims;
-    P.opt = a.cfg.opt; P.reg = a.cfg.reg; P.grad_norm = a.cfg.grad_norm; P.square = a.cov_pass == 2;
+    P.opt = a.cfg.opt; P.reg = a.cfg.reg; P.grad_norm = a.cfg.grad_norm; P.square = a.cov_pass == 2 ? (a.cfg.loss == HM_LOSS_CW ? 2 : 1) : 0;
     P.dyn.eta = sc.eta; P.dyn.adam_alpha = sc.adam_alpha; P.lambda = a.cfg.lambda; P.eps = a.cfg.eps; P.rho = a.cfg.rho;
     P.beta1 = a.cfg.beta1; P.beta2 = a.cfg.beta2; P.alpha = a.cfg.alpha; P.beta = a.cfg.beta;
     P.lambda1 = a.cfg.lambda1; P.lambda2 = a.cfg.lambda2;

@@ -94,6 +94,7 @@ static void defaults(hm_config *c, int task)
     c->pa_c = 1.0f;
     c->pa_epsilon = 0.1f;
     c->cov_r = 0.1f;
+    c->cov_phi = 1.0f;
 }
 
 hm_status parse_options(const char *function_name, const char *options, hm_config *out)
@@ -114,9 +115,12 @@ hm_status parse_options(const char *function_name, const char *options, hm_confi
     else if (fn == "train_arow") { task = HM_TASK_CLASSIFIER; online = HM_LOSS_AROW; }
     else if (fn == "train_arow_regr") { task = HM_TASK_REGRESSOR; online = HM_LOSS_AROW_REGR; }
     else if (fn == "train_arowe_regr") { task = HM_TASK_REGRESSOR; online = HM_LOSS_AROWE_REGR; }
+    else if (fn == "train_cw") { task = HM_TASK_CLASSIFIER; online = HM_LOSS_CW; }
+    else if (fn == "train_scw") { task = HM_TASK_CLASSIFIER; online = HM_LOSS_SCW1; }
+    else if (fn == "train_scw2") { task = HM_TASK_CLASSIFIER; online = HM_LOSS_SCW2; }
     else HM_FAIL(HM_ERR_INVALID_ARGUMENT, "unknown function '%s' (expected train_classifier, train_regressor, train_fm, "
-                 "train_perceptron, train_pa, train_pa1, train_pa2, train_pa1_regr, train_pa2_regr, train_arow, train_arow_regr "
-                 "or train_arowe_regr)", function_name);
+                 "train_perceptron, train_pa, train_pa1, train_pa2, train_pa1_regr, train_pa2_regr, train_arow, train_arow_regr, "
+                 "train_arowe_regr, train_cw, train_scw or train_scw2)", function_name);
     hm_config c;
     defaults(&c, task);
     if (online >= 0) {
@@ -124,8 +128,10 @@ hm_status parse_options(const char *function_name, const char *options, hm_confi
         c.loss = online; c.opt = HM_OPT_SGD; c.eta_sched = HM_ETA_FIXED; c.eta0 = 1.0f; c.reg = HM_REG_NONE;
         if (online >= HM_LOSS_AROW) c.opt = HM_OPT_COV;
     }
-    const bool takes_r = online >= HM_LOSS_AROW;
-    const bool takes_c = online == HM_LOSS_PA1 || online == HM_LOSS_PA2 || online == HM_LOSS_PA1_REGR || online == HM_LOSS_PA2_REGR;
+    const bool takes_r = online >= HM_LOSS_AROW && online <= HM_LOSS_AROWE_REGR;
+    const bool takes_phi = online >= HM_LOSS_CW;
+    const bool takes_c = online == HM_LOSS_PA1 || online == HM_LOSS_PA2 || online == HM_LOSS_PA1_REGR || online == HM_LOSS_PA2_REGR ||
+                         online == HM_LOSS_SCW1 || online == HM_LOSS_SCW2;
     const bool takes_eps = online == HM_LOSS_PA1_REGR || online == HM_LOSS_PA2_REGR || online == HM_LOSS_AROWE_REGR;
 
     std::vector<std::string> tok;
@@ -175,11 +181,14 @@ hm_status parse_options(const char *function_name, const char *options, hm_confi
                             name == "-lambda"))
             HM_FAIL(HM_ERR_INVALID_ARGUMENT, "%s is fixed by %s", name.c_str(), function_name);
         if (name == "-c" || name == "-aggressiveness") {
-            if (!takes_c) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "%s is an option of train_pa1, train_pa2 and their _regr forms", name.c_str());
+            if (!takes_c) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "%s is an option of train_pa1, train_pa2, their _regr forms, train_scw and train_scw2", name.c_str());
             NEED_F(1e-12, 1e12); c.pa_c = (float)d;
         } else if (name == "-epsilon" || name == "-e") {
             if (!takes_eps) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "%s is an option of train_pa1_regr, train_pa2_regr and train_arowe_regr", name.c_str());
             NEED_F(0.0, 1e12); c.pa_epsilon = (float)d;
+        } else if (name == "-phi") {
+            if (!takes_phi) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "-phi is an option of train_cw, train_scw and train_scw2");
+            NEED_F(1e-6, 1e6); c.cov_phi = (float)d;
         } else if (name == "-r") {
             if (!takes_r) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "-r is an option of train_arow, train_arow_regr and train_arowe_regr");
             NEED_F(1e-12, 1e12); c.cov_r = (float)d;

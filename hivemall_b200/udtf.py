@@ -584,3 +584,30 @@ def train_arow_regr(options: str = "", device: int = 0) -> AROWRegressionUDTF:
 
 def train_arowe_regr(options: str = "", device: int = 0) -> AROWeRegressionUDTF:
     return AROWeRegressionUDTF(options, device)
+
+
+# Confidence-weighted (Dredze, Crammer, Pereira 2008) and soft confidence-weighted (Wang, Zhao, Hoi 2012)
+# learners: the same two passes as AROW with other closed forms for the step.
+
+class ConfidenceWeightedUDTF(UDTF):
+    function_name = "train_cw"
+
+
+class SoftConfidenceWeighted1UDTF(UDTF):
+    function_name = "train_scw"
+
+
+class SoftConfidenceWeighted2UDTF(UDTF):
+    function_name = "train_scw2"
+
+
+def train_cw(options: str = "", device: int = 0) -> ConfidenceWeightedUDTF:
+    return ConfidenceWeightedUDTF(options, device)
+
+
+def train_scw(options: str = "", device: int = 0) -> SoftConfidenceWeighted1UDTF:
+    return SoftConfidenceWeighted1UDTF(options, device)
+
+
+def train_scw2(options: str = "", device: int = 0) -> SoftConfidenceWeighted2UDTF:
+    return SoftConfidenceWeighted2UDTF(options, device)

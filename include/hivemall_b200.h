@@ -53,7 +53,9 @@ enum { HM_LOSS_LOG = 0, HM_LOSS_HINGE = 1, HM_LOSS_SQUARED = 2,
        /* learners that keep a per-feature variance beside the weight (train_arow, train_arow_regr,
         * train_arowe_regr): the forward pass also yields the row's variance, and a mini-batch ends in two
         * reduce-and-step launches, one for the weights and one for the variances */
-       HM_LOSS_AROW = 9, HM_LOSS_AROW_REGR = 10, HM_LOSS_AROWE_REGR = 11 };
+       HM_LOSS_AROW = 9, HM_LOSS_AROW_REGR = 10, HM_LOSS_AROWE_REGR = 11,
+       /* ... and the confidence-weighted family on the same two passes (train_cw, train_scw, train_scw2) */
+       HM_LOSS_CW = 12, HM_LOSS_SCW1 = 13, HM_LOSS_SCW2 = 14 };
 enum { HM_OPT_SGD = 0, HM_OPT_ADAGRAD = 1, HM_OPT_ADADELTA = 2, HM_OPT_ADAM = 3, HM_OPT_FTRL = 4,
        HM_OPT_COV = 5 /* set by the variance-keeping learners, not by -opt: state = one variance per feature, 1 at the start */ };
 enum { HM_ETA_FIXED = 0, HM_ETA_INVERSE = 1, HM_ETA_SIMPLE = 2 };
@@ -83,7 +85,8 @@ typedef struct hm_config {
     float   pa_c;            /* passive-aggressive learners: aggressiveness C (PA-I cap, PA-II slack) */
     float   pa_epsilon;      /* ... regression: width of the insensitive zone (also train_arowe_regr) */
     float   cov_r;           /* train_arow*: regularisation r of the variance update */
-    int32_t reserved[5];
+    float   cov_phi;         /* train_cw, train_scw, train_scw2: confidence phi = probit(eta) */
+    int32_t reserved[4];
 } hm_config;
 
 typedef struct hm_udtf hm_udtf; /* opaque learner = one UDTF instance on one GPU */
@@ -132,10 +135,11 @@ hm_status hm_feature_hashing(const uint8_t *bytes, const int64_t *offsets, int64
 /* function_name: "train_classifier" | "train_regressor" | "train_fm", or one of the online learners on the
  * same skeleton: "train_perceptron" | "train_pa" | "train_pa1" | "train_pa2" (labels as train_classifier) |
  * "train_pa1_regr" | "train_pa2_regr" (targets as train_regressor) | "train_arow" (labels) |
- * "train_arow_regr" | "train_arowe_regr" (targets).  Those fix loss, optimizer, eta (1) and regularisation
+ * "train_arow_regr" | "train_arowe_regr" (targets) | "train_cw" | "train_scw" | "train_scw2" (labels).  Those fix loss, optimizer, eta (1) and regularisation
  * (none) themselves and take -mini_batch, -iters, -dims, -grad_norm, -mix_interval, -hash_seed, plus
  * -c / -aggressiveness (train_pa1, train_pa2, train_pa*_regr; default 1), -epsilon / -e (train_pa*_regr,
- * train_arowe_regr; default 0.1) and -r (train_arow*; default 0.1).
+ * train_arowe_regr; default 0.1), -r (train_arow*; default 0.1) and -phi (train_cw, train_scw, train_scw2;
+ * default 1; train_scw and train_scw2 also take -c).
  * Unknown options, missing values and out-of-range numbers are
  * HM_ERR_INVALID_ARGUMENT with the offending token in hm_last_error(). */
 hm_status hm_parse_options(const char *function_name, const char *options, hm_config *out);

@@ -132,6 +132,51 @@ float hmo_row_coef(const hmo_config *c, float m, float y, float xx)
 void hmo_cov_coefs(const hmo_config *c, float m, float y, float v, float *c1, float *c2)
 {
     *c1 = 0.0f; *c2 = 0.0f;
+    if (c->loss >= HMO_LOSS_CW) {
+        /* CW: alpha = max(0, (-(1 + 2 phi M) + sqrt((1 + 2 phi M)^2 - 8 phi (M - phi v))) / (4 phi v)), M = y m;
+         * the precision of feature j grows by 2 alpha phi x_j^2.
+         * SCW (loss phi sqrt(v) - M > 0): SCW-I alpha = min(C, (sqrt(M^2 phi^4 / 4 + v phi^2 zeta) - M psi) / (v zeta)),
+         * psi = 1 + phi^2 / 2, zeta = 1 + phi^2; SCW-II alpha = (gamma - (2 M n + phi^2 M v)) / (2 (n^2 + n v phi^2)),
+         * n = v + 1 / (2C), gamma = phi sqrt(phi^2 M^2 v^2 + 4 n v (n + v phi^2));
+         * sqrt(u) = (sqrt(alpha^2 v^2 phi^2 + 4 v) - alpha v phi) / 2, beta = alpha phi / (sqrt(u) + alpha v phi). */
+        const float phi = c->cov_phi, cc = c->pa_c;
+        if (!(v > 0.0f)) return;
+        const float my = y * m, p2 = phi * phi;
+        float alpha;
+        if (c->loss == HMO_LOSS_CW) {
+            const float q = 1.0f + (2.0f * phi) * my;
+            const float rad = q * q - (8.0f * phi) * (my - phi * v);
+            if (!(rad >= 0.0f)) return;
+            alpha = (sqrtf(rad) - q) / ((4.0f * phi) * v);
+            if (!(alpha > 0.0f)) return;
+            *c1 = -(alpha * y);
+            *c2 = (2.0f * alpha) * phi;
+            return;
+        }
+        if (!(phi * sqrtf(v) - my > 0.0f)) return;
+        const float t1 = my * my;
+        if (c->loss == HMO_LOSS_SCW1) {
+            const float psi = 1.0f + p2 * 0.5f, zeta = 1.0f + p2;
+            const float rad = (t1 * (p2 * p2)) * 0.25f + (v * p2) * zeta;
+            alpha = (sqrtf(rad) - my * psi) / (v * zeta);
+            alpha = fminf(cc, alpha);
+        } else {
+            const float n = v + 0.5f / cc;
+            const float vp2 = v * p2;
+            const float g1 = ((p2 * t1) * v) * v;
+            const float g2 = ((4.0f * n) * v) * (n + vp2);
+            const float gamma = phi * sqrtf(g1 + g2);
+            const float num = gamma - ((2.0f * my) * n + (p2 * my) * v);
+            const float den = 2.0f * (n * n + (n * v) * p2);
+            alpha = num / den;
+        }
+        if (!(alpha > 0.0f)) return;
+        const float avp = (alpha * v) * phi;
+        const float usq = 0.5f * (sqrtf(avp * avp + 4.0f * v) - avp);
+        *c1 = -(alpha * y);
+        *c2 = (alpha * phi) / (usq + avp);
+        return;
+    }
     float l, dir;
     if (c->loss == HMO_LOSS_AROW) { l = 1.0f - y * m; dir = y; if (!(l > 0.0f)) return; }
     else if (c->loss == HMO_LOSS_AROW_REGR) { const float e = y - m; l = fabsf(e); dir = e < 0.0f ? -1.0f : 1.0f; }
@@ -202,8 +247,8 @@ static int train_cov(const hmo_config *c, int64_t n_rows, const int64_t *rowptr,
                 const float m1 = mean_grad(c, g1[j], cnt[j], inv_nb), m2 = mean_grad(c, g2[j], cnt[j], inv_nb);
                 const float s = sg[j];
                 w[j] = w[j] - s * m1;            /* both steps use the variance of the start of the mini-batch */
-                const float ss = s * s;
-                sg[j] = s - ss * m2;
+                if (c->loss == HMO_LOSS_CW) sg[j] = 1.0f / (1.0f / s + m2);       /* the precision grows */
+                else { const float ss = s * s; sg[j] = s - ss * m2; }
                 g1[j] = 0.0; g2[j] = 0.0; cnt[j] = 0;
             }
         }
@@ -225,7 +270,7 @@ double hmo_loss(int32_t loss, float m, float y)
     double z = (double)y * (double)m;
     if (loss == HMO_LOSS_PERCEPTRON) return z <= 0.0 ? -z : 0.0;
     if (loss == HMO_LOSS_PA || loss == HMO_LOSS_PA1 || loss == HMO_LOSS_PA2) loss = HMO_LOSS_HINGE;
-    if (loss == HMO_LOSS_AROW) loss = HMO_LOSS_HINGE;
+    if (loss == HMO_LOSS_AROW || loss >= HMO_LOSS_CW) loss = HMO_LOSS_HINGE;
     if (loss == HMO_LOSS_AROW_REGR || loss == HMO_LOSS_AROWE_REGR) return fabs((double)y - (double)m);
     if (loss == HMO_LOSS_PA1_REGR || loss == HMO_LOSS_PA2_REGR) return fabs((double)y - (double)m);   /* (epsilon not known here) */
     switch (loss) {

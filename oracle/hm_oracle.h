@@ -30,7 +30,10 @@ enum { HMO_LOSS_LOG = 0, HMO_LOSS_HINGE = 1, HMO_LOSS_SQUARED = 2,
        HMO_LOSS_PA1_REGR = 7, HMO_LOSS_PA2_REGR = 8,
        /* adaptive regularization of weights (Crammer, Kulesza, Dredze, NIPS 2009), diagonal covariance:
         * classification, regression, regression with an insensitive zone */
-       HMO_LOSS_AROW = 9, HMO_LOSS_AROW_REGR = 10, HMO_LOSS_AROWE_REGR = 11 };
+       HMO_LOSS_AROW = 9, HMO_LOSS_AROW_REGR = 10, HMO_LOSS_AROWE_REGR = 11,
+       /* confidence-weighted (Dredze, Crammer, Pereira, ICML 2008) and soft confidence-weighted learning
+        * (Wang, Zhao, Hoi, ICML 2012), diagonal covariance */
+       HMO_LOSS_CW = 12, HMO_LOSS_SCW1 = 13, HMO_LOSS_SCW2 = 14 };
 enum { HMO_OPT_SGD = 0, HMO_OPT_ADAGRAD = 1, HMO_OPT_ADADELTA = 2, HMO_OPT_ADAM = 3, HMO_OPT_FTRL = 4,
        HMO_OPT_COV = 5 /* the AROW learners: s1 = per-feature variance, 1 at the start (the CALLER fills it) */ };
 enum { HMO_ETA_FIXED = 0, HMO_ETA_INVERSE = 1, HMO_ETA_SIMPLE = 2 };
@@ -60,6 +63,7 @@ typedef struct hmo_config {
     float   pa_c;                 /* aggressiveness C */
     float   pa_epsilon;           /* regression: insensitive zone */
     float   cov_r;                /* AROW: regularisation r */
+    float   cov_phi;              /* CW / SCW: confidence phi */
 } hmo_config;
 
 /* MurmurHash3_x86_32 (Appleby, public domain algorithm). */

@@ -71,7 +71,10 @@ def main(out_dir):
                         # (s1 = the per-feature variance, 1 where the learner has seen nothing)
                         ("train_arow", f"-mini_batch 16 -dims {dims} -r 0.5"),
                         ("train_arow_regr", f"-mini_batch 16 -dims {dims} -r 0.5"),
-                        ("train_arowe_regr", f"-mini_batch 16 -dims {dims} -r 0.5 -epsilon 0.05")):
+                        ("train_arowe_regr", f"-mini_batch 16 -dims {dims} -r 0.5 -epsilon 0.05"),
+                        ("train_cw", f"-mini_batch 16 -dims {dims} -phi 0.5"),
+                        ("train_scw", f"-mini_batch 16 -dims {dims} -phi 0.8 -c 0.1"),
+                        ("train_scw2", f"-mini_batch 16 -dims {dims} -c 0.1")):
         first = impl.linear(fn, options, small_rows(16, dims, 1))
         before = {"t": first["t"], **{k: _golden.sparse(first[k]) for k in ("w", "s1", "s2")}}
         rows = small_rows(16, dims, 2)

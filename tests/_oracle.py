@@ -21,7 +21,7 @@ class HmoConfig(C.Structure):
         ("alpha", C.c_float), ("beta", C.c_float), ("lambda1", C.c_float), ("lambda2", C.c_float),
         ("factors", C.c_int32), ("fm_classification", C.c_int32), ("sigma", C.c_float),
         ("lambda_w0", C.c_float), ("lambda_w", C.c_float), ("lambda_v", C.c_float),
-        ("seed", C.c_uint32), ("pa_c", C.c_float), ("pa_epsilon", C.c_float), ("cov_r", C.c_float),
+        ("seed", C.c_uint32), ("pa_c", C.c_float), ("pa_epsilon", C.c_float), ("cov_r", C.c_float), ("cov_phi", C.c_float),
     ]
 
 
@@ -114,12 +114,13 @@ _OPTION_FIELDS = {
     "-lambda_v": ("lambda_v", float), "-seed": ("seed", int),
     "-hash_seed": (None, int), "-mix_interval": (None, int),     # not oracle fields
     "-aggressiveness": ("pa_c", float), "-epsilon": ("pa_epsilon", float), "-e": ("pa_epsilon", float),
-    "-r": ("cov_r", float),
+    "-r": ("cov_r", float), "-phi": ("cov_phi", float),
 }
 # online learners on the mini-batch skeleton: function -> (task, loss id)
 _ONLINE = {"train_perceptron": (0, 3), "train_pa": (0, 4), "train_pa1": (0, 5), "train_pa2": (0, 6),
            "train_pa1_regr": (1, 7), "train_pa2_regr": (1, 8),
-           "train_arow": (0, 9), "train_arow_regr": (1, 10), "train_arowe_regr": (1, 11)}
+           "train_arow": (0, 9), "train_arow_regr": (1, 10), "train_arowe_regr": (1, 11),
+           "train_cw": (0, 12), "train_scw": (0, 13), "train_scw2": (0, 14)}
 _ONLINE_FIXED = {"-loss", "-loss_function", "-opt", "-optimizer", "-eta", "-eta0", "-eta_0", "-power_t", "-total_steps",
                  "-t", "-reg", "-regularization", "-lambda"}
 
@@ -128,12 +129,13 @@ def config_from_options(function_name: str, options: str = "") -> HmoConfig:
     """Oracle config of a UDTF option string (no product code involved)."""
     online = _ONLINE.get(function_name)
     task = online[0] if online else {"train_classifier": 0, "train_regressor": 1, "train_fm": 2}[function_name]
-    takes_c = bool(online) and online[1] in (5, 6, 7, 8)
+    takes_c = bool(online) and online[1] in (5, 6, 7, 8, 13, 14)
     takes_eps = bool(online) and online[1] in (7, 8, 11)
-    takes_r = bool(online) and online[1] >= 9
+    takes_r = bool(online) and 9 <= online[1] <= 11
+    takes_phi = bool(online) and online[1] >= 12
     c = HmoConfig()
     c.task = task
-    c.pa_c, c.pa_epsilon, c.cov_r = 1.0, 0.1, 0.1
+    c.pa_c, c.pa_epsilon, c.cov_r, c.cov_phi = 1.0, 0.1, 0.1, 1.0
     c.loss = 2 if task == 1 else 0
     c.opt = 0 if task == 2 else 1
     c.eta_sched, c.reg, c.grad_norm, c.mini_batch, c.iters = 0, 0, 0, 1, 1
@@ -160,9 +162,11 @@ def config_from_options(function_name: str, options: str = "") -> HmoConfig:
         if online and name in _ONLINE_FIXED:
             raise ValueError(f"{name} is fixed by {function_name}")
         if name in ("-c", "-aggressiveness") and not takes_c:
-            raise ValueError(f"{name} is an option of train_pa1, train_pa2 and their _regr forms")
+            raise ValueError(f"{name} is an option of train_pa1, train_pa2, their _regr forms, train_scw and train_scw2")
         if name in ("-epsilon", "-e") and not takes_eps:
             raise ValueError(f"{name} is an option of train_pa1_regr, train_pa2_regr and train_arowe_regr")
+        if name == "-phi" and not takes_phi:
+            raise ValueError("-phi is an option of train_cw, train_scw and train_scw2")
         if name == "-r" and not takes_r:
             raise ValueError("-r is an option of train_arow, train_arow_regr and train_arowe_regr")
         if name == "-c":

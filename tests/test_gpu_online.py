@@ -123,7 +123,10 @@ def test_model_table_and_prediction():
 
 # ---- learners that keep a variance per feature (AROW): forward with margin + variance, two update launches ---
 
-COV = ["train_arow", "train_arow_regr", "train_arowe_regr"]
+COV = ["train_arow", "train_arow_regr", "train_arowe_regr", "train_cw", "train_scw", "train_scw2"]
+COV_REGR = ["train_arow_regr", "train_arowe_regr"]
+COV_OPTS = {"train_arow": "-r 1", "train_arow_regr": "-r 2", "train_arowe_regr": "-r 2 -epsilon 0.05",
+            "train_cw": "-phi 0.5", "train_scw": "-phi 0.8 -c 0.1", "train_scw2": "-c 0.1"}
 
 
 def check_cov(fn, options, data, pushes=None):
@@ -140,12 +143,12 @@ def check_cov(fn, options, data, pushes=None):
 @pytest.mark.parametrize("fn", COV)
 @pytest.mark.parametrize("mb", [1, 64])
 def test_cov_small_batches(fn, mb):
-    if fn == "train_arow":
+    if fn not in COV_REGR:
         data = synth.a9a_like(1024 + 11, seed=4)
-        check_cov(fn, f"-dims 124 -mini_batch {mb} -r 1", data)
+        check_cov(fn, f"-dims 124 -mini_batch {mb} {COV_OPTS[fn]}", data)
     else:
         data = synth.ragged(1500, dims=256, max_nnz=12, seed=6, regression=True)
-        check_cov(fn, f"-dims 256 -mini_batch {mb} -r 2" + (" -epsilon 0.05" if fn == "train_arowe_regr" else ""), data)
+        check_cov(fn, f"-dims 256 -mini_batch {mb} {COV_OPTS[fn]}", data)
 
 
 @pytest.mark.parametrize("fn", COV)
@@ -155,12 +158,12 @@ def test_cov_criteo_shaped_every_tile_size(fn):
     dims = 1 << 18
     for mb, n in ((1024, 5 * 1024 + 77), (8192, 2 * 8192 + 1000), (20000, 45000)):
         data = synth.criteo_like(n, dims=dims, seed=8)
-        if fn != "train_arow":
+        if fn in COV_REGR:
             import torch
             rng = np.random.default_rng(2)
             data.label = data.label * 2.0 + torch.from_numpy(rng.normal(0, 0.3, data.rows).astype(np.float32))
         norm = " -grad_norm count" if mb == 8192 else ""
-        check_cov(fn, f"-dims {dims} -mini_batch {mb} -r 1{norm}", data, pushes=[n // 3, n])
+        check_cov(fn, f"-dims {dims} -mini_batch {mb} {COV_OPTS[fn]}{norm}", data, pushes=[n // 3, n])
 
 
 def test_cov_determinism_replays_and_table():

@@ -146,3 +146,44 @@ def test_arow_learns_and_confidence_grows_with_evidence():
     order = np.argsort(counts[seen])
     sg = res.s1[seen][order]
     assert sg[: len(sg) // 4].mean() > sg[-len(sg) // 4:].mean()
+
+
+# ---- confidence-weighted / soft confidence-weighted (diagonal) ---------------------------------------------
+
+@pytest.mark.parametrize("fn", ["train_cw", "train_scw", "train_scw2"])
+def test_confidence_weighted_first_step(fn):
+    """From w = 0, sigma = 1 the row is uncertain (margin 0 < phi sqrt(v)): a step along y x, variances of the
+    row's features shrink, nothing else moves; SCW-I's step is capped by C."""
+    f, x = [1, 4, 9], np.array([0.5, -2.0, 1.0], np.float32)
+    w, sg = one_row_cov(fn, "", f, x, 1.0)
+    assert (np.sign(w[f]) == np.sign(x)).all()
+    assert (sg[f] < 1.0).all() and (sg[f] > 0.0).all()
+    untouched = np.setdiff1d(np.arange(16), f)
+    assert (sg[untouched] == 1.0).all() and not w[untouched].any()
+    wn, _ = one_row_cov(fn, "", f, x, 0.0)                 # the negative class mirrors it
+    assert np.allclose(wn, -w)
+    if fn == "train_scw":
+        wc, _ = one_row_cov(fn, "-c 0.01", f, x, 1.0)
+        assert np.allclose(wc[f], 0.01 * x, rtol=1e-6)    # alpha = C, sigma = 1
+
+
+@pytest.mark.parametrize("fn", ["train_cw", "train_scw", "train_scw2"])
+def test_confident_and_correct_rows_do_not_step(fn):
+    cfg = _oracle.config_from(hm.parse_options(fn, "-dims 8 -phi 0.5"))
+    w0 = np.zeros(8, np.float32); w0[2] = 5.0
+    sg0 = np.full(8, 0.01, np.float32)
+    res = _oracle.train_linear(cfg, np.array([0, 2]), np.array([2, 3]), np.array([1.0, 1.0], np.float32),
+                               np.array([1.0], np.float32), w=w0, s1=sg0)
+    assert np.array_equal(res.w, w0) and np.array_equal(res.s1, sg0)
+
+
+@pytest.mark.parametrize("fn,opts", [("train_cw", "-phi 0.5"), ("train_scw", "-c 0.1"), ("train_scw2", "-c 0.1")])
+def test_confidence_weighted_learns(fn, opts):
+    data = synth.a9a_like(4096, seed=1)
+    rp, f, v, y = data.numpy()
+    cfg = _oracle.config_from(hm.parse_options(fn, f"-dims 124 -mini_batch 1 {opts}"))
+    res = _oracle.train_linear(cfg, rp, f, v, y)
+    import torch
+    # (hard-margin CW is known to suffer from label noise -- the reason SCW exists; the soft variants do better)
+    assert synth.auc(torch.from_numpy(_oracle.predict_linear(rp, f, v, res.w)), torch.from_numpy(y)) > (0.7 if fn == "train_cw" else 0.78)
+    assert (res.s1 > 0).all() and (res.s1 <= 1.0).all() and np.isfinite(res.w).all()

@@ -59,6 +59,10 @@ def test_numeric_options_round_trip():
     ("train_arow", "-r 0"),
     ("train_pa1", "-r 1"),
     ("train_arow_regr", "-opt sgd"),
+    ("train_cw", "-c 1"),                       # plain CW has no aggressiveness
+    ("train_cw", "-r 1"),
+    ("train_scw", "-phi 0"),
+    ("train_arow", "-phi 1"),
     ("train_classifier", "-eta0 nan"),
     ("train_classifier", "-dims -5"),
 ])
@@ -91,6 +95,9 @@ def test_error_names_the_offending_token():
     ("train_arow", "-r 0.5 -mini_batch 32"),
     ("train_arow_regr", ""),
     ("train_arowe_regr", "-r 2 -epsilon 0.3 -dims 1024"),
+    ("train_cw", "-phi 0.7 -mini_batch 16"),
+    ("train_scw", "-phi 1.2 -c 0.5"),
+    ("train_scw2", ""),
 ])
 def test_oracle_side_parser_agrees_with_the_library(fn, opts):
     """bench.py's CPU arm builds its oracle config with tests/_oracle.config_from_options so that its
@@ -119,3 +126,7 @@ def test_variance_keeping_learner_functions():
         assert (c.task, c.loss, c.opt, c.mini_batch) == (task, loss, 5, 1), fn
         assert abs(c.cov_r - 0.1) < 1e-8 and c.eta0 == 1.0
     assert hm.parse_options("train_arow", "-r 3").cov_r == 3.0
+    for fn, loss in [("train_cw", 12), ("train_scw", 13), ("train_scw2", 14)]:
+        c = hm.parse_options(fn, "")
+        assert (c.task, c.loss, c.opt, c.cov_phi, c.pa_c) == (0, loss, 5, 1.0, 1.0), fn
+    assert hm.parse_options("train_scw", "-phi 0.5 -c 0.25").cov_phi == 0.5

@@ -100,7 +100,45 @@ def np_row_coef(cfg, m, y, xx):
 
 
 def np_cov_coefs(cfg, m, y, v):
-    """AROW (Crammer, Kulesza, Dredze 2009), diagonal: (c1, c2) for the weight and the variance sums."""
+    """AROW (Crammer, Kulesza, Dredze 2009), CW (Dredze, Crammer, Pereira 2008), SCW-I / SCW-II (Wang, Zhao, Hoi
+    2012), diagonal: (c1, c2) for the weight and the variance sums."""
+    Z = (F(0.0), F(0.0))
+    if cfg.loss >= 12:
+        phi, cc = F(cfg.cov_phi), F(cfg.pa_c)
+        if not v > 0:
+            return Z
+        my, p2 = F(y * m), F(phi * phi)
+        if cfg.loss == 12:
+            q = F(F(1.0) + F(F(F(2.0) * phi) * my))
+            rad = F(F(q * q) - F(F(F(8.0) * phi) * F(my - F(phi * v))))
+            if not rad >= 0:
+                return Z
+            alpha = F(F(np.sqrt(rad) - q) / F(F(F(4.0) * phi) * v))
+            if not alpha > 0:
+                return Z
+            return F(-F(alpha * y)), F(F(F(2.0) * alpha) * phi)
+        if not F(F(phi * np.sqrt(v)) - my) > 0:
+            return Z
+        t1 = F(my * my)
+        if cfg.loss == 13:
+            psi, zeta = F(F(1.0) + F(p2 * F(0.5))), F(F(1.0) + p2)
+            rad = F(F(F(t1 * F(p2 * p2)) * F(0.25)) + F(F(v * p2) * zeta))
+            alpha = F(F(np.sqrt(rad) - F(my * psi)) / F(v * zeta))
+            alpha = min(cc, alpha)
+        else:
+            n = F(v + F(F(0.5) / cc))
+            vp2 = F(v * p2)
+            g1 = F(F(F(p2 * t1) * v) * v)
+            g2 = F(F(F(F(4.0) * n) * v) * F(n + vp2))
+            gamma = F(phi * np.sqrt(F(g1 + g2)))
+            num = F(gamma - F(F(F(F(2.0) * my) * n) + F(F(p2 * my) * v)))
+            den = F(F(2.0) * F(F(n * n) + F(F(n * v) * p2)))
+            alpha = F(num / den)
+        if not alpha > 0:
+            return Z
+        avp = F(F(alpha * v) * phi)
+        usq = F(F(0.5) * F(np.sqrt(F(F(avp * avp) + F(F(4.0) * v))) - avp))
+        return F(-F(alpha * y)), F(F(alpha * phi) / F(usq + avp))
     if cfg.loss == 9:
         l, d = F(F(1.0) - F(y * m)), y
         if not l > 0:
@@ -144,7 +182,7 @@ def np_train_cov(cfg, rowptr, feat, val, label):
                     return F(sm * (1.0 / float(b1 - b0))) if cfg.grad_norm == 0 else (F(sm / float(cnts[j])) if cfg.grad_norm == 1 else F(sm))
                 g1, g2, s = mean(s1[j]), mean(s2[j]), sg[j]
                 w[j] = F(w[j] - F(s * g1))
-                sg[j] = F(s - F(F(s * s) * g2))
+                sg[j] = F(F(1.0) / F(F(F(1.0) / s) + g2)) if cfg.loss == 12 else F(s - F(F(s * s) * g2))
     return w, sg, np.zeros(D, F), t
 
 
@@ -251,6 +289,12 @@ def np_train(cfg, rowptr, feat, val, label):
     ("-mini_batch 8 -dims 50 -grad_norm sum -r 10", "train_arow_regr"),
     ("-mini_batch 1 -dims 50 -epsilon 0.05", "train_arowe_regr"),
     ("-mini_batch 5 -dims 50 -epsilon 0.2 -r 2 -iters 2", "train_arowe_regr"),
+    ("-mini_batch 1 -dims 50 -iters 2", "train_cw"),
+    ("-mini_batch 6 -dims 50 -phi 0.5 -grad_norm count", "train_cw"),
+    ("-mini_batch 1 -dims 50 -phi 0.8 -c 0.5", "train_scw"),
+    ("-mini_batch 7 -dims 50 -c 0.05 -iters 2", "train_scw"),
+    ("-mini_batch 1 -dims 50 -phi 1.5 -c 2", "train_scw2"),
+    ("-mini_batch 4 -dims 50 -c 0.3 -grad_norm sum", "train_scw2"),
 ])
 def test_oracle_matches_numpy_restatement(options, fn):
     data = synth.ragged(120, dims=50, max_nnz=9, seed=2, regression=fn in ("train_regressor", "train_pa1_regr", "train_pa2_regr", "train_arow_regr", "train_arowe_regr"))
