@@ -87,6 +87,10 @@ WORKLOADS = {
     "pa1": _wl("train_pa1", "-mini_batch {mb} -dims 16777216 -c 0.1",
                "train_pa1 (passive-aggressive PA-I), 2^24 hashed dims, Criteo-shaped synthetic (39 feats/row)",
                "examples/sec (train_pa1, 2^24 hashed dims, Criteo-shaped)", state_words=1),
+    # ... and one of the learners that keep a variance per feature: two update launches per mini-batch
+    "arow": _wl("train_arow", "-mini_batch {mb} -dims 16777216 -r 1",
+                "train_arow (adaptive regularization of weights, diagonal), 2^24 hashed dims, Criteo-shaped synthetic (39 feats/row)",
+                "examples/sec (train_arow, 2^24 hashed dims, Criteo-shaped)", state_words=2),
 }
 
 

@@ -49,7 +49,7 @@ def test_workload_table():
     sys.path.insert(0, ROOT)
     import bench
     import hivemall_b200 as hm
-    assert set(bench.WORKLOADS) == {"ftrl", "adagrad", "fm16", "adam26", "fm64", "pa1"}
+    assert set(bench.WORKLOADS) == {"ftrl", "adagrad", "fm16", "adam26", "fm64", "pa1", "arow"}
     for name, wl in bench.WORKLOADS.items():
         cfg = hm.parse_options(wl["fn"], bench.options_of(wl))   # every option string parses
         assert cfg.dims == wl["dims"] and cfg.mini_batch == bench.MINI_BATCH, name
