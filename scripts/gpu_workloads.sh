@@ -1,7 +1,7 @@
 #!/bin/bash
 # On the GPU box: the secondary workloads of bench.py on one GPU (BASELINE.json configs[2..4] + the AdaGrad target).
 mkdir -p gpurun_out
-for w in ${@:-adagrad fm16 adam26 fm64 pa1}; do
+for w in ${@:-adagrad fm16 adam26 fm64 pa1 arow}; do
   timeout 600 python bench.py --workload $w --steps 8 --warmup 3 --no-cpu --no-sweep > gpurun_out/bench_$w.json 2> gpurun_out/bench_$w.err
   echo -n "$w rc=$? "; python - $w <<'PY'
 import json,sys
