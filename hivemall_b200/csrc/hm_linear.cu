@@ -377,20 +377,55 @@ __device__ __forceinline__ void hot_end(const FwdParams &P, HS &H, int cta)
 // of its hot elements (what the update kernel would otherwise have found in the sorted stream) go to the
 // accumulators of the row's unit; a lane keeps its first KEEP elements in registers for that, longer rows
 // re-read their tail.
-template <int LD, int LPR>
-__device__ __forceinline__ void forward_rows_hot(const FwdParams &P, int warp_first, int warp_stride,
-                                                 HotSharedT<256 / LPR> &H)
+// What a warp can fetch of its FIRST row before the model is final (a programmatic dependent waits for the
+// previous update at griddepcontrol.wait; the rows do not depend on it): the row's bounds, its label and the
+// first 64 elements.  With one row per warp -- the mid-size mini-batches this is for -- that takes the row
+// pointer -> feature/value chain and the label's round trip out of the time between two updates.
+struct RowPre {
+    int64_t p0, p1;
+    uint32_t f[2];
+    float x[2];
+    float lab;
+};
+__device__ __forceinline__ void preload_first_row(const FwdParams &P, int warp_first, RowPre &pre)
 {
+    const int lane = threadIdx.x & 31;
+    pre.p0 = 0; pre.p1 = 0; pre.lab = 0.0f;
+    pre.f[0] = pre.f[1] = 0u; pre.x[0] = pre.x[1] = 0.0f;
+    if (warp_first < P.n_rows) {
+        const int64_t row = P.row0 + warp_first;
+        pre.p0 = P.rowptr[row]; pre.p1 = P.rowptr[row + 1];
+        if (lane == 0) pre.lab = P.label[row];
+#pragma unroll
+        for (int i = 0; i < 2; i++) {
+            const int64_t p = pre.p0 + lane + i * 32;
+            if (p < pre.p1) { pre.f[i] = __ldcs(P.feature + p); pre.x[i] = __ldcs(P.value + p); }
+        }
+    }
+}
+
+template <int LD, int LPR, bool PRE = false>
+__device__ __forceinline__ void forward_rows_hot(const FwdParams &P, int warp_first, int warp_stride,
+                                                 HotSharedT<256 / LPR> &H, const RowPre *pre = nullptr)
+{
+    static_assert(!PRE || LPR == 32, "the preloaded first row is a warp's row");
     constexpr int RPW = 32 / LPR;
     constexpr int KEEP = LPR == 32 ? 2 : 3;          // 64 or 48 elements of a row stay in registers
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int sub = lane & (LPR - 1), part = lane / LPR;
     const int unit = RPW * warp + part;
+    bool first = PRE;
     for (int rb = warp_first * RPW; rb < P.n_rows; rb += warp_stride * RPW) {
         const int r = rb + part;
         const bool live = r < P.n_rows;
         const int64_t row = P.row0 + (live ? r : rb);
-        const int64_t p0 = live ? P.rowptr[row] : 0, p1 = live ? P.rowptr[row + 1] : 0;
+        int64_t p0, p1;
+        float lab;
+        if (PRE && first) { p0 = pre->p0; p1 = pre->p1; lab = pre->lab; }
+        else {
+            p0 = live ? P.rowptr[row] : 0; p1 = live ? P.rowptr[row + 1] : 0;
+            lab = (live && sub == 0) ? P.label[row] : 0.0f;       // (requested now, used after the sums)
+        }
         double acc = 0.0;
         uint32_t slot[KEEP]; float xk[KEEP];
 #pragma unroll
@@ -398,8 +433,9 @@ __device__ __forceinline__ void forward_rows_hot(const FwdParams &P, int warp_fi
             slot[i] = kHotNone; xk[i] = 0.0f;
             const int64_t p = p0 + sub + i * LPR;
             if (p < p1) {
-                const uint32_t f = __ldcs(P.feature + p);
-                const float x = __ldcs(P.value + p);
+                uint32_t f; float x;
+                if (PRE && first) { f = pre->f[i < 2 ? i : 0]; x = pre->x[i < 2 ? i : 0]; }
+                else { f = __ldcs(P.feature + p); x = __ldcs(P.value + p); }
                 if (f < P.dims) {
                     const uint32_t sl = hot_slot_of(H, f);
                     const float w = sl != kHotNone ? H.w[sl] : weight_at<LD>(P.wv, f);
@@ -422,11 +458,11 @@ __device__ __forceinline__ void forward_rows_hot(const FwdParams &P, int warp_fi
         if (live && sub == 0) {
             const float m = (float)acc;
             P.margin[row - P.block_row0] = m;
-            const float lab = P.label[row];
             const float y = P.task == HM_TASK_CLASSIFIER ? (lab > 0.0f ? 1.0f : -1.0f) : lab;
             dl = row_coef<LD>(P, m, y, row - P.block_row0);
             P.dloss[r] = dl;
         }
+        first = false;
         dl = __shfl_sync(0xffffffffu, dl, part * LPR);
         const int len = (int)min(p1 - p0, (int64_t)0x7fffffff);
         const int maxlen = __reduce_max_sync(0xffffffffu, len);          // (uniform over the warp)
@@ -521,9 +557,11 @@ __global__ void __launch_bounds__(kFwdThreads, 8) linear_forward_kernel(FwdParam
             hot_end(P, H, (int)blockIdx.x);
         } else {
             auto &H = *reinterpret_cast<HotSharedT<8> *>(fwd_dyn);
+            RowPre pre;
+            if (PDL) preload_first_row(P, warp_first, pre);     // (before the prologue's griddepcontrol.wait)
             hot_prologue<LD>(P, H);
             FSTAMP(3);
-            forward_rows_hot<LD, 32>(P, warp_first, warp_stride, H);
+            forward_rows_hot<LD, 32, PDL>(P, warp_first, warp_stride, H, &pre);
             FSTAMP(4);
             hot_end(P, H, (int)blockIdx.x);
             FSTAMP(5);
