@@ -355,3 +355,115 @@ def test_synth_is_deterministic_and_shaped():
     assert np.array_equal(a.label.numpy()[500:], b.label.numpy())
     k = synth.a9a_like(100)
     assert k.nnz == 1400 and int(k.feature.max()) < 123
+
+
+# ---- independent numpy restatement of the factorization machine ----
+
+def np_fmix32(h):
+    h &= 0xFFFFFFFF
+    h ^= h >> 16; h = (h * 0x85EBCA6B) & 0xFFFFFFFF
+    h ^= h >> 13; h = (h * 0xC2B2AE35) & 0xFFFFFFFF
+    h ^= h >> 16
+    return h
+
+
+def np_fm_init(cfg):
+    n = int(cfg.dims) * int(cfg.factors)
+    V = np.empty(n, F)
+    for q in range(n):
+        h = np_fmix32((q * 0x9E3779B1 + int(cfg.seed)) & 0xFFFFFFFF)
+        u = F(F(F(F(h >> 8) * F(5.9604644775390625e-08)) - F(0.5)) * F(2.0))
+        V[q] = F(F(cfg.sigma) * u)
+    return V
+
+
+def np_fm_step(cfg, eta, g, lam, th, acc):
+    g = F(g + F(F(lam) * th))
+    if cfg.opt == 1:
+        G = F(acc + F(g * g))
+        return F(th - F(F(eta * g) / F(np.sqrt(G) + F(cfg.eps)))), G
+    return F(th - F(eta * g)), acc
+
+
+def np_train_fm(cfg, rowptr, feat, val, label):
+    D, B, k = int(cfg.dims), int(cfg.mini_batch), int(cfg.factors)
+    w0, gw0 = F(0.0), F(0.0)
+    w = np.zeros(D, F); gw = np.zeros(D, F)
+    V = np_fm_init(cfg).reshape(D, k); gv = np.zeros((D, k), F)
+    n = len(label); t = 0
+    preds = np.zeros(n, F)
+    for _ in range(cfg.iters):
+        for b0 in range(0, n, B):
+            b1 = min(n, b0 + B)
+            dl, S = [], []
+            g0 = 0.0
+            for i in range(b0, b1):
+                ps = range(rowptr[i], rowptr[i + 1])
+                lin = 0.0
+                for p in ps:
+                    lin += float(F(w[feat[p]] * val[p]))
+                inter = 0.0
+                s_row = []
+                for f in range(k):
+                    Sf, Qf = 0.0, 0.0
+                    for p in ps:
+                        vx = F(V[feat[p], f] * val[p])
+                        Sf += float(vx); Qf += float(F(vx * vx))
+                    s32 = F(Sf)
+                    s_row.append(s32)
+                    inter += float(F(s32 * s32)) - Qf
+                pred = F(float(w0) + lin + 0.5 * inter)
+                preds[i] = pred
+                if cfg.fm_classification:
+                    y = F(1.0) if label[i] > 0 else F(-1.0)
+                    d = np_dloss(0, pred, y)
+                else:
+                    d = F(pred - label[i])
+                dl.append(d); S.append(s_row); g0 += float(d)
+            A1, A2, GS, cnts, order = {}, {}, {}, {}, []
+            for i in range(b0, b1):
+                for p in range(rowptr[i], rowptr[i + 1]):
+                    j = int(feat[p])
+                    if j not in cnts:
+                        cnts[j] = 0; A1[j] = 0.0; A2[j] = 0.0; GS[j] = [0.0] * k; order.append(j)
+                    cnts[j] += 1
+                    c1 = F(dl[i - b0] * val[p])
+                    A1[j] += float(c1)
+                    A2[j] += float(F(c1 * val[p]))
+                    for f in range(k):
+                        GS[j][f] += float(F(c1 * S[i - b0][f]))
+            t += 1
+            eta = F(_oracle.lib().hmo_eta(cfg, t))
+            inv = 1.0 / float(b1 - b0)
+
+            def mean(sm, j):
+                return F(sm * inv) if cfg.grad_norm == 0 else (F(sm / float(cnts[j])) if cfg.grad_norm == 1 else F(sm))
+            w0, gw0 = np_fm_step(cfg, eta, F(g0) if cfg.grad_norm == 2 else F(g0 * inv), cfg.lambda_w0, w0, gw0)
+            for j in order:
+                w[j], gw[j] = np_fm_step(cfg, eta, mean(A1[j], j), cfg.lambda_w, w[j], gw[j])
+                for f in range(k):
+                    G = GS[j][f] - float(V[j, f]) * A2[j]
+                    V[j, f], gv[j, f] = np_fm_step(cfg, eta, mean(G, j), cfg.lambda_v, V[j, f], gv[j, f])
+    return w0, w, V.reshape(-1), gw0, gw, gv.reshape(-1), preds, t
+
+
+@pytest.mark.parametrize("options", [
+    "-factors 3 -classification -opt sgd -mini_batch 7 -dims 40 -eta0 0.1",
+    "-factors 4 -classification -opt adagrad -mini_batch 16 -dims 40 -eta0 0.1 -iters 2",
+    "-factors 2 -opt sgd -mini_batch 5 -dims 40 -eta0 0.02 -lambda0 0.1 -lambdaW 0.05 -lambdaV 0.2",
+    "-factors 5 -opt adagrad -mini_batch 9 -dims 40 -eta0 0.05 -grad_norm count -sigma 0.3 -seed 7",
+    "-factors 1 -classification -opt adagrad -mini_batch 1 -dims 40 -grad_norm sum",
+])
+def test_fm_oracle_matches_numpy_restatement(options):
+    regression = "-classification" not in options
+    data = synth.ragged(90, dims=40, max_nnz=7, seed=4, regression=regression)
+    rp, f, v, y = data.numpy()
+    cfg = _oracle.config_from(hm.parse_options("train_fm", options))
+    assert np.array_equal(_oracle.fm_init_v(cfg), np_fm_init(cfg))
+    res = _oracle.train_fm(cfg, rp, f, v, y)
+    w0, w, V, gw0, gw, gvv, preds, t = np_train_fm(cfg, rp, f, v, y)
+    assert res.t == t
+    assert np.array_equal(res.preds, preds)
+    assert res.w0[0] == w0 and np.array_equal(res.w, w) and np.array_equal(res.V, V)
+    if cfg.opt == 1:
+        assert res.gw0[0] == gw0 and np.array_equal(res.gw, gw) and np.array_equal(res.gv, gvv)
