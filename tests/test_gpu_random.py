@@ -82,3 +82,52 @@ def test_random_fm_configuration_matches_the_oracle(seed):
     u, ref, _ = run_both(options, data, pushes=pushes)
     check(u, ref, adagrad)
     u.destroy()
+
+
+ONLINE = {  # function -> (regression?, option generator)
+    "train_perceptron": (False, lambda r: ""),
+    "train_pa": (False, lambda r: ""),
+    "train_pa1": (False, lambda r: f"-c {r.choice([0.01, 0.3, 5.0])}"),
+    "train_pa2": (False, lambda r: f"-c {r.choice([0.01, 0.3, 5.0])}"),
+    "train_pa1_regr": (True, lambda r: f"-c {r.choice([0.05, 1.0])} -epsilon {r.choice([0.0, 0.05, 0.5])}"),
+    "train_pa2_regr": (True, lambda r: f"-c {r.choice([0.05, 1.0])} -epsilon {r.choice([0.0, 0.05, 0.5])}"),
+    "train_arow": (False, lambda r: f"-r {r.choice([0.1, 1.0, 10.0])}"),
+    "train_arow_regr": (True, lambda r: f"-r {r.choice([0.1, 1.0, 10.0])}"),
+    "train_arowe_regr": (True, lambda r: f"-r {r.choice([0.1, 1.0])} -epsilon {r.choice([0.01, 0.3])}"),
+    "train_cw": (False, lambda r: f"-phi {r.choice([0.2, 1.0, 2.0])}"),
+    "train_scw": (False, lambda r: f"-phi {r.choice([0.2, 1.0, 2.0])} -c {r.choice([0.05, 1.0])}"),
+    "train_scw2": (False, lambda r: f"-phi {r.choice([0.2, 1.0, 2.0])} -c {r.choice([0.05, 1.0])}"),
+}
+
+
+def draw_online_case(seed: int):
+    r = np.random.default_rng(5000 + seed)
+    fn = list(ONLINE)[seed % len(ONLINE)]
+    regression, gen = ONLINE[fn]
+    dims = int(r.choice([17, 300, 5000, (1 << 17) + 1]))
+    rows = int(r.integers(1, 5000))
+    mb = int(r.choice([1, 7, 64, 333, 1024, 2500]))
+    if mb == 1:
+        rows = min(rows, 300)
+    max_nnz = int(r.choice([1, 3, 20, 60]))
+    opts = [gen(r), f"-mini_batch {mb}", f"-dims {dims}", f"-iters {int(r.choice([1, 1, 2]))}",
+            f"-grad_norm {r.choice(['batch', 'count', 'sum'])}"]
+    pushes = None
+    if r.random() < 0.5:
+        cuts = np.sort(r.integers(0, rows + 1, size=int(r.integers(1, 5))))
+        pushes = [int(b - a) for a, b in zip(np.concatenate([[0], cuts]), np.concatenate([cuts, [rows]])) if b > a]
+    return fn, " ".join(o for o in opts if o), dims, rows, max_nnz, pushes, regression
+
+
+@pytest.mark.parametrize("seed", range(36))
+def test_random_online_learner_matches_the_oracle(seed):
+    """The online learners (perceptron, passive-aggressive, AROW, CW, SCW) under the same randomised shapes:
+    weights and, where the learner keeps one, the per-feature variance."""
+    fn, options, dims, rows, max_nnz, pushes, regression = draw_online_case(seed)
+    data = synth.ragged(rows, dims, max_nnz, seed=700 + seed, regression=regression)
+    u, w, state = run_gpu_linear(fn, options, data, pushes=pushes)
+    ref, ref_state = run_oracle_linear(fn, options, data)
+    assert u.step == ref.t, options
+    assert_weights_close(w, ref.w, f"w [{fn} {options}]")
+    assert_weights_close(state, ref_state, f"state [{fn} {options}]")
+    u.destroy()
