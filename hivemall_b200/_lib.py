@@ -40,8 +40,8 @@ class HmConfig(C.Structure):
         ("factors", C.c_int32), ("fm_classification", C.c_int32), ("sigma", C.c_float),
         ("lambda_w0", C.c_float), ("lambda_w", C.c_float), ("lambda_v", C.c_float),
         ("seed", C.c_uint32), ("mix_interval", C.c_int32), ("hash_seed", C.c_uint32),
-        ("pa_c", C.c_float), ("pa_epsilon", C.c_float), ("cov_r", C.c_float), ("cov_phi", C.c_float),
-        ("reserved", C.c_int32 * 4),
+        ("pa_c", C.c_float), ("pa_epsilon", C.c_float), ("cov_r", C.c_float), ("cov_phi", C.c_float), ("loss_param", C.c_float),
+        ("reserved", C.c_int32 * 3),
     ]
 
 

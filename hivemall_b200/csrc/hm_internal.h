@@ -144,7 +144,7 @@ struct LinearArgs {
     const float *sqnorm = nullptr;   // |x|^2 per row of the block being trained (online learners), else NULL
     int cov_pass = 0;                // HM_OPT_COV: 1 = the update launch steps the weights, 2 = the variances
 };
-inline bool loss_keeps_variance(int loss) { return loss >= HM_LOSS_AROW; }
+inline bool loss_keeps_variance(int loss) { return loss >= HM_LOSS_AROW && loss <= HM_LOSS_SCW2; }
 // margin, variance and the two per-row coefficients of the variance-keeping learners (AROW)
 hm_status launch_linear_forward_cov(Launcher &L, const LinearArgs &a, const int64_t *d_rowptr, int64_t row0, int32_t n_rows,
                                     int64_t block_row0, const uint32_t *d_feature, const float *d_value, const float *d_label,

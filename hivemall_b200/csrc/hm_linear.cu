@@ -65,6 +65,29 @@ __device__ __forceinline__ float dloss_of(int loss, float m, float y)
     return __fsub_rn(m, y);
 }
 
+// The other plain losses: derivative with respect to the margin.  p = Huber's threshold or the
+// quantile; eps = width of the insensitive zone.  y is +-1 for the two classification losses.
+__device__ __forceinline__ float dloss_more(int loss, float m, float y, float p, float eps)
+{
+    if (loss == HM_LOSS_SQUARED_HINGE) {               // max(0, 1 - z)^2
+        const float z = __fmul_rn(y, m);
+        return z < 1.0f ? __fmul_rn(__fmul_rn(-2.0f, y), __fsub_rn(1.0f, z)) : 0.0f;
+    }
+    if (loss == HM_LOSS_MODIFIED_HUBER) {              // z >= 1: 0; -1 <= z < 1: (1 - z)^2; z < -1: -4 z
+        const float z = __fmul_rn(y, m);
+        if (z >= 1.0f) return 0.0f;
+        if (z >= -1.0f) return __fmul_rn(__fmul_rn(-2.0f, y), __fsub_rn(1.0f, z));
+        return __fmul_rn(-4.0f, y);
+    }
+    const float e = __fsub_rn(m, y);
+    if (loss == HM_LOSS_HUBER) return fabsf(e) <= p ? e : (e < 0.0f ? -p : p);        // e^2 / 2 inside, c (|e| - c / 2) outside
+    if (loss == HM_LOSS_QUANTILE) return e < 0.0f ? -p : __fsub_rn(1.0f, p);          // tau (y - m) below, (1 - tau)(m - y) above
+    const float a = __fsub_rn(fabsf(e), eps);
+    if (!(a > 0.0f)) return 0.0f;
+    if (loss == HM_LOSS_EPS_INSENSITIVE) return e < 0.0f ? -1.0f : 1.0f;              // max(0, |e| - eps)
+    return __fmul_rn(e < 0.0f ? -2.0f : 2.0f, a);                                       // max(0, |e| - eps)^2
+}
+
 // Online learners on the same skeleton: the number that takes dloss's place for a row is
 // -(step size) * (direction of the correction); xx = |x|^2 of the row (row_sqnorm_kernel).  Perceptron
 // (Rosenblatt): step 1 on a mistake.  Passive-aggressive (Crammer et al. 2006): PA tau = l / xx, PA-I
@@ -172,7 +195,7 @@ struct FwdParams {
     int32_t train;           // 0: prediction only
     int32_t lpr;             // lanes per row: 32, 16 or 8 (chosen by the host from the mean row length)
     const float *sqnorm;     // online learners other than the perceptron: |x|^2 per row of the BLOCK, else NULL
-    float pa_c, pa_eps;
+    float pa_c, pa_eps, loss_param;
     uint32_t dims;
     uint32_t *bad;           // set to 1 when a feature index >= dims is met (that element scores 0)
     // hot features of the block (training only; NULL: none): their weights are read from shared memory
@@ -189,6 +212,7 @@ template <int LD>
 __device__ __forceinline__ float row_coef(const FwdParams &P, float m, float y, int64_t block_row)
 {
     if (P.loss <= HM_LOSS_SQUARED) return dloss_of(P.loss, m, y);
+    if (P.loss >= HM_LOSS_SQUARED_HINGE) return dloss_more(P.loss, m, y, P.loss_param, P.pa_eps);
     const float xx = P.sqnorm ? ld_mode<LD>(P.sqnorm + block_row) : 0.0f;
     return online_coef(P.loss, m, y, xx, P.pa_c, P.pa_eps);
 }
@@ -1129,7 +1153,7 @@ hm_status launch_linear_forward(Launcher &L, const LinearArgs &a, const int64_t 
     P.margin = d_margin; P.dloss = d_dloss;
     P.block_row0 = block_row0; P.row0 = row0; P.n_rows = n_rows;
     P.task = a.cfg.task; P.loss = a.cfg.loss; P.train = 1;
-    P.sqnorm = a.sqnorm; P.pa_c = a.cfg.pa_c; P.pa_eps = a.cfg.pa_epsilon;
+    P.sqnorm = a.sqnorm; P.pa_c = a.cfg.pa_c; P.pa_eps = a.cfg.pa_epsilon; P.loss_param = a.cfg.loss_param;
     P.dims = (uint32_t)a.cfg.dims; P.bad = d_bad;
     const int grid = linear_forward_grid(n_rows);
     if (hc.info && grid > hc.stride) HM_FAIL(HM_ERR_STATE, "hot-feature scratch too small (%d > %d)", grid, hc.stride);
@@ -1180,7 +1204,7 @@ hm_status launch_predict_linear(Launcher &L, const WeightView &wv, int64_t dims,
     P.wv = wv; P.rowptr = d_rowptr; P.feature = d_feature; P.value = d_value; P.label = nullptr;
     P.margin = d_out; P.dloss = nullptr;
     P.block_row0 = 0; P.row0 = 0; P.n_rows = (int32_t)n_rows;
-    P.task = 0; P.loss = 0; P.train = 0; P.sqnorm = nullptr; P.pa_c = 0.f; P.pa_eps = 0.f;
+    P.task = 0; P.loss = 0; P.train = 0; P.sqnorm = nullptr; P.pa_c = 0.f; P.pa_eps = 0.f; P.loss_param = 0.f;
     P.dims = (uint32_t)dims; P.bad = d_bad;
     P.hot = nullptr; P.hot_sum = nullptr; P.hot_cnt = nullptr; P.hot_stride = 0; P.lpr = 32;
     const int grid = grid_for((n_rows + 7) / 8, 8);
@@ -1287,7 +1311,7 @@ hm_status launch_linear_small_batches(Launcher &L, const LinearArgs &a, const in
     P.F.wv = a.wv; P.F.rowptr = d_rowptr; P.F.feature = d_feature; P.F.value = d_value; P.F.label = d_label;
     P.F.margin = d_margin; P.F.dloss = d_dloss; P.F.block_row0 = block_row0;
     P.F.task = a.cfg.task; P.F.loss = a.cfg.loss; P.F.train = 1; P.F.dims = (uint32_t)a.cfg.dims; P.F.bad = d_bad;
-    P.F.sqnorm = a.sqnorm; P.F.pa_c = a.cfg.pa_c; P.F.pa_eps = a.cfg.pa_epsilon;
+    P.F.sqnorm = a.sqnorm; P.F.pa_c = a.cfg.pa_c; P.F.pa_eps = a.cfg.pa_epsilon; P.F.loss_param = a.cfg.loss_param;
     P.U.rec = a.rec; P.U.rec_width = a.rec_width; P.U.ftrl_derived = a.wv.ftrl; P.U.touched = nullptr;
     P.U.skey = d_sorted_key; P.U.spay = d_sorted_pay; P.U.dloss = d_dloss; P.U.seg_off = d_seg_off;
     P.U.dims = (uint32_t)a.cfg.dims; P.U.opt = a.cfg.opt; P.U.reg = a.cfg.reg; P.U.grad_norm = a.cfg.grad_norm;

@@ -95,6 +95,7 @@ static void defaults(hm_config *c, int task)
     c->pa_epsilon = 0.1f;
     c->cov_r = 0.1f;
     c->cov_phi = 1.0f;
+    c->loss_param = 0.0f;
 }
 
 hm_status parse_options(const char *function_name, const char *options, hm_config *out)
@@ -141,6 +142,7 @@ hm_status parse_options(const char *function_name, const char *options, hm_confi
         while (is >> t) tok.push_back(t);
     }
     bool loss_given = false;
+    float huber_c = 1.0f, quantile = 0.5f;
     for (size_t i = 0; i < tok.size(); i++) {
         const std::string &name = tok[i];
         if (name.size() < 2 || name[0] != '-')
@@ -184,8 +186,16 @@ hm_status parse_options(const char *function_name, const char *options, hm_confi
             if (!takes_c) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "%s is an option of train_pa1, train_pa2, their _regr forms, train_scw and train_scw2", name.c_str());
             NEED_F(1e-12, 1e12); c.pa_c = (float)d;
         } else if (name == "-epsilon" || name == "-e") {
-            if (!takes_eps) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "%s is an option of train_pa1_regr, train_pa2_regr and train_arowe_regr", name.c_str());
+            if (!takes_eps && !(online < 0 && task == HM_TASK_REGRESSOR))
+                HM_FAIL(HM_ERR_INVALID_ARGUMENT, "%s is an option of train_pa1_regr, train_pa2_regr, train_arowe_regr and of train_regressor "
+                        "with an epsilon-insensitive loss", name.c_str());
             NEED_F(0.0, 1e12); c.pa_epsilon = (float)d;
+        } else if (name == "-huber_c") {
+            if (online >= 0 || task == HM_TASK_FM) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "-huber_c goes with -loss huber");
+            NEED_F(1e-12, 1e12); huber_c = (float)d;
+        } else if (name == "-quantile" || name == "-tau") {
+            if (online >= 0 || task == HM_TASK_FM) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "%s goes with -loss quantile", name.c_str());
+            NEED_F(0.0, 1.0); quantile = (float)d;
         } else if (name == "-phi") {
             if (!takes_phi) HM_FAIL(HM_ERR_INVALID_ARGUMENT, "-phi is an option of train_cw, train_scw and train_scw2");
             NEED_F(1e-6, 1e6); c.cov_phi = (float)d;
@@ -197,7 +207,15 @@ hm_status parse_options(const char *function_name, const char *options, hm_confi
             if (lv == "logloss" || lv == "logistic" || lv == "log") c.loss = HM_LOSS_LOG;
             else if (lv == "hinge" || lv == "hingeloss") c.loss = HM_LOSS_HINGE;
             else if (lv == "squared" || lv == "squaredloss" || lv == "squared_loss") c.loss = HM_LOSS_SQUARED;
-            else HM_FAIL(HM_ERR_INVALID_ARGUMENT, "option -loss: unknown loss '%s' (logloss, hinge, squared)", v.c_str());
+            else if (lv == "squared_hinge" || lv == "squaredhinge" || lv == "squaredhingeloss") c.loss = HM_LOSS_SQUARED_HINGE;
+            else if (lv == "modified_huber" || lv == "modifiedhuber" || lv == "modifiedhuberloss") c.loss = HM_LOSS_MODIFIED_HUBER;
+            else if (lv == "huber" || lv == "huberloss") c.loss = HM_LOSS_HUBER;
+            else if (lv == "quantile" || lv == "quantileloss") c.loss = HM_LOSS_QUANTILE;
+            else if (lv == "epsilon_insensitive" || lv == "epsiloninsensitive" || lv == "epsiloninsensitiveloss") c.loss = HM_LOSS_EPS_INSENSITIVE;
+            else if (lv == "squared_epsilon_insensitive" || lv == "squaredepsiloninsensitive" || lv == "squaredepsiloninsensitiveloss")
+                c.loss = HM_LOSS_SQUARED_EPS_INSENSITIVE;
+            else HM_FAIL(HM_ERR_INVALID_ARGUMENT, "option -loss: unknown loss '%s' (logloss, hinge, squared_hinge, modified_huber, "
+                         "squared, huber, quantile, epsilon_insensitive, squared_epsilon_insensitive)", v.c_str());
             loss_given = true;
         } else if (name == "-opt" || name == "-optimizer") {
             if (lv == "sgd") c.opt = HM_OPT_SGD;
@@ -277,8 +295,12 @@ hm_status parse_options(const char *function_name, const char *options, hm_confi
     // cross-option checks
     if (task == HM_TASK_CLASSIFIER && c.loss == HM_LOSS_SQUARED && loss_given)
         ;  // allowed: squared loss on +-1 targets
-    if (task == HM_TASK_REGRESSOR && online < 0 && c.loss != HM_LOSS_SQUARED)
-        HM_FAIL(HM_ERR_INVALID_ARGUMENT, "train_regressor supports -loss squared only");
+    const bool regr_loss = c.loss == HM_LOSS_SQUARED || (c.loss >= HM_LOSS_HUBER && c.loss <= HM_LOSS_SQUARED_EPS_INSENSITIVE);
+    if (task == HM_TASK_REGRESSOR && online < 0 && !regr_loss)
+        HM_FAIL(HM_ERR_INVALID_ARGUMENT, "train_regressor takes -loss squared, huber, quantile, epsilon_insensitive or squared_epsilon_insensitive");
+    if (task == HM_TASK_CLASSIFIER && online < 0 && c.loss >= HM_LOSS_HUBER)
+        HM_FAIL(HM_ERR_INVALID_ARGUMENT, "train_classifier takes -loss logloss, hinge, squared_hinge, modified_huber or squared");
+    if (online < 0) c.loss_param = c.loss == HM_LOSS_HUBER ? huber_c : (c.loss == HM_LOSS_QUANTILE ? quantile : 0.0f);
     if (task == HM_TASK_FM && c.opt != HM_OPT_SGD && c.opt != HM_OPT_ADAGRAD)
         HM_FAIL(HM_ERR_INVALID_ARGUMENT, "train_fm supports -opt sgd or adagrad");
     if (task == HM_TASK_FM) c.loss = c.fm_classification ? HM_LOSS_LOG : HM_LOSS_SQUARED;

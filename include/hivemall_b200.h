@@ -55,7 +55,11 @@ enum { HM_LOSS_LOG = 0, HM_LOSS_HINGE = 1, HM_LOSS_SQUARED = 2,
         * reduce-and-step launches, one for the weights and one for the variances */
        HM_LOSS_AROW = 9, HM_LOSS_AROW_REGR = 10, HM_LOSS_AROWE_REGR = 11,
        /* ... and the confidence-weighted family on the same two passes (train_cw, train_scw, train_scw2) */
-       HM_LOSS_CW = 12, HM_LOSS_SCW1 = 13, HM_LOSS_SCW2 = 14 };
+       HM_LOSS_CW = 12, HM_LOSS_SCW1 = 13, HM_LOSS_SCW2 = 14,
+       /* further -loss values of train_classifier (squared hinge, modified Huber) and train_regressor (Huber,
+        * quantile, epsilon-insensitive and its square): plain loss derivatives like the first three */
+       HM_LOSS_SQUARED_HINGE = 15, HM_LOSS_MODIFIED_HUBER = 16, HM_LOSS_HUBER = 17, HM_LOSS_QUANTILE = 18,
+       HM_LOSS_EPS_INSENSITIVE = 19, HM_LOSS_SQUARED_EPS_INSENSITIVE = 20 };
 enum { HM_OPT_SGD = 0, HM_OPT_ADAGRAD = 1, HM_OPT_ADADELTA = 2, HM_OPT_ADAM = 3, HM_OPT_FTRL = 4,
        HM_OPT_COV = 5 /* set by the variance-keeping learners, not by -opt: state = one variance per feature, 1 at the start */ };
 enum { HM_ETA_FIXED = 0, HM_ETA_INVERSE = 1, HM_ETA_SIMPLE = 2 };
@@ -86,7 +90,8 @@ typedef struct hm_config {
     float   pa_epsilon;      /* ... regression: width of the insensitive zone (also train_arowe_regr) */
     float   cov_r;           /* train_arow*: regularisation r of the variance update */
     float   cov_phi;         /* train_cw, train_scw, train_scw2: confidence phi = probit(eta) */
-    int32_t reserved[4];
+    float   loss_param;      /* -loss huber: threshold c (-huber_c, default 1); -loss quantile: tau (-quantile, default 0.5) */
+    int32_t reserved[3];
 } hm_config;
 
 typedef struct hm_udtf hm_udtf; /* opaque learner = one UDTF instance on one GPU */
@@ -132,7 +137,10 @@ hm_status hm_feature_hashing(const uint8_t *bytes, const int64_t *offsets, int64
 
 /* ---- option strings (stands in for the UDTF's getOptions/processOptions) --- */
 
-/* function_name: "train_classifier" | "train_regressor" | "train_fm", or one of the online learners on the
+/* -loss of train_classifier: logloss | hinge | squared_hinge | modified_huber | squared; of train_regressor:
+ * squared | huber (-huber_c, default 1) | quantile (-quantile / -tau, default 0.5) | epsilon_insensitive |
+ * squared_epsilon_insensitive (-epsilon, default 0.1).
+ * function_name: "train_classifier" | "train_regressor" | "train_fm", or one of the online learners on the
  * same skeleton: "train_perceptron" | "train_pa" | "train_pa1" | "train_pa2" (labels as train_classifier) |
  * "train_pa1_regr" | "train_pa2_regr" (targets as train_regressor) | "train_arow" (labels) |
  * "train_arow_regr" | "train_arowe_regr" (targets) | "train_cw" | "train_scw" | "train_scw2" (labels).  Those fix loss, optimizer, eta (1) and regularisation

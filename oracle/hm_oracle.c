@@ -100,10 +100,38 @@ float hmo_dloss(int32_t loss, float m, float y)
     }
 }
 
+static inline int loss_is_pa(int32_t loss) { return loss >= HMO_LOSS_PA && loss <= HMO_LOSS_PA2_REGR; }
+static inline int loss_is_cov(int32_t loss) { return loss >= HMO_LOSS_AROW && loss <= HMO_LOSS_SCW2; }
+
+/* derivative of the further plain losses with respect to the margin */
+static float dloss_more(const hmo_config *c, float m, float y)
+{
+    const int32_t loss = c->loss;
+    const float p = c->loss_param, eps = c->pa_epsilon;
+    if (loss == HMO_LOSS_SQUARED_HINGE) {
+        const float z = y * m;
+        return z < 1.0f ? (-2.0f * y) * (1.0f - z) : 0.0f;
+    }
+    if (loss == HMO_LOSS_MODIFIED_HUBER) {
+        const float z = y * m;
+        if (z >= 1.0f) return 0.0f;
+        if (z >= -1.0f) return (-2.0f * y) * (1.0f - z);
+        return -4.0f * y;
+    }
+    const float e = m - y;
+    if (loss == HMO_LOSS_HUBER) return fabsf(e) <= p ? e : (e < 0.0f ? -p : p);
+    if (loss == HMO_LOSS_QUANTILE) return e < 0.0f ? -p : 1.0f - p;
+    const float a = fabsf(e) - eps;
+    if (!(a > 0.0f)) return 0.0f;
+    if (loss == HMO_LOSS_EPS_INSENSITIVE) return e < 0.0f ? -1.0f : 1.0f;
+    return (e < 0.0f ? -2.0f : 2.0f) * a;
+}
+
 float hmo_row_coef(const hmo_config *c, float m, float y, float xx)
 {
     const int32_t loss = c->loss;
     if (loss <= HMO_LOSS_SQUARED) return hmo_dloss(loss, m, y);
+    if (loss >= HMO_LOSS_SQUARED_HINGE) return dloss_more(c, m, y);
     if (loss == HMO_LOSS_PERCEPTRON) return (y * m <= 0.0f) ? -y : 0.0f;
     float l, dir;
     if (loss == HMO_LOSS_PA1_REGR || loss == HMO_LOSS_PA2_REGR) {
@@ -270,6 +298,14 @@ double hmo_loss(int32_t loss, float m, float y)
     double z = (double)y * (double)m;
     if (loss == HMO_LOSS_PERCEPTRON) return z <= 0.0 ? -z : 0.0;
     if (loss == HMO_LOSS_PA || loss == HMO_LOSS_PA1 || loss == HMO_LOSS_PA2) loss = HMO_LOSS_HINGE;
+    if (loss >= HMO_LOSS_SQUARED_HINGE) {       /* (reporting only; parameters not known here: unit Huber threshold, median, eps 0) */
+        if (loss == HMO_LOSS_SQUARED_HINGE) return z < 1.0 ? (1.0 - z) * (1.0 - z) : 0.0;
+        if (loss == HMO_LOSS_MODIFIED_HUBER) return z >= 1.0 ? 0.0 : (z >= -1.0 ? (1.0 - z) * (1.0 - z) : -4.0 * z);
+        const double e = fabs((double)m - (double)y);
+        if (loss == HMO_LOSS_HUBER) return e <= 1.0 ? 0.5 * e * e : e - 0.5;
+        if (loss == HMO_LOSS_SQUARED_EPS_INSENSITIVE) return e * e;
+        return loss == HMO_LOSS_QUANTILE ? 0.5 * e : e;
+    }
     if (loss == HMO_LOSS_AROW || loss >= HMO_LOSS_CW) loss = HMO_LOSS_HINGE;
     if (loss == HMO_LOSS_AROW_REGR || loss == HMO_LOSS_AROWE_REGR) return fabs((double)y - (double)m);
     if (loss == HMO_LOSS_PA1_REGR || loss == HMO_LOSS_PA2_REGR) return fabs((double)y - (double)m);   /* (epsilon not known here) */
@@ -383,7 +419,7 @@ int hmo_train_linear(const hmo_config *c, int64_t n_rows, const int64_t *rowptr,
                      float *margins, double *loss_sum)
 {
     if (c->mini_batch < 1 || c->dims < 1) return -1;
-    if (c->loss >= HMO_LOSS_AROW) return train_cov(c, n_rows, rowptr, idx, val, label, w, s1, t, margins, loss_sum);
+    if (loss_is_cov(c->loss)) return train_cov(c, n_rows, rowptr, idx, val, label, w, s1, t, margins, loss_sum);
     const int64_t B = c->mini_batch;
     double *gsum = (double *)calloc((size_t)c->dims, sizeof(double));
     uint32_t *cnt = (uint32_t *)calloc((size_t)c->dims, sizeof(uint32_t));
@@ -412,7 +448,7 @@ int hmo_train_linear(const hmo_config *c, int64_t n_rows, const int64_t *rowptr,
                 }
                 float m = (float)acc;
                 float y = target_of(c, label[i]);
-                dl[i - b0] = hmo_row_coef(c, m, y, c->loss >= HMO_LOSS_PA ? row_sqnorm(rowptr, val, i) : 0.0f);
+                dl[i - b0] = hmo_row_coef(c, m, y, loss_is_pa(c->loss) ? row_sqnorm(rowptr, val, i) : 0.0f);
                 lsum += hmo_loss(c->loss, m, y);
                 if (margins) margins[i] = m;
             }
@@ -456,7 +492,7 @@ int hmo_train_linear_mt(const hmo_config *c, int64_t n_rows, const int64_t *rowp
                         float *w, float *s1, float *s2, int64_t *t, int threads)
 {
     if (c->mini_batch < 1 || c->dims < 1 || threads < 1) return -1;
-    if (c->loss >= HMO_LOSS_AROW) return train_cov(c, n_rows, rowptr, idx, val, label, w, s1, t, NULL, NULL);   /* (single thread) */
+    if (loss_is_cov(c->loss)) return train_cov(c, n_rows, rowptr, idx, val, label, w, s1, t, NULL, NULL);   /* (single thread) */
     if (threads > 256) threads = 256;
     const int64_t B = c->mini_batch;
     const int T = threads;
@@ -501,7 +537,7 @@ int hmo_train_linear_mt(const hmo_config *c, int64_t n_rows, const int64_t *rowp
                         my[idx[p] / per_owner + 1]++;
                     }
                     dl[i - b0] = hmo_row_coef(c, (float)acc, target_of(c, label[i]),
-                                              c->loss >= HMO_LOSS_PA ? row_sqnorm(rowptr, val, i) : 0.0f);
+                                              loss_is_pa(c->loss) ? row_sqnorm(rowptr, val, i) : 0.0f);
                 }
                 /* bucket offsets inside this thread's region of `pairs` (region = its element range) */
                 const int64_t base = rowptr[r0] - e0;

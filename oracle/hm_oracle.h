@@ -33,7 +33,11 @@ enum { HMO_LOSS_LOG = 0, HMO_LOSS_HINGE = 1, HMO_LOSS_SQUARED = 2,
        HMO_LOSS_AROW = 9, HMO_LOSS_AROW_REGR = 10, HMO_LOSS_AROWE_REGR = 11,
        /* confidence-weighted (Dredze, Crammer, Pereira, ICML 2008) and soft confidence-weighted learning
         * (Wang, Zhao, Hoi, ICML 2012), diagonal covariance */
-       HMO_LOSS_CW = 12, HMO_LOSS_SCW1 = 13, HMO_LOSS_SCW2 = 14 };
+       HMO_LOSS_CW = 12, HMO_LOSS_SCW1 = 13, HMO_LOSS_SCW2 = 14,
+       /* further plain losses: squared hinge, modified Huber (classification); Huber, quantile (pinball),
+        * epsilon-insensitive and its square (regression) */
+       HMO_LOSS_SQUARED_HINGE = 15, HMO_LOSS_MODIFIED_HUBER = 16, HMO_LOSS_HUBER = 17, HMO_LOSS_QUANTILE = 18,
+       HMO_LOSS_EPS_INSENSITIVE = 19, HMO_LOSS_SQUARED_EPS_INSENSITIVE = 20 };
 enum { HMO_OPT_SGD = 0, HMO_OPT_ADAGRAD = 1, HMO_OPT_ADADELTA = 2, HMO_OPT_ADAM = 3, HMO_OPT_FTRL = 4,
        HMO_OPT_COV = 5 /* the AROW learners: s1 = per-feature variance, 1 at the start (the CALLER fills it) */ };
 enum { HMO_ETA_FIXED = 0, HMO_ETA_INVERSE = 1, HMO_ETA_SIMPLE = 2 };
@@ -64,6 +68,7 @@ typedef struct hmo_config {
     float   pa_epsilon;           /* regression: insensitive zone */
     float   cov_r;                /* AROW: regularisation r */
     float   cov_phi;              /* CW / SCW: confidence phi */
+    float   loss_param;           /* Huber's threshold / the quantile */
 } hmo_config;
 
 /* MurmurHash3_x86_32 (Appleby, public domain algorithm). */

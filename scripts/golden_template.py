@@ -61,8 +61,13 @@ def main(out_dir):
         dump(f"step_{opt}_template.json", {**mark, "function": "train_classifier", "options": options, "dims": dims,
                                             "rows": rows_json(rows), "before": before,
                                             "after": {"t": after["t"], **{k: _golden.sparse(after[k]) for k in ("w", "s1", "s2")}}})
-    # the online learners on the same skeleton: one mini-batch step each
-    for fn, options in (("train_perceptron", f"-mini_batch 16 -dims {dims}"),
+    # the online learners on the same skeleton, the further plain losses (3.3): one mini-batch step each
+    for k, (fn, options) in enumerate((("train_classifier", f"-loss squared_hinge -opt sgd -mini_batch 16 -dims {dims}"),
+                        ("train_classifier", f"-loss modified_huber -opt sgd -mini_batch 16 -dims {dims}"),
+                        ("train_regressor", f"-loss huber -huber_c 0.5 -opt sgd -mini_batch 16 -dims {dims}"),
+                        ("train_regressor", f"-loss quantile -quantile 0.8 -opt sgd -mini_batch 16 -dims {dims}"),
+                        ("train_regressor", f"-loss epsilon_insensitive -epsilon 0.1 -opt sgd -mini_batch 16 -dims {dims}"),
+                        ("train_perceptron", f"-mini_batch 16 -dims {dims}"),
                         ("train_pa", f"-mini_batch 16 -dims {dims}"),
                         ("train_pa1", f"-mini_batch 16 -dims {dims} -c 0.1"),
                         ("train_pa2", f"-mini_batch 16 -dims {dims} -c 0.1"),
@@ -74,12 +79,12 @@ def main(out_dir):
                         ("train_arowe_regr", f"-mini_batch 16 -dims {dims} -r 0.5 -epsilon 0.05"),
                         ("train_cw", f"-mini_batch 16 -dims {dims} -phi 0.5"),
                         ("train_scw", f"-mini_batch 16 -dims {dims} -phi 0.8 -c 0.1"),
-                        ("train_scw2", f"-mini_batch 16 -dims {dims} -c 0.1")):
+                        ("train_scw2", f"-mini_batch 16 -dims {dims} -c 0.1"))):
         first = impl.linear(fn, options, small_rows(16, dims, 1))
         before = {"t": first["t"], **{k: _golden.sparse(first[k]) for k in ("w", "s1", "s2")}}
         rows = small_rows(16, dims, 2)
         after = impl.linear(fn, options, rows, before)
-        dump(f"step_{fn}_template.json", {**mark, "function": fn, "options": options, "dims": dims,
+        dump(f"step_{k:02d}_{fn}_template.json", {**mark, "function": fn, "options": options, "dims": dims,
                                            "rows": rows_json(rows), "before": before,
                                            "after": {"t": after["t"], **{k: _golden.sparse(after[k]) for k in ("w", "s1", "s2")}}})
     v = impl.fm_init("-factors 4 -seed 31 -sigma 0.1", dims)

@@ -21,7 +21,7 @@ class HmoConfig(C.Structure):
         ("alpha", C.c_float), ("beta", C.c_float), ("lambda1", C.c_float), ("lambda2", C.c_float),
         ("factors", C.c_int32), ("fm_classification", C.c_int32), ("sigma", C.c_float),
         ("lambda_w0", C.c_float), ("lambda_w", C.c_float), ("lambda_v", C.c_float),
-        ("seed", C.c_uint32), ("pa_c", C.c_float), ("pa_epsilon", C.c_float), ("cov_r", C.c_float), ("cov_phi", C.c_float),
+        ("seed", C.c_uint32), ("pa_c", C.c_float), ("pa_epsilon", C.c_float), ("cov_r", C.c_float), ("cov_phi", C.c_float), ("loss_param", C.c_float),
     ]
 
 
@@ -91,7 +91,12 @@ def config_from(hm_cfg) -> HmoConfig:
 # the two parsers against each other.
 _ENUMS = {
     "loss": {"logloss": 0, "logistic": 0, "log": 0, "hinge": 1, "hingeloss": 1, "squared": 2, "squaredloss": 2,
-             "squared_loss": 2},
+             "squared_loss": 2,
+             "squared_hinge": 15, "squaredhinge": 15, "squaredhingeloss": 15,
+             "modified_huber": 16, "modifiedhuber": 16, "modifiedhuberloss": 16,
+             "huber": 17, "huberloss": 17, "quantile": 18, "quantileloss": 18,
+             "epsilon_insensitive": 19, "epsiloninsensitive": 19, "epsiloninsensitiveloss": 19,
+             "squared_epsilon_insensitive": 20, "squaredepsiloninsensitive": 20, "squaredepsiloninsensitiveloss": 20},
     "opt": {"sgd": 0, "adagrad": 1, "adadelta": 2, "adam": 3, "ftrl": 4},
     "eta_sched": {"fixed": 0, "inverse": 1, "inv": 1, "invscaling": 1, "simple": 2},
     "reg": {"no": 0, "none": 0, "l1": 1, "l2": 2},
@@ -115,6 +120,7 @@ _OPTION_FIELDS = {
     "-hash_seed": (None, int), "-mix_interval": (None, int),     # not oracle fields
     "-aggressiveness": ("pa_c", float), "-epsilon": ("pa_epsilon", float), "-e": ("pa_epsilon", float),
     "-r": ("cov_r", float), "-phi": ("cov_phi", float),
+    "-huber_c": ("_huber_c", float), "-quantile": ("_quantile", float), "-tau": ("_quantile", float),
 }
 # online learners on the mini-batch skeleton: function -> (task, loss id)
 _ONLINE = {"train_perceptron": (0, 3), "train_pa": (0, 4), "train_pa1": (0, 5), "train_pa2": (0, 6),
@@ -135,7 +141,8 @@ def config_from_options(function_name: str, options: str = "") -> HmoConfig:
     takes_phi = bool(online) and online[1] >= 12
     c = HmoConfig()
     c.task = task
-    c.pa_c, c.pa_epsilon, c.cov_r, c.cov_phi = 1.0, 0.1, 0.1, 1.0
+    c.pa_c, c.pa_epsilon, c.cov_r, c.cov_phi, c.loss_param = 1.0, 0.1, 0.1, 1.0, 0.0
+    extra = {"_huber_c": 1.0, "_quantile": 0.5}
     c.loss = 2 if task == 1 else 0
     c.opt = 0 if task == 2 else 1
     c.eta_sched, c.reg, c.grad_norm, c.mini_batch, c.iters = 0, 0, 0, 1, 1
@@ -163,8 +170,10 @@ def config_from_options(function_name: str, options: str = "") -> HmoConfig:
             raise ValueError(f"{name} is fixed by {function_name}")
         if name in ("-c", "-aggressiveness") and not takes_c:
             raise ValueError(f"{name} is an option of train_pa1, train_pa2, their _regr forms, train_scw and train_scw2")
-        if name in ("-epsilon", "-e") and not takes_eps:
+        if name in ("-epsilon", "-e") and not takes_eps and not (not online and task == 1):
             raise ValueError(f"{name} is an option of train_pa1_regr, train_pa2_regr and train_arowe_regr")
+        if name in ("-huber_c", "-quantile", "-tau") and (online or task == 2):
+            raise ValueError(f"{name} goes with -loss huber / quantile")
         if name == "-phi" and not takes_phi:
             raise ValueError("-phi is an option of train_cw, train_scw and train_scw2")
         if name == "-r" and not takes_r:
@@ -180,6 +189,9 @@ def config_from_options(function_name: str, options: str = "") -> HmoConfig:
         i += 1
         if field is None:
             continue
+        if field.startswith("_"):
+            extra[field] = float(v)
+            continue
         if kind == "enum":
             table = _ENUMS[field]
             if v.lower() not in table:
@@ -187,8 +199,12 @@ def config_from_options(function_name: str, options: str = "") -> HmoConfig:
             setattr(c, field, table[v.lower()])
         else:
             setattr(c, field, kind(v))
-    if task == 1 and not online and c.loss != 2:
-        raise ValueError("train_regressor supports -loss squared only")
+    if task == 1 and not online and c.loss not in (2, 17, 18, 19, 20):
+        raise ValueError("train_regressor takes -loss squared, huber, quantile, epsilon_insensitive or squared_epsilon_insensitive")
+    if task == 0 and not online and c.loss >= 17:
+        raise ValueError("train_classifier takes -loss logloss, hinge, squared_hinge, modified_huber or squared")
+    if not online:
+        c.loss_param = extra["_huber_c"] if c.loss == 17 else (extra["_quantile"] if c.loss == 18 else 0.0)
     if task == 2:
         c.loss = 0 if c.fm_classification else 2
         c.task = 1          # (as config_from: the FM entry points do not read it)

@@ -268,3 +268,26 @@ def test_one_mini_batch_larger_than_the_block_cap():
     assert_weights_close(u.array_to_host("w"), ref.w)
     assert_weights_close(u.array_to_host("state"), ref.s1, "state")
     u.destroy()
+
+
+@pytest.mark.parametrize("fn,loss", [("train_classifier", "squared_hinge"), ("train_classifier", "modified_huber"),
+                                     ("train_regressor", "huber -huber_c 0.5"), ("train_regressor", "quantile -quantile 0.8"),
+                                     ("train_regressor", "epsilon_insensitive -epsilon 0.1"),
+                                     ("train_regressor", "squared_epsilon_insensitive -epsilon 0.1")])
+def test_further_losses_on_the_hot_path(fn, loss):
+    """The further plain losses through the launch shape of the headline in small: Criteo-shaped rows, 4096-row
+    mini-batches, hot features reduced in the forward kernel, several pushes."""
+    import torch
+    dims = 1 << 18
+    data = synth.criteo_like(3 * 4096 + 99, dims=dims, seed=21)
+    if fn == "train_regressor":
+        rng = np.random.default_rng(4)
+        data.label = data.label * 2.0 + torch.from_numpy(rng.normal(0, 0.5, data.rows).astype(np.float32))
+    options = f"-loss {loss} -opt adagrad -mini_batch 4096 -dims {dims} -eta0 0.05"
+    u, w, state = run_gpu_linear(fn, options, data, pushes=[5000, 8000])
+    assert len(u.hot_features()) >= 13
+    ref, ref_state = run_oracle_linear(fn, options, data)
+    assert_weights_close(w, ref.w)
+    assert_weights_close(state, ref_state, "state")
+    assert np.count_nonzero(ref.w) > 1000
+    u.destroy()

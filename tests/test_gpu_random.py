@@ -119,6 +119,38 @@ def draw_online_case(seed: int):
     return fn, " ".join(o for o in opts if o), dims, rows, max_nnz, pushes, regression
 
 
+def draw_loss_case(seed: int):
+    r = np.random.default_rng(9000 + seed)
+    losses = [("train_classifier", "squared_hinge", ""), ("train_classifier", "modified_huber", ""),
+              ("train_regressor", "huber", f"-huber_c {r.choice([0.1, 1.0, 3.0])}"),
+              ("train_regressor", "quantile", f"-quantile {r.choice([0.1, 0.5, 0.9])}"),
+              ("train_regressor", "epsilon_insensitive", f"-epsilon {r.choice([0.0, 0.1, 0.5])}"),
+              ("train_regressor", "squared_epsilon_insensitive", f"-epsilon {r.choice([0.0, 0.1, 0.5])}")]
+    fn, loss, extra = losses[seed % len(losses)]
+    opt = r.choice(["sgd", "adagrad", "adadelta", "adam", "ftrl"])
+    dims = int(r.choice([17, 300, 5000, (1 << 17) + 1]))
+    rows = int(r.integers(1, 5000))
+    mb = int(r.choice([1, 7, 64, 333, 1024, 2500]))
+    if mb == 1:
+        rows = min(rows, 300)
+    opts = [f"-loss {loss}", extra, f"-opt {opt}", f"-mini_batch {mb}", f"-dims {dims}", f"-eta0 {r.choice([0.01, 0.05])}",
+            f"-grad_norm {r.choice(['batch', 'count', 'sum'])}"]
+    return fn, " ".join(o for o in opts if o), dims, rows, int(r.choice([1, 3, 20, 60]))
+
+
+@pytest.mark.parametrize("seed", range(24))
+def test_random_further_losses_match_the_oracle(seed):
+    """squared hinge, modified Huber, Huber, quantile, epsilon-insensitive and its square with every optimizer."""
+    fn, options, dims, rows, max_nnz = draw_loss_case(seed)
+    data = synth.ragged(rows, dims, max_nnz, seed=900 + seed, regression=(fn == "train_regressor"))
+    u, w, state = run_gpu_linear(fn, options, data)
+    ref, ref_state = run_oracle_linear(fn, options, data)
+    assert u.step == ref.t, options
+    assert_weights_close(w, ref.w, f"w [{fn} {options}]")
+    assert_weights_close(state, ref_state, f"state [{fn} {options}]")
+    u.destroy()
+
+
 @pytest.mark.parametrize("seed", range(36))
 def test_random_online_learner_matches_the_oracle(seed):
     """The online learners (perceptron, passive-aggressive, AROW, CW, SCW) under the same randomised shapes:

@@ -43,6 +43,12 @@ def test_numeric_options_round_trip():
     ("train_classifier", "loss logloss"),
     ("train_classifier", "-factors 4"),
     ("train_regressor", "-loss logloss"),
+    ("train_regressor", "-loss squared_hinge"),
+    ("train_classifier", "-loss huber"),
+    ("train_classifier", "-loss quantile"),
+    ("train_classifier", "-epsilon 0.1"),
+    ("train_regressor", "-quantile 1.5"),
+    ("train_pa1", "-huber_c 1"),
     ("train_fm", "-opt adam"),
     ("train_fm", "-loss logloss"),
     ("train_everything", ""),
@@ -98,6 +104,12 @@ def test_error_names_the_offending_token():
     ("train_cw", "-phi 0.7 -mini_batch 16"),
     ("train_scw", "-phi 1.2 -c 0.5"),
     ("train_scw2", ""),
+    ("train_classifier", "-loss squared_hinge -opt sgd"),
+    ("train_classifier", "-loss ModifiedHuber"),
+    ("train_regressor", "-loss huber -huber_c 0.7"),
+    ("train_regressor", "-loss quantile -tau 0.9 -mini_batch 32"),
+    ("train_regressor", "-loss epsilon_insensitive -epsilon 0.3"),
+    ("train_regressor", "-loss squared_epsilon_insensitive"),
 ])
 def test_oracle_side_parser_agrees_with_the_library(fn, opts):
     """bench.py's CPU arm builds its oracle config with tests/_oracle.config_from_options so that its
@@ -130,3 +142,14 @@ def test_variance_keeping_learner_functions():
         c = hm.parse_options(fn, "")
         assert (c.task, c.loss, c.opt, c.cov_phi, c.pa_c) == (0, loss, 5, 1.0, 1.0), fn
     assert hm.parse_options("train_scw", "-phi 0.5 -c 0.25").cov_phi == 0.5
+
+
+def test_further_plain_losses():
+    c = hm.parse_options("train_regressor", "-loss huber")
+    assert (c.loss, c.loss_param) == (17, 1.0)
+    c = hm.parse_options("train_regressor", "-loss quantile")
+    assert (c.loss, c.loss_param) == (18, 0.5)
+    c = hm.parse_options("train_regressor", "-loss epsilon_insensitive -epsilon 0.25")
+    assert (c.loss, c.pa_epsilon, c.loss_param) == (19, 0.25, 0.0)
+    assert hm.parse_options("train_classifier", "-loss squaredhinge").loss == 15
+    assert hm.parse_options("train_classifier", "-loss modified_huber").loss == 16

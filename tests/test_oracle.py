@@ -73,12 +73,37 @@ def np_dloss(loss, m, y):
     return F(m - y)
 
 
+def np_dloss_more(cfg, m, y):
+    """squared hinge, modified Huber; Huber, quantile, epsilon-insensitive and its square."""
+    loss, p, eps = cfg.loss, F(cfg.loss_param), F(cfg.pa_epsilon)
+    if loss in (15, 16):
+        z = F(y * m)
+        if loss == 15:
+            return F(F(F(-2.0) * y) * F(F(1.0) - z)) if z < 1 else F(0.0)
+        if z >= 1:
+            return F(0.0)
+        return F(F(F(-2.0) * y) * F(F(1.0) - z)) if z >= -1 else F(F(-4.0) * y)
+    e = F(m - y)
+    if loss == 17:
+        return e if abs(e) <= p else (F(-p) if e < 0 else p)
+    if loss == 18:
+        return F(-p) if e < 0 else F(F(1.0) - p)
+    a = F(abs(e) - eps)
+    if not a > 0:
+        return F(0.0)
+    if loss == 19:
+        return F(-1.0) if e < 0 else F(1.0)
+    return F((F(-2.0) if e < 0 else F(2.0)) * a)
+
+
 def np_row_coef(cfg, m, y, xx):
     """The per-row coefficient for any loss id: the loss derivative, or the online learner's signed step
     (perceptron; passive-aggressive PA / PA-I / PA-II, Crammer et al. 2006, classification and regression)."""
     loss = cfg.loss
     if loss <= 2:
         return np_dloss(loss, m, y)
+    if loss >= 15:
+        return np_dloss_more(cfg, m, y)
     if loss == 3:
         return F(-y) if F(y * m) <= F(0.0) else F(0.0)
     if loss in (7, 8):
@@ -187,7 +212,7 @@ def np_train_cov(cfg, rowptr, feat, val, label):
 
 
 def np_train(cfg, rowptr, feat, val, label):
-    if cfg.loss >= 9:
+    if 9 <= cfg.loss <= 14:
         return np_train_cov(cfg, rowptr, feat, val, label)
     D, B = int(cfg.dims), int(cfg.mini_batch)
     w = np.zeros(D, F); s1 = np.zeros(D, F); s2 = np.zeros(D, F)
@@ -269,6 +294,13 @@ def np_train(cfg, rowptr, feat, val, label):
     ("-loss logloss -opt adam -mini_batch 6 -dims 50 -eta0 0.05 -iters 3", "train_classifier"),
     ("-loss squared -opt adam -mini_batch 10 -dims 50 -eta0 0.01 -beta1 0.8 -beta2 0.99 -eta simple -total_steps 30", "train_regressor"),
     ("-loss hinge -opt sgd -mini_batch 7 -dims 50 -reg l1 -lambda 0.01 -eta0 0.3", "train_classifier"),
+    # the further plain losses
+    ("-loss squared_hinge -opt adagrad -mini_batch 7 -dims 50 -iters 2", "train_classifier"),
+    ("-loss modified_huber -opt sgd -mini_batch 5 -dims 50 -eta0 0.3 -iters 2", "train_classifier"),
+    ("-loss huber -huber_c 0.3 -opt adagrad -mini_batch 9 -dims 50", "train_regressor"),
+    ("-loss quantile -quantile 0.8 -opt sgd -mini_batch 6 -dims 50 -eta0 0.05", "train_regressor"),
+    ("-loss epsilon_insensitive -epsilon 0.2 -opt adam -mini_batch 8 -dims 50 -eta0 0.01", "train_regressor"),
+    ("-loss squared_epsilon_insensitive -epsilon 0.05 -opt ftrl -mini_batch 4 -dims 50", "train_regressor"),
     # online learners on the same skeleton
     ("-mini_batch 1 -dims 50 -iters 2", "train_perceptron"),
     ("-mini_batch 6 -dims 50", "train_perceptron"),
