@@ -106,3 +106,35 @@ def test_malformed_files_are_argument_errors(tmp_path):
     w = u.array_to_host("w")
     assert w[3] == np.float32(0.5) and w[10] == np.float32(-1.25e-3) and np.count_nonzero(w) == 2
     u.destroy()
+
+
+def test_online_learners_tables(tmp_path):
+    """The passive-aggressive learners have no optimizer slots: train -> save -> load -> continue is exact.  The
+    variance-keeping learners save their weights; a fresh learner that loads them starts from variance 1 again,
+    and the variances of a run can be carried over as array `state`, after which continuing is exact too."""
+    dims, mb = 1 << 14, 512
+    data = synth.criteo_like(6 * mb, dims=dims, seed=9)
+    rp, f, v, y = data.numpy()
+    cut = 4 * mb
+    for fn, opts in (("train_pa1", f"-mini_batch {mb} -dims {dims} -c 0.1"), ("train_arow", f"-mini_batch {mb} -dims {dims} -r 1")):
+        whole = hm.UDTF(opts, 0, function_name=fn)
+        whole.process_batch(rp, f, v, y)
+        whole.close()
+        first = hm.UDTF(opts, 0, function_name=fn)
+        first.process_batch(rp[: cut + 1], f, v, y[:cut])
+        path = str(tmp_path / f"{fn}.tsv")
+        n = first.save_model_table(path)
+        second = hm.UDTF(opts, 0, function_name=fn)
+        assert second.load_model_table(path) == n > 100
+        assert np.array_equal(second.array_to_host("w"), first.array_to_host("w"))
+        if fn == "train_arow":
+            assert (second.array_to_host("state") == 1.0).all()
+            second.array_from_host("state", first.array_to_host("state"))
+        second.step = first.step
+        second.process_batch(rp[cut:] - rp[cut], f[rp[cut]:], v[rp[cut]:], y[cut:])
+        second.close()
+        assert np.array_equal(second.array_to_host("w"), whole.array_to_host("w")), fn
+        if fn == "train_arow":
+            assert np.array_equal(second.array_to_host("state"), whole.array_to_host("state"))
+        for u in (whole, first, second):
+            u.destroy()
