@@ -284,6 +284,13 @@ def cpu_baseline(rows: int, threads: int, workload: str = "ftrl", mini_batch: in
         _oracle.train_fm(cfg, rowptr, feature, value, label)
         dt = time.perf_counter() - t0
         what = "hmo_train_fm (scalar)"
+    elif 9 <= cfg.loss <= 14:
+        # the variance-keeping learners: the oracle's loop for them is single-threaded (hmo_train_linear_mt falls back to it)
+        threads = 1
+        t0 = time.perf_counter()
+        _oracle.train_linear_mt(cfg, rowptr, feature, value, label, 1)
+        dt = time.perf_counter() - t0
+        what = "train_cov (scalar)"
     else:
         t0 = time.perf_counter()
         _oracle.train_linear_mt(cfg, rowptr, feature, value, label, threads)
