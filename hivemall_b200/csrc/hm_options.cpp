@@ -58,6 +58,35 @@ static bool to_i(const std::string &v, int64_t *out)
     return true;
 }
 
+// Inverse of the standard normal distribution function (P. J. Acklam's rational approximation, relative
+// error < 1.2e-9), in double: the confidence-weighted learners' -eta (a probability in (0.5, 1)) becomes
+// phi = probit(eta).  tests/_oracle.py restates it with the same operations.
+static double probit(double p)
+{
+    static const double a[6] = {-3.969683028665376e+01, 2.209460984245205e+02, -2.759285104469687e+02,
+                                1.383577518672690e+02, -3.066479806614716e+01, 2.506628277459239e+00};
+    static const double b[5] = {-5.447609879822406e+01, 1.615858368580409e+02, -1.556989798598866e+02,
+                                6.680131188771972e+01, -1.328068155288572e+01};
+    static const double c[6] = {-7.784894002430293e-03, -3.223964580411365e-01, -2.400758277161838e+00,
+                                -2.549732539343734e+00, 4.374664141464968e+00, 2.938163982698783e+00};
+    static const double d[4] = {7.784695709041462e-03, 3.224671290700398e-01, 2.445134137142996e+00,
+                                3.754408661907416e+00};
+    const double plow = 0.02425, phigh = 1.0 - plow;
+    if (p < plow) {
+        const double q = std::sqrt(-2.0 * std::log(p));
+        return (((((c[0] * q + c[1]) * q + c[2]) * q + c[3]) * q + c[4]) * q + c[5]) /
+               ((((d[0] * q + d[1]) * q + d[2]) * q + d[3]) * q + 1.0);
+    }
+    if (p > phigh) {
+        const double q = std::sqrt(-2.0 * std::log(1.0 - p));
+        return -(((((c[0] * q + c[1]) * q + c[2]) * q + c[3]) * q + c[4]) * q + c[5]) /
+               ((((d[0] * q + d[1]) * q + d[2]) * q + d[3]) * q + 1.0);
+    }
+    const double q = p - 0.5, r = q * q;
+    return (((((a[0] * r + a[1]) * r + a[2]) * r + a[3]) * r + a[4]) * r + a[5]) * q /
+           (((((b[0] * r + b[1]) * r + b[2]) * r + b[3]) * r + b[4]) * r + 1.0);
+}
+
 static void defaults(hm_config *c, int task)
 {
     std::memset(c, 0, sizeof(*c));
@@ -177,6 +206,10 @@ hm_status parse_options(const char *function_name, const char *options, hm_confi
         };
 #define NEED_F(lo, hi) if (!need_f((lo), (hi))) return HM_ERR_INVALID_ARGUMENT
 #define NEED_I(lo, hi) if (!need_i((lo), (hi))) return HM_ERR_INVALID_ARGUMENT
+        if (takes_phi && name == "-eta") {       // the confidence as a probability: phi = probit(eta)
+            NEED_F(0.5000001, 0.9999999); c.cov_phi = (float)probit(d);
+            continue;
+        }
         if (online >= 0 && (name == "-loss" || name == "-loss_function" || name == "-opt" || name == "-optimizer" ||
                             name == "-eta" || name == "-eta0" || name == "-eta_0" || name == "-power_t" ||
                             name == "-total_steps" || name == "-t" || name == "-reg" || name == "-regularization" ||

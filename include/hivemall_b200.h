@@ -147,7 +147,7 @@ hm_status hm_feature_hashing(const uint8_t *bytes, const int64_t *offsets, int64
  * (none) themselves and take -mini_batch, -iters, -dims, -grad_norm, -mix_interval, -hash_seed, plus
  * -c / -aggressiveness (train_pa1, train_pa2, train_pa*_regr; default 1), -epsilon / -e (train_pa*_regr,
  * train_arowe_regr; default 0.1), -r (train_arow*; default 0.1) and -phi (train_cw, train_scw, train_scw2;
- * default 1; train_scw and train_scw2 also take -c).
+ * default 1; or -eta, a probability in (0.5, 1), with phi = probit(eta); train_scw and train_scw2 also take -c).
  * Unknown options, missing values and out-of-range numbers are
  * HM_ERR_INVALID_ARGUMENT with the offending token in hm_last_error(). */
 hm_status hm_parse_options(const char *function_name, const char *options, hm_config *out);

@@ -131,6 +131,32 @@ _ONLINE_FIXED = {"-loss", "-loss_function", "-opt", "-optimizer", "-eta", "-eta0
                  "-t", "-reg", "-regularization", "-lambda"}
 
 
+def _probit(p: float) -> float:
+    """Acklam's approximation of the inverse normal distribution function, the operations of hm_options.cpp."""
+    import math
+    a = (-3.969683028665376e+01, 2.209460984245205e+02, -2.759285104469687e+02, 1.383577518672690e+02,
+         -3.066479806614716e+01, 2.506628277459239e+00)
+    b = (-5.447609879822406e+01, 1.615858368580409e+02, -1.556989798598866e+02, 6.680131188771972e+01,
+         -1.328068155288572e+01)
+    c = (-7.784894002430293e-03, -3.223964580411365e-01, -2.400758277161838e+00, -2.549732539343734e+00,
+         4.374664141464968e+00, 2.938163982698783e+00)
+    d = (7.784695709041462e-03, 3.224671290700398e-01, 2.445134137142996e+00, 3.754408661907416e+00)
+    plow = 0.02425
+    phigh = 1.0 - plow
+    if p < plow:
+        q = math.sqrt(-2.0 * math.log(p))
+        return (((((c[0] * q + c[1]) * q + c[2]) * q + c[3]) * q + c[4]) * q + c[5]) / \
+               ((((d[0] * q + d[1]) * q + d[2]) * q + d[3]) * q + 1.0)
+    if p > phigh:
+        q = math.sqrt(-2.0 * math.log(1.0 - p))
+        return -(((((c[0] * q + c[1]) * q + c[2]) * q + c[3]) * q + c[4]) * q + c[5]) / \
+               ((((d[0] * q + d[1]) * q + d[2]) * q + d[3]) * q + 1.0)
+    q = p - 0.5
+    r = q * q
+    return (((((a[0] * r + a[1]) * r + a[2]) * r + a[3]) * r + a[4]) * r + a[5]) * q / \
+           (((((b[0] * r + b[1]) * r + b[2]) * r + b[3]) * r + b[4]) * r + 1.0)
+
+
 def config_from_options(function_name: str, options: str = "") -> HmoConfig:
     """Oracle config of a UDTF option string (no product code involved)."""
     online = _ONLINE.get(function_name)
@@ -165,6 +191,15 @@ def config_from_options(function_name: str, options: str = "") -> HmoConfig:
             c.fm_classification = 1
             continue
         if name in ("-dense", "-densemodel"):
+            continue
+        if takes_phi and name == "-eta":
+            if i >= len(tok):
+                raise ValueError("option '-eta' needs a value")
+            eta = float(tok[i])
+            i += 1
+            if not 0.5000001 <= eta <= 0.9999999:
+                raise ValueError("option -eta: a probability in (0.5, 1)")
+            c.cov_phi = _probit(eta)
             continue
         if online and name in _ONLINE_FIXED:
             raise ValueError(f"{name} is fixed by {function_name}")

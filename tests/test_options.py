@@ -68,6 +68,8 @@ def test_numeric_options_round_trip():
     ("train_cw", "-c 1"),                       # plain CW has no aggressiveness
     ("train_cw", "-r 1"),
     ("train_scw", "-phi 0"),
+    ("train_cw", "-eta 0.5"),                   # a probability strictly above one half
+    ("train_cw", "-eta fixed"),
     ("train_arow", "-phi 1"),
     ("train_classifier", "-eta0 nan"),
     ("train_classifier", "-dims -5"),
@@ -104,6 +106,9 @@ def test_error_names_the_offending_token():
     ("train_cw", "-phi 0.7 -mini_batch 16"),
     ("train_scw", "-phi 1.2 -c 0.5"),
     ("train_scw2", ""),
+    ("train_cw", "-eta 0.85"),
+    ("train_scw", "-eta 0.99 -c 0.5"),
+    ("train_scw2", "-eta 0.51"),
     ("train_classifier", "-loss squared_hinge -opt sgd"),
     ("train_classifier", "-loss ModifiedHuber"),
     ("train_regressor", "-loss huber -huber_c 0.7"),
@@ -153,3 +158,12 @@ def test_further_plain_losses():
     assert (c.loss, c.pa_epsilon, c.loss_param) == (19, 0.25, 0.0)
     assert hm.parse_options("train_classifier", "-loss squaredhinge").loss == 15
     assert hm.parse_options("train_classifier", "-loss modified_huber").loss == 16
+
+
+def test_confidence_as_a_probability():
+    """-eta of the confidence-weighted learners is a probability: phi = probit(eta)."""
+    from scipy.stats import norm
+    for eta in (0.51, 0.7, 0.85, 0.975, 0.999):
+        phi = hm.parse_options("train_cw", f"-eta {eta}").cov_phi
+        assert abs(phi - norm.ppf(eta)) < 1e-6 * max(1.0, norm.ppf(eta))
+    assert abs(hm.parse_options("train_scw", "-eta 0.975").cov_phi - 1.959964) < 1e-5
